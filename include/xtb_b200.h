@@ -1,0 +1,170 @@
+/*
+ * xtb_b200.h -- C ABI of the B200-native tight-binding hot path (XTANT-3 graft).
+ *
+ * This is the drop-in boundary for the per-MD-step path
+ *     neighbour list -> radial tables -> H/S block assembly -> [eigensolve, outside]
+ *     -> rho = C f C^T, rho_E = C (f E) C^T -> Hellmann-Feynman forces (+ supercell force)
+ * of the reference Fortran code.  The reference has no FFI of its own (plain module
+ * procedures on derived types), so each entry point below names the reference
+ * procedure it replaces (file:line under Source_files/ of N-Medvedev/XTANT-3).
+ * The Fortran-side ISO_C_BINDING stub that forwards to these symbols is
+ * xtant-3_b200/fortran/xtant_b200_shim.f90 and is described in INTEGRATION.md.
+ *
+ * Conventions
+ *  - every array is Fortran column-major, FP64 (real(8)) or int32 (default integer);
+ *  - atom / kind indices in arguments and list outputs are 1-based, as in the reference;
+ *  - a NULL output pointer means "keep the result on the device only";
+ *  - host arrays are owned by the caller; nothing is retained past the call;
+ *  - return value 0 = ok, otherwise an XTB_E* code; text via xtb_last_error()
+ *    (the Fortran shim maps non-zero to Save_error_details(Err, 6, text), Objects.f90:1309);
+ *  - one caller thread per context (the reference calls this path from the master
+ *    thread only, TB.f90:227-272); contexts are independent.
+ *  - there is NO CPU fallback: without a CUDA device xtb_create fails with XTB_ENODEV.
+ */
+#ifndef XTB_B200_H
+#define XTB_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XTB_OK        0
+#define XTB_EINVAL    1   /* bad argument / call order */
+#define XTB_ENODEV    2   /* no usable CUDA device */
+#define XTB_ECUDA     3   /* CUDA runtime error (text has the detail) */
+#define XTB_ENOMEM    4   /* device allocation failed */
+#define XTB_ECAPACITY 5   /* neighbour capacity exceeded */
+#define XTB_ESTATE    6   /* stage called before its inputs exist */
+
+/* TB parametrisation kinds; mirrors the `select type` arms of TB.f90:247-317,459-487 */
+#define XTB_TB_NONE     0
+#define XTB_TB_NRL      1   /* type is (TB_H_NRL)      spd, non-orthogonal, 9 orbitals/atom */
+#define XTB_TB_PETTIFOR 2   /* type is (TB_H_Pettifor) sp3, orthogonal,     4 orbitals/atom */
+#define XTB_TB_DFTB     3   /* type is (TB_H_DFTB)     s/sp3/sp3d5 tables,  1/4/9 orbitals/atom */
+
+/* type(TB_H_NRL), Objects.f90:190-200; file order of the 10 channels is
+ * ss,sp,pp_sigma,pp_pi,sd,pd_sigma,pd_pi,dd_sigma,dd_pi,dd_delta (Read_input_data.f90:4075-4150) */
+typedef struct xtb_nrl_pair {
+    int32_t ind_split;     /* 1: eg on-site uses set 4, else set 3 */
+    int32_t ind_overlap;   /* 1: overlap radial form Eq.(23) with delta(l,l') */
+    double  lambd;         /* embedded-density exponent */
+    double  Rc, lden;      /* cut-off radius [bohr], screening length */
+    double  al[4], bl[4], cl[4], dl[4];
+    double  ellm[10], fllm[10], gllm[10], hllm[10];
+    double  pllm[10], qllm[10], rllm[10], sllm[10];
+} xtb_nrl_pair;
+
+/* type(TB_H_Pettifor), Objects.f90:170-174 */
+typedef struct xtb_pettifor_pair {
+    double Es, Ep;
+    double nc[4], rc[4], c0[4], c1[4], c2[4], c3[4], V0[4];
+    double r0, n, r1, rm;
+} xtb_pettifor_pair;
+
+/* type(TB_H_DFTB), Objects.f90:202-222 -- tables flattened, one entry per (KOA1,KOA2) */
+typedef struct xtb_dftb_pair {
+    double  rcut, d;          /* Fermi-like cut-off [A] */
+    double  Ed, Ep, Es;       /* on-site energies [eV] (of kind KOA1) */
+    int32_t n_r;              /* radial grid points */
+    int32_t pad_;
+    const double* Rr;         /* [n_r]     radial grid [A], uniform, Rr[0] = dr */
+    const double* Vr;         /* [n_r*10]  column-major (ir, channel) [eV] */
+    const double* Sr;         /* [n_r*10]  overlaps */
+} xtb_dftb_pair;
+
+typedef struct xtb_ctx xtb_ctx;
+
+/* ---- life cycle ------------------------------------------------------------------- */
+int  xtb_create (xtb_ctx** out, int device_ordinal);
+int  xtb_destroy(xtb_ctx* ctx);
+const char* xtb_last_error(const xtb_ctx* ctx);
+const char* xtb_version(void);
+/* run all kernels of this context on `cuda_stream` (a cudaStream_t); default: own stream */
+int  xtb_set_stream(xtb_ctx* ctx, void* cuda_stream);
+int  xtb_sync(xtb_ctx* ctx);
+
+/* ---- parameters: flattening of Scell%TB_Hamil(:,:) (TB.f90:459-487) ---------------- */
+/* p[(koa1-1) + n_kinds*(koa2-1)] = TB_Hamil(koa1,koa2) */
+int  xtb_set_params_nrl     (xtb_ctx*, int n_kinds, const xtb_nrl_pair* p);
+int  xtb_set_params_pettifor(xtb_ctx*, int n_kinds, const xtb_pettifor_pair* p);
+int  xtb_set_params_dftb    (xtb_ctx*, int n_kinds, int n_orb /*1,4,9*/, const xtb_dftb_pair* p);
+
+/* ---- system: MDAtoms(:)%KOA, %S and Scell%supce (Objects.f90:552-581,692-845) ------ */
+int  xtb_set_system(xtb_ctx*, int na, const int32_t* koa /*[na], 1-based*/,
+                    const double* S /*[3*na] relative coords*/, const double supce[9] /*(3,3) col-major*/);
+/* rows (atoms, 1-based inclusive range) this context owns in a multi-GPU run; default all.
+ * Replaces the round-robin split `do i = 1+rank, N, nranks` of the MPI build (TB_NRL.f90:267-327). */
+int  xtb_set_partition(xtb_ctx*, int atom_first, int atom_last);
+
+/* ---- S1: get_near_neighbours -> Find_nearest_neighbours (Atomic_tools.f90:562,4230;
+ *      minimum image = shortest_distance_OLD :4028-4131).  rm_angstrom <= 0: derive the
+ *      cut-off from the parameters exactly as get_near_neighbours does (:574-586).
+ *      Dense outputs have the reference shapes:
+ *        nn_size(na), nn_list(na,na), nn_dist(na,na,4), nn_dist_s(na,na,3); unused = 0 / 1d8 / untouched. */
+int  xtb_neighbours(xtb_ctx*, double rm_angstrom, int32_t* nn_size, int32_t* nn_list,
+                    double* nn_dist, double* nn_dist_s);
+/* compact (ELL) copy: list[k + cap*(i-1)], dist[c + 4*(k + cap*(i-1))], dist_s[c + 3*(...)] */
+int  xtb_neighbours_compact(xtb_ctx*, int cap, int32_t* nn_size, int32_t* nn_list,
+                            double* nn_dist, double* nn_dist_s, int* max_nn_out);
+
+/* ---- S2a: Construct_M_x1 (TB.f90:3430) and Construct_Vij_NRL (TB_NRL.f90:1956,2116) /
+ *      Construct_M_Vs (TB_Pettifor.f90:227) / Construct_Vij_DFTB (TB_DFTB.f90:56).
+ *      Dense outputs M_V*(na,na,nv), M_lmn/M_x1/M_xrr(3,na,na); any may be NULL. */
+int  xtb_radial(xtb_ctx*, double* M_Vij, double* M_dVij, double* M_SVij, double* M_dSVij,
+                double* M_lmn, double* M_x1, double* M_xrr);
+
+/* ---- S2b: Hamil_tot_NRL assembly part (TB_NRL.f90:226-397) / Hamil_tot (TB_Pettifor.f90:1658)
+ *      / Hamil_tot_DFTB (TB_DFTB.f90:319): dense H_non [eV] and Sij, (N,N), N = na*n_orb.
+ *      S may be NULL for orthogonal parametrisations.  In a partitioned run only the column
+ *      panels of the owned atoms are written (host copies cover the same panels). */
+int  xtb_assemble_HS(xtb_ctx*, double* H_non, double* Sij);
+
+/* ---- eigensolve boundary (outside the graft): Scell%Ha(N,N) (column n = state n),
+ *      Scell%Ei(N) [eV], Scell%fe(N) (occupations incl. spin factor).  *_device: pointers
+ *      are device memory that stays valid until the next xtb_set_eigen* call (zero copy). */
+int  xtb_set_eigen       (xtb_ctx*, const double* Ha, const double* Ei, const double* fe);
+int  xtb_set_eigen_device(xtb_ctx*, const double* dHa, const double* dEi, const double* dfe);
+
+/* ---- S3: Construct_Aij (TB.f90:4328) and Construct_Aij_x_En (TB.f90:4401).
+ *      Computed on the neighbour pattern only (every consumer reads only those blocks,
+ *      TB.f90:250-299,5544-5573); dense outputs (N,N) are zero outside the pattern.
+ *      f_cut: states with fe(n) <= f_cut are skipped (0 = bit-safe: only exact zeros). */
+int  xtb_density(xtb_ctx*, double* Aij, double* Aij_x_Ei);
+int  xtb_set_density_cutoff(xtb_ctx*, double f_cut);
+
+/* ---- S4: get_dHij_drij_NRL (TB_NRL.f90:2412) / dHij_s (TB_Pettifor.f90:141) /
+ *      get_dHij_drij_DFTB (TB_DFTB.f90:781): MDatoms(k)%forces%att(1:3) = dE/ds_k [eV].
+ *      F_att(3,na); in a partitioned run only owned atoms are written. */
+int  xtb_forces(xtb_ctx*, double* F_att);
+
+/* ---- S5: Attract_TB_Forces_Press_NRL (TB_NRL.f90:2742) / Attract_TB_Forces_Press
+ *      (TB_Pettifor.f90:1134) / _DFTB (TB_DFTB.f90:1135): Scell%SCforce%att(3,3) col-major.
+ *      In a partitioned run this is the partial sum over owned atoms. */
+int  xtb_pressure(xtb_ctx*, double SCforce_att[9]);
+
+/* ---- introspection / zero-copy interop (device pointers valid until the producing stage
+ *      is re-run or the context destroyed) ------------------------------------------- */
+#define XTB_BUF_H        1   /* dense H_non (N,N) */
+#define XTB_BUF_S        2   /* dense Sij (N,N) */
+#define XTB_BUF_RHO      3   /* block-sparse rho   [n_blocks][n_orb*n_orb] */
+#define XTB_BUF_RHOE     4   /* block-sparse rho_E */
+#define XTB_BUF_FORCES   5   /* (3,na) */
+#define XTB_BUF_ROWPTR   6   /* int32 [na+1]: first block of atom i (block 0 = on-site) */
+#define XTB_BUF_NNLIST   7   /* int32 ELL list, 0-based, [cap*na] */
+#define XTB_BUF_NNSIZE   8   /* int32 [na] */
+#define XTB_BUF_SCFORCE  9   /* 9 doubles */
+int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
+/* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
+ *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap */
+long long xtb_counter(const xtb_ctx*, int which);
+/* device time [ms] of the last run of a stage (CUDA events on the context stream):
+ * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure */
+double xtb_stage_ms(const xtb_ctx*, int stage);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XTB_B200_H */

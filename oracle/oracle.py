@@ -1,0 +1,301 @@
+"""ORACLE (test infrastructure) -- Python driver of oracle/liboracle.so.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  It restates, on the CPU, the reference's per-MD-step tight-binding path
+(see the header of oracle/xtant_oracle.c for the file:line map and the "parity unpinned" note).
+
+The eigensolve between assembly and density follows the reference exactly:
+  Loewdin_Orthogonalization   Source_files/TB_NRL.f90:985-1060   (dsyev(S), X = U s^-1/2, H' = X^T H X)
+  sym_diagonalize(H')         Source_files/Algebra_tools.f90:882-966 (dsyevd)
+  Ha = X V                    Source_files/TB_NRL.f90:421
+using scipy's LAPACK (the reference links MKL; both are "a LAPACK", unpinned).
+"""
+import ctypes as C
+import importlib
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+if _ROOT not in sys.path:
+    sys.path.insert(0, _ROOT)
+_pkg = importlib.import_module("xtant-3_b200")
+_abi = importlib.import_module("xtant-3_b200._abi")
+
+G_RY, G_AU2A, G_A2AU = 13.6056981, 0.529177249, 1.8897259885789     # Universal_constants.f90:67,103,104
+G_E = 1.602176634e-19                                                 # :51
+
+_LIB = None
+_pd = C.POINTER(C.c_double)
+_pi = C.POINTER(C.c_int)
+
+
+def build(force=False):
+    so = os.path.join(_HERE, "liboracle.so")
+    src = [os.path.join(_HERE, f) for f in ("xtant_oracle.c", "sk_tables.h", "pettifor_oracle.c")]
+    src = [s for s in src if os.path.exists(s)]
+    if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_HERE, "liboracle.so")
+        if not os.path.exists(so):
+            build()
+        _LIB = C.CDLL(so)
+        _LIB.orc_neighbours.restype = C.c_int
+        _LIB.orc_num_threads.restype = C.c_int
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def num_threads():
+    return int(lib().orc_num_threads())
+
+
+def nrl_params_array(params):
+    arr = (_abi.NrlPair * len(params))()
+    for i, d in enumerate(params):
+        arr[i] = _abi.nrl_pair_from_dict(d)
+    return arr
+
+
+def cutoff_radius(wl):
+    """get_near_neighbours cut-off, Atomic_tools.f90:574-586 (NRL: max(Rc)*g_au2A; Pettifor: max(rm))."""
+    if wl["tb"] == "nrl":
+        return max(p["Rc"] for p in wl["params"]) * G_AU2A
+    if wl["tb"] == "pettifor":
+        return max(p["rm"] for p in wl["params"])
+    raise ValueError(wl["tb"])
+
+
+class Neigh:
+    """compact ELL neighbour list (0-based)"""
+
+    def __init__(self, na, cap):
+        self.na, self.cap = na, cap
+        self.size = np.zeros(na, dtype=np.int32)
+        self.list = np.zeros((na, cap), dtype=np.int32)
+        self.dist = np.zeros((na, cap, 4), dtype=np.float64)
+        self.dist_s = np.zeros((na, cap, 3), dtype=np.float64)
+
+    @property
+    def max_nn(self):
+        return int(self.size.max()) if self.na else 0
+
+    def n_blocks(self):
+        return int(self.size.sum()) + self.na
+
+
+def neighbours(wl, rm=None, cap=None):
+    na = wl["na"]
+    S = np.ascontiguousarray(wl["S"], dtype=np.float64)
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    rm = cutoff_radius(wl) if rm is None else rm
+    cap = cap or min(max(na - 1, 1), 256)
+    while True:
+        nb = Neigh(na, cap)
+        mx = lib().orc_neighbours(C.c_int(na), _p(S), _p(h), C.c_double(rm), C.c_int(cap),
+                                  _p(nb.size), _p(nb.list), _p(nb.dist), _p(nb.dist_s))
+        if mx <= cap:
+            return nb
+        cap = mx
+
+
+def geometry(wl, nb):
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    lmn = np.zeros((nb.na, nb.cap, 3)); xrr = np.zeros_like(lmn); x1 = np.zeros_like(lmn)
+    lib().orc_geometry(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.dist), _p(h), _p(lmn), _p(xrr), _p(x1))
+    return lmn, xrr, x1
+
+
+def _koa0(wl):
+    return np.ascontiguousarray(wl["koa"].astype(np.int32) - 1)
+
+
+def nrl_radial(wl, nb):
+    rad = np.zeros((nb.na, nb.cap, 40))
+    TB = nrl_params_array(wl["params"])
+    lib().orc_nrl_radial(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(_koa0(wl)),
+                         C.c_int(wl["n_kinds"]), TB, _p(rad))
+    return rad
+
+
+def nrl_embedded_density(wl, nb):
+    rho = np.zeros(nb.na)
+    TB = nrl_params_array(wl["params"])
+    lib().orc_nrl_embedded_density(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist),
+                                   _p(_koa0(wl)), C.c_int(wl["n_kinds"]), TB, _p(rho))
+    return rho
+
+
+def nrl_assemble_HS(wl, nb, lmn, rad):
+    N = nb.na * 9
+    H = np.zeros((N, N), order="F"); S = np.zeros((N, N), order="F")
+    TB = nrl_params_array(wl["params"])
+    lib().orc_nrl_assemble_HS(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(lmn), _p(rad),
+                              _p(_koa0(wl)), C.c_int(wl["n_kinds"]), TB, _p(H), _p(S))
+    return H, S
+
+
+def eigensolve_nonorthogonal(H, S):
+    """Loewdin_Orthogonalization + sym_diagonalize + back-transform (TB_NRL.f90:985-1060,409,421)."""
+    from scipy.linalg import lapack
+    w, U, info = lapack.dsyev(S, compute_v=1, lower=0)
+    assert info == 0
+    eps = 1e-8
+    if (w < 0).any() or (np.abs(w) < eps).any():
+        w = np.abs(w)
+    s = np.where(np.abs(w) > eps, 1.0 / np.sqrt(np.where(np.abs(w) > eps, w, 1.0)), 0.0)
+    X = U * s[None, :]
+    Hp = X.T @ (H @ X)
+    Hp = 0.5 * (Hp + Hp.T)
+    Ei, V, info = lapack.dsyevd(Hp, compute_v=1, lower=0)
+    assert info == 0
+    Ha = X @ V
+    return np.asfortranarray(Ha), Ei, w
+
+
+def eigensolve_orthogonal(H):
+    """sym_diagonalize(Ha) directly, S = I (TB_Pettifor.f90:1455)."""
+    from scipy.linalg import lapack
+    Ei, V, info = lapack.dsyevd(np.asfortranarray(H), compute_v=1, lower=0)
+    assert info == 0
+    return np.asfortranarray(V), Ei
+
+
+def density_dense(Ha, fe, Ei=None):
+    """Construct_Aij / Construct_Aij_x_En (TB.f90:4328-4469): Atemp = w*Ha ; Aij = Atemp Ha^T (dgemm)."""
+    w = fe if Ei is None else fe * Ei
+    return np.asfortranarray((Ha * w[None, :]) @ Ha.T)
+
+
+def density_blocks(nb, n_orb, Ha, fe, Ei, atom_first=0, atom_last=None):
+    na = nb.na
+    atom_last = na if atom_last is None else atom_last
+    Ha = np.asfortranarray(Ha)
+    K = Ha.shape[1]
+    rho = np.zeros((na, nb.cap + 1, n_orb * n_orb)); rhoE = np.zeros_like(rho)
+    lib().orc_density_blocks(C.c_int(na), C.c_int(n_orb), C.c_int(nb.cap), _p(nb.size), _p(nb.list), C.c_int(K), _p(Ha),
+                             _p(np.ascontiguousarray(fe)), _p(np.ascontiguousarray(Ei)),
+                             C.c_int(atom_first), C.c_int(atom_last), _p(rho), _p(rhoE))
+    return rho, rhoE
+
+
+def gather_blocks(nb, n_orb, A):
+    blk = np.zeros((nb.na, nb.cap + 1, n_orb * n_orb))
+    lib().orc_gather_blocks(C.c_int(nb.na), C.c_int(n_orb), C.c_int(nb.cap), _p(nb.size), _p(nb.list),
+                            _p(np.asfortranarray(A)), _p(blk))
+    return blk
+
+
+def _common(wl, nb, lmn, rad):
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    TB = nrl_params_array(wl["params"])
+    return h, TB, _koa0(wl)
+
+
+def nrl_forces_verbatim(wl, nb, lmn, rad, Aij, AijE):
+    h, TB, koa = _common(wl, nb, lmn, rad)
+    F = np.zeros((nb.na, 3))
+    lib().orc_nrl_forces_verbatim(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(lmn), _p(rad),
+                                  _p(koa), C.c_int(wl["n_kinds"]), TB, _p(h), _p(np.asfortranarray(Aij)),
+                                  _p(np.asfortranarray(AijE)), _p(F))
+    return F
+
+
+def nrl_forces_sparse(wl, nb, lmn, rad, rho_blk, rhoE_blk, atom_first=0, atom_last=None):
+    h, TB, koa = _common(wl, nb, lmn, rad)
+    atom_last = nb.na if atom_last is None else atom_last
+    F = np.zeros((nb.na, 3))
+    lib().orc_nrl_forces_sparse(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(lmn), _p(rad),
+                                _p(koa), C.c_int(wl["n_kinds"]), TB, _p(h), _p(rho_blk), _p(rhoE_blk),
+                                C.c_int(atom_first), C.c_int(atom_last), _p(F))
+    return F
+
+
+def nrl_pressure_verbatim(wl, nb, lmn, rad, Aij, AijE):
+    h, TB, koa = _common(wl, nb, lmn, rad)
+    att = np.zeros(9)
+    lib().orc_nrl_pressure_verbatim(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(nb.dist_s),
+                                    _p(lmn), _p(rad), _p(koa), C.c_int(wl["n_kinds"]), TB, _p(h),
+                                    _p(np.asfortranarray(Aij)), _p(np.asfortranarray(AijE)), _p(att))
+    return att.reshape(3, 3, order="F")
+
+
+def nrl_pressure_sparse(wl, nb, lmn, rad, rho_blk, rhoE_blk, atom_first=0, atom_last=None):
+    h, TB, koa = _common(wl, nb, lmn, rad)
+    atom_last = nb.na if atom_last is None else atom_last
+    att = np.zeros(9)
+    lib().orc_nrl_pressure_sparse(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(nb.dist_s),
+                                  _p(lmn), _p(rad), _p(koa), C.c_int(wl["n_kinds"]), TB, _p(h), _p(rho_blk), _p(rhoE_blk),
+                                  C.c_int(atom_first), C.c_int(atom_last), _p(att))
+    return att.reshape(3, 3, order="F")
+
+
+def ks_block(V, l, m, n):
+    ts = np.zeros(81)
+    lib().orc_ks_block(_p(np.ascontiguousarray(V, dtype=np.float64)), C.c_double(l), C.c_double(m), C.c_double(n), _p(ts))
+    return ts.reshape(9, 9, order="F")
+
+
+def dks_block(V, dV, l, m, n, dl, dm, dn, test_variant=False):
+    ts = np.zeros(81)
+    lib().orc_dks_block(_p(np.ascontiguousarray(V, dtype=np.float64)), _p(np.ascontiguousarray(dV, dtype=np.float64)),
+                        C.c_double(l), C.c_double(m), C.c_double(n), C.c_double(dl), C.c_double(dm), C.c_double(dn),
+                        C.c_int(1 if test_variant else 0), _p(ts))
+    return ts.reshape(9, 9, order="F")
+
+
+# ---- unit conversions used by the tolerance statements of the tests ---------------------------
+def forces_cartesian(F_s, supce):
+    """dE/ds_k [eV] -> dE/dR_k [eV/A].  R = s.h  (x_c = sum_k s_k supce(k,c), Atomic_tools.f90:4101)
+    so dE/ds_k(alpha) = sum_c dE/dR_c supce(alpha,c)  =>  dE/dR = solve(supce, dE/ds)."""
+    return np.linalg.solve(np.asarray(supce), np.asarray(F_s).T).T
+
+
+def pressure_GPa(att, supce):
+    """Potential part of Get_pressure: Potential_super_cell_forces + super_cell_forces + stress
+    (Atomic_tools.f90:2532-2634, TB.f90:5679-5692) with rep = 0 and no kinetic term; W_PR cancels.
+       att' = att*g_e/1e10 ; total(j,i) = att'(i,j) ; total = -total ; sigma(i,j) = d det(h)/d h(i,j) ;
+       stress(i,j) = total(i,j) * inv(sigma)(i,j) * 1e40 [Pa]  (ELEMENT-wise, as the Fortran `*`) ;
+       P = trace/3.  Returns (P [GPa], stress [GPa])."""
+    h = np.asarray(supce, dtype=np.float64)
+    total = -(np.asarray(att) * G_E / 1e10).T
+    sigma = np.linalg.det(h) * np.linalg.inv(h).T          # cofactor matrix (d_detH_d_h_a_b)
+    stress = total * np.linalg.inv(sigma) * 1e40
+    return np.trace(stress) / 3.0 * 1e-9, stress * 1e-9
+
+
+# ---- whole path, for parity tests ----------------------------------------------------------------
+def nrl_step(wl, with_pressure=True, verbatim=False):
+    nb = neighbours(wl)
+    lmn, xrr, x1 = geometry(wl, nb)
+    rad = nrl_radial(wl, nb)
+    H, S = nrl_assemble_HS(wl, nb, lmn, rad)
+    Ha, Ei, wS = eigensolve_nonorthogonal(H, S)
+    wk = importlib.import_module("xtant-3_b200.workloads")
+    fe, mu = wk.occupations(Ei, wl["n_electrons"], wl["Te_eV"])
+    out = dict(nb=nb, lmn=lmn, xrr=xrr, x1=x1, rad=rad, H=H, S=S, Ha=Ha, Ei=Ei, fe=fe, mu=mu, eigen_S=wS)
+    if verbatim:
+        Aij = density_dense(Ha, fe); AijE = density_dense(Ha, fe, Ei)
+        out.update(Aij=Aij, AijE=AijE)
+        out["rho"], out["rhoE"] = gather_blocks(nb, 9, Aij), gather_blocks(nb, 9, AijE)
+        out["F"] = nrl_forces_verbatim(wl, nb, lmn, rad, Aij, AijE)
+        if with_pressure:
+            out["P"] = nrl_pressure_verbatim(wl, nb, lmn, rad, Aij, AijE)
+    else:
+        out["rho"], out["rhoE"] = density_blocks(nb, 9, Ha, fe, Ei)
+        out["F"] = nrl_forces_sparse(wl, nb, lmn, rad, out["rho"], out["rhoE"])
+        if with_pressure:
+            out["P"] = nrl_pressure_sparse(wl, nb, lmn, rad, out["rho"], out["rhoE"])
+    return out

@@ -1,0 +1,115 @@
+"""ctypes view of include/xtb_b200.h: structs, constants and the library loader.
+
+The CUDA extension is mandatory: `load()` raises if libxtb_b200.so is missing or cannot be
+loaded -- there is no CPU fallback anywhere in the product path.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libxtb_b200.so")
+
+XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE = range(7)
+XTB_TB_NONE, XTB_TB_NRL, XTB_TB_PETTIFOR, XTB_TB_DFTB = range(4)
+
+BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE = range(1, 10)
+CNT_NA, CNT_NORB, CNT_N, CNT_MAXNN, CNT_NBLOCKS, CNT_NPAIRS, CNT_LAUNCHES, CNT_KKEPT, CNT_CAP = range(9)
+STAGE_NEIGH, STAGE_ASSEMBLE, STAGE_DENSITY, STAGE_FORCES, STAGE_PRESSURE = range(1, 6)
+
+_d4 = C.c_double * 4
+_d10 = C.c_double * 10
+
+
+class NrlPair(C.Structure):
+    """struct xtb_nrl_pair == type(TB_H_NRL), Objects.f90:190-200"""
+    _fields_ = [("ind_split", C.c_int32), ("ind_overlap", C.c_int32),
+                ("lambd", C.c_double), ("Rc", C.c_double), ("lden", C.c_double),
+                ("al", _d4), ("bl", _d4), ("cl", _d4), ("dl", _d4),
+                ("ellm", _d10), ("fllm", _d10), ("gllm", _d10), ("hllm", _d10),
+                ("pllm", _d10), ("qllm", _d10), ("rllm", _d10), ("sllm", _d10)]
+
+
+class PettiforPair(C.Structure):
+    """struct xtb_pettifor_pair == type(TB_H_Pettifor), Objects.f90:170-174"""
+    _fields_ = [("Es", C.c_double), ("Ep", C.c_double),
+                ("nc", _d4), ("rc", _d4), ("c0", _d4), ("c1", _d4), ("c2", _d4), ("c3", _d4), ("V0", _d4),
+                ("r0", C.c_double), ("n", C.c_double), ("r1", C.c_double), ("rm", C.c_double)]
+
+
+class DftbPair(C.Structure):
+    """struct xtb_dftb_pair == type(TB_H_DFTB), Objects.f90:202-222 (tables flattened)"""
+    _fields_ = [("rcut", C.c_double), ("d", C.c_double),
+                ("Ed", C.c_double), ("Ep", C.c_double), ("Es", C.c_double),
+                ("n_r", C.c_int32), ("pad_", C.c_int32),
+                ("Rr", C.POINTER(C.c_double)), ("Vr", C.POINTER(C.c_double)), ("Sr", C.POINTER(C.c_double))]
+
+
+def nrl_pair_from_dict(d):
+    p = NrlPair()
+    p.ind_split, p.ind_overlap = int(d["ind_split"]), int(d["ind_overlap"])
+    p.lambd, p.Rc, p.lden = float(d["lambd"]), float(d["Rc"]), float(d["lden"])
+    for k in ("al", "bl", "cl", "dl"):
+        setattr(p, k, _d4(*d[k]))
+    for k in ("ellm", "fllm", "gllm", "hllm", "pllm", "qllm", "rllm", "sllm"):
+        setattr(p, k, _d10(*d[k]))
+    return p
+
+
+def pettifor_pair_from_dict(d):
+    p = PettiforPair()
+    p.Es, p.Ep = float(d["Es"]), float(d["Ep"])
+    for k in ("nc", "rc", "c0", "c1", "c2", "c3", "V0"):
+        setattr(p, k, _d4(*d[k]))
+    p.r0, p.n, p.r1, p.rm = float(d["r0"]), float(d["n"]), float(d["r1"]), float(d["rm"])
+    return p
+
+
+_pd = C.POINTER(C.c_double)
+_pi = C.POINTER(C.c_int32)
+
+# name -> (restype, argtypes); every symbol include/xtb_b200.h declares
+SIGNATURES = {
+    "xtb_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int]),
+    "xtb_destroy": (C.c_int, [C.c_void_p]),
+    "xtb_last_error": (C.c_char_p, [C.c_void_p]),
+    "xtb_version": (C.c_char_p, []),
+    "xtb_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "xtb_sync": (C.c_int, [C.c_void_p]),
+    "xtb_set_params_nrl": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(NrlPair)]),
+    "xtb_set_params_pettifor": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PettiforPair)]),
+    "xtb_set_params_dftb": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(DftbPair)]),
+    "xtb_set_system": (C.c_int, [C.c_void_p, C.c_int, _pi, _pd, _pd]),
+    "xtb_set_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "xtb_neighbours": (C.c_int, [C.c_void_p, C.c_double, _pi, _pi, _pd, _pd]),
+    "xtb_neighbours_compact": (C.c_int, [C.c_void_p, C.c_int, _pi, _pi, _pd, _pd, C.POINTER(C.c_int)]),
+    "xtb_radial": (C.c_int, [C.c_void_p, _pd, _pd, _pd, _pd, _pd, _pd, _pd]),
+    "xtb_assemble_HS": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_set_eigen": (C.c_int, [C.c_void_p, _pd, _pd, _pd]),
+    "xtb_set_eigen_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "xtb_density": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_set_density_cutoff": (C.c_int, [C.c_void_p, C.c_double]),
+    "xtb_forces": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_device_buffer": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "xtb_counter": (C.c_longlong, [C.c_void_p, C.c_int]),
+    "xtb_stage_ms": (C.c_double, [C.c_void_p, C.c_int]),
+}
+
+_lib = None
+
+
+def load():
+    """dlopen libxtb_b200.so (built in-tree by __graft_entry__.build()).  Fails loudly."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"CUDA extension {LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`. "
+            "There is no CPU fallback for the tight-binding hot path.")
+    lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if a declared symbol is not exported
+        fn.restype, fn.argtypes = res, args
+    _lib = lib
+    return lib

@@ -1,0 +1,133 @@
+"""Deterministic workloads of the hot path: the five BASELINE.json configs plus
+small cells for tests.  Generator seeds are part of the contract.
+
+A workload is a dict:
+    name, tb ("nrl" | "pettifor"), n_orb, na, koa (int32 [na], 1-based kinds), S (float64 [na,3],
+    relative coordinates), supce (float64 [3,3], supce[a,b] == Scell%supce(a+1,b+1)),
+    params (list of parameter dicts, (KOA1,KOA2) column-major), n_kinds, n_electrons, Te_eV
+"""
+import json
+import os
+
+import numpy as np
+
+_DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
+K_B_EV = 8.617333262e-5
+
+
+def _load(name):
+    with open(os.path.join(_DATA, name)) as f:
+        return json.load(f)
+
+
+def load_params(kind, element):
+    return _load(f"params_{kind}_{element}.json")
+
+
+_FCC = np.array([[0, 0, 0], [0.5, 0.5, 0], [0.5, 0, 0.5], [0, 0.5, 0.5]], dtype=np.float64)
+_DIA = np.vstack([_FCC, _FCC + 0.25])
+
+
+def lattice(basis, a, reps, sigma, seed):
+    """Orthorhombic supercell of `reps` conventional cells, Gaussian displacements sigma [A]."""
+    nx, ny, nz = reps
+    cells = np.array([[i, j, k] for i in range(nx) for j in range(ny) for k in range(nz)], dtype=np.float64)
+    frac = (cells[:, None, :] + basis[None, :, :]).reshape(-1, 3)
+    L = np.array([nx * a, ny * a, nz * a])
+    cart = frac * a
+    if sigma > 0:
+        rng = np.random.default_rng(seed)
+        cart = cart + rng.normal(0.0, sigma, size=cart.shape)
+    S = np.mod(cart / L, 1.0)
+    supce = np.diag(L)
+    return np.ascontiguousarray(S), supce
+
+
+def _wl(name, tb, element, S, supce, n_el_per_atom, Te_eV, koa=None):
+    na = S.shape[0]
+    return dict(name=name, tb=tb, n_orb=9 if tb == "nrl" else 4, na=na,
+                koa=np.ones(na, dtype=np.int32) if koa is None else np.asarray(koa, dtype=np.int32),
+                S=np.ascontiguousarray(S, dtype=np.float64), supce=np.ascontiguousarray(supce, dtype=np.float64),
+                params=[load_params(tb, element)], n_kinds=1, element=element,
+                n_electrons=float(n_el_per_atom * na), Te_eV=float(Te_eV))
+
+
+def _from_cell(name, tb, element, cellfile, n_el_per_atom, Te_eV):
+    c = _load(cellfile)
+    return _wl(name, tb, element, np.array(c["S"]), np.array(c["supce"]), n_el_per_atom, Te_eV, koa=c["koa"])
+
+
+def diamond64():   # config 1
+    return _from_cell("diamond64", "pettifor", "C", "cell_diamond64.json", 4, 300.0 * K_B_EV)
+
+
+def si216():       # config 2
+    S, h = lattice(_DIA, 5.44, (3, 3, 3), 0.05, 216)
+    return _wl("si216", "nrl", "Si", S, h, 4, 2.0)
+
+
+def al500():       # config 3 (triclinic cell from the reference's SAVE files)
+    return _from_cell("al500", "nrl", "Al", "cell_al500.json", 3, 1000.0 * K_B_EV)
+
+
+def ac1000():      # config 4
+    S, h = lattice(_DIA, 3.5588, (5, 5, 5), 0.25, 1000)
+    return _wl("ac1000", "pettifor", "C", S, h, 4, 1.0)
+
+
+def au4096():      # config 5 (north star)
+    S, h = lattice(_FCC, 4.0782, (8, 8, 16), 0.05, 4096)
+    return _wl("au4096", "nrl", "Au", S, h, 11, 0.1)
+
+
+def au108():       # small NRL metal cell from the reference's SAVE files (tests)
+    return _from_cell("au108", "nrl", "Au", "cell_au108.json", 11, 0.1)
+
+
+def au_fcc(reps, sigma=0.05, seed=1):
+    S, h = lattice(_FCC, 4.0782, reps, sigma, seed)
+    w = _wl(f"au_fcc_{reps[0]}x{reps[1]}x{reps[2]}", "nrl", "Au", S, h, 11, 0.1)
+    return w
+
+
+def si_dia(reps, sigma=0.05, seed=2):
+    S, h = lattice(_DIA, 5.44, reps, sigma, seed)
+    return _wl(f"si_dia_{reps[0]}x{reps[1]}x{reps[2]}", "nrl", "Si", S, h, 4, 2.0)
+
+
+def c_dia(reps, sigma=0.05, seed=3):
+    S, h = lattice(_DIA, 3.5588, reps, sigma, seed)
+    return _wl(f"c_dia_{reps[0]}x{reps[1]}x{reps[2]}", "pettifor", "C", S, h, 4, 1.0)
+
+
+CONFIGS = {"diamond64": diamond64, "si216": si216, "al500": al500, "ac1000": ac1000, "au4096": au4096}
+
+
+# ---- electron occupations (input of the density stage; produced by Electron_tools in the reference) ----
+def fermi(E, mu, Te_eV):
+    """Fermi_distribution, Electron_tools.f90:1896-1909 (spin factor 2)."""
+    with np.errstate(over="ignore"):
+        return 2.0 / (1.0 + np.exp((E - mu) / Te_eV))
+
+
+def occupations(E, n_electrons, Te_eV):
+    """mu from N_e by bisection (as Electron_Fixed_Te, Electron_tools.f90:2660), then f_n."""
+    lo, hi = float(E.min()) - 50.0 * Te_eV - 1.0, float(E.max()) + 50.0 * Te_eV + 1.0
+    for _ in range(200):
+        mu = 0.5 * (lo + hi)
+        if fermi(E, mu, Te_eV).sum() < n_electrons:
+            lo = mu
+        else:
+            hi = mu
+    mu = 0.5 * (lo + hi)
+    return fermi(E, mu, Te_eV), mu
+
+
+def synthetic_eigen(N, filling=0.61, Te_eV=0.1, seed=7, dtype=np.float64):
+    """Kernel-throughput stand-in for the eigensolve at sizes no CPU can diagonalise
+    (SURVEY.md 8d item 5): C = N(0,1)/sqrt(N), E sorted uniform(-10,40), f = Fermi at `filling`."""
+    rng = np.random.default_rng(seed)
+    E = np.sort(rng.uniform(-10.0, 40.0, size=N))
+    fe, mu = occupations(E, 2.0 * filling * N, Te_eV)
+    C = rng.standard_normal((N, N)).astype(dtype) / np.sqrt(N)
+    return np.asfortranarray(C), E, fe
