@@ -134,6 +134,9 @@ int  xtb_set_eigen_device(xtb_ctx*, const double* dHa, const double* dEi, const 
  *      f_cut: states with fe(n) <= f_cut are skipped (0 = bit-safe: only exact zeros). */
 int  xtb_density(xtb_ctx*, double* Aij, double* Aij_x_Ei);
 int  xtb_set_density_cutoff(xtb_ctx*, double f_cut);
+/* multi-GPU only: after the owner blocks of all ranks have been exchanged into XTB_BUF_RHO/RHOE
+ * (one allgather, replaces the MPI_Allreduce of the dense Aij, TB.f90:4374), fill the mirrored blocks. */
+int  xtb_density_mirror(xtb_ctx*);
 
 /* ---- S4: get_dHij_drij_NRL (TB_NRL.f90:2412) / dHij_s (TB_Pettifor.f90:141) /
  *      get_dHij_drij_DFTB (TB_DFTB.f90:781): MDatoms(k)%forces%att(1:3) = dE/ds_k [eV].
@@ -158,10 +161,12 @@ int  xtb_pressure(xtb_ctx*, double SCforce_att[9]);
 #define XTB_BUF_SCFORCE  9   /* 9 doubles */
 int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
- *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap */
+ *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,
+ *           9 / 10 shared-memory slots / pipeline stages of the last density kernel */
 long long xtb_counter(const xtb_ctx*, int which);
 /* device time [ms] of the last run of a stage (CUDA events on the context stream):
- * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure */
+ * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure,
+ * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3) */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 
 #ifdef __cplusplus

@@ -1,0 +1,183 @@
+"""Pins of the CPU oracle (oracle/), run without a GPU.
+
+The reference ships no golden vectors for this path ("parity unpinned"), so the
+oracle is pinned by: (i) its two algorithmic forms agreeing (verbatim dense per-atom derivative
+matrices of the reference vs. the sparse-equivalent form used at scale), (ii) finite differences of
+its own band energy for everything that is an exact derivative (with the reference's one known
+non-derivative, d_t_dxz_dx2_y2, switched to the exact form for that check only), (iii) physical
+invariants, (iv) committed regression values (tests/golden/oracle_regression.json) produced by
+tests/golden/make_regression.py so that later edits of the oracle cannot drift silently.
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+@pytest.fixture(scope="module")
+def au32(orc, wk):
+    wl = wk.au_fcc((2, 2, 2), sigma=0.12, seed=11)
+    return wl, orc.nrl_step(wl, verbatim=True)
+
+
+def test_neighbour_list_properties(orc, wk):
+    wl = wk.au_fcc((2, 2, 2), sigma=0.05, seed=5)
+    nb = orc.neighbours(wl)
+    rm = orc.cutoff_radius(wl)
+    assert nb.size.min() > 0
+    for i in range(nb.na):
+        m = nb.size[i]
+        lst = nb.list[i, :m]
+        assert (np.diff(lst) > 0).all()                 # ascending j, each atom at most once
+        assert i not in lst
+        assert (nb.dist[i, :m, 3] < rm).all()
+        np.testing.assert_allclose(np.linalg.norm(nb.dist[i, :m, :3], axis=1), nb.dist[i, :m, 3], rtol=1e-15)
+        # x = s.h with the stored image-shifted relative vector
+        np.testing.assert_allclose(nb.dist_s[i, :m] @ wl["supce"], nb.dist[i, :m, :3], rtol=0, atol=1e-13)
+        for k in range(m):                              # symmetric list, antisymmetric vectors
+            j = lst[k]
+            kk = list(nb.list[j, :nb.size[j]]).index(i)
+            assert nb.dist[j, kk, 3] == nb.dist[i, k, 3]
+            np.testing.assert_array_equal(nb.dist[j, kk, :3], -nb.dist[i, k, :3])
+
+
+def test_minimum_image_is_minimum(orc, wk):
+    wl = wk.al500()                                     # triclinic cell from the reference's SAVE files
+    sub = dict(wl); sub["S"] = wl["S"][:60].copy(); sub["koa"] = wl["koa"][:60].copy(); sub["na"] = 60
+    nb = orc.neighbours(sub, rm=1e9, cap=59)
+    h = sub["supce"]
+    shifts = np.array([[i, j, k] for i in (-1, 0, 1) for j in (-1, 0, 1) for k in (-1, 0, 1)], dtype=float)
+    for i in (0, 7, 33):
+        for k in range(nb.size[i]):
+            j = nb.list[i, k]
+            d = (sub["S"][i] - sub["S"][j])[None, :] + shifts
+            r = np.linalg.norm(d @ h, axis=1)
+            assert abs(r.min() - nb.dist[i, k, 3]) < 1e-12
+
+
+def test_hs_symmetric_and_onsite_identity(au32):
+    wl, o = au32
+    H, S = o["H"], o["S"]
+    assert np.abs(H - H.T).max() == 0.0 and np.abs(S - S.T).max() == 0.0
+    for a in range(wl["na"]):
+        np.testing.assert_array_equal(S[9 * a:9 * a + 9, 9 * a:9 * a + 9], np.eye(9))
+    assert o["eigen_S"].min() > 0
+
+
+def test_eigen_and_density_invariants(au32):
+    wl, o = au32
+    Ha, S, H, Ei, fe = o["Ha"], o["S"], o["H"], o["Ei"], o["fe"]
+    N = H.shape[0]
+    np.testing.assert_allclose(Ha.T @ S @ Ha, np.eye(N), atol=5e-10)
+    np.testing.assert_allclose(H @ Ha, (S @ Ha) * Ei[None, :], atol=5e-9)
+    assert abs((o["Aij"] * S).sum() - wl["n_electrons"]) < 1e-8            # tr(rho S) = N_e
+    assert abs((o["AijE"] * S).sum() - (fe * Ei).sum()) < 1e-7             # tr(rho_E S) = sum f E
+    assert abs(fe.sum() - wl["n_electrons"]) < 1e-9
+
+
+def test_verbatim_equals_sparse(orc, au32):
+    wl, o = au32
+    nb = o["nb"]
+    rho, rhoE = orc.density_blocks(nb, 9, o["Ha"], o["fe"], o["Ei"])
+    np.testing.assert_allclose(rho, o["rho"], atol=1e-12)
+    np.testing.assert_allclose(rhoE, o["rhoE"], atol=1e-11)
+    Fs = orc.nrl_forces_sparse(wl, nb, o["lmn"], o["rad"], o["rho"], o["rhoE"])
+    Ps = orc.nrl_pressure_sparse(wl, nb, o["lmn"], o["rad"], o["rho"], o["rhoE"])
+    assert np.abs(Fs - o["F"]).max() <= 1e-13 * max(1.0, np.abs(o["F"]).max())
+    assert np.abs(Ps - o["P"]).max() <= 1e-12 * max(1.0, np.abs(o["P"]).max())
+
+
+def test_translation_invariance(au32):
+    _, o = au32
+    assert np.abs(o["F"].sum(axis=0)).max() < 1e-10
+
+
+def _band_energy(orc, wl, fe):
+    from scipy.linalg import eigh
+    nb = orc.neighbours(wl)
+    lmn, _, _ = orc.geometry(wl, nb)
+    rad = orc.nrl_radial(wl, nb)
+    H, S = orc.nrl_assemble_HS(wl, nb, lmn, rad)
+    return float((eigh(H, S, eigvals_only=True) * fe).sum())
+
+
+def test_forces_are_band_energy_gradient_when_quirk_off(orc, wk):
+    """Hellmann-Feynman at frozen occupations: F_k = d(sum_n f_n E_n)/ds_k.  Holds for the oracle with the
+    exact d_t_dxz_dx2_y2; with the reference's formula (strict) it must NOT hold -- both are asserted."""
+    wl = wk.au_fcc((2, 2, 2), sigma=0.15, seed=3)
+    o = orc.nrl_step(wl, with_pressure=False)
+    fe = o["fe"]
+    picks = [(0, 0), (5, 1), (17, 2)]
+    fd = []
+    for k, a in picks:
+        d = 1e-5
+        wp = dict(wl); wp["S"] = wl["S"].copy(); wp["S"][k, a] += d
+        wm = dict(wl); wm["S"] = wl["S"].copy(); wm["S"][k, a] -= d
+        fd.append((_band_energy(orc, wp, fe) - _band_energy(orc, wm, fe)) / (2 * d))
+    fd = np.array(fd)
+    try:
+        orc.lib().orc_set_strict_reference(C.c_int(0))
+        F0 = orc.nrl_forces_sparse(wl, o["nb"], o["lmn"], o["rad"], o["rho"], o["rhoE"])
+    finally:
+        orc.lib().orc_set_strict_reference(C.c_int(1))
+    F1 = o["F"]
+    exact = np.array([F0[k, a] for k, a in picks])
+    strict = np.array([F1[k, a] for k, a in picks])
+    np.testing.assert_allclose(exact, fd, rtol=0, atol=2e-6)
+    assert np.abs(strict - fd).max() > 1e-3          # the reference quirk is really reproduced
+
+
+def test_pressure_is_band_energy_gradient_wrt_cell_when_quirk_off(orc, wk):
+    """SCforce%att(k,i) (flat k1 = (gamma-1)*3+delta) = g_A2au*g_au2A-consistent dE/dh(gamma,delta)."""
+    wl = wk.au_fcc((2, 2, 2), sigma=0.15, seed=4)
+    o = orc.nrl_step(wl, with_pressure=False)
+    fe = o["fe"]
+    try:
+        orc.lib().orc_set_strict_reference(C.c_int(0))
+        P0 = orc.nrl_pressure_sparse(wl, o["nb"], o["lmn"], o["rad"], o["rho"], o["rhoE"])
+    finally:
+        orc.lib().orc_set_strict_reference(C.c_int(1))
+    for ga, de in [(0, 0), (1, 2), (2, 1)]:
+        d = 1e-5
+        hp = wl["supce"].copy(); hp[ga, de] += d
+        hm = wl["supce"].copy(); hm[ga, de] -= d
+        wp = dict(wl); wp["supce"] = hp
+        wm = dict(wl); wm["supce"] = hm
+        fd = (_band_energy(orc, wp, fe) - _band_energy(orc, wm, fe)) / (2 * d)
+        got = P0.reshape(-1, order="F")[ga * 3 + de]
+        # the reference mixes g_A2au (radial part) with g_au2A*g_A2au (angular part): ~3e-8 relative
+        assert abs(got - fd) < 5e-6 * max(1.0, abs(fd)), (ga, de, got, fd)
+
+
+def test_sk_tables_transpose_relation(orc):
+    """d_KS_sp3d5_TEST^T == d_KS_sp3d5 (why the pressure path, which transposes the TEST block, is
+    consistent with the force path: SURVEY.md 9 item 3)."""
+    rng = np.random.default_rng(0)
+    V, dV = rng.normal(size=10), rng.normal(size=10)
+    v = rng.normal(size=3); v /= np.linalg.norm(v)
+    dv = rng.normal(size=3)
+    a = orc.dks_block(V, dV, *v, *dv, test_variant=False)
+    b = orc.dks_block(V, dV, *v, *dv, test_variant=True)
+    np.testing.assert_array_equal(a, b.T)
+    # value block: sign structure under inversion of the direction
+    k1 = orc.ks_block(V, *v)
+    k2 = orc.ks_block(V, *(-v))
+    np.testing.assert_allclose(k2, k1.T, atol=1e-15)
+
+
+def test_regression_values(orc, wk):
+    path = os.path.join(HERE, "golden", "oracle_regression.json")
+    ref = json.load(open(path))
+    for name, r in ref.items():
+        wl = getattr(wk, r["workload"])(*[tuple(a) if isinstance(a, list) else a for a in r.get("args", [])], **r.get("kwargs", {}))
+        o = orc.nrl_step(wl)
+        assert o["nb"].size.sum() == r["n_pairs"], name
+        np.testing.assert_allclose(np.abs(o["H"]).sum(), r["H_abs_sum"], rtol=1e-11, err_msg=name)
+        np.testing.assert_allclose(np.abs(o["S"]).sum(), r["S_abs_sum"], rtol=1e-11, err_msg=name)
+        np.testing.assert_allclose(o["Ei"][[0, len(o["Ei"]) // 2, -1]], r["Ei_pick"], rtol=1e-9, atol=1e-9, err_msg=name)
+        np.testing.assert_allclose(o["F"][:4].ravel(), r["F_first4"], rtol=1e-7, atol=1e-8, err_msg=name)
+        np.testing.assert_allclose(o["P"].ravel(order="F"), r["P"], rtol=1e-7, atol=1e-7, err_msg=name)

@@ -88,6 +88,7 @@ SIGNATURES = {
     "xtb_set_eigen_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "xtb_density": (C.c_int, [C.c_void_p, _pd, _pd]),
     "xtb_set_density_cutoff": (C.c_int, [C.c_void_p, C.c_double]),
+    "xtb_density_mirror": (C.c_int, [C.c_void_p]),
     "xtb_forces": (C.c_int, [C.c_void_p, _pd]),
     "xtb_pressure": (C.c_int, [C.c_void_p, _pd]),
     "xtb_device_buffer": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),

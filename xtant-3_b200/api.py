@@ -1,0 +1,187 @@
+"""Host-side binding of the C ABI (include/xtb_b200.h) used by tests, smoke() and bench.py.
+
+`TBContext` is a thin object over an `xtb_ctx*`; its methods are named after the reference
+procedures they stand in for (same argument meaning, results in the reference's array shapes):
+
+    get_near_neighbours            Source_files/Atomic_tools.f90:562
+    Construct_M_x1 / Construct_Vij_NRL   Source_files/TB.f90:3430, TB_NRL.f90:1956   (-> radial_tables)
+    construct_TB_H_NRL / construct_TB_H_Pettifor   TB_NRL.f90:74, TB_Pettifor.f90:1427  (-> assemble_HS)
+    Construct_Aij / Construct_Aij_x_En   TB.f90:4328,4401                             (-> density)
+    get_dHij_drij_NRL / dHij_s     TB_NRL.f90:2412, TB_Pettifor.f90:141               (-> forces)
+    Attract_TB_Forces_Press_NRL / Attract_TB_Forces_Press  TB_NRL.f90:2742, TB_Pettifor.f90:1134 (-> pressure)
+
+Errors: every non-zero ABI status raises XtbError(code, text) -- the reference records
+(Save_error_details) and continues; a Python caller gets an exception instead.
+Nothing here computes: all arithmetic happens in libxtb_b200.so on the GPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+
+
+class XtbError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"xtb error {code}: {text}")
+        self.code = code
+
+
+def _dp(a):
+    return None if a is None else a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _ip(a):
+    return None if a is None else a.ctypes.data_as(C.POINTER(C.c_int32))
+
+
+class TBContext:
+    def __init__(self, device=0):
+        self.lib = _abi.load()
+        h = C.c_void_p()
+        rc = self.lib.xtb_create(C.byref(h), int(device))
+        if rc != 0:
+            raise XtbError(rc, "xtb_create failed (no CUDA device? there is no CPU fallback)")
+        self.h = h
+        self.na = 0
+        self.n_orb = 0
+        self.tb = None
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def _ck(self, rc):
+        if rc != 0:
+            raise XtbError(rc, self.lib.xtb_last_error(self.h).decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.xtb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def counter(self, which):
+        return int(self.lib.xtb_counter(self.h, which))
+
+    def stage_ms(self, stage):
+        return float(self.lib.xtb_stage_ms(self.h, stage))
+
+    def set_stream(self, cuda_stream_ptr):
+        self._ck(self.lib.xtb_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def sync(self):
+        self._ck(self.lib.xtb_sync(self.h))
+
+    def device_buffer(self, which):
+        p = C.c_void_p(); n = C.c_size_t()
+        self._ck(self.lib.xtb_device_buffer(self.h, which, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    # -- inputs -----------------------------------------------------------------------------
+    def set_workload(self, wl):
+        """parameters + system of a workloads.py dict"""
+        nk = wl["n_kinds"]
+        if wl["tb"] == "nrl":
+            arr = (_abi.NrlPair * (nk * nk))(*[_abi.nrl_pair_from_dict(d) for d in wl["params"]])
+            self._ck(self.lib.xtb_set_params_nrl(self.h, nk, arr))
+            self.n_orb = 9
+        elif wl["tb"] == "pettifor":
+            arr = (_abi.PettiforPair * (nk * nk))(*[_abi.pettifor_pair_from_dict(d) for d in wl["params"]])
+            self._ck(self.lib.xtb_set_params_pettifor(self.h, nk, arr))
+            self.n_orb = 4
+        else:
+            raise ValueError(wl["tb"])
+        self.tb = wl["tb"]
+        self.set_system(wl["koa"], wl["S"], wl["supce"])
+
+    def set_system(self, koa, S, supce):
+        koa = np.ascontiguousarray(koa, dtype=np.int32)
+        S = np.ascontiguousarray(S, dtype=np.float64)
+        h = np.asfortranarray(supce, dtype=np.float64)
+        self.na = int(koa.shape[0])
+        self._ck(self.lib.xtb_set_system(self.h, self.na, _ip(koa), _dp(S), _dp(h)))
+
+    def set_partition(self, first, last):
+        self._ck(self.lib.xtb_set_partition(self.h, int(first), int(last)))
+
+    # -- S1 ---------------------------------------------------------------------------------
+    def get_near_neighbours(self, rm=0.0, dense=False):
+        """returns dict(size, list, dist, dist_s); dense=True gives the reference shapes
+        Near_neighbor_size(na), _list(na,na) (1-based, 0 = empty), _dist(na,na,4), _dist_s(na,na,3);
+        dense=False the compact (na,max_nn[,c]) arrays with 0-based atom indices."""
+        na = self.na
+        if dense:
+            size = np.zeros(na, dtype=np.int32)
+            lst = np.zeros((na, na), dtype=np.int32, order="F")
+            dist = np.zeros((na, na, 4), order="F")
+            dist_s = np.zeros((na, na, 3), order="F")
+            self._ck(self.lib.xtb_neighbours(self.h, float(rm), _ip(size), _ip(lst), _dp(dist), _dp(dist_s)))
+            return dict(size=size, list=lst, dist=dist, dist_s=dist_s)
+        self._ck(self.lib.xtb_neighbours(self.h, float(rm), None, None, None, None))
+        mx = max(self.counter(_abi.CNT_MAXNN), 1)
+        size = np.zeros(na, dtype=np.int32)
+        lst = np.zeros((na, mx), dtype=np.int32)
+        dist = np.zeros((na, mx, 4)); dist_s = np.zeros((na, mx, 3))
+        m = C.c_int()
+        self._ck(self.lib.xtb_neighbours_compact(self.h, mx, _ip(size), _ip(lst), _dp(dist), _dp(dist_s), C.byref(m)))
+        return dict(size=size, list=lst, dist=dist, dist_s=dist_s, max_nn=m.value)
+
+    # -- S2 ---------------------------------------------------------------------------------
+    def radial_tables(self):
+        """Construct_M_x1 + Construct_Vij_NRL in the reference's dense shapes (small systems)."""
+        na = self.na
+        out = {k: np.zeros((na, na, 10), order="F") for k in ("M_Vij", "M_dVij", "M_SVij", "M_dSVij")}
+        out.update({k: np.zeros((3, na, na), order="F") for k in ("M_lmn", "M_x1", "M_xrr")})
+        self._ck(self.lib.xtb_radial(self.h, _dp(out["M_Vij"]), _dp(out["M_dVij"]), _dp(out["M_SVij"]), _dp(out["M_dSVij"]),
+                                     _dp(out["M_lmn"]), _dp(out["M_x1"]), _dp(out["M_xrr"])))
+        return out
+
+    def assemble_HS(self, to_host=True):
+        N = self.na * self.n_orb
+        if not to_host:
+            self._ck(self.lib.xtb_assemble_HS(self.h, None, None))
+            return None, None
+        H = np.zeros((N, N), order="F")
+        S = np.zeros((N, N), order="F") if self.tb != "pettifor" else None
+        self._ck(self.lib.xtb_assemble_HS(self.h, _dp(H), _dp(S)))
+        return H, S
+
+    # -- eigensolve boundary ------------------------------------------------------------------
+    def set_eigen(self, Ha, Ei, fe):
+        Ha = np.asfortranarray(Ha, dtype=np.float64)
+        self._keep = (Ha, np.ascontiguousarray(Ei, dtype=np.float64), np.ascontiguousarray(fe, dtype=np.float64))
+        self._ck(self.lib.xtb_set_eigen(self.h, _dp(self._keep[0]), _dp(self._keep[1]), _dp(self._keep[2])))
+
+    def set_eigen_device(self, dHa, dEi, dfe):
+        """device pointers (ints), e.g. torch tensors' data_ptr(); zero copy"""
+        self._ck(self.lib.xtb_set_eigen_device(self.h, C.c_void_p(dHa), C.c_void_p(dEi), C.c_void_p(dfe)))
+
+    def set_density_cutoff(self, f_cut):
+        self._ck(self.lib.xtb_set_density_cutoff(self.h, float(f_cut)))
+
+    # -- S3 ---------------------------------------------------------------------------------
+    def density(self, dense=False):
+        if not dense:
+            self._ck(self.lib.xtb_density(self.h, None, None))
+            return None, None
+        N = self.na * self.n_orb
+        A = np.zeros((N, N), order="F"); AE = np.zeros((N, N), order="F")
+        self._ck(self.lib.xtb_density(self.h, _dp(A), _dp(AE)))
+        return A, AE
+
+    def density_mirror(self):
+        self._ck(self.lib.xtb_density_mirror(self.h))
+
+    # -- S4 / S5 ------------------------------------------------------------------------------
+    def forces(self):
+        F = np.zeros((self.na, 3))
+        self._ck(self.lib.xtb_forces(self.h, _dp(F)))
+        return F
+
+    def pressure(self):
+        att = np.zeros(9)
+        self._ck(self.lib.xtb_pressure(self.h, _dp(att)))
+        return att.reshape(3, 3, order="F")

@@ -1,0 +1,438 @@
+// S3 -- occupation-weighted density matrices rho = C f C^T and rho_E = C (f E) C^T on the neighbour pattern.
+//
+// Replaces Construct_Aij (Source_files/TB.f90:4328-4398) and Construct_Aij_x_En (TB.f90:4401-4469):
+//     Atemp(i,:) = w(:)*Ha(i,:) ; Aij = Atemp * Ha^T   (dgemm 'N','T'),  w = fe  resp.  fe*Ei.
+// The reference forms the full N x N products (2 x 2N^3 flop); every consumer reads only the blocks
+// (atom i, {i} U NN(i)) (TB.f90:250-299,5544-5573; TB_NRL.f90:2594-2596,2794-2796), so only those are
+// evaluated, and each unordered pair only once (rho is symmetric): the pair (i,j) is evaluated by its
+// "owner" (balanced half-list rule below) and mirrored into the other block afterwards.
+//
+// B200 mapping (FP64 tensor cores; tcgen05 has no FP64 kind, the native op is DMMA.8x8x4):
+//   prep   : state compaction (skip f_n <= f_cut), weights, and a tiled transposed copy of the eigenvectors
+//            Ct[chunk of 16 states][atom][4 k-steps][n_orb rows][4 states]  -- one contiguous tile
+//            (1152 B for n_orb = 9) per (chunk, atom), laid out so that DMMA fragment loads from shared
+//            memory are bank-conflict free without padding.
+//   main   : persistent CTAs, one atom i at a time.  A producer warp streams the tiles of i and of its
+//            owned neighbours through a multi-stage shared-memory ring with cp.async.bulk (TMA bulk
+//            copies, mbarrier complete_tx); 8 consumer warps issue mma.sync.m8n8k4.f64:
+//                D[row = orbital nu of neighbour j][col = (rho|rho_E, orbital mu of i)] +=
+//                    C[j nu, n] * (w_n C[i mu, n])
+//            i.e. M = packed neighbour rows, N = 24 = 9 (rho) + 9 (rho_E) + 6 pad, K = states.
+//            rho and rho_E share the A operand, so one pass over the eigenvectors produces both.
+//   mirror : non-owner blocks filled by transposition, so S4/S5 stream complete rows of blocks.
+// Algorithmic flops (roofline numerator): 2 matrices * 2 * n_orb^2 * K_kept * (n_pairs/2 + na).
+#include "xtb_ctx.h"
+#include <cstdint>
+
+namespace {
+
+constexpr int KC = 16;                 // states per chunk
+constexpr int NCW = 8;                 // consumer warps
+constexpr int NTHREADS = (NCW + 1) * 32;
+
+// balanced half-list ownership: exactly one of own(i,j), own(j,i) is true for i != j
+__host__ __device__ __forceinline__ bool owns(int i, int j) { return ((i + j) & 1) ? (i < j) : (i > j); }
+
+// ---------------- prep ----------------
+// order-preserving compaction of the kept states; single CTA (K <= a few 1e5)
+__global__ void keep_kernel(long long K, const double* __restrict__ fe, const double* __restrict__ Ei, double f_cut,
+                            int* __restrict__ keep, double* __restrict__ wf, double* __restrict__ wfe, int* __restrict__ nkeep) {
+    __shared__ int buf[1024];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (long long base = 0; base < K; base += 1024) {
+        const long long n = base + threadIdx.x;
+        const int flag = (n < K && fe[n] > f_cut) ? 1 : 0;
+        buf[threadIdx.x] = flag;
+        __syncthreads();
+        for (int off = 1; off < 1024; off <<= 1) {
+            int t = threadIdx.x >= off ? buf[threadIdx.x - off] : 0;
+            __syncthreads();
+            buf[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (flag) {
+            const int pos = carry + buf[threadIdx.x] - 1;
+            keep[pos] = (int)n;
+            wf[pos] = fe[n];                 // Atemp = distre * Ha           TB.f90:4378
+            wfe[pos] = fe[n] * Ei[n];        // Atemp = distre * En * Ha      TB.f90:4459
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += buf[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *nkeep = carry;
+}
+
+__global__ void pad_weights_kernel(int nkeep, int kpad, double* __restrict__ wf, double* __restrict__ wfe) {
+    const int t = nkeep + blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < kpad) { wf[t] = 0.0; wfe[t] = 0.0; }
+}
+
+// Ct[chunk][atom][s][r][t] = Ha[atom*NO + r, keep[chunk*16 + 4 s + t]]  (0 beyond nkeep)
+// one CTA per (chunk, group of 32 atoms): reads 16 columns x (32*NO) contiguous rows, writes contiguous tiles.
+template <int NO>
+__global__ void __launch_bounds__(256) ct_tile_kernel(int na, long long N, int nkeep, const int* __restrict__ keep,
+                                                     const double* __restrict__ Ha, double* __restrict__ Ct) {
+    constexpr int AT = 32;
+    __shared__ double tile[KC][AT * NO + 1];
+    const int chunk = blockIdx.x;
+    const int atom0 = blockIdx.y * AT;
+    const int nat = min(AT, na - atom0);
+    const int nrow = nat * NO;
+    for (int kk = 0; kk < KC; ++kk) {
+        const int ks = chunk * KC + kk;
+        const double* src = ks < nkeep ? Ha + (size_t)keep[ks] * N + (size_t)atom0 * NO : nullptr;
+        for (int r = threadIdx.x; r < nrow; r += blockDim.x) tile[kk][r] = src ? src[r] : 0.0;
+    }
+    __syncthreads();
+    double* dst = Ct + ((size_t)chunk * na + atom0) * (NO * KC);
+    const int tot = nat * NO * KC;
+    for (int e = threadIdx.x; e < tot; e += blockDim.x) {
+        const int a = e / (NO * KC);
+        int rem = e - a * (NO * KC);
+        const int s = rem / (NO * 4); rem -= s * (NO * 4);
+        const int r = rem >> 2, t = rem & 3;
+        dst[e] = tile[4 * s + t][a * NO + r];
+    }
+}
+
+// ---------------- PTX helpers ----------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(b)), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+}
+
+// ---------------- main kernel ----------------
+// dynamic smem: [STAGES][ slotcap*NO*KC doubles | 2*KC doubles (wf, wfe) ]  then barriers and slot tables
+template <int NO, int MT>
+__global__ void __launch_bounds__(NTHREADS, 1)
+density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, int nchunks,
+                    const int* __restrict__ nn_size, const int* __restrict__ nn_list, const int* __restrict__ rowptr,
+                    const double* __restrict__ Ct, const double* __restrict__ wf, const double* __restrict__ wfe,
+                    double* __restrict__ rho, double* __restrict__ rhoE) {
+    static_assert(NO == 9, "column packing below is written for the 9-orbital (18 -> 24 columns) case");
+    constexpr int TILE = NO * KC;                       // doubles per (atom, chunk) tile
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int stage_doubles = slotcap * TILE + 2 * KC;
+    double* sbuf = reinterpret_cast<double*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(sbuf + (size_t)stages * stage_doubles);
+    uint64_t* empty = full + stages;
+    int* slot_q = reinterpret_cast<int*>(empty + stages);     // [slotcap] list ordinal of slot s (s >= 1)
+    int* slot_atom = slot_q + slotcap;                        // [slotcap] atom of slot s (slot 0 = i)
+    int* owned_q = slot_atom + slotcap;                       // [cap] ordinals of all owned neighbours of i
+    __shared__ int n_owned_sh;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int g = lane >> 2, t = lane & 3;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NCW); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    uint32_t it = 0;     // running chunk counter (same sequence in producer and consumers)
+
+    for (int i = a0 + blockIdx.x; i < a1; i += gridDim.x) {
+        // ---- owned neighbours of i, in list order (warp 0, ordered compaction) ----
+        __syncthreads();
+        if (warp == 0) {
+            const int m = nn_size[i];
+            int cnt = 0;
+            for (int base = 0; base < m; base += 32) {
+                const int q = base + lane;
+                bool f = false;
+                if (q < m) f = owns(i, nn_list[(size_t)i * cap + q]);
+                const unsigned mask = __ballot_sync(0xffffffffu, f);
+                if (f) owned_q[cnt + __popc(mask & ((1u << lane) - 1u))] = q;
+                cnt += __popc(mask);
+            }
+            if (lane == 0) n_owned_sh = cnt;
+        }
+        __syncthreads();
+        const int n_owned = n_owned_sh;
+        // ---- sub-tasks of at most slotcap-1 neighbours (slot 0 is always atom i itself) ----
+        for (int first = 0; first == 0 || first < n_owned; first += slotcap - 1) {
+            const int nn = min(slotcap - 1, n_owned - first);
+            const int nslots = nn + 1;
+            __syncthreads();
+            for (int s = threadIdx.x; s < nslots; s += blockDim.x) {
+                if (s == 0) { slot_q[0] = -1; slot_atom[0] = i; }
+                else { const int q = owned_q[first + s - 1]; slot_q[s] = q; slot_atom[s] = nn_list[(size_t)i * cap + q]; }
+            }
+            __syncthreads();
+            const int nrows = nslots * NO;
+            const int ntiles = (nrows + 7) >> 3;
+
+            if (warp == NCW) {
+                // ===== producer warp: stream tiles of all slots for every chunk =====
+                const uint32_t bytes = (uint32_t)(nslots * TILE + 2 * KC) * 8u;
+                for (int ch = 0; ch < nchunks; ++ch, ++it) {
+                    const int st = it % stages;
+                    const uint32_t ph = (it / stages) & 1u;
+                    mbar_wait(&empty[st], ph ^ 1u);
+                    double* dstage = sbuf + (size_t)st * stage_doubles;
+                    if (lane == 0) {
+                        mbar_expect_tx(&full[st], bytes);
+                        bulk_g2s(dstage + slotcap * TILE, wf + (size_t)ch * KC, KC * 8, &full[st]);
+                        bulk_g2s(dstage + slotcap * TILE + KC, wfe + (size_t)ch * KC, KC * 8, &full[st]);
+                    }
+                    __syncwarp();
+                    const double* csrc = Ct + (size_t)ch * na * TILE;
+                    for (int s = lane; s < nslots; s += 32)
+                        bulk_g2s(dstage + s * TILE, csrc + (size_t)slot_atom[s] * TILE, TILE * 8, &full[st]);
+                }
+            } else {
+                // ===== consumer warps =====
+                double acc[MT][3][2];
+                int off[MT];
+#pragma unroll
+                for (int mt = 0; mt < MT; ++mt) {
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) { acc[mt][c][0] = 0.0; acc[mt][c][1] = 0.0; }
+                    const int R = 8 * (warp + NCW * mt) + g;
+                    const int sl = R / NO, r = R - sl * NO;
+                    off[mt] = (R < nrows) ? sl * TILE + 4 * r + t : t;
+                }
+                for (int ch = 0; ch < nchunks; ++ch, ++it) {
+                    const int st = it % stages;
+                    const uint32_t ph = (it / stages) & 1u;
+                    mbar_wait(&full[st], ph);
+                    const double* stg = sbuf + (size_t)st * stage_doubles;
+                    const double* wsm = stg + slotcap * TILE;
+#pragma unroll
+                    for (int s = 0; s < 4; ++s) {
+                        const double w_f = wsm[4 * s + t], w_e = wsm[KC + 4 * s + t];
+                        const double ci = stg[NO * 4 * s + 4 * g + t];            // C[i, mu = g][k]
+                        const double c8 = stg[NO * 4 * s + 32 + t];               // C[i, mu = 8][k]
+                        const double b0 = ci * w_f, b1 = ci * w_e;
+                        const double b2 = g == 0 ? c8 * w_f : (g == 1 ? c8 * w_e : 0.0);
+#pragma unroll
+                        for (int mt = 0; mt < MT; ++mt) {
+                            if (warp + NCW * mt < ntiles) {       // warp-uniform
+                                const double a = stg[off[mt] + NO * 4 * s];
+                                dmma884(acc[mt][0][0], acc[mt][0][1], a, b0);
+                                dmma884(acc[mt][1][0], acc[mt][1][1], a, b1);
+                                dmma884(acc[mt][2][0], acc[mt][2][1], a, b2);
+                            }
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&empty[st]);
+                }
+                // ---- epilogue: D(row R -> (slot, nu), col -> (matrix, mu)) -> block (i, slot)[mu + 9 nu] ----
+                const size_t b0i = (size_t)rowptr[i];
+#pragma unroll
+                for (int mt = 0; mt < MT; ++mt) {
+                    const int R = 8 * (warp + NCW * mt) + g;
+                    if (R < nrows) {
+                        const int sl = R / NO, nu = R - sl * NO;
+                        if (sl > 0 || first == 0) {     // the on-site block belongs to the first sub-task only
+                            const size_t blk = (b0i + (sl == 0 ? 0 : 1 + slot_q[sl])) * (NO * NO);
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int cc = 2 * t + e;
+                                rho[blk + cc + NO * nu] = acc[mt][0][e];
+                                rhoE[blk + cc + NO * nu] = acc[mt][1][e];
+                                if (cc == 0) rho[blk + 8 + NO * nu] = acc[mt][2][e];
+                                if (cc == 1) rhoE[blk + 8 + NO * nu] = acc[mt][2][e];
+                            }
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ---------------- simple CUDA-core kernel (cross-check of the DMMA path; also the generic-n_orb path) ----------------
+// one CTA per owned block; thread (mu,nu) accumulates over the kept states in their compacted order.
+template <int NO>
+__global__ void __launch_bounds__(128) density_simple_kernel(int na, int a0, int a1, int cap, long long N, int nkeep,
+                                                            const int* __restrict__ keep, const int* __restrict__ nn_size,
+                                                            const int* __restrict__ nn_list, const int* __restrict__ rowptr,
+                                                            const double* __restrict__ Ha, const double* __restrict__ wf,
+                                                            const double* __restrict__ wfe, double* __restrict__ rho,
+                                                            double* __restrict__ rhoE) {
+    const int i = a0 + blockIdx.y;
+    const int q = blockIdx.x;        // 0 = on-site
+    if (q > nn_size[i]) return;
+    const int j = q == 0 ? i : nn_list[(size_t)i * cap + q - 1];
+    if (q > 0 && !owns(i, j)) return;
+    if (threadIdx.x >= NO * NO) return;
+    const int mu = threadIdx.x % NO, nu = threadIdx.x / NO;
+    const double* ci = Ha + (size_t)i * NO + mu;
+    const double* cj = Ha + (size_t)j * NO + nu;
+    double s = 0.0, e = 0.0;
+    for (int kk = 0; kk < nkeep; ++kk) {
+        const size_t o = (size_t)keep[kk] * N;
+        const double a = ci[o], b = cj[o];
+        s += (wf[kk] * a) * b;
+        e += (wfe[kk] * a) * b;
+    }
+    const size_t blk = ((size_t)rowptr[i] + q) * (NO * NO);
+    rho[blk + mu + NO * nu] = s;
+    rhoE[blk + mu + NO * nu] = e;
+}
+
+// non-owner blocks = transpose of the owner's block
+template <int NO>
+__global__ void mirror_blocks_kernel(int na, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
+                                     const int* __restrict__ rev, const int* __restrict__ rowptr,
+                                     double* __restrict__ rho, double* __restrict__ rhoE) {
+    const int i = blockIdx.y;
+    const int q = blockIdx.x;
+    if (q >= nn_size[i]) return;
+    const size_t e = (size_t)i * cap + q;
+    const int j = nn_list[e];
+    if (owns(i, j)) return;
+    const int rv = rev[e];
+    if (rv < 0) return;
+    if (threadIdx.x >= NO * NO) return;
+    const int mu = threadIdx.x % NO, nu = threadIdx.x / NO;
+    const size_t dst = ((size_t)rowptr[i] + 1 + q) * (NO * NO) + mu + NO * nu;
+    const size_t src = ((size_t)rowptr[j] + 1 + rv) * (NO * NO) + nu + NO * mu;
+    rho[dst] = rho[src];
+    rhoE[dst] = rhoE[src];
+}
+
+template <int NO>
+int run_density(xtb_ctx* c) {
+    const int na = c->na;
+    const long long N = (long long)na * NO;
+    const long long K = c->K;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_keep, sizeof(int) * K))) return rc;
+    if ((rc = xtb_reserve(c, c->d_wf, sizeof(double) * (K + KC)))) return rc;
+    if ((rc = xtb_reserve(c, c->d_wfe, sizeof(double) * (K + KC)))) return rc;
+    if ((rc = xtb_reserve(c, c->d_nkeep, 16))) return rc;
+    if ((rc = xtb_reserve(c, c->d_rho, sizeof(double) * NO * NO * (size_t)c->n_blocks))) return rc;
+    if ((rc = xtb_reserve(c, c->d_rhoE, sizeof(double) * NO * NO * (size_t)c->n_blocks))) return rc;
+    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    keep_kernel<<<1, 1024, 0, c->stream>>>(K, c->d_fe, c->d_Ei, c->f_cut, (int*)c->d_keep.p, (double*)c->d_wf.p,
+                                           (double*)c->d_wfe.p, (int*)c->d_nkeep.p);
+    XTB_LAUNCH_CHECK(c);
+    int nkeep = 0;
+    XTB_CUDA(c, cudaMemcpyAsync(&nkeep, c->d_nkeep.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->k_kept = nkeep;
+    const int nchunks = (nkeep + KC - 1) / KC;
+    const int kpad = nchunks * KC;
+    const int nown = c->a1 - c->a0;
+    // blocks that no kernel below writes (atoms outside [a0,a1)) must not hold garbage
+    XTB_CUDA(c, cudaMemsetAsync(c->d_rho.p, 0, sizeof(double) * NO * NO * (size_t)c->n_blocks, c->stream));
+    XTB_CUDA(c, cudaMemsetAsync(c->d_rhoE.p, 0, sizeof(double) * NO * NO * (size_t)c->n_blocks, c->stream));
+    bool use_dmma = (c->density_impl == 1) && NO == 9 && nown > 0;
+    if (use_dmma) {
+        if (kpad > nkeep) {
+            pad_weights_kernel<<<1, KC, 0, c->stream>>>(nkeep, kpad, (double*)c->d_wf.p, (double*)c->d_wfe.p);
+            XTB_LAUNCH_CHECK(c);
+        }
+        if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)kpad * N + 1024))) return rc;
+        if (nchunks > 0) {
+            dim3 grid(nchunks, (na + 31) / 32);
+            ct_tile_kernel<NO><<<grid, 256, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, c->d_Ha, (double*)c->d_Ct.p);
+            XTB_LAUNCH_CHECK(c);
+        }
+        XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+        // slot capacity / stages from the shared-memory budget
+        constexpr int MT = 7;
+        int slotcap = (c->max_nn + 1) / 2 + 9;                 // balanced ownership: ~half the neighbours (+ slack), + self
+        if (slotcap > MT * NCW * 8 / NO) slotcap = MT * NCW * 8 / NO;     // rows must fit MT tiles per warp
+        if (slotcap > c->max_nn + 1) slotcap = c->max_nn + 1;
+        if (slotcap < 2) slotcap = 2;
+        const size_t tile_b = (size_t)NO * KC * 8;
+        const size_t fixed = 2 * 8 * 8 + sizeof(int) * (2 * (size_t)slotcap + c->cap) + 64;
+        const size_t budget = 220 * 1024;
+        int stages = 4;
+        while (stages > 2 && stages * (slotcap * tile_b + 2 * KC * 8) + fixed > budget) --stages;
+        while (stages * (slotcap * tile_b + 2 * KC * 8) + fixed > budget && slotcap > 2) --slotcap;
+        const size_t smem = stages * (slotcap * tile_b + 2 * KC * 8) + 2 * 8 * stages + sizeof(int) * (2 * (size_t)slotcap + c->cap) + 64;
+        auto kern = density_dmma_kernel<NO == 9 ? 9 : 9, MT>;
+        XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int grid = c->sm_count < nown ? c->sm_count : nown;
+        kern<<<grid, NTHREADS, smem, c->stream>>>(na, c->a0, c->a1, c->cap, slotcap, stages, nchunks, (const int*)c->d_nn_size.p,
+                                                  (const int*)c->d_nn_list.p, (const int*)c->d_rowptr.p, (const double*)c->d_Ct.p,
+                                                  (const double*)c->d_wf.p, (const double*)c->d_wfe.p, (double*)c->d_rho.p,
+                                                  (double*)c->d_rhoE.p);
+        XTB_LAUNCH_CHECK(c);
+        c->density_slotcap = slotcap; c->density_stages = stages;
+    } else if (nown > 0) {
+        XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+        dim3 grid(c->max_nn + 1, nown);
+        density_simple_kernel<NO><<<grid, 128, 0, c->stream>>>(na, c->a0, c->a1, c->cap, N, nkeep, (const int*)c->d_keep.p,
+                                                               (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                               (const int*)c->d_rowptr.p, c->d_Ha, (const double*)c->d_wf.p,
+                                                               (const double*)c->d_wfe.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
+        XTB_LAUNCH_CHECK(c);
+    } else {
+        XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+    }
+    XTB_CUDA(c, cudaEventRecord(c->ev_mid2, c->stream));
+    // mirror (complete only when every owner block is local: single-GPU, or after the caller's allgather)
+    if (c->a0 == 0 && c->a1 == na && c->max_nn > 0) {
+        dim3 grid(c->max_nn, na);
+        mirror_blocks_kernel<NO><<<grid, 96, 0, c->stream>>>(na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                             (const int*)c->d_rev.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p,
+                                                             (double*)c->d_rhoE.p);
+        XTB_LAUNCH_CHECK(c);
+    }
+    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f, msk = 0.f;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    cudaEventElapsedTime(&msk, c->ev_mid, c->ev_mid2);
+    c->stage_ms[3] = ms;
+    c->stage_ms[7] = msk;       // main contraction kernel alone
+    c->have_density = true;
+    return XTB_OK;
+}
+
+}  // namespace
+
+int xtb_impl_density(xtb_ctx* c) {
+    if (c->n_orb == 9) return run_density<9>(c);
+    if (c->n_orb == 4) return run_density<4>(c);
+    XTB_FAIL(c, XTB_EINVAL, "density: unsupported n_orb %d", c->n_orb);
+}
+
+int xtb_impl_mirror_density(xtb_ctx* c) {
+    if (c->max_nn <= 0) return XTB_OK;
+    dim3 grid(c->max_nn, c->na);
+    if (c->n_orb == 9)
+        mirror_blocks_kernel<9><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                            (const int*)c->d_rev.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
+    else
+        mirror_blocks_kernel<4><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                            (const int*)c->d_rev.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
+    XTB_LAUNCH_CHECK(c);
+    return XTB_OK;
+}

@@ -1,0 +1,227 @@
+// S1 -- neighbour list on the device.
+//
+// Replaces get_near_neighbours -> Find_nearest_neighbours (Source_files/Atomic_tools.f90:562,4230-4294)
+// with the minimum-image search of shortest_distance_OLD (Atomic_tools.f90:4028-4131).
+// Semantics kept bit-exactly:
+//   * x = sum_k (S_i(k) - S_j(k) + zb(k)) * supce(k,c), summed k = 1..3 starting from 0 (:4098-4104),
+//     no FMA contraction (explicit __dmul_rn / __dadd_rn);
+//   * 27 images scanned zb1, zb2, zb3 ascending, replace if r1 <= a_r (:4107); start value = image 0 (:4064-4072);
+//   * neighbour iff a_r < rm (:4255); appended in ascending j (ordered warp compaction).
+// B200 mapping: one warp per atom i, lanes stride over j; the reference's serial O(27 Na^2)
+// double loop becomes Na warps; sqrt is only taken when the squared distances cannot decide
+// the `<=` (exact: sqrt is monotone, and a relative gap of 1e-14 in r^2 is far above 1 ulp).
+#include "xtb_ctx.h"
+
+namespace {
+
+__device__ __forceinline__ double sum3(double a, double b, double c) {
+    // ((0 + a) + b) + c  -- the reference accumulates into a zero-initialised variable
+    return __dadd_rn(__dadd_rn(__dadd_rn(0.0, a), b), c);
+}
+__device__ __forceinline__ double norm2(double x, double y, double z) {
+    return __dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z));
+}
+
+struct MinImage {
+    double x, y, z, r, sx, sy, sz;
+};
+
+// h[k + 3*c] = supce(k+1, c+1)
+__device__ __forceinline__ MinImage min_image(const double Si[3], const double Sj[3], const double* __restrict__ h) {
+    double ds[3] = {__dsub_rn(Si[0], Sj[0]), __dsub_rn(Si[1], Sj[1]), __dsub_rn(Si[2], Sj[2])};
+    // products p[k][z][c] = (ds_k + zb) * supce(k,c), zb = -1,0,1 -> z = 0,1,2
+    double dsz[3][3];
+    double p[3][3][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int z = 0; z < 3; ++z) {
+            dsz[k][z] = __dadd_rn(ds[k], (double)(z - 1));
+#pragma unroll
+            for (int c = 0; c < 3; ++c) p[k][z][c] = __dmul_rn(dsz[k][z], h[k + 3 * c]);
+        }
+    // start: un-shifted image, from ds itself (:4064-4072)
+    double bx = sum3(__dmul_rn(ds[0], h[0]), __dmul_rn(ds[1], h[1]), __dmul_rn(ds[2], h[2]));
+    double by = sum3(__dmul_rn(ds[0], h[3]), __dmul_rn(ds[1], h[4]), __dmul_rn(ds[2], h[5]));
+    double bz = sum3(__dmul_rn(ds[0], h[6]), __dmul_rn(ds[1], h[7]), __dmul_rn(ds[2], h[8]));
+    double bq = norm2(bx, by, bz);
+    double br = -1.0;                 // sqrt(bq) computed lazily
+    int b1 = 1, b2 = 1, b3 = 1;       // image indices of the current best (z index); start = "no zb added"
+    bool shifted = false;             // whether sx,sy,sz carry a zb (even zb = 0 adds "+0.0")
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                double x0 = sum3(p[0][i][0], p[1][j][0], p[2][k][0]);
+                double y0 = sum3(p[0][i][1], p[1][j][1], p[2][k][1]);
+                double z0 = sum3(p[0][i][2], p[1][j][2], p[2][k][2]);
+                double q = norm2(x0, y0, z0);
+                bool take;
+                if (q <= bq) take = true;                        // sqrt monotone => r1 <= a_r
+                else if (q > bq * (1.0 + 1e-14)) take = false;   // r1 > a_r for sure
+                else {                                           // undecidable on squares: compare the rounded roots
+                    if (br < 0.0) br = __dsqrt_rn(bq);
+                    take = (__dsqrt_rn(q) <= br);
+                }
+                if (take) { bx = x0; by = y0; bz = z0; bq = q; br = -1.0; b1 = i; b2 = j; b3 = k; shifted = true; }
+            }
+    MinImage o;
+    o.x = bx; o.y = by; o.z = bz; o.r = __dsqrt_rn(bq);
+    o.sx = shifted ? dsz[0][b1] : ds[0];
+    o.sy = shifted ? dsz[1][b2] : ds[1];
+    o.sz = shifted ? dsz[2][b3] : ds[2];
+    return o;
+}
+
+__global__ void __launch_bounds__(256) nn_build_kernel(int na, const double* __restrict__ S, const double* __restrict__ hmat,
+                                                      double rm, int cap, int* __restrict__ nn_size,
+                                                      int* __restrict__ nn_list, double* __restrict__ nn_dist,
+                                                      double* __restrict__ nn_dist_s, int* __restrict__ max_nn) {
+    __shared__ double h[9];
+    if (threadIdx.x < 9) h[threadIdx.x] = hmat[threadIdx.x];
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= na) return;
+    const double Si[3] = {S[3 * i], S[3 * i + 1], S[3 * i + 2]};
+    int count = 0;
+    for (int base = 0; base < na; base += 32) {
+        const int j = base + lane;
+        bool isn = false;
+        MinImage mi;
+        if (j < na && j != i) {
+            const double Sj[3] = {S[3 * j], S[3 * j + 1], S[3 * j + 2]};
+            mi = min_image(Si, Sj, h);
+            isn = mi.r < rm;
+        }
+        const unsigned mask = __ballot_sync(0xffffffffu, isn);
+        if (isn) {
+            const int pos = count + __popc(mask & ((1u << lane) - 1u));
+            if (pos < cap) {
+                const size_t e = (size_t)i * cap + pos;
+                nn_list[e] = j;
+                double4 d4 = make_double4(mi.x, mi.y, mi.z, mi.r);
+                *reinterpret_cast<double4*>(nn_dist + 4 * e) = d4;
+                nn_dist_s[3 * e] = mi.sx; nn_dist_s[3 * e + 1] = mi.sy; nn_dist_s[3 * e + 2] = mi.sz;
+            }
+        }
+        count += __popc(mask);
+    }
+    if (lane == 0) {
+        nn_size[i] = count < cap ? count : cap;
+        atomicMax(max_nn, count);
+    }
+}
+
+// rowptr[i] = first block of atom i (blocks: on-site, then list order); rowptr[na] = n_blocks.
+// rev[e] = position of atom i in the list of its neighbour nn_list[e] (lists ascend in j) or -1.
+__global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* __restrict__ rowptr) {
+    __shared__ int carry;
+    __shared__ int buf[1024];
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < na; base += 1024) {
+        int i = base + threadIdx.x;
+        int v = i < na ? nn_size[i] + 1 : 0;
+        buf[threadIdx.x] = v;
+        __syncthreads();
+        for (int off = 1; off < 1024; off <<= 1) {
+            int t = threadIdx.x >= off ? buf[threadIdx.x - off] : 0;
+            __syncthreads();
+            buf[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (i < na) rowptr[i] = carry + buf[threadIdx.x] - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += buf[1023];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) rowptr[na] = carry;
+}
+
+__global__ void nn_rev_kernel(int na, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
+                              int* __restrict__ rev) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (long long)na * cap) return;
+    const int i = (int)(t / cap), k = (int)(t % cap);
+    if (k >= nn_size[i]) { rev[t] = -1; return; }
+    const int j = nn_list[t];
+    const int* L = nn_list + (size_t)j * cap;
+    int lo = 0, hi = nn_size[j] - 1, pos = -1;
+    while (lo <= hi) {
+        int mid = (lo + hi) >> 1;
+        int v = L[mid];
+        if (v == i) { pos = mid; break; }
+        if (v < i) lo = mid + 1; else hi = mid - 1;
+    }
+    rev[t] = pos;
+}
+
+}  // namespace
+
+int xtb_impl_neighbours(xtb_ctx* c, double rm) {
+    const int na = c->na;
+    if (na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_neighbours: no system set");
+    // capacity guess from the mean density (grown and re-run if exceeded)
+    if (c->cap <= 0) {
+        const double* h = c->h_supce;
+        double vol = h[0] * (h[4] * h[8] - h[5] * h[7]) - h[3] * (h[1] * h[8] - h[2] * h[7]) + h[6] * (h[1] * h[5] - h[2] * h[4]);
+        vol = vol < 0 ? -vol : vol;
+        double est = vol > 0 ? na * (4.18879020478639 * rm * rm * rm) / vol : na;
+        int cap = (int)(est * 1.5) + 16;
+        if (cap > na - 1) cap = na - 1;
+        if (cap < 1) cap = 1;
+        c->cap = cap;
+    }
+    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    for (int attempt = 0; attempt < 4; ++attempt) {
+        const int cap = c->cap;
+        const size_t ne = (size_t)na * cap;
+        int rc;
+        if ((rc = xtb_reserve(c, c->d_nn_size, sizeof(int) * na))) return rc;
+        if ((rc = xtb_reserve(c, c->d_nn_list, sizeof(int) * ne))) return rc;
+        if ((rc = xtb_reserve(c, c->d_rev, sizeof(int) * ne))) return rc;
+        if ((rc = xtb_reserve(c, c->d_nn_dist, sizeof(double) * 4 * ne))) return rc;
+        if ((rc = xtb_reserve(c, c->d_nn_dist_s, sizeof(double) * 3 * ne))) return rc;
+        if ((rc = xtb_reserve(c, c->d_rowptr, sizeof(int) * (na + 1)))) return rc;
+        if ((rc = xtb_reserve(c, c->d_maxnn, sizeof(int) * 4))) return rc;
+        if ((rc = xtb_reserve(c, c->d_scratch, 256))) return rc;
+        XTB_CUDA(c, cudaMemsetAsync(c->d_maxnn.p, 0, sizeof(int) * 4, c->stream));
+        XTB_CUDA(c, cudaMemcpyAsync(c->d_scratch.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
+        const int warps_per_block = 8;
+        nn_build_kernel<<<(na + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, c->stream>>>(
+            na, (const double*)c->d_S.p, (const double*)c->d_scratch.p, rm, cap, (int*)c->d_nn_size.p,
+            (int*)c->d_nn_list.p, (double*)c->d_nn_dist.p, (double*)c->d_nn_dist_s.p, (int*)c->d_maxnn.p);
+        XTB_LAUNCH_CHECK(c);
+        int mx = 0;
+        XTB_CUDA(c, cudaMemcpyAsync(&mx, c->d_maxnn.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (mx <= cap) { c->max_nn = mx; break; }
+        if (attempt == 3) XTB_FAIL(c, XTB_ECAPACITY, "neighbour capacity %d exceeded (%d) after retries", cap, mx);
+        c->cap = mx + 8 > na - 1 ? na - 1 : mx + 8;
+        if (c->cap < mx) c->cap = mx;
+    }
+    nn_rowptr_kernel<<<1, 1024, 0, c->stream>>>(na, (const int*)c->d_nn_size.p, (int*)c->d_rowptr.p);
+    XTB_LAUNCH_CHECK(c);
+    {
+        const long long tot = (long long)na * c->cap;
+        nn_rev_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c->stream>>>(na, c->cap, (const int*)c->d_nn_size.p,
+                                                                           (const int*)c->d_nn_list.p, (int*)c->d_rev.p);
+        XTB_LAUNCH_CHECK(c);
+    }
+    int nb = 0;
+    XTB_CUDA(c, cudaMemcpyAsync(&nb, (int*)c->d_rowptr.p + na, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->stage_ms[1] = ms;
+    c->n_blocks = nb;
+    c->n_pairs = nb - na;
+    c->rm = rm;
+    c->have_neigh = true;
+    c->have_HS = c->have_density = c->have_dens = false;
+    return XTB_OK;
+}

@@ -1,0 +1,267 @@
+// S2 -- NRL radial functions + Slater-Koster H/S block assembly + dense panels.
+//
+// Replaces Construct_Vij_NRL_OMP (Source_files/TB_NRL.f90:2116-2244), Hamil_tot_NRL's assembly part
+// (:226-397) with Hamilton_one_NRL (:1798-1856), rho_NRL (:2248-2287), Get_overlap_S_matrix (:1724-1744)
+// and KS_sp3d5 (TB_Koster_Slater.f90:5234-5348).
+//
+// Reference data flow: dense M_Vij/M_SVij (Na,Na,10) tables -> 9x9 blocks scattered into zero-filled
+// dense Hij,Sij (N,N) -> mirror -> *g_Ry.  Here:
+//   k1  nrl_dens_kernel    one thread per atom: embedded density rho_j (list order, as the reference sums)
+//   k2  nrl_blocks_kernel  one thread per (block, matrix): radial functions in registers, SK rotation in
+//                          registers, 81 entries to the block-sparse store Hblk/Sblk (block (j,q) holds
+//                          rows of neighbour i, columns of outer atom j -- the reference placement)
+//   k3  dense_panel_kernel one CTA per owned atom j: writes the 9 dense columns of j for H and S, every
+//                          element exactly once (zeros included), fully coalesced streaming stores.
+//                          Algorithmic bytes = 2*8*N*(9*n_owned): the HBM-write roofline of this stage.
+// Semantics kept: pair (a>b) evaluated once with TB(kind(b),kind(a)) and r from the list of b (:2151-2159);
+// block (rows a, cols b) uses the direction cosines of a's list entry for b (M_lmn(:,a,b), :1849);
+// the other triangle is the element transpose (:369-390); |S| <= 1e-12 -> 0 (:359); H *= g_Ry (:394).
+#include "nrl_device.cuh"
+#include "sk_device.cuh"
+
+namespace {
+
+__global__ void nrl_dens_kernel(int na, int cap, int n_kinds, const int* __restrict__ koa, const int* __restrict__ nn_size,
+                                const int* __restrict__ nn_list, const double* __restrict__ nn_dist,
+                                const xtb_nrl_pair* __restrict__ TB, double* __restrict__ dens) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= na) return;
+    double rho = 0.0;
+    const int m = nn_size[j];
+    for (int q = 0; q < m; ++q) {
+        const size_t e = (size_t)j * cap + q;
+        const int i = nn_list[e];
+        const xtb_nrl_pair& P = TB[koa[j] + n_kinds * koa[i]];
+        const double r = nn_dist[4 * e + 3] * XTB_G_A2AU;
+        double X, dX;
+        nrl::envelope(P, r, X, dX);
+        rho += X;
+    }
+    dens[j] = rho;
+}
+
+// one thread per (block, mat); block b of atom j: q = b - rowptr[j]; q == 0 on-site, else list entry q-1
+__global__ void __launch_bounds__(128) nrl_blocks_kernel(int na, int a0, int a1, int cap, int n_kinds,
+                                                        const int* __restrict__ koa, const int* __restrict__ nn_size,
+                                                        const int* __restrict__ nn_list, const int* __restrict__ rev,
+                                                        const double* __restrict__ nn_dist, const int* __restrict__ rowptr,
+                                                        const xtb_nrl_pair* __restrict__ TB, const double* __restrict__ dens,
+                                                        double* __restrict__ Hblk, double* __restrict__ Sblk) {
+    // thread -> (atom j, slot q, mat); ELL indexing keeps the decode cheap: t = ((j-a0)*(cap+1) + q)*2 + mat
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long per_atom = 2LL * (cap + 1);
+    const int j = a0 + (int)(t / per_atom);
+    if (j >= a1) return;
+    const int rem = (int)(t % per_atom);
+    const int q = rem >> 1, mat = rem & 1;
+    if (q > nn_size[j]) return;
+    double* out = (mat == 0 ? Hblk : Sblk) + ((size_t)rowptr[j] + q) * 81;
+    if (q == 0) {   // on-site: diag(h_s, h_p x3, h_t2g x3, h_eg x2) * g_Ry ; S = I
+        const xtb_nrl_pair& P = TB[koa[j] + n_kinds * koa[j]];
+        const double rho = dens[j];
+        double hv[4];
+#pragma unroll
+        for (int s = 0; s < 4; ++s) hv[s] = nrl::onsite(rho, P.al[s], P.bl[s], P.cl[s], P.dl[s]) * XTB_G_RY;
+        for (int e = 0; e < 81; ++e) out[e] = 0.0;
+        for (int o = 0; o < 9; ++o) out[o * 10] = mat == 0 ? hv[nrl::onsite_set(o, P.ind_split)] : 1.0;
+        return;
+    }
+    const size_t e = (size_t)j * cap + (q - 1);
+    const int i = nn_list[e];
+    const int rv = rev[e];
+    if (rv < 0) {   // asymmetric list: the reference's dense tables hold zeros there
+        for (int x = 0; x < 81; ++x) out[x] = 0.0;
+        return;
+    }
+    const size_t ei = (size_t)i * cap + rv;      // entry of j in the list of i
+    // radial: unique pair evaluated from the smaller index' entry with TB(kind(small), kind(large))
+    const int small = i < j ? i : j, large = i < j ? j : i;
+    const double r = nn_dist[4 * (i < j ? ei : e) + 3] * XTB_G_A2AU;
+    const xtb_nrl_pair& P = TB[koa[small] + n_kinds * koa[large]];
+    double V[10], dV[10];
+    nrl::radial10(P, mat, r, V, dV);
+    // direction cosines: the entry of the LARGER index atom (rows) for the smaller (cols)
+    const size_t el = (i > j) ? ei : e;
+    const double4 d4 = *reinterpret_cast<const double4*>(nn_dist + 4 * el);
+    const double l = d4.x / d4.w, m = d4.y / d4.w, n = d4.z / d4.w;
+    double up[45];
+    sk::block_sp3d5_upper<double>(V, l, m, n, up);
+    const double scale = mat == 0 ? XTB_G_RY : 1.0;
+    // computed block C has rows = larger atom, cols = smaller atom.  Stored block = (rows i, cols j):
+    // i > j: stored = C ; i < j: stored = C^T.
+    const bool direct = i > j;
+#pragma unroll
+    for (int a = 0; a < 9; ++a)
+#pragma unroll
+        for (int b = a; b < 9; ++b) {
+            double u = up[sk::ut(a, b)];
+            if (mat == 1 && fabs(u) <= 1e-12) u = 0.0;
+            u *= scale;
+            const double lo = (a == b) ? u : u * sk::lower_sign(a, b);
+            // C(a,b) = u, C(b,a) = lo
+            if (direct) { out[a + 9 * b] = u; if (a != b) out[b + 9 * a] = lo; }
+            else        { out[b + 9 * a] = u; if (a != b) out[a + 9 * b] = lo; }
+        }
+}
+
+}  // namespace
+
+// Generic: dense column panels of the owned atoms from a block-sparse store.
+// blk(b)[mu + no*nu]: mu = orbital of the ROW atom (neighbour i, or j itself for the first block), nu = orbital of j.
+template <int NO, bool TR>
+__global__ void __launch_bounds__(256) dense_panel_kernel(int na, int a0, int cap, const int* __restrict__ nn_size,
+                                                         const int* __restrict__ nn_list, const int* __restrict__ rowptr,
+                                                         const double* __restrict__ Ablk, const double* __restrict__ Bblk,
+                                                         double* __restrict__ A, double* __restrict__ B) {
+    extern __shared__ int sm_i[];
+    int* nbl = sm_i;             // [cap]
+    int* slot = sm_i + cap;      // [256]
+    const int j = a0 + blockIdx.x;
+    const int m = nn_size[j];
+    for (int q = threadIdx.x; q < m; q += blockDim.x) nbl[q] = nn_list[(size_t)j * cap + q];
+    __syncthreads();
+    const size_t N = (size_t)na * NO;
+    const size_t b0 = (size_t)rowptr[j];
+    constexpr int TA = 256;      // row atoms per tile
+    for (int tile = 0; tile < na; tile += TA) {
+        {
+            const int ia = tile + threadIdx.x;
+            int s = -1;
+            if (ia == j) s = 0;
+            else if (ia < na) {
+                int lo = 0, hi = m - 1;
+                while (lo <= hi) {
+                    const int mid = (lo + hi) >> 1;
+                    const int v = nbl[mid];
+                    if (v == ia) { s = mid + 1; break; }
+                    if (v < ia) lo = mid + 1; else hi = mid - 1;
+                }
+            }
+            slot[threadIdx.x] = s;
+        }
+        __syncthreads();
+        const int nat = min(TA, na - tile);
+        const int nrow = nat * NO;
+        for (int c = 0; c < NO; ++c) {
+            const size_t col = ((size_t)j * NO + c) * N + (size_t)tile * NO;
+            for (int e = threadIdx.x; e < nrow; e += blockDim.x) {
+                const int il = e / NO, orb = e - il * NO;
+                const int s = slot[il];
+                double va = 0.0, vb = 0.0;
+                if (s >= 0) {
+                    const size_t off = (b0 + s) * (NO * NO) + (TR ? c + NO * orb : orb + NO * c);
+                    va = Ablk[off];
+                    if (Bblk) vb = Bblk[off];
+                }
+                __stcs(A + col + e, va);
+                if (B) __stcs(B + col + e, vb);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+template <int NO>
+static void launch_panel(xtb_ctx* c, int nown, size_t smem, const double* Ablk, const double* Bblk, double* A, double* B, bool tr) {
+    if (tr)
+        dense_panel_kernel<NO, true><<<nown, 256, smem, c->stream>>>(c->na, c->a0, c->cap, (const int*)c->d_nn_size.p,
+                                                                     (const int*)c->d_nn_list.p, (const int*)c->d_rowptr.p, Ablk, Bblk, A, B);
+    else
+        dense_panel_kernel<NO, false><<<nown, 256, smem, c->stream>>>(c->na, c->a0, c->cap, (const int*)c->d_nn_size.p,
+                                                                      (const int*)c->d_nn_list.p, (const int*)c->d_rowptr.p, Ablk, Bblk, A, B);
+}
+
+int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, double* A, double* B, bool tr) {
+    const int nown = c->a1 - c->a0;
+    if (nown <= 0) return XTB_OK;
+    const size_t smem = sizeof(int) * (c->cap + 256);
+    if (c->n_orb == 9) launch_panel<9>(c, nown, smem, Ablk, Bblk, A, B, tr);
+    else if (c->n_orb == 4) launch_panel<4>(c, nown, smem, Ablk, Bblk, A, B, tr);
+    else if (c->n_orb == 1) launch_panel<1>(c, nown, smem, Ablk, Bblk, A, B, tr);
+    else XTB_FAIL(c, XTB_EINVAL, "unsupported n_orb %d", c->n_orb);
+    XTB_LAUNCH_CHECK(c);
+    return XTB_OK;
+}
+
+// compact per-entry tables for the drop-in outputs of xtb_radial (never used by the device hot path)
+__global__ void nrl_tables_kernel(int na, int cap, int n_kinds, const int* __restrict__ koa, const int* __restrict__ nn_size,
+                                  const int* __restrict__ nn_list, const int* __restrict__ rev, const double* __restrict__ nn_dist,
+                                  const xtb_nrl_pair* __restrict__ TB, const double* __restrict__ hmat,
+                                  double* __restrict__ rad, double* __restrict__ geo) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (long long)na * cap) return;
+    const int j = (int)(t / cap), q = (int)(t % cap);
+    if (q >= nn_size[j]) return;
+    const int i = nn_list[t];
+    const double4 d4 = *reinterpret_cast<const double4*>(nn_dist + 4 * t);
+    double* g = geo + 9 * t;
+    const double l = d4.x / d4.w, m = d4.y / d4.w, n = d4.z / d4.w;
+    g[0] = l; g[1] = m; g[2] = n;                               // M_lmn   TB.f90:3512-3514
+    g[3] = l / d4.w; g[4] = m / d4.w; g[5] = n / d4.w;          // M_xrr   :3516-3518
+    for (int a = 0; a < 3; ++a) g[6 + a] = d4.x * hmat[a] + d4.y * hmat[a + 3] + d4.z * hmat[a + 6];   // M_x1 :3505-3507
+    double* o = rad + 40 * t;
+    const int rv = rev[t];
+    if (rv < 0) { for (int c = 0; c < 40; ++c) o[c] = 0.0; return; }
+    const int small = i < j ? i : j, large = i < j ? j : i;
+    const double r = (j < i ? d4.w : nn_dist[4 * ((size_t)i * cap + rv) + 3]) * XTB_G_A2AU;
+    const xtb_nrl_pair& P = TB[koa[small] + n_kinds * koa[large]];
+    nrl::radial10(P, 0, r, o, o + 10);
+    nrl::radial10(P, 1, r, o + 20, o + 30);
+}
+
+int xtb_impl_nrl_tables(xtb_ctx* c, double* d_rad, double* d_geo) {
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_hdev, sizeof(double) * 9))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
+    const long long tot = (long long)c->na * c->cap;
+    nrl_tables_kernel<<<(unsigned)((tot + 127) / 128), 128, 0, c->stream>>>(c->na, c->cap, c->n_kinds, (const int*)c->d_koa.p,
+                                                                           (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                                           (const int*)c->d_rev.p, (const double*)c->d_nn_dist.p,
+                                                                           (const xtb_nrl_pair*)c->d_params.p, (const double*)c->d_hdev.p,
+                                                                           d_rad, d_geo);
+    XTB_LAUNCH_CHECK(c);
+    return XTB_OK;
+}
+
+int xtb_impl_nrl_dens(xtb_ctx* c) {
+    const int na = c->na;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_dens, sizeof(double) * na))) return rc;
+    nrl_dens_kernel<<<(na + 127) / 128, 128, 0, c->stream>>>(na, c->cap, c->n_kinds, (const int*)c->d_koa.p,
+                                                             (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                             (const double*)c->d_nn_dist.p, (const xtb_nrl_pair*)c->d_params.p,
+                                                             (double*)c->d_dens.p);
+    XTB_LAUNCH_CHECK(c);
+    c->have_dens = true;
+    return XTB_OK;
+}
+
+int xtb_impl_nrl_assemble(xtb_ctx* c) {
+    const int na = c->na;
+    const size_t N = (size_t)na * 9;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 81 * (size_t)c->n_blocks))) return rc;
+    if ((rc = xtb_reserve(c, c->d_Sblk, sizeof(double) * 81 * (size_t)c->n_blocks))) return rc;
+    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
+    if ((rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
+    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    if ((rc = xtb_impl_nrl_dens(c))) return rc;
+    const int nown = c->a1 - c->a0;
+    const long long nthreads = 2LL * (c->cap + 1) * nown;
+    nrl_blocks_kernel<<<(unsigned)((nthreads + 127) / 128), 128, 0, c->stream>>>(
+        na, c->a0, c->a1, c->cap, c->n_kinds, (const int*)c->d_koa.p, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+        (const int*)c->d_rev.p, (const double*)c->d_nn_dist.p, (const int*)c->d_rowptr.p, (const xtb_nrl_pair*)c->d_params.p,
+        (const double*)c->d_dens.p, (double*)c->d_Hblk.p, (double*)c->d_Sblk.p);
+    XTB_LAUNCH_CHECK(c);
+    XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+    if ((rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, (const double*)c->d_Sblk.p, (double*)c->d_H.p, (double*)c->d_S2.p, false))) return rc;
+    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f, ms2 = 0.f;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    cudaEventElapsedTime(&ms2, c->ev_mid, c->ev1);
+    c->stage_ms[2] = ms;
+    c->stage_ms[6] = ms2;     // dense panel kernel alone
+    c->have_HS = true;
+    return XTB_OK;
+}

@@ -1,0 +1,404 @@
+// C ABI of libxtb_b200 (include/xtb_b200.h): argument checking, host<->device staging in the
+// reference's array shapes, and dispatch on the TB parametrisation (the `select type` arms of
+// Source_files/TB.f90:247-317,459-487 collapse to ctx->tb).  All arithmetic is in the stage files.
+#include "xtb_ctx.h"
+#include <cstdlib>
+#include <cstring>
+#include <new>
+
+int xtb_reserve(xtb_ctx* c, DevBuf& b, size_t bytes) {
+    if (bytes == 0) bytes = 16;
+    if (b.bytes >= bytes) return XTB_OK;
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr; b.bytes = 0;
+    cudaError_t e = cudaMalloc(&b.p, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        XTB_FAIL(c, XTB_ENOMEM, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
+    }
+    b.bytes = bytes;
+    return XTB_OK;
+}
+void xtb_free(DevBuf& b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr; b.bytes = 0;
+}
+
+extern "C" {
+
+const char* xtb_version(void) { return "xtb_b200 0.1 (sm_100a, FP64)"; }
+
+int xtb_create(xtb_ctx** out, int device) {
+    if (!out) return XTB_EINVAL;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) { cudaGetLastError(); return XTB_ENODEV; }
+    if (device < 0 || device >= n) return XTB_ENODEV;
+    if (cudaSetDevice(device) != cudaSuccess) { cudaGetLastError(); return XTB_ENODEV; }
+    xtb_ctx* c = new (std::nothrow) xtb_ctx();
+    if (!c) return XTB_ENOMEM;
+    c->device = device;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return XTB_ECUDA; }
+    c->own_stream = true;
+    cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1); cudaEventCreate(&c->ev_mid); cudaEventCreate(&c->ev_mid2);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+    const char* impl = getenv("XTB_DENSITY_IMPL");
+    if (impl) c->density_impl = atoi(impl);
+    *out = c;
+    return XTB_OK;
+}
+
+int xtb_destroy(xtb_ctx* c) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf* all[] = {&c->d_params, &c->d_koa, &c->d_S, &c->d_nn_size, &c->d_nn_list, &c->d_nn_dist, &c->d_nn_dist_s, &c->d_rev,
+                     &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
+                     &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
+                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab};
+    for (DevBuf* b : all) xtb_free(*b);
+    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return XTB_OK;
+}
+
+const char* xtb_last_error(const xtb_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int xtb_set_stream(xtb_ctx* c, void* s) {
+    if (!c) return XTB_EINVAL;
+    if (c->own_stream) { cudaStreamSynchronize(c->stream); cudaStreamDestroy(c->stream); c->own_stream = false; }
+    c->stream = (cudaStream_t)s;
+    return XTB_OK;
+}
+
+int xtb_sync(xtb_ctx* c) {
+    if (!c) return XTB_EINVAL;
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+static int upload_params(xtb_ctx* c, const void* p, size_t bytes) {
+    int rc = xtb_reserve(c, c->d_params, bytes);
+    if (rc) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_params.p, p, bytes, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_neigh = c->have_HS = c->have_density = c->have_dens = false;
+    return XTB_OK;
+}
+
+int xtb_set_params_nrl(xtb_ctx* c, int n_kinds, const xtb_nrl_pair* p) {
+    if (!c) return XTB_EINVAL;
+    if (n_kinds <= 0 || !p) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_nrl: n_kinds=%d", n_kinds);
+    cudaSetDevice(c->device);
+    c->h_nrl.assign(p, p + (size_t)n_kinds * n_kinds);
+    c->tb = XTB_TB_NRL; c->n_kinds = n_kinds; c->n_orb = 9;      // NRL is always sp3d5 (TB_NRL.f90:255)
+    return upload_params(c, p, sizeof(xtb_nrl_pair) * (size_t)n_kinds * n_kinds);
+}
+
+int xtb_set_params_pettifor(xtb_ctx* c, int n_kinds, const xtb_pettifor_pair* p) {
+    if (!c) return XTB_EINVAL;
+    if (n_kinds <= 0 || !p) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_pettifor: n_kinds=%d", n_kinds);
+    cudaSetDevice(c->device);
+    c->h_pet.assign(p, p + (size_t)n_kinds * n_kinds);
+    c->tb = XTB_TB_PETTIFOR; c->n_kinds = n_kinds; c->n_orb = 4;
+    return upload_params(c, p, sizeof(xtb_pettifor_pair) * (size_t)n_kinds * n_kinds);
+}
+
+int xtb_set_params_dftb(xtb_ctx* c, int, int, const xtb_dftb_pair*) {
+    if (!c) return XTB_EINVAL;
+    XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_dftb: the DFTB branch is not built yet (SURVEY.md 8a row a11)");
+}
+
+int xtb_set_system(xtb_ctx* c, int na, const int32_t* koa, const double* S, const double* supce) {
+    if (!c) return XTB_EINVAL;
+    if (na <= 0 || !koa || !S || !supce) XTB_FAIL(c, XTB_EINVAL, "xtb_set_system: bad arguments (na=%d)", na);
+    if (c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_set_system: set the TB parameters first");
+    cudaSetDevice(c->device);
+    std::vector<int32_t> k0(na);
+    for (int i = 0; i < na; ++i) {
+        if (koa[i] < 1 || koa[i] > c->n_kinds) XTB_FAIL(c, XTB_EINVAL, "atom %d has kind %d outside 1..%d", i + 1, koa[i], c->n_kinds);
+        k0[i] = koa[i] - 1;
+    }
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_koa, sizeof(int32_t) * na))) return rc;
+    if ((rc = xtb_reserve(c, c->d_S, sizeof(double) * 3 * na))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_koa.p, k0.data(), sizeof(int32_t) * na, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_S.p, S, sizeof(double) * 3 * na, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    memcpy(c->h_supce, supce, sizeof(double) * 9);
+    if (na != c->na) { c->cap = 0; c->a0 = 0; c->a1 = na; }
+    c->na = na;
+    c->have_neigh = c->have_HS = c->have_density = c->have_dens = false;
+    return XTB_OK;
+}
+
+int xtb_set_partition(xtb_ctx* c, int first, int last) {
+    if (!c) return XTB_EINVAL;
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_partition: no system set");
+    if (first < 1 || last > c->na || last < first - 1) XTB_FAIL(c, XTB_EINVAL, "xtb_set_partition: bad range %d..%d", first, last);
+    c->a0 = first - 1; c->a1 = last;
+    c->have_HS = c->have_density = false;
+    return XTB_OK;
+}
+
+// cut-off as get_near_neighbours derives it (Atomic_tools.f90:574-586)
+static double default_cutoff(const xtb_ctx* c) {
+    double rm = 0.0;
+    if (c->tb == XTB_TB_NRL) { for (auto& p : c->h_nrl) rm = p.Rc > rm ? p.Rc : rm; rm *= XTB_G_AU2A; }
+    else if (c->tb == XTB_TB_PETTIFOR) { for (auto& p : c->h_pet) rm = p.rm > rm ? p.rm : rm; }
+    return rm;
+}
+
+int xtb_neighbours_compact(xtb_ctx* c, int cap, int32_t* nn_size, int32_t* nn_list, double* nn_dist, double* nn_dist_s, int* max_nn_out) {
+    if (!c) return XTB_EINVAL;
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_neighbours_compact: run xtb_neighbours first");
+    cudaSetDevice(c->device);
+    if (max_nn_out) *max_nn_out = c->max_nn;
+    if (cap < c->max_nn && (nn_list || nn_dist || nn_dist_s)) XTB_FAIL(c, XTB_ECAPACITY, "cap %d < max_nn %d", cap, c->max_nn);
+    const int na = c->na, dc = c->cap;
+    if (nn_size) XTB_CUDA(c, cudaMemcpyAsync(nn_size, c->d_nn_size.p, sizeof(int) * na, cudaMemcpyDeviceToHost, c->stream));
+    if (nn_list) XTB_CUDA(c, cudaMemcpy2DAsync(nn_list, sizeof(int) * cap, c->d_nn_list.p, sizeof(int) * dc, sizeof(int) * (cap < dc ? cap : dc), na, cudaMemcpyDeviceToHost, c->stream));
+    if (nn_dist) XTB_CUDA(c, cudaMemcpy2DAsync(nn_dist, 32 * (size_t)cap, c->d_nn_dist.p, 32 * (size_t)dc, 32 * (size_t)(cap < dc ? cap : dc), na, cudaMemcpyDeviceToHost, c->stream));
+    if (nn_dist_s) XTB_CUDA(c, cudaMemcpy2DAsync(nn_dist_s, 24 * (size_t)cap, c->d_nn_dist_s.p, 24 * (size_t)dc, 24 * (size_t)(cap < dc ? cap : dc), na, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_neighbours(xtb_ctx* c, double rm, int32_t* nn_size, int32_t* nn_list, double* nn_dist, double* nn_dist_s) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_neighbours: no system set");
+    if (rm <= 0.0) rm = default_cutoff(c);
+    if (rm <= 0.0) XTB_FAIL(c, XTB_EINVAL, "xtb_neighbours: no cut-off radius");
+    int rc = xtb_impl_neighbours(c, rm);
+    if (rc) return rc;
+    if (!nn_size && !nn_list && !nn_dist && !nn_dist_s) return XTB_OK;
+    // expand the compact device list into the reference's dense (Na,Na[,4|3]) host arrays.
+    // Reference initialisation (Atomic_tools.f90:4241-4243): size = 0, list = 0, dist = 1d8; dist_s untouched.
+    const int na = c->na, mx = c->max_nn > 0 ? c->max_nn : 1;
+    std::vector<int32_t> sz(na), li((size_t)na * mx);
+    std::vector<double> di((size_t)na * mx * 4), ds((size_t)na * mx * 3);
+    if ((rc = xtb_neighbours_compact(c, mx, sz.data(), li.data(), di.data(), ds.data(), nullptr))) return rc;
+    const size_t n2 = (size_t)na * na;
+    if (nn_size) memcpy(nn_size, sz.data(), sizeof(int32_t) * na);
+    if (nn_list) memset(nn_list, 0, sizeof(int32_t) * n2);
+    if (nn_dist) for (size_t t = 0; t < 4 * n2; ++t) nn_dist[t] = 1e8;
+    for (int i = 0; i < na; ++i)
+        for (int k = 0; k < sz[i]; ++k) {
+            const size_t e = (size_t)i * mx + k;
+            const size_t d = (size_t)i + (size_t)na * k;               // (i, k) column-major
+            if (nn_list) nn_list[d] = li[e] + 1;
+            if (nn_dist) for (int q = 0; q < 4; ++q) nn_dist[d + n2 * q] = di[4 * e + q];
+            if (nn_dist_s) for (int q = 0; q < 3; ++q) nn_dist_s[d + n2 * q] = ds[3 * e + q];
+        }
+    return XTB_OK;
+}
+
+int xtb_radial(xtb_ctx* c, double* M_Vij, double* M_dVij, double* M_SVij, double* M_dSVij, double* M_lmn, double* M_x1, double* M_xrr) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_radial: run xtb_neighbours first");
+    if (c->tb != XTB_TB_NRL) XTB_FAIL(c, XTB_EINVAL, "xtb_radial: dense tables are provided for the NRL branch only");
+    if (!M_Vij && !M_dVij && !M_SVij && !M_dSVij && !M_lmn && !M_x1 && !M_xrr) return XTB_OK;   // fused on the device otherwise
+    const int na = c->na, cap = c->cap;
+    const size_t ne = (size_t)na * cap;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_tab, sizeof(double) * 49 * ne))) return rc;
+    double* d_rad = (double*)c->d_tab.p;
+    double* d_geo = d_rad + 40 * ne;
+    if ((rc = xtb_impl_nrl_tables(c, d_rad, d_geo))) return rc;
+    std::vector<double> rad(40 * ne), geo(9 * ne);
+    std::vector<int32_t> sz(na), li(ne);
+    XTB_CUDA(c, cudaMemcpyAsync(rad.data(), d_rad, sizeof(double) * 40 * ne, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaMemcpyAsync(geo.data(), d_geo, sizeof(double) * 9 * ne, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaMemcpyAsync(sz.data(), c->d_nn_size.p, sizeof(int) * na, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaMemcpyAsync(li.data(), c->d_nn_list.p, sizeof(int) * ne, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    const size_t n2 = (size_t)na * na;
+    double* Mv[4] = {M_Vij, M_dVij, M_SVij, M_dSVij};
+    for (int t = 0; t < 4; ++t) if (Mv[t]) memset(Mv[t], 0, sizeof(double) * 10 * n2);         // TB_NRL.f90:2137-2140
+    double* Mg[3] = {M_lmn, M_xrr, M_x1};
+    for (int t = 0; t < 3; ++t) if (Mg[t]) memset(Mg[t], 0, sizeof(double) * 3 * n2);           // TB.f90:3448-3450
+    for (int i = 0; i < na; ++i)
+        for (int k = 0; k < sz[i]; ++k) {
+            const size_t e = (size_t)i * cap + k;
+            const int j = li[e];
+            for (int t = 0; t < 4; ++t) if (Mv[t])
+                for (int ch = 0; ch < 10; ++ch) Mv[t][(size_t)i + (size_t)na * j + n2 * ch] = rad[40 * e + 10 * t + ch];   // M(i,j,ch)
+            for (int t = 0; t < 3; ++t) if (Mg[t])
+                for (int a = 0; a < 3; ++a) Mg[t][a + 3 * ((size_t)i + (size_t)na * j)] = geo[9 * e + 3 * t + a];          // M(a,i,j)
+        }
+    return XTB_OK;
+}
+
+int xtb_assemble_HS(xtb_ctx* c, double* H_non, double* Sij) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_assemble_HS: run xtb_neighbours first");
+    int rc;
+    if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_assemble(c);
+    else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_assemble(c);
+    else XTB_FAIL(c, XTB_EINVAL, "xtb_assemble_HS: no TB parametrisation set");
+    if (rc) return rc;
+    const size_t N = (size_t)c->na * c->n_orb;
+    const size_t off = (size_t)c->a0 * c->n_orb * N, cnt = (size_t)(c->a1 - c->a0) * c->n_orb * N;
+    if (H_non && cnt) XTB_CUDA(c, cudaMemcpyAsync(H_non + off, (double*)c->d_H.p + off, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+    if (Sij && cnt) {
+        if (c->tb == XTB_TB_PETTIFOR) XTB_FAIL(c, XTB_EINVAL, "xtb_assemble_HS: orthogonal parametrisation has no overlap matrix");
+        XTB_CUDA(c, cudaMemcpyAsync(Sij + off, (double*)c->d_S2.p + off, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+    }
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_set_eigen_device(xtb_ctx* c, const double* dHa, const double* dEi, const double* dfe) {
+    if (!c) return XTB_EINVAL;
+    if (!dHa || !dEi || !dfe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen_device: null pointer");
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_eigen_device: no system set");
+    c->d_Ha = dHa; c->d_Ei = dEi; c->d_fe = dfe;
+    c->K = (long long)c->na * c->n_orb;
+    c->have_eigen = true; c->have_density = false;
+    return XTB_OK;
+}
+
+int xtb_set_eigen(xtb_ctx* c, const double* Ha, const double* Ei, const double* fe) {
+    if (!c) return XTB_EINVAL;
+    if (!Ha || !Ei || !fe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen: null pointer");
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_eigen: no system set");
+    cudaSetDevice(c->device);
+    const size_t N = (size_t)c->na * c->n_orb;
+    int rc;
+    if ((rc = xtb_reserve(c, c->own_Ha, sizeof(double) * N * N))) return rc;
+    if ((rc = xtb_reserve(c, c->own_Ei, sizeof(double) * N))) return rc;
+    if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->own_Ha.p, Ha, sizeof(double) * N * N, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaMemcpyAsync(c->own_Ei.p, Ei, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return xtb_set_eigen_device(c, (const double*)c->own_Ha.p, (const double*)c->own_Ei.p, (const double*)c->own_fe.p);
+}
+
+int xtb_set_density_cutoff(xtb_ctx* c, double f_cut) {
+    if (!c) return XTB_EINVAL;
+    if (!(f_cut >= 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_set_density_cutoff: f_cut must be >= 0");
+    c->f_cut = f_cut;
+    return XTB_OK;
+}
+
+int xtb_density(xtb_ctx* c, double* Aij, double* Aij_x_Ei) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_density: run xtb_neighbours first");
+    if (!c->have_eigen) XTB_FAIL(c, XTB_ESTATE, "xtb_density: no eigenvectors set (xtb_set_eigen)");
+    int rc = xtb_impl_density(c);
+    if (rc) return rc;
+    if (Aij || Aij_x_Ei) {
+        // dense (N,N) outputs: zero outside the neighbour pattern (documented in the header)
+        if (c->a0 != 0 || c->a1 != c->na) XTB_FAIL(c, XTB_EINVAL, "xtb_density: dense outputs need the full (unpartitioned) context");
+        const size_t N = (size_t)c->na * c->n_orb;
+        if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;     // reuse the dense scratch (H is consumed by now)
+        c->have_HS = false;
+        double* outs[2] = {Aij, Aij_x_Ei};
+        const double* blks[2] = {(const double*)c->d_rho.p, (const double*)c->d_rhoE.p};
+        for (int t = 0; t < 2; ++t) {
+            if (!outs[t]) continue;
+            if ((rc = xtb_dense_from_blocks(c, blks[t], nullptr, (double*)c->d_H.p, nullptr, true))) return rc;
+            XTB_CUDA(c, cudaMemcpyAsync(outs[t], c->d_H.p, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
+            XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+        }
+    }
+    return XTB_OK;
+}
+
+int xtb_density_mirror(xtb_ctx* c) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_density) XTB_FAIL(c, XTB_ESTATE, "xtb_density_mirror: run xtb_density first");
+    int rc = xtb_impl_mirror_density(c);
+    if (rc) return rc;
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_forces(xtb_ctx* c, double* F_att) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_density) XTB_FAIL(c, XTB_ESTATE, "xtb_forces: run xtb_density first");
+    int rc;
+    if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_forces(c);
+    else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_forces(c);
+    else XTB_FAIL(c, XTB_EINVAL, "xtb_forces: no TB parametrisation set");
+    if (rc) return rc;
+    const size_t cnt = (size_t)(c->a1 - c->a0) * 3;
+    if (F_att && cnt) {
+        XTB_CUDA(c, cudaMemcpyAsync(F_att + 3 * (size_t)c->a0, (double*)c->d_F.p + 3 * (size_t)c->a0, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
+int xtb_pressure(xtb_ctx* c, double* SCforce_att) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_density) XTB_FAIL(c, XTB_ESTATE, "xtb_pressure: run xtb_density first");
+    int rc;
+    if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_pressure(c);
+    else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_pressure(c);
+    else XTB_FAIL(c, XTB_EINVAL, "xtb_pressure: no TB parametrisation set");
+    if (rc) return rc;
+    if (SCforce_att) {
+        XTB_CUDA(c, cudaMemcpyAsync(SCforce_att, c->d_SC.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
+int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
+    if (!c || !dptr) return XTB_EINVAL;
+    const size_t N = (size_t)c->na * c->n_orb;
+    const size_t nb2 = (size_t)c->n_orb * c->n_orb;
+    DevBuf* b = nullptr; size_t used = 0;
+    switch (which) {
+        case XTB_BUF_H: b = &c->d_H; used = 8 * N * N; break;
+        case XTB_BUF_S: b = &c->d_S2; used = 8 * N * N; break;
+        case XTB_BUF_RHO: b = &c->d_rho; used = 8 * nb2 * (size_t)c->n_blocks; break;
+        case XTB_BUF_RHOE: b = &c->d_rhoE; used = 8 * nb2 * (size_t)c->n_blocks; break;
+        case XTB_BUF_FORCES: b = &c->d_F; used = 24 * (size_t)c->na; break;
+        case XTB_BUF_ROWPTR: b = &c->d_rowptr; used = 4 * ((size_t)c->na + 1); break;
+        case XTB_BUF_NNLIST: b = &c->d_nn_list; used = 4 * (size_t)c->na * c->cap; break;
+        case XTB_BUF_NNSIZE: b = &c->d_nn_size; used = 4 * (size_t)c->na; break;
+        case XTB_BUF_SCFORCE: b = &c->d_SC; used = 72; break;
+        default: XTB_FAIL(c, XTB_EINVAL, "xtb_device_buffer: unknown buffer %d", which);
+    }
+    if (!b->p) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: buffer %d not produced yet", which);
+    *dptr = b->p;
+    if (bytes) *bytes = used;
+    return XTB_OK;
+}
+
+long long xtb_counter(const xtb_ctx* c, int which) {
+    if (!c) return -1;
+    switch (which) {
+        case 0: return c->na;
+        case 1: return c->n_orb;
+        case 2: return (long long)c->na * c->n_orb;
+        case 3: return c->max_nn;
+        case 4: return c->n_blocks;
+        case 5: return c->n_pairs;
+        case 6: return c->launches;
+        case 7: return c->k_kept;
+        case 8: return c->cap;
+        case 9: return c->density_slotcap;
+        case 10: return c->density_stages;
+        default: return -1;
+    }
+}
+
+double xtb_stage_ms(const xtb_ctx* c, int stage) {
+    if (!c || stage < 1 || stage > 7) return -1.0;
+    return c->stage_ms[stage];
+}
+
+}  // extern "C"
