@@ -198,6 +198,27 @@ def gather_blocks(nb, n_orb, A):
     return blk
 
 
+def nrl_assemble_panels(wl, nb, lmn, rad, j_first, j_last):
+    N = nb.na * 9
+    w = (j_last - j_first) * 9
+    Hp = np.zeros((N, w), order="F"); Sp = np.zeros((N, w), order="F")
+    TB = nrl_params_array(wl["params"])
+    lib().orc_nrl_assemble_panels(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(lmn), _p(rad),
+                                  _p(_koa0(wl)), C.c_int(wl["n_kinds"]), TB, C.c_int(j_first), C.c_int(j_last), _p(Hp), _p(Sp))
+    return Hp, Sp
+
+
+def density_blocks_rows(nb, n_orb, Ct_rows, rowmap, fe, Ei, a_first, a_last):
+    """Ct_rows: (n_gathered_atoms*n_orb, K) C-contiguous; rowmap[atom] -> gathered index or -1."""
+    K = Ct_rows.shape[1]
+    rho = np.zeros((nb.na, nb.cap + 1, n_orb * n_orb)); rhoE = np.zeros_like(rho)
+    lib().orc_density_blocks_rows(C.c_int(nb.na), C.c_int(n_orb), C.c_int(nb.cap), _p(nb.size), _p(nb.list), C.c_int(K),
+                                  _p(np.ascontiguousarray(Ct_rows)), _p(np.ascontiguousarray(rowmap, dtype=np.int32)),
+                                  _p(np.ascontiguousarray(fe)), _p(np.ascontiguousarray(Ei)),
+                                  C.c_int(a_first), C.c_int(a_last), _p(rho), _p(rhoE))
+    return rho, rhoE
+
+
 def _common(wl, nb, lmn, rad):
     h = np.asfortranarray(wl["supce"], dtype=np.float64)
     TB = nrl_params_array(wl["params"])

@@ -782,6 +782,105 @@ void orc_nrl_pressure_sparse(int na, int cap, const int* nn_size, const int* nn_
     for (int q = 0; q < 9; ++q) att[q] = accH[q] - accS[q];
 }
 
+
+/* ------------------------------------------------------------------------------------------
+ * Range / sampled variants used by bench.py's cpu_baseline and --impl reference legs: identical
+ * arithmetic, restricted to a sub-range of atoms so that a bounded sample of the 4096-atom workload
+ * can be timed (every stage is a loop over atoms with equal work per atom).
+ * ---------------------------------------------------------------------------------------- */
+/* column panels [j_first, j_last) of H and S: Hp, Sp are (N, 9*(j_last-j_first)) column-major */
+void orc_nrl_assemble_panels(int na, int cap, const int* nn_size, const int* nn_list, const double* nn_dist,
+                             const double* lmn, const double* rad, const int* koa, int n_kinds,
+                             const xtb_nrl_pair* TB, int j_first, int j_last, double* Hp, double* Sp) {
+    const int n_orb = 9;
+    const size_t N = (size_t)na * n_orb;
+    const double epsylon = 1e-12;
+    memset(Hp, 0, N * (size_t)(j_last - j_first) * n_orb * sizeof(double));
+    memset(Sp, 0, N * (size_t)(j_last - j_first) * n_orb * sizeof(double));
+#pragma omp parallel for schedule(dynamic, 1)
+    for (int j = j_first; j < j_last; ++j) {
+        for (int atom_2 = 0; atom_2 <= nn_size[j]; ++atom_2) {
+            int i = (atom_2 == 0) ? j : nn_list[(size_t)j * cap + atom_2 - 1];
+            double B[81], Sb[81], Hij1[81], Sij1[81];
+            if (i == j) {
+                memset(Hij1, 0, sizeof Hij1); memset(Sij1, 0, sizeof Sij1);
+                const xtb_nrl_pair* P = &TB[koa[j] + n_kinds * koa[i]];
+                double rho = rho_NRL(j, cap, nn_size, nn_list, nn_dist, koa, n_kinds, TB);
+                for (int o = 0; o < 9; ++o) {
+                    int q = onsite_set(o, P->ind_split);
+                    Hij1[o + 9 * o] = On_site_NRL(rho, P->al[q], P->bl[q], P->cl[q], P->dl[q]);
+                    Sij1[o + 9 * o] = 1.0;
+                }
+            } else {
+                /* block (rows larger, cols smaller) from the larger atom's entry; the other one is its transpose */
+                int big = i > j ? i : j, sml = i > j ? j : i;
+                int kk = find_entry(nn_size, nn_list, cap, big, sml);
+                memset(B, 0, sizeof B); memset(Sb, 0, sizeof Sb);
+                if (kk >= 0) {
+                    size_t e = (size_t)big * cap + kk;
+                    orc_KS_sp3d5(rad + e * 40,      lmn[e * 3], lmn[e * 3 + 1], lmn[e * 3 + 2], B);
+                    orc_KS_sp3d5(rad + e * 40 + 20, lmn[e * 3], lmn[e * 3 + 1], lmn[e * 3 + 2], Sb);
+                }
+                for (int a = 0; a < 9; ++a)
+                    for (int b = 0; b < 9; ++b) {
+                        /* wanted (rows i, cols j) */
+                        Hij1[a + 9 * b] = (i > j) ? B[a + 9 * b] : B[b + 9 * a];
+                        Sij1[a + 9 * b] = (i > j) ? Sb[a + 9 * b] : Sb[b + 9 * a];
+                    }
+            }
+            for (int j1 = 0; j1 < n_orb; ++j1) {
+                size_t l = (size_t)(j - j_first) * n_orb + j1;
+                for (int i1 = 0; i1 < n_orb; ++i1) {
+                    size_t k = (size_t)i * n_orb + i1;
+                    double sv = Sij1[i1 + 9 * j1];
+                    if (fabs(sv) <= epsylon) sv = 0.0;
+                    Hp[k + N * l] = Hij1[i1 + 9 * j1] * G_RY;
+                    Sp[k + N * l] = sv;
+                }
+            }
+        }
+    }
+}
+
+/* density blocks of atoms [a_first, a_last) from a row-gathered, row-major copy of the eigenvectors:
+ * Ct_rows[(rowmap[atom]*n_orb + mu)*K + n]; rowmap[atom] < 0 = row not gathered (must not be needed). */
+void orc_density_blocks_rows(int na, int n_orb, int cap, const int* nn_size, const int* nn_list,
+                             int K, const double* Ct_rows, const int* rowmap, const double* fe, const double* Ei,
+                             int a_first, int a_last, double* rho_blk, double* rhoE_blk) {
+    const int nb2 = n_orb * n_orb;
+    (void)na;
+    double* wa = (double*)malloc(sizeof(double) * 2 * (size_t)K * n_orb);
+    double* wf = wa, *we = wa + (size_t)K * n_orb;
+    for (int i = a_first; i < a_last; ++i) {
+        /* Atemp rows of atom i: fe*Ha and fe*Ei*Ha (TB.f90:4378,4459) */
+#pragma omp parallel for schedule(static)
+        for (int mu = 0; mu < n_orb; ++mu)
+            for (int n = 0; n < K; ++n) {
+                double c = Ct_rows[((size_t)rowmap[i] * n_orb + mu) * K + n];
+                wf[(size_t)mu * K + n] = fe[n] * c;
+                we[(size_t)mu * K + n] = fe[n] * Ei[n] * c;
+            }
+        /* one block per task; the state sum is a BLAS-style (re-associated, SIMD) dot product, as in dgemm */
+#pragma omp parallel for schedule(dynamic, 1)
+        for (int k = 0; k <= nn_size[i]; ++k) {
+            int j = (k == 0) ? i : nn_list[(size_t)i * cap + k - 1];
+            double* ob = rho_blk  + ((size_t)i * (cap + 1) + k) * nb2;
+            double* oe = rhoE_blk + ((size_t)i * (cap + 1) + k) * nb2;
+            for (int nu = 0; nu < n_orb; ++nu) {
+                const double* cj = Ct_rows + ((size_t)rowmap[j] * n_orb + nu) * K;
+                for (int mu = 0; mu < n_orb; ++mu) {
+                    const double* a = wf + (size_t)mu * K, *b = we + (size_t)mu * K;
+                    double s2 = 0.0, t2 = 0.0;
+#pragma omp simd reduction(+ : s2, t2)
+                    for (int n = 0; n < K; ++n) { s2 += a[n] * cj[n]; t2 += b[n] * cj[n]; }
+                    ob[mu + n_orb * nu] = s2; oe[mu + n_orb * nu] = t2;
+                }
+            }
+        }
+    }
+    free(wa);
+}
+
 /* single-block accessors for unit tests of the Slater-Koster tables */
 void orc_ks_block(const double* V, double l, double m, double n, double* ts) { orc_KS_sp3d5(V, l, m, n, ts); }
 void orc_dks_block(const double* V, const double* dV, double l, double m, double n,

@@ -124,7 +124,9 @@ def test_density_blocks_parity(case, orc, api, impl):
     for got, ref, nm in ((gA, o["rho"], "rho"), (gAE, o["rhoE"], "rho_E")):
         d = np.abs(got[mask] - ref[mask]).max()
         assert d <= 1e-11 * np.abs(ref[mask]).max(), f"{nm} impl={impl}: {d:.3e}"
-    assert np.array_equal(A, A.T)                       # mirrored blocks are exact transposes
+    # mirrored blocks are exact transposes; on-site blocks are symmetric to rounding only
+    off = np.kron(~np.eye(wl["na"], dtype=bool), np.ones((9, 9), dtype=bool))
+    assert np.array_equal(A[off], A.T[off]) and np.allclose(A, A.T, rtol=0, atol=1e-13)
     # outside the neighbour pattern the dense drop-in output is zero by contract
     N = A.shape[0]
     pat = np.zeros((wl["na"], wl["na"]), dtype=bool)

@@ -129,6 +129,10 @@ class TBContext:
         self._ck(self.lib.xtb_neighbours_compact(self.h, mx, _ip(size), _ip(lst), _dp(dist), _dp(dist_s), C.byref(m)))
         return dict(size=size, list=lst, dist=dist, dist_s=dist_s, max_nn=m.value)
 
+    def get_near_neighbours_device(self, rm=0.0):
+        """S1 with every output kept on the device (NULL host pointers)."""
+        self._ck(self.lib.xtb_neighbours(self.h, float(rm), None, None, None, None))
+
     # -- S2 ---------------------------------------------------------------------------------
     def radial_tables(self):
         """Construct_M_x1 + Construct_Vij_NRL in the reference's dense shapes (small systems)."""
@@ -180,6 +184,13 @@ class TBContext:
         F = np.zeros((self.na, 3))
         self._ck(self.lib.xtb_forces(self.h, _dp(F)))
         return F
+
+    def forces_device(self):
+        """S4 with the result kept on the device (XTB_BUF_FORCES)."""
+        self._ck(self.lib.xtb_forces(self.h, None))
+
+    def pressure_device(self):
+        self._ck(self.lib.xtb_pressure(self.h, None))
 
     def pressure(self):
         att = np.zeros(9)
