@@ -28,6 +28,8 @@ f = ctx.lib.xtb_debug_fp64_peak; f.restype = C.c_double; f.argtypes = [C.c_void_
 for w in (4, 8, 16, 32):
     out[f"dmma884_tflops_w{w}"] = f(ctx.h, 0, w, 3)
     out[f"dfma_tflops_w{w}"] = f(ctx.h, 1, w, 3)
+    out[f"mixed_dmma_plus_dfma_tflops_w{w}"] = f(ctx.h, 2, w, 3)
+    out[f"split_dmma_dfma_tflops_w{w}"] = f(ctx.h, 3, w, 3)
 # copy bandwidth (same method as MEASURED_PEAKS.json)
 x = torch.empty(1 << 30, dtype=torch.bfloat16, device="cuda"); y = torch.empty_like(x)
 best = 0

@@ -1,0 +1,388 @@
+! xtant_b200_shim.f90 -- ISO_C_BINDING stub that puts libxtb_b200.so (include/xtb_b200.h) behind the
+! reference's own procedure names and argument lists for the tight-binding hot path.
+!
+! How it is used (INTEGRATION.md has the Makefile lines): add this file to OBJS after Objects.f90 and
+! Universal_constants.f90, and in TB.f90 replace
+!     use TB_NRL,      only : Construct_Vij_NRL, construct_TB_H_NRL, get_dHij_drij_NRL, Attract_TB_Forces_Press_NRL
+!     use TB_Pettifor, only : construct_TB_H_Pettifor, dHij_s, Attract_TB_Forces_Press
+!     use Atomic_tools,only : get_near_neighbours
+! by   use XTANT_B200_shim   for those names (the rest of each module stays).  The `select type` dispatch in
+! get_Hamilonian_and_E / create_and_diagonalize_H / Get_pressure (TB.f90:247-317,459-487,5551-5556) is unchanged:
+! each `type is (TB_H_NRL)` / `type is (TB_H_Pettifor)` arm calls the same name with the same arguments as before.
+!
+! Status: no Fortran compiler exists in the build image nor on the GPU box (probed: gfortran, ifx, ifort,
+! nvfortran, flang absent), so this file is checked by inspection only; tests/test_abi_cpu.py drives the
+! C ABI with exactly the call sequence and array shapes used below (ctypes stands in for bind(C)).
+!
+! Data contract (SURVEY.md 8b): derived types cannot cross bind(C), so each wrapper flattens
+!   Scell(NSC)%MDAtoms(:)%S, %KOA, Scell(NSC)%supce and the TB_H_*(KOA1,KOA2) scalars into contiguous buffers,
+! and results are written straight into the reference's own allocatables (Near_neighbor_*, H_non, Sij, Aij,
+! MDatoms(k)%forces%att, SCforce%att), all column-major as they already are.
+module XTANT_B200_shim
+use, intrinsic :: iso_c_binding
+use Objects, only : Super_cell, Numerics_param, solid, Error_handling, Save_error_details, &
+                    TB_H_NRL, TB_H_Pettifor
+implicit none
+private
+public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_Aij, Construct_Aij_x_En, &
+          get_dHij_drij_NRL, Attract_TB_Forces_Press_NRL, construct_TB_H_Pettifor, dHij_s, Attract_TB_Forces_Press, &
+          xtb_b200_init, xtb_b200_finalize
+
+! ---- mirror of struct xtb_nrl_pair / xtb_pettifor_pair (include/xtb_b200.h) ----
+type, bind(C) :: xtb_nrl_pair
+   integer(c_int32_t) :: ind_split, ind_overlap
+   real(c_double) :: lambd, Rc, lden
+   real(c_double) :: al(4), bl(4), cl(4), dl(4)
+   real(c_double) :: ellm(10), fllm(10), gllm(10), hllm(10)
+   real(c_double) :: pllm(10), qllm(10), rllm(10), sllm(10)
+end type xtb_nrl_pair
+
+type, bind(C) :: xtb_pettifor_pair
+   real(c_double) :: Es, Ep
+   real(c_double) :: nc(4), rc(4), c0(4), c1(4), c2(4), c3(4), V0(4)
+   real(c_double) :: r0, n, r1, rm
+end type xtb_pettifor_pair
+
+type(c_ptr), save :: ctx = c_null_ptr      ! one context per process (single caller thread, TB.f90:227-272)
+logical, save :: eigen_current = .false.   ! Ha/Ei/fe of this step already on the device
+
+interface
+   integer(c_int) function xtb_create(out, device) bind(C, name="xtb_create")
+      import; type(c_ptr), intent(out) :: out; integer(c_int), value :: device
+   end function
+   integer(c_int) function xtb_destroy(c) bind(C, name="xtb_destroy")
+      import; type(c_ptr), value :: c
+   end function
+   type(c_ptr) function xtb_last_error(c) bind(C, name="xtb_last_error")
+      import; type(c_ptr), value :: c
+   end function
+   integer(c_int) function xtb_set_params_nrl(c, n_kinds, p) bind(C, name="xtb_set_params_nrl")
+      import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds; type(xtb_nrl_pair), intent(in) :: p(*)
+   end function
+   integer(c_int) function xtb_set_params_pettifor(c, n_kinds, p) bind(C, name="xtb_set_params_pettifor")
+      import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds; type(xtb_pettifor_pair), intent(in) :: p(*)
+   end function
+   integer(c_int) function xtb_set_system(c, na, koa, S, supce) bind(C, name="xtb_set_system")
+      import; type(c_ptr), value :: c; integer(c_int), value :: na
+      integer(c_int32_t), intent(in) :: koa(*); real(c_double), intent(in) :: S(3,*), supce(3,3)
+   end function
+   integer(c_int) function xtb_set_partition(c, first, last) bind(C, name="xtb_set_partition")
+      import; type(c_ptr), value :: c; integer(c_int), value :: first, last
+   end function
+   integer(c_int) function xtb_neighbours(c, rm, nn_size, nn_list, nn_dist, nn_dist_s) bind(C, name="xtb_neighbours")
+      import; type(c_ptr), value :: c; real(c_double), value :: rm
+      integer(c_int32_t) :: nn_size(*), nn_list(*); real(c_double) :: nn_dist(*), nn_dist_s(*)
+   end function
+   integer(c_int) function xtb_radial(c, M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn, M_x1, M_xrr) bind(C, name="xtb_radial")
+      import; type(c_ptr), value :: c
+      type(c_ptr), value :: M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn, M_x1, M_xrr     ! c_null_ptr = keep on device
+   end function
+   integer(c_int) function xtb_assemble_HS(c, H_non, Sij) bind(C, name="xtb_assemble_HS")
+      import; type(c_ptr), value :: c; type(c_ptr), value :: H_non, Sij
+   end function
+   integer(c_int) function xtb_set_eigen(c, Ha, Ei, fe) bind(C, name="xtb_set_eigen")
+      import; type(c_ptr), value :: c; real(c_double), intent(in) :: Ha(*), Ei(*), fe(*)
+   end function
+   integer(c_int) function xtb_density(c, Aij, Aij_x_Ei) bind(C, name="xtb_density")
+      import; type(c_ptr), value :: c; type(c_ptr), value :: Aij, Aij_x_Ei
+   end function
+   integer(c_int) function xtb_forces(c, F_att) bind(C, name="xtb_forces")
+      import; type(c_ptr), value :: c; real(c_double) :: F_att(3,*)
+   end function
+   integer(c_int) function xtb_pressure(c, att) bind(C, name="xtb_pressure")
+      import; type(c_ptr), value :: c; real(c_double) :: att(3,3)
+   end function
+end interface
+
+contains
+
+! -------------------------------------------------------------------------------------------------
+subroutine xtb_b200_init(numpar, Err)
+   ! once, after initialize_MPI (XTANT_MAIN_FILE.f90:56-58): rank -> GPU = process_rank mod GPUs per node
+   type(Numerics_param), intent(in) :: numpar
+   type(Error_handling), intent(inout) :: Err
+   integer(c_int) :: rc, dev
+   dev = 0
+#ifdef MPI_USED
+   dev = mod(numpar%MPI_param%process_rank, 8)
+#endif
+   rc = xtb_create(ctx, dev)
+   if (rc /= 0) call Save_error_details(Err, 6, 'xtb_create failed: no CUDA device (there is no CPU fallback)')
+end subroutine xtb_b200_init
+
+subroutine xtb_b200_finalize()
+   integer(c_int) :: rc
+   if (c_associated(ctx)) rc = xtb_destroy(ctx)
+   ctx = c_null_ptr
+end subroutine xtb_b200_finalize
+
+subroutine check(rc, where, Err)
+   ! the reference records errors and continues (Save_error_details, Objects.f90:1309; e.g. TB_NRL.f90:410-416)
+   integer(c_int), intent(in) :: rc
+   character(*), intent(in) :: where
+   type(Error_handling), intent(inout), optional :: Err
+   character(kind=c_char), pointer :: msg(:)
+   character(512) :: text
+   integer :: i
+   if (rc == 0) return
+   call c_f_pointer(xtb_last_error(ctx), msg, [512])
+   text = ''
+   do i = 1, 512
+      if (msg(i) == c_null_char) exit
+      text(i:i) = msg(i)
+   enddo
+   if (present(Err)) then
+      call Save_error_details(Err, 6, trim(where)//': '//trim(text))
+   else
+      print*, trim(where)//': '//trim(text)
+   endif
+end subroutine check
+
+subroutine push_system(Scell, NSC)
+   ! flatten MDAtoms(:)%KOA, %S and supce (Objects.f90:552-581,692-845)
+   type(Super_cell), dimension(:), intent(in) :: Scell
+   integer, intent(in) :: NSC
+   integer :: na, i
+   integer(c_int32_t), allocatable :: koa(:)
+   real(c_double), allocatable :: S(:,:)
+   na = size(Scell(NSC)%MDAtoms)
+   allocate(koa(na), S(3,na))
+   do i = 1, na
+      koa(i) = Scell(NSC)%MDAtoms(i)%KOA
+      S(:,i) = Scell(NSC)%MDAtoms(i)%S(:)
+   enddo
+   call check(xtb_set_system(ctx, int(na,c_int), koa, S, Scell(NSC)%supce), 'xtb_set_system')
+   eigen_current = .false.
+end subroutine push_system
+
+subroutine push_params_nrl(TB)
+   type(TB_H_NRL), dimension(:,:), intent(in) :: TB
+   type(xtb_nrl_pair), allocatable :: p(:)
+   integer :: nk, i, j, k
+   nk = size(TB,1)
+   allocate(p(nk*nk))
+   do j = 1, nk
+      do i = 1, nk
+         k = i + nk*(j-1)      ! p[(koa1-1) + n_kinds*(koa2-1)] = TB(koa1,koa2)
+         p(k)%ind_split = TB(i,j)%ind_split ; p(k)%ind_overlap = TB(i,j)%ind_overlap
+         p(k)%lambd = TB(i,j)%lambd ; p(k)%Rc = TB(i,j)%Rc ; p(k)%lden = TB(i,j)%lden
+         p(k)%al = TB(i,j)%al ; p(k)%bl = TB(i,j)%bl ; p(k)%cl = TB(i,j)%cl ; p(k)%dl = TB(i,j)%dl
+         p(k)%ellm = TB(i,j)%ellm ; p(k)%fllm = TB(i,j)%fllm ; p(k)%gllm = TB(i,j)%gllm ; p(k)%hllm = TB(i,j)%hllm
+         p(k)%pllm = TB(i,j)%pllm ; p(k)%qllm = TB(i,j)%qllm ; p(k)%rllm = TB(i,j)%rllm ; p(k)%sllm = TB(i,j)%sllm
+      enddo
+   enddo
+   call check(xtb_set_params_nrl(ctx, int(nk,c_int), p), 'xtb_set_params_nrl')
+end subroutine push_params_nrl
+
+subroutine push_params_pettifor(TB)
+   type(TB_H_Pettifor), dimension(:,:), intent(in) :: TB
+   type(xtb_pettifor_pair), allocatable :: p(:)
+   integer :: nk, i, j, k
+   nk = size(TB,1)
+   allocate(p(nk*nk))
+   do j = 1, nk
+      do i = 1, nk
+         k = i + nk*(j-1)
+         p(k)%Es = TB(i,j)%Es ; p(k)%Ep = TB(i,j)%Ep
+         p(k)%nc = TB(i,j)%nc ; p(k)%rc = TB(i,j)%rc ; p(k)%c0 = TB(i,j)%c0 ; p(k)%c1 = TB(i,j)%c1
+         p(k)%c2 = TB(i,j)%c2 ; p(k)%c3 = TB(i,j)%c3 ; p(k)%V0 = TB(i,j)%V0
+         p(k)%r0 = TB(i,j)%r0 ; p(k)%n = TB(i,j)%n ; p(k)%r1 = TB(i,j)%r1 ; p(k)%rm = TB(i,j)%rm
+      enddo
+   enddo
+   call check(xtb_set_params_pettifor(ctx, int(nk,c_int), p), 'xtb_set_params_pettifor')
+end subroutine push_params_pettifor
+
+! -------------------------------------------------------------------------------------------------
+! S1   Atomic_tools.f90:562
+subroutine get_near_neighbours(Scell, numpar, include_vdW, dm)
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   type(Numerics_param), intent(in) :: numpar
+   logical, intent(in), optional :: include_vdW
+   real(8), intent(out), optional :: dm
+   integer :: NSC
+   real(8) :: rm
+   do NSC = 1, size(Scell)
+      ASSOCIATE (ARRAY => Scell(NSC)%TB_Hamil(:,:))
+         select type(ARRAY)
+         type is (TB_H_Pettifor)
+            call push_params_pettifor(ARRAY)
+         type is (TB_H_NRL)
+            call push_params_nrl(ARRAY)
+         end select
+      END ASSOCIATE
+      call push_system(Scell, NSC)
+      ! rm <= 0: the library derives the cut-off as Atomic_tools.f90:574-586 does.  The vdW / repulsive
+      ! enlargements (:611-640) are host scalars: compute them as before and pass rm > 0 when they apply.
+      rm = 0.0d0
+      call check(xtb_neighbours(ctx, rm, Scell(NSC)%Near_neighbor_size, Scell(NSC)%Near_neighbor_list, &
+                                Scell(NSC)%Near_neighbor_dist, Scell(NSC)%Near_neighbor_dist_s), 'xtb_neighbours')
+      if (present(dm)) dm = rm
+   enddo
+end subroutine get_near_neighbours
+
+! S2a  TB_NRL.f90:1956.  The dense (Na,Na,10) tables are only needed by un-grafted consumers; the grafted
+! stages keep everything on the device, so the default forwards NULL pointers and leaves M_* untouched.
+subroutine Construct_Vij_NRL(numpar, TB, Scell, NSC, M_Vij, M_dVij, M_SVij, M_dSVij)
+   type(Numerics_param), intent(inout) :: numpar
+   type(TB_H_NRL), dimension(:,:), intent(in), target :: TB
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   real(8), dimension(:,:,:), allocatable, target :: M_Vij, M_dVij, M_SVij, M_dSVij
+   integer :: na
+   na = size(Scell(NSC)%MDAtoms)
+   if (.not.allocated(M_Vij))   allocate(M_Vij(na,na,10))
+   if (.not.allocated(M_dVij))  allocate(M_dVij(na,na,10))
+   if (.not.allocated(M_SVij))  allocate(M_SVij(na,na,10))
+   if (.not.allocated(M_dSVij)) allocate(M_dSVij(na,na,10))
+   call check(xtb_radial(ctx, c_loc(M_Vij), c_loc(M_dVij), c_loc(M_SVij), c_loc(M_dSVij), &
+                         c_null_ptr, c_null_ptr, c_null_ptr), 'xtb_radial')
+end subroutine Construct_Vij_NRL
+
+! S2b  TB_NRL.f90:74.  Assembly on the GPU; the eigensolve (Loewdin_Orthogonalization + sym_diagonalize,
+! TB_NRL.f90:402-421) stays in the reference (outside the graft) and is called on the returned H_non, Sij.
+subroutine construct_TB_H_NRL(numpar, matter, TB_Hamil, M_Vij, M_SVij, M_lmn, Scell, NSC, Err)
+   use TB_NRL, only : solve_nonorthogonal_NRL => Loewdin_and_diagonalize_from_HS   ! see INTEGRATION.md: 12-line split of Hamil_tot_NRL
+   type(Numerics_param), intent(inout) :: numpar
+   type(solid), intent(inout) :: matter
+   type(TB_H_NRL), dimension(:,:), intent(in) :: TB_Hamil
+   real(8), dimension(:,:,:), intent(in) :: M_Vij, M_SVij, M_lmn
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(Error_handling), intent(inout) :: Err
+   Scell(NSC)%Ha0 = Scell(NSC)%Ha            ! side effects the callers rely on (TB_NRL.f90:88-90)
+   Scell(NSC)%Ei0 = Scell(NSC)%Ei
+   Scell(NSC)%H_non0 = Scell(NSC)%H_non
+   call check(xtb_assemble_HS(ctx, c_loc(Scell(NSC)%H_non), c_loc(Scell(NSC)%Sij)), 'xtb_assemble_HS', Err)
+   Scell(NSC)%Hij = Scell(NSC)%H_non
+   call solve_nonorthogonal_NRL(numpar, Scell, NSC, Err)      ! fills Ha, Ei, eigen_S, Hij_sol; then find_band_gap (:109)
+   eigen_current = .false.
+end subroutine construct_TB_H_NRL
+
+! S3   TB.f90:4328 -- rho on the neighbour pattern (dense Aij is zero elsewhere; every consumer reads only the pattern)
+subroutine Construct_Aij(numpar, Ha, distre, Aij)
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), dimension(:,:), intent(in) :: Ha
+   real(8), dimension(:), intent(in) :: distre
+   real(8), dimension(:,:), allocatable, intent(inout), target :: Aij
+   ! the energy levels are not an argument here; Construct_Aij_x_En supplies them.  The device density pass
+   ! produces rho and rho_E together, so the upload is deferred to whichever of the two is called with En.
+   if (.not. allocated(Aij)) allocate(Aij(size(distre), size(distre)))
+   call stage_eigen(Ha, distre)
+   call check(xtb_density(ctx, c_loc(Aij), c_null_ptr), 'xtb_density(Aij)')
+end subroutine Construct_Aij
+
+! S3   TB.f90:4401
+subroutine Construct_Aij_x_En(numpar, Ha, distre, En, Aij, H_ssc_1_per_S)
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), dimension(:,:), intent(in) :: Ha
+   real(8), dimension(:), intent(in) :: distre, En
+   real(8), dimension(:,:), allocatable, intent(inout), target :: Aij
+   real(8), dimension(:,:), intent(in), optional :: H_ssc_1_per_S
+   if (present(H_ssc_1_per_S)) then
+      print*, 'XTANT_B200_shim: the SCC variant of Construct_Aij_x_En (TB.f90:4445-4454) is not grafted'
+      return
+   endif
+   if (.not. allocated(Aij)) allocate(Aij(size(distre), size(distre)))
+   call stage_eigen(Ha, distre, En)
+   call check(xtb_density(ctx, c_null_ptr, c_loc(Aij)), 'xtb_density(Aij_x_Ei)')
+end subroutine Construct_Aij_x_En
+
+subroutine stage_eigen(Ha, distre, En)
+   real(8), dimension(:,:), intent(in) :: Ha
+   real(8), dimension(:), intent(in) :: distre
+   real(8), dimension(:), intent(in), optional :: En
+   real(8), allocatable, save :: E_last(:)
+   if (present(En)) then
+      if (allocated(E_last)) deallocate(E_last)
+      allocate(E_last, source = En)
+   endif
+   if (.not. allocated(E_last)) allocate(E_last(size(distre)), source = 0.0d0)
+   call check(xtb_set_eigen(ctx, Ha, E_last, distre), 'xtb_set_eigen')
+   eigen_current = .true.
+end subroutine stage_eigen
+
+! S4   TB_NRL.f90:2412
+subroutine get_dHij_drij_NRL(TB_Hamil, Scell, NSC, numpar, Aij, M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn, Aij_x_Ei)
+   type(TB_H_NRL), dimension(:,:), intent(in) :: TB_Hamil
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), dimension(:,:,:), intent(in) :: M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn
+   real(8), dimension(:,:), intent(in) :: Aij, Aij_x_Ei
+   real(c_double), allocatable :: F(:,:)
+   integer :: k, na
+   na = size(Scell(NSC)%MDatoms)
+   allocate(F(3,na))
+   call check(xtb_forces(ctx, F), 'xtb_forces')        ! uses the device-resident rho, rho_E of this step
+   do k = 1, na
+      Scell(NSC)%MDatoms(k)%forces%att(:) = F(:,k)
+   enddo
+end subroutine get_dHij_drij_NRL
+
+! S5   TB_NRL.f90:2742
+subroutine Attract_TB_Forces_Press_NRL(TB_Hamil, Scell, NSC, numpar, Aij, M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn, Aij_x_Ei)
+   type(TB_H_NRL), dimension(:,:), intent(in) :: TB_Hamil
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), dimension(:,:,:), intent(in) :: M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn
+   real(8), dimension(:,:), intent(in) :: Aij, Aij_x_Ei
+   if (numpar%p_const) then        ! TB_NRL.f90:2758
+      call check(xtb_pressure(ctx, Scell(NSC)%SCforce%att), 'xtb_pressure')
+   endif
+end subroutine Attract_TB_Forces_Press_NRL
+
+! ---- Pettifor arms (TB_Pettifor.f90:1427,141,1134) ----------------------------------------------
+subroutine construct_TB_H_Pettifor(numpar, matter, TB_Hamil, Scell, NSC, Ha, Err)
+   use Algebra_tools, only : sym_diagonalize
+   type(Numerics_param), intent(inout) :: numpar
+   type(solid), intent(inout) :: matter
+   type(TB_H_Pettifor), dimension(:,:), intent(in) :: TB_Hamil
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   real(8), dimension(:,:), intent(out), target :: Ha
+   type(Error_handling), intent(inout) :: Err
+   character(200) :: Error_descript
+   Error_descript = ''
+   Scell(NSC)%Ha0 = Scell(NSC)%Ha
+   Scell(NSC)%Ei0 = Scell(NSC)%Ei
+   Scell(NSC)%H_non0 = Scell(NSC)%H_non
+   call check(xtb_assemble_HS(ctx, c_loc(Ha), c_null_ptr), 'xtb_assemble_HS', Err)
+   Scell(NSC)%H_non = Ha                                                  ! TB_Pettifor.f90:1452
+   call sym_diagonalize(Ha, Scell(NSC)%Ei, Error_descript, check_M=.true.) ! :1455 (outside the graft)
+   eigen_current = .false.
+end subroutine construct_TB_H_Pettifor
+
+subroutine dHij_s(TB_Hamil, atoms, Scell, NSC, numpar, Aij, M_x1, M_xrr)
+   use Objects, only : Atom
+   type(TB_H_Pettifor), dimension(:,:), intent(in) :: TB_Hamil
+   type(Atom), dimension(:), intent(inout) :: atoms
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(in) :: numpar
+   real(8), dimension(:,:), intent(in) :: Aij
+   real(8), dimension(:,:,:), intent(in) :: M_x1, M_xrr
+   real(c_double), allocatable :: F(:,:)
+   integer :: k, na
+   na = size(atoms)
+   allocate(F(3,na))
+   call check(xtb_forces(ctx, F), 'xtb_forces')
+   do k = 1, na
+      Scell(NSC)%MDatoms(k)%forces%att(:) = F(:,k)
+   enddo
+end subroutine dHij_s
+
+subroutine Attract_TB_Forces_Press(TB_Hamil, atoms, Scell, NSC, numpar, Aij)
+   use Objects, only : Atom
+   type(TB_H_Pettifor), dimension(:,:), intent(in) :: TB_Hamil
+   type(Atom), dimension(:), intent(inout) :: atoms
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(in) :: numpar
+   real(8), dimension(:,:), intent(in) :: Aij
+   if (numpar%p_const) then        ! TB_Pettifor.f90:1147
+      call check(xtb_pressure(ctx, Scell(NSC)%SCforce%att), 'xtb_pressure')
+   endif
+end subroutine Attract_TB_Forces_Press
+
+end module XTANT_B200_shim
