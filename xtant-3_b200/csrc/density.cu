@@ -14,11 +14,12 @@
 //            memory are bank-conflict free without padding.
 //   main   : persistent CTAs, one atom i at a time.  A producer warp streams the tiles of i and of its
 //            owned neighbours through a multi-stage shared-memory ring with cp.async.bulk (TMA bulk
-//            copies, mbarrier complete_tx); 8 consumer warps issue mma.sync.m8n8k4.f64:
-//                D[row = orbital nu of neighbour j][col = (rho|rho_E, orbital mu of i)] +=
-//                    C[j nu, n] * (w_n C[i mu, n])
-//            i.e. M = packed neighbour rows, N = 24 = 9 (rho) + 9 (rho_E) + 6 pad, K = states.
-//            rho and rho_E share the A operand, so one pass over the eigenvectors produces both.
+//            copies, mbarrier complete_tx); a second helper warp weights the B operand (f_n C[i], f_n E_n C[i])
+//            once per chunk; 8 consumer warps issue mma.sync.m8n8k4.f64:
+//                D[row = orbital nu of neighbour j][col = orbital mu < 8 of i] += C[j nu, n] * (w_n C[i mu, n])
+//            once with w = f (rho) and once with w = f E (rho_E) -- M = packed neighbour rows, K = states --
+//            and the ninth orbital of i as two DFMA per row tile.  rho and rho_E share the A operand, so one
+//            pass over the eigenvectors produces both.
 //   mirror : non-owner blocks filled by transposition, so S4/S5 stream complete rows of blocks.
 // Algorithmic flops (roofline numerator): 2 matrices * 2 * n_orb^2 * K_kept * (n_pairs/2 + na).
 #include "xtb_ctx.h"
@@ -28,10 +29,9 @@ namespace {
 
 constexpr int KC = 16;                 // states per chunk
 constexpr int NCW = 8;                 // consumer warps
-constexpr int NTHREADS = (NCW + 1) * 32;
 
-// balanced half-list ownership: exactly one of own(i,j), own(j,i) is true for i != j
-__host__ __device__ __forceinline__ bool owns(int i, int j) { return ((i + j) & 1) ? (i < j) : (i > j); }
+// pair ownership (exactly one of the two atoms owns an unordered pair) comes from the neighbour stage: own[e],
+// see nn_rev_kernel in neighbours.cu (positive half-space orientation: balanced work per atom).
 
 // ---------------- prep ----------------
 // order-preserving compaction of the kept states; single CTA (K <= a few 1e5)
@@ -126,40 +126,129 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                 : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+        : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
 }
 
 // ---------------- main kernel ----------------
-// dynamic smem: [STAGES][ slotcap*NO*KC doubles | 2*KC doubles (wf, wfe) ]  then barriers and slot tables
+// Shared memory per pipeline stage (doubles):
+//   [slotcap][SLOT]   tiles, SLOT = 148: the 144-double (atom, chunk) tile [4 k-steps][NO rows][4 states] plus 4 pad
+//                     doubles, so that row R = 9*slot + r of k-step s sits at bank16 = 4*((R + s) mod 4) + t and the
+//                     8 rows x 4 states of a DMMA A fragment are conflict-free for every tile, also across slots;
+//   [4][BROW]         B operand of atom i, already weighted: per k-step 32 doubles f*C[i,mu=0..7] in fragment order,
+//                     32 doubles f*E*C[i,mu<8], then f*C[i,8,t] (4) and f*E*C[i,8,t] (4);  BROW = 72
+//   [2][KC]           the weights f_n, f_n*E_n of the chunk
+// Warp roles: warps 0..NCW-1 consume; warp NCW issues the TMA bulk copies (producer); warp NCW+1 scales the B operand
+// once per chunk (instead of 8 warps x 4 k-steps doing it redundantly on the FP64 pipe the DMMAs need).
+// Barriers per stage: full (TMA bytes landed) -> bready (B operand scaled) -> consumers -> empty (NCW arrivals).
+//
+// Column packing: the 18 useful columns (rho | rho_E) x 9 orbitals of i are issued as two DMMA column tiles
+// (mu = 0..7 for rho and for rho_E) plus two DFMA per row tile for mu = 8.  DMMA and DFMA share the FP64
+// execution resource on B200 (profiles/r01_probe_fp64_peaks.json), so this issues exactly the useful flops,
+// where a third, 2/8-full DMMA column tile would waste 25 % of the pipe.
+constexpr int SLOT = 148;
+constexpr int BROW = 72;
+constexpr int NWARPS = NCW + 2;
+constexpr int NTHREADS2 = NWARPS * 32;
+
+struct StagePtrs {
+    double* tiles; double* B; double* w;
+};
+
 template <int NO, int MT>
-__global__ void __launch_bounds__(NTHREADS, 1)
+__device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_doubles, int slotcap, int stages,
+                                                uint64_t* full, uint64_t* bready, uint64_t* empty, uint32_t& it, int nchunks,
+                                                int nrows, int ntiles, int warp, int lane, const int* slot_q, size_t b0i,
+                                                bool first_subtask, double* __restrict__ rho, double* __restrict__ rhoE) {
+    const int g = lane >> 2, t = lane & 3;
+    double acc0[MT][2], acc1[MT][2], p8f[MT], p8e[MT];
+    int off[MT];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+        acc0[mt][0] = acc0[mt][1] = acc1[mt][0] = acc1[mt][1] = 0.0;
+        p8f[mt] = p8e[mt] = 0.0;
+        const int R = 8 * (warp + NCW * mt) + g;
+        const int sl = R / NO, r = R - sl * NO;
+        off[mt] = (R < nrows) ? sl * SLOT + 4 * r + t : t;      // rows beyond the task read row 0 (results dropped)
+    }
+    const int boff = slotcap * SLOT;
+    for (int ch = 0; ch < nchunks; ++ch, ++it) {
+        const int st = it % stages;
+        const uint32_t ph = (it / stages) & 1u;
+        mbar_wait(&full[st], ph);
+        mbar_wait(&bready[st], ph);
+        const double* stg = sbuf + (size_t)st * stage_doubles;
+        const double* Bs = stg + boff;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            const double b0 = Bs[s * BROW + lane];
+            const double b1 = Bs[s * BROW + 32 + lane];
+            const double b8f = Bs[s * BROW + 64 + t];
+            const double b8e = Bs[s * BROW + 68 + t];
+            double a[MT];
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) a[mt] = stg[off[mt] + NO * 4 * s];
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+                dmma884(acc0[mt][0], acc0[mt][1], a[mt], b0);
+                dmma884(acc1[mt][0], acc1[mt][1], a[mt], b1);
+                p8f[mt] = fma(a[mt], b8f, p8f[mt]);
+                p8e[mt] = fma(a[mt], b8e, p8e[mt]);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[st]);
+    }
+    // ---- epilogue: D(row R -> (slot, nu), col -> mu) -> block (i, slot)[mu + NO*nu] ----
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+        // mu = 8: sum the four k-slices held by the lanes t = 0..3 of row g
+        double f8 = p8f[mt], e8 = p8e[mt];
+        f8 += __shfl_xor_sync(0xffffffffu, f8, 1); e8 += __shfl_xor_sync(0xffffffffu, e8, 1);
+        f8 += __shfl_xor_sync(0xffffffffu, f8, 2); e8 += __shfl_xor_sync(0xffffffffu, e8, 2);
+        const int tile = warp + NCW * mt;
+        const int R = 8 * tile + g;
+        if (tile < ntiles && R < nrows) {
+            const int sl = R / NO, nu = R - sl * NO;
+            if (sl > 0 || first_subtask) {     // the on-site block belongs to the first sub-task only
+                const size_t blk = (b0i + (sl == 0 ? 0 : 1 + slot_q[sl])) * (NO * NO) + NO * nu;
+                rho[blk + 2 * t] = acc0[mt][0];  rho[blk + 2 * t + 1] = acc0[mt][1];
+                rhoE[blk + 2 * t] = acc1[mt][0]; rhoE[blk + 2 * t + 1] = acc1[mt][1];
+                if (t == 0) rho[blk + 8] = f8;
+                if (t == 1) rhoE[blk + 8] = e8;
+            }
+        }
+    }
+}
+
+template <int NO>
+__global__ void __launch_bounds__(NTHREADS2, 1)
 density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, int nchunks,
-                    const int* __restrict__ nn_size, const int* __restrict__ nn_list, const int* __restrict__ rowptr,
-                    const double* __restrict__ Ct, const double* __restrict__ wf, const double* __restrict__ wfe,
-                    double* __restrict__ rho, double* __restrict__ rhoE) {
-    static_assert(NO == 9, "column packing below is written for the 9-orbital (18 -> 24 columns) case");
-    constexpr int TILE = NO * KC;                       // doubles per (atom, chunk) tile
+                    const int* __restrict__ nn_size, const int* __restrict__ nn_list, const signed char* __restrict__ own,
+                    const int* __restrict__ rowptr, const double* __restrict__ Ct, const double* __restrict__ wf,
+                    const double* __restrict__ wfe, double* __restrict__ rho, double* __restrict__ rhoE) {
+    static_assert(NO == 9, "column packing is written for the 9-orbital case (8 DMMA columns + 1 DFMA column per matrix)");
+    constexpr int TILE = NO * KC;                       // doubles per (atom, chunk) tile in global memory
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int stage_doubles = slotcap * TILE + 2 * KC;
+    const int stage_doubles = slotcap * SLOT + 4 * BROW + 2 * KC;
     double* sbuf = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(sbuf + (size_t)stages * stage_doubles);
-    uint64_t* empty = full + stages;
+    uint64_t* bready = full + stages;
+    uint64_t* empty = bready + stages;
     int* slot_q = reinterpret_cast<int*>(empty + stages);     // [slotcap] list ordinal of slot s (s >= 1)
     int* slot_atom = slot_q + slotcap;                        // [slotcap] atom of slot s (slot 0 = i)
     int* owned_q = slot_atom + slotcap;                       // [cap] ordinals of all owned neighbours of i
     __shared__ int n_owned_sh;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int g = lane >> 2, t = lane & 3;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], NCW); }
+        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&bready[s], 1); mbar_init(&empty[s], NCW); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
-    uint32_t it = 0;     // running chunk counter (same sequence in producer and consumers)
+    uint32_t it = 0;     // running chunk counter (same sequence in every role)
 
     for (int i = a0 + blockIdx.x; i < a1; i += gridDim.x) {
         // ---- owned neighbours of i, in list order (warp 0, ordered compaction) ----
@@ -169,8 +258,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
             int cnt = 0;
             for (int base = 0; base < m; base += 32) {
                 const int q = base + lane;
-                bool f = false;
-                if (q < m) f = owns(i, nn_list[(size_t)i * cap + q]);
+                const bool f = q < m && own[(size_t)i * cap + q] != 0;
                 const unsigned mask = __ballot_sync(0xffffffffu, f);
                 if (f) owned_q[cnt + __popc(mask & ((1u << lane) - 1u))] = q;
                 cnt += __popc(mask);
@@ -179,6 +267,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
         }
         __syncthreads();
         const int n_owned = n_owned_sh;
+        const size_t b0i = (size_t)rowptr[i];
         // ---- sub-tasks of at most slotcap-1 neighbours (slot 0 is always atom i itself) ----
         for (int first = 0; first == 0 || first < n_owned; first += slotcap - 1) {
             const int nn = min(slotcap - 1, n_owned - first);
@@ -193,7 +282,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
             const int ntiles = (nrows + 7) >> 3;
 
             if (warp == NCW) {
-                // ===== producer warp: stream tiles of all slots for every chunk =====
+                // ===== producer warp: stream the tiles of all slots for every chunk =====
                 const uint32_t bytes = (uint32_t)(nslots * TILE + 2 * KC) * 8u;
                 for (int ch = 0; ch < nchunks; ++ch, ++it) {
                     const int st = it % stages;
@@ -202,71 +291,51 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
                     double* dstage = sbuf + (size_t)st * stage_doubles;
                     if (lane == 0) {
                         mbar_expect_tx(&full[st], bytes);
-                        bulk_g2s(dstage + slotcap * TILE, wf + (size_t)ch * KC, KC * 8, &full[st]);
-                        bulk_g2s(dstage + slotcap * TILE + KC, wfe + (size_t)ch * KC, KC * 8, &full[st]);
+                        bulk_g2s(dstage + slotcap * SLOT + 4 * BROW, wf + (size_t)ch * KC, KC * 8, &full[st]);
+                        bulk_g2s(dstage + slotcap * SLOT + 4 * BROW + KC, wfe + (size_t)ch * KC, KC * 8, &full[st]);
                     }
                     __syncwarp();
                     const double* csrc = Ct + (size_t)ch * na * TILE;
                     for (int s = lane; s < nslots; s += 32)
-                        bulk_g2s(dstage + s * TILE, csrc + (size_t)slot_atom[s] * TILE, TILE * 8, &full[st]);
+                        bulk_g2s(dstage + s * SLOT, csrc + (size_t)slot_atom[s] * TILE, TILE * 8, &full[st]);
                 }
-            } else {
-                // ===== consumer warps =====
-                double acc[MT][3][2];
-                int off[MT];
-#pragma unroll
-                for (int mt = 0; mt < MT; ++mt) {
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) { acc[mt][c][0] = 0.0; acc[mt][c][1] = 0.0; }
-                    const int R = 8 * (warp + NCW * mt) + g;
-                    const int sl = R / NO, r = R - sl * NO;
-                    off[mt] = (R < nrows) ? sl * TILE + 4 * r + t : t;
-                }
+            } else if (warp == NCW + 1) {
+                // ===== B warp: weighted B operand of atom i, once per chunk =====
                 for (int ch = 0; ch < nchunks; ++ch, ++it) {
                     const int st = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
                     mbar_wait(&full[st], ph);
-                    const double* stg = sbuf + (size_t)st * stage_doubles;
-                    const double* wsm = stg + slotcap * TILE;
+                    double* stg = sbuf + (size_t)st * stage_doubles;
+                    double* Bs = stg + slotcap * SLOT;
+                    const double* wsm = Bs + 4 * BROW;
+                    const int g = lane >> 2, t = lane & 3;
 #pragma unroll
                     for (int s = 0; s < 4; ++s) {
                         const double w_f = wsm[4 * s + t], w_e = wsm[KC + 4 * s + t];
-                        const double ci = stg[NO * 4 * s + 4 * g + t];            // C[i, mu = g][k]
-                        const double c8 = stg[NO * 4 * s + 32 + t];               // C[i, mu = 8][k]
-                        const double b0 = ci * w_f, b1 = ci * w_e;
-                        const double b2 = g == 0 ? c8 * w_f : (g == 1 ? c8 * w_e : 0.0);
-#pragma unroll
-                        for (int mt = 0; mt < MT; ++mt) {
-                            if (warp + NCW * mt < ntiles) {       // warp-uniform
-                                const double a = stg[off[mt] + NO * 4 * s];
-                                dmma884(acc[mt][0][0], acc[mt][0][1], a, b0);
-                                dmma884(acc[mt][1][0], acc[mt][1][1], a, b1);
-                                dmma884(acc[mt][2][0], acc[mt][2][1], a, b2);
-                            }
+                        const double ci = stg[NO * 4 * s + 4 * g + t];            // C[i, mu = g][state 4 s + t]
+                        Bs[s * BROW + lane] = ci * w_f;                           // Atemp = distre * Ha        TB.f90:4378
+                        Bs[s * BROW + 32 + lane] = ci * w_e;                      // Atemp = distre * En * Ha   TB.f90:4459
+                        if (g == 0) {
+                            const double c8 = stg[NO * 4 * s + 32 + t];           // C[i, mu = 8][state]
+                            Bs[s * BROW + 64 + t] = c8 * w_f;
+                            Bs[s * BROW + 68 + t] = c8 * w_e;
                         }
                     }
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&empty[st]);
+                    if (lane == 0) mbar_arrive(&bready[st]);     // release: the stores above are visible to the waiters
                 }
-                // ---- epilogue: D(row R -> (slot, nu), col -> (matrix, mu)) -> block (i, slot)[mu + 9 nu] ----
-                const size_t b0i = (size_t)rowptr[i];
-#pragma unroll
-                for (int mt = 0; mt < MT; ++mt) {
-                    const int R = 8 * (warp + NCW * mt) + g;
-                    if (R < nrows) {
-                        const int sl = R / NO, nu = R - sl * NO;
-                        if (sl > 0 || first == 0) {     // the on-site block belongs to the first sub-task only
-                            const size_t blk = (b0i + (sl == 0 ? 0 : 1 + slot_q[sl])) * (NO * NO);
-#pragma unroll
-                            for (int e = 0; e < 2; ++e) {
-                                const int cc = 2 * t + e;
-                                rho[blk + cc + NO * nu] = acc[mt][0][e];
-                                rhoE[blk + cc + NO * nu] = acc[mt][1][e];
-                                if (cc == 0) rho[blk + 8 + NO * nu] = acc[mt][2][e];
-                                if (cc == 1) rhoE[blk + 8 + NO * nu] = acc[mt][2][e];
-                            }
-                        }
-                    }
+            } else {
+                // ===== consumer warps =====
+                const int mt_need = (ntiles + NCW - 1) / NCW;
+                const bool fs = first == 0;
+                switch (mt_need) {
+                    case 1: consume_subtask<NO, 1>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
+                    case 2: consume_subtask<NO, 2>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
+                    case 3: consume_subtask<NO, 3>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
+                    case 4: consume_subtask<NO, 4>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
+                    case 5: consume_subtask<NO, 5>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
+                    case 6: consume_subtask<NO, 6>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
+                    default: consume_subtask<NO, 7>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
                 }
             }
         }
@@ -278,7 +347,8 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
 template <int NO>
 __global__ void __launch_bounds__(128) density_simple_kernel(int na, int a0, int a1, int cap, long long N, int nkeep,
                                                             const int* __restrict__ keep, const int* __restrict__ nn_size,
-                                                            const int* __restrict__ nn_list, const int* __restrict__ rowptr,
+                                                            const int* __restrict__ nn_list, const signed char* __restrict__ own,
+                                                            const int* __restrict__ rowptr,
                                                             const double* __restrict__ Ha, const double* __restrict__ wf,
                                                             const double* __restrict__ wfe, double* __restrict__ rho,
                                                             double* __restrict__ rhoE) {
@@ -286,7 +356,7 @@ __global__ void __launch_bounds__(128) density_simple_kernel(int na, int a0, int
     const int q = blockIdx.x;        // 0 = on-site
     if (q > nn_size[i]) return;
     const int j = q == 0 ? i : nn_list[(size_t)i * cap + q - 1];
-    if (q > 0 && !owns(i, j)) return;
+    if (q > 0 && !own[(size_t)i * cap + q - 1]) return;
     if (threadIdx.x >= NO * NO) return;
     const int mu = threadIdx.x % NO, nu = threadIdx.x / NO;
     const double* ci = Ha + (size_t)i * NO + mu;
@@ -306,14 +376,14 @@ __global__ void __launch_bounds__(128) density_simple_kernel(int na, int a0, int
 // non-owner blocks = transpose of the owner's block
 template <int NO>
 __global__ void mirror_blocks_kernel(int na, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
-                                     const int* __restrict__ rev, const int* __restrict__ rowptr,
+                                     const int* __restrict__ rev, const signed char* __restrict__ own, const int* __restrict__ rowptr,
                                      double* __restrict__ rho, double* __restrict__ rhoE) {
     const int i = blockIdx.y;
     const int q = blockIdx.x;
     if (q >= nn_size[i]) return;
     const size_t e = (size_t)i * cap + q;
     const int j = nn_list[e];
-    if (owns(i, j)) return;
+    if (own[e]) return;
     const int rv = rev[e];
     if (rv < 0) return;
     if (threadIdx.x >= NO * NO) return;
@@ -363,26 +433,30 @@ int run_density(xtb_ctx* c) {
             XTB_LAUNCH_CHECK(c);
         }
         XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
-        // slot capacity / stages from the shared-memory budget
-        constexpr int MT = 7;
-        int slotcap = (c->max_nn + 1) / 2 + 9;                 // balanced ownership: ~half the neighbours (+ slack), + self
-        if (slotcap > MT * NCW * 8 / NO) slotcap = MT * NCW * 8 / NO;     // rows must fit MT tiles per warp
+        // slot capacity / stages from the shared-memory budget (227 KB per CTA)
+        constexpr int MTMAX = 7;
+        int slotcap = (c->max_nn + 1) / 2 + 6;                 // balanced ownership: half the neighbours (+ slack), + self
+        if (slotcap > MTMAX * NCW * 8 / NO) slotcap = MTMAX * NCW * 8 / NO;     // rows must fit MTMAX tiles per warp
         if (slotcap > c->max_nn + 1) slotcap = c->max_nn + 1;
         if (slotcap < 2) slotcap = 2;
-        const size_t tile_b = (size_t)NO * KC * 8;
-        const size_t fixed = 2 * 8 * 8 + sizeof(int) * (2 * (size_t)slotcap + c->cap) + 64;
-        const size_t budget = 220 * 1024;
+        auto stage_bytes = [](int sc) { return (size_t)(sc * SLOT + 4 * BROW + 2 * KC) * 8; };
+        auto fixed_bytes = [&](int sc, int st) { return (size_t)3 * 8 * st + sizeof(int) * (2 * (size_t)sc + c->cap) + 64; };
+        const size_t budget = 227 * 1024 - 1024;
         int stages = 4;
-        while (stages > 2 && stages * (slotcap * tile_b + 2 * KC * 8) + fixed > budget) --stages;
-        while (stages * (slotcap * tile_b + 2 * KC * 8) + fixed > budget && slotcap > 2) --slotcap;
-        const size_t smem = stages * (slotcap * tile_b + 2 * KC * 8) + 2 * 8 * stages + sizeof(int) * (2 * (size_t)slotcap + c->cap) + 64;
-        auto kern = density_dmma_kernel<NO == 9 ? 9 : 9, MT>;
+        while (stages > 2 && stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages) > budget) {
+            // prefer 4 stages with a slightly smaller slot capacity over 3 stages, as long as the mean fits
+            if (slotcap > (c->max_nn + 1) / 2 + 2) --slotcap; else --stages;
+        }
+        while (stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages) > budget && slotcap > 2) --slotcap;
+        const size_t smem = stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages);
+        auto kern = density_dmma_kernel<NO == 9 ? 9 : 9>;
         XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int grid = c->sm_count < nown ? c->sm_count : nown;
-        kern<<<grid, NTHREADS, smem, c->stream>>>(na, c->a0, c->a1, c->cap, slotcap, stages, nchunks, (const int*)c->d_nn_size.p,
-                                                  (const int*)c->d_nn_list.p, (const int*)c->d_rowptr.p, (const double*)c->d_Ct.p,
-                                                  (const double*)c->d_wf.p, (const double*)c->d_wfe.p, (double*)c->d_rho.p,
-                                                  (double*)c->d_rhoE.p);
+        kern<<<grid, NTHREADS2, smem, c->stream>>>(na, c->a0, c->a1, c->cap, slotcap, stages, nchunks, (const int*)c->d_nn_size.p,
+                                                   (const int*)c->d_nn_list.p, (const signed char*)c->d_own.p,
+                                                   (const int*)c->d_rowptr.p, (const double*)c->d_Ct.p,
+                                                   (const double*)c->d_wf.p, (const double*)c->d_wfe.p, (double*)c->d_rho.p,
+                                                   (double*)c->d_rhoE.p);
         XTB_LAUNCH_CHECK(c);
         c->density_slotcap = slotcap; c->density_stages = stages;
     } else if (nown > 0) {
@@ -390,7 +464,7 @@ int run_density(xtb_ctx* c) {
         dim3 grid(c->max_nn + 1, nown);
         density_simple_kernel<NO><<<grid, 128, 0, c->stream>>>(na, c->a0, c->a1, c->cap, N, nkeep, (const int*)c->d_keep.p,
                                                                (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                               (const int*)c->d_rowptr.p, c->d_Ha, (const double*)c->d_wf.p,
+                                                               (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, c->d_Ha, (const double*)c->d_wf.p,
                                                                (const double*)c->d_wfe.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
         XTB_LAUNCH_CHECK(c);
     } else {
@@ -401,7 +475,7 @@ int run_density(xtb_ctx* c) {
     if (c->a0 == 0 && c->a1 == na && c->max_nn > 0) {
         dim3 grid(c->max_nn, na);
         mirror_blocks_kernel<NO><<<grid, 96, 0, c->stream>>>(na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                             (const int*)c->d_rev.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p,
+                                                             (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p,
                                                              (double*)c->d_rhoE.p);
         XTB_LAUNCH_CHECK(c);
     }
@@ -429,10 +503,10 @@ int xtb_impl_mirror_density(xtb_ctx* c) {
     dim3 grid(c->max_nn, c->na);
     if (c->n_orb == 9)
         mirror_blocks_kernel<9><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                            (const int*)c->d_rev.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
+                                                            (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
     else
         mirror_blocks_kernel<4><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                            (const int*)c->d_rev.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
+                                                            (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
     XTB_LAUNCH_CHECK(c);
     return XTB_OK;
 }

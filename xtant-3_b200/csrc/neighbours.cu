@@ -141,12 +141,20 @@ __global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* _
     if (threadIdx.x == 0) rowptr[na] = carry;
 }
 
+// own[e] = 1 iff atom i "owns" the unordered pair (i, j = nn_list[e]) in the symmetric density pass: the pair is
+// oriented by the sign of the minimum-image displacement stored in the SMALLER-index atom's entry (positive
+// half-space, lexicographic in x,y,z), so exactly one side owns it and, on a lattice with inversion symmetry,
+// every atom owns half of its neighbours (equal work per atom).  Pairs missing from the partner's list are owned.
+__device__ __forceinline__ bool positive_halfspace(const double* d) {
+    return d[0] > 0.0 || (d[0] == 0.0 && (d[1] > 0.0 || (d[1] == 0.0 && d[2] > 0.0)));
+}
+
 __global__ void nn_rev_kernel(int na, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
-                              int* __restrict__ rev) {
+                              const double* __restrict__ nn_dist, int* __restrict__ rev, signed char* __restrict__ own) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= (long long)na * cap) return;
     const int i = (int)(t / cap), k = (int)(t % cap);
-    if (k >= nn_size[i]) { rev[t] = -1; return; }
+    if (k >= nn_size[i]) { rev[t] = -1; own[t] = 0; return; }
     const int j = nn_list[t];
     const int* L = nn_list + (size_t)j * cap;
     int lo = 0, hi = nn_size[j] - 1, pos = -1;
@@ -157,6 +165,9 @@ __global__ void nn_rev_kernel(int na, int cap, const int* __restrict__ nn_size, 
         if (v < i) lo = mid + 1; else hi = mid - 1;
     }
     rev[t] = pos;
+    bool o = true;
+    if (pos >= 0) o = (i < j) ? positive_halfspace(nn_dist + 4 * t) : !positive_halfspace(nn_dist + 4 * ((size_t)j * cap + pos));
+    own[t] = o ? 1 : 0;
 }
 
 }  // namespace
@@ -183,6 +194,7 @@ int xtb_impl_neighbours(xtb_ctx* c, double rm) {
         if ((rc = xtb_reserve(c, c->d_nn_size, sizeof(int) * na))) return rc;
         if ((rc = xtb_reserve(c, c->d_nn_list, sizeof(int) * ne))) return rc;
         if ((rc = xtb_reserve(c, c->d_rev, sizeof(int) * ne))) return rc;
+        if ((rc = xtb_reserve(c, c->d_own, ne))) return rc;
         if ((rc = xtb_reserve(c, c->d_nn_dist, sizeof(double) * 4 * ne))) return rc;
         if ((rc = xtb_reserve(c, c->d_nn_dist_s, sizeof(double) * 3 * ne))) return rc;
         if ((rc = xtb_reserve(c, c->d_rowptr, sizeof(int) * (na + 1)))) return rc;
@@ -208,7 +220,8 @@ int xtb_impl_neighbours(xtb_ctx* c, double rm) {
     {
         const long long tot = (long long)na * c->cap;
         nn_rev_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c->stream>>>(na, c->cap, (const int*)c->d_nn_size.p,
-                                                                           (const int*)c->d_nn_list.p, (int*)c->d_rev.p);
+                                                                           (const int*)c->d_nn_list.p, (const double*)c->d_nn_dist.p,
+                                                                           (int*)c->d_rev.p, (signed char*)c->d_own.p);
         XTB_LAUNCH_CHECK(c);
     }
     int nb = 0;

@@ -42,7 +42,7 @@ struct xtb_ctx {
     int cap = 0, max_nn = 0;
     long long n_pairs = 0, n_blocks = 0;
     double rm = 0.0;
-    DevBuf d_nn_size, d_nn_list, d_nn_dist, d_nn_dist_s, d_rev, d_rowptr, d_maxnn;
+    DevBuf d_nn_size, d_nn_list, d_nn_dist, d_nn_dist_s, d_rev, d_own, d_rowptr, d_maxnn;
     bool have_neigh = false, have_dens = false;
     // NRL per-atom quantities
     DevBuf d_dens;              // embedded density rho_j
