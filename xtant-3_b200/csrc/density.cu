@@ -138,7 +138,7 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 //   [4][BROW]         B operand of atom i, already weighted: per k-step 32 doubles f*C[i,mu=0..7] in fragment order,
 //                     32 doubles f*E*C[i,mu<8], then f*C[i,8,t] (4) and f*E*C[i,8,t] (4);  BROW = 72
 //   [2][KC]           the weights f_n, f_n*E_n of the chunk
-// Warp roles: warps 0..NCW-1 consume; warp NCW issues the TMA bulk copies (producer); warp NCW+1 scales the B operand
+// Warp roles: warps 0..NCW-1 consume; warps NCW+1.. issue the TMA bulk copies (producers); warp NCW scales the B operand
 // once per chunk (instead of 8 warps x 4 k-steps doing it redundantly on the FP64 pipe the DMMAs need).
 // Barriers per stage: full (TMA bytes landed) -> bready (B operand scaled) -> consumers -> empty (NCW arrivals).
 //
@@ -148,7 +148,8 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 // where a third, 2/8-full DMMA column tile would waste 25 % of the pipe.
 constexpr int SLOT = 148;
 constexpr int BROW = 72;
-constexpr int NWARPS = NCW + 2;
+constexpr int NPROD = 4;                // producer warps (bulk-copy issue is serialised per lane within a warp)
+constexpr int NWARPS = NCW + 1 + NPROD;
 constexpr int NTHREADS2 = NWARPS * 32;
 
 struct StagePtrs {
@@ -159,7 +160,7 @@ template <int NO, int MT>
 __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_doubles, int slotcap, int stages,
                                                 uint64_t* full, uint64_t* bready, uint64_t* empty, uint32_t& it, int nchunks,
                                                 int nrows, int ntiles, int warp, int lane, const int* slot_q, size_t b0i,
-                                                bool first_subtask, double* __restrict__ rho, double* __restrict__ rhoE) {
+                                                bool first_subtask, int dbg, double* __restrict__ rho, double* __restrict__ rhoE) {
     const int g = lane >> 2, t = lane & 3;
     double acc0[MT][2], acc1[MT][2], p8f[MT], p8e[MT];
     int off[MT];
@@ -179,6 +180,7 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
         mbar_wait(&bready[st], ph);
         const double* stg = sbuf + (size_t)st * stage_doubles;
         const double* Bs = stg + boff;
+        if (!(dbg & 1))
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
             const double b0 = Bs[s * BROW + lane];
@@ -223,7 +225,7 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
 
 template <int NO>
 __global__ void __launch_bounds__(NTHREADS2, 1)
-density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, int nchunks,
+density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, int nchunks, int dbg,
                     const int* __restrict__ nn_size, const int* __restrict__ nn_list, const signed char* __restrict__ own,
                     const int* __restrict__ rowptr, const double* __restrict__ Ct, const double* __restrict__ wf,
                     const double* __restrict__ wfe, double* __restrict__ rho, double* __restrict__ rhoE) {
@@ -243,7 +245,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&bready[s], 1); mbar_init(&empty[s], NCW); }
+        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], NPROD); mbar_init(&bready[s], 1); mbar_init(&empty[s], NCW); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -281,9 +283,12 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
             const int nrows = nslots * NO;
             const int ntiles = (nrows + 7) >> 3;
 
-            if (warp == NCW) {
-                // ===== producer warp: stream the tiles of all slots for every chunk =====
-                const uint32_t bytes = (uint32_t)(nslots * TILE + 2 * KC) * 8u;
+            if (warp > NCW) {
+                // ===== producer warps: stream the tiles of all slots for every chunk; slot s belongs to producer s % NPROD =====
+                const int pw = warp - NCW - 1;
+                const int ncopy = (dbg & 2) ? (nslots + 3) / 4 : nslots;     // debug: quarter of the data
+                const int mine = ncopy > pw ? (ncopy - pw + NPROD - 1) / NPROD : 0;
+                const uint32_t bytes = (uint32_t)(mine * TILE + (pw == 0 ? 2 * KC : 0)) * 8u;
                 for (int ch = 0; ch < nchunks; ++ch, ++it) {
                     const int st = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
@@ -291,15 +296,19 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
                     double* dstage = sbuf + (size_t)st * stage_doubles;
                     if (lane == 0) {
                         mbar_expect_tx(&full[st], bytes);
-                        bulk_g2s(dstage + slotcap * SLOT + 4 * BROW, wf + (size_t)ch * KC, KC * 8, &full[st]);
-                        bulk_g2s(dstage + slotcap * SLOT + 4 * BROW + KC, wfe + (size_t)ch * KC, KC * 8, &full[st]);
+                        if (pw == 0) {
+                            bulk_g2s(dstage + slotcap * SLOT + 4 * BROW, wf + (size_t)ch * KC, KC * 8, &full[st]);
+                            bulk_g2s(dstage + slotcap * SLOT + 4 * BROW + KC, wfe + (size_t)ch * KC, KC * 8, &full[st]);
+                        }
                     }
                     __syncwarp();
                     const double* csrc = Ct + (size_t)ch * na * TILE;
-                    for (int s = lane; s < nslots; s += 32)
+                    for (int k = lane; k < mine; k += 32) {
+                        const int s = k * NPROD + pw;
                         bulk_g2s(dstage + s * SLOT, csrc + (size_t)slot_atom[s] * TILE, TILE * 8, &full[st]);
+                    }
                 }
-            } else if (warp == NCW + 1) {
+            } else if (warp == NCW) {
                 // ===== B warp: weighted B operand of atom i, once per chunk =====
                 for (int ch = 0; ch < nchunks; ++ch, ++it) {
                     const int st = it % stages;
@@ -329,13 +338,13 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
                 const int mt_need = (ntiles + NCW - 1) / NCW;
                 const bool fs = first == 0;
                 switch (mt_need) {
-                    case 1: consume_subtask<NO, 1>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
-                    case 2: consume_subtask<NO, 2>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
-                    case 3: consume_subtask<NO, 3>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
-                    case 4: consume_subtask<NO, 4>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
-                    case 5: consume_subtask<NO, 5>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
-                    case 6: consume_subtask<NO, 6>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
-                    default: consume_subtask<NO, 7>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, rho, rhoE); break;
+                    case 1: consume_subtask<NO, 1>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
+                    case 2: consume_subtask<NO, 2>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
+                    case 3: consume_subtask<NO, 3>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
+                    case 4: consume_subtask<NO, 4>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
+                    case 5: consume_subtask<NO, 5>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
+                    case 6: consume_subtask<NO, 6>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
+                    default: consume_subtask<NO, 7>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
                 }
             }
         }
@@ -452,7 +461,7 @@ int run_density(xtb_ctx* c) {
         auto kern = density_dmma_kernel<NO == 9 ? 9 : 9>;
         XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int grid = c->sm_count < nown ? c->sm_count : nown;
-        kern<<<grid, NTHREADS2, smem, c->stream>>>(na, c->a0, c->a1, c->cap, slotcap, stages, nchunks, (const int*)c->d_nn_size.p,
+        kern<<<grid, NTHREADS2, smem, c->stream>>>(na, c->a0, c->a1, c->cap, slotcap, stages, nchunks, c->density_dbg, (const int*)c->d_nn_size.p,
                                                    (const int*)c->d_nn_list.p, (const signed char*)c->d_own.p,
                                                    (const int*)c->d_rowptr.p, (const double*)c->d_Ct.p,
                                                    (const double*)c->d_wf.p, (const double*)c->d_wfe.p, (double*)c->d_rho.p,

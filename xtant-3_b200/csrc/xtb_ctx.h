@@ -69,6 +69,7 @@ struct xtb_ctx {
     int density_slotcap = 0, density_stages = 0;
     double stage_ms[8] = {0};
     int sm_count = 148;
+    int density_dbg = 0;        // XTB_DENSITY_DBG: bit0 consumers skip the math, bit1 producer copies 1/4 of the tiles (timing experiments only)
     int density_impl = 1;       // 1 = DMMA + bulk-copy pipeline, 0 = simple CUDA-core kernel (debug / cross-check)
 };
 
