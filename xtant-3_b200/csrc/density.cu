@@ -27,8 +27,12 @@
 
 namespace {
 
-constexpr int KC = 16;                 // states per chunk
-constexpr int NCW = 8;                 // consumer warps
+#ifndef XTB_KC
+#define XTB_KC 16
+#endif
+constexpr int KC = XTB_KC;             // states per chunk
+constexpr int KS = KC / 4;             // DMMA k-steps per chunk
+constexpr int CT_AT = 512 / KC;        // atoms per CTA of the re-tiling kernel (static shared memory budget)
 
 // pair ownership (exactly one of the two atoms owns an unordered pair) comes from the neighbour stage: own[e],
 // see nn_rev_kernel in neighbours.cu (positive half-space orientation: balanced work per atom).
@@ -71,11 +75,11 @@ __global__ void pad_weights_kernel(int nkeep, int kpad, double* __restrict__ wf,
 }
 
 // Ct[chunk][atom][s][r][t] = Ha[atom*NO + r, keep[chunk*16 + 4 s + t]]  (0 beyond nkeep)
-// one CTA per (chunk, group of 32 atoms): reads 16 columns x (32*NO) contiguous rows, writes contiguous tiles.
+// one CTA per (chunk, group of CT_AT atoms): reads KC columns x (CT_AT*NO) contiguous rows, writes contiguous tiles.
 template <int NO>
 __global__ void __launch_bounds__(256) ct_tile_kernel(int na, long long N, int nkeep, const int* __restrict__ keep,
                                                      const double* __restrict__ Ha, double* __restrict__ Ct) {
-    constexpr int AT = 32;
+    constexpr int AT = CT_AT;
     __shared__ double tile[KC][AT * NO + 1];
     const int chunk = blockIdx.x;
     const int atom0 = blockIdx.y * AT;
@@ -120,10 +124,26 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
         "WAIT_DONE:\n"
         "}\n" ::"r"(smem_u32(b)), "r"(parity) : "memory");
 }
+// polling wait (mbarrier.test_wait never suspends the warp): lowest wake-up latency, for the helper warps
+__device__ __forceinline__ void mbar_spin(uint64_t* b, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(done) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    } while (!done);
+}
 // TMA bulk copy global -> shared, completion signalled on an mbarrier (SASS: UBLKCP)
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+// L2 prefetch of a contiguous global range (no shared-memory destination): hides the DRAM latency of a later bulk copy
+__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
     asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -146,17 +166,16 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 // (mu = 0..7 for rho and for rho_E) plus two DFMA per row tile for mu = 8.  DMMA and DFMA share the FP64
 // execution resource on B200 (profiles/r01_probe_fp64_peaks.json), so this issues exactly the useful flops,
 // where a third, 2/8-full DMMA column tile would waste 25 % of the pipe.
-constexpr int SLOT = 148;
+constexpr int SLOT = 9 * KC + 4;       // 148 (KC = 16) / 292 (KC = 32): both = 4 mod 16
 constexpr int BROW = 72;
+constexpr int PF_AHEAD = 6;             // L2 prefetch distance in chunks (148 CTAs x ~45 tiles x 1152 B x 6 = 46 MB of the 126 MB L2)
 constexpr int NPROD = 4;                // producer warps (bulk-copy issue is serialised per lane within a warp)
-constexpr int NWARPS = NCW + 1 + NPROD;
-constexpr int NTHREADS2 = NWARPS * 32;
 
 struct StagePtrs {
     double* tiles; double* B; double* w;
 };
 
-template <int NO, int MT>
+template <int NO, int NCW, int MT>
 __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_doubles, int slotcap, int stages,
                                                 uint64_t* full, uint64_t* bready, uint64_t* empty, uint32_t& it, int nchunks,
                                                 int nrows, int ntiles, int warp, int lane, const int* slot_q, size_t b0i,
@@ -182,7 +201,7 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
         const double* Bs = stg + boff;
         if (!(dbg & 1))
 #pragma unroll
-        for (int s = 0; s < 4; ++s) {
+        for (int s = 0; s < KS; ++s) {
             const double b0 = Bs[s * BROW + lane];
             const double b1 = Bs[s * BROW + 32 + lane];
             const double b8f = Bs[s * BROW + 64 + t];
@@ -192,10 +211,14 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
             for (int mt = 0; mt < MT; ++mt) a[mt] = stg[off[mt] + NO * 4 * s];
 #pragma unroll
             for (int mt = 0; mt < MT; ++mt) {
-                dmma884(acc0[mt][0], acc0[mt][1], a[mt], b0);
-                dmma884(acc1[mt][0], acc1[mt][1], a[mt], b1);
-                p8f[mt] = fma(a[mt], b8f, p8f[mt]);
-                p8e[mt] = fma(a[mt], b8e, p8e[mt]);
+                if (!(dbg & 8)) {
+                    dmma884(acc0[mt][0], acc0[mt][1], a[mt], b0);
+                    dmma884(acc1[mt][0], acc1[mt][1], a[mt], b1);
+                }
+                if (!(dbg & 4)) {
+                    p8f[mt] = fma(a[mt], b8f, p8f[mt]);
+                    p8e[mt] = fma(a[mt], b8e, p8e[mt]);
+                }
             }
         }
         __syncwarp();
@@ -223,8 +246,8 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
     }
 }
 
-template <int NO>
-__global__ void __launch_bounds__(NTHREADS2, 1)
+template <int NO, int NCW>
+__global__ void __launch_bounds__((NCW + 1 + NPROD) * 32, 1)
 density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, int nchunks, int dbg,
                     const int* __restrict__ nn_size, const int* __restrict__ nn_list, const signed char* __restrict__ own,
                     const int* __restrict__ rowptr, const double* __restrict__ Ct, const double* __restrict__ wf,
@@ -232,10 +255,11 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
     static_assert(NO == 9, "column packing is written for the 9-orbital case (8 DMMA columns + 1 DFMA column per matrix)");
     constexpr int TILE = NO * KC;                       // doubles per (atom, chunk) tile in global memory
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int stage_doubles = slotcap * SLOT + 4 * BROW + 2 * KC;
+    const int stage_doubles = slotcap * SLOT + KS * BROW + 2 * KC;
     double* sbuf = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(sbuf + (size_t)stages * stage_doubles);
-    uint64_t* bready = full + stages;
+    uint64_t* bfull = full + stages;          // slot 0 (atom i) + weights landed: the B warp can start early
+    uint64_t* bready = bfull + stages;
     uint64_t* empty = bready + stages;
     int* slot_q = reinterpret_cast<int*>(empty + stages);     // [slotcap] list ordinal of slot s (s >= 1)
     int* slot_atom = slot_q + slotcap;                        // [slotcap] atom of slot s (slot 0 = i)
@@ -245,7 +269,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], NPROD); mbar_init(&bready[s], 1); mbar_init(&empty[s], NCW); }
+        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], NPROD); mbar_init(&bfull[s], 1); mbar_init(&bready[s], 1); mbar_init(&empty[s], NCW); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
@@ -287,25 +311,36 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
                 // ===== producer warps: stream the tiles of all slots for every chunk; slot s belongs to producer s % NPROD =====
                 const int pw = warp - NCW - 1;
                 const int ncopy = (dbg & 2) ? (nslots + 3) / 4 : nslots;     // debug: quarter of the data
-                const int mine = ncopy > pw ? (ncopy - pw + NPROD - 1) / NPROD : 0;
-                const uint32_t bytes = (uint32_t)(mine * TILE + (pw == 0 ? 2 * KC : 0)) * 8u;
+                // slot 0 and the weights go to their own barrier (bfull) so the B warp overlaps with the other copies
+                const int others = ncopy - 1;                                   // slots 1 .. ncopy-1
+                const int mine = others > pw ? (others - pw + NPROD - 1) / NPROD : 0;
+                const uint32_t bytes = (uint32_t)(mine * TILE) * 8u;
+                const int pf = (dbg & 16) ? PF_AHEAD : 0;     // L2 prefetch is off by default: its issue cost outweighs the latency it hides
                 for (int ch = 0; ch < nchunks; ++ch, ++it) {
                     const int st = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
-                    mbar_wait(&empty[st], ph ^ 1u);
+                    mbar_spin(&empty[st], ph ^ 1u);
                     double* dstage = sbuf + (size_t)st * stage_doubles;
+                    const double* csrc = Ct + (size_t)ch * na * TILE;
                     if (lane == 0) {
-                        mbar_expect_tx(&full[st], bytes);
                         if (pw == 0) {
-                            bulk_g2s(dstage + slotcap * SLOT + 4 * BROW, wf + (size_t)ch * KC, KC * 8, &full[st]);
-                            bulk_g2s(dstage + slotcap * SLOT + 4 * BROW + KC, wfe + (size_t)ch * KC, KC * 8, &full[st]);
+                            mbar_expect_tx(&bfull[st], (uint32_t)(TILE + 2 * KC) * 8u);
+                            bulk_g2s(dstage, csrc + (size_t)slot_atom[0] * TILE, TILE * 8, &bfull[st]);
+                            bulk_g2s(dstage + slotcap * SLOT + KS * BROW, wf + (size_t)ch * KC, KC * 8, &bfull[st]);
+                            bulk_g2s(dstage + slotcap * SLOT + KS * BROW + KC, wfe + (size_t)ch * KC, KC * 8, &bfull[st]);
                         }
+                        mbar_expect_tx(&full[st], bytes);
                     }
                     __syncwarp();
-                    const double* csrc = Ct + (size_t)ch * na * TILE;
                     for (int k = lane; k < mine; k += 32) {
-                        const int s = k * NPROD + pw;
+                        const int s = 1 + k * NPROD + pw;
                         bulk_g2s(dstage + s * SLOT, csrc + (size_t)slot_atom[s] * TILE, TILE * 8, &full[st]);
+                    }
+                    if (pf > 0 && ch + pf < nchunks) {      // warm the L2 for the chunk `pf` ahead (same slots)
+                        const double* psrc = Ct + (size_t)(ch + pf) * na * TILE;
+                        if (pw == 0 && lane == 0) bulk_prefetch_l2(psrc + (size_t)slot_atom[0] * TILE, TILE * 8);
+                        for (int k = lane; k < mine; k += 32)
+                            bulk_prefetch_l2(psrc + (size_t)slot_atom[1 + k * NPROD + pw] * TILE, TILE * 8);
                     }
                 }
             } else if (warp == NCW) {
@@ -313,13 +348,13 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
                 for (int ch = 0; ch < nchunks; ++ch, ++it) {
                     const int st = it % stages;
                     const uint32_t ph = (it / stages) & 1u;
-                    mbar_wait(&full[st], ph);
+                    mbar_spin(&bfull[st], ph);
                     double* stg = sbuf + (size_t)st * stage_doubles;
                     double* Bs = stg + slotcap * SLOT;
-                    const double* wsm = Bs + 4 * BROW;
+                    const double* wsm = Bs + KS * BROW;
                     const int g = lane >> 2, t = lane & 3;
 #pragma unroll
-                    for (int s = 0; s < 4; ++s) {
+                    for (int s = 0; s < KS; ++s) {
                         const double w_f = wsm[4 * s + t], w_e = wsm[KC + 4 * s + t];
                         const double ci = stg[NO * 4 * s + 4 * g + t];            // C[i, mu = g][state 4 s + t]
                         Bs[s * BROW + lane] = ci * w_f;                           // Atemp = distre * Ha        TB.f90:4378
@@ -337,15 +372,10 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
                 // ===== consumer warps =====
                 const int mt_need = (ntiles + NCW - 1) / NCW;
                 const bool fs = first == 0;
-                switch (mt_need) {
-                    case 1: consume_subtask<NO, 1>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
-                    case 2: consume_subtask<NO, 2>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
-                    case 3: consume_subtask<NO, 3>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
-                    case 4: consume_subtask<NO, 4>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
-                    case 5: consume_subtask<NO, 5>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
-                    case 6: consume_subtask<NO, 6>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
-                    default: consume_subtask<NO, 7>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); break;
-                }
+                constexpr int MTMAX = NCW == 8 ? 7 : NCW == 12 ? 5 : 4;      // row tiles per warp (register budget)
+#define XTB_CASE(M) if constexpr (M <= MTMAX) { if (mt_need == M || (M == MTMAX && mt_need > M)) consume_subtask<NO, NCW, M>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); }
+                XTB_CASE(1) XTB_CASE(2) XTB_CASE(3) XTB_CASE(4) XTB_CASE(5) XTB_CASE(6) XTB_CASE(7)
+#undef XTB_CASE
             }
         }
     }
@@ -437,19 +467,20 @@ int run_density(xtb_ctx* c) {
         }
         if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)kpad * N + 1024))) return rc;
         if (nchunks > 0) {
-            dim3 grid(nchunks, (na + 31) / 32);
+            dim3 grid(nchunks, (na + CT_AT - 1) / CT_AT);
             ct_tile_kernel<NO><<<grid, 256, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, c->d_Ha, (double*)c->d_Ct.p);
             XTB_LAUNCH_CHECK(c);
         }
         XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
         // slot capacity / stages from the shared-memory budget (227 KB per CTA)
-        constexpr int MTMAX = 7;
+        const int NCW = c->density_ncw == 16 ? 16 : c->density_ncw == 12 ? 12 : 8;
+        const int MTMAX = NCW == 8 ? 7 : NCW == 12 ? 5 : 4;
         int slotcap = (c->max_nn + 1) / 2 + 6;                 // balanced ownership: half the neighbours (+ slack), + self
         if (slotcap > MTMAX * NCW * 8 / NO) slotcap = MTMAX * NCW * 8 / NO;     // rows must fit MTMAX tiles per warp
         if (slotcap > c->max_nn + 1) slotcap = c->max_nn + 1;
         if (slotcap < 2) slotcap = 2;
-        auto stage_bytes = [](int sc) { return (size_t)(sc * SLOT + 4 * BROW + 2 * KC) * 8; };
-        auto fixed_bytes = [&](int sc, int st) { return (size_t)3 * 8 * st + sizeof(int) * (2 * (size_t)sc + c->cap) + 64; };
+        auto stage_bytes = [](int sc) { return (size_t)(sc * SLOT + KS * BROW + 2 * KC) * 8; };
+        auto fixed_bytes = [&](int sc, int st) { return (size_t)4 * 8 * st + sizeof(int) * (2 * (size_t)sc + c->cap) + 64; };
         const size_t budget = 227 * 1024 - 1024;
         int stages = 4;
         while (stages > 2 && stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages) > budget) {
@@ -458,14 +489,14 @@ int run_density(xtb_ctx* c) {
         }
         while (stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages) > budget && slotcap > 2) --slotcap;
         const size_t smem = stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages);
-        auto kern = density_dmma_kernel<NO == 9 ? 9 : 9>;
-        XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int grid = c->sm_count < nown ? c->sm_count : nown;
-        kern<<<grid, NTHREADS2, smem, c->stream>>>(na, c->a0, c->a1, c->cap, slotcap, stages, nchunks, c->density_dbg, (const int*)c->d_nn_size.p,
-                                                   (const int*)c->d_nn_list.p, (const signed char*)c->d_own.p,
-                                                   (const int*)c->d_rowptr.p, (const double*)c->d_Ct.p,
-                                                   (const double*)c->d_wf.p, (const double*)c->d_wfe.p, (double*)c->d_rho.p,
-                                                   (double*)c->d_rhoE.p);
+#define XTB_LAUNCH(W) { auto kern = density_dmma_kernel<9, W>; \
+        XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        kern<<<grid, (W + 1 + NPROD) * 32, smem, c->stream>>>(na, c->a0, c->a1, c->cap, slotcap, stages, nchunks, c->density_dbg, \
+            (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, \
+            (const double*)c->d_Ct.p, (const double*)c->d_wf.p, (const double*)c->d_wfe.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p); }
+        if (NCW == 16) XTB_LAUNCH(16) else if (NCW == 12) XTB_LAUNCH(12) else XTB_LAUNCH(8)
+#undef XTB_LAUNCH
         XTB_LAUNCH_CHECK(c);
         c->density_slotcap = slotcap; c->density_stages = stages;
     } else if (nown > 0) {

@@ -143,9 +143,14 @@ __global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* _
 
 // own[e] = 1 iff atom i "owns" the unordered pair (i, j = nn_list[e]) in the symmetric density pass: the pair is
 // oriented by the sign of the minimum-image displacement stored in the SMALLER-index atom's entry (positive
-// half-space, lexicographic in x,y,z), so exactly one side owns it and, on a lattice with inversion symmetry,
+// half-space of a generic direction), so exactly one side owns it and, on a lattice with inversion symmetry,
 // every atom owns half of its neighbours (equal work per atom).  Pairs missing from the partner's list are owned.
 __device__ __forceinline__ bool positive_halfspace(const double* d) {
+    // orientation by the sign of d.v, v a generic direction: no low-index lattice plane is perpendicular to it, so
+    // thermal displacements flip (and correlate) only the few neighbours with |d.v| below the noise; on a lattice
+    // with inversion symmetry every atom then owns half of its neighbours.  Exact ties fall back to lexicographic order.
+    const double p = d[0] + 0.754877666246693 * d[1] + 0.569840290998053 * d[2];
+    if (p != 0.0) return p > 0.0;
     return d[0] > 0.0 || (d[0] == 0.0 && (d[1] > 0.0 || (d[1] == 0.0 && d[2] > 0.0)));
 }
 

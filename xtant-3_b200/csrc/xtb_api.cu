@@ -45,6 +45,8 @@ int xtb_create(xtb_ctx** out, int device) {
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
     const char* impl = getenv("XTB_DENSITY_IMPL");
     if (impl) c->density_impl = atoi(impl);
+    const char* ncw = getenv("XTB_DENSITY_NCW");
+    if (ncw) c->density_ncw = atoi(ncw);
     const char* dbg = getenv("XTB_DENSITY_DBG");
     if (dbg) c->density_dbg = atoi(dbg);
     *out = c;

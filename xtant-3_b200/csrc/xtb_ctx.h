@@ -70,6 +70,7 @@ struct xtb_ctx {
     double stage_ms[8] = {0};
     int sm_count = 148;
     int density_dbg = 0;        // XTB_DENSITY_DBG: bit0 consumers skip the math, bit1 producer copies 1/4 of the tiles (timing experiments only)
+    int density_ncw = 8;        // consumer warps of the density kernel (8, 12 or 16); XTB_DENSITY_NCW
     int density_impl = 1;       // 1 = DMMA + bulk-copy pipeline, 0 = simple CUDA-core kernel (debug / cross-check)
 };
 
