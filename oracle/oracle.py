@@ -320,3 +320,81 @@ def nrl_step(wl, with_pressure=True, verbatim=False):
         if with_pressure:
             out["P"] = nrl_pressure_sparse(wl, nb, lmn, rad, out["rho"], out["rhoE"])
     return out
+
+
+# ---- Pettifor (orthogonal sp3) branch: oracle/pettifor_oracle.c ---------------------------------------
+def pettifor_params_array(params):
+    arr = (_abi.PettiforPair * len(params))()
+    for i, d in enumerate(params):
+        arr[i] = _abi.pettifor_pair_from_dict(d)
+    return arr
+
+
+def pet_assemble_H(wl, nb):
+    """Hamil_tot, TB_Pettifor.f90:1658-1810: dense H (N,N) [eV], N = 4*na (before diagonalisation)."""
+    N = 4 * nb.na
+    H = np.zeros((N, N), order="F")
+    S = np.ascontiguousarray(wl["S"], dtype=np.float64)
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    lib().orc_pet_assemble_H(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(S), _p(h),
+                             _p(nb.size), _p(nb.list), pettifor_params_array(wl["params"]), _p(H))
+    return H
+
+
+def pet_forces_verbatim(wl, nb, Aij):
+    """dHij_s with dense per-atom derivative matrices (TB_Pettifor.f90:141-223,463-521,354-399)."""
+    F = np.zeros((nb.na, 3))
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    A = np.asfortranarray(Aij)
+    lib().orc_pet_forces_verbatim(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(h), _p(nb.size),
+                                  _p(nb.list), _p(nb.dist), pettifor_params_array(wl["params"]), _p(A), _p(F))
+    return F
+
+
+def pet_forces_sparse(wl, nb, rho_blk, atom_first=0, atom_last=None):
+    F = np.zeros((nb.na, 3))
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    rho_blk = np.ascontiguousarray(rho_blk)
+    atom_last = nb.na if atom_last is None else atom_last
+    lib().orc_pet_forces_sparse(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(h), _p(nb.size),
+                                _p(nb.list), _p(nb.dist), pettifor_params_array(wl["params"]), _p(rho_blk),
+                                C.c_int(atom_first), C.c_int(atom_last), _p(F))
+    return F
+
+
+def pet_pressure(wl, nb, rho_blk):
+    """Attract_TB_Forces_Press, TB_Pettifor.f90:1134-1198 -> SCforce%att(3,3)."""
+    att = np.zeros(9)
+    rho_blk = np.ascontiguousarray(rho_blk)
+    lib().orc_pet_pressure(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(nb.size), _p(nb.list),
+                           _p(nb.dist), _p(nb.dist_s), pettifor_params_array(wl["params"]), _p(rho_blk), _p(att))
+    return att.reshape(3, 3, order="F")
+
+
+def eigensolve_orthogonal(H):
+    """sym_diagonalize -> dsyevd (Algebra_tools.f90:882-966), as construct_TB_H_Pettifor calls it (TB_Pettifor.f90:1455)."""
+    from scipy.linalg import lapack
+    w, v, info = lapack.dsyevd(np.asfortranarray(H), compute_v=1, lower=0)
+    if info != 0:
+        raise RuntimeError(f"dsyevd info={info}")
+    return np.asfortranarray(v), w
+
+
+def pettifor_step(wl, with_pressure=True, verbatim=False):
+    nb = neighbours(wl)
+    H = pet_assemble_H(wl, nb)
+    Ha, Ei = eigensolve_orthogonal(H)
+    wk = importlib.import_module("xtant-3_b200.workloads")
+    fe, mu = wk.occupations(Ei, wl["n_electrons"], wl["Te_eV"])
+    out = dict(nb=nb, H=H, Ha=Ha, Ei=Ei, fe=fe, mu=mu)
+    if verbatim:
+        Aij = density_dense(Ha, fe)
+        out["Aij"] = Aij
+        out["rho"] = gather_blocks(nb, 4, Aij)
+        out["F"] = pet_forces_verbatim(wl, nb, Aij)
+    else:
+        out["rho"], out["rhoE"] = density_blocks(nb, 4, Ha, fe, Ei)
+        out["F"] = pet_forces_sparse(wl, nb, out["rho"])
+    if with_pressure:
+        out["P"] = pet_pressure(wl, nb, out["rho"])
+    return out

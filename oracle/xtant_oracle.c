@@ -887,3 +887,6 @@ void orc_dks_block(const double* V, const double* dV, double l, double m, double
                    double dl, double dm, double dn, int test_variant, double* ts) {
     orc_d_KS_sp3d5_sgn(V, dV, l, m, n, dl, dm, dn, test_variant ? +1.0 : -1.0, ts);
 }
+
+/* Pettifor (orthogonal sp3) branch: shares the helpers above */
+#include "pettifor_oracle.c"
