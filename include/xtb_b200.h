@@ -122,6 +122,16 @@ int  xtb_radial(xtb_ctx*, double* M_Vij, double* M_dVij, double* M_SVij, double*
  *      panels of the owned atoms are written (host copies cover the same panels). */
 int  xtb_assemble_HS(xtb_ctx*, double* H_non, double* Sij);
 
+/* Multi-GPU form of S2b (replaces the MPI build's `MPI_Allreduce` of the dense Hij, Sij, TB_NRL.f90:326-327):
+ *   xtb_assemble_blocks  computes only the 4x4 / 9x9 blocks of the OWNED atoms into the block stores
+ *                        XTB_BUF_HBLK / XTB_BUF_SBLK ([rowptr[j]+q][mu + n_orb*nu], rows = neighbour q-1 or j itself, cols = j);
+ *   the caller allgathers the contiguous block ranges of all ranks (0.4 GB instead of 21.7 GB of dense panels at the
+ *   north-star size), then
+ *   xtb_expand_dense     writes the dense column panels of atoms first..last (1-based, inclusive) from the block stores
+ *                        (every element exactly once, zeros included); host pointers may be NULL. */
+int  xtb_assemble_blocks(xtb_ctx*);
+int  xtb_expand_dense(xtb_ctx*, int atom_first, int atom_last, double* H_non, double* Sij);
+
 /* ---- eigensolve boundary (outside the graft): Scell%Ha(N,N) (column n = state n),
  *      Scell%Ei(N) [eV], Scell%fe(N) (occupations incl. spin factor).  *_device: pointers
  *      are device memory that stays valid until the next xtb_set_eigen* call (zero copy). */
@@ -159,6 +169,8 @@ int  xtb_pressure(xtb_ctx*, double SCforce_att[9]);
 #define XTB_BUF_NNLIST   7   /* int32 ELL list, 0-based, [cap*na] */
 #define XTB_BUF_NNSIZE   8   /* int32 [na] */
 #define XTB_BUF_SCFORCE  9   /* 9 doubles */
+#define XTB_BUF_HBLK    10   /* block-sparse H [n_blocks][n_orb*n_orb] (eV) */
+#define XTB_BUF_SBLK    11   /* block-sparse S */
 int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
  *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,

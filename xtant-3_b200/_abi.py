@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libxtb_b200.so")
 XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE = range(7)
 XTB_TB_NONE, XTB_TB_NRL, XTB_TB_PETTIFOR, XTB_TB_DFTB = range(4)
 
-BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE = range(1, 10)
+BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK = range(1, 12)
 CNT_NA, CNT_NORB, CNT_N, CNT_MAXNN, CNT_NBLOCKS, CNT_NPAIRS, CNT_LAUNCHES, CNT_KKEPT, CNT_CAP = range(9)
 STAGE_NEIGH, STAGE_ASSEMBLE, STAGE_DENSITY, STAGE_FORCES, STAGE_PRESSURE = range(1, 6)
 
@@ -84,6 +84,8 @@ SIGNATURES = {
     "xtb_neighbours_compact": (C.c_int, [C.c_void_p, C.c_int, _pi, _pi, _pd, _pd, C.POINTER(C.c_int)]),
     "xtb_radial": (C.c_int, [C.c_void_p, _pd, _pd, _pd, _pd, _pd, _pd, _pd]),
     "xtb_assemble_HS": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_assemble_blocks": (C.c_int, [C.c_void_p]),
+    "xtb_expand_dense": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _pd, _pd]),
     "xtb_set_eigen": (C.c_int, [C.c_void_p, _pd, _pd, _pd]),
     "xtb_set_eigen_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "xtb_density": (C.c_int, [C.c_void_p, _pd, _pd]),

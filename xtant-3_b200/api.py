@@ -153,6 +153,21 @@ class TBContext:
         self._ck(self.lib.xtb_assemble_HS(self.h, _dp(H), _dp(S)))
         return H, S
 
+    def assemble_blocks(self):
+        """S2 for the owned atoms, block stores only (multi-GPU: allgather the blocks, then expand_dense)."""
+        self._ck(self.lib.xtb_assemble_blocks(self.h))
+
+    def expand_dense(self, first=1, last=None, to_host=False):
+        last = self.na if last is None else last
+        if not to_host:
+            self._ck(self.lib.xtb_expand_dense(self.h, int(first), int(last), None, None))
+            return None, None
+        N = self.na * self.n_orb
+        H = np.zeros((N, N), order="F")
+        S = np.zeros((N, N), order="F") if self.tb != "pettifor" else None
+        self._ck(self.lib.xtb_expand_dense(self.h, int(first), int(last), _dp(H), _dp(S)))
+        return H, S
+
     # -- eigensolve boundary ------------------------------------------------------------------
     def set_eigen(self, Ha, Ei, fe):
         Ha = np.asfortranarray(Ha, dtype=np.float64)

@@ -240,6 +240,6 @@ int xtb_impl_neighbours(xtb_ctx* c, double rm) {
     c->n_pairs = nb - na;
     c->rm = rm;
     c->have_neigh = true;
-    c->have_HS = c->have_density = c->have_dens = false;
+    c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
     return XTB_OK;
 }

@@ -162,22 +162,23 @@ __global__ void __launch_bounds__(256) dense_panel_kernel(int na, int a0, int ca
 }
 
 template <int NO>
-static void launch_panel(xtb_ctx* c, int nown, size_t smem, const double* Ablk, const double* Bblk, double* A, double* B, bool tr) {
+static void launch_panel(xtb_ctx* c, int f0, int nown, size_t smem, const double* Ablk, const double* Bblk, double* A, double* B, bool tr) {
     if (tr)
-        dense_panel_kernel<NO, true><<<nown, 256, smem, c->stream>>>(c->na, c->a0, c->cap, (const int*)c->d_nn_size.p,
+        dense_panel_kernel<NO, true><<<nown, 256, smem, c->stream>>>(c->na, f0, c->cap, (const int*)c->d_nn_size.p,
                                                                      (const int*)c->d_nn_list.p, (const int*)c->d_rowptr.p, Ablk, Bblk, A, B);
     else
-        dense_panel_kernel<NO, false><<<nown, 256, smem, c->stream>>>(c->na, c->a0, c->cap, (const int*)c->d_nn_size.p,
+        dense_panel_kernel<NO, false><<<nown, 256, smem, c->stream>>>(c->na, f0, c->cap, (const int*)c->d_nn_size.p,
                                                                       (const int*)c->d_nn_list.p, (const int*)c->d_rowptr.p, Ablk, Bblk, A, B);
 }
 
-int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, double* A, double* B, bool tr) {
-    const int nown = c->a1 - c->a0;
+int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, double* A, double* B, bool tr, int f0, int f1) {
+    if (f0 < 0) { f0 = c->a0; f1 = c->a1; }      // default: the owned atoms
+    const int nown = f1 - f0;
     if (nown <= 0) return XTB_OK;
     const size_t smem = sizeof(int) * (c->cap + 256);
-    if (c->n_orb == 9) launch_panel<9>(c, nown, smem, Ablk, Bblk, A, B, tr);
-    else if (c->n_orb == 4) launch_panel<4>(c, nown, smem, Ablk, Bblk, A, B, tr);
-    else if (c->n_orb == 1) launch_panel<1>(c, nown, smem, Ablk, Bblk, A, B, tr);
+    if (c->n_orb == 9) launch_panel<9>(c, f0, nown, smem, Ablk, Bblk, A, B, tr);
+    else if (c->n_orb == 4) launch_panel<4>(c, f0, nown, smem, Ablk, Bblk, A, B, tr);
+    else if (c->n_orb == 1) launch_panel<1>(c, f0, nown, smem, Ablk, Bblk, A, B, tr);
     else XTB_FAIL(c, XTB_EINVAL, "unsupported n_orb %d", c->n_orb);
     XTB_LAUNCH_CHECK(c);
     return XTB_OK;
@@ -236,25 +237,29 @@ int xtb_impl_nrl_dens(xtb_ctx* c) {
     return XTB_OK;
 }
 
-int xtb_impl_nrl_assemble(xtb_ctx* c) {
+int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense) {
     const int na = c->na;
     const size_t N = (size_t)na * 9;
     int rc;
     if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 81 * (size_t)c->n_blocks))) return rc;
     if ((rc = xtb_reserve(c, c->d_Sblk, sizeof(double) * 81 * (size_t)c->n_blocks))) return rc;
-    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
-    if ((rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
+    if (dense) {
+        if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
+        if ((rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
+    }
     XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     if ((rc = xtb_impl_nrl_dens(c))) return rc;
     const int nown = c->a1 - c->a0;
     const long long nthreads = 2LL * (c->cap + 1) * nown;
-    nrl_blocks_kernel<<<(unsigned)((nthreads + 127) / 128), 128, 0, c->stream>>>(
-        na, c->a0, c->a1, c->cap, c->n_kinds, (const int*)c->d_koa.p, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-        (const int*)c->d_rev.p, (const double*)c->d_nn_dist.p, (const int*)c->d_rowptr.p, (const xtb_nrl_pair*)c->d_params.p,
-        (const double*)c->d_dens.p, (double*)c->d_Hblk.p, (double*)c->d_Sblk.p);
-    XTB_LAUNCH_CHECK(c);
+    if (nthreads > 0) {
+        nrl_blocks_kernel<<<(unsigned)((nthreads + 127) / 128), 128, 0, c->stream>>>(
+            na, c->a0, c->a1, c->cap, c->n_kinds, (const int*)c->d_koa.p, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+            (const int*)c->d_rev.p, (const double*)c->d_nn_dist.p, (const int*)c->d_rowptr.p, (const xtb_nrl_pair*)c->d_params.p,
+            (const double*)c->d_dens.p, (double*)c->d_Hblk.p, (double*)c->d_Sblk.p);
+        XTB_LAUNCH_CHECK(c);
+    }
     XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
-    if ((rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, (const double*)c->d_Sblk.p, (double*)c->d_H.p, (double*)c->d_S2.p, false))) return rc;
+    if (dense && (rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, (const double*)c->d_Sblk.p, (double*)c->d_H.p, (double*)c->d_S2.p, false))) return rc;
     XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     float ms = 0.f, ms2 = 0.f;
@@ -262,6 +267,7 @@ int xtb_impl_nrl_assemble(xtb_ctx* c) {
     cudaEventElapsedTime(&ms2, c->ev_mid, c->ev1);
     c->stage_ms[2] = ms;
     c->stage_ms[6] = ms2;     // dense panel kernel alone
-    c->have_HS = true;
+    c->have_blocks = true;
+    c->have_HS = dense;
     return XTB_OK;
 }

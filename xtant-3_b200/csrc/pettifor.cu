@@ -241,12 +241,12 @@ __global__ void pet_sum9_kernel(int n, const double* __restrict__ partial, doubl
 
 }  // namespace
 
-int xtb_impl_pettifor_assemble(xtb_ctx* c) {
+int xtb_impl_pettifor_assemble(xtb_ctx* c, bool dense) {
     const int na = c->na;
     const size_t N = (size_t)na * 4;
     int rc;
     if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 16 * (size_t)c->n_blocks))) return rc;
-    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
+    if (dense && (rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
     XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     const int nown = c->a1 - c->a0;
     const long long nthreads = (long long)(c->cap + 1) * nown;
@@ -258,7 +258,7 @@ int xtb_impl_pettifor_assemble(xtb_ctx* c) {
         XTB_LAUNCH_CHECK(c);
     }
     XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
-    if ((rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, nullptr, (double*)c->d_H.p, nullptr, false))) return rc;
+    if (dense && (rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, nullptr, (double*)c->d_H.p, nullptr, false))) return rc;
     XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     float ms = 0.f, ms2 = 0.f;
@@ -266,7 +266,8 @@ int xtb_impl_pettifor_assemble(xtb_ctx* c) {
     cudaEventElapsedTime(&ms2, c->ev_mid, c->ev1);
     c->stage_ms[2] = ms;
     c->stage_ms[6] = ms2;
-    c->have_HS = true;
+    c->have_blocks = true;
+    c->have_HS = dense;
     return XTB_OK;
 }
 

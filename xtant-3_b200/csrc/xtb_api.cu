@@ -88,7 +88,7 @@ static int upload_params(xtb_ctx* c, const void* p, size_t bytes) {
     if (rc) return rc;
     XTB_CUDA(c, cudaMemcpyAsync(c->d_params.p, p, bytes, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->have_neigh = c->have_HS = c->have_density = c->have_dens = false;
+    c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
     return XTB_OK;
 }
 
@@ -134,7 +134,7 @@ int xtb_set_system(xtb_ctx* c, int na, const int32_t* koa, const double* S, cons
     memcpy(c->h_supce, supce, sizeof(double) * 9);
     if (na != c->na) { c->cap = 0; c->a0 = 0; c->a1 = na; }
     c->na = na;
-    c->have_neigh = c->have_HS = c->have_density = c->have_dens = false;
+    c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
     return XTB_OK;
 }
 
@@ -242,8 +242,8 @@ int xtb_assemble_HS(xtb_ctx* c, double* H_non, double* Sij) {
     cudaSetDevice(c->device);
     if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_assemble_HS: run xtb_neighbours first");
     int rc;
-    if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_assemble(c);
-    else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_assemble(c);
+    if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_assemble(c, true);
+    else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_assemble(c, true);
     else XTB_FAIL(c, XTB_EINVAL, "xtb_assemble_HS: no TB parametrisation set");
     if (rc) return rc;
     const size_t N = (size_t)c->na * c->n_orb;
@@ -254,6 +254,41 @@ int xtb_assemble_HS(xtb_ctx* c, double* H_non, double* Sij) {
         XTB_CUDA(c, cudaMemcpyAsync(Sij + off, (double*)c->d_S2.p + off, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
     }
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_assemble_blocks(xtb_ctx* c) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_assemble_blocks: run xtb_neighbours first");
+    if (c->tb == XTB_TB_NRL) return xtb_impl_nrl_assemble(c, false);
+    if (c->tb == XTB_TB_PETTIFOR) return xtb_impl_pettifor_assemble(c, false);
+    XTB_FAIL(c, XTB_EINVAL, "xtb_assemble_blocks: no TB parametrisation set");
+}
+
+int xtb_expand_dense(xtb_ctx* c, int first, int last, double* H_non, double* Sij) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_blocks) XTB_FAIL(c, XTB_ESTATE, "xtb_expand_dense: no block store (xtb_assemble_blocks / xtb_assemble_HS first)");
+    if (first < 1 || last > c->na || last < first - 1) XTB_FAIL(c, XTB_EINVAL, "xtb_expand_dense: bad range %d..%d", first, last);
+    const bool ortho = c->tb == XTB_TB_PETTIFOR;
+    if (Sij && ortho) XTB_FAIL(c, XTB_EINVAL, "xtb_expand_dense: orthogonal parametrisation has no overlap matrix");
+    const size_t N = (size_t)c->na * c->n_orb;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
+    if (!ortho && (rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
+    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    if ((rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, ortho ? nullptr : (const double*)c->d_Sblk.p, (double*)c->d_H.p,
+                                    ortho ? nullptr : (double*)c->d_S2.p, false, first - 1, last))) return rc;
+    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    const size_t off = (size_t)(first - 1) * c->n_orb * N, cnt = (size_t)(last - first + 1) * c->n_orb * N;
+    if (H_non && cnt) XTB_CUDA(c, cudaMemcpyAsync(H_non + off, (double*)c->d_H.p + off, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+    if (Sij && cnt) XTB_CUDA(c, cudaMemcpyAsync(Sij + off, (double*)c->d_S2.p + off, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->stage_ms[6] = ms;
+    c->have_HS = true;
     return XTB_OK;
 }
 
@@ -374,6 +409,8 @@ int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
         case XTB_BUF_NNLIST: b = &c->d_nn_list; used = 4 * (size_t)c->na * c->cap; break;
         case XTB_BUF_NNSIZE: b = &c->d_nn_size; used = 4 * (size_t)c->na; break;
         case XTB_BUF_SCFORCE: b = &c->d_SC; used = 72; break;
+        case XTB_BUF_HBLK: b = &c->d_Hblk; used = 8 * nb2 * (size_t)c->n_blocks; break;
+        case XTB_BUF_SBLK: b = &c->d_Sblk; used = 8 * nb2 * (size_t)c->n_blocks; break;
         default: XTB_FAIL(c, XTB_EINVAL, "xtb_device_buffer: unknown buffer %d", which);
     }
     if (!b->p) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: buffer %d not produced yet", which);

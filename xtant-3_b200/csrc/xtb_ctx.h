@@ -50,7 +50,7 @@ struct xtb_ctx {
     // block-sparse H, S ([n_blocks][n_orb^2], block (j,q): rows = neighbour / j itself, cols = j) and dense H, S
     DevBuf d_Hblk, d_Sblk;
     DevBuf d_H, d_S2;
-    bool have_HS = false;
+    bool have_HS = false, have_blocks = false;
     // eigen
     const double* d_Ha = nullptr; const double* d_Ei = nullptr; const double* d_fe = nullptr;
     DevBuf own_Ha, own_Ei, own_fe;
@@ -104,9 +104,9 @@ void xtb_free(DevBuf& b);
 
 // stage implementations (one translation unit each)
 int xtb_impl_neighbours(xtb_ctx* c, double rm);
-int xtb_impl_nrl_assemble(xtb_ctx* c);
+int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense);     // dense = false: block stores only
 int xtb_impl_nrl_dens(xtb_ctx* c);          // embedded densities rho_j (needed by S2 and by the on-site force terms)
-int xtb_impl_pettifor_assemble(xtb_ctx* c);
+int xtb_impl_pettifor_assemble(xtb_ctx* c, bool dense);
 int xtb_impl_density(xtb_ctx* c);
 int xtb_impl_nrl_forces(xtb_ctx* c);
 int xtb_impl_nrl_pressure(xtb_ctx* c);
@@ -115,4 +115,4 @@ int xtb_impl_pettifor_pressure(xtb_ctx* c);
 int xtb_impl_mirror_density(xtb_ctx* c);
 int xtb_impl_nrl_tables(xtb_ctx* c, double* d_rad, double* d_geo);   // compact M_V*/M_lmn/M_xrr/M_x1 per list entry
 // dense column panels of the owned atoms from a block store; tr: block holds (rows j, cols neighbour)
-int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, double* A, double* B, bool tr);
+int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, double* A, double* B, bool tr, int f0 = -1, int f1 = -1);
