@@ -398,3 +398,82 @@ def pettifor_step(wl, with_pressure=True, verbatim=False):
     if with_pressure:
         out["P"] = pet_pressure(wl, nb, out["rho"])
     return out
+
+
+# ---- DFTB branch: oracle/dftb_oracle.c ----------------------------------------------------------------
+def dftb_cutoff(wl):
+    """get_near_neighbours for TB_H_DFTB, Atomic_tools.f90:588-591: rm = max(rcut) + 10*max(d)."""
+    return max(p["rcut"] for p in wl["params"]) + 10.0 * max(p["d"] for p in wl["params"])
+
+
+def dftb_radial(wl, nb):
+    """Construct_Vij_DFTB, TB_DFTB.f90:56-228 -> compact (na, cap, 4, 10): M_Vij, M_dVij, M_SVij, M_dSVij of entry (j, a2)."""
+    rad = np.zeros((nb.na, nb.cap, 40))
+    TB, keep = _abi.dftb_pair_array(wl["params"])
+    lib().orc_dftb_radial(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(_koa0(wl)),
+                          C.c_int(wl["n_kinds"]), TB, C.c_int(wl["basis"]), _p(rad))
+    return rad
+
+
+def dftb_assemble_HS(wl, nb, lmn, rad):
+    N = nb.na * wl["n_orb"]
+    H = np.zeros((N, N), order="F"); S = np.zeros((N, N), order="F")
+    TB, keep = _abi.dftb_pair_array(wl["params"])
+    lib().orc_dftb_assemble_HS(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(lmn), _p(rad),
+                               _p(_koa0(wl)), C.c_int(wl["n_kinds"]), TB, C.c_int(wl["basis"]), _p(H), _p(S))
+    return H, S
+
+
+def dftb_forces_verbatim(wl, nb, lmn, rad, Aij, AijE):
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    TB, keep = _abi.dftb_pair_array(wl["params"])
+    F = np.zeros((nb.na, 3))
+    lib().orc_dftb_forces_verbatim(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(lmn), _p(rad),
+                                   _p(_koa0(wl)), C.c_int(wl["n_kinds"]), TB, C.c_int(wl["basis"]), _p(h),
+                                   _p(np.asfortranarray(Aij)), _p(np.asfortranarray(AijE)), _p(F))
+    return F
+
+
+def dftb_forces_sparse(wl, nb, lmn, rad, rho_blk, rhoE_blk, atom_first=0, atom_last=None):
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    TB, keep = _abi.dftb_pair_array(wl["params"])
+    atom_last = nb.na if atom_last is None else atom_last
+    F = np.zeros((nb.na, 3))
+    lib().orc_dftb_forces_sparse(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(lmn), _p(rad),
+                                 _p(_koa0(wl)), C.c_int(wl["n_kinds"]), TB, C.c_int(wl["basis"]), _p(h),
+                                 _p(np.ascontiguousarray(rho_blk)), _p(np.ascontiguousarray(rhoE_blk)),
+                                 C.c_int(atom_first), C.c_int(atom_last), _p(F))
+    return F
+
+
+def dftb_pressure(wl, nb, lmn, rad, rho_blk, rhoE_blk, atom_first=0, atom_last=None):
+    TB, keep = _abi.dftb_pair_array(wl["params"])
+    atom_last = nb.na if atom_last is None else atom_last
+    att = np.zeros(9)
+    lib().orc_dftb_pressure(C.c_int(nb.na), C.c_int(nb.cap), _p(nb.size), _p(nb.list), _p(nb.dist), _p(nb.dist_s), _p(lmn),
+                            _p(rad), _p(_koa0(wl)), C.c_int(wl["n_kinds"]), TB, C.c_int(wl["basis"]),
+                            _p(np.ascontiguousarray(rho_blk)), _p(np.ascontiguousarray(rhoE_blk)),
+                            C.c_int(atom_first), C.c_int(atom_last), _p(att))
+    return att.reshape(3, 3, order="F")
+
+
+def dftb_step(wl, with_pressure=True, verbatim=False):
+    nb = neighbours(wl, rm=dftb_cutoff(wl))
+    lmn, xrr, x1 = geometry(wl, nb)
+    rad = dftb_radial(wl, nb)
+    H, S = dftb_assemble_HS(wl, nb, lmn, rad)
+    Ha, Ei, wS = eigensolve_nonorthogonal(H, S)
+    wk = importlib.import_module("xtant-3_b200.workloads")
+    fe, mu = wk.occupations(Ei, wl["n_electrons"], wl["Te_eV"])
+    no = wl["n_orb"]
+    out = dict(nb=nb, lmn=lmn, rad=rad, H=H, S=S, Ha=Ha, Ei=Ei, fe=fe, mu=mu, eigen_S=wS)
+    out["rho"], out["rhoE"] = density_blocks(nb, no, Ha, fe, Ei)
+    if verbatim:
+        Aij = density_dense(Ha, fe); AijE = density_dense(Ha, fe, Ei)
+        out.update(Aij=Aij, AijE=AijE)
+        out["F"] = dftb_forces_verbatim(wl, nb, lmn, rad, Aij, AijE)
+    else:
+        out["F"] = dftb_forces_sparse(wl, nb, lmn, rad, out["rho"], out["rhoE"])
+    if with_pressure:
+        out["P"] = dftb_pressure(wl, nb, lmn, rad, out["rho"], out["rhoE"])
+    return out

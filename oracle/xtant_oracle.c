@@ -890,3 +890,4 @@ void orc_dks_block(const double* V, const double* dV, double l, double m, double
 
 /* Pettifor (orthogonal sp3) branch: shares the helpers above */
 #include "pettifor_oracle.c"
+#include "dftb_oracle.c"

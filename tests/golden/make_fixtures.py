@@ -7,6 +7,8 @@ It writes
     xtant-3_b200/data/params_nrl_{Au,Al,Si}.json    NRL parameter sets
     xtant-3_b200/data/params_pettifor_C.json        Pettifor parameter set
     xtant-3_b200/data/cell_{diamond64,al500,au108}.json   relative coords + supercell
+    xtant-3_b200/data/dftb_{matsci_SiAl,mio_CH}.npz  DFTB Slater-Koster tables (INPUT_DATA/DFTB/<set>/<A>-<B>.skf, read by
+                                                     xtant-3_b200/skf.py = read_skf_file, Dealing_with_DFTB.f90:48-149)
 The parsers restate the reference readers:
     read_Mehl_TB_Hamiltonian      Source_files/Read_input_data.f90:3963-4158
     read_Pettifor_TB_Hamiltonian  Source_files/Read_input_data.f90:3377-3661
@@ -14,6 +16,7 @@ The parsers restate the reference readers:
       (file line i of SAVE_supercell.dat = column i of supce)
 Only numbers are copied (they are model parameters / coordinates, not code).
 """
+import importlib
 import json
 import os
 import re
@@ -117,6 +120,13 @@ def main():
         with open(os.path.join(OUT, name), "w") as f:
             json.dump(d, f, indent=0, separators=(",", ":"))
         print("wrote", name, {k: (len(v) if isinstance(v, list) else v) for k, v in d.items() if k in ("koa", "Rc", "rm")})
+    # DFTB table sets: pair index (KOA1-1) + n*(KOA2-1) <- file "<El(KOA1)>-<El(KOA2)>.skf" (Read_input_data.f90:4224)
+    sys.path.insert(0, os.path.join(HERE, "..", ".."))
+    skf = importlib.import_module("xtant-3_b200.skf")
+    for name, folder, els in (("matsci_SiAl", "matsci-0-3", ["Si", "Al"]), ("mio_CH", "mio-1-1", ["C", "H"])):
+        pairs = [skf.parse_skf(f"{REF}/DFTB/{folder}/{a}-{b}.skf", a == b) for b in els for a in els]
+        skf.save_set(name, els, pairs)
+        print("wrote", f"dftb_{name}.npz", els, [p["Vr"].shape for p in pairs])
 
 
 if __name__ == "__main__":

@@ -34,3 +34,13 @@ for name, c in CASES.items():
                      F_first4=[float(x) for x in o["F"][:4].ravel()], P=[float(x) for x in o["P"].ravel(order="F")])
     print(name, out[name]["n_pairs"], out[name]["Ei_pick"])
 json.dump(out, open(os.path.join(HERE, "oracle_regression.json"), "w"), indent=1)
+
+# DFTB branch: tests/golden/dftb_regression.json (same status: the oracle's own outputs, frozen)
+dout = {}
+for name, fn in (("sial", wk.sial_zb), ("ch", wk.ch_zb)):
+    o = orc.dftb_step(fn(), verbatim=False)
+    dout[name] = dict(nn_size=[int(x) for x in o["nb"].size], H_head=[float(x) for x in o["H"][:9, :18].ravel()],
+                      S_head=[float(x) for x in o["S"][:9, :18].ravel()], Ei_head=[float(x) for x in o["Ei"][:16]],
+                      F_head=[float(x) for x in o["F"][:8].ravel()], P=[float(x) for x in o["P"].ravel()])
+    print(name, sum(dout[name]["nn_size"]), dout[name]["Ei_head"][:2])
+json.dump(dout, open(os.path.join(HERE, "dftb_regression.json"), "w"), indent=0)

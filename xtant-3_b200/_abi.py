@@ -64,6 +64,27 @@ def pettifor_pair_from_dict(d):
     return p
 
 
+def dftb_pair_array(params):
+    """-> (ctypes array of DftbPair, list of the numpy arrays the pointers refer to: keep it alive during the call)"""
+    import numpy as np
+    arr = (DftbPair * len(params))()
+    keep = []
+    for i, d in enumerate(params):
+        Rr = np.ascontiguousarray(d["Rr"], dtype=np.float64)
+        Vr = np.asfortranarray(d["Vr"], dtype=np.float64)      # (ir, channel) column-major
+        Sr = np.asfortranarray(d["Sr"], dtype=np.float64)
+        assert Vr.shape == (Rr.shape[0], 10) and Sr.shape == Vr.shape
+        keep += [Rr, Vr, Sr]
+        p = arr[i]
+        p.rcut, p.d = float(d["rcut"]), float(d["d"])
+        p.Ed, p.Ep, p.Es = float(d["Ed"]), float(d["Ep"]), float(d["Es"])
+        p.n_r, p.pad_ = int(Rr.shape[0]), 0
+        p.Rr = Rr.ctypes.data_as(C.POINTER(C.c_double))
+        p.Vr = Vr.ctypes.data_as(C.POINTER(C.c_double))
+        p.Sr = Sr.ctypes.data_as(C.POINTER(C.c_double))
+    return arr, keep
+
+
 _pd = C.POINTER(C.c_double)
 _pi = C.POINTER(C.c_int32)
 

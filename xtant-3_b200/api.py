@@ -5,7 +5,7 @@ procedures they stand in for (same argument meaning, results in the reference's 
 
     get_near_neighbours            Source_files/Atomic_tools.f90:562
     Construct_M_x1 / Construct_Vij_NRL   Source_files/TB.f90:3430, TB_NRL.f90:1956   (-> radial_tables)
-    construct_TB_H_NRL / construct_TB_H_Pettifor   TB_NRL.f90:74, TB_Pettifor.f90:1427  (-> assemble_HS)
+    construct_TB_H_NRL / construct_TB_H_Pettifor / construct_TB_H_DFTB   TB_NRL.f90:74, TB_Pettifor.f90:1427, TB_DFTB.f90:284  (-> assemble_HS)
     Construct_Aij / Construct_Aij_x_En   TB.f90:4328,4401                             (-> density)
     get_dHij_drij_NRL / dHij_s     TB_NRL.f90:2412, TB_Pettifor.f90:141               (-> forces)
     Attract_TB_Forces_Press_NRL / Attract_TB_Forces_Press  TB_NRL.f90:2742, TB_Pettifor.f90:1134 (-> pressure)
@@ -92,6 +92,10 @@ class TBContext:
             arr = (_abi.PettiforPair * (nk * nk))(*[_abi.pettifor_pair_from_dict(d) for d in wl["params"]])
             self._ck(self.lib.xtb_set_params_pettifor(self.h, nk, arr))
             self.n_orb = 4
+        elif wl["tb"] == "dftb":
+            arr, keep = _abi.dftb_pair_array(wl["params"])     # tables are copied by the library during the call
+            self._ck(self.lib.xtb_set_params_dftb(self.h, nk, int(wl["n_orb"]), arr))
+            self.n_orb = int(wl["n_orb"])
         else:
             raise ValueError(wl["tb"])
         self.tb = wl["tb"]
@@ -135,9 +139,10 @@ class TBContext:
 
     # -- S2 ---------------------------------------------------------------------------------
     def radial_tables(self):
-        """Construct_M_x1 + Construct_Vij_NRL in the reference's dense shapes (small systems)."""
+        """Construct_M_x1 + Construct_Vij_NRL / Construct_Vij_DFTB in the reference's dense shapes (small systems)."""
         na = self.na
-        out = {k: np.zeros((na, na, 10), order="F") for k in ("M_Vij", "M_dVij", "M_SVij", "M_dSVij")}
+        nv = 10 if self.tb == "nrl" else {1: 1, 4: 4, 9: 10}[self.n_orb]
+        out = {k: np.zeros((na, na, nv), order="F") for k in ("M_Vij", "M_dVij", "M_SVij", "M_dSVij")}
         out.update({k: np.zeros((3, na, na), order="F") for k in ("M_lmn", "M_x1", "M_xrr")})
         self._ck(self.lib.xtb_radial(self.h, _dp(out["M_Vij"]), _dp(out["M_dVij"]), _dp(out["M_SVij"]), _dp(out["M_dSVij"]),
                                      _dp(out["M_lmn"]), _dp(out["M_x1"]), _dp(out["M_xrr"])))

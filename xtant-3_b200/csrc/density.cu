@@ -535,13 +535,17 @@ int run_density(xtb_ctx* c) {
 int xtb_impl_density(xtb_ctx* c) {
     if (c->n_orb == 9) return run_density<9>(c);
     if (c->n_orb == 4) return run_density<4>(c);
+    if (c->n_orb == 1) return run_density<1>(c);
     XTB_FAIL(c, XTB_EINVAL, "density: unsupported n_orb %d", c->n_orb);
 }
 
 int xtb_impl_mirror_density(xtb_ctx* c) {
     if (c->max_nn <= 0) return XTB_OK;
     dim3 grid(c->max_nn, c->na);
-    if (c->n_orb == 9)
+    if (c->n_orb == 1)
+        mirror_blocks_kernel<1><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                            (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
+    else if (c->n_orb == 9)
         mirror_blocks_kernel<9><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
                                                             (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
     else

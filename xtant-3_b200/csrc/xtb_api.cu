@@ -2,6 +2,7 @@
 // reference's array shapes, and dispatch on the TB parametrisation (the `select type` arms of
 // Source_files/TB.f90:247-317,459-487 collapse to ctx->tb).  All arithmetic is in the stage files.
 #include "xtb_ctx.h"
+#include "dftb_device.cuh"
 #include <cstdlib>
 #include <cstring>
 #include <new>
@@ -60,7 +61,7 @@ int xtb_destroy(xtb_ctx* c) {
     DevBuf* all[] = {&c->d_params, &c->d_koa, &c->d_S, &c->d_nn_size, &c->d_nn_list, &c->d_nn_dist, &c->d_nn_dist_s, &c->d_rev, &c->d_own,
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
-                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab};
+                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab};
     for (DevBuf* b : all) xtb_free(*b);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -110,9 +111,33 @@ int xtb_set_params_pettifor(xtb_ctx* c, int n_kinds, const xtb_pettifor_pair* p)
     return upload_params(c, p, sizeof(xtb_pettifor_pair) * (size_t)n_kinds * n_kinds);
 }
 
-int xtb_set_params_dftb(xtb_ctx* c, int, int, const xtb_dftb_pair*) {
+int xtb_set_params_dftb(xtb_ctx* c, int n_kinds, int n_orb, const xtb_dftb_pair* p) {
     if (!c) return XTB_EINVAL;
-    XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_dftb: the DFTB branch is not built yet (SURVEY.md 8a row a11)");
+    if (n_kinds <= 0 || !p) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_dftb: n_kinds=%d", n_kinds);
+    if (n_orb != 1 && n_orb != 4 && n_orb != 9) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_dftb: n_orb=%d (1 = s, 4 = sp3, 9 = sp3d5)", n_orb);
+    cudaSetDevice(c->device);
+    // flatten the tables: one buffer of doubles, per pair Rr[n_r], Vr[n_r*10], Sr[n_r*10]
+    const int np = n_kinds * n_kinds;
+    std::vector<DftbDev> dev(np);
+    std::vector<double> tab;
+    double rcmax = 0.0, dmax = 0.0;
+    for (int q = 0; q < np; ++q) {
+        const xtb_dftb_pair& s = p[q];
+        if (s.n_r < 2 || !s.Rr || !s.Vr || !s.Sr) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_dftb: pair %d has no tables (n_r=%d)", q, s.n_r);
+        if (!(s.d > 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_dftb: pair %d has smoothing width d=%g", q, s.d);
+        DftbDev& d = dev[q];
+        d.rcut = s.rcut; d.d = s.d; d.Ed = s.Ed; d.Ep = s.Ep; d.Es = s.Es; d.n_r = s.n_r; d.pad_ = 0;
+        d.off_R = (long long)tab.size(); tab.insert(tab.end(), s.Rr, s.Rr + s.n_r);
+        d.off_V = (long long)tab.size(); tab.insert(tab.end(), s.Vr, s.Vr + (size_t)s.n_r * 10);
+        d.off_S = (long long)tab.size(); tab.insert(tab.end(), s.Sr, s.Sr + (size_t)s.n_r * 10);
+        rcmax = s.rcut > rcmax ? s.rcut : rcmax; dmax = s.d > dmax ? s.d : dmax;
+    }
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_dftb_tab, sizeof(double) * tab.size()))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_dftb_tab.p, tab.data(), sizeof(double) * tab.size(), cudaMemcpyHostToDevice, c->stream));
+    c->tb = XTB_TB_DFTB; c->n_kinds = n_kinds; c->n_orb = n_orb;
+    c->dftb_rm = rcmax + 10.0 * dmax;
+    return upload_params(c, dev.data(), sizeof(DftbDev) * (size_t)np);
 }
 
 int xtb_set_system(xtb_ctx* c, int na, const int32_t* koa, const double* S, const double* supce) {
@@ -152,6 +177,7 @@ static double default_cutoff(const xtb_ctx* c) {
     double rm = 0.0;
     if (c->tb == XTB_TB_NRL) { for (auto& p : c->h_nrl) rm = p.Rc > rm ? p.Rc : rm; rm *= XTB_G_AU2A; }
     else if (c->tb == XTB_TB_PETTIFOR) { for (auto& p : c->h_pet) rm = p.rm > rm ? p.rm : rm; }
+    else if (c->tb == XTB_TB_DFTB) rm = c->dftb_rm;
     return rm;
 }
 
@@ -204,7 +230,8 @@ int xtb_radial(xtb_ctx* c, double* M_Vij, double* M_dVij, double* M_SVij, double
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
     if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_radial: run xtb_neighbours first");
-    if (c->tb != XTB_TB_NRL) XTB_FAIL(c, XTB_EINVAL, "xtb_radial: dense tables are provided for the NRL branch only");
+    if (c->tb != XTB_TB_NRL && c->tb != XTB_TB_DFTB) XTB_FAIL(c, XTB_EINVAL, "xtb_radial: dense tables are provided for the NRL and DFTB branches");
+    const int nv = c->tb == XTB_TB_NRL ? 10 : dftb::n_v(c->n_orb);     // channels of M_V*(na,na,nv)
     if (!M_Vij && !M_dVij && !M_SVij && !M_dSVij && !M_lmn && !M_x1 && !M_xrr) return XTB_OK;   // fused on the device otherwise
     const int na = c->na, cap = c->cap;
     const size_t ne = (size_t)na * cap;
@@ -212,7 +239,7 @@ int xtb_radial(xtb_ctx* c, double* M_Vij, double* M_dVij, double* M_SVij, double
     if ((rc = xtb_reserve(c, c->d_tab, sizeof(double) * 49 * ne))) return rc;
     double* d_rad = (double*)c->d_tab.p;
     double* d_geo = d_rad + 40 * ne;
-    if ((rc = xtb_impl_nrl_tables(c, d_rad, d_geo))) return rc;
+    if ((rc = (c->tb == XTB_TB_NRL ? xtb_impl_nrl_tables(c, d_rad, d_geo) : xtb_impl_dftb_tables(c, d_rad, d_geo)))) return rc;
     std::vector<double> rad(40 * ne), geo(9 * ne);
     std::vector<int32_t> sz(na), li(ne);
     XTB_CUDA(c, cudaMemcpyAsync(rad.data(), d_rad, sizeof(double) * 40 * ne, cudaMemcpyDeviceToHost, c->stream));
@@ -222,7 +249,7 @@ int xtb_radial(xtb_ctx* c, double* M_Vij, double* M_dVij, double* M_SVij, double
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     const size_t n2 = (size_t)na * na;
     double* Mv[4] = {M_Vij, M_dVij, M_SVij, M_dSVij};
-    for (int t = 0; t < 4; ++t) if (Mv[t]) memset(Mv[t], 0, sizeof(double) * 10 * n2);         // TB_NRL.f90:2137-2140
+    for (int t = 0; t < 4; ++t) if (Mv[t]) memset(Mv[t], 0, sizeof(double) * nv * n2);         // TB_NRL.f90:2137-2140, TB_DFTB.f90:86-89
     double* Mg[3] = {M_lmn, M_xrr, M_x1};
     for (int t = 0; t < 3; ++t) if (Mg[t]) memset(Mg[t], 0, sizeof(double) * 3 * n2);           // TB.f90:3448-3450
     for (int i = 0; i < na; ++i)
@@ -230,7 +257,7 @@ int xtb_radial(xtb_ctx* c, double* M_Vij, double* M_dVij, double* M_SVij, double
             const size_t e = (size_t)i * cap + k;
             const int j = li[e];
             for (int t = 0; t < 4; ++t) if (Mv[t])
-                for (int ch = 0; ch < 10; ++ch) Mv[t][(size_t)i + (size_t)na * j + n2 * ch] = rad[40 * e + 10 * t + ch];   // M(i,j,ch)
+                for (int ch = 0; ch < nv; ++ch) Mv[t][(size_t)i + (size_t)na * j + n2 * ch] = rad[40 * e + 10 * t + ch];   // M(i,j,ch)
             for (int t = 0; t < 3; ++t) if (Mg[t])
                 for (int a = 0; a < 3; ++a) Mg[t][a + 3 * ((size_t)i + (size_t)na * j)] = geo[9 * e + 3 * t + a];          // M(a,i,j)
         }
@@ -244,6 +271,7 @@ int xtb_assemble_HS(xtb_ctx* c, double* H_non, double* Sij) {
     int rc;
     if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_assemble(c, true);
     else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_assemble(c, true);
+    else if (c->tb == XTB_TB_DFTB) rc = xtb_impl_dftb_assemble(c, true);
     else XTB_FAIL(c, XTB_EINVAL, "xtb_assemble_HS: no TB parametrisation set");
     if (rc) return rc;
     const size_t N = (size_t)c->na * c->n_orb;
@@ -263,6 +291,7 @@ int xtb_assemble_blocks(xtb_ctx* c) {
     if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_assemble_blocks: run xtb_neighbours first");
     if (c->tb == XTB_TB_NRL) return xtb_impl_nrl_assemble(c, false);
     if (c->tb == XTB_TB_PETTIFOR) return xtb_impl_pettifor_assemble(c, false);
+    if (c->tb == XTB_TB_DFTB) return xtb_impl_dftb_assemble(c, false);
     XTB_FAIL(c, XTB_EINVAL, "xtb_assemble_blocks: no TB parametrisation set");
 }
 
@@ -368,6 +397,7 @@ int xtb_forces(xtb_ctx* c, double* F_att) {
     int rc;
     if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_forces(c);
     else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_forces(c);
+    else if (c->tb == XTB_TB_DFTB) rc = xtb_impl_dftb_forces(c);
     else XTB_FAIL(c, XTB_EINVAL, "xtb_forces: no TB parametrisation set");
     if (rc) return rc;
     const size_t cnt = (size_t)(c->a1 - c->a0) * 3;
@@ -385,6 +415,7 @@ int xtb_pressure(xtb_ctx* c, double* SCforce_att) {
     int rc;
     if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_pressure(c);
     else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_pressure(c);
+    else if (c->tb == XTB_TB_DFTB) rc = xtb_impl_dftb_pressure(c);
     else XTB_FAIL(c, XTB_EINVAL, "xtb_pressure: no TB parametrisation set");
     if (rc) return rc;
     if (SCforce_att) {

@@ -30,7 +30,9 @@ struct xtb_ctx {
     int n_orb = 0;
     std::vector<xtb_nrl_pair> h_nrl;
     std::vector<xtb_pettifor_pair> h_pet;
-    DevBuf d_params;            // array of the active pair struct
+    DevBuf d_params;            // array of the active pair struct (DFTB: array of DftbDev, dftb_device.cuh)
+    DevBuf d_dftb_tab;          // DFTB: all radial grids and tables, one buffer of doubles
+    double dftb_rm = 0.0;       // DFTB: max(rcut) + 10*max(d)  (get_near_neighbours, Atomic_tools.f90:588-591)
 
     // system
     int na = 0;
@@ -113,6 +115,10 @@ int xtb_impl_nrl_pressure(xtb_ctx* c);
 int xtb_impl_pettifor_forces(xtb_ctx* c);
 int xtb_impl_pettifor_pressure(xtb_ctx* c);
 int xtb_impl_mirror_density(xtb_ctx* c);
+int xtb_impl_dftb_assemble(xtb_ctx* c, bool dense);
+int xtb_impl_dftb_forces(xtb_ctx* c);
+int xtb_impl_dftb_pressure(xtb_ctx* c);
+int xtb_impl_dftb_tables(xtb_ctx* c, double* d_rad, double* d_geo);  // compact tables, nv channels per list entry
 int xtb_impl_nrl_tables(xtb_ctx* c, double* d_rad, double* d_geo);   // compact M_V*/M_lmn/M_xrr/M_x1 per list entry
 // dense column panels of the owned atoms from a block store; tr: block holds (rows j, cols neighbour)
 int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, double* A, double* B, bool tr, int f0 = -1, int f1 = -1);

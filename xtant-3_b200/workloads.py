@@ -100,6 +100,56 @@ def c_dia(reps, sigma=0.05, seed=3):
     return _wl(f"c_dia_{reps[0]}x{reps[1]}x{reps[2]}", "pettifor", "C", S, h, 4, 1.0)
 
 
+# ---- DFTB branch: tables from xtant-3_b200/data/dftb_*.npz (skf.py) ----
+_ZB_A, _ZB_B = _FCC, _FCC + 0.25      # zincblende sublattices
+
+
+def _wl_dftb(name, setname, rcut, d, S, supce, koa, n_el_per_kind, Te_eV, kinds=None, force_s_basis=False):
+    import importlib
+    skf = importlib.import_module("xtant-3_b200.skf")
+    elements, basis, pairs = skf.load_set(setname, rcut, d)
+    if kinds is not None:            # sub-set of the elements of the table set
+        nk = len(elements)
+        pairs = [pairs[a + nk * b] for b in kinds for a in kinds]
+        elements = [elements[k] for k in kinds]
+        if force_s_basis:            # test-only: drop the p level so that idnetify_basis_size picks the s basis
+            for p in pairs:
+                p["Ep"] = 0.0
+                p["Ed"] = 0.0
+        basis, pairs = skf.finish_set(pairs, rcut, d)
+    koa = np.asarray(koa, dtype=np.int32)
+    na = S.shape[0]
+    return dict(name=name, tb="dftb", basis=basis, n_orb=(1, 4, 9)[basis], na=na, koa=koa,
+                S=np.ascontiguousarray(S, dtype=np.float64), supce=np.ascontiguousarray(supce, dtype=np.float64),
+                params=pairs, n_kinds=len(elements), element="-".join(elements),
+                n_electrons=float(sum(n_el_per_kind[k - 1] for k in koa)), Te_eV=float(Te_eV))
+
+
+def _zincblende(a, reps, sigma, seed):
+    S, h = lattice(np.vstack([_ZB_A, _ZB_B]), a, reps, sigma, seed)
+    koa = np.tile(np.array([1, 1, 1, 1, 2, 2, 2, 2], dtype=np.int32), reps[0] * reps[1] * reps[2])
+    return S, h, koa
+
+
+def sial_zb(reps=(2, 2, 2), sigma=0.05, seed=64):
+    """Si/Al zincblende cell, matsci-0-3 sp3d5 tables, cut-off of INPUT_DATA/SiAl/TB_Hamiltonian_parameters.txt (5.0, 0.1 A)"""
+    S, h, koa = _zincblende(5.6, reps, sigma, seed)
+    return _wl_dftb(f"sial_zb_{reps[0]}x{reps[1]}x{reps[2]}", "matsci_SiAl", 5.0, 0.1, S, h, koa, (4, 3), 0.5)
+
+
+def ch_zb(reps=(2, 2, 2), sigma=0.05, seed=65):
+    """C/H zincblende-ordered cell, mio-1-1 tables (sp3 basis: H carries the shifted p level), cut-off 3.5 + 10*0.1 A"""
+    S, h, koa = _zincblende(3.7, reps, sigma, seed)
+    return _wl_dftb(f"ch_zb_{reps[0]}x{reps[1]}x{reps[2]}", "mio_CH", 3.5, 0.1, S, h, koa, (4, 1), 0.5)
+
+
+def h_sc(reps=(3, 3, 3), a=2.4, sigma=0.05, seed=66):
+    """hydrogen simple-cubic cell, mio-1-1 H-H table restricted to the s basis (test of the basis_ind = 0 branch)"""
+    S, h = lattice(np.zeros((1, 3)), a, reps, sigma, seed)
+    return _wl_dftb(f"h_sc_{reps[0]}x{reps[1]}x{reps[2]}", "mio_CH", 3.0, 0.1, S, h, np.ones(S.shape[0], dtype=np.int32),
+                    (1,), 0.5, kinds=[1], force_s_basis=True)
+
+
 CONFIGS = {"diamond64": diamond64, "si216": si216, "al500": al500, "ac1000": ac1000, "au4096": au4096}
 
 
