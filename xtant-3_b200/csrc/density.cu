@@ -124,10 +124,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
         "WAIT_DONE:\n"
         "}\n" ::"r"(smem_u32(b)), "r"(parity) : "memory");
 }
+// non-blocking phase test
+__device__ __forceinline__ uint32_t mbar_test(uint64_t* b, uint32_t parity) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return done;
+}
 // polling wait (mbarrier.test_wait never suspends the warp): lowest wake-up latency, for the helper warps
-__device__ __forceinline__ void mbar_spin(uint64_t* b, uint32_t parity) {
+__device__ __forceinline__ void mbar_spin(uint64_t* b, uint32_t parity, bool nap = false) {
     uint32_t done;
     do {
+        if (nap) __nanosleep(40);
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
@@ -168,17 +180,69 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 // where a third, 2/8-full DMMA column tile would waste 25 % of the pipe.
 constexpr int SLOT = 9 * KC + 4;       // 148 (KC = 16) / 292 (KC = 32): both = 4 mod 16
 constexpr int BROW = 72;
-constexpr int PF_AHEAD = 6;             // L2 prefetch distance in chunks (148 CTAs x ~45 tiles x 1152 B x 6 = 46 MB of the 126 MB L2)
-constexpr int NPROD = 4;                // producer warps (bulk-copy issue is serialised per lane within a warp)
+constexpr int NPROD = 3;                // producer warps (bulk-copy issue is serialised per lane within a warp); 8 + 1 + 3 = 12 warps = 3 per SM sub-partition -> 168 registers per thread
 
-struct StagePtrs {
-    double* tiles; double* B; double* w;
+// ---- lock-step between CTAs ----
+// The CTAs of one round work on spatially adjacent atoms, so at the same chunk index they read largely the same tiles of
+// Ct: as long as they stay within a few chunks of each other the 126 MB L2 serves most of the ~40x reuse of every tile.
+// Left alone they drift apart (tasks differ by a row tile or two) and every tile is fetched from HBM again (340 GB
+// instead of ~50 GB per launch, measured).  The producers therefore publish their position (round, sub-task, chunk) and
+// do not run more than `lead` chunks ahead of the slowest CTA.  The slowest CTA never waits; should a CTA not be
+// resident (foreign work on an SM) the wait gives up after a bounded number of polls and throttling is switched off.
+constexpr int SYNC_EVERY = 16;      // position published / checked every this many chunks (one L2 round trip per check)
+__device__ __forceinline__ void st_relaxed(long long* p, long long v) {
+    asm volatile("st.relaxed.gpu.global.s64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ long long ld_relaxed(const long long* p) {
+    long long v;
+    asm volatile("ld.relaxed.gpu.global.s64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+// returns false if the wait was abandoned (a CTA did not move for ~10 ms, e.g. it is not resident): the caller then
+// stops throttling -- lock-step is a bandwidth optimisation, never a correctness requirement
+__device__ __forceinline__ bool throttle(long long* prog, long long pos, int lead, int lane) {
+    if (lane == 0) st_relaxed(prog + blockIdx.x, pos);
+    for (int tries = 0; tries < 8192; ++tries) {
+        long long m = 0x7fffffffffffffffLL;
+        for (int b = lane; b < (int)gridDim.x; b += 32)
+            if (b != (int)blockIdx.x) { const long long v = ld_relaxed(prog + b); m = v < m ? v : m; }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { const long long v = __shfl_xor_sync(0xffffffffu, m, o); m = v < m ? v : m; }
+        if (m + lead >= pos) return true;
+    }
+    return false;
+}
+
+// ring position shared by all roles: stage index and phase parity, advanced without integer division
+struct Ring {
+    uint32_t st, ph;
+    __device__ __forceinline__ void next(uint32_t stages) { if (++st == stages) { st = 0; ph ^= 1u; } }
 };
 
-template <int NO, int NCW, int MT>
-__device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_doubles, int slotcap, int stages,
-                                                uint64_t* full, uint64_t* bready, uint64_t* empty, uint32_t& it, int nchunks,
-                                                int nrows, int ntiles, int warp, int lane, const int* slot_q, size_t b0i,
+// operands of one k-step of one warp: MT A fragments + the B fragments (rho, rho_E, and the mu = 8 columns)
+template <int MT>
+struct Frag {
+    double a[MT], b0, b1, b8f, b8e;
+};
+template <int NO, int MT>
+__device__ __forceinline__ void load_frag(Frag<MT>& f, const double* __restrict__ stg, const double* __restrict__ Bs,
+                                          const int (&off)[MT], int s, int lane, int t) {
+    f.b0 = Bs[s * BROW + lane];
+    f.b1 = Bs[s * BROW + 32 + lane];
+    f.b8f = Bs[s * BROW + 64 + t];
+    f.b8e = Bs[s * BROW + 68 + t];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) f.a[mt] = stg[off[mt] + NO * 4 * s];
+}
+
+// Consumer warp, one sub-task (atom i + up to slotcap-1 owned neighbours), MT row tiles.
+// The chunk loop is software-pipelined across the stage boundary: the operands of k-step 0 of the NEXT chunk are
+// fetched (after its barriers) before the math of the last k-step of the current chunk is issued, so the barrier
+// round trip and the shared-memory latency hide behind 12 DMMAs instead of idling the FP64 pipe once per chunk.
+template <int NO, int NCW, int MT, bool DBG>
+__device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_doubles, int boff, uint32_t stages,
+                                                uint64_t* full, uint64_t* bready, uint64_t* empty, Ring& rg, int nchunks,
+                                                int nrows, int warp, int lane, const int* slot_q, size_t b0i,
                                                 bool first_subtask, int dbg, double* __restrict__ rho, double* __restrict__ rhoE) {
     const int g = lane >> 2, t = lane & 3;
     double acc0[MT][2], acc1[MT][2], p8f[MT], p8e[MT];
@@ -190,39 +254,50 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
         const int R = 8 * (warp + NCW * mt) + g;
         const int sl = R / NO, r = R - sl * NO;
         off[mt] = (R < nrows) ? sl * SLOT + 4 * r + t : t;      // rows beyond the task read row 0 (results dropped)
+        asm volatile("" : "+r"(off[mt]));                      // keep it in a register (no per-chunk re-derivation)
     }
-    const int boff = slotcap * SLOT;
-    for (int ch = 0; ch < nchunks; ++ch, ++it) {
-        const int st = it % stages;
-        const uint32_t ph = (it / stages) & 1u;
-        mbar_wait(&full[st], ph);
-        mbar_wait(&bready[st], ph);
-        const double* stg = sbuf + (size_t)st * stage_doubles;
-        const double* Bs = stg + boff;
-        if (!(dbg & 1))
+    if (nchunks > 0) {
+        const double* stg = sbuf + (size_t)rg.st * stage_doubles;
+        mbar_wait(&full[rg.st], rg.ph);
+        mbar_wait(&bready[rg.st], rg.ph);
+        Frag<MT> f0, f1;      // double buffer: even k-steps compute from f0 while f1 is loaded, odd k-steps the other way round
+        load_frag<NO, MT>(f0, stg, stg + boff, off, 0, lane, t);
+        static_assert(KS % 2 == 0, "the fragment double buffer needs an even number of k-steps per chunk");
+        for (int ch = 0; ch < nchunks; ++ch) {
+            Ring rn = rg;
+            rn.next(stages);
+            const double* stg_n = sbuf + (size_t)rn.st * stage_doubles;
+            uint32_t ready = 0;
 #pragma unroll
-        for (int s = 0; s < KS; ++s) {
-            const double b0 = Bs[s * BROW + lane];
-            const double b1 = Bs[s * BROW + 32 + lane];
-            const double b8f = Bs[s * BROW + 64 + t];
-            const double b8e = Bs[s * BROW + 68 + t];
-            double a[MT];
-#pragma unroll
-            for (int mt = 0; mt < MT; ++mt) a[mt] = stg[off[mt] + NO * 4 * s];
-#pragma unroll
-            for (int mt = 0; mt < MT; ++mt) {
-                if (!(dbg & 8)) {
-                    dmma884(acc0[mt][0], acc0[mt][1], a[mt], b0);
-                    dmma884(acc1[mt][0], acc1[mt][1], a[mt], b1);
+            for (int s = 0; s < KS; ++s) {
+                Frag<MT>& cu = (s & 1) ? f1 : f0;
+                Frag<MT>& nx = (s & 1) ? f0 : f1;
+                if (s + 1 < KS) {
+                    load_frag<NO, MT>(nx, stg, stg + boff, off, s + 1, lane, t);
+                    // probe the barriers of the next stage one k-step early: the answer is in a register long before it is needed
+                    if (s + 2 == KS && ch + 1 < nchunks) ready = mbar_test(&full[rn.st], rn.ph) & mbar_test(&bready[rn.st], rn.ph);
+                } else if (ch + 1 < nchunks) {
+                    if (!ready) { mbar_wait(&full[rn.st], rn.ph); mbar_wait(&bready[rn.st], rn.ph); }
+                    load_frag<NO, MT>(nx, stg_n, stg_n + boff, off, 0, lane, t);
                 }
-                if (!(dbg & 4)) {
-                    p8f[mt] = fma(a[mt], b8f, p8f[mt]);
-                    p8e[mt] = fma(a[mt], b8e, p8e[mt]);
+                if (!DBG || !(dbg & 1)) {
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt) {
+                        dmma884(acc0[mt][0], acc0[mt][1], cu.a[mt], cu.b0);
+                        dmma884(acc1[mt][0], acc1[mt][1], cu.a[mt], cu.b1);
+                        if (!DBG || !(dbg & 8)) {
+                            p8f[mt] = fma(cu.a[mt], cu.b8f, p8f[mt]);
+                            p8e[mt] = fma(cu.a[mt], cu.b8e, p8e[mt]);
+                        }
+                    }
                 }
             }
+            // every shared-memory read of this stage has been issued (in order, ahead of the arrive)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[rg.st]);
+            rg = rn;
+            stg = stg_n;
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[st]);
     }
     // ---- epilogue: D(row R -> (slot, nu), col -> mu) -> block (i, slot)[mu + NO*nu] ----
 #pragma unroll
@@ -231,9 +306,8 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
         double f8 = p8f[mt], e8 = p8e[mt];
         f8 += __shfl_xor_sync(0xffffffffu, f8, 1); e8 += __shfl_xor_sync(0xffffffffu, e8, 1);
         f8 += __shfl_xor_sync(0xffffffffu, f8, 2); e8 += __shfl_xor_sync(0xffffffffu, e8, 2);
-        const int tile = warp + NCW * mt;
-        const int R = 8 * tile + g;
-        if (tile < ntiles && R < nrows) {
+        const int R = 8 * (warp + NCW * mt) + g;
+        if (R < nrows) {
             const int sl = R / NO, nu = R - sl * NO;
             if (sl > 0 || first_subtask) {     // the on-site block belongs to the first sub-task only
                 const size_t blk = (b0i + (sl == 0 ? 0 : 1 + slot_q[sl])) * (NO * NO) + NO * nu;
@@ -246,15 +320,28 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
     }
 }
 
-template <int NO, int NCW>
+// consumer warp with no row tile in this sub-task: it still takes part in the empty barriers
+__device__ __forceinline__ void consume_idle(uint32_t stages, uint64_t* full, uint64_t* bready, uint64_t* empty, Ring& rg,
+                                             int nchunks, int lane) {
+    for (int ch = 0; ch < nchunks; ++ch) {
+        mbar_wait(&full[rg.st], rg.ph);
+        mbar_wait(&bready[rg.st], rg.ph);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[rg.st]);
+        rg.next(stages);
+    }
+}
+
+template <int NO, int NCW, bool DBG>
 __global__ void __launch_bounds__((NCW + 1 + NPROD) * 32, 1)
-density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, int nchunks, int dbg,
+density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, int nchunks, int dbg, int maxsub, int lead, long long* __restrict__ prog,
                     const int* __restrict__ nn_size, const int* __restrict__ nn_list, const signed char* __restrict__ own,
                     const int* __restrict__ rowptr, const double* __restrict__ Ct, const double* __restrict__ wf,
                     const double* __restrict__ wfe, double* __restrict__ rho, double* __restrict__ rhoE) {
     static_assert(NO == 9, "column packing is written for the 9-orbital case (8 DMMA columns + 1 DFMA column per matrix)");
     constexpr int TILE = NO * KC;                       // doubles per (atom, chunk) tile in global memory
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    const uint32_t stages = (uint32_t)stages_;
     const int stage_doubles = slotcap * SLOT + KS * BROW + 2 * KC;
     double* sbuf = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(sbuf + (size_t)stages * stage_doubles);
@@ -269,14 +356,15 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < stages; ++s) { mbar_init(&full[s], NPROD); mbar_init(&bfull[s], 1); mbar_init(&bready[s], 1); mbar_init(&empty[s], NCW); }
+        for (uint32_t s = 0; s < stages; ++s) { mbar_init(&full[s], NPROD); mbar_init(&bfull[s], 1); mbar_init(&bready[s], 1); mbar_init(&empty[s], NCW); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
 
-    uint32_t it = 0;     // running chunk counter (same sequence in every role)
+    Ring rg; rg.st = 0; rg.ph = 0;     // running ring position (same sequence in every role)
 
-    for (int i = a0 + blockIdx.x; i < a1; i += gridDim.x) {
+    int round = 0;
+    for (int i = a0 + blockIdx.x; i < a1; i += gridDim.x, ++round) {
         // ---- owned neighbours of i, in list order (warp 0, ordered compaction) ----
         __syncthreads();
         if (warp == 0) {
@@ -295,7 +383,8 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
         const int n_owned = n_owned_sh;
         const size_t b0i = (size_t)rowptr[i];
         // ---- sub-tasks of at most slotcap-1 neighbours (slot 0 is always atom i itself) ----
-        for (int first = 0; first == 0 || first < n_owned; first += slotcap - 1) {
+        int sub = 0;
+        for (int first = 0; first == 0 || first < n_owned; first += slotcap - 1, ++sub) {
             const int nn = min(slotcap - 1, n_owned - first);
             const int nslots = nn + 1;
             __syncthreads();
@@ -310,49 +399,50 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
             if (warp > NCW) {
                 // ===== producer warps: stream the tiles of all slots for every chunk; slot s belongs to producer s % NPROD =====
                 const int pw = warp - NCW - 1;
-                const int ncopy = (dbg & 2) ? (nslots + 3) / 4 : nslots;     // debug: quarter of the data
+                const int ncopy = (DBG && (dbg & 2)) ? (nslots + 3) / 4 : nslots;     // debug: quarter of the data
                 // slot 0 and the weights go to their own barrier (bfull) so the B warp overlaps with the other copies
                 const int others = ncopy - 1;                                   // slots 1 .. ncopy-1
                 const int mine = others > pw ? (others - pw + NPROD - 1) / NPROD : 0;
                 const uint32_t bytes = (uint32_t)(mine * TILE) * 8u;
-                const int pf = (dbg & 16) ? PF_AHEAD : 0;     // L2 prefetch is off by default: its issue cost outweighs the latency it hides
-                for (int ch = 0; ch < nchunks; ++ch, ++it) {
-                    const int st = it % stages;
-                    const uint32_t ph = (it / stages) & 1u;
-                    mbar_spin(&empty[st], ph ^ 1u);
-                    double* dstage = sbuf + (size_t)st * stage_doubles;
-                    const double* csrc = Ct + (size_t)ch * na * TILE;
+                const double* csrc = Ct;
+                const double* w1 = wf; const double* w2 = wfe;
+                // this lane's source / destination offsets do not change from chunk to chunk
+                const int k0 = lane < mine ? 1 + lane * NPROD + pw : -1;
+                const int k1 = lane + 32 < mine ? 1 + (lane + 32) * NPROD + pw : -1;
+                const size_t src0 = k0 >= 0 ? (size_t)slot_atom[k0] * TILE : 0, src1 = k1 >= 0 ? (size_t)slot_atom[k1] * TILE : 0;
+                const size_t srcB = (size_t)slot_atom[0] * TILE;
+                const long long pos0 = ((long long)round * maxsub + sub) * nchunks;
+                for (int ch = 0; ch < nchunks; ++ch) {
+                    if (lead > 0 && pw == 0 && (ch % SYNC_EVERY) == 0 && !throttle(prog, pos0 + ch, lead, lane)) lead = 0;   // the other producers cannot pass warp 0 by more than the ring
+                    mbar_spin(&empty[rg.st], rg.ph ^ 1u, DBG && (dbg & 4));
+                    double* dstage = sbuf + (size_t)rg.st * stage_doubles;
                     if (lane == 0) {
                         if (pw == 0) {
-                            mbar_expect_tx(&bfull[st], (uint32_t)(TILE + 2 * KC) * 8u);
-                            bulk_g2s(dstage, csrc + (size_t)slot_atom[0] * TILE, TILE * 8, &bfull[st]);
-                            bulk_g2s(dstage + slotcap * SLOT + KS * BROW, wf + (size_t)ch * KC, KC * 8, &bfull[st]);
-                            bulk_g2s(dstage + slotcap * SLOT + KS * BROW + KC, wfe + (size_t)ch * KC, KC * 8, &bfull[st]);
+                            mbar_expect_tx(&bfull[rg.st], (uint32_t)(TILE + 2 * KC) * 8u);
+                            bulk_g2s(dstage, csrc + srcB, TILE * 8, &bfull[rg.st]);
+                            bulk_g2s(dstage + slotcap * SLOT + KS * BROW, w1, KC * 8, &bfull[rg.st]);
+                            bulk_g2s(dstage + slotcap * SLOT + KS * BROW + KC, w2, KC * 8, &bfull[rg.st]);
                         }
-                        mbar_expect_tx(&full[st], bytes);
+                        mbar_expect_tx(&full[rg.st], bytes);
                     }
                     __syncwarp();
-                    for (int k = lane; k < mine; k += 32) {
+                    if (k0 >= 0) bulk_g2s(dstage + k0 * SLOT, csrc + src0, TILE * 8, &full[rg.st]);
+                    if (k1 >= 0) bulk_g2s(dstage + k1 * SLOT, csrc + src1, TILE * 8, &full[rg.st]);
+                    for (int k = lane + 64; k < mine; k += 32) {      // only for slot capacities beyond 64 * NPROD
                         const int s = 1 + k * NPROD + pw;
-                        bulk_g2s(dstage + s * SLOT, csrc + (size_t)slot_atom[s] * TILE, TILE * 8, &full[st]);
+                        bulk_g2s(dstage + s * SLOT, csrc + (size_t)slot_atom[s] * TILE, TILE * 8, &full[rg.st]);
                     }
-                    if (pf > 0 && ch + pf < nchunks) {      // warm the L2 for the chunk `pf` ahead (same slots)
-                        const double* psrc = Ct + (size_t)(ch + pf) * na * TILE;
-                        if (pw == 0 && lane == 0) bulk_prefetch_l2(psrc + (size_t)slot_atom[0] * TILE, TILE * 8);
-                        for (int k = lane; k < mine; k += 32)
-                            bulk_prefetch_l2(psrc + (size_t)slot_atom[1 + k * NPROD + pw] * TILE, TILE * 8);
-                    }
+                    csrc += (size_t)na * TILE; w1 += KC; w2 += KC;
+                    rg.next(stages);
                 }
             } else if (warp == NCW) {
                 // ===== B warp: weighted B operand of atom i, once per chunk =====
-                for (int ch = 0; ch < nchunks; ++ch, ++it) {
-                    const int st = it % stages;
-                    const uint32_t ph = (it / stages) & 1u;
-                    mbar_spin(&bfull[st], ph);
-                    double* stg = sbuf + (size_t)st * stage_doubles;
+                const int g = lane >> 2, t = lane & 3;
+                for (int ch = 0; ch < nchunks; ++ch) {
+                    mbar_spin(&bfull[rg.st], rg.ph, DBG && (dbg & 4));
+                    double* stg = sbuf + (size_t)rg.st * stage_doubles;
                     double* Bs = stg + slotcap * SLOT;
                     const double* wsm = Bs + KS * BROW;
-                    const int g = lane >> 2, t = lane & 3;
 #pragma unroll
                     for (int s = 0; s < KS; ++s) {
                         const double w_f = wsm[4 * s + t], w_e = wsm[KC + 4 * s + t];
@@ -366,19 +456,24 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages, in
                         }
                     }
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(&bready[st]);     // release: the stores above are visible to the waiters
+                    if (lane == 0) mbar_arrive(&bready[rg.st]);     // release: the stores above are visible to the waiters
+                    rg.next(stages);
                 }
             } else {
-                // ===== consumer warps =====
-                const int mt_need = (ntiles + NCW - 1) / NCW;
+                // ===== consumer warps: row tiles warp, warp + NCW, ... of this sub-task =====
+                const int my_tiles = ntiles > warp ? (ntiles - warp + NCW - 1) / NCW : 0;
                 const bool fs = first == 0;
-                constexpr int MTMAX = NCW == 8 ? 7 : NCW == 12 ? 5 : 4;      // row tiles per warp (register budget)
-#define XTB_CASE(M) if constexpr (M <= MTMAX) { if (mt_need == M || (M == MTMAX && mt_need > M)) consume_subtask<NO, NCW, M>(sbuf, stage_doubles, slotcap, stages, full, bready, empty, it, nchunks, nrows, ntiles, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); }
+                const int boff = slotcap * SLOT;
+                constexpr int MTMAX = NCW == 8 ? 7 : 5;      // row tiles per warp (register budget)
+#define XTB_CASE(M) if constexpr (M <= MTMAX) { if (my_tiles == M) consume_subtask<NO, NCW, M, DBG>(sbuf, stage_doubles, boff, stages, full, bready, empty, rg, nchunks, nrows, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); }
+                if (my_tiles == 0) consume_idle(stages, full, bready, empty, rg, nchunks, lane);
                 XTB_CASE(1) XTB_CASE(2) XTB_CASE(3) XTB_CASE(4) XTB_CASE(5) XTB_CASE(6) XTB_CASE(7)
 #undef XTB_CASE
             }
         }
     }
+    // this CTA is done: it no longer holds anyone back
+    if (warp == NCW + 1 && lane == 0) st_relaxed(prog + blockIdx.x, 0x7ffffffffffffff0LL);
 }
 
 // ---------------- simple CUDA-core kernel (cross-check of the DMMA path; also the generic-n_orb path) ----------------
@@ -473,8 +568,8 @@ int run_density(xtb_ctx* c) {
         }
         XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
         // slot capacity / stages from the shared-memory budget (227 KB per CTA)
-        const int NCW = c->density_ncw == 16 ? 16 : c->density_ncw == 12 ? 12 : 8;
-        const int MTMAX = NCW == 8 ? 7 : NCW == 12 ? 5 : 4;
+        const int NCW = c->density_ncw == 12 ? 12 : 8;
+        const int MTMAX = NCW == 8 ? 7 : 5;
         int slotcap = (c->max_nn + 1) / 2 + 6;                 // balanced ownership: half the neighbours (+ slack), + self
         if (slotcap > MTMAX * NCW * 8 / NO) slotcap = MTMAX * NCW * 8 / NO;     // rows must fit MTMAX tiles per warp
         if (slotcap > c->max_nn + 1) slotcap = c->max_nn + 1;
@@ -490,12 +585,21 @@ int run_density(xtb_ctx* c) {
         while (stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages) > budget && slotcap > 2) --slotcap;
         const size_t smem = stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages);
         int grid = c->sm_count < nown ? c->sm_count : nown;
-#define XTB_LAUNCH(W) { auto kern = density_dmma_kernel<9, W>; \
+        if ((rc = xtb_reserve(c, c->d_prog, sizeof(long long) * (size_t)c->sm_count))) return rc;
+        XTB_CUDA(c, cudaMemsetAsync(c->d_prog.p, 0, sizeof(long long) * (size_t)c->sm_count, c->stream));
+        const int maxsub = slotcap > 1 ? (c->max_nn + slotcap - 2) / (slotcap - 1) + 1 : 1;
+        int a_na = na, a_a0 = c->a0, a_a1 = c->a1, a_cap = c->cap, a_slot = slotcap, a_st = stages, a_nch = nchunks, a_dbg = c->density_dbg, a_ms = maxsub, a_lead = c->density_lead;
+        long long* a_prog = (long long*)c->d_prog.p;
+        const int* a_sz = (const int*)c->d_nn_size.p; const int* a_li = (const int*)c->d_nn_list.p;
+        const signed char* a_own = (const signed char*)c->d_own.p; const int* a_rp = (const int*)c->d_rowptr.p;
+        const double* a_ct = (const double*)c->d_Ct.p; const double* a_wf = (const double*)c->d_wf.p; const double* a_wfe = (const double*)c->d_wfe.p;
+        double* a_rho = (double*)c->d_rho.p; double* a_rhoE = (double*)c->d_rhoE.p;
+        void* args[] = {&a_na, &a_a0, &a_a1, &a_cap, &a_slot, &a_st, &a_nch, &a_dbg, &a_ms, &a_lead, &a_prog, &a_sz, &a_li, &a_own, &a_rp,
+                        &a_ct, &a_wf, &a_wfe, &a_rho, &a_rhoE};
+#define XTB_LAUNCH(W, D) { auto kern = density_dmma_kernel<9, W, D>; \
         XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        kern<<<grid, (W + 1 + NPROD) * 32, smem, c->stream>>>(na, c->a0, c->a1, c->cap, slotcap, stages, nchunks, c->density_dbg, \
-            (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, \
-            (const double*)c->d_Ct.p, (const double*)c->d_wf.p, (const double*)c->d_wfe.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p); }
-        if (NCW == 16) XTB_LAUNCH(16) else if (NCW == 12) XTB_LAUNCH(12) else XTB_LAUNCH(8)
+        XTB_CUDA(c, cudaLaunchKernel((const void*)kern, dim3(grid), dim3((W + 1 + NPROD) * 32), args, smem, c->stream)); }
+        if (c->density_dbg) XTB_LAUNCH(8, true) else if (NCW == 12) XTB_LAUNCH(12, false) else XTB_LAUNCH(8, false)
 #undef XTB_LAUNCH
         XTB_LAUNCH_CHECK(c);
         c->density_slotcap = slotcap; c->density_stages = stages;

@@ -48,6 +48,8 @@ int xtb_create(xtb_ctx** out, int device) {
     if (impl) c->density_impl = atoi(impl);
     const char* ncw = getenv("XTB_DENSITY_NCW");
     if (ncw) c->density_ncw = atoi(ncw);
+    const char* lead = getenv("XTB_DENSITY_LEAD");
+    if (lead) c->density_lead = atoi(lead);
     const char* dbg = getenv("XTB_DENSITY_DBG");
     if (dbg) c->density_dbg = atoi(dbg);
     *out = c;
@@ -61,7 +63,7 @@ int xtb_destroy(xtb_ctx* c) {
     DevBuf* all[] = {&c->d_params, &c->d_koa, &c->d_S, &c->d_nn_size, &c->d_nn_list, &c->d_nn_dist, &c->d_nn_dist_s, &c->d_rev, &c->d_own,
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
-                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab};
+                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog};
     for (DevBuf* b : all) xtb_free(*b);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
     if (c->own_stream) cudaStreamDestroy(c->stream);

@@ -63,6 +63,7 @@ struct xtb_ctx {
     DevBuf d_keep, d_wf, d_wfe, d_Ct, d_nkeep;   // kept state indices, weights, tiled transposed C
     long long k_kept = 0;
     DevBuf d_rho, d_rhoE;       // block-sparse [n_blocks][n_orb^2]
+    DevBuf d_prog;              // density kernel: per-CTA progress counters (lock-step throttle)
     bool have_density = false;
     // forces / pressure
     DevBuf d_F, d_SC, d_scratch, d_hdev, d_ppart, d_tab;
@@ -71,8 +72,9 @@ struct xtb_ctx {
     int density_slotcap = 0, density_stages = 0;
     double stage_ms[8] = {0};
     int sm_count = 148;
-    int density_dbg = 0;        // XTB_DENSITY_DBG: bit0 consumers skip the math, bit1 producer copies 1/4 of the tiles (timing experiments only)
-    int density_ncw = 8;        // consumer warps of the density kernel (8, 12 or 16); XTB_DENSITY_NCW
+    int density_dbg = 0;        // XTB_DENSITY_DBG (timing experiments only, separate kernel instantiation): 1 no math, 2 quarter of the tile copies, 4 helper warps nap while polling, 8 no DFMA
+    int density_ncw = 8;        // consumer warps of the density kernel (8 or 12); XTB_DENSITY_NCW
+    int density_lead = 64;      // chunks a CTA of the density kernel may run ahead of the slowest one (0 = no lock-step); XTB_DENSITY_LEAD
     int density_impl = 1;       // 1 = DMMA + bulk-copy pipeline, 0 = simple CUDA-core kernel (debug / cross-check)
 };
 
