@@ -138,6 +138,16 @@ int  xtb_expand_dense(xtb_ctx*, int atom_first, int atom_last, double* H_non, do
 int  xtb_set_eigen       (xtb_ctx*, const double* Ha, const double* Ei, const double* fe);
 int  xtb_set_eigen_device(xtb_ctx*, const double* dHa, const double* dEi, const double* dfe);
 
+/* Optional on-device eigensolve (the north star feeds end-to-end steps this way so that H, S and Ha
+ *      never cross PCIe).  Same algebra as Loewdin_Orthogonalization (TB_NRL.f90:985-1060) + sym_diagonalize (Algebra_tools.f90:
+ *      882-966) + the back-transform Ha = X V (TB_NRL.f90:421), on the device-resident H_non / Sij of the last xtb_assemble_HS,
+ *      with cuSOLVER Dsyevd / cuBLAS Dgemm bound at run time (XTB_ESTATE if the libraries are absent).  Leaves Ha and Ei on the
+ *      device; host copies of Ei(N), eigen_S(N) (eigenvalues of S, Scell%eigen_S) and Ha(N,N) are optional (NULL = skip).
+ *      xtb_set_occupations then supplies Scell%fe(N) (the host computes it from Ei as Electron_tools does) and arms xtb_density. */
+int  xtb_eigensolve(xtb_ctx*, double* Ei, double* eigen_S, double* Ha);
+int  xtb_get_eigenvalues(xtb_ctx*, double* Ei /*N*/);       /* Scell%Ei from the device (any eigen source) */
+int  xtb_set_occupations(xtb_ctx*, const double* fe /*N*/);   /* Scell%fe; eigenvectors / eigenvalues stay as they are */
+
 /* ---- S3: Construct_Aij (TB.f90:4328) and Construct_Aij_x_En (TB.f90:4401).
  *      Computed on the neighbour pattern only (every consumer reads only those blocks,
  *      TB.f90:250-299,5544-5573); dense outputs (N,N) are zero outside the pattern.
@@ -178,7 +188,7 @@ int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 long long xtb_counter(const xtb_ctx*, int which);
 /* device time [ms] of the last run of a stage (CUDA events on the context stream):
  * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure,
- * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3) */
+ * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3), 8 xtb_eigensolve */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 
 #ifdef __cplusplus

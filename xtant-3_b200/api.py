@@ -183,6 +183,23 @@ class TBContext:
         """device pointers (ints), e.g. torch tensors' data_ptr(); zero copy"""
         self._ck(self.lib.xtb_set_eigen_device(self.h, C.c_void_p(dHa), C.c_void_p(dEi), C.c_void_p(dfe)))
 
+    def eigensolve(self, want_Ha=False):
+        """on-device Loewdin + Dsyevd + back-transform (TB_NRL.f90:985-1060,402-421); returns (Ei, eigen_S[, Ha])"""
+        N = self.na * self.n_orb
+        Ei = np.zeros(N); wS = np.zeros(N)
+        Ha = np.zeros((N, N), order="F") if want_Ha else None
+        self._ck(self.lib.xtb_eigensolve(self.h, _dp(Ei), _dp(wS), _dp(Ha)))
+        return (Ei, wS, Ha) if want_Ha else (Ei, wS)
+
+    def get_eigenvalues(self):
+        Ei = np.zeros(self.na * self.n_orb)
+        self._ck(self.lib.xtb_get_eigenvalues(self.h, _dp(Ei)))
+        return Ei
+
+    def set_occupations(self, fe):
+        fe = np.ascontiguousarray(fe, dtype=np.float64)
+        self._ck(self.lib.xtb_set_occupations(self.h, _dp(fe)))
+
     def set_density_cutoff(self, f_cut):
         self._ck(self.lib.xtb_set_density_cutoff(self.h, float(f_cut)))
 

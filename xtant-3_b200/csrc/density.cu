@@ -76,29 +76,55 @@ __global__ void pad_weights_kernel(int nkeep, int kpad, double* __restrict__ wf,
 
 // Ct[chunk][atom][s][r][t] = Ha[atom*NO + r, keep[chunk*16 + 4 s + t]]  (0 beyond nkeep)
 // one CTA per (chunk, group of CT_AT atoms): reads KC columns x (CT_AT*NO) contiguous rows, writes contiguous tiles.
+// HBM-bound (8*N*K bytes in, the same out): every thread keeps KC independent 128-bit loads in flight, the transpose
+// goes through shared memory with a row pitch that makes both phases conflict-free, stores are 128-bit and coalesced.
+constexpr int CT_THREADS = 160;
 template <int NO>
-__global__ void __launch_bounds__(256) ct_tile_kernel(int na, long long N, int nkeep, const int* __restrict__ keep,
-                                                     const double* __restrict__ Ha, double* __restrict__ Ct) {
+__global__ void __launch_bounds__(CT_THREADS) ct_tile_kernel(int na, long long N, int nkeep, const int* __restrict__ keep,
+                                                            const double* __restrict__ Ha, double* __restrict__ Ct) {
     constexpr int AT = CT_AT;
-    __shared__ double tile[KC][AT * NO + 1];
+    constexpr int P = AT * NO + 4;                   // pitch = 4 mod 8: the 64-bit banks of (t, t+2) x 8 rows are disjoint
+    __shared__ __align__(16) double tile[KC][P];
+    __shared__ long long colbase[KC];
     const int chunk = blockIdx.x;
     const int atom0 = blockIdx.y * AT;
     const int nat = min(AT, na - atom0);
     const int nrow = nat * NO;
-    for (int kk = 0; kk < KC; ++kk) {
-        const int ks = chunk * KC + kk;
-        const double* src = ks < nkeep ? Ha + (size_t)keep[ks] * N + (size_t)atom0 * NO : nullptr;
-        for (int r = threadIdx.x; r < nrow; r += blockDim.x) tile[kk][r] = src ? src[r] : 0.0;
+    if (threadIdx.x < KC) {
+        const int ks = chunk * KC + threadIdx.x;
+        colbase[threadIdx.x] = ks < nkeep ? (long long)keep[ks] * N + (long long)atom0 * NO : -1;
     }
     __syncthreads();
-    double* dst = Ct + ((size_t)chunk * na + atom0) * (NO * KC);
-    const int tot = nat * NO * KC;
-    for (int e = threadIdx.x; e < tot; e += blockDim.x) {
+    if ((N & 1) == 0 && (nrow & 1) == 0) {           // 16-byte aligned columns: AT is even, so atom0*NO is even
+        for (int r2 = threadIdx.x; r2 < (nrow >> 1); r2 += CT_THREADS) {
+            double2 v[KC];
+#pragma unroll
+            for (int kk = 0; kk < KC; ++kk) {
+                const long long cb = colbase[kk];
+                v[kk] = cb >= 0 ? __ldcs(reinterpret_cast<const double2*>(Ha + cb) + r2) : make_double2(0.0, 0.0);
+            }
+#pragma unroll
+            for (int kk = 0; kk < KC; ++kk) *reinterpret_cast<double2*>(&tile[kk][2 * r2]) = v[kk];
+        }
+    } else {
+        for (int r = threadIdx.x; r < nrow; r += CT_THREADS) {
+            double v[KC];
+#pragma unroll
+            for (int kk = 0; kk < KC; ++kk) { const long long cb = colbase[kk]; v[kk] = cb >= 0 ? __ldcs(Ha + cb + r) : 0.0; }
+#pragma unroll
+            for (int kk = 0; kk < KC; ++kk) tile[kk][r] = v[kk];
+        }
+    }
+    __syncthreads();
+    double2* dst = reinterpret_cast<double2*>(Ct + ((size_t)chunk * na + atom0) * (NO * KC));     // 16-byte aligned: NO*KC is even
+    const int tot2 = nat * NO * KC / 2;
+    for (int e2 = threadIdx.x; e2 < tot2; e2 += CT_THREADS) {
+        const int e = 2 * e2;
         const int a = e / (NO * KC);
         int rem = e - a * (NO * KC);
         const int s = rem / (NO * 4); rem -= s * (NO * 4);
-        const int r = rem >> 2, t = rem & 3;
-        dst[e] = tile[4 * s + t][a * NO + r];
+        const int r = rem >> 2, t = rem & 3;          // t is 0 or 2
+        dst[e2] = make_double2(tile[4 * s + t][a * NO + r], tile[4 * s + t + 1][a * NO + r]);
     }
 }
 
@@ -152,10 +178,6 @@ __device__ __forceinline__ void mbar_spin(uint64_t* b, uint32_t parity, bool nap
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-// L2 prefetch of a contiguous global range (no shared-memory destination): hides the DRAM latency of a later bulk copy
-__device__ __forceinline__ void bulk_prefetch_l2(const void* src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
     asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
@@ -563,7 +585,7 @@ int run_density(xtb_ctx* c) {
         if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)kpad * N + 1024))) return rc;
         if (nchunks > 0) {
             dim3 grid(nchunks, (na + CT_AT - 1) / CT_AT);
-            ct_tile_kernel<NO><<<grid, 256, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, c->d_Ha, (double*)c->d_Ct.p);
+            ct_tile_kernel<NO><<<grid, CT_THREADS, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, c->d_Ha, (double*)c->d_Ct.p);
             XTB_LAUNCH_CHECK(c);
         }
         XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));

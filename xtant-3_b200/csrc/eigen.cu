@@ -1,0 +1,179 @@
+// Eigensolve glue on the device -- the step BETWEEN assembly and density that the graft does
+// not own.  It exists so that an end-to-end MD step never moves the N x N matrices over PCIe: H_non and Sij stay where
+// xtb_assemble_HS left them, the eigenvectors stay where xtb_density reads them.
+//
+// Same algebra as the reference, with cuSOLVER / cuBLAS library calls in place of LAPACK / MKL:
+//   Loewdin_Orthogonalization   Source_files/TB_NRL.f90:985-1060   dsyev(S) -> w, U ; negative w -> |w| ;
+//                                                                   X = U diag(1/sqrt(w), 0 where |w| <= 1e-8) ;
+//                                                                   H' = X^T (H X)
+//   sym_diagonalize(H')         Source_files/Algebra_tools.f90:882-966 (dsyevd)  -> Ei, V
+//   Ha = X V                    Source_files/TB_NRL.f90:421 / TB_DFTB.f90:535
+//   DFTB only: |H'| < 1e-10 -> 0 before the diagonalisation (TB_DFTB.f90:517-519)
+//   orthogonal branch (Pettifor): sym_diagonalize(H) directly (TB_Pettifor.f90:1455)
+// The libraries are bound at run time (dlopen), so libxtb_b200.so itself has no link-time dependency on them; when they
+// are missing xtb_eigensolve reports XTB_ESTATE and the caller keeps using xtb_set_eigen with host LAPACK eigenvectors.
+#include "xtb_ctx.h"
+#include <dlfcn.h>
+
+namespace {
+
+typedef void* handle_t;
+typedef int (*fn_create_t)(handle_t*);
+typedef int (*fn_destroy_t)(handle_t);
+typedef int (*fn_setstream_t)(handle_t, cudaStream_t);
+typedef int (*fn_syevd_buf_t)(handle_t, int /*jobz*/, int /*uplo*/, int n, const double* A, int lda, const double* W, int* lwork);
+typedef int (*fn_syevd_t)(handle_t, int, int, int n, double* A, int lda, double* W, double* work, int lwork, int* info);
+typedef int (*fn_dgemm_t)(handle_t, int ta, int tb, int m, int n, int k, const double* alpha, const double* A, int lda,
+                          const double* B, int ldb, const double* beta, double* Cm, int ldc);
+
+struct Libs {
+    bool tried = false, ok = false;
+    std::string why;
+    void* so_solver = nullptr; void* so_blas = nullptr;
+    fn_create_t sv_create = nullptr; fn_destroy_t sv_destroy = nullptr; fn_setstream_t sv_stream = nullptr;
+    fn_syevd_buf_t sv_buf = nullptr; fn_syevd_t sv_syevd = nullptr;
+    fn_create_t bl_create = nullptr; fn_destroy_t bl_destroy = nullptr; fn_setstream_t bl_stream = nullptr; fn_dgemm_t bl_dgemm = nullptr;
+    handle_t sv = nullptr, bl = nullptr;
+};
+Libs g_libs;
+
+void* open_any(const char* const* names) {
+    for (int i = 0; names[i]; ++i) {
+        void* h = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
+        if (h) return h;
+    }
+    return nullptr;
+}
+
+bool bind_libs() {
+    Libs& L = g_libs;
+    if (L.tried) return L.ok;
+    L.tried = true;
+    static const char* const solver[] = {"libcusolver.so.11", "libcusolver.so", "/usr/local/cuda/lib64/libcusolver.so.11", nullptr};
+    static const char* const blas[] = {"libcublas.so.12", "libcublas.so", "/usr/local/cuda/lib64/libcublas.so.12", nullptr};
+    L.so_blas = open_any(blas);
+    L.so_solver = open_any(solver);
+    if (!L.so_solver || !L.so_blas) { L.why = "cuSOLVER / cuBLAS shared libraries not found"; return false; }
+#define BIND(field, so, type, name) L.field = (type)dlsym(L.so, name); if (!L.field) { L.why = std::string("missing symbol ") + name; return false; }
+    BIND(sv_create, so_solver, fn_create_t, "cusolverDnCreate")
+    BIND(sv_destroy, so_solver, fn_destroy_t, "cusolverDnDestroy")
+    BIND(sv_stream, so_solver, fn_setstream_t, "cusolverDnSetStream")
+    BIND(sv_buf, so_solver, fn_syevd_buf_t, "cusolverDnDsyevd_bufferSize")
+    BIND(sv_syevd, so_solver, fn_syevd_t, "cusolverDnDsyevd")
+    BIND(bl_create, so_blas, fn_create_t, "cublasCreate_v2")
+    BIND(bl_destroy, so_blas, fn_destroy_t, "cublasDestroy_v2")
+    BIND(bl_stream, so_blas, fn_setstream_t, "cublasSetStream_v2")
+    BIND(bl_dgemm, so_blas, fn_dgemm_t, "cublasDgemm_v2")
+#undef BIND
+    if (L.sv_create(&L.sv) != 0 || L.bl_create(&L.bl) != 0) { L.why = "cusolverDnCreate / cublasCreate failed"; return false; }
+    L.ok = true;
+    return true;
+}
+
+constexpr int JOB_VECTOR = 1;     // CUSOLVER_EIG_MODE_VECTOR
+constexpr int FILL_UPPER = 1;     // CUBLAS_FILL_MODE_UPPER
+constexpr int OP_N = 0, OP_T = 1; // CUBLAS_OP_N / CUBLAS_OP_T
+
+// X(:, i) *= s_i with s_i = 1/sqrt(|w_i|) if |w_i| > eps else 0; w <- |w| when the spectrum has a negative / tiny value
+__global__ void loewdin_scale_kernel(long long N, const double* __restrict__ w, const int* __restrict__ fix, double* __restrict__ X) {
+    const long long col = blockIdx.y;
+    double ev = w[col];
+    if (*fix && ev < 0.0) ev = fabs(ev);                        // TB_NRL.f90:1022-1026
+    const double s = fabs(ev) > 1e-8 ? 1.0 / sqrt(ev) : 0.0;     // :1031
+    for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < N; r += (long long)gridDim.x * blockDim.x)
+        X[r + N * col] *= s;
+}
+// fix = 1 iff any eigenvalue is negative or |w| < eps (N_neg > 0 or N_zero > 0, :1019-1026)
+__global__ void loewdin_flag_kernel(long long N, const double* __restrict__ w, int* __restrict__ fix) {
+    __shared__ int any;
+    if (threadIdx.x == 0) any = 0;
+    __syncthreads();
+    for (long long i = threadIdx.x; i < N; i += blockDim.x)
+        if (w[i] < 0.0 || fabs(w[i]) < 1e-8) any = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) *fix = any;
+}
+__global__ void chop_kernel(long long n, double* __restrict__ A, double eps) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        if (fabs(A[i]) < eps) A[i] = 0.0;
+}
+
+int syevd(xtb_ctx* c, int n, double* A, double* W, std::string what) {
+    Libs& L = g_libs;
+    int lwork = 0;
+    if (L.sv_buf(L.sv, JOB_VECTOR, FILL_UPPER, n, A, n, W, &lwork) != 0) XTB_FAIL(c, XTB_ECUDA, "cusolverDnDsyevd_bufferSize failed (%s)", what.c_str());
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_eig_work, sizeof(double) * (size_t)lwork + 16))) return rc;
+    int* d_info = (int*)((double*)c->d_eig_work.p + lwork);
+    if (L.sv_syevd(L.sv, JOB_VECTOR, FILL_UPPER, n, A, n, W, (double*)c->d_eig_work.p, lwork, d_info) != 0)
+        XTB_FAIL(c, XTB_ECUDA, "cusolverDnDsyevd failed to launch (%s)", what.c_str());
+    int info = 0;
+    XTB_CUDA(c, cudaMemcpyAsync(&info, d_info, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (info != 0) XTB_FAIL(c, XTB_ECUDA, "Dsyevd(%s): info = %d", what.c_str(), info);    // the reference records LAPACK failures the same way (TB_NRL.f90:410-416)
+    return XTB_OK;
+}
+
+}  // namespace
+
+int xtb_impl_eigensolve(xtb_ctx* c) {
+    if (!bind_libs()) XTB_FAIL(c, XTB_ESTATE, "xtb_eigensolve: %s", g_libs.why.c_str());
+    Libs& L = g_libs;
+    const long long N = (long long)c->na * c->n_orb;
+    if (N > 46000) XTB_FAIL(c, XTB_EINVAL, "xtb_eigensolve: N = %lld exceeds the 32-bit element count of cusolverDnDsyevd", N);
+    const int n = (int)N;
+    const size_t nn = (size_t)N * N;
+    const bool ortho = c->tb == XTB_TB_PETTIFOR;
+    int rc;
+    L.sv_stream(L.sv, c->stream); L.bl_stream(L.bl, c->stream);
+    if ((rc = xtb_reserve(c, c->own_Ha, sizeof(double) * nn))) return rc;
+    if ((rc = xtb_reserve(c, c->own_Ei, sizeof(double) * N))) return rc;
+    if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
+    if ((rc = xtb_reserve(c, c->d_eigS, sizeof(double) * N + 16))) return rc;
+    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    double* Ha = (double*)c->own_Ha.p;
+    double* Ei = (double*)c->own_Ei.p;
+    if (ortho) {      // TB_Pettifor.f90:1455: the assembled matrix is diagonalised in place
+        XTB_CUDA(c, cudaMemcpyAsync(Ha, c->d_H.p, sizeof(double) * nn, cudaMemcpyDeviceToDevice, c->stream));
+        rc = syevd(c, n, Ha, Ei, "H");
+        if (rc) return rc;
+    } else {
+        if ((rc = xtb_reserve(c, c->d_eig_X, sizeof(double) * nn))) return rc;
+        if ((rc = xtb_reserve(c, c->d_eig_T, sizeof(double) * nn))) return rc;
+        double* X = (double*)c->d_eig_X.p; double* T = (double*)c->d_eig_T.p;
+        double* wS = (double*)c->d_eigS.p; int* fix = (int*)(wS + N);
+        const double one = 1.0, zero = 0.0;
+        XTB_CUDA(c, cudaMemcpyAsync(X, c->d_S2.p, sizeof(double) * nn, cudaMemcpyDeviceToDevice, c->stream));
+        rc = syevd(c, n, X, wS, "S");
+        if (rc) return rc;                                      // :1012
+        loewdin_flag_kernel<<<1, 1024, 0, c->stream>>>(N, wS, fix);
+        XTB_LAUNCH_CHECK(c);
+        loewdin_scale_kernel<<<dim3(8, n), 256, 0, c->stream>>>(N, wS, fix, X);             // X = U s^-1/2   :1036
+        XTB_LAUNCH_CHECK(c);
+        if (L.bl_dgemm(L.bl, OP_N, OP_N, n, n, n, &one, (const double*)c->d_H.p, n, X, n, &zero, T, n) != 0)   // H X   (dsymm, :1049)
+            XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(H X) failed");
+        if (L.bl_dgemm(L.bl, OP_T, OP_N, n, n, n, &one, X, n, T, n, &zero, Ha, n) != 0)                       // X^T (H X)  :1054
+            XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(X^T H X) failed");
+        if (c->tb == XTB_TB_DFTB) {
+            chop_kernel<<<1184, 256, 0, c->stream>>>((long long)nn, Ha, 1e-10);
+            XTB_LAUNCH_CHECK(c);
+        }
+        rc = syevd(c, n, Ha, Ei, "H'");
+        if (rc) return rc;                                     // TB_NRL.f90:409
+        if (L.bl_dgemm(L.bl, OP_N, OP_N, n, n, n, &one, X, n, Ha, n, &zero, T, n) != 0)      // Ha = X V   :421
+            XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(X V) failed");
+        // the eigenvectors now live in T: swap the roles of the two buffers
+        DevBuf tmp = c->own_Ha; c->own_Ha = c->d_eig_T; c->d_eig_T = tmp;
+    }
+    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    c->eigen_ms = ms;
+    c->d_Ha = (const double*)c->own_Ha.p; c->d_Ei = (const double*)c->own_Ei.p; c->d_fe = (const double*)c->own_fe.p;
+    c->K = N;
+    c->have_eigvec = true;
+    c->have_eigen = false;          // occupations still to come (xtb_set_occupations)
+    c->have_density = false;
+    return XTB_OK;
+}

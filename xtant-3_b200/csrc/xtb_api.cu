@@ -63,7 +63,7 @@ int xtb_destroy(xtb_ctx* c) {
     DevBuf* all[] = {&c->d_params, &c->d_koa, &c->d_S, &c->d_nn_size, &c->d_nn_list, &c->d_nn_dist, &c->d_nn_dist_s, &c->d_rev, &c->d_own,
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
-                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog};
+                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS};
     for (DevBuf* b : all) xtb_free(*b);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -328,6 +328,7 @@ int xtb_set_eigen_device(xtb_ctx* c, const double* dHa, const double* dEi, const
     if (!dHa || !dEi || !dfe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen_device: null pointer");
     if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_eigen_device: no system set");
     c->d_Ha = dHa; c->d_Ei = dEi; c->d_fe = dfe;
+    c->have_eigvec = false;
     c->K = (long long)c->na * c->n_orb;
     c->have_eigen = true; c->have_density = false;
     return XTB_OK;
@@ -348,6 +349,47 @@ int xtb_set_eigen(xtb_ctx* c, const double* Ha, const double* Ei, const double* 
     XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     return xtb_set_eigen_device(c, (const double*)c->own_Ha.p, (const double*)c->own_Ei.p, (const double*)c->own_fe.p);
+}
+
+int xtb_eigensolve(xtb_ctx* c, double* Ei, double* eigen_S, double* Ha) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_HS) XTB_FAIL(c, XTB_ESTATE, "xtb_eigensolve: no dense H_non / Sij on the device (xtb_assemble_HS or xtb_expand_dense first)");
+    if (c->a0 != 0 || c->a1 != c->na) XTB_FAIL(c, XTB_EINVAL, "xtb_eigensolve: needs the complete matrices (expand all column panels first)");
+    int rc = xtb_impl_eigensolve(c);
+    if (rc) return rc;
+    const size_t N = (size_t)c->na * c->n_orb;
+    if (Ei) XTB_CUDA(c, cudaMemcpyAsync(Ei, c->own_Ei.p, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
+    if (eigen_S && c->tb != XTB_TB_PETTIFOR) XTB_CUDA(c, cudaMemcpyAsync(eigen_S, c->d_eigS.p, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
+    if (Ha) XTB_CUDA(c, cudaMemcpyAsync(Ha, c->own_Ha.p, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_get_eigenvalues(xtb_ctx* c, double* Ei) {
+    if (!c) return XTB_EINVAL;
+    if (!Ei) XTB_FAIL(c, XTB_EINVAL, "xtb_get_eigenvalues: null pointer");
+    if (!c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_get_eigenvalues: no eigenvalues on the device");
+    cudaSetDevice(c->device);
+    XTB_CUDA(c, cudaMemcpyAsync(Ei, c->d_Ei, sizeof(double) * (size_t)c->na * c->n_orb, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_set_occupations(xtb_ctx* c, const double* fe) {
+    if (!c) return XTB_EINVAL;
+    if (!fe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_occupations: null pointer");
+    if (!c->d_Ha || !c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_set_occupations: no eigenvectors on the device (xtb_eigensolve, xtb_set_eigen or xtb_set_eigen_device first)");
+    cudaSetDevice(c->device);
+    const size_t N = (size_t)c->na * c->n_orb;
+    int rc;
+    if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->d_fe = (const double*)c->own_fe.p;       // Ha and Ei stay where they are (device eigensolve result or the caller's buffers)
+    c->K = (long long)N;
+    c->have_eigen = true; c->have_density = false;
+    return XTB_OK;
 }
 
 int xtb_set_density_cutoff(xtb_ctx* c, double f_cut) {
@@ -471,7 +513,8 @@ long long xtb_counter(const xtb_ctx* c, int which) {
 }
 
 double xtb_stage_ms(const xtb_ctx* c, int stage) {
-    if (!c || stage < 1 || stage > 7) return -1.0;
+    if (!c || stage < 1 || stage > 8) return -1.0;
+    if (stage == 8) return c->eigen_ms;
     return c->stage_ms[stage];
 }
 

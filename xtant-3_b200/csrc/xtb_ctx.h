@@ -58,6 +58,9 @@ struct xtb_ctx {
     DevBuf own_Ha, own_Ei, own_fe;
     long long K = 0;            // number of states (columns of Ha)
     bool have_eigen = false;
+    bool have_eigvec = false;   // Ha, Ei produced on the device by xtb_eigensolve (occupations pending)
+    DevBuf d_eig_work, d_eig_X, d_eig_T, d_eigS;   // cuSOLVER workspace, Loewdin X, scratch, eigenvalues of S
+    double eigen_ms = 0.0;
     // density
     double f_cut = 0.0;
     DevBuf d_keep, d_wf, d_wfe, d_Ct, d_nkeep;   // kept state indices, weights, tiled transposed C
@@ -117,6 +120,7 @@ int xtb_impl_nrl_pressure(xtb_ctx* c);
 int xtb_impl_pettifor_forces(xtb_ctx* c);
 int xtb_impl_pettifor_pressure(xtb_ctx* c);
 int xtb_impl_mirror_density(xtb_ctx* c);
+int xtb_impl_eigensolve(xtb_ctx* c);        // eigen.cu: Loewdin + Dsyevd + back-transform on the device-resident H, S
 int xtb_impl_dftb_assemble(xtb_ctx* c, bool dense);
 int xtb_impl_dftb_forces(xtb_ctx* c);
 int xtb_impl_dftb_pressure(xtb_ctx* c);
