@@ -33,6 +33,18 @@ sys.path.insert(0, ROOT)
 METRIC = "ms/MD-step (H/S build + rho + HF forces)"
 
 
+def _density_traffic():
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture (profiles/), or None"""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_density_traffic.json")))
+    if not files:
+        return None
+    try:
+        return json.load(open(files[-1]))["dram_bytes_per_launch"]
+    except Exception:
+        return None
+
+
 def _peaks():
     try:
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -219,7 +231,8 @@ def run_own(args):
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": "density_dmma_kernel (rho and rho_E on the neighbour pattern, FP64 DMMA.8x8x4)",
                          "achieved": ach, "peak": dgemm_tf, "unit": "TFLOP/s", "frac": (ach / dgemm_tf) if ach else None,
-                         "traffic": None, "flops_per_launch": flops,
+                         "traffic": _density_traffic() if world == 1 else None, "traffic_unit": "bytes (dram read + write per launch, ncu)",
+                         "flops_per_launch": flops,
                          "peak_source": "in-run torch.matmul fp64 8192^3 (cuBLAS DGEMM, burst); MEASURED_PEAKS.json has no FP64 entry",
                          "peak_pipe_dmma884": dmma_tf},
             "roofline_hbm_stage": {"bound": "hbm", "kernel": "dense_panel_kernel (dense H and S columns, every element once)",
