@@ -64,6 +64,15 @@ typedef struct xtb_pettifor_pair {
     double r0, n, r1, rm;
 } xtb_pettifor_pair;
 
+/* type(TB_Rep_Pettifor), Objects.f90:95-100 (repulsive part of the Pettifor-type parametrisation;
+ * file order read_Pettifor_TB_repulsive, Read_input_data.f90:2908-3056) */
+typedef struct xtb_pettifor_rep_pair {
+    double E0_TB;            /* [eV] constant shift per atom */
+    double a0[5];            /* polynomial f(x) = a0 + a1 x + ... + a4 x^4 */
+    double phi0, d0, m, mc, dc, d1, dm;
+    double c0[4];            /* cubic tail of phi(r) on d1 < r <= dm */
+} xtb_pettifor_rep_pair;
+
 /* type(TB_H_DFTB), Objects.f90:202-222 -- tables flattened, one entry per (KOA1,KOA2) */
 typedef struct xtb_dftb_pair {
     double  rcut, d;          /* Fermi-like cut-off [A] */
@@ -91,6 +100,9 @@ int  xtb_sync(xtb_ctx* ctx);
 int  xtb_set_params_nrl     (xtb_ctx*, int n_kinds, const xtb_nrl_pair* p);
 int  xtb_set_params_pettifor(xtb_ctx*, int n_kinds, const xtb_pettifor_pair* p);
 int  xtb_set_params_dftb    (xtb_ctx*, int n_kinds, int n_orb /*1,4,9*/, const xtb_dftb_pair* p);
+/* Scell%TB_Repuls(:,:) of type TB_Rep_Pettifor; call after xtb_set_params_pettifor (n_kinds must match).
+ * Raises the neighbour cut-off to max(dm) when that is longer than max(rm) (Atomic_tools.f90:609-613). */
+int  xtb_set_params_pettifor_rep(xtb_ctx*, int n_kinds, const xtb_pettifor_rep_pair* p);
 
 /* ---- system: MDAtoms(:)%KOA, %S and Scell%supce (Objects.f90:552-581,692-845) ------ */
 int  xtb_set_system(xtb_ctx*, int na, const int32_t* koa /*[na], 1-based*/,
@@ -168,6 +180,16 @@ int  xtb_forces(xtb_ctx*, double* F_att);
  *      In a partitioned run this is the partial sum over owned atoms. */
 int  xtb_pressure(xtb_ctx*, double SCforce_att[9]);
 
+/* ---- repulsive pair terms of the Pettifor branch on the same neighbour stream.
+ *      xtb_repulsive_energy    get_Erep_s        (TB_Pettifor.f90:2074): E_rep = sum_i [f(sum_j phi(r_ij)) + E0_TB] [eV],
+ *                              Epot(na) = MDAtoms(i)%Epot (may be NULL)
+ *      xtb_repulsive_forces    dErdr_s           (TB_Pettifor.f90:2162): MDatoms(k)%forces%rep(1:3) = dE_rep/ds_k, F_rep(3,na)
+ *      xtb_repulsive_pressure  dErdr_Pressure_s  (TB_Pettifor.f90:2634): Scell%SCforce%rep(3,3) col-major
+ *      Need only the neighbour list (no eigenvectors).  Partitioned run: owned atoms / partial sums, as S4 / S5. */
+int  xtb_repulsive_energy  (xtb_ctx*, double* E_rep, double* Epot);
+int  xtb_repulsive_forces  (xtb_ctx*, double* F_rep);
+int  xtb_repulsive_pressure(xtb_ctx*, double SCforce_rep[9]);
+
 /* ---- introspection / zero-copy interop (device pointers valid until the producing stage
  *      is re-run or the context destroyed) ------------------------------------------- */
 #define XTB_BUF_H        1   /* dense H_non (N,N) */
@@ -181,6 +203,7 @@ int  xtb_pressure(xtb_ctx*, double SCforce_att[9]);
 #define XTB_BUF_SCFORCE  9   /* 9 doubles */
 #define XTB_BUF_HBLK    10   /* block-sparse H [n_blocks][n_orb*n_orb] (eV) */
 #define XTB_BUF_SBLK    11   /* block-sparse S */
+#define XTB_BUF_FREP    12   /* (3,na) repulsive forces */
 int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
  *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,
@@ -188,7 +211,8 @@ int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 long long xtb_counter(const xtb_ctx*, int which);
 /* device time [ms] of the last run of a stage (CUDA events on the context stream):
  * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure,
- * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3), 8 xtb_eigensolve */
+ * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3), 8 xtb_eigensolve,
+ * 9 repulsive energy + forces, 10 repulsive pressure, 11 xtb_coupling */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 
 #ifdef __cplusplus

@@ -51,6 +51,7 @@ def lib():
         _LIB = C.CDLL(so)
         _LIB.orc_neighbours.restype = C.c_int
         _LIB.orc_num_threads.restype = C.c_int
+        _LIB.orc_pet_erep.restype = C.c_double
     return _LIB
 
 
@@ -74,7 +75,10 @@ def cutoff_radius(wl):
     if wl["tb"] == "nrl":
         return max(p["Rc"] for p in wl["params"]) * G_AU2A
     if wl["tb"] == "pettifor":
-        return max(p["rm"] for p in wl["params"])
+        rm = max(p["rm"] for p in wl["params"])
+        if wl.get("rep_params"):                       # repulsive part longer than the attractive: Atomic_tools.f90:609-613
+            rm = max(rm, max(p["dm"] for p in wl["rep_params"]))
+        return rm
     raise ValueError(wl["tb"])
 
 
@@ -369,6 +373,42 @@ def pet_pressure(wl, nb, rho_blk):
     lib().orc_pet_pressure(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(nb.size), _p(nb.list),
                            _p(nb.dist), _p(nb.dist_s), pettifor_params_array(wl["params"]), _p(rho_blk), _p(att))
     return att.reshape(3, 3, order="F")
+
+
+def pettifor_rep_params_array(params):
+    arr = (_abi.PettiforRepPair * len(params))()
+    for i, d in enumerate(params):
+        arr[i] = _abi.pettifor_rep_pair_from_dict(d)
+    return arr
+
+
+def pet_erep(wl, nb):
+    """get_Erep_s, TB_Pettifor.f90:2074-2105 -> (E_rep, Epot(na))"""
+    Epot = np.zeros(nb.na)
+    E = lib().orc_pet_erep(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(nb.size), _p(nb.list),
+                           _p(nb.dist), pettifor_rep_params_array(wl["rep_params"]), _p(Epot))
+    return float(E), Epot
+
+
+def pet_rep_forces(wl, nb, verbatim=False, atom_first=0, atom_last=None):
+    """dErdr_s, TB_Pettifor.f90:2162-2306 -> forces%rep (na,3); verbatim = the reference's O(na^2 nn) loop nest"""
+    F = np.zeros((nb.na, 3))
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    args = (C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(h), _p(nb.size), _p(nb.list),
+            _p(nb.dist), pettifor_rep_params_array(wl["rep_params"]))
+    if verbatim:
+        lib().orc_pet_rep_forces_verbatim(*args, _p(F))
+    else:
+        lib().orc_pet_rep_forces_sparse(*args, C.c_int(atom_first), C.c_int(nb.na if atom_last is None else atom_last), _p(F))
+    return F
+
+
+def pet_rep_pressure(wl, nb):
+    """dErdr_Pressure_s, TB_Pettifor.f90:2634-2690 -> SCforce%rep(3,3)"""
+    rep = np.zeros(9)
+    lib().orc_pet_rep_pressure(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(nb.size), _p(nb.list),
+                               _p(nb.dist), _p(nb.dist_s), pettifor_rep_params_array(wl["rep_params"]), _p(rep))
+    return rep.reshape(3, 3, order="F")
 
 
 def eigensolve_orthogonal(H):

@@ -282,3 +282,156 @@ void orc_pet_pressure(int na, int cap, int n_kinds, const int* koa, const int* n
         }
     free(dwr);
 }
+
+/* ===== repulsive part: TB_Pettifor.f90 fx :2108-2123, phi :2126-2158, dphi :2695-2734, dfx :2776-2792,
+ * get_Erep_s :2074-2105, dErdr_s :2162-2306 (OpenMP arm), dErdr_Pressure_s :2634-2690.
+ * REP[(k1) + nk*(k2)] = TB_Repuls(k1+1, k2+1); struct xtb_pettifor_rep_pair = type(TB_Rep_Pettifor), Objects.f90:95-100. */
+static double pet_fx(const xtb_pettifor_rep_pair* R, double x) {                 /* :2108 */
+    const double x2 = x * x;
+    return R->a0[0] + R->a0[1] * x + R->a0[2] * x2 + R->a0[3] * x2 * x + R->a0[4] * x2 * x2;
+}
+
+static double pet_dfx(const xtb_pettifor_rep_pair* R, double x) {                /* :2776 */
+    const double x2 = x * x;
+    return R->a0[1] + R->a0[2] * x * 2.0 + R->a0[3] * x2 * 3.0 + R->a0[4] * x * x2 * 4.0;
+}
+
+static double pet_phi(const xtb_pettifor_rep_pair* R, double r) {                /* :2126 */
+    if (r > R->dm) return 0.0;
+    if (r > R->d1) {
+        const double x1 = r - R->d1, x2 = x1 * x1;
+        return R->c0[0] + R->c0[1] * x1 + R->c0[2] * x2 + R->c0[3] * x1 * x2;
+    }
+    if (r <= 0.0) return 0.0;
+    return R->phi0 * pow(R->d0 / r, R->m) * exp(R->m * (-pow(r / R->dc, R->mc) + pow(R->d0 / R->dc, R->mc)));
+}
+
+static double pet_dphi(const xtb_pettifor_rep_pair* R, double r) {               /* :2695 (Phi_precalc absent at both call sites) */
+    const double x1 = r - R->d1;
+    if (r > R->dm) return 0.0;
+    if (r > R->d1) return R->c0[1] + R->c0[2] * x1 * 2.0 + R->c0[3] * x1 * x1 * 3.0;
+    if (r <= 0.0) return 0.0;
+    return -R->m * pet_phi(R, r) / r * (1.0 + R->mc * pow(r / R->dc, R->mc));
+}
+
+/* get_Erep_s :2074.  Epot[i] = MDAtoms(i)%Epot; returns the total. */
+double orc_pet_erep(int na, int cap, int n_kinds, const int* koa, const int* nn_size, const int* nn_list,
+                    const double* nn_dist, const xtb_pettifor_rep_pair* REP, double* Epot) {
+    double a = 0.0;
+    for (int i1 = 0; i1 < na; ++i1) {
+        double b = 0.0;
+        for (int a2 = 0; a2 < nn_size[i1]; ++a2) {
+            const size_t e = (size_t)i1 * cap + a2;
+            const int j1 = nn_list[e];
+            if (j1 != i1) b = b + pet_phi(REP + koa[j1] + n_kinds * koa[i1], nn_dist[4 * e + 3]);
+        }
+        const xtb_pettifor_rep_pair* R = REP + koa[i1] + n_kinds * koa[i1];
+        const double E_pot = pet_fx(R, b) + R->E0_TB;
+        a = a + E_pot;
+        if (Epot) Epot[i1] = E_pot;
+    }
+    return a;
+}
+
+/* dErdr_s :2232-2300 verbatim: for every ian, every i1, the whole list of i1 (O(na^2 nn)). F[3*ian + al] = forces%rep(al). */
+void orc_pet_rep_forces_verbatim(int na, int cap, int n_kinds, const int* koa, const double* h, const int* nn_size,
+                                 const int* nn_list, const double* nn_dist, const xtb_pettifor_rep_pair* REP, double* F) {
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int ian = 0; ian < na; ++ian) {
+        double Erx[3] = {0.0, 0.0, 0.0};
+        for (int i1 = 0; i1 < na; ++i1) {
+            double dpsi[3] = {0.0, 0.0, 0.0}, psi = 0.0;
+            for (int a2 = 0; a2 < nn_size[i1]; ++a2) {
+                const size_t e = (size_t)i1 * cap + a2;
+                const int j1 = nn_list[e];
+                const int dik = ian == i1, djk = ian == j1;
+                if (j1 != i1 || (dik - djk) != 0) {
+                    const double x = nn_dist[4 * e], y = nn_dist[4 * e + 1], z = nn_dist[4 * e + 2], a_r = nn_dist[4 * e + 3];
+                    const xtb_pettifor_rep_pair* R = REP + koa[j1] + n_kinds * koa[i1];
+                    psi = psi + pet_phi(R, a_r);
+                    double x1[3];
+                    x1[0] = x * H_(1, 1) + y * H_(1, 2) + z * H_(1, 3);
+                    x1[1] = x * H_(2, 1) + y * H_(2, 2) + z * H_(2, 3);
+                    x1[2] = x * H_(3, 1) + y * H_(3, 2) + z * H_(3, 3);
+                    const double b = pet_dphi(R, a_r);
+                    const double ddlta = (double)(dik - djk) / a_r;
+                    const double b_delta = b * ddlta;
+                    dpsi[0] = dpsi[0] + b_delta * x1[0];
+                    dpsi[1] = dpsi[1] + b_delta * x1[1];
+                    dpsi[2] = dpsi[2] + b_delta * x1[2];
+                }
+            }
+            const double a = pet_dfx(REP + koa[i1] + n_kinds * koa[i1], psi);
+            Erx[0] = Erx[0] + a * dpsi[0];
+            Erx[1] = Erx[1] + a * dpsi[1];
+            Erx[2] = Erx[2] + a * dpsi[2];
+        }
+        F[3 * ian] = Erx[0]; F[3 * ian + 1] = Erx[1]; F[3 * ian + 2] = Erx[2];
+    }
+}
+
+/* sparse-equivalent: psi_i once per atom; for ian only i1 = ian (all its entries) and the i1 that list ian contribute. */
+void orc_pet_rep_forces_sparse(int na, int cap, int n_kinds, const int* koa, const double* h, const int* nn_size,
+                               const int* nn_list, const double* nn_dist, const xtb_pettifor_rep_pair* REP,
+                               int atom_first, int atom_last, double* F) {
+    double* dfpsi = (double*)malloc(sizeof(double) * (size_t)na);
+    for (int i1 = 0; i1 < na; ++i1) {
+        double psi = 0.0;
+        for (int a2 = 0; a2 < nn_size[i1]; ++a2) {
+            const size_t e = (size_t)i1 * cap + a2;
+            psi = psi + pet_phi(REP + koa[nn_list[e]] + n_kinds * koa[i1], nn_dist[4 * e + 3]);
+        }
+        dfpsi[i1] = pet_dfx(REP + koa[i1] + n_kinds * koa[i1], psi);
+    }
+#pragma omp parallel for schedule(dynamic, 8)
+    for (int ian = atom_first; ian < atom_last; ++ian) {
+        double Erx[3] = {0.0, 0.0, 0.0};
+        for (int i1 = 0; i1 < na; ++i1) {                   /* i1 ascending, as the reference accumulates */
+            int lo = 0, hi = nn_size[i1];
+            if (i1 != ian) {
+                lo = find_entry(nn_size, nn_list, cap, i1, ian);
+                if (lo < 0) continue;
+                hi = lo + 1;
+            }
+            double dpsi[3] = {0.0, 0.0, 0.0};
+            for (int a2 = lo; a2 < hi; ++a2) {
+                const size_t e = (size_t)i1 * cap + a2;
+                const int j1 = nn_list[e];
+                const double x = nn_dist[4 * e], y = nn_dist[4 * e + 1], z = nn_dist[4 * e + 2], a_r = nn_dist[4 * e + 3];
+                const double b = pet_dphi(REP + koa[j1] + n_kinds * koa[i1], a_r);
+                const double b_delta = b * ((double)((ian == i1) - (ian == j1)) / a_r);
+                dpsi[0] = dpsi[0] + b_delta * (x * H_(1, 1) + y * H_(1, 2) + z * H_(1, 3));
+                dpsi[1] = dpsi[1] + b_delta * (x * H_(2, 1) + y * H_(2, 2) + z * H_(2, 3));
+                dpsi[2] = dpsi[2] + b_delta * (x * H_(3, 1) + y * H_(3, 2) + z * H_(3, 3));
+            }
+            Erx[0] = Erx[0] + dfpsi[i1] * dpsi[0];
+            Erx[1] = Erx[1] + dfpsi[i1] * dpsi[1];
+            Erx[2] = Erx[2] + dfpsi[i1] * dpsi[2];
+        }
+        F[3 * ian] = Erx[0]; F[3 * ian + 1] = Erx[1]; F[3 * ian + 2] = Erx[2];
+    }
+    free(dfpsi);
+}
+
+/* dErdr_Pressure_s :2634-2690.  rep[l + 3*k] = SCforce%rep(l+1, k+1) (l: relative-coordinate index, k: Cartesian index). */
+void orc_pet_rep_pressure(int na, int cap, int n_kinds, const int* koa, const int* nn_size, const int* nn_list,
+                          const double* nn_dist, const double* nn_dist_s, const xtb_pettifor_rep_pair* REP, double* rep) {
+    for (int e9 = 0; e9 < 9; ++e9) rep[e9] = 0.0;
+    for (int i = 0; i < na; ++i) {
+        double Rep_Pr[9] = {0}, psi = 0.0;
+        for (int a2 = 0; a2 < nn_size[i]; ++a2) {
+            const size_t e = (size_t)i * cap + a2;
+            const int j = nn_list[e];
+            if (i == j) continue;
+            const double r = nn_dist[4 * e + 3];
+            const xtb_pettifor_rep_pair* R = REP + koa[j] + n_kinds * koa[i];
+            psi = psi + pet_phi(R, r);
+            const double dpsy = pet_dphi(R, r);
+            for (int k = 0; k < 3; ++k)
+                for (int l = 0; l < 3; ++l)
+                    Rep_Pr[l + 3 * k] = Rep_Pr[l + 3 * k] + dpsy * nn_dist[4 * e + k] * nn_dist_s[3 * e + l] / r;
+        }
+        const double df_psy = pet_dfx(REP + koa[i] + n_kinds * koa[i], psi);
+        for (int e9 = 0; e9 < 9; ++e9) rep[e9] = rep[e9] + df_psy * Rep_Pr[e9];
+    }
+}

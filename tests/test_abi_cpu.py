@@ -36,6 +36,7 @@ def test_struct_layout_matches_header():
     abi = importlib.import_module("xtant-3_b200._abi")
     assert C.sizeof(abi.NrlPair) == 8 + 3 * 8 + 16 * 8 + 80 * 8
     assert C.sizeof(abi.PettiforPair) == (2 + 28 + 4) * 8
+    assert C.sizeof(abi.PettiforRepPair) == (1 + 5 + 7 + 4) * 8
 
 
 def test_no_cpu_fallback():

@@ -12,9 +12,10 @@ LIB_PATH = os.path.join(_HERE, "libxtb_b200.so")
 XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE = range(7)
 XTB_TB_NONE, XTB_TB_NRL, XTB_TB_PETTIFOR, XTB_TB_DFTB = range(4)
 
-BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK = range(1, 12)
+BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK, BUF_FREP = range(1, 13)
 CNT_NA, CNT_NORB, CNT_N, CNT_MAXNN, CNT_NBLOCKS, CNT_NPAIRS, CNT_LAUNCHES, CNT_KKEPT, CNT_CAP = range(9)
 STAGE_NEIGH, STAGE_ASSEMBLE, STAGE_DENSITY, STAGE_FORCES, STAGE_PRESSURE = range(1, 6)
+STAGE_REP_FORCES, STAGE_REP_PRESSURE, STAGE_COUPLING = 9, 10, 11
 
 _d4 = C.c_double * 4
 _d10 = C.c_double * 10
@@ -34,6 +35,13 @@ class PettiforPair(C.Structure):
     _fields_ = [("Es", C.c_double), ("Ep", C.c_double),
                 ("nc", _d4), ("rc", _d4), ("c0", _d4), ("c1", _d4), ("c2", _d4), ("c3", _d4), ("V0", _d4),
                 ("r0", C.c_double), ("n", C.c_double), ("r1", C.c_double), ("rm", C.c_double)]
+
+
+class PettiforRepPair(C.Structure):
+    """struct xtb_pettifor_rep_pair == type(TB_Rep_Pettifor), Objects.f90:95-100"""
+    _fields_ = [("E0_TB", C.c_double), ("a0", C.c_double * 5),
+                ("phi0", C.c_double), ("d0", C.c_double), ("m", C.c_double), ("mc", C.c_double), ("dc", C.c_double),
+                ("d1", C.c_double), ("dm", C.c_double), ("c0", _d4)]
 
 
 class DftbPair(C.Structure):
@@ -61,6 +69,16 @@ def pettifor_pair_from_dict(d):
     for k in ("nc", "rc", "c0", "c1", "c2", "c3", "V0"):
         setattr(p, k, _d4(*d[k]))
     p.r0, p.n, p.r1, p.rm = float(d["r0"]), float(d["n"]), float(d["r1"]), float(d["rm"])
+    return p
+
+
+def pettifor_rep_pair_from_dict(d):
+    p = PettiforRepPair()
+    p.E0_TB = float(d["E0_TB"])
+    p.a0 = (C.c_double * 5)(*d["a0"])
+    for k in ("phi0", "d0", "m", "mc", "dc", "d1", "dm"):
+        setattr(p, k, float(d[k]))
+    p.c0 = _d4(*d["c0"])
     return p
 
 
@@ -99,6 +117,7 @@ SIGNATURES = {
     "xtb_set_params_nrl": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(NrlPair)]),
     "xtb_set_params_pettifor": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PettiforPair)]),
     "xtb_set_params_dftb": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(DftbPair)]),
+    "xtb_set_params_pettifor_rep": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PettiforRepPair)]),
     "xtb_set_system": (C.c_int, [C.c_void_p, C.c_int, _pi, _pd, _pd]),
     "xtb_set_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "xtb_neighbours": (C.c_int, [C.c_void_p, C.c_double, _pi, _pi, _pd, _pd]),
@@ -117,6 +136,9 @@ SIGNATURES = {
     "xtb_density_mirror": (C.c_int, [C.c_void_p]),
     "xtb_forces": (C.c_int, [C.c_void_p, _pd]),
     "xtb_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_repulsive_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_repulsive_forces": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_repulsive_pressure": (C.c_int, [C.c_void_p, _pd]),
     "xtb_device_buffer": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "xtb_counter": (C.c_longlong, [C.c_void_p, C.c_int]),
     "xtb_stage_ms": (C.c_double, [C.c_void_p, C.c_int]),

@@ -9,6 +9,7 @@ procedures they stand in for (same argument meaning, results in the reference's 
     Construct_Aij / Construct_Aij_x_En   TB.f90:4328,4401                             (-> density)
     get_dHij_drij_NRL / dHij_s     TB_NRL.f90:2412, TB_Pettifor.f90:141               (-> forces)
     Attract_TB_Forces_Press_NRL / Attract_TB_Forces_Press  TB_NRL.f90:2742, TB_Pettifor.f90:1134 (-> pressure)
+    get_Erep_s / dErdr_s / dErdr_Pressure_s   TB_Pettifor.f90:2074,2162,2634        (same names)
 
 Errors: every non-zero ABI status raises XtbError(code, text) -- the reference records
 (Save_error_details) and continues; a Python caller gets an exception instead.
@@ -92,6 +93,9 @@ class TBContext:
             arr = (_abi.PettiforPair * (nk * nk))(*[_abi.pettifor_pair_from_dict(d) for d in wl["params"]])
             self._ck(self.lib.xtb_set_params_pettifor(self.h, nk, arr))
             self.n_orb = 4
+            if wl.get("rep_params"):
+                rep = (_abi.PettiforRepPair * (nk * nk))(*[_abi.pettifor_rep_pair_from_dict(d) for d in wl["rep_params"]])
+                self._ck(self.lib.xtb_set_params_pettifor_rep(self.h, nk, rep))
         elif wl["tb"] == "dftb":
             arr, keep = _abi.dftb_pair_array(wl["params"])     # tables are copied by the library during the call
             self._ck(self.lib.xtb_set_params_dftb(self.h, nk, int(wl["n_orb"]), arr))
@@ -233,3 +237,22 @@ class TBContext:
         att = np.zeros(9)
         self._ck(self.lib.xtb_pressure(self.h, _dp(att)))
         return att.reshape(3, 3, order="F")
+
+    # -- repulsive pair terms of the Pettifor branch ----------------------
+    def get_Erep_s(self):
+        """get_Erep_s, TB_Pettifor.f90:2074 -> (E_rep [eV], MDAtoms(:)%Epot)"""
+        E = np.zeros(1); Epot = np.zeros(self.na)
+        self._ck(self.lib.xtb_repulsive_energy(self.h, _dp(E), _dp(Epot)))
+        return float(E[0]), Epot
+
+    def dErdr_s(self):
+        """dErdr_s, TB_Pettifor.f90:2162 -> forces%rep (na,3), d/ds units [eV]"""
+        F = np.zeros((self.na, 3))
+        self._ck(self.lib.xtb_repulsive_forces(self.h, _dp(F)))
+        return F
+
+    def dErdr_Pressure_s(self):
+        """dErdr_Pressure_s, TB_Pettifor.f90:2634 -> SCforce%rep(3,3)"""
+        rep = np.zeros(9)
+        self._ck(self.lib.xtb_repulsive_pressure(self.h, _dp(rep)))
+        return rep.reshape(3, 3, order="F")

@@ -63,7 +63,8 @@ int xtb_destroy(xtb_ctx* c) {
     DevBuf* all[] = {&c->d_params, &c->d_koa, &c->d_S, &c->d_nn_size, &c->d_nn_list, &c->d_nn_dist, &c->d_nn_dist_s, &c->d_rev, &c->d_own,
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
-                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS};
+                     &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
+                     &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep};
     for (DevBuf* b : all) xtb_free(*b);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -109,8 +110,24 @@ int xtb_set_params_pettifor(xtb_ctx* c, int n_kinds, const xtb_pettifor_pair* p)
     if (n_kinds <= 0 || !p) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_pettifor: n_kinds=%d", n_kinds);
     cudaSetDevice(c->device);
     c->h_pet.assign(p, p + (size_t)n_kinds * n_kinds);
+    c->h_pet_rep.clear();                                      // a new attractive set drops the repulsive one
     c->tb = XTB_TB_PETTIFOR; c->n_kinds = n_kinds; c->n_orb = 4;
     return upload_params(c, p, sizeof(xtb_pettifor_pair) * (size_t)n_kinds * n_kinds);
+}
+
+int xtb_set_params_pettifor_rep(xtb_ctx* c, int n_kinds, const xtb_pettifor_rep_pair* p) {
+    if (!c) return XTB_EINVAL;
+    if (c->tb != XTB_TB_PETTIFOR) XTB_FAIL(c, XTB_ESTATE, "xtb_set_params_pettifor_rep: call xtb_set_params_pettifor first");
+    if (n_kinds != c->n_kinds || !p) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_pettifor_rep: n_kinds=%d (attractive part has %d)", n_kinds, c->n_kinds);
+    cudaSetDevice(c->device);
+    const size_t cnt = (size_t)n_kinds * n_kinds;
+    c->h_pet_rep.assign(p, p + cnt);
+    int rc = xtb_reserve(c, c->d_rep_params, sizeof(xtb_pettifor_rep_pair) * cnt);
+    if (rc) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_rep_params.p, p, sizeof(xtb_pettifor_rep_pair) * cnt, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;   // the cut-off may have grown
+    return XTB_OK;
 }
 
 int xtb_set_params_dftb(xtb_ctx* c, int n_kinds, int n_orb, const xtb_dftb_pair* p) {
@@ -178,7 +195,10 @@ int xtb_set_partition(xtb_ctx* c, int first, int last) {
 static double default_cutoff(const xtb_ctx* c) {
     double rm = 0.0;
     if (c->tb == XTB_TB_NRL) { for (auto& p : c->h_nrl) rm = p.Rc > rm ? p.Rc : rm; rm *= XTB_G_AU2A; }
-    else if (c->tb == XTB_TB_PETTIFOR) { for (auto& p : c->h_pet) rm = p.rm > rm ? p.rm : rm; }
+    else if (c->tb == XTB_TB_PETTIFOR) {
+        for (auto& p : c->h_pet) rm = p.rm > rm ? p.rm : rm;
+        for (auto& p : c->h_pet_rep) rm = p.dm > rm ? p.dm : rm;      // `if (rm < r(1)) rm = r(1)`, Atomic_tools.f90:611-613
+    }
     else if (c->tb == XTB_TB_DFTB) rm = c->dftb_rm;
     return rm;
 }
@@ -469,6 +489,52 @@ int xtb_pressure(xtb_ctx* c, double* SCforce_att) {
     return XTB_OK;
 }
 
+// ---- repulsive pair terms ----
+static int rep_ready(xtb_ctx* c, const char* who) {
+    if (c->tb != XTB_TB_PETTIFOR || c->h_pet_rep.empty()) XTB_FAIL(c, XTB_ESTATE, "%s: no repulsive parameters (xtb_set_params_pettifor_rep)", who);
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "%s: run xtb_neighbours first", who);
+    return XTB_OK;
+}
+
+int xtb_repulsive_energy(xtb_ctx* c, double* E_rep, double* Epot) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = rep_ready(c, "xtb_repulsive_energy"))) return rc;
+    if ((rc = xtb_impl_pettifor_rep_energy(c))) return rc;
+    if (E_rep) XTB_CUDA(c, cudaMemcpyAsync(E_rep, c->d_Erep.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (Epot) XTB_CUDA(c, cudaMemcpyAsync(Epot, c->d_Epot.p, sizeof(double) * c->na, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_repulsive_forces(xtb_ctx* c, double* F_rep) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = rep_ready(c, "xtb_repulsive_forces"))) return rc;
+    if ((rc = xtb_impl_pettifor_rep_forces(c))) return rc;
+    const size_t cnt = (size_t)(c->a1 - c->a0) * 3;
+    if (F_rep && cnt) {
+        XTB_CUDA(c, cudaMemcpyAsync(F_rep + 3 * (size_t)c->a0, (double*)c->d_Frep.p + 3 * (size_t)c->a0, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
+int xtb_repulsive_pressure(xtb_ctx* c, double* SCforce_rep) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = rep_ready(c, "xtb_repulsive_pressure"))) return rc;
+    if ((rc = xtb_impl_pettifor_rep_pressure(c))) return rc;
+    if (SCforce_rep) {
+        XTB_CUDA(c, cudaMemcpyAsync(SCforce_rep, c->d_SCrep.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
 int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
     if (!c || !dptr) return XTB_EINVAL;
     const size_t N = (size_t)c->na * c->n_orb;
@@ -486,6 +552,7 @@ int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
         case XTB_BUF_SCFORCE: b = &c->d_SC; used = 72; break;
         case XTB_BUF_HBLK: b = &c->d_Hblk; used = 8 * nb2 * (size_t)c->n_blocks; break;
         case XTB_BUF_SBLK: b = &c->d_Sblk; used = 8 * nb2 * (size_t)c->n_blocks; break;
+        case XTB_BUF_FREP: b = &c->d_Frep; used = 24 * (size_t)c->na; break;
         default: XTB_FAIL(c, XTB_EINVAL, "xtb_device_buffer: unknown buffer %d", which);
     }
     if (!b->p) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: buffer %d not produced yet", which);
@@ -513,7 +580,7 @@ long long xtb_counter(const xtb_ctx* c, int which) {
 }
 
 double xtb_stage_ms(const xtb_ctx* c, int stage) {
-    if (!c || stage < 1 || stage > 8) return -1.0;
+    if (!c || stage < 1 || stage > 11) return -1.0;
     if (stage == 8) return c->eigen_ms;
     return c->stage_ms[stage];
 }

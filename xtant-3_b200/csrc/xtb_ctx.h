@@ -30,6 +30,8 @@ struct xtb_ctx {
     int n_orb = 0;
     std::vector<xtb_nrl_pair> h_nrl;
     std::vector<xtb_pettifor_pair> h_pet;
+    std::vector<xtb_pettifor_rep_pair> h_pet_rep;   // empty: no repulsive part set
+    DevBuf d_rep_params;
     DevBuf d_params;            // array of the active pair struct (DFTB: array of DftbDev, dftb_device.cuh)
     DevBuf d_dftb_tab;          // DFTB: all radial grids and tables, one buffer of doubles
     double dftb_rm = 0.0;       // DFTB: max(rcut) + 10*max(d)  (get_near_neighbours, Atomic_tools.f90:588-591)
@@ -70,10 +72,12 @@ struct xtb_ctx {
     bool have_density = false;
     // forces / pressure
     DevBuf d_F, d_SC, d_scratch, d_hdev, d_ppart, d_tab;
+    // repulsive pair terms (pettifor_rep.cu)
+    DevBuf d_Epot, d_dfpsi, d_Erep, d_Frep, d_SCrep;
     // timing
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mid = nullptr, ev_mid2 = nullptr;
     int density_slotcap = 0, density_stages = 0;
-    double stage_ms[8] = {0};
+    double stage_ms[12] = {0};   // 1..7 and 9..11 (8 = eigen_ms), see xtb_stage_ms
     int sm_count = 148;
     int density_dbg = 0;        // XTB_DENSITY_DBG (timing experiments only, separate kernel instantiation): 1 no math, 2 quarter of the tile copies, 4 helper warps nap while polling, 8 no DFMA
     int density_ncw = 8;        // consumer warps of the density kernel (8 or 12); XTB_DENSITY_NCW
@@ -119,6 +123,9 @@ int xtb_impl_nrl_forces(xtb_ctx* c);
 int xtb_impl_nrl_pressure(xtb_ctx* c);
 int xtb_impl_pettifor_forces(xtb_ctx* c);
 int xtb_impl_pettifor_pressure(xtb_ctx* c);
+int xtb_impl_pettifor_rep_energy(xtb_ctx* c);      // pettifor_rep.cu
+int xtb_impl_pettifor_rep_forces(xtb_ctx* c);
+int xtb_impl_pettifor_rep_pressure(xtb_ctx* c);
 int xtb_impl_mirror_density(xtb_ctx* c);
 int xtb_impl_eigensolve(xtb_ctx* c);        // eigen.cu: Loewdin + Dsyevd + back-transform on the device-resident H, S
 int xtb_impl_dftb_assemble(xtb_ctx* c, bool dense);

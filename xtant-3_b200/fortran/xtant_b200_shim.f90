@@ -21,12 +21,12 @@
 module XTANT_B200_shim
 use, intrinsic :: iso_c_binding
 use Objects, only : Super_cell, Numerics_param, solid, Error_handling, Save_error_details, &
-                    TB_H_NRL, TB_H_Pettifor
+                    TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor
 implicit none
 private
 public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_Aij, Construct_Aij_x_En, &
           get_dHij_drij_NRL, Attract_TB_Forces_Press_NRL, construct_TB_H_Pettifor, dHij_s, Attract_TB_Forces_Press, &
-          xtb_b200_init, xtb_b200_finalize
+          get_Erep_s, dErdr_s, dErdr_Pressure_s, xtb_b200_init, xtb_b200_finalize
 
 ! ---- mirror of struct xtb_nrl_pair / xtb_pettifor_pair (include/xtb_b200.h) ----
 type, bind(C) :: xtb_nrl_pair
@@ -42,6 +42,13 @@ type, bind(C) :: xtb_pettifor_pair
    real(c_double) :: nc(4), rc(4), c0(4), c1(4), c2(4), c3(4), V0(4)
    real(c_double) :: r0, n, r1, rm
 end type xtb_pettifor_pair
+
+type, bind(C) :: xtb_pettifor_rep_pair      ! type(TB_Rep_Pettifor), Objects.f90:95-100
+   real(c_double) :: E0_TB
+   real(c_double) :: a0(5)
+   real(c_double) :: phi0, d0, m, mc, dc, d1, dm
+   real(c_double) :: c0(4)
+end type xtb_pettifor_rep_pair
 
 type(c_ptr), save :: ctx = c_null_ptr      ! one context per process (single caller thread, TB.f90:227-272)
 logical, save :: eigen_current = .false.   ! Ha/Ei/fe of this step already on the device
@@ -61,6 +68,18 @@ interface
    end function
    integer(c_int) function xtb_set_params_pettifor(c, n_kinds, p) bind(C, name="xtb_set_params_pettifor")
       import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds; type(xtb_pettifor_pair), intent(in) :: p(*)
+   end function
+   integer(c_int) function xtb_set_params_pettifor_rep(c, n_kinds, p) bind(C, name="xtb_set_params_pettifor_rep")
+      import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds; type(xtb_pettifor_rep_pair), intent(in) :: p(*)
+   end function
+   integer(c_int) function xtb_repulsive_energy(c, E_rep, Epot) bind(C, name="xtb_repulsive_energy")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: E_rep; real(c_double), intent(out) :: Epot(*)
+   end function
+   integer(c_int) function xtb_repulsive_forces(c, F_rep) bind(C, name="xtb_repulsive_forces")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: F_rep(3,*)
+   end function
+   integer(c_int) function xtb_repulsive_pressure(c, rep) bind(C, name="xtb_repulsive_pressure")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: rep(3,3)
    end function
    integer(c_int) function xtb_set_system(c, na, koa, S, supce) bind(C, name="xtb_set_system")
       import; type(c_ptr), value :: c; integer(c_int), value :: na
@@ -210,9 +229,17 @@ subroutine get_near_neighbours(Scell, numpar, include_vdW, dm)
             call push_params_nrl(ARRAY)
          end select
       END ASSOCIATE
+      if (allocated(Scell(NSC)%TB_Repuls)) then
+         ASSOCIATE (ARRAY => Scell(NSC)%TB_Repuls(:,:))
+            select type(ARRAY)
+            type is (TB_Rep_Pettifor)
+               call push_params_pettifor_rep(ARRAY)    ! also raises the cut-off to max(dm), Atomic_tools.f90:609-613
+            end select
+         END ASSOCIATE
+      endif
       call push_system(Scell, NSC)
-      ! rm <= 0: the library derives the cut-off as Atomic_tools.f90:574-586 does.  The vdW / repulsive
-      ! enlargements (:611-640) are host scalars: compute them as before and pass rm > 0 when they apply.
+      ! rm <= 0: the library derives the cut-off as Atomic_tools.f90:574-613 does.  The vdW enlargement
+      ! (:633-640) is a host scalar: compute it as before and pass rm > 0 when it applies.
       rm = 0.0d0
       call check(xtb_neighbours(ctx, rm, Scell(NSC)%Near_neighbor_size, Scell(NSC)%Near_neighbor_list, &
                                 Scell(NSC)%Near_neighbor_dist, Scell(NSC)%Near_neighbor_dist_s), 'xtb_neighbours')
@@ -384,5 +411,68 @@ subroutine Attract_TB_Forces_Press(TB_Hamil, atoms, Scell, NSC, numpar, Aij)
       call check(xtb_pressure(ctx, Scell(NSC)%SCforce%att), 'xtb_pressure')
    endif
 end subroutine Attract_TB_Forces_Press
+
+! ---- repulsive part of the Pettifor-type branch (TB_Pettifor.f90:2074,2162,2634; called from TB.f90 get_pot_nrg / get_total_forces)
+subroutine push_params_pettifor_rep(TB)
+   type(TB_Rep_Pettifor), dimension(:,:), intent(in) :: TB
+   type(xtb_pettifor_rep_pair), allocatable :: p(:)
+   integer :: nk, i, j, k
+   nk = size(TB,1)
+   allocate(p(nk*nk))
+   do j = 1, nk
+      do i = 1, nk
+         k = i + nk*(j-1)
+         p(k)%E0_TB = TB(i,j)%E0_TB ; p(k)%a0 = TB(i,j)%a0 ; p(k)%c0 = TB(i,j)%c0
+         p(k)%phi0 = TB(i,j)%phi0 ; p(k)%d0 = TB(i,j)%d0 ; p(k)%m = TB(i,j)%m ; p(k)%mc = TB(i,j)%mc
+         p(k)%dc = TB(i,j)%dc ; p(k)%d1 = TB(i,j)%d1 ; p(k)%dm = TB(i,j)%dm
+      enddo
+   enddo
+   call check(xtb_set_params_pettifor_rep(ctx, int(nk,c_int), p), 'xtb_set_params_pettifor_rep')
+end subroutine push_params_pettifor_rep
+
+subroutine get_Erep_s(TB_Repuls, Scell, NSC, numpar, a)
+   type(TB_Rep_Pettifor), dimension(:,:), intent(in) :: TB_Repuls
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(in) :: numpar
+   real(8), intent(out) :: a
+   real(c_double), allocatable :: Epot(:)
+   integer :: i, na
+   na = size(Scell(NSC)%MDAtoms)
+   allocate(Epot(na))
+   call check(xtb_repulsive_energy(ctx, a, Epot), 'xtb_repulsive_energy')
+   do i = 1, na
+      Scell(NSC)%MDAtoms(i)%Epot = Epot(i)      ! TB_Pettifor.f90:2103
+   enddo
+end subroutine get_Erep_s
+
+subroutine dErdr_s(TB_Repuls, atoms, Scell, NSC, numpar)
+   use Objects, only : Atom
+   type(TB_Rep_Pettifor), dimension(:,:), intent(in) :: TB_Repuls
+   type(Atom), dimension(:), intent(in) :: atoms
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(c_double), allocatable :: F(:,:)
+   integer :: k, na
+   na = size(atoms)
+   allocate(F(3,na))
+   call check(xtb_repulsive_forces(ctx, F), 'xtb_repulsive_forces')
+   do k = 1, na
+      Scell(NSC)%MDatoms(k)%forces%rep(:) = F(:,k)     ! TB_Pettifor.f90:2299
+   enddo
+end subroutine dErdr_s
+
+subroutine dErdr_Pressure_s(TB_Repuls, atoms, Scell, NSC, numpar)
+   use Objects, only : Atom
+   type(TB_Rep_Pettifor), dimension(:,:), intent(in) :: TB_Repuls
+   type(Atom), dimension(:), intent(in) :: atoms
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(in) :: numpar
+   if (numpar%p_const) then        ! TB_Pettifor.f90:2646
+      call check(xtb_repulsive_pressure(ctx, Scell(NSC)%SCforce%rep), 'xtb_repulsive_pressure')
+   endif
+end subroutine dErdr_Pressure_s
 
 end module XTANT_B200_shim

@@ -1,0 +1,175 @@
+"""Readers for the reference's own input files on this path.  Host-side, pure Python.
+
+Each function restates one reader of Source_files/Read_input_data.f90 (list-directed `read(FN,*)`: the first
+numeric token(s) of a line, Fortran `d` exponents) and returns the dict the C-ABI structs are filled from
+(`_abi.*_from_dict`):
+
+    read_Mehl_TB_Hamiltonian        Read_input_data.f90:3963-4158  ->  xtb_nrl_pair           (NRL)
+    read_Pettifor_TB_Hamiltonian    Read_input_data.f90:3377-3661  ->  xtb_pettifor_pair
+    read_Pettifor_TB_repulsive      Read_input_data.f90:2908-3056  ->  xtb_pettifor_rep_pair
+    read_SAVE                       Dealing_with_output_files.f90:2120-2158 (writer) / Initial_configuration.f90:1594 (reader)
+                                    SAVE_atoms.dat + SAVE_supercell.dat -> koa, S, supce
+    read_unit_cell                  Unit_cell_equilibrium.txt + Unit_cell_atom_relative_coordinates.txt
+                                    (Initial_configuration.f90:  set_initial_configuration) -> replicated supercell
+The matching writers (`write_*`) exist so that tests can round-trip without the reference tree being present.
+"""
+import numpy as np
+
+
+def _num(tok):
+    return float(tok.lower().replace("d", "e"))
+
+
+def _lines(path):
+    with open(path) as f:
+        return f.read().splitlines()
+
+
+def read_Mehl_TB_Hamiltonian(path):
+    """NRL parameter file.  Line 1 name, line 2 `ind_split ind_overlap ind`, line 3 `Rc lden`, then lambda, the on-site
+    sets (a,b,c,d) x {s,p,t2g[,eg]}, then 10 channels x (e,f,[g,]h) for H and for S (file order ss,sp,pp_s,pp_p,sd,pd_s,pd_p,
+    dd_s,dd_p,dd_d)."""
+    lines = _lines(path)
+    if lines[0].split()[0] not in ("Mehl", "NRL"):
+        raise ValueError(f"{path}: not an NRL parameter file ({lines[0]!r})")
+    it = iter(lines[1:])
+    t = next(it).split()
+    ind_split, ind_overlap, ind = int(t[0]), int(t[1]), int(t[2])
+    t = next(it).split()
+    p = {"ind_split": ind_split, "ind_overlap": ind_overlap, "Rc": _num(t[0]), "lden": _num(t[1])}
+
+    def nxt():
+        return _num(next(it).split()[0])
+
+    p["lambd"] = nxt()
+    al, bl, cl, dl = [0.0] * 4, [0.0] * 4, [0.0] * 4, [0.0] * 4
+    for s in range(4 if ind_split == 1 else 3):
+        al[s] = nxt(); bl[s] = nxt(); cl[s] = nxt(); dl[s] = nxt()
+    p.update(al=al, bl=bl, cl=cl, dl=dl)
+    for names in (("ellm", "fllm", "gllm", "hllm"), ("pllm", "qllm", "rllm", "sllm")):
+        arrs = [[0.0] * 10 for _ in range(4)]
+        for c in range(10):
+            arrs[0][c] = nxt()
+            arrs[1][c] = nxt()
+            arrs[2][c] = nxt() if ind > 0 else 0.0
+            arrs[3][c] = nxt()
+        for n, a in zip(names, arrs):
+            p[n] = a
+    return p
+
+
+def read_Pettifor_TB_Hamiltonian(path):
+    lines = _lines(path)
+    if lines[0].split()[0] != "Pettifor":
+        raise ValueError(f"{path}: not a Pettifor parameter file ({lines[0]!r})")
+    v = [_num(l.split()[0]) for l in lines[1:] if l.strip()]
+    p = {"Es": v[0], "Ep": v[1], "V0": v[2:6], "r0": v[6], "n": v[7], "r1": v[8], "rm": v[9],
+         "nc": v[10:14], "rc": v[14:18]}
+    c = v[18:34]
+    for q, name in enumerate(("c0", "c1", "c2", "c3")):
+        p[name] = [c[4 * i + q] for i in range(4)]
+    return p
+
+
+_REP_ORDER = ("E0_TB", "phi0", "m", "mc", "d0", "d1", "dm", "dc")
+
+
+def read_Pettifor_TB_repulsive(path):
+    """file order E0_TB, phi0, m, mc, d0, d1, dm, dc, c0(1:4), a0(1:5)  (Read_input_data.f90:2919-3048)"""
+    lines = _lines(path)
+    if lines[0].split()[0] != "Pettifor":
+        raise ValueError(f"{path}: not a Pettifor repulsive file ({lines[0]!r})")
+    v = [_num(l.split()[0]) for l in lines[1:] if l.strip()]
+    if len(v) < 17:
+        raise ValueError(f"{path}: {len(v)} numbers, 17 expected")
+    p = dict(zip(_REP_ORDER, v[:8]))
+    p["c0"] = v[8:12]
+    p["a0"] = v[12:17]
+    return p
+
+
+def read_SAVE(atoms_path, cell_path):
+    """SAVE_atoms.dat: `KOA S(1:3) ...` per atom; SAVE_supercell.dat: file line i = COLUMN i of supce
+    (`Scell%supce(:,i) = temp_vec`, Initial_configuration.f90:2409-2418)."""
+    koa, S = [], []
+    for line in _lines(atoms_path):
+        t = line.split()
+        if not t:
+            continue
+        koa.append(int(t[0]))
+        S.append([_num(x) for x in t[1:4]])
+    rows = [l.split() for l in _lines(cell_path)]
+    rows = [r for r in rows if r][:3]
+    cols = [[_num(x) for x in r] for r in rows]
+    supce = [[cols[b][a] for b in range(3)] for a in range(3)]
+    return {"koa": koa, "S": S, "supce": supce}
+
+
+def read_unit_cell(cell_path, coords_path, reps):
+    """Unit_cell_equilibrium.txt (first three lines; line i = column i of the unit cell) and
+    Unit_cell_atom_relative_coordinates.txt (`KOA s1 s2 s3`), replicated as set_initial_coords does
+    (Initial_configuration.f90:2241-2285: loops nx, ny, nz outermost-first, unit-cell atoms innermost;
+    S = (s + n)/ncell; the reference's +-1e-10 random shift is left out) and wrapped into [0,1)
+    (check_periodic_boundaries).  supce(:,i) = ncell_i * unit_cell(:,i) (:2546-2548)."""
+    rows = [l.split() for l in _lines(cell_path)]
+    rows = [r for r in rows if r][:3]
+    unit = np.array([[_num(x) for x in r[:3]] for r in rows]).T          # unit[:, i] = file line i
+    koa0, rel = [], []
+    for line in _lines(coords_path):
+        t = line.split()
+        if len(t) < 4:
+            continue
+        koa0.append(int(t[0]))
+        rel.append([_num(x) for x in t[1:4]])
+    rel = np.array(rel)
+    ncell = np.array(reps, dtype=np.float64)
+    koa, S = [], []
+    for nx in range(reps[0]):
+        for ny in range(reps[1]):
+            for nz in range(reps[2]):
+                for k in range(len(koa0)):
+                    S.append((rel[k] + np.array([nx, ny, nz], dtype=np.float64)) / ncell)
+                    koa.append(koa0[k])
+    S = np.mod(np.array(S), 1.0)
+    supce = unit * ncell[None, :]
+    return {"koa": koa, "S": S.tolist(), "supce": supce.tolist()}
+
+
+# ---- writers in the reference's file formats (tests round-trip through them) ----------------------------------
+def _f(x):
+    return f"{x:.16e}".replace("e", "d")
+
+
+def write_Pettifor_TB_repulsive(path, p):
+    vals = [p[k] for k in _REP_ORDER] + list(p["c0"]) + list(p["a0"])
+    with open(path, "w") as f:
+        f.write("Pettifor\n" + "".join(f"{_f(v)}\t! \n" for v in vals))
+
+
+def write_Pettifor_TB_Hamiltonian(path, p):
+    vals = [p["Es"], p["Ep"]] + list(p["V0"]) + [p["r0"], p["n"], p["r1"], p["rm"]] + list(p["nc"]) + list(p["rc"])
+    for i in range(4):
+        vals += [p["c0"][i], p["c1"][i], p["c2"][i], p["c3"][i]]
+    with open(path, "w") as f:
+        f.write("Pettifor\n" + "".join(f"{_f(v)}\n" for v in vals))
+
+
+def write_Mehl_TB_Hamiltonian(path, p):
+    out = ["NRL", f"{p['ind_split']} {p['ind_overlap']} 1", f"{_f(p['Rc'])} {_f(p['lden'])}", _f(p["lambd"])]
+    for s in range(4 if p["ind_split"] == 1 else 3):
+        out += [_f(p[k][s]) for k in ("al", "bl", "cl", "dl")]
+    for names in (("ellm", "fllm", "gllm", "hllm"), ("pllm", "qllm", "rllm", "sllm")):
+        for c in range(10):
+            out += [_f(p[n][c]) for n in names]
+    with open(path, "w") as f:
+        f.write("\n".join(out) + "\n")
+
+
+def write_SAVE(atoms_path, cell_path, cell):
+    with open(atoms_path, "w") as f:
+        for k, s in zip(cell["koa"], cell["S"]):
+            f.write(f"  {int(k)}  " + "  ".join(f"{x:.16E}" for x in s) + "\n")
+    h = np.array(cell["supce"])
+    with open(cell_path, "w") as f:
+        for i in range(3):
+            f.write(" " + " ".join(f"{h[a, i]:.16E}" for a in range(3)) + "\n")

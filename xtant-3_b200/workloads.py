@@ -49,6 +49,7 @@ def _wl(name, tb, element, S, supce, n_el_per_atom, Te_eV, koa=None):
                 koa=np.ones(na, dtype=np.int32) if koa is None else np.asarray(koa, dtype=np.int32),
                 S=np.ascontiguousarray(S, dtype=np.float64), supce=np.ascontiguousarray(supce, dtype=np.float64),
                 params=[load_params(tb, element)], n_kinds=1, element=element,
+                rep_params=[load_params("pettifor_rep", element)] if tb == "pettifor" else None,
                 n_electrons=float(n_el_per_atom * na), Te_eV=float(Te_eV))
 
 
