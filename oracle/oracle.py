@@ -517,3 +517,50 @@ def dftb_step(wl, with_pressure=True, verbatim=False):
     if with_pressure:
         out["P"] = dftb_pressure(wl, nb, lmn, rad, out["rho"], out["rhoE"])
     return out
+
+
+# ---- nonadiabatic coupling matrix -------------------------------------------------------------
+def coupling_Mij_loops(Ha, Ha0, Sij=None, kind_M=0):
+    """Electron_ion_coupling_Mij, Nonadiabatic.f90:782-945, statement by statement (pure Python loops: small N only).
+    kind_M = -1: the `case(-1)` arm (:816-874); anything else: Tully's expression, the `case default` arm (:876-938)."""
+    N = Ha.shape[0]
+    eps = 1.0e-13                                                         # :812
+    Mij = np.zeros((N, N))
+    Norm0 = np.array([np.sqrt(np.sum(Ha0[:, i] * Ha0[:, i])) for i in range(N)])      # :823 / :883
+    Norm1 = np.array([np.sqrt(np.sum(Ha[:, i] * Ha[:, i])) for i in range(N)])
+    tij = np.zeros((N, N))
+    if Sij is not None:                                                   # :829-842 / :889-902
+        for i in range(N):
+            for k in range(N):
+                tij[i, k] = 0.0 if Norm1[i] < eps else np.sum(Sij[k, :] * Ha[:, i] / Norm1[i])
+    for i in range(N):
+        psi0 = np.zeros(N) if Norm0[i] < eps else Ha0[:, i] / Norm0[i]
+        psi_back = np.zeros(N) if Norm1[i] < eps else Ha[:, i] / Norm1[i]
+        for j in range(i, N):
+            if i == j:
+                continue
+            Norm_val1 = 0.0 if Norm1[j] < eps else 1.0 / Norm1[j]
+            Norm_val0 = 0.0 if Norm0[j] < eps else 1.0 / Norm0[j]
+            if kind_M == -1:
+                Mij[i, j] = np.sum(psi0 * tij[j, :]) if Sij is not None else np.sum(psi0 * Ha[:, j] * Norm_val1)      # :862-866
+            elif Sij is not None:
+                Mij[i, j] = np.sum(psi0 * tij[j, :] - (Ha0[:, j] * Norm_val0) * tij[i, :])                            # :927
+            else:
+                Mij[i, j] = np.sum(psi0 * (Ha[:, j] * Norm_val1) - (Ha0[:, j] * Norm_val0) * psi_back)                # :930
+            Mij[j, i] = Mij[i, j]
+    if kind_M != -1:
+        Mij = Mij * 0.5                                                   # :938
+    return Mij
+
+
+def coupling_Mij(Ha, Ha0, Sij=None, kind_M=0):
+    """Same result through matrix products (what the loops amount to): G = psi0^T S psi ;
+    Tully: M(i<j) = (G(i,j) - G(j,i))/2 ; case(-1): M(i<j) = G(i,j) ; M(j,i) = M(i,j) ; M(i,i) = 0."""
+    eps = 1.0e-13
+    n0 = np.sqrt((Ha0 * Ha0).sum(axis=0)); n1 = np.sqrt((Ha * Ha).sum(axis=0))
+    i0 = np.where(n0 < eps, 0.0, 1.0 / np.where(n0 < eps, 1.0, n0))
+    i1 = np.where(n1 < eps, 0.0, 1.0 / np.where(n1 < eps, 1.0, n1))
+    P0 = Ha0 * i0[None, :]; P1 = Ha * i1[None, :]
+    G = P0.T @ (P1 if Sij is None else Sij @ P1)
+    U = np.triu(G if kind_M == -1 else 0.5 * (G - G.T), 1)
+    return U + U.T
