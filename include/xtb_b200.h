@@ -190,6 +190,17 @@ int  xtb_repulsive_energy  (xtb_ctx*, double* E_rep, double* Epot);
 int  xtb_repulsive_forces  (xtb_ctx*, double* F_rep);
 int  xtb_repulsive_pressure(xtb_ctx*, double SCforce_rep[9]);
 
+/* ---- Electron_ion_coupling_Mij (Nonadiabatic.f90:782-945), the two more N^3 contractions of an
+ *      "electron-ion coupling" run.  Ha0 = eigenvectors of the previous step (Scell%Ha0, saved by construct_TB_H_* as
+ *      `Ha0 = Ha`, TB_NRL.f90:88): xtb_save_eigen_prev copies the context's current eigenvectors device-to-device,
+ *      xtb_set_eigen_prev uploads a host Ha0(N,N).  xtb_coupling: kind_M = -1 -> the `case(-1)` arm, anything else ->
+ *      Tully's expression (default arm); the overlap matrix is the block-sparse S of the last xtb_assemble_HS /
+ *      xtb_assemble_blocks (all atoms), absent for the orthogonal branch.  Mij(N,N) host copy optional (NULL = device only).
+ *      Not partitioned: in a multi-GPU run every rank that calls it computes the whole matrix. */
+int  xtb_save_eigen_prev(xtb_ctx*);
+int  xtb_set_eigen_prev (xtb_ctx*, const double* Ha0);
+int  xtb_coupling       (xtb_ctx*, int kind_M, double* Mij);
+
 /* ---- introspection / zero-copy interop (device pointers valid until the producing stage
  *      is re-run or the context destroyed) ------------------------------------------- */
 #define XTB_BUF_H        1   /* dense H_non (N,N) */
@@ -204,6 +215,7 @@ int  xtb_repulsive_pressure(xtb_ctx*, double SCforce_rep[9]);
 #define XTB_BUF_HBLK    10   /* block-sparse H [n_blocks][n_orb*n_orb] (eV) */
 #define XTB_BUF_SBLK    11   /* block-sparse S */
 #define XTB_BUF_FREP    12   /* (3,na) repulsive forces */
+#define XTB_BUF_MIJ     13   /* (N,N) coupling matrix of the last xtb_coupling */
 int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
  *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,
@@ -212,7 +224,7 @@ long long xtb_counter(const xtb_ctx*, int which);
 /* device time [ms] of the last run of a stage (CUDA events on the context stream):
  * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure,
  * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3), 8 xtb_eigensolve,
- * 9 repulsive energy + forces, 10 repulsive pressure, 11 xtb_coupling */
+ * 9 repulsive energy + forces, 10 repulsive pressure, 11 xtb_coupling (12 / 13: its norms + S*Ha part / its DGEMM) */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 
 #ifdef __cplusplus

@@ -12,7 +12,7 @@ LIB_PATH = os.path.join(_HERE, "libxtb_b200.so")
 XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE = range(7)
 XTB_TB_NONE, XTB_TB_NRL, XTB_TB_PETTIFOR, XTB_TB_DFTB = range(4)
 
-BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK, BUF_FREP = range(1, 13)
+BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK, BUF_FREP, BUF_MIJ = range(1, 14)
 CNT_NA, CNT_NORB, CNT_N, CNT_MAXNN, CNT_NBLOCKS, CNT_NPAIRS, CNT_LAUNCHES, CNT_KKEPT, CNT_CAP = range(9)
 STAGE_NEIGH, STAGE_ASSEMBLE, STAGE_DENSITY, STAGE_FORCES, STAGE_PRESSURE = range(1, 6)
 STAGE_REP_FORCES, STAGE_REP_PRESSURE, STAGE_COUPLING = 9, 10, 11
@@ -139,6 +139,9 @@ SIGNATURES = {
     "xtb_repulsive_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
     "xtb_repulsive_forces": (C.c_int, [C.c_void_p, _pd]),
     "xtb_repulsive_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_save_eigen_prev": (C.c_int, [C.c_void_p]),
+    "xtb_set_eigen_prev": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_coupling": (C.c_int, [C.c_void_p, C.c_int, _pd]),
     "xtb_device_buffer": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
     "xtb_counter": (C.c_longlong, [C.c_void_p, C.c_int]),
     "xtb_stage_ms": (C.c_double, [C.c_void_p, C.c_int]),

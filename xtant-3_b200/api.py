@@ -10,6 +10,7 @@ procedures they stand in for (same argument meaning, results in the reference's 
     get_dHij_drij_NRL / dHij_s     TB_NRL.f90:2412, TB_Pettifor.f90:141               (-> forces)
     Attract_TB_Forces_Press_NRL / Attract_TB_Forces_Press  TB_NRL.f90:2742, TB_Pettifor.f90:1134 (-> pressure)
     get_Erep_s / dErdr_s / dErdr_Pressure_s   TB_Pettifor.f90:2074,2162,2634        (same names)
+    Electron_ion_coupling_Mij      Nonadiabatic.f90:782                               (same name)
 
 Errors: every non-zero ABI status raises XtbError(code, text) -- the reference records
 (Save_error_details) and continues; a Python caller gets an exception instead.
@@ -256,3 +257,23 @@ class TBContext:
         rep = np.zeros(9)
         self._ck(self.lib.xtb_repulsive_pressure(self.h, _dp(rep)))
         return rep.reshape(3, 3, order="F")
+
+    # -- nonadiabatic coupling matrix -------------------------------------
+    def save_eigen_prev(self):
+        """Scell%Ha0 = Scell%Ha (TB_NRL.f90:88), device to device"""
+        self._ck(self.lib.xtb_save_eigen_prev(self.h))
+
+    def set_eigen_prev(self, Ha0):
+        Ha0 = np.asfortranarray(Ha0, dtype=np.float64)
+        self._ck(self.lib.xtb_set_eigen_prev(self.h, _dp(Ha0)))
+
+    def Electron_ion_coupling_Mij(self, kind_M=0, to_host=True):
+        """Electron_ion_coupling_Mij(wr, Ha, Ha0, Mij, kind_M, Sij), Nonadiabatic.f90:782: Ha = current eigenvectors of the
+        context, Ha0 = save_eigen_prev / set_eigen_prev, Sij = the assembled overlap (absent for the orthogonal branch)."""
+        if not to_host:
+            self._ck(self.lib.xtb_coupling(self.h, int(kind_M), None))
+            return None
+        N = self.na * self.n_orb
+        M = np.zeros((N, N), order="F")
+        self._ck(self.lib.xtb_coupling(self.h, int(kind_M), _dp(M)))
+        return M

@@ -1,0 +1,175 @@
+// Nonadiabatic electron-ion coupling matrix.
+//
+// Replaces Electron_ion_coupling_Mij (Source_files/Nonadiabatic.f90:782-945):
+//   psi0_i = Ha0(:,i)/|Ha0(:,i)|, psi_j = Ha(:,j)/|Ha(:,j)|  (Euclidean norms, 0 when < 1e-13, :812-826)
+//   tij(j,:) = S psi_j                                          (:829-842, only with an overlap matrix)
+//   Tully (default arm, :876-938):  Mij(i<j) = 1/2 [ psi0_i . S psi_j - psi0_j . S psi_i ],  Mij(j,i) = Mij(i,j), Mij(i,i) = 0
+//   kind_M = -1 (:816-874):         Mij(i<j) = psi0_i . S psi_j,                              Mij(j,i) = Mij(i,j)
+// Reference data flow: tij is N^2 dot products of length N against the DENSE Sij (an un-blocked N^3 loop nest), then
+// N^2/2 more dot products of length N -- 2 N^3 multiply-adds in scalar loops.
+// Here:  T = S Ha with S taken BLOCK-SPARSE from the S2 block store (2*81*B*N flop instead of 2 N^3: 50x fewer at the
+//        north-star size), G = Ha0^T T as one library DGEMM (a plain dense GEMM: cuBLAS, bound at run time in eigen.cu),
+//        and one in-place tile-pair kernel that applies the norms, antisymmetrises and mirrors (HBM-bound, N^2 doubles
+//        read and written once).  Normalisation is applied to G(i,j) instead of to the vectors (same value up to rounding).
+#include "xtb_ctx.h"
+
+namespace {
+
+constexpr int CT = 256;
+
+// inv[n] = 1/|A(:,n)| (0 when the norm is below eps); one CTA per column, fixed-order tree
+__global__ void __launch_bounds__(CT) col_invnorm_kernel(long long N, const double* __restrict__ A, double eps, double* __restrict__ inv) {
+    __shared__ double buf[CT];
+    const double* col = A + (size_t)N * blockIdx.x;
+    double s = 0.0;
+    for (long long r = threadIdx.x; r < N; r += CT) { const double v = col[r]; s += v * v; }
+    buf[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = CT / 2; off > 0; off >>= 1) {
+        if (threadIdx.x < off) buf[threadIdx.x] += buf[threadIdx.x + off];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const double nr = sqrt(buf[0]);
+        inv[blockIdx.x] = nr < eps ? 0.0 : 1.0 / nr;
+    }
+}
+
+// T(rows of atom j, n) = sum_{q} blk(j,q)^T C(rows of atom i_q, n);  blk(j,q)(mu,nu) = S(i_q mu, j nu)  (block store of S2).
+// CTA = (atom j, 2*ST consecutive states); the atom's blocks are staged once in shared memory (stride 82: 16-byte aligned
+// rows), each thread carries two states: 18 accumulators, 81 broadcast LDS per 162 DFMA.
+constexpr int ST = 128;
+template <int NO>
+__global__ void __launch_bounds__(ST) spmm_blocks_kernel(int na, long long N, long long K, int cap, const int* __restrict__ nn_size,
+                                                        const int* __restrict__ nn_list, const int* __restrict__ rowptr,
+                                                        const double* __restrict__ Sblk, const double* __restrict__ Cm,
+                                                        double* __restrict__ T) {
+    extern __shared__ __align__(16) double sb[];
+    constexpr int NB = NO * NO, LD = NB + (NB & 1);
+    const int j = blockIdx.x;
+    const int m = nn_size[j];
+    const double* g = Sblk + (size_t)rowptr[j] * NB;
+    for (int e = threadIdx.x; e < (m + 1) * NB; e += ST) sb[(e / NB) * LD + (e % NB)] = g[e];
+    __syncthreads();
+    const long long n0 = (long long)blockIdx.y * (2 * ST) + threadIdx.x, n1 = n0 + ST;
+    const bool ok0 = n0 < K, ok1 = n1 < K;
+    if (!ok0) return;
+    double a0[NO], a1[NO];
+#pragma unroll
+    for (int nu = 0; nu < NO; ++nu) { a0[nu] = 0.0; a1[nu] = 0.0; }
+    for (int q = 0; q <= m; ++q) {
+        const int i = q == 0 ? j : nn_list[(size_t)j * cap + q - 1];
+        const double* c0 = Cm + (size_t)i * NO + (size_t)N * n0;
+        const double* c1 = Cm + (size_t)i * NO + (size_t)N * (ok1 ? n1 : n0);
+        double x0[NO], x1[NO];
+#pragma unroll
+        for (int mu = 0; mu < NO; ++mu) { x0[mu] = __ldg(c0 + mu); x1[mu] = __ldg(c1 + mu); }
+        const double* b = sb + q * LD;
+#pragma unroll
+        for (int nu = 0; nu < NO; ++nu)
+#pragma unroll
+            for (int mu = 0; mu < NO; ++mu) {
+                const double s = b[mu + NO * nu];
+                a0[nu] = fma(s, x0[mu], a0[nu]);
+                a1[nu] = fma(s, x1[mu], a1[nu]);
+            }
+    }
+    double* t0 = T + (size_t)j * NO + (size_t)N * n0;
+#pragma unroll
+    for (int nu = 0; nu < NO; ++nu) t0[nu] = a0[nu];
+    if (ok1) {
+        double* t1 = T + (size_t)j * NO + (size_t)N * n1;
+#pragma unroll
+        for (int nu = 0; nu < NO; ++nu) t1[nu] = a1[nu];
+    }
+}
+
+// in place on G (N x N, column-major): tile pair (a, b), a <= b, 32 x 32 tiles through shared memory.
+//   g(i,j) = G(i,j) inv0[i] inv1[j];  Tully: M(i,j) = M(j,i) = (g(i,j) - g(j,i))/2 for i < j;  kind -1: M(i,j) = M(j,i) = g(i,j);  M(i,i) = 0
+__global__ void __launch_bounds__(256) antisym_kernel(long long N, int kind, const double* __restrict__ inv0,
+                                                     const double* __restrict__ inv1, double* __restrict__ G) {
+    __shared__ double U[32][33], L[32][33];
+    const int a = blockIdx.x, b = blockIdx.y;                     // tile pair, a <= b
+    if (a > b) return;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;       // 32 x 8
+    const long long r0 = 32LL * a, c0 = 32LL * b;
+    for (int yy = ty; yy < 32; yy += 8) {
+        const long long iu = r0 + tx, ju = c0 + yy;                // upper tile element G(iu, ju)
+        U[yy][tx] = (iu < N && ju < N) ? G[iu + N * ju] * inv0[iu] * inv1[ju] : 0.0;
+        const long long il = c0 + tx, jl = r0 + yy;                // lower tile element G(il, jl)
+        L[yy][tx] = (il < N && jl < N) ? G[il + N * jl] * inv0[il] * inv1[jl] : 0.0;
+    }
+    __syncthreads();
+    for (int yy = ty; yy < 32; yy += 8) {
+        // upper tile position (i = r0 + tx, j = c0 + yy): g(i,j) = U[yy][tx], g(j,i) = L[tx][yy]
+        {
+            const long long i = r0 + tx, j = c0 + yy;
+            if (i < N && j < N) {
+                double v;
+                if (i == j) v = 0.0;
+                else if (i < j) v = kind == -1 ? U[yy][tx] : 0.5 * (U[yy][tx] - L[tx][yy]);
+                else v = kind == -1 ? L[tx][yy] : 0.5 * (L[tx][yy] - U[yy][tx]);      // diagonal tile, below the diagonal
+                G[i + N * j] = v;
+            }
+        }
+        if (a != b) {   // lower tile position (i = c0 + tx, j = r0 + yy), always i > j: M(i,j) = M(j,i), pair (j,i) sits in U[tx][yy]
+            const long long i = c0 + tx, j = r0 + yy;
+            if (i < N && j < N) G[i + N * j] = kind == -1 ? U[tx][yy] : 0.5 * (U[tx][yy] - L[yy][tx]);
+        }
+    }
+}
+
+}  // namespace
+
+int xtb_impl_coupling(xtb_ctx* c, int kind_M) {
+    const long long N = (long long)c->na * c->n_orb, K = c->K;
+    if (K != N) XTB_FAIL(c, XTB_EINVAL, "xtb_coupling: needs all N = %lld states (have %lld)", N, K);
+    if (N > 46000) XTB_FAIL(c, XTB_EINVAL, "xtb_coupling: N = %lld exceeds the 32-bit leading dimension of cublasDgemm", N);
+    const bool ortho = c->tb == XTB_TB_PETTIFOR;
+    const size_t nn = (size_t)N * N;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_cpl_M, sizeof(double) * nn))) return rc;
+    if ((rc = xtb_reserve(c, c->d_cpl_inv, sizeof(double) * 2 * N))) return rc;
+    if (!ortho && (rc = xtb_reserve(c, c->d_cpl_T, sizeof(double) * nn))) return rc;
+    double* inv0 = (double*)c->d_cpl_inv.p; double* inv1 = inv0 + N;
+    const double* Ha0 = (const double*)c->d_Ha0.p;
+    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    col_invnorm_kernel<<<(unsigned)N, CT, 0, c->stream>>>(N, Ha0, 1.0e-13, inv0);        // Norm0, eps  :812,:883
+    XTB_LAUNCH_CHECK(c);
+    col_invnorm_kernel<<<(unsigned)N, CT, 0, c->stream>>>(N, c->d_Ha, 1.0e-13, inv1);    // Norm1       :884
+    XTB_LAUNCH_CHECK(c);
+    const double* Tm = c->d_Ha;                                    // orthogonal basis: S = 1
+    if (!ortho) {
+        const dim3 grid((unsigned)c->na, (unsigned)((K + 2 * ST - 1) / (2 * ST)));
+        const size_t smem = sizeof(double) * (size_t)(c->max_nn + 1) * 82;
+        if (c->n_orb == 9) {
+            XTB_CUDA(c, cudaFuncSetAttribute(spmm_blocks_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            spmm_blocks_kernel<9><<<grid, ST, smem, c->stream>>>(c->na, N, K, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                                  (const int*)c->d_rowptr.p, (const double*)c->d_Sblk.p, c->d_Ha, (double*)c->d_cpl_T.p);
+        } else if (c->n_orb == 4) {
+            XTB_CUDA(c, cudaFuncSetAttribute(spmm_blocks_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            spmm_blocks_kernel<4><<<grid, ST, smem, c->stream>>>(c->na, N, K, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                                  (const int*)c->d_rowptr.p, (const double*)c->d_Sblk.p, c->d_Ha, (double*)c->d_cpl_T.p);
+        } else {
+            spmm_blocks_kernel<1><<<grid, ST, smem, c->stream>>>(c->na, N, K, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                                  (const int*)c->d_rowptr.p, (const double*)c->d_Sblk.p, c->d_Ha, (double*)c->d_cpl_T.p);
+        }
+        XTB_LAUNCH_CHECK(c);
+        Tm = (const double*)c->d_cpl_T.p;
+    }
+    XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+    if ((rc = xtb_blas_dgemm(c, true, false, (int)N, (int)N, (int)N, Ha0, (int)N, Tm, (int)N, (double*)c->d_cpl_M.p, (int)N))) return rc;   // G = Ha0^T T
+    XTB_CUDA(c, cudaEventRecord(c->ev_mid2, c->stream));
+    const unsigned nt = (unsigned)((N + 31) / 32);
+    antisym_kernel<<<dim3(nt, nt), 256, 0, c->stream>>>(N, kind_M == -1 ? -1 : 0, inv0, inv1, (double*)c->d_cpl_M.p);
+    XTB_LAUNCH_CHECK(c);
+    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0.f, ms_spmm = 0.f, ms_gemm = 0.f;
+    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+    cudaEventElapsedTime(&ms_spmm, c->ev0, c->ev_mid);
+    cudaEventElapsedTime(&ms_gemm, c->ev_mid, c->ev_mid2);
+    c->stage_ms[11] = ms;
+    c->coupling_spmm_ms = ms_spmm; c->coupling_gemm_ms = ms_gemm;
+    return XTB_OK;
+}

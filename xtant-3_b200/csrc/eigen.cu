@@ -116,6 +116,17 @@ int syevd(xtb_ctx* c, int n, double* A, double* W, std::string what) {
 
 }  // namespace
 
+// C = op(A) op(B) through the run-time bound cuBLAS (plain library GEMM; also used by coupling.cu)
+int xtb_blas_dgemm(xtb_ctx* c, bool ta, bool tb, int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* Cm, int ldc) {
+    if (!bind_libs()) XTB_FAIL(c, XTB_ESTATE, "cuBLAS not available: %s", g_libs.why.c_str());
+    Libs& L = g_libs;
+    L.bl_stream(L.bl, c->stream);
+    const double one = 1.0, zero = 0.0;
+    if (L.bl_dgemm(L.bl, ta ? OP_T : OP_N, tb ? OP_T : OP_N, m, n, k, &one, A, lda, B, ldb, &zero, Cm, ldc) != 0)
+        XTB_FAIL(c, XTB_ECUDA, "cublasDgemm failed (m=%d n=%d k=%d)", m, n, k);
+    return XTB_OK;
+}
+
 int xtb_impl_eigensolve(xtb_ctx* c) {
     if (!bind_libs()) XTB_FAIL(c, XTB_ESTATE, "xtb_eigensolve: %s", g_libs.why.c_str());
     Libs& L = g_libs;

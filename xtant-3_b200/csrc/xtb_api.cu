@@ -64,7 +64,7 @@ int xtb_destroy(xtb_ctx* c) {
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
                      &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
-                     &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep};
+                     &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep};
     for (DevBuf* b : all) xtb_free(*b);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -489,6 +489,53 @@ int xtb_pressure(xtb_ctx* c, double* SCforce_att) {
     return XTB_OK;
 }
 
+// ---- nonadiabatic coupling ----
+int xtb_save_eigen_prev(xtb_ctx* c) {
+    if (!c) return XTB_EINVAL;
+    if (!c->d_Ha) XTB_FAIL(c, XTB_ESTATE, "xtb_save_eigen_prev: no eigenvectors on the device");
+    cudaSetDevice(c->device);
+    const size_t N = (size_t)c->na * c->n_orb;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_Ha0, sizeof(double) * N * N))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_Ha0.p, c->d_Ha, sizeof(double) * N * N, cudaMemcpyDeviceToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_Ha0 = true;
+    return XTB_OK;
+}
+
+int xtb_set_eigen_prev(xtb_ctx* c, const double* Ha0) {
+    if (!c) return XTB_EINVAL;
+    if (!Ha0) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen_prev: null pointer");
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_eigen_prev: no system set");
+    cudaSetDevice(c->device);
+    const size_t N = (size_t)c->na * c->n_orb;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_Ha0, sizeof(double) * N * N))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_Ha0.p, Ha0, sizeof(double) * N * N, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_Ha0 = true;
+    return XTB_OK;
+}
+
+int xtb_coupling(xtb_ctx* c, int kind_M, double* Mij) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->d_Ha) XTB_FAIL(c, XTB_ESTATE, "xtb_coupling: no eigenvectors on the device (xtb_set_eigen / xtb_eigensolve first)");
+    if (!c->have_Ha0) XTB_FAIL(c, XTB_ESTATE, "xtb_coupling: no previous-step eigenvectors (xtb_save_eigen_prev / xtb_set_eigen_prev first)");
+    if (c->tb != XTB_TB_PETTIFOR) {
+        if (!c->have_blocks) XTB_FAIL(c, XTB_ESTATE, "xtb_coupling: no overlap blocks on the device (xtb_assemble_HS first)");
+        if (c->a0 != 0 || c->a1 != c->na) XTB_FAIL(c, XTB_EINVAL, "xtb_coupling: needs the overlap blocks of all atoms (not partitioned)");
+    }
+    int rc = xtb_impl_coupling(c, kind_M);
+    if (rc) return rc;
+    if (Mij) {
+        const size_t N = (size_t)c->na * c->n_orb;
+        XTB_CUDA(c, cudaMemcpyAsync(Mij, c->d_cpl_M.p, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
 // ---- repulsive pair terms ----
 static int rep_ready(xtb_ctx* c, const char* who) {
     if (c->tb != XTB_TB_PETTIFOR || c->h_pet_rep.empty()) XTB_FAIL(c, XTB_ESTATE, "%s: no repulsive parameters (xtb_set_params_pettifor_rep)", who);
@@ -553,6 +600,7 @@ int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
         case XTB_BUF_HBLK: b = &c->d_Hblk; used = 8 * nb2 * (size_t)c->n_blocks; break;
         case XTB_BUF_SBLK: b = &c->d_Sblk; used = 8 * nb2 * (size_t)c->n_blocks; break;
         case XTB_BUF_FREP: b = &c->d_Frep; used = 24 * (size_t)c->na; break;
+        case XTB_BUF_MIJ: b = &c->d_cpl_M; used = 8 * N * N; break;
         default: XTB_FAIL(c, XTB_EINVAL, "xtb_device_buffer: unknown buffer %d", which);
     }
     if (!b->p) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: buffer %d not produced yet", which);
@@ -580,8 +628,10 @@ long long xtb_counter(const xtb_ctx* c, int which) {
 }
 
 double xtb_stage_ms(const xtb_ctx* c, int stage) {
-    if (!c || stage < 1 || stage > 11) return -1.0;
+    if (!c || stage < 1 || stage > 13) return -1.0;
     if (stage == 8) return c->eigen_ms;
+    if (stage == 12) return c->coupling_spmm_ms;
+    if (stage == 13) return c->coupling_gemm_ms;
     return c->stage_ms[stage];
 }
 

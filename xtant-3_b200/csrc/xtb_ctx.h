@@ -74,6 +74,10 @@ struct xtb_ctx {
     DevBuf d_F, d_SC, d_scratch, d_hdev, d_ppart, d_tab;
     // repulsive pair terms (pettifor_rep.cu)
     DevBuf d_Epot, d_dfpsi, d_Erep, d_Frep, d_SCrep;
+    // nonadiabatic coupling (coupling.cu): eigenvectors of the previous step, T = S Ha, G -> Mij, inverse column norms
+    DevBuf d_Ha0, d_cpl_T, d_cpl_M, d_cpl_inv;
+    bool have_Ha0 = false;
+    double coupling_spmm_ms = 0.0, coupling_gemm_ms = 0.0;
     // timing
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mid = nullptr, ev_mid2 = nullptr;
     int density_slotcap = 0, density_stages = 0;
@@ -127,6 +131,8 @@ int xtb_impl_pettifor_rep_energy(xtb_ctx* c);      // pettifor_rep.cu
 int xtb_impl_pettifor_rep_forces(xtb_ctx* c);
 int xtb_impl_pettifor_rep_pressure(xtb_ctx* c);
 int xtb_impl_mirror_density(xtb_ctx* c);
+int xtb_impl_coupling(xtb_ctx* c, int kind_M);      // coupling.cu
+int xtb_blas_dgemm(xtb_ctx* c, bool ta, bool tb, int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* Cm, int ldc);
 int xtb_impl_eigensolve(xtb_ctx* c);        // eigen.cu: Loewdin + Dsyevd + back-transform on the device-resident H, S
 int xtb_impl_dftb_assemble(xtb_ctx* c, bool dense);
 int xtb_impl_dftb_forces(xtb_ctx* c);
