@@ -155,27 +155,38 @@ def run_own(args):
     Cm, dE, dfe, E, fe = make_eigen_device(torch, wk, wl, N)
     ctx.set_eigen_device(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
 
+    trace = {} if os.environ.get("XTB_BENCH_PHASES") else None
+
+    def _ph(name, fn):
+        """run one phase; with XTB_BENCH_PHASES=1 also accumulate its synchronised wall time (diagnostic runs only)"""
+        if trace is None:
+            return fn()
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        r = fn()
+        torch.cuda.synchronize(); trace[name] = trace.get(name, 0.0) + (time.perf_counter() - t0) * 1e3
+        return r
+
     def step():
-        ctx.get_near_neighbours_device()
+        _ph("neighbours", ctx.get_near_neighbours_device)
         if world == 1:
-            ctx.assemble_HS(to_host=False)
+            _ph("assemble_HS", lambda: ctx.assemble_HS(to_host=False))
         else:
             # owners compute their H/S blocks; the block ranges are all-gathered over NVLink (0.42 GB in total instead of
             # 21.7 GB of dense panels) and every rank expands the replicated dense H_non, Sij locally for the eigensolve
             ctx.set_partition(a0 + 1, a1)
-            ctx.assemble_blocks()
-            rp = interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy()
-            for which in (abi.BUF_HBLK, abi.BUF_SBLK):
-                mg.allgather_blocks(interop.buffer(ctx, which), rp, na, 81, rank, world)
-            ctx.expand_dense(1, na)
-        ctx.density()
+            _ph("assemble_blocks", ctx.assemble_blocks)
+            rp = _ph("rowptr_d2h", lambda: interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy())
+            _ph("allgather_HS_blocks", lambda: mg.allgather_blocks([interop.buffer(ctx, abi.BUF_HBLK), interop.buffer(ctx, abi.BUF_SBLK)],
+                                                                   rp, na, 81, rank, world))
+            _ph("expand_dense", lambda: ctx.expand_dense(1, na))
+        _ph("density", ctx.density)
         if world > 1:
-            for which in (abi.BUF_RHO, abi.BUF_RHOE):
-                mg.allgather_blocks(interop.buffer(ctx, which), rp, na, 81, rank, world)
-            ctx.density_mirror()
-        ctx.forces_device()
+            _ph("allgather_rho_blocks", lambda: mg.allgather_blocks([interop.buffer(ctx, abi.BUF_RHO), interop.buffer(ctx, abi.BUF_RHOE)],
+                                                                    rp, na, 81, rank, world))
+            _ph("density_mirror", ctx.density_mirror)
+        _ph("forces", ctx.forces_device)
         if world > 1:
-            mg.allgather_forces(interop.buffer(ctx, abi.BUF_FORCES), na, rank, world)
+            _ph("allgather_forces", lambda: mg.allgather_forces(interop.buffer(ctx, abi.BUF_FORCES), na, rank, world))
 
     def sync_all():
         torch.cuda.synchronize()
@@ -206,6 +217,8 @@ def run_own(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     n_blocks, n_pairs, k_kept = ctx.counter(4), ctx.counter(5), ctx.counter(7)
+    if trace is not None:
+        print(f"[phases rank {rank}] " + json.dumps({k: round(v / (args.steps + args.warmup), 3) for k, v in trace.items()}), file=sys.stderr)
 
     out = None
     if rank == 0:
@@ -373,14 +386,12 @@ def run_e2e_multi(torch, ctx, wl, E, fe, world, rank, a0, a1, args):
         ctx._ck(lib.xtb_set_partition(hnd, a0 + 1, a1))
         ctx._ck(lib.xtb_assemble_blocks(hnd))
         rp = interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy()
-        for which in (abi.BUF_HBLK, abi.BUF_SBLK):
-            mg.allgather_blocks(interop.buffer(ctx, which), rp, na, 81, rank, world)
+        mg.allgather_blocks([interop.buffer(ctx, abi.BUF_HBLK), interop.buffer(ctx, abi.BUF_SBLK)], rp, na, 81, rank, world)
         ctx._ck(lib.xtb_expand_dense(hnd, 1, na, None, None))
         ctx._ck(lib.xtb_get_eigenvalues(hnd, api._dp(Ei_host)))                             # D2H: Ei
         ctx._ck(lib.xtb_set_occupations(hnd, api._dp(fh)))                                  # H2D: fe
         ctx._ck(lib.xtb_density(hnd, None, None))
-        for which in (abi.BUF_RHO, abi.BUF_RHOE):
-            mg.allgather_blocks(interop.buffer(ctx, which), rp, na, 81, rank, world)
+        mg.allgather_blocks([interop.buffer(ctx, abi.BUF_RHO), interop.buffer(ctx, abi.BUF_RHOE)], rp, na, 81, rank, world)
         ctx._ck(lib.xtb_density_mirror(hnd))
         ctx._ck(lib.xtb_forces(hnd, api._dp(Fh)))                                           # D2H: owned forces
         mg.allgather_forces(interop.buffer(ctx, abi.BUF_FORCES), na, rank, world)

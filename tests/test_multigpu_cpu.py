@@ -41,6 +41,11 @@ def _worker(rank, world, port, na, n_orb, seed, out):
         F = torch.full((3 * na,), np.nan, dtype=torch.float64)
         F[3 * a0:3 * a1] = torch.from_numpy(full_F[3 * a0:3 * a1])
         mg.allgather_blocks(blocks, rowptr, na, nb2, rank, world)
+        # two block stores in one collective (H and S / rho and rho_E)
+        pair = [torch.full((full_blocks.size,), np.nan, dtype=torch.float64) for _ in range(2)]
+        pair[0][b0:b1] = torch.from_numpy(full_blocks[b0:b1]); pair[1][b0:b1] = torch.from_numpy(-2.0 * full_blocks[b0:b1])
+        mg.allgather_blocks(pair, rowptr, na, nb2, rank, world)
+        assert np.array_equal(pair[0].numpy(), full_blocks) and np.array_equal(pair[1].numpy(), -2.0 * full_blocks)
         mg.allgather_panels(dense, na, n_orb, rank, world)
         mg.allgather_forces(F, na, rank, world)
         P = torch.arange(9, dtype=torch.float64) * (rank + 1)

@@ -79,10 +79,21 @@ __global__ void pad_weights_kernel(int nkeep, int kpad, double* __restrict__ wf,
 // HBM-bound (8*N*K bytes in, the same out): every thread keeps KC independent 128-bit loads in flight, the transpose
 // goes through shared memory with a row pitch that makes both phases conflict-free, stores are 128-bit and coalesced.
 constexpr int CT_THREADS = 160;
+// partitioned run: groups of CT_AT atoms whose tiles some owned atom reads (itself or a neighbour).  Benign race: all write 1.
+__global__ void need_groups_kernel(int a0, int a1, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
+                                   int* __restrict__ need) {
+    const int k = a0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= a1) return;
+    need[k / CT_AT] = 1;
+    const int m = nn_size[k];
+    for (int q = 0; q < m; ++q) need[nn_list[(size_t)k * cap + q] / CT_AT] = 1;
+}
 template <int NO>
 __global__ void __launch_bounds__(CT_THREADS) ct_tile_kernel(int na, long long N, int nkeep, const int* __restrict__ keep,
+                                                            const int* __restrict__ need /*per atom group, or null = all*/,
                                                             const double* __restrict__ Ha, double* __restrict__ Ct) {
     constexpr int AT = CT_AT;
+    if (need && !need[blockIdx.y]) return;           // partitioned run: no owned atom reads the tiles of this group
     constexpr int P = AT * NO + 4;                   // pitch = 4 mod 8: the 64-bit banks of (t, t+2) x 8 rows are disjoint
     __shared__ __align__(16) double tile[KC][P];
     __shared__ long long colbase[KC];
@@ -585,7 +596,16 @@ int run_density(xtb_ctx* c) {
         if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)kpad * N + 1024))) return rc;
         if (nchunks > 0) {
             dim3 grid(nchunks, (na + CT_AT - 1) / CT_AT);
-            ct_tile_kernel<NO><<<grid, CT_THREADS, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, c->d_Ha, (double*)c->d_Ct.p);
+            const int* need = nullptr;
+            if (nown < na) {      // re-tile only what the owned atoms read (own rows + halo)
+                if ((rc = xtb_reserve(c, c->d_ctneed, sizeof(int) * grid.y))) return rc;
+                XTB_CUDA(c, cudaMemsetAsync(c->d_ctneed.p, 0, sizeof(int) * grid.y, c->stream));
+                need_groups_kernel<<<(nown + 127) / 128, 128, 0, c->stream>>>(c->a0, c->a1, c->cap, (const int*)c->d_nn_size.p,
+                                                                             (const int*)c->d_nn_list.p, (int*)c->d_ctneed.p);
+                XTB_LAUNCH_CHECK(c);
+                need = (const int*)c->d_ctneed.p;
+            }
+            ct_tile_kernel<NO><<<grid, CT_THREADS, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, need, c->d_Ha, (double*)c->d_Ct.p);
             XTB_LAUNCH_CHECK(c);
         }
         XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));

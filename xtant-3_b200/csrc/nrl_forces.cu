@@ -19,6 +19,7 @@
 // streamed with 128-bit loads; one thread per (neighbour, matrix, direction) differentiates the
 // Slater-Koster block in registers (forward-mode dual numbers) and contracts it; partial sums are
 // reduced in shared memory in list order.
+#include <cstdlib>
 #include "nrl_device.cuh"
 #include "sk_device.cuh"
 
@@ -74,7 +75,8 @@ __device__ __forceinline__ void dblock_upper(const double* V, const double* dV, 
 constexpr int FT = 256;
 
 // ---- forces: one CTA per owned atom k ----
-__global__ void __launch_bounds__(FT) nrl_forces_kernel(int na, int a0, int cap, int mx, int n_kinds, const int* __restrict__ koa,
+template <int MINB>
+__global__ void __launch_bounds__(FT, MINB) nrl_forces_kernel(int na, int a0, int cap, int mx, int n_kinds, const int* __restrict__ koa,
                                                        const int* __restrict__ nn_size, const int* __restrict__ nn_list,
                                                        const int* __restrict__ rev, const double* __restrict__ nn_dist,
                                                        const int* __restrict__ rowptr, const xtb_nrl_pair* __restrict__ TB,
@@ -303,10 +305,13 @@ int xtb_impl_nrl_forces(xtb_ctx* c) {
         const int mx = c->max_nn > 0 ? c->max_nn : 1;
         const size_t small = sizeof(double) * ((size_t)mx * 11 + 2);
         const size_t big = small + sizeof(double) * (((size_t)(mx + 1) * 81 + 1) * 2);
-        const int stage_blocks = big <= 200 * 1024 ? 1 : 0;      // else read the blocks straight from L2
+        const char* ev = getenv("XTB_FORCES_MODE");              // experiments: 0 = staged blocks, 1 CTA/SM; 1 = direct reads, 2 CTAs/SM
+        const int mode = ev ? atoi(ev) : 1;
+        const int stage_blocks = (mode == 0 && big <= 200 * 1024) ? 1 : 0;      // else read the blocks straight from L1 / L2
         const size_t smem = stage_blocks ? big : small;
-        XTB_CUDA(c, cudaFuncSetAttribute(nrl_forces_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        nrl_forces_kernel<<<nown, FT, smem, c->stream>>>(c->na, c->a0, c->cap, mx, c->n_kinds, (const int*)c->d_koa.p,
+        auto kern = mode == 0 ? nrl_forces_kernel<1> : nrl_forces_kernel<2>;
+        XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<nown, FT, smem, c->stream>>>(c->na, c->a0, c->cap, mx, c->n_kinds, (const int*)c->d_koa.p,
                                                          (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, (const int*)c->d_rev.p,
                                                          (const double*)c->d_nn_dist.p, (const int*)c->d_rowptr.p,
                                                          (const xtb_nrl_pair*)c->d_params.p, (const double*)c->d_hdev.p,

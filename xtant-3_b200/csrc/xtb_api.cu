@@ -64,7 +64,7 @@ int xtb_destroy(xtb_ctx* c) {
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
                      &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
-                     &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep};
+                     &c->d_ctneed, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep};
     for (DevBuf* b : all) xtb_free(*b);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
     if (c->own_stream) cudaStreamDestroy(c->stream);

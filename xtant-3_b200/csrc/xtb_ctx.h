@@ -68,6 +68,7 @@ struct xtb_ctx {
     DevBuf d_keep, d_wf, d_wfe, d_Ct, d_nkeep;   // kept state indices, weights, tiled transposed C
     long long k_kept = 0;
     DevBuf d_rho, d_rhoE;       // block-sparse [n_blocks][n_orb^2]
+    DevBuf d_ctneed;            // partitioned run: atom groups whose eigenvector tiles are re-tiled
     DevBuf d_prog;              // density kernel: per-CTA progress counters (lock-step throttle)
     bool have_density = false;
     // forces / pressure

@@ -30,16 +30,32 @@ def ranges(na, world):
     return [partition(na, world, r) for r in range(world)]
 
 
-def _gather_segments(buf, segs, rank, group=None):
-    """in-place all-gather of variable-length contiguous segments of the 1-D tensor `buf`:
-    rank r owns buf[segs[r][0]:segs[r][1]]; afterwards every rank holds all segments.
-    Equal lengths that tile the buffer use one all_gather_into_tensor; otherwise a padded all_gather."""
+_scratch = {}
+
+
+def _scratch_buf(key, n, like):
+    t = _scratch.get(key)
+    if t is None or t.numel() < n or t.device != like.device or t.dtype != like.dtype:
+        t = torch.empty(n, dtype=like.dtype, device=like.device)
+        _scratch[key] = t
+    return t[:n]
+
+
+def _gather_segments(bufs, segs, rank, group=None):
+    """in-place all-gather of variable-length contiguous segments of the 1-D tensors `bufs` (one tensor or a list of
+    tensors sharing the same segmentation): rank r owns buf[segs[r][0]:segs[r][1]] of every buffer; afterwards every rank
+    holds all segments.  ONE collective for all buffers: equal lengths that tile a single buffer gather in place;
+    otherwise the segments are packed into a flat send buffer of max-length slots, gathered with
+    all_gather_into_tensor, and the foreign segments copied out."""
+    if isinstance(bufs, torch.Tensor):
+        bufs = [bufs]
     world = len(segs)
     if world == 1:
         return
     lens = [e - b for b, e in segs]
     contiguous = all(segs[r][1] == segs[r + 1][0] for r in range(world - 1))
-    if len(set(lens)) == 1 and lens[0] > 0 and contiguous:
+    if len(bufs) == 1 and len(set(lens)) == 1 and lens[0] > 0 and contiguous:
+        buf = bufs[0]
         b0, e1 = segs[0][0], segs[-1][1]
         mine = buf[segs[rank][0]:segs[rank][1]].clone()
         dist.all_gather_into_tensor(buf[b0:e1], mine, group=group)
@@ -47,19 +63,24 @@ def _gather_segments(buf, segs, rank, group=None):
     mx = max(lens)
     if mx == 0:
         return
-    send = torch.zeros(mx, dtype=buf.dtype, device=buf.device)
+    nb = len(bufs)
+    send = _scratch_buf(("send", nb), nb * mx, bufs[0])
+    recv = _scratch_buf(("recv", nb), world * nb * mx, bufs[0])
     b, e = segs[rank]
-    send[:e - b] = buf[b:e]
-    recv = [torch.empty(mx, dtype=buf.dtype, device=buf.device) for _ in range(world)]
-    dist.all_gather(recv, send, group=group)
+    for k, buf in enumerate(bufs):
+        send[k * mx:k * mx + (e - b)] = buf[b:e]          # the tail of a short slot is never read back
+    dist.all_gather_into_tensor(recv, send, group=group)
     for r, (b, e) in enumerate(segs):
         if r != rank and e > b:
-            buf[b:e] = recv[r][:e - b]
+            for k, buf in enumerate(bufs):
+                o = (r * nb + k) * mx
+                buf[b:e] = recv[o:o + (e - b)]
 
 
 def allgather_blocks(blocks, rowptr, na, nb2, rank, world, group=None):
-    """blocks: 1-D tensor [n_blocks * nb2] (block store); rank r owns the blocks of its atoms, i.e. the contiguous
-    range rowptr[a0] .. rowptr[a1].  rowptr: host sequence / tensor of length na + 1."""
+    """blocks: 1-D tensor [n_blocks * nb2] (block store) or a list of such tensors (H and S, or rho and rho_E: one
+    collective for the pair); rank r owns the blocks of its atoms, i.e. the contiguous range rowptr[a0] .. rowptr[a1].
+    rowptr: host sequence / tensor of length na + 1."""
     segs = [(int(rowptr[a0]) * nb2, int(rowptr[a1]) * nb2) for a0, a1 in ranges(na, world)]
     _gather_segments(blocks, segs, rank, group)
 
