@@ -1,0 +1,89 @@
+"""Edge cases of the hot path on the GPU (through the C ABI), each against the oracle:
+isolated atoms (empty neighbour lists), a single atom, a ragged cell where the neighbour capacity has to grow between
+two calls on the same context, a very small cell where an atom meets several periodic images (the reference keeps the
+single minimum image, overwrite semantics), and an empty owned range in a partitioned run."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _step(c, o, wl, orc, tolF=1e-9):
+    g = c.get_near_neighbours()
+    np.testing.assert_array_equal(g["size"], o["nb"].size)
+    H, S = c.assemble_HS()
+    assert np.abs(H - o["H"]).max() <= 1e-12 * max(1.0, np.abs(o["H"]).max())
+    if S is not None:
+        assert np.abs(S - o["S"]).max() <= 1e-12
+    c.set_eigen(o["Ha"], o["Ei"], o["fe"])
+    c.density()
+    F = c.forces()
+    dF = np.abs(orc.forces_cartesian(F, wl["supce"]) - orc.forces_cartesian(o["F"], wl["supce"])).max()
+    assert dF <= tolF, dF
+    return F
+
+
+def test_isolated_atoms_have_empty_lists(wk, orc, api):
+    S = np.array([[0.1, 0.1, 0.1], [0.6, 0.6, 0.6], [0.1, 0.6, 0.35]])
+    wl = wk._wl("iso3", "nrl", "Au", S, np.diag([40.0, 40.0, 40.0]), 11, 0.1)
+    o = orc.nrl_step(wl, with_pressure=True)
+    assert o["nb"].size.sum() == 0
+    c = api.TBContext(0); c.set_workload(wl)
+    F = _step(c, o, wl, orc)
+    assert not F.any()
+    assert np.abs(c.pressure() - o["P"]).max() <= 1e-12
+    c.close()
+
+
+def test_single_atom(wk, orc, api):
+    wl = wk._wl("one", "pettifor", "C", np.array([[0.3, 0.4, 0.5]]), np.diag([30.0, 30.0, 30.0]), 4, 0.1)
+    o = orc.pettifor_step(wl)
+    c = api.TBContext(0); c.set_workload(wl)
+    F = _step(c, o, wl, orc)
+    assert not F.any()
+    E, Epot = c.get_Erep_s()
+    Eo, _ = orc.pet_erep(wl, o["nb"])
+    assert E == Eo
+    c.close()
+
+
+def test_capacity_grows_on_the_same_context(wk, orc, api):
+    """dilute cell first (small capacity guess), then a dense one with the same atom count"""
+    c = api.TBContext(0)
+    S, h = wk.lattice(wk._FCC, 9.0, (2, 2, 2), 0.0, 0)
+    wl0 = wk._wl("dilute", "nrl", "Au", S, h, 11, 0.1)
+    c.set_workload(wl0)
+    g = c.get_near_neighbours()
+    assert g["size"].max() == 0 or g["size"].max() < 20
+    wl1 = wk.au_fcc((2, 2, 2), sigma=0.1, seed=4)
+    assert wl1["na"] == wl0["na"]
+    o = orc.nrl_step(wl1, with_pressure=False)
+    c.set_system(wl1["koa"], wl1["S"], wl1["supce"])
+    _step(c, o, wl1, orc)
+    c.close()
+
+
+def test_tiny_cell_many_images(wk, orc, api):
+    """1x1x1 fcc Au (4 atoms, a = 4.08 A < cut-off 6.6 A): every pair has several images inside the cut-off; the reference
+    keeps one (Atomic_tools.f90:4080-4131) and so must the library"""
+    wl = wk.au_fcc((1, 1, 1), sigma=0.1, seed=3)
+    o = orc.nrl_step(wl, with_pressure=False)
+    assert o["nb"].size.max() == wl["na"] - 1
+    c = api.TBContext(0); c.set_workload(wl)
+    _step(c, o, wl, orc)
+    c.close()
+
+
+def test_empty_owned_range(wk, api):
+    wl = wk.au_fcc((2, 2, 2), sigma=0.1, seed=4)
+    c = api.TBContext(0); c.set_workload(wl)
+    c.get_near_neighbours_device()
+    c.set_partition(5, 4)                       # first = last + 1: this rank owns nothing
+    c.assemble_blocks()
+    C_, E, fe = wk.synthetic_eigen(wl["na"] * 9, seed=2)
+    c.set_eigen(C_, E, fe)
+    c.density()
+    F = c.forces()
+    assert not F.any()
+    assert not c.pressure().any()
+    c.close()
