@@ -87,3 +87,22 @@ def test_empty_owned_range(wk, api):
     assert not F.any()
     assert not c.pressure().any()
     c.close()
+
+
+def test_split_work_units_give_the_same_blocks(wk, api, monkeypatch):
+    """density kernel with the owned neighbours of an atom split over two CTAs (XTB_DENSITY_SPLIT, used for atoms that need
+    two sub-tasks when the persistent grid has few rounds): same rho / rho_E blocks"""
+    import importlib
+    abi = importlib.import_module("xtant-3_b200._abi"); interop = importlib.import_module("xtant-3_b200.interop")
+    wl = wk.au108()
+    C_, E, fe = wk.synthetic_eigen(wl["na"] * 9, seed=5)
+    res = []
+    for sp in ("1", "2", "3"):
+        monkeypatch.setenv("XTB_DENSITY_SPLIT", sp)
+        c = api.TBContext(0); c.set_workload(wl); c.get_near_neighbours_device(); c.set_eigen(C_, E, fe)
+        c.density()
+        res.append((interop.buffer(c, abi.BUF_RHO).cpu().numpy().copy(), interop.buffer(c, abi.BUF_RHOE).cpu().numpy().copy()))
+        c.close()
+    for r, e in res[1:]:
+        assert np.abs(r - res[0][0]).max() <= 1e-14 * np.abs(res[0][0]).max()
+        assert np.abs(e - res[0][1]).max() <= 1e-14 * np.abs(res[0][1]).max()

@@ -24,6 +24,7 @@
 // Algorithmic flops (roofline numerator): 2 matrices * 2 * n_orb^2 * K_kept * (n_pairs/2 + na).
 #include "xtb_ctx.h"
 #include <cstdint>
+#include <cstdlib>
 
 namespace {
 
@@ -367,7 +368,7 @@ __device__ __forceinline__ void consume_idle(uint32_t stages, uint64_t* full, ui
 
 template <int NO, int NCW, bool DBG>
 __global__ void __launch_bounds__((NCW + 1 + NPROD) * 32, 1)
-density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, int nchunks, int dbg, int maxsub, int lead, long long* __restrict__ prog,
+density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, int nchunks, int dbg, int maxsub, int lead, int split, long long* __restrict__ prog,
                     const int* __restrict__ nn_size, const int* __restrict__ nn_list, const signed char* __restrict__ own,
                     const int* __restrict__ rowptr, const double* __restrict__ Ct, const double* __restrict__ wf,
                     const double* __restrict__ wfe, double* __restrict__ rho, double* __restrict__ rhoE) {
@@ -397,7 +398,10 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
     Ring rg; rg.st = 0; rg.ph = 0;     // running ring position (same sequence in every role)
 
     int round = 0;
-    for (int i = a0 + blockIdx.x; i < a1; i += gridDim.x, ++round) {
+    // work unit = (owned atom, part of its owned neighbours); split > 1 only when the owned range is too short to fill
+    // the persistent grid evenly (few rounds): the unit then costs 1/split of an atom (+ the atom's own tile again)
+    for (int u = blockIdx.x; u < (a1 - a0) * split; u += gridDim.x, ++round) {
+        const int i = a0 + u / split, part = u - (u / split) * split;
         // ---- owned neighbours of i, in list order (warp 0, ordered compaction) ----
         __syncthreads();
         if (warp == 0) {
@@ -413,11 +417,14 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
             if (lane == 0) n_owned_sh = cnt;
         }
         __syncthreads();
-        const int n_owned = n_owned_sh;
+        const int n_all = n_owned_sh;
+        const int per = (n_all + split - 1) / split;
+        const int lo = part * per, n_owned = min(n_all, lo + per);      // this unit: owned neighbours lo .. n_owned-1
+        if (part > 0 && lo >= n_owned) continue;                        // the on-site block belongs to part 0 (uniform per CTA)
         const size_t b0i = (size_t)rowptr[i];
         // ---- sub-tasks of at most slotcap-1 neighbours (slot 0 is always atom i itself) ----
         int sub = 0;
-        for (int first = 0; first == 0 || first < n_owned; first += slotcap - 1, ++sub) {
+        for (int first = lo; first == lo || first < n_owned; first += slotcap - 1, ++sub) {
             const int nn = min(slotcap - 1, n_owned - first);
             const int nslots = nn + 1;
             __syncthreads();
@@ -626,17 +633,22 @@ int run_density(xtb_ctx* c) {
         }
         while (stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages) > budget && slotcap > 2) --slotcap;
         const size_t smem = stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages);
-        int grid = c->sm_count < nown ? c->sm_count : nown;
+        // few rounds on the persistent grid (partitioned runs, small cells) AND atoms that need two sub-tasks anyway (more
+        // owned neighbours than slots, e.g. al500: 88 of 176): give the two halves to different CTAs.  Atoms that fit one
+        // sub-task are NOT split: half the row tiles per warp costs 36 % per unit of work (measured, au4096: 94.6 vs 69.3 ms).
+        int split = (nown < 6 * c->sm_count && nown > c->sm_count / 2 && c->max_nn / 2 >= slotcap - 1) ? 2 : 1;
+        if (const char* ev = getenv("XTB_DENSITY_SPLIT")) { const int v = atoi(ev); if (v >= 1 && v <= 4) split = v; }
+        int grid = c->sm_count < nown * split ? c->sm_count : nown * split;
         if ((rc = xtb_reserve(c, c->d_prog, sizeof(long long) * (size_t)c->sm_count))) return rc;
         XTB_CUDA(c, cudaMemsetAsync(c->d_prog.p, 0, sizeof(long long) * (size_t)c->sm_count, c->stream));
         const int maxsub = slotcap > 1 ? (c->max_nn + slotcap - 2) / (slotcap - 1) + 1 : 1;
-        int a_na = na, a_a0 = c->a0, a_a1 = c->a1, a_cap = c->cap, a_slot = slotcap, a_st = stages, a_nch = nchunks, a_dbg = c->density_dbg, a_ms = maxsub, a_lead = c->density_lead;
+        int a_na = na, a_a0 = c->a0, a_a1 = c->a1, a_cap = c->cap, a_slot = slotcap, a_st = stages, a_nch = nchunks, a_dbg = c->density_dbg, a_ms = maxsub, a_lead = c->density_lead, a_split = split;
         long long* a_prog = (long long*)c->d_prog.p;
         const int* a_sz = (const int*)c->d_nn_size.p; const int* a_li = (const int*)c->d_nn_list.p;
         const signed char* a_own = (const signed char*)c->d_own.p; const int* a_rp = (const int*)c->d_rowptr.p;
         const double* a_ct = (const double*)c->d_Ct.p; const double* a_wf = (const double*)c->d_wf.p; const double* a_wfe = (const double*)c->d_wfe.p;
         double* a_rho = (double*)c->d_rho.p; double* a_rhoE = (double*)c->d_rhoE.p;
-        void* args[] = {&a_na, &a_a0, &a_a1, &a_cap, &a_slot, &a_st, &a_nch, &a_dbg, &a_ms, &a_lead, &a_prog, &a_sz, &a_li, &a_own, &a_rp,
+        void* args[] = {&a_na, &a_a0, &a_a1, &a_cap, &a_slot, &a_st, &a_nch, &a_dbg, &a_ms, &a_lead, &a_split, &a_prog, &a_sz, &a_li, &a_own, &a_rp,
                         &a_ct, &a_wf, &a_wfe, &a_rho, &a_rhoE};
 #define XTB_LAUNCH(W, D) { auto kern = density_dmma_kernel<9, W, D>; \
         XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
