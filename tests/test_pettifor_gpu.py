@@ -79,6 +79,38 @@ def test_density_forces_pressure(case, orc):
     assert np.array_equal(c.forces(), F) and np.array_equal(c.pressure(), P)      # deterministic
 
 
+def test_density_warp_kernel_vs_per_element_kernel(case, orc, api):
+    """n_orb = 4 runs the warp-per-block kernel (density.cu, density_warp_kernel); XTB_DENSITY_IMPL=0 selects the
+    one-thread-per-element cross-check kernel.  Both against the oracle (rho and rho_E), and against each other."""
+    import os
+    wl, o, _ = case
+    nb = o["nb"]
+    mask = (np.arange(nb.cap + 1)[None, :] <= nb.size[:, None])
+    got = {}
+    for impl in (1, 0):
+        os.environ["XTB_DENSITY_IMPL"] = str(impl)
+        try:
+            c = api.TBContext(0)
+        finally:
+            os.environ.pop("XTB_DENSITY_IMPL", None)
+        c.set_workload(wl)
+        c.get_near_neighbours()
+        c.set_eigen(o["Ha"], o["Ei"], o["fe"])
+        A, AE = c.density(dense=True)
+        got[impl] = (A, AE)
+        for M, key in ((A, "rho"), (AE, "rhoE")):
+            g = orc.gather_blocks(nb, 4, M)
+            d = np.abs(g[mask] - o[key][mask]).max()
+            assert d <= 1e-11 * np.abs(o[key][mask]).max(), (impl, key, d)
+        off = np.kron(~np.eye(wl["na"], dtype=bool), np.ones((4, 4), dtype=bool))
+        assert np.array_equal(A[off], A.T[off]) and np.array_equal(AE[off], AE.T[off])
+        A2, AE2 = c.density(dense=True)
+        assert np.array_equal(A, A2) and np.array_equal(AE, AE2)              # deterministic
+        c.close()
+    for a, b in zip(got[1], got[0]):
+        assert np.abs(a - b).max() <= 1e-12 * np.abs(b).max()
+
+
 def test_ac1000_config4(wk, orc, api):
     """config 4 (1000-atom disordered carbon): list bit-exact, H parity on the full cell, forces against the
     sparse oracle for all atoms with oracle eigenvectors."""

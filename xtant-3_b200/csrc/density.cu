@@ -547,6 +547,70 @@ __global__ void __launch_bounds__(128) density_simple_kernel(int na, int a0, int
     rhoE[blk + mu + NO * nu] = e;
 }
 
+// ---------------- small-basis kernel (sp3: Pettifor-type and DFTB sp sets, n_orb <= 4) ----------------
+// One warp per owned block (i, q).  Lanes stride the kept states; the NO rows of atom i and of atom j in one state are
+// NO consecutive doubles of an eigenvector column (one 32-byte sector for NO = 4), so every load instruction of the warp
+// fetches whole sectors (the one-thread-per-element kernel above reads one double per 32-byte sector).  Each lane keeps
+// the 2 x NO x NO partial sums of its states; fixed-order butterfly at the end (same bits on every run).
+// Bound: L2 bandwidth -- 2 * 8 * NO bytes per (block, state) for 4 NO^2 flop; the eigenvectors (8 N K bytes) stay in L2.
+constexpr int DW_WARPS = 4;
+template <int NO>
+__global__ void __launch_bounds__(32 * DW_WARPS) density_warp_kernel(int a0, int a1, int cap, long long N, int nkeep,
+                                                                     const int* __restrict__ keep, const int* __restrict__ nn_size,
+                                                                     const int* __restrict__ nn_list, const signed char* __restrict__ own,
+                                                                     const int* __restrict__ rowptr, const double* __restrict__ Ha,
+                                                                     const double* __restrict__ wf, const double* __restrict__ wfe,
+                                                                     double* __restrict__ rho, double* __restrict__ rhoE) {
+    const int i = a0 + blockIdx.y;
+    const int q = blockIdx.x * DW_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;        // 0 = on-site
+    if (i >= a1 || q > nn_size[i]) return;
+    if (q > 0 && !own[(size_t)i * cap + q - 1]) return;
+    const int j = q == 0 ? i : nn_list[(size_t)i * cap + q - 1];
+    const double* ci = Ha + (size_t)i * NO;
+    const double* cj = Ha + (size_t)j * NO;
+    double s[NO * NO], e[NO * NO];
+#pragma unroll
+    for (int x = 0; x < NO * NO; ++x) { s[x] = 0.0; e[x] = 0.0; }
+    const bool vec = (NO % 2 == 0) && (N % 2 == 0);          // 16-byte aligned rows of an atom in every column
+    for (int kk = lane; kk < nkeep; kk += 32) {
+        const size_t o = (size_t)keep[kk] * N;
+        const double w1 = wf[kk], w2 = wfe[kk];
+        double a[NO], b[NO];
+        if (vec) {
+#pragma unroll
+            for (int m = 0; m < NO / 2; ++m) {
+                const double2 va = __ldg(reinterpret_cast<const double2*>(ci + o) + m);
+                const double2 vb = __ldg(reinterpret_cast<const double2*>(cj + o) + m);
+                a[2 * m] = va.x; a[2 * m + 1] = va.y; b[2 * m] = vb.x; b[2 * m + 1] = vb.y;
+            }
+        } else {
+#pragma unroll
+            for (int m = 0; m < NO; ++m) { a[m] = __ldg(ci + o + m); b[m] = __ldg(cj + o + m); }
+        }
+#pragma unroll
+        for (int mu = 0; mu < NO; ++mu) {
+            const double af = w1 * a[mu], ae = w2 * a[mu];          // Atemp = distre * Ha ; distre * En * Ha   TB.f90:4378,4459
+#pragma unroll
+            for (int nu = 0; nu < NO; ++nu) {
+                s[mu + NO * nu] = fma(af, b[nu], s[mu + NO * nu]);
+                e[mu + NO * nu] = fma(ae, b[nu], e[mu + NO * nu]);
+            }
+        }
+    }
+#pragma unroll
+    for (int x = 0; x < NO * NO; ++x) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            s[x] += __shfl_xor_sync(0xffffffffu, s[x], off);
+            e[x] += __shfl_xor_sync(0xffffffffu, e[x], off);
+        }
+    }
+    const size_t blk = ((size_t)rowptr[i] + q) * (NO * NO);
+#pragma unroll
+    for (int x = 0; x < NO * NO; ++x)
+        if (lane == (x & 31)) { rho[blk + x] = s[x]; rhoE[blk + x] = e[x]; }
+}
+
 // non-owner blocks = transpose of the owner's block
 template <int NO>
 __global__ void mirror_blocks_kernel(int na, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
@@ -657,6 +721,17 @@ int run_density(xtb_ctx* c) {
 #undef XTB_LAUNCH
         XTB_LAUNCH_CHECK(c);
         c->density_slotcap = slotcap; c->density_stages = stages;
+    } else if (nown > 0 && NO <= 4 && c->density_impl == 1) {
+        XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+        if constexpr (NO <= 4) {
+            dim3 grid((c->max_nn + 1 + DW_WARPS - 1) / DW_WARPS, nown);
+            density_warp_kernel<NO><<<grid, 32 * DW_WARPS, 0, c->stream>>>(c->a0, c->a1, c->cap, N, nkeep, (const int*)c->d_keep.p,
+                                                                            (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                                            (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, c->d_Ha,
+                                                                            (const double*)c->d_wf.p, (const double*)c->d_wfe.p,
+                                                                            (double*)c->d_rho.p, (double*)c->d_rhoE.p);
+        }
+        XTB_LAUNCH_CHECK(c);
     } else if (nown > 0) {
         XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
         dim3 grid(c->max_nn + 1, nown);
