@@ -156,6 +156,10 @@ def run_own(args):
     ctx.set_eigen_device(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
 
     trace = {} if os.environ.get("XTB_BENCH_PHASES") else None
+    # N > 1: "replicated" (default; north star: H/S row blocks all-gathered over NVLink to a replicated eigensolve) or
+    # "panels" (variant: every rank writes only the dense column panels of its atoms -- 1-D column-block layout)
+    replicate_dense = os.environ.get("XTB_BENCH_DENSE_LAYOUT", "replicated") != "panels"
+    layout = {"replicated": replicate_dense}
 
     def _ph(name, fn):
         """run one phase; with XTB_BENCH_PHASES=1 also accumulate its synchronised wall time (diagnostic runs only)"""
@@ -172,13 +176,19 @@ def run_own(args):
             _ph("assemble_HS", lambda: ctx.assemble_HS(to_host=False))
         else:
             # owners compute their H/S blocks; the block ranges are all-gathered over NVLink (0.42 GB in total instead of
-            # 21.7 GB of dense panels) and every rank expands the replicated dense H_non, Sij locally for the eigensolve
+            # 21.7 GB of dense panels) and every rank expands the replicated dense H_non, Sij locally for the eigensolve.
+            # XTB_BENCH_DENSE_LAYOUT=panels (variant, not the headline): every rank writes only the column panels of its
+            # atoms, so that across the job every dense element is written once (1-D column-block layout, the input layout
+            # of a multi-GPU eigensolver such as cusolverMgSyevd) and no H/S exchange is needed.
             ctx.set_partition(a0 + 1, a1)
             _ph("assemble_blocks", ctx.assemble_blocks)
             rp = _ph("rowptr_d2h", lambda: interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy())
-            _ph("allgather_HS_blocks", lambda: mg.allgather_blocks([interop.buffer(ctx, abi.BUF_HBLK), interop.buffer(ctx, abi.BUF_SBLK)],
-                                                                   rp, na, 81, rank, world))
-            _ph("expand_dense", lambda: ctx.expand_dense(1, na))
+            if layout["replicated"]:
+                _ph("allgather_HS_blocks", lambda: mg.allgather_blocks([interop.buffer(ctx, abi.BUF_HBLK), interop.buffer(ctx, abi.BUF_SBLK)],
+                                                                       rp, na, 81, rank, world))
+                _ph("expand_dense", lambda: ctx.expand_dense(1, na))
+            else:
+                _ph("expand_dense", lambda: ctx.expand_dense(a0 + 1, a1))
         _ph("density", ctx.density)
         if world > 1:
             _ph("allgather_rho_blocks", lambda: mg.allgather_blocks([interop.buffer(ctx, abi.BUF_RHO), interop.buffer(ctx, abi.BUF_RHOE)],
@@ -228,7 +238,7 @@ def run_own(args):
         flops = 2 * 2 * 81 * k_kept * (n_pairs / 2 + na) * own_frac
         ach = flops / (stage[7] * 1e-3) * 1e-12 if stage[7] > 0 else None
         hbm = peaks["hbm_gbs"] if peaks else 6650.0
-        hs_bytes = 2 * 8 * N * N * own_frac
+        hs_bytes = 2 * 8 * N * N * (1.0 if (world > 1 and replicate_dense) else own_frac)
         out = {
             "metric": METRIC, "value": ms, "unit": "ms", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -236,7 +246,9 @@ def run_own(args):
             "config": {"workload": f"{wl['name']}: synthetic Au fcc 8x8x16 supercell ({na} atoms, N={N} orbitals), NRL spd TB",
                        "n_pairs": n_pairs, "n_blocks": n_blocks, "states_kept": k_kept, "l2_policy": "inputs larger than L2 "
                        "(eigenvectors 10.9 GB, H/S 21.7 GB per step)", "eigensolve": "outside graft; synthetic resident eigenvectors",
-                       "partition": "atom rows" if world > 1 else "single GPU"},
+                       "partition": "atom rows" if world > 1 else "single GPU",
+                       "dense_layout": ("single GPU" if world == 1 else "replicated on every rank" if replicate_dense
+                                        else "column panels of the owned atoms (each dense element written once in the job)")},
             "stage_ms": {"neighbours": stage[1], "assembly": stage[2], "density": stage[3], "forces": stage[4],
                          "dense_panel_kernel": stage[6], "density_kernel": stage[7]},
             "pair_blocks_per_s": n_blocks * own_frac / (stage[2] * 1e-3) if stage[2] > 0 else None,
@@ -266,6 +278,27 @@ def run_own(args):
         finally:
             ctx.set_density_cutoff(0.0)
             ctx.density()
+    # ---- informational variant at N > 1 (not the headline): dense H_non / Sij as column panels of the owned atoms, no
+    # H/S exchange (see step()).  Same timing rules: warm-up, K steps between barriers, CUDA events, max over ranks.
+    if world > 1 and replicate_dense:
+        layout["replicated"] = False
+        for _ in range(args.warmup):
+            step()
+        sync_all()
+        v0 = torch.cuda.Event(enable_timing=True); v1 = torch.cuda.Event(enable_timing=True)
+        v0.record(stream)
+        for _ in range(args.steps):
+            step()
+        v1.record(stream)
+        sync_all()
+        t = torch.tensor([v0.elapsed_time(v1) / args.steps], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        layout["replicated"] = True
+        if out is not None:
+            out["variant_dense_column_panels"] = {
+                "ms_per_step": float(t.item()), "dense_panel_kernel_ms": ctx.stage_ms(6),
+                "note": "every rank writes only the dense columns of its atoms (each element once in the job; the 1-D "
+                        "column-block input layout of a multi-GPU eigensolver); no H/S block all-gather"}
     # ---- e2e through the C ABI with host buffers (rank-local share of the work at N > 1) ----
     if not args.no_e2e:
         e2e = run_e2e(torch, ctx, wl, Cm, E, fe, world, rank, a0, a1, args)
@@ -379,6 +412,7 @@ def run_e2e_multi(torch, ctx, wl, E, fe, world, rank, a0, a1, args):
     S = np.ascontiguousarray(wl["S"]); h = np.asfortranarray(wl["supce"])
     lib, hnd = ctx.lib, ctx.h
     n = max(args.e2e_steps, 3)
+    replicate = os.environ.get("XTB_BENCH_DENSE_LAYOUT", "replicated") != "panels"
 
     def step():
         ctx._ck(lib.xtb_set_system(hnd, na, api._ip(koa), api._dp(S), api._dp(h)))          # H2D: S, KOA (replicated)
@@ -386,8 +420,11 @@ def run_e2e_multi(torch, ctx, wl, E, fe, world, rank, a0, a1, args):
         ctx._ck(lib.xtb_set_partition(hnd, a0 + 1, a1))
         ctx._ck(lib.xtb_assemble_blocks(hnd))
         rp = interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy()
-        mg.allgather_blocks([interop.buffer(ctx, abi.BUF_HBLK), interop.buffer(ctx, abi.BUF_SBLK)], rp, na, 81, rank, world)
-        ctx._ck(lib.xtb_expand_dense(hnd, 1, na, None, None))
+        if replicate:
+            mg.allgather_blocks([interop.buffer(ctx, abi.BUF_HBLK), interop.buffer(ctx, abi.BUF_SBLK)], rp, na, 81, rank, world)
+            ctx._ck(lib.xtb_expand_dense(hnd, 1, na, None, None))
+        else:
+            ctx._ck(lib.xtb_expand_dense(hnd, a0 + 1, a1, None, None))
         ctx._ck(lib.xtb_get_eigenvalues(hnd, api._dp(Ei_host)))                             # D2H: Ei
         ctx._ck(lib.xtb_set_occupations(hnd, api._dp(fh)))                                  # H2D: fe
         ctx._ck(lib.xtb_density(hnd, None, None))
@@ -406,8 +443,9 @@ def run_e2e_multi(torch, ctx, wl, E, fe, world, rank, a0, a1, args):
     ms = (time.perf_counter() - t0) * 1e3 / n
     return {"value": ms, "unit": "ms", "h2d_bytes_per_step": world * (8 * (3 * na + 9 + N) + 4 * na),
             "d2h_bytes_per_step": world * 8 * N + 8 * 3 * na, "steps": n,
-            "flow": "per-rank C ABI with host buffers (S, KOA, fe in; Ei, owned forces out); H/S blocks, rho blocks and forces "
-                    "exchanged over NVLink (all-gather); dense H_non / Sij and the eigenvectors never cross PCIe"}
+            "flow": "per-rank C ABI with host buffers (S, KOA, fe in; Ei, owned forces out); "
+                    + ("H/S blocks, " if replicate else "dense H_non / Sij as owned column panels; ")
+                    + "rho blocks and forces exchanged over NVLink (all-gather); dense H_non / Sij and the eigenvectors never cross PCIe"}
 
 
 def cpu_sample(wl, args, check=None, n_panel=48, n_dens=16, n_force=96):
