@@ -76,8 +76,14 @@ def ac1000():      # config 4
     return _wl("ac1000", "pettifor", "C", S, h, 4, 1.0)
 
 
-def au4096():      # config 5 (north star)
-    S, h = lattice(_FCC, 4.0782, (8, 8, 16), 0.05, 4096)
+def au4096():      # config 5 (north star): 8 x 8 x 16 conventional cells
+    """Atoms are numbered with the LONG axis (z, 16 cells) as the outermost loop, so that contiguous atom ranges -- the
+    multi-GPU row partition -- are compact z-slabs (8 ranks: 2 cells = 8.2 A thick against a 8.7 A cut-off; numbered
+    along x they would be 4.1 A thick and 7/8 of the cell would be halo).  Built as the 16 x 8 x 8 lattice with the
+    axes rotated (x, y, z) -> (z, x, y); fcc is invariant under that rotation."""
+    S, h = lattice(_FCC, 4.0782, (16, 8, 8), 0.05, 4096)
+    S = np.ascontiguousarray(S[:, [1, 2, 0]])
+    h = np.diag([h[1, 1], h[2, 2], h[0, 0]])
     return _wl("au4096", "nrl", "Au", S, h, 11, 0.1)
 
 
