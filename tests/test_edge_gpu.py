@@ -106,3 +106,23 @@ def test_split_work_units_give_the_same_blocks(wk, api, monkeypatch):
     for r, e in res[1:]:
         assert np.abs(r - res[0][0]).max() <= 1e-14 * np.abs(res[0][0]).max()
         assert np.abs(e - res[0][1]).max() <= 1e-14 * np.abs(res[0][1]).max()
+
+
+def test_split_tail_round_gives_the_same_blocks(wk, api, monkeypatch):
+    """last, partly filled round of the persistent density grid: its atoms are given to two CTAs each (automatic when
+    they fill at most half the grid, e.g. 512 owned atoms on 148 SMs; forced here from owned atom 50 / 0 / 107 on):
+    bit-identical rho / rho_E blocks (the order of the state sum of a block does not depend on the unit that owns it)"""
+    import importlib
+    abi = importlib.import_module("xtant-3_b200._abi"); interop = importlib.import_module("xtant-3_b200.interop")
+    wl = wk.au108()
+    C_, E, fe = wk.synthetic_eigen(wl["na"] * 9, seed=6)
+    res = []
+    for tail in ("-1", "50", "0", "107"):
+        monkeypatch.setenv("XTB_DENSITY_TAIL", tail)
+        c = api.TBContext(0); c.set_workload(wl); c.get_near_neighbours_device(); c.set_eigen(C_, E, fe)
+        c.density()
+        res.append((interop.buffer(c, abi.BUF_RHO).cpu().numpy().copy(), interop.buffer(c, abi.BUF_RHOE).cpu().numpy().copy()))
+        c.close()
+    assert np.abs(res[0][0]).max() > 0
+    for r, e in res[1:]:
+        assert np.array_equal(r, res[0][0]) and np.array_equal(e, res[0][1])
