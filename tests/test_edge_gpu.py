@@ -126,3 +126,26 @@ def test_split_tail_round_gives_the_same_blocks(wk, api, monkeypatch):
     assert np.abs(res[0][0]).max() > 0
     for r, e in res[1:]:
         assert np.array_equal(r, res[0][0]) and np.array_equal(e, res[0][1])
+
+
+@pytest.mark.parametrize("name", ["diamond64", "au_4x4x5", "si216"])
+def test_single_image_neighbour_path_is_bit_identical_to_the_27_image_scan(wk, api, monkeypatch, name):
+    """orthorhombic cells with every edge > 2 rm take the one-image path (neighbours.cu, min_image_ortho); XTB_NN_SCAN27=1
+    forces the reference's 27-image scan: same sizes, lists, distances and fractional shifts, bit for bit."""
+    wl = {"diamond64": wk.diamond64, "si216": wk.si216,
+          "au_4x4x5": lambda: wk.au_fcc((5, 5, 6), sigma=0.08, seed=11)}[name]()
+    got = []
+    for scan in ("1", "0"):
+        monkeypatch.setenv("XTB_NN_SCAN27", scan)
+        c = api.TBContext(0); c.set_workload(wl)
+        g = c.get_near_neighbours()
+        got.append(g)
+        c.close()
+    a, b = got
+    assert a["size"].sum() > 0
+    np.testing.assert_array_equal(a["size"], b["size"])
+    m = int(a["size"].max())
+    mask = np.arange(m)[None, :] < a["size"][:, None]
+    np.testing.assert_array_equal(a["list"][:, :m][mask], b["list"][:, :m][mask])
+    assert np.array_equal(a["dist"][:, :m][mask], b["dist"][:, :m][mask])
+    assert np.array_equal(a["dist_s"][:, :m][mask], b["dist_s"][:, :m][mask])

@@ -11,6 +11,8 @@
 // double loop becomes Na warps; sqrt is only taken when the squared distances cannot decide
 // the `<=` (exact: sqrt is monotone, and a relative gap of 1e-14 in r^2 is far above 1 ulp).
 #include "xtb_ctx.h"
+#include <cmath>
+#include <cstdlib>
 
 namespace {
 
@@ -75,6 +77,34 @@ __device__ __forceinline__ MinImage min_image(const double Si[3], const double S
     return o;
 }
 
+// Orthorhombic cell with every edge longer than 2 rm: the squared distance is separable per axis, so the image the
+// 27-scan ends with is the per-axis minimum of |ds_k + zb| (ties to the later zb, as the scan's `<=`), and it is the
+// only image that can pass `a_r < rm`.  Two images of one axis are never confused by rounding for a pair inside the
+// cut-off: they would both have |component| ~ L/2 > rm.  The chosen image is evaluated with the same operations as in
+// the scan, so every stored number has the same bits; pairs outside the cut-off are not stored at all.
+__device__ __forceinline__ MinImage min_image_ortho(const double Si[3], const double Sj[3], const double* __restrict__ h) {
+    double d[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const double ds = __dsub_rn(Si[k], Sj[k]);
+        double best = __dadd_rn(ds, -1.0);
+#pragma unroll
+        for (int z = 1; z < 3; ++z) {
+            const double v = __dadd_rn(ds, (double)(z - 1));
+            if (fabs(v) <= fabs(best)) best = v;
+        }
+        d[k] = best;
+    }
+    MinImage o;
+    o.x = sum3(__dmul_rn(d[0], h[0]), __dmul_rn(d[1], h[1]), __dmul_rn(d[2], h[2]));
+    o.y = sum3(__dmul_rn(d[0], h[3]), __dmul_rn(d[1], h[4]), __dmul_rn(d[2], h[5]));
+    o.z = sum3(__dmul_rn(d[0], h[6]), __dmul_rn(d[1], h[7]), __dmul_rn(d[2], h[8]));
+    o.r = __dsqrt_rn(norm2(o.x, o.y, o.z));
+    o.sx = d[0]; o.sy = d[1]; o.sz = d[2];
+    return o;
+}
+
+template <bool ORTHO>
 __global__ void __launch_bounds__(256) nn_build_kernel(int na, const double* __restrict__ S, const double* __restrict__ hmat,
                                                       double rm, int cap, int* __restrict__ nn_size,
                                                       int* __restrict__ nn_list, double* __restrict__ nn_dist,
@@ -93,7 +123,7 @@ __global__ void __launch_bounds__(256) nn_build_kernel(int na, const double* __r
         MinImage mi;
         if (j < na && j != i) {
             const double Sj[3] = {S[3 * j], S[3 * j + 1], S[3 * j + 2]};
-            mi = min_image(Si, Sj, h);
+            mi = ORTHO ? min_image_ortho(Si, Sj, h) : min_image(Si, Sj, h);
             isn = mi.r < rm;
         }
         const unsigned mask = __ballot_sync(0xffffffffu, isn);
@@ -208,9 +238,18 @@ int xtb_impl_neighbours(xtb_ctx* c, double rm) {
         XTB_CUDA(c, cudaMemsetAsync(c->d_maxnn.p, 0, sizeof(int) * 4, c->stream));
         XTB_CUDA(c, cudaMemcpyAsync(c->d_scratch.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
         const int warps_per_block = 8;
-        nn_build_kernel<<<(na + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0, c->stream>>>(
-            na, (const double*)c->d_S.p, (const double*)c->d_scratch.p, rm, cap, (int*)c->d_nn_size.p,
-            (int*)c->d_nn_list.p, (double*)c->d_nn_dist.p, (double*)c->d_nn_dist_s.p, (int*)c->d_maxnn.p);
+        // single-image path: diagonal cell, every edge > 2 rm (see min_image_ortho); XTB_NN_SCAN27=1 forces the full scan
+        const double* hh = c->h_supce;
+        bool ortho = hh[1] == 0.0 && hh[2] == 0.0 && hh[3] == 0.0 && hh[5] == 0.0 && hh[6] == 0.0 && hh[7] == 0.0;
+        for (int k = 0; k < 3 && ortho; ++k) ortho = fabs(hh[4 * k]) > 2.0 * rm * (1.0 + 1e-9);
+        if (const char* ev = getenv("XTB_NN_SCAN27")) { if (atoi(ev) == 1) ortho = false; }
+        const dim3 g((na + warps_per_block - 1) / warps_per_block), b(warps_per_block * 32);
+        if (ortho)
+            nn_build_kernel<true><<<g, b, 0, c->stream>>>(na, (const double*)c->d_S.p, (const double*)c->d_scratch.p, rm, cap, (int*)c->d_nn_size.p,
+                                                          (int*)c->d_nn_list.p, (double*)c->d_nn_dist.p, (double*)c->d_nn_dist_s.p, (int*)c->d_maxnn.p);
+        else
+            nn_build_kernel<false><<<g, b, 0, c->stream>>>(na, (const double*)c->d_S.p, (const double*)c->d_scratch.p, rm, cap, (int*)c->d_nn_size.p,
+                                                           (int*)c->d_nn_list.p, (double*)c->d_nn_dist.p, (double*)c->d_nn_dist_s.p, (int*)c->d_maxnn.p);
         XTB_LAUNCH_CHECK(c);
         int mx = 0;
         XTB_CUDA(c, cudaMemcpyAsync(&mx, c->d_maxnn.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
