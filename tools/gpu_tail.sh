@@ -25,3 +25,4 @@ for rng in ((1, 512), (1025, 1536)):
 print(json.dumps(out))
 open("gpurun_out/r01m_tail.json", "w").write(json.dumps(out))
 P
+python bench.py --no-cpu --no-e2e --steps 5 --warmup 3 2>/dev/null | python -c "import sys,json; j=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('N=1', j['value'], j['stage_ms'])"

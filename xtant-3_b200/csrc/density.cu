@@ -368,8 +368,7 @@ __device__ __forceinline__ void consume_idle(uint32_t stages, uint64_t* full, ui
 
 template <int NO, int NCW, bool DBG>
 __global__ void __launch_bounds__((NCW + 1 + NPROD) * 32, 1)
-density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, int nchunks, int dbg, int maxsub, int lead, int split, int tail_from, int tsplit,
-                    long long* __restrict__ prog,
+density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, int nchunks, int dbg, int maxsub, int lead, int split, long long* __restrict__ prog,
                     const int* __restrict__ nn_size, const int* __restrict__ nn_list, const signed char* __restrict__ own,
                     const int* __restrict__ rowptr, const double* __restrict__ Ct, const double* __restrict__ wf,
                     const double* __restrict__ wfe, double* __restrict__ rho, double* __restrict__ rhoE) {
@@ -401,13 +400,8 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
     int round = 0;
     // work unit = (owned atom, part of its owned neighbours); split > 1 only when the owned range is too short to fill
     // the persistent grid evenly (few rounds): the unit then costs 1/split of an atom (+ the atom's own tile again)
-    // Units from `tail_from` on (the last, partly filled round of the grid) are split `tsplit` ways instead, so that the
-    // round's atoms spread over the idle CTAs: 512 owned atoms on 148 SMs take 3.7 instead of 4 rounds.
-    const int nunits = tail_from + ((a1 - a0) - tail_from / split) * tsplit;
-    for (int u = blockIdx.x; u < nunits; u += gridDim.x, ++round) {
-        int i, part, sp;
-        if (u < tail_from) { sp = split; i = a0 + u / split; part = u - (u / split) * split; }
-        else { const int v = u - tail_from; sp = tsplit; i = a0 + tail_from / split + v / tsplit; part = v - (v / tsplit) * tsplit; }
+    for (int u = blockIdx.x; u < (a1 - a0) * split; u += gridDim.x, ++round) {
+        const int i = a0 + u / split, part = u - (u / split) * split;
         // ---- owned neighbours of i, in list order (warp 0, ordered compaction) ----
         __syncthreads();
         if (warp == 0) {
@@ -424,7 +418,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
         }
         __syncthreads();
         const int n_all = n_owned_sh;
-        const int per = (n_all + sp - 1) / sp;
+        const int per = (n_all + split - 1) / split;
         const int lo = part * per, n_owned = min(n_all, lo + per);      // this unit: owned neighbours lo .. n_owned-1
         if (part > 0 && lo >= n_owned) continue;                        // the on-site block belongs to part 0 (uniform per CTA)
         const size_t b0i = (size_t)rowptr[i];
@@ -709,33 +703,49 @@ int run_density(xtb_ctx* c) {
         int split = (nown < 6 * c->sm_count && nown > c->sm_count / 2 && c->max_nn / 2 >= slotcap - 1) ? 2 : 1;
         if (const char* ev = getenv("XTB_DENSITY_SPLIT")) { const int v = atoi(ev); if (v >= 1 && v <= 4) split = v; }
         int grid = c->sm_count < nown * split ? c->sm_count : nown * split;
-        // last round of the persistent grid: if its atoms fill at most half the CTAs, give each atom to two CTAs
-        int tail_from = nown * split, tsplit = split;
-        if (split == 1 && nown > grid) {
-            const int full = (nown / grid) * grid, rest = nown - full;
-            if (rest > 0 && 2 * rest <= grid) { tail_from = full; tsplit = 2; }
-        }
-        if (const char* ev = getenv("XTB_DENSITY_TAIL")) {      // tests: "<first split atom>" (0-based within the owned range), split 2
-            const int v = atoi(ev);
-            if (split == 1 && v >= 0 && v < nown) { tail_from = v; tsplit = 2; } else if (v < 0) { tail_from = nown * split; tsplit = split; }
-        }
         if ((rc = xtb_reserve(c, c->d_prog, sizeof(long long) * (size_t)c->sm_count))) return rc;
         XTB_CUDA(c, cudaMemsetAsync(c->d_prog.p, 0, sizeof(long long) * (size_t)c->sm_count, c->stream));
         const int maxsub = slotcap > 1 ? (c->max_nn + slotcap - 2) / (slotcap - 1) + 1 : 1;
-        int a_na = na, a_a0 = c->a0, a_a1 = c->a1, a_cap = c->cap, a_slot = slotcap, a_st = stages, a_nch = nchunks, a_dbg = c->density_dbg, a_ms = maxsub, a_lead = c->density_lead, a_split = split, a_tail = tail_from, a_tsplit = tsplit;
+        int a_na = na, a_a0 = c->a0, a_a1 = c->a1, a_cap = c->cap, a_slot = slotcap, a_st = stages, a_nch = nchunks, a_dbg = c->density_dbg, a_ms = maxsub, a_lead = c->density_lead, a_split = split;
         long long* a_prog = (long long*)c->d_prog.p;
         const int* a_sz = (const int*)c->d_nn_size.p; const int* a_li = (const int*)c->d_nn_list.p;
         const signed char* a_own = (const signed char*)c->d_own.p; const int* a_rp = (const int*)c->d_rowptr.p;
         const double* a_ct = (const double*)c->d_Ct.p; const double* a_wf = (const double*)c->d_wf.p; const double* a_wfe = (const double*)c->d_wfe.p;
         double* a_rho = (double*)c->d_rho.p; double* a_rhoE = (double*)c->d_rhoE.p;
-        void* args[] = {&a_na, &a_a0, &a_a1, &a_cap, &a_slot, &a_st, &a_nch, &a_dbg, &a_ms, &a_lead, &a_split, &a_tail, &a_tsplit, &a_prog, &a_sz, &a_li, &a_own, &a_rp,
+        void* args[] = {&a_na, &a_a0, &a_a1, &a_cap, &a_slot, &a_st, &a_nch, &a_dbg, &a_ms, &a_lead, &a_split, &a_prog, &a_sz, &a_li, &a_own, &a_rp,
                         &a_ct, &a_wf, &a_wfe, &a_rho, &a_rhoE};
 #define XTB_LAUNCH(W, D) { auto kern = density_dmma_kernel<9, W, D>; \
         XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         XTB_CUDA(c, cudaLaunchKernel((const void*)kern, dim3(grid), dim3((W + 1 + NPROD) * 32), args, smem, c->stream)); }
-        if (c->density_dbg) XTB_LAUNCH(8, true) else if (NCW == 12) XTB_LAUNCH(12, false) else XTB_LAUNCH(8, false)
+        // Last round of the persistent grid: if its atoms fill at most half the CTAs, they run as a second launch of the
+        // same kernel with two units per atom (512 owned atoms on 148 SMs: 3 + 0.68 rounds instead of 4).  The CTAs of a
+        // launch run in lock-step and finish together, so the second launch starts on an idle GPU; the kernel itself is
+        // untouched (an in-kernel tail decode cost 1.3 % of the single-GPU run through register allocation, measured).
+        int tail_from = nown;                      // first owned atom (0-based within the range) of the split tail
+        if (split == 1 && nown > grid) {
+            const int full = (nown / grid) * grid, rest = nown - full;
+            if (rest > 0 && 2 * rest <= grid) tail_from = full;
+        }
+        if (const char* ev = getenv("XTB_DENSITY_TAIL")) {      // tests: force the position of the tail (negative = none)
+            const int v = atoi(ev);
+            tail_from = (split == 1 && v >= 0 && v < nown) ? v : nown;
+        }
+#define XTB_LAUNCH_ALL if (c->density_dbg) XTB_LAUNCH(8, true) else if (NCW == 12) XTB_LAUNCH(12, false) else XTB_LAUNCH(8, false)
+        if (tail_from > 0) {
+            a_a1 = c->a0 + tail_from;
+            grid = c->sm_count < tail_from * split ? c->sm_count : tail_from * split;
+            XTB_LAUNCH_ALL
+            XTB_LAUNCH_CHECK(c);
+        }
+        if (tail_from < nown) {
+            if (tail_from > 0) XTB_CUDA(c, cudaMemsetAsync(c->d_prog.p, 0, sizeof(long long) * (size_t)c->sm_count, c->stream));
+            a_a0 = c->a0 + tail_from; a_a1 = c->a1; a_split = 2;
+            grid = c->sm_count < (nown - tail_from) * 2 ? c->sm_count : (nown - tail_from) * 2;
+            XTB_LAUNCH_ALL
+            XTB_LAUNCH_CHECK(c);
+        }
+#undef XTB_LAUNCH_ALL
 #undef XTB_LAUNCH
-        XTB_LAUNCH_CHECK(c);
         c->density_slotcap = slotcap; c->density_stages = stages;
     } else if (nown > 0 && NO <= 4 && c->density_impl == 1) {
         XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
