@@ -299,6 +299,21 @@ def run_own(args):
                 "ms_per_step": float(t.item()), "dense_panel_kernel_ms": ctx.stage_ms(6),
                 "note": "every rank writes only the dense columns of its atoms (each element once in the job; the 1-D "
                         "column-block input layout of a multi-GPU eigensolver); no H/S block all-gather"}
+    # ---- N > 1: the partitioned, exchanged result against the same step computed by rank 0 alone on its GPU ----
+    if world > 1:
+        step(); sync_all()
+        if rank == 0:
+            got = [interop.buffer(ctx, b).clone() for b in (abi.BUF_FORCES, abi.BUF_RHO, abi.BUF_RHOE, abi.BUF_HBLK, abi.BUF_SBLK)]
+            ctx.set_partition(1, na)
+            ctx.get_near_neighbours_device(); ctx.assemble_HS(to_host=False); ctx.density(); ctx.forces_device()
+            torch.cuda.synchronize()
+            names = ("forces_eV_per_A(frac. coords as returned)", "rho", "rho_E", "H_blocks", "S_blocks")
+            ref = [interop.buffer(ctx, b) for b in (abi.BUF_FORCES, abi.BUF_RHO, abi.BUF_RHOE, abi.BUF_HBLK, abi.BUF_SBLK)]
+            out["multi_gpu_vs_single_gpu_max_abs_diff"] = {n: float((g - r).abs().max().item()) for n, g, r in zip(names, got, ref)}
+            out["multi_gpu_vs_single_gpu_max_abs_diff"]["forces_scale"] = float(ref[0].abs().max().item())
+            del got, ref
+        ctx.set_partition(a0 + 1, a1)
+        sync_all()
     # ---- e2e through the C ABI with host buffers (rank-local share of the work at N > 1) ----
     if not args.no_e2e:
         e2e = run_e2e(torch, ctx, wl, Cm, E, fe, world, rank, a0, a1, args)

@@ -41,6 +41,17 @@ def _scratch_buf(key, n, like):
     return t[:n]
 
 
+def _direct_gather(bufs, group):
+    """XTB_MG_GATHER=direct selects the copy-free exchange on CUDA tensors over NCCL (default: packed slots)"""
+    import os
+    if os.environ.get("XTB_MG_GATHER", "packed") != "direct" or not bufs[0].is_cuda:
+        return False
+    try:
+        return dist.get_backend(group) == "nccl"
+    except Exception:
+        return False
+
+
 def _gather_segments(bufs, segs, rank, group=None):
     """in-place all-gather of variable-length contiguous segments of the 1-D tensors `bufs` (one tensor or a list of
     tensors sharing the same segmentation): rank r owns buf[segs[r][0]:segs[r][1]] of every buffer; afterwards every rank
@@ -62,6 +73,13 @@ def _gather_segments(bufs, segs, rank, group=None):
         return
     mx = max(lens)
     if mx == 0:
+        return
+    if _direct_gather(bufs, group) and min(lens) > 0:
+        # NCCL: all_gather with the destination views themselves as outputs.  For unequal lengths ProcessGroupNCCL
+        # runs it as one coalesced group of broadcasts (root r -> segment r), so nothing is packed or copied out.
+        for buf in bufs:
+            outs = [buf[b:e] for b, e in segs]
+            dist.all_gather(outs, outs[rank], group=group)
         return
     nb = len(bufs)
     send = _scratch_buf(("send", nb), nb * mx, bufs[0])
