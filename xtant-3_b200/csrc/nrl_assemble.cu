@@ -40,22 +40,15 @@ __global__ void nrl_dens_kernel(int na, int cap, int n_kinds, const int* __restr
     dens[j] = rho;
 }
 
-// one thread per (block, mat); block b of atom j: q = b - rowptr[j]; q == 0 on-site, else list entry q-1
-__global__ void __launch_bounds__(128) nrl_blocks_kernel(int na, int a0, int a1, int cap, int n_kinds,
-                                                        const int* __restrict__ koa, const int* __restrict__ nn_size,
-                                                        const int* __restrict__ nn_list, const int* __restrict__ rev,
-                                                        const double* __restrict__ nn_dist, const int* __restrict__ rowptr,
-                                                        const xtb_nrl_pair* __restrict__ TB, const double* __restrict__ dens,
-                                                        double* __restrict__ Hblk, double* __restrict__ Sblk) {
-    // thread -> (atom j, slot q, mat); ELL indexing keeps the decode cheap: t = ((j-a0)*(cap+1) + q)*2 + mat
-    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long per_atom = 2LL * (cap + 1);
-    const int j = a0 + (int)(t / per_atom);
-    if (j >= a1) return;
-    const int rem = (int)(t % per_atom);
-    const int q = rem >> 1, mat = rem & 1;
-    if (q > nn_size[j]) return;
-    double* out = (mat == 0 ? Hblk : Sblk) + ((size_t)rowptr[j] + q) * 81;
+// one thread per (block, mat) does the arithmetic (radial functions, SK rotation: all in registers); block b of atom j:
+// q = b - rowptr[j]; q == 0 on-site, else list entry q-1.  The 81 entries go to the thread's row of a shared-memory
+// staging area first and each warp then writes the blocks of its 32 threads out cooperatively: every store instruction
+// covers 256 contiguous bytes of the block store (a thread writing its own 648-byte block touched 32 sectors per store).
+constexpr int NB_THREADS = 128;
+__device__ __forceinline__ void nrl_block_values(int j, int q, int mat, int cap, int n_kinds, const int* __restrict__ koa,
+                                                 const int* __restrict__ nn_list, const int* __restrict__ rev,
+                                                 const double* __restrict__ nn_dist, const xtb_nrl_pair* __restrict__ TB,
+                                                 const double* __restrict__ dens, double* __restrict__ out) {
     if (q == 0) {   // on-site: diag(h_s, h_p x3, h_t2g x3, h_eg x2) * g_Ry ; S = I
         const xtb_nrl_pair& P = TB[koa[j] + n_kinds * koa[j]];
         const double rho = dens[j];
@@ -102,6 +95,38 @@ __global__ void __launch_bounds__(128) nrl_blocks_kernel(int na, int a0, int a1,
             if (direct) { out[a + 9 * b] = u; if (a != b) out[b + 9 * a] = lo; }
             else        { out[b + 9 * a] = u; if (a != b) out[a + 9 * b] = lo; }
         }
+}
+
+__global__ void __launch_bounds__(NB_THREADS) nrl_blocks_kernel(int na, int a0, int a1, int cap, int n_kinds,
+                                                               const int* __restrict__ koa, const int* __restrict__ nn_size,
+                                                               const int* __restrict__ nn_list, const int* __restrict__ rev,
+                                                               const double* __restrict__ nn_dist, const int* __restrict__ rowptr,
+                                                               const xtb_nrl_pair* __restrict__ TB, const double* __restrict__ dens,
+                                                               double* __restrict__ Hblk, double* __restrict__ Sblk) {
+    extern __shared__ double stage_out[];          // [NB_THREADS][81]
+    // thread -> (atom j, slot q, mat); ELL indexing keeps the decode cheap: t = ((j-a0)*(cap+1) + q)*2 + mat
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long per_atom = 2LL * (cap + 1);
+    const int j = a0 + (int)(t / per_atom);
+    const int rem = (int)(t % per_atom);
+    const int q = rem >> 1, mat = rem & 1;
+    double* dst = nullptr;
+    if (j < a1 && q <= nn_size[j]) {
+        dst = (mat == 0 ? Hblk : Sblk) + ((size_t)rowptr[j] + q) * 81;
+        nrl_block_values(j, q, mat, cap, n_kinds, koa, nn_list, rev, nn_dist, TB, dens, stage_out + threadIdx.x * 81);
+    }
+    __syncwarp();
+    const int lane = threadIdx.x & 31;
+    const double* wsrc = stage_out + (threadIdx.x - lane) * 81;
+#pragma unroll 4
+    for (int s = 0; s < 32; ++s) {
+        double* d = reinterpret_cast<double*>(__shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(dst), s));
+        if (d == nullptr) continue;
+        const double* src = wsrc + s * 81;
+        d[lane] = src[lane];
+        d[lane + 32] = src[lane + 32];
+        if (lane < 17) d[lane + 64] = src[lane + 64];
+    }
 }
 
 }  // namespace
@@ -252,7 +277,9 @@ int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense) {
     const int nown = c->a1 - c->a0;
     const long long nthreads = 2LL * (c->cap + 1) * nown;
     if (nthreads > 0) {
-        nrl_blocks_kernel<<<(unsigned)((nthreads + 127) / 128), 128, 0, c->stream>>>(
+        const size_t stage_bytes = sizeof(double) * 81 * NB_THREADS;       // 83 KB: two CTAs per SM
+        XTB_CUDA(c, cudaFuncSetAttribute(nrl_blocks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)stage_bytes));
+        nrl_blocks_kernel<<<(unsigned)((nthreads + NB_THREADS - 1) / NB_THREADS), NB_THREADS, stage_bytes, c->stream>>>(
             na, c->a0, c->a1, c->cap, c->n_kinds, (const int*)c->d_koa.p, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
             (const int*)c->d_rev.p, (const double*)c->d_nn_dist.p, (const int*)c->d_rowptr.p, (const xtb_nrl_pair*)c->d_params.p,
             (const double*)c->d_dens.p, (double*)c->d_Hblk.p, (double*)c->d_Sblk.p);
