@@ -547,18 +547,46 @@ __global__ void __launch_bounds__(128) density_simple_kernel(int na, int a0, int
     rhoE[blk + mu + NO * nu] = e;
 }
 
-// ---------------- small-basis kernel (sp3: Pettifor-type and DFTB sp sets, n_orb <= 4) ----------------
-// One warp per owned block (i, q).  Lanes stride the kept states; the NO rows of atom i and of atom j in one state are
-// NO consecutive doubles of an eigenvector column (one 32-byte sector for NO = 4), so every load instruction of the warp
-// fetches whole sectors (the one-thread-per-element kernel above reads one double per 32-byte sector).  Each lane keeps
-// the 2 x NO x NO partial sums of its states; fixed-order butterfly at the end (same bits on every run).
-// Bound: L2 bandwidth -- 2 * 8 * NO bytes per (block, state) for 4 NO^2 flop; the eigenvectors (8 N K bytes) stay in L2.
+// ---------------- small-basis kernels (sp3: Pettifor-type and DFTB sp sets, n_orb <= 4) ----------------
+// prep: X[atom][kept state kk][NO rows] = Ha[atom*NO + r, keep[kk]] -- the rows of one atom for consecutive states are
+// consecutive in memory.  (In Ha itself consecutive states of an atom are N*8 bytes apart, so a warp whose lanes stride
+// the states touches 32 cache lines per load instruction: the first version of the kernel below ran at 71 % L1TEX
+// throughput with every other unit idle, profiles/r01r_ncu_warp_full_summary.csv.)  CTA = (32 states, DR_AT atoms),
+// transposed through shared memory, both phases coalesced; HBM/L2-bound, 2 * 8 * N * K bytes.
+constexpr int DR_AT = 16;
+template <int NO>
+__global__ void __launch_bounds__(256) rows_by_state_kernel(int na, long long N, int nkeep, const int* __restrict__ keep,
+                                                            const double* __restrict__ Ha, double* __restrict__ X) {
+    constexpr int W = DR_AT * NO;
+    __shared__ double tile[32][W + 1];
+    __shared__ long long colbase[32];
+    const int k0 = blockIdx.x * 32, atom0 = blockIdx.y * DR_AT;
+    const int nat = min(DR_AT, na - atom0), ns = min(32, nkeep - k0);
+    if (threadIdx.x < 32) colbase[threadIdx.x] = threadIdx.x < ns ? (long long)keep[k0 + threadIdx.x] * N + (long long)atom0 * NO : -1;
+    __syncthreads();
+    const int w = nat * NO;
+    for (int idx = threadIdx.x; idx < 32 * w; idx += 256) {
+        const int st = idx / w, e = idx - st * w;
+        if (st < ns) tile[st][e] = Ha[colbase[st] + e];
+    }
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < nat * ns * NO; idx += 256) {
+        const int a = idx / (ns * NO), rem = idx - a * (ns * NO);
+        const int st = rem / NO, r = rem - st * NO;
+        X[((size_t)(atom0 + a) * nkeep + k0 + st) * NO + r] = tile[st][a * NO + r];
+    }
+}
+
+// One warp per owned block (i, q).  Lanes stride the kept states; lane kk reads the NO rows of atom i and of atom j of
+// its state from X (32 bytes each for NO = 4; the 32 lanes of a load instruction cover 1 KB contiguous = 8 cache lines).
+// Each lane keeps the 2 x NO x NO partial sums of its states; fixed-order butterfly at the end (same bits on every run).
+// Bound: L1/L2 bandwidth -- 2 * 8 * NO bytes per (block, state) for 4 NO^2 flop.
 constexpr int DW_WARPS = 4;
 template <int NO>
-__global__ void __launch_bounds__(32 * DW_WARPS) density_warp_kernel(int a0, int a1, int cap, long long N, int nkeep,
-                                                                     const int* __restrict__ keep, const int* __restrict__ nn_size,
+__global__ void __launch_bounds__(32 * DW_WARPS) density_warp_kernel(int a0, int a1, int cap, int nkeep,
+                                                                     const int* __restrict__ nn_size,
                                                                      const int* __restrict__ nn_list, const signed char* __restrict__ own,
-                                                                     const int* __restrict__ rowptr, const double* __restrict__ Ha,
+                                                                     const int* __restrict__ rowptr, const double* __restrict__ X,
                                                                      const double* __restrict__ wf, const double* __restrict__ wfe,
                                                                      double* __restrict__ rho, double* __restrict__ rhoE) {
     const int i = a0 + blockIdx.y;
@@ -566,26 +594,25 @@ __global__ void __launch_bounds__(32 * DW_WARPS) density_warp_kernel(int a0, int
     if (i >= a1 || q > nn_size[i]) return;
     if (q > 0 && !own[(size_t)i * cap + q - 1]) return;
     const int j = q == 0 ? i : nn_list[(size_t)i * cap + q - 1];
-    const double* ci = Ha + (size_t)i * NO;
-    const double* cj = Ha + (size_t)j * NO;
+    const double* ci = X + (size_t)i * nkeep * NO;
+    const double* cj = X + (size_t)j * nkeep * NO;
     double s[NO * NO], e[NO * NO];
 #pragma unroll
     for (int x = 0; x < NO * NO; ++x) { s[x] = 0.0; e[x] = 0.0; }
-    const bool vec = (NO % 2 == 0) && (N % 2 == 0);          // 16-byte aligned rows of an atom in every column
+#pragma unroll 2
     for (int kk = lane; kk < nkeep; kk += 32) {
-        const size_t o = (size_t)keep[kk] * N;
         const double w1 = wf[kk], w2 = wfe[kk];
         double a[NO], b[NO];
-        if (vec) {
+        if constexpr (NO % 2 == 0) {          // rows of (atom, state) start at a multiple of 16 bytes
 #pragma unroll
             for (int m = 0; m < NO / 2; ++m) {
-                const double2 va = __ldg(reinterpret_cast<const double2*>(ci + o) + m);
-                const double2 vb = __ldg(reinterpret_cast<const double2*>(cj + o) + m);
+                const double2 va = __ldg(reinterpret_cast<const double2*>(ci + (size_t)kk * NO) + m);
+                const double2 vb = __ldg(reinterpret_cast<const double2*>(cj + (size_t)kk * NO) + m);
                 a[2 * m] = va.x; a[2 * m + 1] = va.y; b[2 * m] = vb.x; b[2 * m + 1] = vb.y;
             }
         } else {
 #pragma unroll
-            for (int m = 0; m < NO; ++m) { a[m] = __ldg(ci + o + m); b[m] = __ldg(cj + o + m); }
+            for (int m = 0; m < NO; ++m) { a[m] = __ldg(ci + (size_t)kk * NO + m); b[m] = __ldg(cj + (size_t)kk * NO + m); }
         }
 #pragma unroll
         for (int mu = 0; mu < NO; ++mu) {
@@ -748,12 +775,18 @@ int run_density(xtb_ctx* c) {
 #undef XTB_LAUNCH
         c->density_slotcap = slotcap; c->density_stages = stages;
     } else if (nown > 0 && NO <= 4 && c->density_impl == 1) {
-        XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
         if constexpr (NO <= 4) {
+            if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)(nkeep > 0 ? nkeep : 1) * N + 1024))) return rc;
+            if (nkeep > 0) {
+                dim3 g((nkeep + 31) / 32, (na + DR_AT - 1) / DR_AT);
+                rows_by_state_kernel<NO><<<g, 256, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, c->d_Ha, (double*)c->d_Ct.p);
+                XTB_LAUNCH_CHECK(c);
+            }
+            XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
             dim3 grid((c->max_nn + 1 + DW_WARPS - 1) / DW_WARPS, nown);
-            density_warp_kernel<NO><<<grid, 32 * DW_WARPS, 0, c->stream>>>(c->a0, c->a1, c->cap, N, nkeep, (const int*)c->d_keep.p,
+            density_warp_kernel<NO><<<grid, 32 * DW_WARPS, 0, c->stream>>>(c->a0, c->a1, c->cap, nkeep,
                                                                             (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                                            (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, c->d_Ha,
+                                                                            (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (const double*)c->d_Ct.p,
                                                                             (const double*)c->d_wf.p, (const double*)c->d_wfe.p,
                                                                             (double*)c->d_rho.p, (double*)c->d_rhoE.p);
         }
