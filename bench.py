@@ -151,6 +151,8 @@ def run_own(args):
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
     ctx.set_workload(wl)
+    if world > 1 and os.environ.get("XTB_BENCH_BLOCK_LAYOUT", "segmented") != "compact":
+        ctx.set_block_layout(world)      # equal-capacity segment per rank in every block store: in-place all-gathers
     a0, a1 = mg.partition(na, world, rank)
     Cm, dE, dfe, E, fe = make_eigen_device(torch, wk, wl, N)
     ctx.set_eigen_device(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
@@ -247,6 +249,8 @@ def run_own(args):
                        "n_pairs": n_pairs, "n_blocks": n_blocks, "states_kept": k_kept, "l2_policy": "inputs larger than L2 "
                        "(eigenvectors 10.9 GB, H/S 21.7 GB per step)", "eigensolve": "outside graft; synthetic resident eigenvectors",
                        "partition": "atom rows" if world > 1 else "single GPU",
+                       "block_exchange": (None if world == 1 else "packed slots + copy-out" if os.environ.get("XTB_BENCH_BLOCK_LAYOUT", "segmented") == "compact"
+                                          else "in-place all-gather of equal-capacity segments (xtb_set_block_layout)"),
                        "dense_layout": ("single GPU" if world == 1 else "replicated on every rank" if replicate_dense
                                         else "column panels of the owned atoms (each dense element written once in the job)")},
             "stage_ms": {"neighbours": stage[1], "assembly": stage[2], "density": stage[3], "forces": stage[4],

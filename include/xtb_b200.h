@@ -110,6 +110,12 @@ int  xtb_set_system(xtb_ctx*, int na, const int32_t* koa /*[na], 1-based*/,
 /* rows (atoms, 1-based inclusive range) this context owns in a multi-GPU run; default all.
  * Replaces the round-robin split `do i = 1+rank, N, nranks` of the MPI build (TB_NRL.f90:267-327). */
 int  xtb_set_partition(xtb_ctx*, int atom_first, int atom_last);
+/* Multi-GPU block layout (optional; call before xtb_neighbours, same value on every rank): the block stores (H, S, rho,
+ * rho_E) are laid out in `parts` equal-capacity segments, one per contiguous range of ceil(na/parts) atoms, so that the
+ * owners' ranges are exchanged by ONE in-place all-gather (no packing).  rowptr then has gaps; every access is
+ * rowptr[atom] + q, so nothing else changes.  parts = 1 (default): compact.  No reference counterpart (the MPI build
+ * all-reduces whole dense arrays, MPI_subroutines.f90:3965-3982). */
+int  xtb_set_block_layout(xtb_ctx*, int parts);
 
 /* ---- S1: get_near_neighbours -> Find_nearest_neighbours (Atomic_tools.f90:562,4230;
  *      minimum image = shortest_distance_OLD :4028-4131).  rm_angstrom <= 0: derive the

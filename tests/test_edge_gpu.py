@@ -149,3 +149,37 @@ def test_single_image_neighbour_path_is_bit_identical_to_the_27_image_scan(wk, a
     np.testing.assert_array_equal(a["list"][:, :m][mask], b["list"][:, :m][mask])
     assert np.array_equal(a["dist"][:, :m][mask], b["dist"][:, :m][mask])
     assert np.array_equal(a["dist_s"][:, :m][mask], b["dist_s"][:, :m][mask])
+
+
+def test_segmented_block_layout_gives_identical_results(wk, api):
+    """xtb_set_block_layout(parts): block stores in equal-capacity segments per atom range (one in-place all-gather in a
+    multi-GPU run).  Dense H/S, dense rho / rho_E, forces and pressure are bit-identical to the compact layout; the pair
+    count is unchanged; the segments start at multiples of the largest range's block count."""
+    import importlib
+    abi = importlib.import_module("xtant-3_b200._abi"); interop = importlib.import_module("xtant-3_b200.interop")
+    import torch
+    wl = wk.au108()
+    C_, E, fe = wk.synthetic_eigen(wl["na"] * 9, seed=9)
+    res = []
+    for parts in (1, 3, 8):
+        c = api.TBContext(0); c.set_workload(wl); c.set_block_layout(parts)
+        c.get_near_neighbours_device()
+        H, S = c.assemble_HS()
+        c.set_eigen(C_, E, fe)
+        A, AE = c.density(dense=True)
+        F = c.forces(); P = c.pressure()
+        rp = interop.buffer(c, abi.BUF_ROWPTR, torch.int32).cpu().numpy()
+        res.append((H, S, A, AE, F, P, c.counter(5), c.counter(4), rp))
+        c.close()
+    na = wl["na"]
+    for parts, r in zip((3, 8), res[1:]):
+        for a, b in zip(r[:6], res[0][:6]):
+            assert np.array_equal(a, b)
+        assert r[6] == res[0][6]                         # real pairs
+        per = (na + parts - 1) // parts
+        mx = r[8][na] // parts
+        assert r[8][na] == parts * mx and r[7] == parts * mx >= res[0][7]
+        for k in range(parts):
+            if k * per < na:
+                assert r[8][k * per] == k * mx
+    assert res[0][8][na] == res[0][6] + na               # compact: n_blocks = pairs + atoms

@@ -120,6 +120,7 @@ SIGNATURES = {
     "xtb_set_params_pettifor_rep": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(PettiforRepPair)]),
     "xtb_set_system": (C.c_int, [C.c_void_p, C.c_int, _pi, _pd, _pd]),
     "xtb_set_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "xtb_set_block_layout": (C.c_int, [C.c_void_p, C.c_int]),
     "xtb_neighbours": (C.c_int, [C.c_void_p, C.c_double, _pi, _pi, _pd, _pd]),
     "xtb_neighbours_compact": (C.c_int, [C.c_void_p, C.c_int, _pi, _pi, _pd, _pd, C.POINTER(C.c_int)]),
     "xtb_radial": (C.c_int, [C.c_void_p, _pd, _pd, _pd, _pd, _pd, _pd, _pd]),

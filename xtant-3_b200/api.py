@@ -116,6 +116,11 @@ class TBContext:
     def set_partition(self, first, last):
         self._ck(self.lib.xtb_set_partition(self.h, int(first), int(last)))
 
+    def set_block_layout(self, parts):
+        """block stores in `parts` equal-capacity segments (one per contiguous atom range of the row partition): the
+        ranges are then exchanged with one in-place all-gather (multigpu.allgather_blocks).  Before the neighbour list."""
+        self._ck(self.lib.xtb_set_block_layout(self.h, int(parts)))
+
     # -- S1 ---------------------------------------------------------------------------------
     def get_near_neighbours(self, rm=0.0, dense=False):
         """returns dict(size, list, dist, dist_s); dense=True gives the reference shapes

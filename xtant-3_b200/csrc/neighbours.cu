@@ -147,7 +147,11 @@ __global__ void __launch_bounds__(256) nn_build_kernel(int na, const double* __r
 
 // rowptr[i] = first block of atom i (blocks: on-site, then list order); rowptr[na] = n_blocks.
 // rev[e] = position of atom i in the list of its neighbour nn_list[e] (lists ascend in j) or -1.
-__global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* __restrict__ rowptr) {
+// parts > 1 (xtb_set_block_layout): the blocks of the `parts` contiguous atom ranges of the row partition (ceil(na/parts)
+// atoms each) start at multiples of the largest range's block count, so that the ranges are equal-length segments of every
+// block store and one in-place all-gather exchanges them.  The gaps are never addressed (every access is rowptr[atom] + q).
+// meta[1] = number of real blocks (na + number of list entries).
+__global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* __restrict__ rowptr, int parts, int* __restrict__ meta) {
     __shared__ int carry;
     __shared__ int buf[1024];
     if (threadIdx.x == 0) carry = 0;
@@ -168,7 +172,25 @@ __global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* _
         if (threadIdx.x == 1023) carry += buf[1023];
         __syncthreads();
     }
-    if (threadIdx.x == 0) rowptr[na] = carry;
+    if (threadIdx.x == 0) { rowptr[na] = carry; meta[1] = carry; }
+    if (parts <= 1) return;
+    __syncthreads();
+    // segment bases and the largest segment (parts <= 1024)
+    const int per = (na + parts - 1) / parts;
+    __shared__ int mx;
+    if (threadIdx.x == 0) mx = 0;
+    __syncthreads();
+    if ((int)threadIdx.x < parts) {
+        const int b = min(na, (int)threadIdx.x * per), e = min(na, ((int)threadIdx.x + 1) * per);
+        buf[threadIdx.x] = rowptr[b];
+        atomicMax(&mx, rowptr[e] - rowptr[b]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < na; i += 1024) {
+        const int r = i / per;
+        rowptr[i] = r * mx + (rowptr[i] - buf[r]);
+    }
+    if (threadIdx.x == 0) rowptr[na] = parts * mx;
 }
 
 // own[e] = 1 iff atom i "owns" the unordered pair (i, j = nn_list[e]) in the symmetric density pass: the pair is
@@ -259,7 +281,7 @@ int xtb_impl_neighbours(xtb_ctx* c, double rm) {
         c->cap = mx + 8 > na - 1 ? na - 1 : mx + 8;
         if (c->cap < mx) c->cap = mx;
     }
-    nn_rowptr_kernel<<<1, 1024, 0, c->stream>>>(na, (const int*)c->d_nn_size.p, (int*)c->d_rowptr.p);
+    nn_rowptr_kernel<<<1, 1024, 0, c->stream>>>(na, (const int*)c->d_nn_size.p, (int*)c->d_rowptr.p, c->layout_parts, (int*)c->d_maxnn.p);
     XTB_LAUNCH_CHECK(c);
     {
         const long long tot = (long long)na * c->cap;
@@ -268,15 +290,16 @@ int xtb_impl_neighbours(xtb_ctx* c, double rm) {
                                                                            (int*)c->d_rev.p, (signed char*)c->d_own.p);
         XTB_LAUNCH_CHECK(c);
     }
-    int nb = 0;
+    int nb = 0, nreal = 0;
     XTB_CUDA(c, cudaMemcpyAsync(&nb, (int*)c->d_rowptr.p + na, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaMemcpyAsync(&nreal, (int*)c->d_maxnn.p + 1, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     float ms = 0.f;
     cudaEventElapsedTime(&ms, c->ev0, c->ev1);
     c->stage_ms[1] = ms;
     c->n_blocks = nb;
-    c->n_pairs = nb - na;
+    c->n_pairs = nreal - na;      // real list entries (nb counts the layout gaps of xtb_set_block_layout as well)
     c->rm = rm;
     c->have_neigh = true;
     c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;

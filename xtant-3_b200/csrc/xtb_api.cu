@@ -18,6 +18,9 @@ int xtb_reserve(xtb_ctx* c, DevBuf& b, size_t bytes) {
         XTB_FAIL(c, XTB_ENOMEM, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
     }
     b.bytes = bytes;
+    // zero once at (re)allocation: padding that no kernel addresses (ELL slack, the gaps of xtb_set_block_layout) then holds
+    // zeros instead of stale memory, so whole-buffer copies and exchanges are deterministic
+    cudaMemsetAsync(b.p, 0, bytes, c->stream);
     return XTB_OK;
 }
 void xtb_free(DevBuf& b) {
@@ -188,6 +191,16 @@ int xtb_set_partition(xtb_ctx* c, int first, int last) {
     if (first < 1 || last > c->na || last < first - 1) XTB_FAIL(c, XTB_EINVAL, "xtb_set_partition: bad range %d..%d", first, last);
     c->a0 = first - 1; c->a1 = last;
     c->have_HS = c->have_density = false;
+    return XTB_OK;
+}
+
+int xtb_set_block_layout(xtb_ctx* c, int parts) {
+    if (!c) return XTB_EINVAL;
+    if (parts < 1 || parts > 1024) XTB_FAIL(c, XTB_EINVAL, "xtb_set_block_layout: parts = %d (1..1024)", parts);
+    if (parts != c->layout_parts) {
+        c->layout_parts = parts;
+        c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;     // rowptr changes: rebuild the list
+    }
     return XTB_OK;
 }
 

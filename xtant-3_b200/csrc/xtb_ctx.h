@@ -39,6 +39,7 @@ struct xtb_ctx {
     // system
     int na = 0;
     int a0 = 0, a1 = 0;         // owned atom range [a0, a1) (0-based)
+    int layout_parts = 1;       // block stores in this many equal-capacity segments (xtb_set_block_layout)
     double h_supce[9] = {0};
     DevBuf d_koa, d_S;          // int32 [na] (0-based kinds), double [3*na]
     // neighbour list (ELL, capacity cap) for ALL atoms (positions are replicated; the list is

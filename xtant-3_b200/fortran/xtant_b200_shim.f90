@@ -88,6 +88,9 @@ interface
    integer(c_int) function xtb_set_partition(c, first, last) bind(C, name="xtb_set_partition")
       import; type(c_ptr), value :: c; integer(c_int), value :: first, last
    end function
+   integer(c_int) function xtb_set_block_layout(c, parts) bind(C, name="xtb_set_block_layout")
+      import; type(c_ptr), value :: c; integer(c_int), value :: parts
+   end function
    integer(c_int) function xtb_neighbours(c, rm, nn_size, nn_list, nn_dist, nn_dist_s) bind(C, name="xtb_neighbours")
       import; type(c_ptr), value :: c; real(c_double), value :: rm
       integer(c_int32_t) :: nn_size(*), nn_list(*); real(c_double) :: nn_dist(*), nn_dist_s(*)

@@ -65,11 +65,14 @@ def _gather_segments(bufs, segs, rank, group=None):
         return
     lens = [e - b for b, e in segs]
     contiguous = all(segs[r][1] == segs[r + 1][0] for r in range(world - 1))
-    if len(bufs) == 1 and len(set(lens)) == 1 and lens[0] > 0 and contiguous:
-        buf = bufs[0]
+    if len(set(lens)) == 1 and lens[0] > 0 and contiguous:
+        # equal segments that tile the buffer (forces; block stores laid out with xtb_set_block_layout): in place
         b0, e1 = segs[0][0], segs[-1][1]
-        mine = buf[segs[rank][0]:segs[rank][1]].clone()
-        dist.all_gather_into_tensor(buf[b0:e1], mine, group=group)
+        for buf in bufs:
+            mine = buf[segs[rank][0]:segs[rank][1]]
+            if not (buf.is_cuda and dist.get_backend(group) == "nccl"):
+                mine = mine.clone()          # gloo does not take an input that aliases the output
+            dist.all_gather_into_tensor(buf[b0:e1], mine, group=group)
         return
     mx = max(lens)
     if mx == 0:
