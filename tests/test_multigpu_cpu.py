@@ -46,6 +46,22 @@ def _worker(rank, world, port, na, n_orb, seed, out):
         pair[0][b0:b1] = torch.from_numpy(full_blocks[b0:b1]); pair[1][b0:b1] = torch.from_numpy(-2.0 * full_blocks[b0:b1])
         mg.allgather_blocks(pair, rowptr, na, nb2, rank, world)
         assert np.array_equal(pair[0].numpy(), full_blocks) and np.array_equal(pair[1].numpy(), -2.0 * full_blocks)
+        # segmented block layout (xtb_set_block_layout): every rank's range starts at a multiple of the largest range's
+        # block count; the segments are equal and tile the buffer, so the pair goes through the in-place path
+        per = (na + world - 1) // world
+        cnt = [int(rowptr[min(na, (r + 1) * per)] - rowptr[min(na, r * per)]) for r in range(world)]
+        if min(cnt) > 0:
+            mx = max(cnt)
+            rp_seg = np.array([(i // per) * mx + int(rowptr[i] - rowptr[(i // per) * per]) for i in range(na)] + [world * mx])
+            full_seg = np.zeros(world * mx * nb2)
+            for i in range(na):
+                n = int(rowptr[i + 1] - rowptr[i]) * nb2
+                full_seg[rp_seg[i] * nb2:rp_seg[i] * nb2 + n] = full_blocks[int(rowptr[i]) * nb2:int(rowptr[i]) * nb2 + n]
+            s0, s1 = int(rp_seg[a0]) * nb2, int(rp_seg[a1]) * nb2
+            seg = [torch.full((full_seg.size,), np.nan, dtype=torch.float64) for _ in range(2)]
+            seg[0][s0:s1] = torch.from_numpy(full_seg[s0:s1]); seg[1][s0:s1] = torch.from_numpy(3.0 * full_seg[s0:s1])
+            mg.allgather_blocks(seg, rp_seg, na, nb2, rank, world)
+            assert np.array_equal(seg[0].numpy(), full_seg) and np.array_equal(seg[1].numpy(), 3.0 * full_seg)
         mg.allgather_panels(dense, na, n_orb, rank, world)
         mg.allgather_forces(F, na, rank, world)
         P = torch.arange(9, dtype=torch.float64) * (rank + 1)
