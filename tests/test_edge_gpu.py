@@ -128,12 +128,12 @@ def test_split_tail_round_gives_the_same_blocks(wk, api, monkeypatch):
         assert np.array_equal(r, res[0][0]) and np.array_equal(e, res[0][1])
 
 
-@pytest.mark.parametrize("name", ["diamond64", "au_4x4x5", "si216"])
+@pytest.mark.parametrize("name", ["c_3x3x3", "au_5x5x6", "si216"])
 def test_single_image_neighbour_path_is_bit_identical_to_the_27_image_scan(wk, api, monkeypatch, name):
     """orthorhombic cells with every edge > 2 rm take the one-image path (neighbours.cu, min_image_ortho); XTB_NN_SCAN27=1
     forces the reference's 27-image scan: same sizes, lists, distances and fractional shifts, bit for bit."""
-    wl = {"diamond64": wk.diamond64, "si216": wk.si216,
-          "au_4x4x5": lambda: wk.au_fcc((5, 5, 6), sigma=0.08, seed=11)}[name]()
+    wl = {"c_3x3x3": lambda: wk.c_dia((3, 3, 3), sigma=0.1, seed=5), "si216": wk.si216,
+          "au_5x5x6": lambda: wk.au_fcc((5, 5, 6), sigma=0.08, seed=11)}[name]()
     got = []
     for scan in ("1", "0"):
         monkeypatch.setenv("XTB_NN_SCAN27", scan)

@@ -181,3 +181,41 @@ def test_regression_values(orc, wk):
         np.testing.assert_allclose(o["Ei"][[0, len(o["Ei"]) // 2, -1]], r["Ei_pick"], rtol=1e-9, atol=1e-9, err_msg=name)
         np.testing.assert_allclose(o["F"][:4].ravel(), r["F_first4"], rtol=1e-7, atol=1e-8, err_msg=name)
         np.testing.assert_allclose(o["P"].ravel(order="F"), r["P"], rtol=1e-7, atol=1e-7, err_msg=name)
+
+
+@pytest.mark.parametrize("name", ["c_3x3x3", "si216", "au_5x5x6"])
+def test_single_image_rule_reproduces_the_27_image_scan(orc, wk, name):
+    """The claim behind the device's one-image neighbour path (neighbours.cu, min_image_ortho), checked on the CPU against
+    the oracle's 27-image scan (Atomic_tools.f90:4028-4131): in an orthorhombic cell with every edge > 2 rm the image the
+    scan ends with is, for every pair inside the cut-off, the per-axis minimum of |ds_k + zb| (ties to the later zb),
+    and evaluating that one image with the scan's own operation order gives the same bits."""
+    wl = {"c_3x3x3": lambda: wk.c_dia((3, 3, 3), sigma=0.1, seed=5), "si216": wk.si216,
+          "au_5x5x6": lambda: wk.au_fcc((5, 5, 6), sigma=0.08, seed=11)}[name]()
+    rm = orc.cutoff_radius(wl)
+    h = np.asarray(wl["supce"], dtype=np.float64)
+    assert np.count_nonzero(h - np.diag(np.diag(h))) == 0 and (np.abs(np.diag(h)) > 2.0 * rm * (1 + 1e-9)).all()
+    nb = orc.neighbours(wl)
+    S = np.asarray(wl["S"], dtype=np.float64)
+    na = wl["na"]
+    ds = S[:, None, :] - S[None, :, :]                                   # ds[i, j, k] = S_i(k) - S_j(k)
+    best = ds + (-1.0)
+    for zb in (0.0, 1.0):
+        v = ds + zb
+        take = np.abs(v) <= np.abs(best)
+        best = np.where(take, v, best)
+    # x_c = ((0 + d_0 supce(0,c)) + d_1 supce(1,c)) + d_2 supce(2,c)   (the reference accumulates from zero)
+    x = np.zeros((na, na, 3))
+    for c in range(3):
+        acc = np.zeros((na, na))
+        for k in range(3):
+            acc = acc + best[:, :, k] * h[k, c]
+        x[:, :, c] = acc
+    r = np.sqrt(x[:, :, 0] * x[:, :, 0] + x[:, :, 1] * x[:, :, 1] + x[:, :, 2] * x[:, :, 2])
+    isn = (r < rm) & ~np.eye(na, dtype=bool)
+    assert np.array_equal(isn.sum(axis=1), nb.size)
+    for i in range(na):
+        js = np.nonzero(isn[i])[0]                                      # ascending j: the list order
+        m = nb.size[i]
+        assert np.array_equal(js, nb.list[i, :m])
+        assert np.array_equal(x[i, js], nb.dist[i, :m, :3]) and np.array_equal(r[i, js], nb.dist[i, :m, 3])
+        assert np.array_equal(best[i, js], nb.dist_s[i, :m])
