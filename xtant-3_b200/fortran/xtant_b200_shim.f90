@@ -6,6 +6,8 @@
 !     use TB_NRL,      only : Construct_Vij_NRL, construct_TB_H_NRL, get_dHij_drij_NRL, Attract_TB_Forces_Press_NRL
 !     use TB_Pettifor, only : construct_TB_H_Pettifor, dHij_s, Attract_TB_Forces_Press
 !     use Atomic_tools,only : get_near_neighbours
+!     use TB_DFTB,     only : Construct_Vij_DFTB, construct_TB_H_DFTB, get_dHij_drij_DFTB, Attract_TB_Forces_Press_DFTB
+!     use Nonadiabatic,only : Electron_ion_coupling_Mij
 ! by   use XTANT_B200_shim   for those names (the rest of each module stays).  The `select type` dispatch in
 ! get_Hamilonian_and_E / create_and_diagonalize_H / Get_pressure (TB.f90:247-317,459-487,5551-5556) is unchanged:
 ! each `type is (TB_H_NRL)` / `type is (TB_H_Pettifor)` arm calls the same name with the same arguments as before.
@@ -21,12 +23,15 @@
 module XTANT_B200_shim
 use, intrinsic :: iso_c_binding
 use Objects, only : Super_cell, Numerics_param, solid, Error_handling, Save_error_details, &
-                    TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor
+                    TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor, TB_H_DFTB
 implicit none
 private
 public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_Aij, Construct_Aij_x_En, &
           get_dHij_drij_NRL, Attract_TB_Forces_Press_NRL, construct_TB_H_Pettifor, dHij_s, Attract_TB_Forces_Press, &
-          get_Erep_s, dErdr_s, dErdr_Pressure_s, xtb_b200_init, xtb_b200_finalize
+          get_Erep_s, dErdr_s, dErdr_Pressure_s, xtb_b200_init, xtb_b200_finalize, &
+          Construct_Vij_DFTB, construct_TB_H_DFTB, get_dHij_drij_DFTB, Attract_TB_Forces_Press_DFTB, &
+          Electron_ion_coupling_Mij, xtb_b200_set_partition, xtb_b200_assemble_blocks, xtb_b200_expand_dense, &
+          xtb_b200_density_mirror, xtb_b200_eigensolve
 
 ! ---- mirror of struct xtb_nrl_pair / xtb_pettifor_pair (include/xtb_b200.h) ----
 type, bind(C) :: xtb_nrl_pair
@@ -49,6 +54,11 @@ type, bind(C) :: xtb_pettifor_rep_pair      ! type(TB_Rep_Pettifor), Objects.f90
    real(c_double) :: phi0, d0, m, mc, dc, d1, dm
    real(c_double) :: c0(4)
 end type xtb_pettifor_rep_pair
+type, bind(C) :: xtb_dftb_pair              ! type(TB_H_DFTB), Objects.f90:202-222 (tables by address: they stay where they are)
+   real(c_double) :: rcut, d, Ed, Ep, Es
+   integer(c_int) :: n_r, pad_
+   type(c_ptr) :: Rr, Vr, Sr
+end type
 
 type(c_ptr), save :: ctx = c_null_ptr      ! one context per process (single caller thread, TB.f90:227-272)
 logical, save :: eigen_current = .false.   ! Ha/Ei/fe of this step already on the device
@@ -113,6 +123,45 @@ interface
    end function
    integer(c_int) function xtb_pressure(c, att) bind(C, name="xtb_pressure")
       import; type(c_ptr), value :: c; real(c_double) :: att(3,3)
+   end function
+   integer(c_int) function xtb_set_params_dftb(c, n_kinds, n_orb, p) bind(C, name="xtb_set_params_dftb")
+      import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds, n_orb; type(xtb_dftb_pair), intent(in) :: p(*)
+   end function
+   integer(c_int) function xtb_assemble_blocks(c) bind(C, name="xtb_assemble_blocks")
+      import; type(c_ptr), value :: c
+   end function
+   integer(c_int) function xtb_expand_dense(c, first, last, H_non, Sij) bind(C, name="xtb_expand_dense")
+      import; type(c_ptr), value :: c; integer(c_int), value :: first, last; type(c_ptr), value :: H_non, Sij
+   end function
+   integer(c_int) function xtb_density_mirror(c) bind(C, name="xtb_density_mirror")
+      import; type(c_ptr), value :: c
+   end function
+   integer(c_int) function xtb_set_density_cutoff(c, f_cut) bind(C, name="xtb_set_density_cutoff")
+      import; type(c_ptr), value :: c; real(c_double), value :: f_cut
+   end function
+   integer(c_int) function xtb_eigensolve(c, Ei, eigen_S, Ha) bind(C, name="xtb_eigensolve")
+      import; type(c_ptr), value :: c; type(c_ptr), value :: Ei, eigen_S, Ha
+   end function
+   integer(c_int) function xtb_get_eigenvalues(c, Ei) bind(C, name="xtb_get_eigenvalues")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: Ei(*)
+   end function
+   integer(c_int) function xtb_set_occupations(c, fe) bind(C, name="xtb_set_occupations")
+      import; type(c_ptr), value :: c; real(c_double), intent(in) :: fe(*)
+   end function
+   integer(c_int) function xtb_save_eigen_prev(c) bind(C, name="xtb_save_eigen_prev")
+      import; type(c_ptr), value :: c
+   end function
+   integer(c_int) function xtb_set_eigen_prev(c, Ha0) bind(C, name="xtb_set_eigen_prev")
+      import; type(c_ptr), value :: c; real(c_double), intent(in) :: Ha0(*)
+   end function
+   integer(c_int) function xtb_coupling(c, kind_M, Mij) bind(C, name="xtb_coupling")
+      import; type(c_ptr), value :: c; integer(c_int), value :: kind_M; type(c_ptr), value :: Mij
+   end function
+   integer(c_int) function xtb_sync(c) bind(C, name="xtb_sync")
+      import; type(c_ptr), value :: c
+   end function
+   real(c_double) function xtb_stage_ms(c, stage) bind(C, name="xtb_stage_ms")
+      import; type(c_ptr), value :: c; integer(c_int), value :: stage
    end function
 end interface
 
@@ -230,6 +279,8 @@ subroutine get_near_neighbours(Scell, numpar, include_vdW, dm)
             call push_params_pettifor(ARRAY)
          type is (TB_H_NRL)
             call push_params_nrl(ARRAY)
+         type is (TB_H_DFTB)
+            call push_params_dftb(ARRAY, numpar%basis_size_ind)
          end select
       END ASSOCIATE
       if (allocated(Scell(NSC)%TB_Repuls)) then
@@ -477,5 +528,164 @@ subroutine dErdr_Pressure_s(TB_Repuls, atoms, Scell, NSC, numpar)
       call check(xtb_repulsive_pressure(ctx, Scell(NSC)%SCforce%rep), 'xtb_repulsive_pressure')
    endif
 end subroutine dErdr_Pressure_s
+
+! ---- DFTB arms (TB_DFTB.f90:56,284,781,1135) ------------------------------------------------------
+! The radial tables Rr(:), Vr(:,:), Sr(:,:) of every TB_H_DFTB(KOA1,KOA2) are handed over by address (the library copies
+! them to the device once); n_orb follows identify_DFTB_orbitals_per_atom(numpar%basis_size_ind) (TB_DFTB.f90:2237-2248).
+subroutine push_params_dftb(TB, basis_size_ind)
+   type(TB_H_DFTB), dimension(:,:), intent(in), target :: TB
+   integer, intent(in) :: basis_size_ind
+   type(xtb_dftb_pair), allocatable :: p(:)
+   integer :: nk, i, j, k, n_orb
+   nk = size(TB,1)
+   allocate(p(nk*nk))
+   do j = 1, nk
+      do i = 1, nk
+         k = i + nk*(j-1)      ! p[(koa1-1) + n_kinds*(koa2-1)] = TB(koa1,koa2)
+         p(k)%rcut = TB(i,j)%rcut ; p(k)%d = TB(i,j)%d
+         p(k)%Ed = TB(i,j)%Ed ; p(k)%Ep = TB(i,j)%Ep ; p(k)%Es = TB(i,j)%Es
+         p(k)%n_r = int(size(TB(i,j)%Rr), c_int) ; p(k)%pad_ = 0_c_int
+         p(k)%Rr = c_loc(TB(i,j)%Rr) ; p(k)%Vr = c_loc(TB(i,j)%Vr) ; p(k)%Sr = c_loc(TB(i,j)%Sr)   ! Vr(ir,channel): column-major as the header asks
+      enddo
+   enddo
+   select case (basis_size_ind)
+   case (0) ; n_orb = 1
+   case (1) ; n_orb = 4
+   case default ; n_orb = 9
+   end select
+   call check(xtb_set_params_dftb(ctx, int(nk,c_int), int(n_orb,c_int), p), 'xtb_set_params_dftb')
+end subroutine push_params_dftb
+
+! S2a  TB_DFTB.f90:56.  As for NRL: the dense (Na,Na,N_bs) tables are only produced for un-grafted consumers.
+subroutine Construct_Vij_DFTB(numpar, TB, Scell, NSC, M_Vij, M_dVij, M_SVij, M_dSVij)
+   type(Numerics_param), intent(inout) :: numpar
+   type(TB_H_DFTB), dimension(:,:), intent(in) :: TB
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   real(8), dimension(:,:,:), allocatable, target :: M_Vij, M_dVij, M_SVij, M_dSVij
+   integer :: na, N_bs
+   na = size(Scell(NSC)%MDAtoms)
+   select case (numpar%basis_size_ind)      ! identify_DFTB_basis_size, TB_DFTB.f90:2224
+   case (0) ; N_bs = 1
+   case (1) ; N_bs = 4
+   case default ; N_bs = 10
+   end select
+   if (.not.allocated(M_Vij))   allocate(M_Vij(na,na,N_bs))
+   if (.not.allocated(M_dVij))  allocate(M_dVij(na,na,N_bs))
+   if (.not.allocated(M_SVij))  allocate(M_SVij(na,na,N_bs))
+   if (.not.allocated(M_dSVij)) allocate(M_dSVij(na,na,N_bs))
+   call check(xtb_radial(ctx, c_loc(M_Vij), c_loc(M_dVij), c_loc(M_SVij), c_loc(M_dSVij), &
+                         c_null_ptr, c_null_ptr, c_null_ptr), 'xtb_radial')
+end subroutine Construct_Vij_DFTB
+
+! S2b  TB_DFTB.f90:284.  Non-SCC arm only (the SCC corrections H_scc_0/1 are outside the graft, SURVEY.md 8).
+subroutine construct_TB_H_DFTB(numpar, matter, TB_Hamil, M_Vij, M_SVij, M_lmn, Scell, NSC, Err, scc, H_scc_0, H_scc_1)
+   use TB_NRL, only : solve_nonorthogonal => Loewdin_and_diagonalize_from_HS   ! the same split as for NRL (INTEGRATION.md)
+   type(Numerics_param), intent(inout) :: numpar
+   type(solid), intent(inout) :: matter
+   type(TB_H_DFTB), dimension(:,:), intent(in) :: TB_Hamil
+   real(8), dimension(:,:,:), intent(in) :: M_Vij, M_SVij, M_lmn
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(Error_handling), intent(inout) :: Err
+   integer, intent(in), optional :: scc
+   real(8), dimension(:,:), intent(inout), optional :: H_scc_0, H_scc_1
+   if (present(scc) .and. present(H_scc_0) .and. present(H_scc_1)) then
+      call Save_error_details(Err, 6, 'XTANT_B200_shim: the SCC arm of construct_TB_H_DFTB (TB_DFTB.f90:303-304) is not grafted')
+      return
+   endif
+   Scell(NSC)%Ha0 = Scell(NSC)%Ha            ! TB_DFTB.f90:298-300
+   Scell(NSC)%Ei0 = Scell(NSC)%Ei
+   Scell(NSC)%H_non0 = Scell(NSC)%H_non
+   call check(xtb_assemble_HS(ctx, c_loc(Scell(NSC)%H_non), c_loc(Scell(NSC)%Sij)), 'xtb_assemble_HS', Err)
+   Scell(NSC)%Hij = Scell(NSC)%H_non
+   call solve_nonorthogonal(numpar, Scell, NSC, Err)      ! Ha, Ei, eigen_S, Hij_sol; then find_band_gap (:314)
+   eigen_current = .false.
+end subroutine construct_TB_H_DFTB
+
+! S4   TB_DFTB.f90:781
+subroutine get_dHij_drij_DFTB(numpar, Scell, NSC, Aij, M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn, Aij_x_Ei)
+   type(Numerics_param), intent(inout) :: numpar
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   real(8), dimension(:,:,:), intent(in) :: M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn
+   real(8), dimension(:,:), intent(in) :: Aij, Aij_x_Ei
+   real(c_double), allocatable :: F(:,:)
+   integer :: k, na
+   na = size(Scell(NSC)%MDatoms)
+   allocate(F(3,na))
+   call check(xtb_forces(ctx, F), 'xtb_forces')        ! uses the device-resident rho, rho_E of this step
+   do k = 1, na
+      Scell(NSC)%MDatoms(k)%forces%att(:) = F(:,k)
+   enddo
+end subroutine get_dHij_drij_DFTB
+
+! S5   TB_DFTB.f90:1135
+subroutine Attract_TB_Forces_Press_DFTB(Scell, NSC, numpar, Aij, M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn, Aij_x_Ei)
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), dimension(:,:,:), intent(in) :: M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn
+   real(8), dimension(:,:), intent(in) :: Aij, Aij_x_Ei
+   if (numpar%p_const) then
+      call check(xtb_pressure(ctx, Scell(NSC)%SCforce%att), 'xtb_pressure')
+   endif
+end subroutine Attract_TB_Forces_Press_DFTB
+
+! ---- nonadiabatic coupling (Nonadiabatic.f90:782-945) ---------------------------------------------
+! Ha and the overlap blocks of this step are on the device already (xtb_set_eigen / xtb_eigensolve, xtb_assemble_HS);
+! Ha0 is uploaded unless xtb_save_eigen_prev kept it there.  wr and Sij are part of the reference signature only.
+subroutine Electron_ion_coupling_Mij(wr, Ha, Ha0, Mij, kind_M, Sij)
+   real(8), dimension(:), intent(in) :: wr
+   real(8), dimension(:,:), intent(in) :: Ha, Ha0
+   real(8), dimension(:,:), allocatable, intent(inout), target :: Mij
+   integer, intent(in), optional :: kind_M
+   real(8), dimension(:,:), intent(in), optional :: Sij
+   integer(c_int) :: km
+   integer :: N
+   N = size(wr)
+   if (.not. allocated(Mij)) allocate(Mij(N,N))
+   km = 0_c_int                                  ! default arm: Tully (Nonadiabatic.f90:876)
+   if (present(kind_M)) km = int(kind_M, c_int)
+   if (.not. eigen_current) call check(xtb_set_eigen(ctx, Ha, wr, wr), 'xtb_set_eigen')   ! occupations are not used by the coupling
+   call check(xtb_set_eigen_prev(ctx, Ha0), 'xtb_set_eigen_prev')
+   call check(xtb_coupling(ctx, km, c_loc(Mij)), 'xtb_coupling')
+end subroutine Electron_ion_coupling_Mij
+
+! ---- MPI build (TB_NRL.f90:267-327, MPI_subroutines.f90:3965-3982) ---------------------------------
+! Each rank owns a contiguous range of atoms.  The block ranges are exchanged by the host program (one MPI_Allgatherv /
+! NCCL all-gather per block store on the device pointers of xtb_device_buffer) between these calls; see INTEGRATION.md.
+subroutine xtb_b200_set_partition(first, last, n_ranks)
+   integer, intent(in) :: first, last
+   integer, intent(in), optional :: n_ranks      ! equal-capacity segments: the exchange is then one in-place all-gather
+   if (present(n_ranks)) call check(xtb_set_block_layout(ctx, int(n_ranks,c_int)), 'xtb_set_block_layout')
+   call check(xtb_set_partition(ctx, int(first,c_int), int(last,c_int)), 'xtb_set_partition')
+end subroutine xtb_b200_set_partition
+
+subroutine xtb_b200_assemble_blocks()
+   call check(xtb_assemble_blocks(ctx), 'xtb_assemble_blocks')
+end subroutine xtb_b200_assemble_blocks
+
+subroutine xtb_b200_expand_dense(first, last, H_non, Sij)
+   integer, intent(in) :: first, last
+   real(8), dimension(:,:), intent(inout), target :: H_non, Sij
+   call check(xtb_expand_dense(ctx, int(first,c_int), int(last,c_int), c_loc(H_non), c_loc(Sij)), 'xtb_expand_dense')
+end subroutine xtb_b200_expand_dense
+
+subroutine xtb_b200_density_mirror()
+   call check(xtb_density_mirror(ctx), 'xtb_density_mirror')
+end subroutine xtb_b200_density_mirror
+
+! on-device eigensolve (Loewdin + Dsyevd + back-transform as TB_NRL.f90:985-1060,402-421) for device-resident steps
+subroutine xtb_b200_eigensolve(Ei, eigen_S, Ha)
+   real(8), dimension(:), intent(out), target :: Ei, eigen_S
+   real(8), dimension(:,:), intent(out), target, optional :: Ha
+   if (present(Ha)) then
+      call check(xtb_eigensolve(ctx, c_loc(Ei), c_loc(eigen_S), c_loc(Ha)), 'xtb_eigensolve')
+   else
+      call check(xtb_eigensolve(ctx, c_loc(Ei), c_loc(eigen_S), c_null_ptr), 'xtb_eigensolve')
+   endif
+   eigen_current = .true.
+end subroutine xtb_b200_eigensolve
 
 end module XTANT_B200_shim
