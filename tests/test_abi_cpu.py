@@ -61,3 +61,28 @@ def test_product_never_imports_oracle():
                 for line in txt.splitlines():
                     if re.search(r"^\s*(import|from|#include)\b.*oracle", line) or "liboracle" in line:
                         raise AssertionError(f"{f} reaches into oracle/: {line.strip()}")
+
+
+def test_fortran_shim_interfaces_match_the_header():
+    """the ISO_C_BINDING interface block of the shim (no Fortran compiler here: checked by parsing) binds only symbols the
+    header declares, with the same number of arguments, and covers every entry point a Fortran caller of the path needs"""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "xtb_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", " ", hdr, flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\b(xtb_[A-Za-z_0-9]+)\s*\(([^;{]*?)\)\s*;", hdr, flags=re.S):
+        args = m.group(2).strip()
+        protos[m.group(1)] = 0 if args in ("", "void") else len(args.split(","))
+    shim = open(os.path.join(root, "xtant-3_b200", "fortran", "xtant_b200_shim.f90")).read()
+    bound = {}
+    for m in re.finditer(r"function\s+(xtb_[A-Za-z_0-9]+)\s*\(([^)]*)\)\s*bind\(C,\s*name=\"(xtb_[A-Za-z_0-9]+)\"\)", shim, flags=re.I):
+        assert m.group(1).lower() == m.group(3).lower()
+        bound[m.group(3)] = len([a for a in m.group(2).split(",") if a.strip()])
+    assert len(bound) >= 30
+    for name, n in bound.items():
+        assert name in protos, f"shim binds {name}, which the header does not declare"
+        assert protos[name] == n, f"{name}: {n} arguments in the shim, {protos[name]} in the header"
+    # introspection / zero-copy / stream entry points are for the Python and C++ hosts; everything else must be bound
+    host_only = {"xtb_version", "xtb_set_stream", "xtb_counter", "xtb_device_buffer", "xtb_neighbours_compact", "xtb_set_eigen_device"}
+    assert set(protos) - set(bound) <= host_only, sorted(set(protos) - set(bound) - host_only)
