@@ -86,3 +86,35 @@ def test_fortran_shim_interfaces_match_the_header():
     # introspection / zero-copy / stream entry points are for the Python and C++ hosts; everything else must be bound
     host_only = {"xtb_version", "xtb_set_stream", "xtb_counter", "xtb_device_buffer", "xtb_neighbours_compact", "xtb_set_eigen_device"}
     assert set(protos) - set(bound) <= host_only, sorted(set(protos) - set(bound) - host_only)
+
+
+def test_fortran_shim_struct_mirrors_match_ctypes_layout():
+    """the bind(C) derived types of the shim have the field order, counts and sizes of the ctypes mirrors of the header
+    structs (which test_struct_layout_matches_header ties to the header itself)"""
+    import re
+    import ctypes as CT
+    import importlib
+    abi = importlib.import_module("xtant-3_b200._abi")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    shim = open(os.path.join(root, "xtant-3_b200", "fortran", "xtant_b200_shim.f90")).read()
+    mirrors = {"xtb_nrl_pair": abi.NrlPair, "xtb_pettifor_pair": abi.PettiforPair,
+               "xtb_pettifor_rep_pair": abi.PettiforRepPair, "xtb_dftb_pair": abi.DftbPair}
+    size = {"c_double": 8, "c_int": 4, "c_int32_t": 4, "c_ptr": 8}
+    for name, cls in mirrors.items():
+        m = re.search(r"type,\s*bind\(C\)\s*::\s*" + name + r"\b(.*?)end type", shim, flags=re.S | re.I)
+        assert m, name
+        fields = []
+        for line in m.group(1).splitlines():
+            line = line.split("!")[0].strip()
+            mm = re.match(r"(?:real|integer|type)\((\w+)\)\s*::\s*(.*)", line)
+            if not mm:
+                continue
+            for item in re.findall(r"(\w+)(?:\((\d+)\))?", mm.group(2)):
+                fields.append((item[0], size[mm.group(1)], int(item[1]) if item[1] else 1))
+        ct = [(n, CT.sizeof(t)) for n, t in cls._fields_]
+        assert [f[0] for f in fields] == [n for n, _ in ct], (name, [f[0] for f in fields], [n for n, _ in ct])
+        assert [f[1] * f[2] for f in fields] == [s for _, s in ct], name
+        off = 0                                          # natural alignment, as bind(C) and the C compiler lay it out
+        for _, sz, cnt in fields:
+            off = (off + sz - 1) // sz * sz + sz * cnt
+        assert (off + 7) // 8 * 8 == CT.sizeof(cls), name
