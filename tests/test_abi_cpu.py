@@ -118,3 +118,23 @@ def test_fortran_shim_struct_mirrors_match_ctypes_layout():
         for _, sz, cnt in fields:
             off = (off + sz - 1) // sz * sz + sz * cnt
         assert (off + 7) // 8 * 8 == CT.sizeof(cls), name
+
+
+def test_fortran_shim_wrappers_keep_the_reference_argument_lists():
+    """every reference procedure the shim re-exposes has the reference's own dummy-argument list (names and order), as
+    recorded from the reference sources by tests/golden/make_signatures.py"""
+    import json
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    ref = json.load(open(os.path.join(root, "tests", "golden", "reference_signatures.json")))
+    shim = open(os.path.join(root, "xtant-3_b200", "fortran", "xtant_b200_shim.f90")).read()
+    shim = re.sub(r"&\s*\n\s*&?", " ", shim)
+    mine = {}
+    for m in re.finditer(r"^\s*subroutine\s+(\w+)\s*\(([^)]*)\)", shim, flags=re.M | re.I):
+        mine.setdefault(m.group(1).lower(), [a.strip().lower() for a in m.group(2).split(",") if a.strip()])
+    pub = re.search(r"public ::(.*?)\n\s*\n", shim, flags=re.S).group(1).lower()
+    assert len(ref) == 18
+    for name, sig in ref.items():
+        assert name.lower() in mine, name
+        assert re.search(r"\b" + name.lower() + r"\b", pub), f"{name} is not public in the shim"
+        assert mine[name.lower()] == sig["args"], (name, sig["file"], mine[name.lower()], sig["args"])
