@@ -138,3 +138,14 @@ def test_fortran_shim_wrappers_keep_the_reference_argument_lists():
         assert name.lower() in mine, name
         assert re.search(r"\b" + name.lower() + r"\b", pub), f"{name} is not public in the shim"
         assert mine[name.lower()] == sig["args"], (name, sig["file"], mine[name.lower()], sig["args"])
+
+
+def test_python_host_mirror_has_the_reference_procedure_names():
+    """the host-side mirror (api.TBContext) exposes every re-exposed reference procedure under its own name"""
+    import importlib
+    import json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    api = importlib.import_module("xtant-3_b200.api")
+    ref = json.load(open(os.path.join(root, "tests", "golden", "reference_signatures.json")))
+    missing = [n for n in ref if not callable(getattr(api.TBContext, n, None))]
+    assert not missing, missing

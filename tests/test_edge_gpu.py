@@ -183,3 +183,34 @@ def test_segmented_block_layout_gives_identical_results(wk, api):
             if k * per < na:
                 assert r[8][k * per] == k * mx
     assert res[0][8][na] == res[0][6] + na               # compact: n_blocks = pairs + atoms
+
+
+def test_reference_procedure_names_on_the_host_mirror(wk, api):
+    """the reference-named methods are the same calls as the generic ones, and refuse the wrong parametrisation arm"""
+    wl = wk.au_fcc((2, 2, 2))
+    c = api.TBContext(0); c.set_workload(wl)
+    c.get_near_neighbours()
+    H, S = c.construct_TB_H_NRL()
+    H2, S2 = c.assemble_HS()
+    assert np.array_equal(H, H2) and np.array_equal(S, S2)
+    t = c.Construct_Vij_NRL()
+    assert t["M_Vij"].shape == (wl["na"], wl["na"], 10)
+    C_, E, fe = wk.synthetic_eigen(wl["na"] * 9, seed=4)
+    c.set_eigen(C_, E, fe)
+    A = c.Construct_Aij(); AE = c.Construct_Aij_x_En()
+    A2, AE2 = c.density(dense=True)
+    assert np.array_equal(A, A2) and np.array_equal(AE, AE2)
+    assert np.array_equal(c.get_dHij_drij_NRL(), c.forces())
+    assert np.array_equal(c.Attract_TB_Forces_Press_NRL(), c.pressure())
+    for wrong in (c.dHij_s, c.construct_TB_H_Pettifor, c.get_dHij_drij_DFTB, c.Construct_Vij_DFTB):
+        with pytest.raises(api.XtbError):
+            wrong()
+    c.close()
+    wlp = wk.diamond64()
+    c = api.TBContext(0); c.set_workload(wlp)
+    c.get_near_neighbours()
+    Hp = c.construct_TB_H_Pettifor()
+    assert np.array_equal(Hp, c.assemble_HS()[0])
+    with pytest.raises(api.XtbError):
+        c.construct_TB_H_NRL()
+    c.close()

@@ -282,3 +282,71 @@ class TBContext:
         M = np.zeros((N, N), order="F")
         self._ck(self.lib.xtb_coupling(self.h, int(kind_M), _dp(M)))
         return M
+
+    # -- the reference's own procedure names for the same calls (the parametrisation arms of TB.f90:247-317,459-487) ----
+    def _arm(self, *kinds):
+        if self.tb not in kinds:
+            raise XtbError(-1, f"this context holds a {self.tb!r} parametrisation; the procedure belongs to {kinds}")
+
+    def Construct_Vij_NRL(self):
+        """Construct_Vij_NRL, TB_NRL.f90:1956 -> dict(M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn, M_x1, M_xrr), dense shapes"""
+        self._arm("nrl")
+        return self.radial_tables()
+
+    def Construct_Vij_DFTB(self):
+        """Construct_Vij_DFTB, TB_DFTB.f90:56"""
+        self._arm("dftb")
+        return self.radial_tables()
+
+    def construct_TB_H_NRL(self):
+        """construct_TB_H_NRL -> Hamil_tot_NRL assembly part, TB_NRL.f90:74,226-397 -> (H_non, Sij); the eigensolve stays outside"""
+        self._arm("nrl")
+        return self.assemble_HS()
+
+    def construct_TB_H_Pettifor(self):
+        """construct_TB_H_Pettifor -> Hamil_tot, TB_Pettifor.f90:1427,1658 -> H (orthogonal basis: no overlap matrix)"""
+        self._arm("pettifor")
+        return self.assemble_HS()[0]
+
+    def construct_TB_H_DFTB(self):
+        """construct_TB_H_DFTB -> Hamil_tot_DFTB, TB_DFTB.f90:284,319 (non-SCC arm) -> (H_non, Sij)"""
+        self._arm("dftb")
+        return self.assemble_HS()
+
+    def Construct_Aij(self):
+        """Construct_Aij, TB.f90:4328 -> Aij (N,N), zero outside the neighbour pattern"""
+        return self.density(dense=True)[0]
+
+    def Construct_Aij_x_En(self):
+        """Construct_Aij_x_En, TB.f90:4401 -> Aij_x_Ei (N,N)"""
+        return self.density(dense=True)[1]
+
+    def get_dHij_drij_NRL(self):
+        """get_dHij_drij_NRL, TB_NRL.f90:2412 -> MDatoms(:)%forces%att as (na, 3), dE/ds [eV]"""
+        self._arm("nrl")
+        return self.forces()
+
+    def dHij_s(self):
+        """dHij_s, TB_Pettifor.f90:141"""
+        self._arm("pettifor")
+        return self.forces()
+
+    def get_dHij_drij_DFTB(self):
+        """get_dHij_drij_DFTB, TB_DFTB.f90:781"""
+        self._arm("dftb")
+        return self.forces()
+
+    def Attract_TB_Forces_Press_NRL(self):
+        """Attract_TB_Forces_Press_NRL, TB_NRL.f90:2742 -> SCforce%att (3,3)"""
+        self._arm("nrl")
+        return self.pressure()
+
+    def Attract_TB_Forces_Press(self):
+        """Attract_TB_Forces_Press, TB_Pettifor.f90:1134"""
+        self._arm("pettifor")
+        return self.pressure()
+
+    def Attract_TB_Forces_Press_DFTB(self):
+        """Attract_TB_Forces_Press_DFTB, TB_DFTB.f90:1135"""
+        self._arm("dftb")
+        return self.pressure()
