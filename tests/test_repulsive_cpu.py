@@ -16,6 +16,7 @@ import pytest
 
 A_DIAMOND = 3.5588     # INPUT_DATA/Diamond/Unit_cell_equilibrium.txt:1-3
 A_GOLD = 4.0782        # INPUT_DATA/Gold/Unit_cell_equilibrium.txt:1-3
+A_SILICON = 5.44       # INPUT_DATA/Silicon/Unit_cell_equilibrium.txt:1-3
 
 
 @pytest.fixture(scope="module")
@@ -112,6 +113,24 @@ def test_physics_pin_gold_lattice_constant(wk, orc):
     a_min = _fit_minimum(sc, np.array(E)) * A_GOLD
     assert abs(a_min / A_GOLD - 1.0) < 5e-3, a_min              # measured: 4.0757 A (0.06 %) on the 108-atom Gamma-point cell
     assert -4.0 < E[2] < -3.5                                   # eV/atom (measured -3.687; 4x4x4 cell: -3.821)
+
+
+def test_physics_pin_silicon_lattice_constant(wk, orc):
+    """Third pin, sp3d5 NRL set with split d on-site levels (INPUT_DATA/Silicon/NRL): the band energy of diamond-structure Si
+    is minimal at the reference's own equilibrium cell (5.44 A; the oracle gives 5.433 A on the 64-atom Gamma-point cell)."""
+    sc = np.array([0.94, 0.97, 1.0, 1.03, 1.06])
+    E = []
+    for s in sc:
+        S, h = wk.lattice(wk._DIA, A_SILICON * s, (2, 2, 2), 0.0, 0)
+        wl = wk._wl("x", "nrl", "Si", S, h, 4, 0.1)
+        nb = orc.neighbours(wl)
+        lmn, xrr, x1 = orc.geometry(wl, nb)
+        H, Sm = orc.nrl_assemble_HS(wl, nb, lmn, orc.nrl_radial(wl, nb))
+        Ha, Ei, wS = orc.eigensolve_nonorthogonal(H, Sm)
+        fe, mu = wk.occupations(Ei, wl["n_electrons"], wl["Te_eV"])
+        E.append((fe * Ei).sum() / wl["na"])
+    a_min = _fit_minimum(sc, np.array(E)) * A_SILICON
+    assert abs(a_min / A_SILICON - 1.0) < 5e-3, a_min           # measured: 5.4329 A (0.13 %)
 
 
 # ---- readers -------------------------------------------------------------------------------------------------
