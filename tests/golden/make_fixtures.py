@@ -5,6 +5,7 @@ Run once in the build container (needs /root/reference, which does not exist on 
     python tests/golden/make_fixtures.py
 It writes
     xtant-3_b200/data/params_nrl_{Au,Al,Si}.json    NRL parameter sets
+    xtant-3_b200/data/params_pettifor{,_rep}_Si.json   second Pettifor-type set (Silicon/Pettifor): physics pin of the oracle
     xtant-3_b200/data/params_pettifor_C.json        Pettifor parameter set
     xtant-3_b200/data/params_pettifor_rep_C.json    Pettifor repulsive parameter set
     xtant-3_b200/data/cell_{diamond64,al500,au108}.json   relative coords + supercell
@@ -42,6 +43,8 @@ def main():
         "params_nrl_Si.json": lambda: parse_nrl(f"{REF}/Silicon/NRL/Si_Si_TB_Hamiltonian_parameters.txt"),
         "params_pettifor_C.json": lambda: parse_pettifor(f"{REF}/Diamond/C_C_TB_Hamiltonian_parameters.txt"),
         "params_pettifor_rep_C.json": lambda: parse_pettifor_rep(f"{REF}/Diamond/C_C_TB_Repulsive_parameters.txt"),
+        "params_pettifor_Si.json": lambda: parse_pettifor(f"{REF}/Silicon/Pettifor/Si_Si_TB_Hamiltonian_parameters.txt"),
+        "params_pettifor_rep_Si.json": lambda: parse_pettifor_rep(f"{REF}/Silicon/Pettifor/Si_Si_TB_Repulsive_parameters.txt"),
         "cell_diamond64.json": lambda: parse_cell(f"{REF}/Diamond/64_atoms/SAVE_atoms.dat",
                                                   f"{REF}/Diamond/64_atoms/SAVE_supercell.dat"),
         "cell_al500.json": lambda: parse_cell(f"{REF}/Aluminum/SAVE_atoms_500atoms.dat",

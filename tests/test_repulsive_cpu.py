@@ -133,6 +133,24 @@ def test_physics_pin_silicon_lattice_constant(wk, orc):
     assert abs(a_min / A_SILICON - 1.0) < 5e-3, a_min           # measured: 5.4329 A (0.13 %)
 
 
+def test_physics_pin_silicon_pettifor_set(wk, orc):
+    """Fourth pin, a second Pettifor-type set read from the reference's own parameter files (INPUT_DATA/Silicon/Pettifor,
+    through readers.py): E_band + E_rep of diamond-structure Si is minimal at 5.4515 A (reference cell 5.44 A, 0.2 %) with
+    a depth of -4.60 eV/atom (the cohesive energy of silicon the set was fitted to is 4.6 eV)."""
+    sc = np.array([0.95, 0.975, 1.0, 1.025, 1.05])
+    E = []
+    for s in sc:
+        S, h = wk.lattice(wk._DIA, A_SILICON * s, (2, 2, 2), 0.0, 0)
+        wl = wk._wl("x", "pettifor", "Si", S, h, 4, 0.025)
+        nb = orc.neighbours(wl)
+        Ha, Ei = orc.eigensolve_orthogonal(orc.pet_assemble_H(wl, nb))
+        fe, mu = wk.occupations(Ei, wl["n_electrons"], wl["Te_eV"])
+        E.append(((fe * Ei).sum() + orc.pet_erep(wl, nb)[0]) / wl["na"])
+    a_min = _fit_minimum(sc, np.array(E)) * A_SILICON
+    assert abs(a_min / A_SILICON - 1.0) < 5e-3, a_min           # measured: 5.4515 A
+    assert -4.75 < E[2] < -4.45                                  # measured -4.599 eV/atom
+
+
 # ---- readers -------------------------------------------------------------------------------------------------
 def test_readers_round_trip(tmp_path, wk):
     rd = importlib.import_module("xtant-3_b200.readers")
