@@ -1,6 +1,6 @@
 """CPU tests of the repulsive part of the Pettifor-type branch, oracle/pettifor_oracle.c
 (get_Erep_s, dErdr_s, dErdr_Pressure_s; TB_Pettifor.f90:2074,2162,2634), of the input-file readers
-(xtant-3_b200/readers.py) and two PHYSICS PINS of the oracle against the reference's own fixtures:
+(xtant-3_b200/readers.py) and four PHYSICS PINS of the oracle against the reference's own fixtures:
 
 The reference ships no expected numbers for this path, but it ships the equilibrium lattice constants its
 parametrisations were relaxed to (INPUT_DATA/<material>/Unit_cell_equilibrium.txt).  The oracle's total energy
@@ -178,6 +178,12 @@ def test_readers_on_the_reference_files(wk):
     assert rd.read_Pettifor_TB_repulsive(f"{ref}/Diamond/C_C_TB_Repulsive_parameters.txt") == wk.load_params("pettifor_rep", "C")
     assert rd.read_Pettifor_TB_Hamiltonian(f"{ref}/Diamond/C_C_TB_Hamiltonian_parameters.txt") == wk.load_params("pettifor", "C")
     assert rd.read_Mehl_TB_Hamiltonian(f"{ref}/Gold/NRL/Au_Au_TB_Hamiltonian_parameters.txt") == wk.load_params("nrl", "Au")
+    assert rd.read_Mehl_TB_Hamiltonian(f"{ref}/Silicon/NRL/Si_Si_TB_Hamiltonian_parameters.txt") == wk.load_params("nrl", "Si")
+    assert rd.read_Mehl_TB_Hamiltonian(f"{ref}/Aluminum/NRL/Al_Al_TB_Hamiltonian_parameters.txt") == wk.load_params("nrl", "Al")
+    assert rd.read_Pettifor_TB_Hamiltonian(f"{ref}/Silicon/Pettifor/Si_Si_TB_Hamiltonian_parameters.txt") == wk.load_params("pettifor", "Si")
+    assert rd.read_Pettifor_TB_repulsive(f"{ref}/Silicon/Pettifor/Si_Si_TB_Repulsive_parameters.txt") == wk.load_params("pettifor_rep", "Si")
+    s = rd.read_unit_cell(f"{ref}/Silicon/Unit_cell_equilibrium.txt", f"{ref}/Silicon/Unit_cell_atom_relative_coordinates.txt", (1, 1, 1))
+    assert np.allclose(np.diag(s["supce"]), A_SILICON) and len(s["koa"]) == 8
     assert rd.read_SAVE(f"{ref}/Aluminum/SAVE_atoms_500atoms.dat", f"{ref}/Aluminum/SAVE_supercell_500atoms.dat") == wk._load("cell_al500.json")
     u = rd.read_unit_cell(f"{ref}/Gold/Unit_cell_equilibrium.txt", f"{ref}/Gold/Unit_cell_atom_relative_coordinates.txt", (2, 2, 3))
     assert len(u["koa"]) == 48 and np.allclose(np.diag(u["supce"]), [2 * A_GOLD, 2 * A_GOLD, 3 * A_GOLD])
