@@ -10,7 +10,10 @@
  * restatement is pinned only by (i) line-by-line correspondence with the cited reference
  * lines, (ii) agreement of its two algorithmic forms (verbatim dense per-atom derivative
  * matrices vs. sparse-equivalent), (iii) physical invariants and finite differences of the
- * parts that are exact derivatives (tests/test_oracle_*.py).
+ * parts that are exact derivatives (tests/test_oracle_*.py), (iv) four physics known-answers
+ * on the reference's own input files: the total energy of this restatement is minimal at the
+ * equilibrium cells the reference ships for its C and Si Pettifor-type sets and its Au and Si
+ * NRL sets, to 0.06-0.2 % (tests/test_repulsive_cpu.py).
  *
  * Every function cites the reference lines (under Source_files/) it follows.
  * Build: see oracle/Makefile (gcc -O2 -ffp-contract=off -fopenmp; no FMA contraction so the
