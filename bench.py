@@ -467,22 +467,29 @@ def run_e2e_multi(torch, ctx, wl, E, fe, world, rank, a0, a1, args):
                     + "rho blocks and forces exchanged over NVLink (all-gather); dense H_non / Sij and the eigenvectors never cross PCIe"}
 
 
-def cpu_sample(wl, args, check=None, n_panel=48, n_dens=16, n_force=96):
-    """oracle (CPU restatement of the reference algorithm, sparse-equivalent form) on a bounded sample of the SAME
-    workload, host cores only (no GPU anywhere in this function): full neighbour list + radial tables + `n_panel`
-    H/S column panels + rho/rho_E blocks of `n_dens` atoms + forces of `n_force` atoms, each extrapolated linearly
-    in atoms (every stage is an equal-work loop over atoms).  Eigenvector rows / rho blocks are synthetic of the
-    same shape and distribution (timing does not depend on their values).
-    check = (rowptr, rho, rhoE, F) numpy copies of a device step: the force sample then runs on the device's own
-    rho blocks and doubles as a full-size parity spot check."""
+def cpu_sample(wl, args, check=None, n_dens=256, threads=None):
+    """oracle (CPU restatement of the reference algorithm, sparse-equivalent form) on the SAME workload, host cores only (no
+    GPU anywhere in this function).  The cheap stages run IN FULL: neighbour list, radial tables, H/S assembly of every
+    column panel (in slabs of 128 atoms, each slab's dense panels written and dropped) and the forces of every atom.  Only
+    the rho / rho_E contraction is sampled: the blocks of the first `n_dens` atoms (all their neighbours' eigenvector rows
+    gathered), scaled by na / n_dens -- every atom of the cell has the same number of blocks within 3 %.
+    Eigenvector rows / rho blocks are synthetic of the same shape and distribution (timing does not depend on the values).
+    check = (rowptr, rho, rhoE, F) numpy copies of a device step: the forces then run on the device's own rho blocks
+    and double as a full-size parity check.  threads: OpenMP threads to pin (default: all host cores)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import oracle as orc
     wk = importlib.import_module("xtant-3_b200.workloads")
+    cores = orc.set_num_threads(threads or os.cpu_count() or 1)
     na, N = wl["na"], wl["na"] * 9
+    n_dens = min(n_dens, na)
     t = {}
     t0 = time.perf_counter(); nb = orc.neighbours(wl, cap=128); t["neighbours"] = time.perf_counter() - t0
     t0 = time.perf_counter(); lmn, xrr, x1 = orc.geometry(wl, nb); rad = orc.nrl_radial(wl, nb); t["radial"] = time.perf_counter() - t0
-    t0 = time.perf_counter(); orc.nrl_assemble_panels(wl, nb, lmn, rad, 0, n_panel); t["assembly"] = (time.perf_counter() - t0) * na / n_panel
+    t0 = time.perf_counter()
+    slab = 128
+    for j0 in range(0, na, slab):
+        orc.nrl_assemble_panels(wl, nb, lmn, rad, j0, min(j0 + slab, na))
+    t["assembly"] = time.perf_counter() - t0
     # eigenvector rows of the sampled atoms and their neighbours
     rng = np.random.default_rng(7)
     E = np.sort(rng.uniform(-10.0, 40.0, size=N))
@@ -494,13 +501,22 @@ def cpu_sample(wl, args, check=None, n_panel=48, n_dens=16, n_force=96):
     Ct = rng.standard_normal((len(atoms) * 9, kk)) / np.sqrt(N)
     t0 = time.perf_counter()
     orc.density_blocks_rows(nb, 9, Ct, rowmap, fe[keep], E[keep], 0, n_dens)
-    t["density"] = (time.perf_counter() - t0) * na / n_dens
+    dens_sample = time.perf_counter() - t0
+    t["density"] = dens_sample * na / n_dens
+    del Ct
     # what the reference itself does for rho and rho_E: two dense dgemm('N','T') of order N (TB.f90:4386,4465);
     # sampled as a 256-row panel with numpy's BLAS, scaled to N rows.  Reported beside, not inside, `value`.
     m = 256
     A = rng.standard_normal((m, kk)); B = rng.standard_normal((2304, kk))
-    t0 = time.perf_counter(); (A @ B.T); td = time.perf_counter() - t0
+    try:                                   # numpy's BLAS took its thread count from the environment at import: pin it as well
+        from threadpoolctl import threadpool_limits
+        with threadpool_limits(limits=cores):
+            (A[:8] @ B.T)
+            t0 = time.perf_counter(); (A @ B.T); td = time.perf_counter() - t0
+    except ImportError:
+        t0 = time.perf_counter(); (A @ B.T); td = time.perf_counter() - t0
     dense_ms = 1e3 * 2 * td * (N / m) * (N / 2304)
+    del A, B
     if check is not None:
         rp, rho_d, rhoE_d, Fg = check
         rho = np.zeros((na, nb.cap + 1, 81)); rhoE = np.zeros_like(rho)
@@ -511,25 +527,32 @@ def cpu_sample(wl, args, check=None, n_panel=48, n_dens=16, n_force=96):
     else:
         rho = rng.standard_normal((na, nb.cap + 1, 81)) * 0.05; rhoE = rng.standard_normal((na, nb.cap + 1, 81)) * 0.05
     t0 = time.perf_counter()
-    Fo = orc.nrl_forces_sparse(wl, nb, lmn, rad, rho, rhoE, 0, n_force)
-    t["forces"] = (time.perf_counter() - t0) * na / n_force
+    Fo = orc.nrl_forces_sparse(wl, nb, lmn, rad, rho, rhoE)
+    t["forces"] = time.perf_counter() - t0
     total_ms = 1e3 * sum(t.values())
-    out = {"value": total_ms, "unit": "ms", "cores": orc.num_threads(), "kind": "port",
-           "sample": f"full neighbour list ({na} atoms) + radial tables + {n_panel} H/S column panels + rho/rho_E of "
-                     f"{n_dens} atoms + forces of {n_force} atoms, each scaled to {na} atoms; sparse-equivalent form of the "
+    measured_ms = 1e3 * (t["neighbours"] + t["radial"] + t["assembly"] + t["forces"] + dens_sample)
+    out = {"value": total_ms, "unit": "ms", "cores": cores, "kind": "port", "sampled": True, "extrapolated": True,
+           "scale_factors": {"neighbours": 1.0, "radial": 1.0, "assembly": 1.0, "forces": 1.0, "density": na / n_dens},
+           "measured_ms_before_scaling": measured_ms,
+           "sample": f"neighbour list, radial tables, H/S assembly (all {na} column panels) and forces of all {na} atoms in full; "
+                     f"rho/rho_E blocks of {n_dens} atoms scaled by {na / n_dens:g}; sparse-equivalent form of the "
                      "reference algorithm (its verbatim force loop needs 2 x 32.6 GB per thread at this size)",
            "stage_ms": {k: 1e3 * v for k, v in t.items()},
-           "reference_dense_dgemm_density_ms": dense_ms}
+           "variant_reference_dense_dgemm": {"density_ms": dense_ms, "value": total_ms - 1e3 * t["density"] + dense_ms,
+                                             "note": "rho and rho_E as the reference forms them: two dense dgemm('N','T') of order N "
+                                                     "(TB.f90:4386,4465), numpy BLAS on a 256-row panel scaled to N rows; the other stages as above"}}
     if check is not None:
-        out["full_size_force_check_eV_per_A"] = float(np.abs(orc.forces_cartesian(Fg[:n_force], wl["supce"]) -
-                                                            orc.forces_cartesian(Fo[:n_force], wl["supce"])).max())
+        out["full_size_force_check_eV_per_A"] = float(np.abs(orc.forces_cartesian(Fg, wl["supce"]) -
+                                                            orc.forces_cartesian(Fo, wl["supce"])).max())
     return out
 
 
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation of the path.  The reference is Fortran and no Fortran
-    compiler exists on either machine, so this is the oracle port (kind 'port'), all host threads, each step a bounded
-    sample of the workload (see cpu_sample).  No GPU, none of the library's kernels."""
+    compiler exists on either machine, so this is the oracle port (kind 'port') on ALL host cores -- the thread count is
+    pinned explicitly (torchrun exports OMP_NUM_THREADS=1) and reported; each step = cpu_sample (cheap stages in full, the
+    rho contraction sampled on 256 atoms and scaled: `sampled` / `extrapolated` / `scale_factors` in the line).  Under
+    torchrun rank 0 alone runs it.  No GPU, none of the library's kernels."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -545,7 +568,7 @@ def run_reference(args):
     cb = vals[-1]; cb["value"] = ms
     out = {"impl": "reference", "metric": METRIC, "value": ms, "unit": "ms", "n_gpus": args.gpus, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
-           "dtype": "f64", "data": "synthetic",
+           "dtype": "f64", "data": "synthetic", "sampled": True, "extrapolated": True, "cores": cb["cores"],
            "config": {"workload": f"{wl['name']}: synthetic Au fcc 8x8x16 supercell ({wl['na']} atoms, N={N} orbitals), NRL spd TB"},
            "cpu_baseline": cb,
            "e2e": {"value": ms, "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}

@@ -225,7 +225,8 @@ int  xtb_coupling       (xtb_ctx*, int kind_M, double* Mij);
 int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
  *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,
- *           9 / 10 shared-memory slots / pipeline stages of the last density kernel */
+ *           9 / 10 shared-memory slots / pipeline stages of the last density kernel,
+ *           11 work units (atom pairs + single atoms) of the last two-column-atom density launch */
 long long xtb_counter(const xtb_ctx*, int which);
 /* device time [ms] of the last run of a stage (CUDA events on the context stream):
  * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure,

@@ -63,6 +63,12 @@ def num_threads():
     return int(lib().orc_num_threads())
 
 
+def set_num_threads(n):
+    """pin the OpenMP thread count of the oracle (a launcher may have exported OMP_NUM_THREADS=1)"""
+    lib().orc_set_num_threads(C.c_int(int(n)))
+    return num_threads()
+
+
 def nrl_params_array(params):
     arr = (_abi.NrlPair * len(params))()
     for i, d in enumerate(params):

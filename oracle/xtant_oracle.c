@@ -54,6 +54,16 @@ int orc_num_threads(void) {
 #endif
 }
 
+/* the reference's OpenMP build takes its thread count from the environment (OMP_NUM_THREADS); a launcher such as
+ * torchrun exports OMP_NUM_THREADS=1, so the timed baseline pins it explicitly (bench.py --impl reference) */
+void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 /* ------------------------------------------------------------------------------------------
  * S1  neighbour list.  shortest_distance_OLD (Atomic_tools.f90:4028-4131) inside
  *     Find_nearest_neighbours (Atomic_tools.f90:4230-4294).

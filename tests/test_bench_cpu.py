@@ -15,7 +15,8 @@ def _run(env_extra, *args):
 
 
 def test_reference_arm_line():
-    r = _run({}, "--impl", "reference", "--steps", "1", "--warmup", "0")
+    # a launcher's OMP_NUM_THREADS=1 (torchrun) must not turn the baseline into a one-core run
+    r = _run({"OMP_NUM_THREADS": "1"}, "--impl", "reference", "--steps", "1", "--warmup", "0")
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
     assert len(lines) == 1
@@ -25,7 +26,11 @@ def test_reference_arm_line():
     assert j["steps"] == 1 and j["warmup"] == 0 and j["dtype"] == "f64" and j["data"] == "synthetic"
     assert "au4096" in j["config"]["workload"]
     cb = j["cpu_baseline"]
-    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == j["value"] and cb["unit"] == "ms" and cb["sample"]
+    assert cb["kind"] == "port" and cb["value"] == j["value"] and cb["unit"] == "ms" and cb["sample"]
+    assert cb["cores"] == os.cpu_count() == j["cores"]
+    assert j["sampled"] is True and j["extrapolated"] is True and cb["scale_factors"]["density"] == 4096 / 256
+    assert all(cb["scale_factors"][k] == 1.0 for k in ("neighbours", "radial", "assembly", "forces"))
+    assert cb["variant_reference_dense_dgemm"]["density_ms"] > 0
     assert j["e2e"] == {"value": j["value"], "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
 
 

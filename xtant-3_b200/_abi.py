@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libxtb_b200.so")
+# XTB_LIB_VARIANT=<tag> loads libxtb_b200_<tag>.so (kernel experiments built with tools/r02/build_variants.sh); default: the product library
+LIB_PATH = os.path.join(_HERE, "libxtb_b200%s.so" % (("_" + os.environ["XTB_LIB_VARIANT"]) if os.environ.get("XTB_LIB_VARIANT") else ""))
 
 XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE = range(7)
 XTB_TB_NONE, XTB_TB_NRL, XTB_TB_PETTIFOR, XTB_TB_DFTB = range(4)

@@ -25,6 +25,7 @@
 #include "xtb_ctx.h"
 #include <cstdint>
 #include <cstdlib>
+#include <type_traits>
 
 namespace {
 
@@ -292,6 +293,9 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
     }
     if (nchunks > 0) {
         const double* stg = sbuf + (size_t)rg.st * stage_doubles;
+#ifdef XTB_EXP_STAGGER
+        if (warp >= 4) __nanosleep(XTB_EXP_STAGGER);      // experiment: de-phase the two consumer warps of a sub-partition
+#endif
         mbar_wait(&full[rg.st], rg.ph);
         mbar_wait(&bready[rg.st], rg.ph);
         Frag<MT> f0, f1;      // double buffer: even k-steps compute from f0 while f1 is loaded, odd k-steps the other way round
@@ -516,6 +520,8 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
     if (warp == NCW + 1 && lane == 0) st_relaxed(prog + blockIdx.x, 0x7ffffffffffffff0LL);
 }
 
+#include "density_pair.cuh"
+
 // ---------------- simple CUDA-core kernel (cross-check of the DMMA path; also the generic-n_orb path) ----------------
 // one CTA per owned block; thread (mu,nu) accumulates over the kept states in their compacted order.
 template <int NO>
@@ -685,7 +691,7 @@ int run_density(xtb_ctx* c) {
     // blocks that no kernel below writes (atoms outside [a0,a1)) must not hold garbage
     XTB_CUDA(c, cudaMemsetAsync(c->d_rho.p, 0, sizeof(double) * NO * NO * (size_t)c->n_blocks, c->stream));
     XTB_CUDA(c, cudaMemsetAsync(c->d_rhoE.p, 0, sizeof(double) * NO * NO * (size_t)c->n_blocks, c->stream));
-    bool use_dmma = (c->density_impl == 1) && NO == 9 && nown > 0;
+    bool use_dmma = (c->density_impl >= 1) && NO == 9 && nown > 0;
     if (use_dmma) {
         if (kpad > nkeep) {
             pad_weights_kernel<<<1, KC, 0, c->stream>>>(nkeep, kpad, (double*)c->d_wf.p, (double*)c->d_wfe.p);
@@ -707,6 +713,50 @@ int run_density(xtb_ctx* c) {
             XTB_LAUNCH_CHECK(c);
         }
         XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+        if (c->density_impl == 2) {
+            // ---- two column atoms per CTA (density_pair.cuh) ----
+            const int gcap = 2 * c->max_nn + 4;
+            const size_t budget = 227 * 1024 - 1024;
+            // slot capacity: the union of the two owned sets of a pair of neighbours is ~2/3 of the sum (half-balls displaced by
+            // one bond), + the two atoms; never more than 8 * MUMAX row tiles per column atom can be dealt, and 3 stages must fit
+            int slotcap = (int)(0.7 * c->max_nn) + 6;
+            if (slotcap > c->max_nn + 3) slotcap = c->max_nn + 3;
+            if (slotcap < 4) slotcap = 4;
+            while (slotcap > 4 && pairk::smem_bytes(slotcap, 3, gcap) > budget) --slotcap;
+            int stages = 3;
+            while (stages < 6 && pairk::smem_bytes(slotcap, stages + 1, gcap) <= budget) ++stages;
+            const size_t smem = pairk::smem_bytes(slotcap, stages, gcap);
+            if (smem > budget) XTB_FAIL(c, XTB_ECAPACITY, "density: %d neighbours per atom do not fit the unit tables in shared memory", c->max_nn);
+            // units: matching of the owned atoms on the device (no host round trip; the kernel reads the unit count from memory)
+            if ((rc = xtb_reserve(c, c->d_units, sizeof(int) * (2 * (size_t)nown + 4 * (size_t)na + 4)))) return rc;
+            if ((rc = xtb_reserve(c, c->d_pairw, sizeof(unsigned) * (size_t)na * c->cap))) return rc;
+            int* d_units = (int*)c->d_units.p; int* d_nunits = d_units + 2 * (size_t)nown;
+            int* d_partner = d_nunits + 4; int* d_prop = d_partner + na; int* d_nown = d_prop + na;
+            pairk::own_count_kernel<<<(na + 127) / 128, 128, 0, c->stream>>>(na, c->cap, (const int*)c->d_nn_size.p, (const signed char*)c->d_own.p, d_nown);
+            XTB_LAUNCH_CHECK(c);
+            pairk::pair_weights_kernel<<<(nown + 3) / 4, 128, 0, c->stream>>>(c->a0, c->a1, c->cap, slotcap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                                              (const signed char*)c->d_own.p, d_nown, (unsigned*)c->d_pairw.p);
+            XTB_LAUNCH_CHECK(c);
+            pairk::pair_match_kernel<<<1, 1024, 0, c->stream>>>(c->a0, c->a1, c->cap, c->density_pairing ? 16 : 0, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                                (const unsigned*)c->d_pairw.p, d_partner, d_prop, d_units, d_nunits);
+            XTB_LAUNCH_CHECK(c);
+            const int wmin = slotcap - 2 < 40 ? slotcap - 2 : 40;       // every window but the last holds at least this many row atoms
+            const int maxsub = (2 * c->max_nn + 2 + wmin - 1) / wmin + 1;
+            int grid = c->sm_count < nown ? c->sm_count : nown;          // units <= owned atoms; surplus CTAs leave at once
+            if ((rc = xtb_reserve(c, c->d_prog, sizeof(long long) * (size_t)c->sm_count))) return rc;
+            XTB_CUDA(c, cudaMemsetAsync(c->d_prog.p, 0, sizeof(long long) * (size_t)c->sm_count, c->stream));
+            pairk::KArgs A;
+            A.na = na; A.nunits = d_nunits; A.cap = c->cap; A.slotcap = slotcap; A.stages = stages; A.nchunks = nchunks; A.maxsub = maxsub;
+            A.lead = c->density_lead; A.dbg = c->density_dbg; A.prog = (long long*)c->d_prog.p; A.units = d_units;
+            A.nn_size = (const int*)c->d_nn_size.p; A.nn_list = (const int*)c->d_nn_list.p; A.own = (const signed char*)c->d_own.p;
+            A.rowptr = (const int*)c->d_rowptr.p; A.Ct = (const double*)c->d_Ct.p; A.wf = (const double*)c->d_wf.p; A.wfe = (const double*)c->d_wfe.p;
+            A.rho = (double*)c->d_rho.p; A.rhoE = (double*)c->d_rhoE.p;
+            XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));         // the contraction kernel alone (stage 7)
+            XTB_CUDA(c, cudaFuncSetAttribute(pairk::density_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            pairk::density_pair_kernel<<<grid, pairk::THREADS, smem, c->stream>>>(A, gcap);
+            XTB_LAUNCH_CHECK(c);
+            c->density_slotcap = slotcap; c->density_stages = stages;
+        } else {
         // slot capacity / stages from the shared-memory budget (227 KB per CTA)
         const int NCW = c->density_ncw == 12 ? 12 : 8;
         const int MTMAX = NCW == 8 ? 7 : 5;
@@ -774,7 +824,8 @@ int run_density(xtb_ctx* c) {
 #undef XTB_LAUNCH_ALL
 #undef XTB_LAUNCH
         c->density_slotcap = slotcap; c->density_stages = stages;
-    } else if (nown > 0 && NO <= 4 && c->density_impl == 1) {
+        }
+    } else if (nown > 0 && NO <= 4 && c->density_impl >= 1) {
         if constexpr (NO <= 4) {
             if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)(nkeep > 0 ? nkeep : 1) * N + 1024))) return rc;
             if (nkeep > 0) {

@@ -53,6 +53,8 @@ int xtb_create(xtb_ctx** out, int device) {
     if (ncw) c->density_ncw = atoi(ncw);
     const char* lead = getenv("XTB_DENSITY_LEAD");
     if (lead) c->density_lead = atoi(lead);
+    const char* pairing = getenv("XTB_DENSITY_PAIRING");
+    if (pairing) c->density_pairing = atoi(pairing);
     const char* dbg = getenv("XTB_DENSITY_DBG");
     if (dbg) c->density_dbg = atoi(dbg);
     *out = c;
@@ -67,7 +69,7 @@ int xtb_destroy(xtb_ctx* c) {
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
                      &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
-                     &c->d_ctneed, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep};
+                     &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep};
     for (DevBuf* b : all) xtb_free(*b);
     cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
     if (c->own_stream) cudaStreamDestroy(c->stream);
@@ -636,6 +638,13 @@ long long xtb_counter(const xtb_ctx* c, int which) {
         case 8: return c->cap;
         case 9: return c->density_slotcap;
         case 10: return c->density_stages;
+        case 11: {      // work units of the last pair-kernel launch (pairs + singles); synchronises the stream
+            if (c->density_impl != 2 || !c->d_units.p || c->n_orb != 9) return -1;
+            int n = -1;
+            cudaStreamSynchronize(c->stream);
+            if (cudaMemcpy(&n, (const int*)c->d_units.p + 2 * (size_t)(c->a1 - c->a0), sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+            return n;
+        }
         default: return -1;
     }
 }

@@ -71,6 +71,8 @@ struct xtb_ctx {
     DevBuf d_rho, d_rhoE;       // block-sparse [n_blocks][n_orb^2]
     DevBuf d_ctneed;            // partitioned run: atom groups whose eigenvector tiles are re-tiled
     DevBuf d_prog;              // density kernel: per-CTA progress counters (lock-step throttle)
+    DevBuf d_units, d_pairw;    // pair density kernel: (i1, i2) per work unit + matching scratch; candidate-pair weights
+    int density_pairing = 1;    // 0: no matching rounds (every atom a single unit; XTB_DENSITY_PAIRING, experiments)
     bool have_density = false;
     // forces / pressure
     DevBuf d_F, d_SC, d_scratch, d_hdev, d_ppart, d_tab;
@@ -88,7 +90,7 @@ struct xtb_ctx {
     int density_dbg = 0;        // XTB_DENSITY_DBG (timing experiments only, separate kernel instantiation): 1 no math, 2 quarter of the tile copies, 4 helper warps nap while polling, 8 no DFMA
     int density_ncw = 8;        // consumer warps of the density kernel (8 or 12); XTB_DENSITY_NCW
     int density_lead = 64;      // chunks a CTA of the density kernel may run ahead of the slowest one (0 = no lock-step); XTB_DENSITY_LEAD
-    int density_impl = 1;       // 1 = DMMA + bulk-copy pipeline, 0 = simple CUDA-core kernel (debug / cross-check)
+    int density_impl = 1;       // 1 = DMMA + bulk-copy pipeline, one column atom per CTA; 2 = the same with two column atoms per CTA (density_pair.cuh); 0 = simple CUDA-core kernel (debug / cross-check)
 };
 
 #define XTB_FAIL(ctx, code, ...)                                   \
