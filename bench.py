@@ -151,54 +151,39 @@ def run_own(args):
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
     ctx.set_workload(wl)
-    if world > 1 and os.environ.get("XTB_BENCH_BLOCK_LAYOUT", "segmented") != "compact":
-        ctx.set_block_layout(world)      # equal-capacity segment per rank in every block store: in-place all-gathers
-    a0, a1 = mg.partition(na, world, rank)
+    a0, a1 = mg.partition(na, world, rank)      # = the range xtb_comm_init gives this rank
     Cm, dE, dfe, E, fe = make_eigen_device(torch, wk, wl, N)
     ctx.set_eigen_device(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
 
-    trace = {} if os.environ.get("XTB_BENCH_PHASES") else None
-    # N > 1: "replicated" (default; north star: H/S row blocks all-gathered over NVLink to a replicated eigensolve) or
+    # N > 1: one NCCL communicator INSIDE the library (xtb_comm_init): rank 0 draws the id, torch.distributed only carries its
+    # 128 bytes to the other ranks (what MPI_Bcast does for the Fortran caller).  Every exchange of the step then runs in
+    # libxtb_b200.so: H/S block segments all-gathered, rho / rho_E halo only, forces all-gathered.
+    if world > 1:
+        box = [ctx.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        ctx.comm_init(box[0], rank, world)
+    # "replicated" (default; north star: H/S row blocks all-gathered over NVLink to a replicated eigensolve) or
     # "panels" (variant: every rank writes only the dense column panels of its atoms -- 1-D column-block layout)
     replicate_dense = os.environ.get("XTB_BENCH_DENSE_LAYOUT", "replicated") != "panels"
     layout = {"replicated": replicate_dense}
-
-    def _ph(name, fn):
-        """run one phase; with XTB_BENCH_PHASES=1 also accumulate its synchronised wall time (diagnostic runs only)"""
-        if trace is None:
-            return fn()
-        torch.cuda.synchronize(); t0 = time.perf_counter()
-        r = fn()
-        torch.cuda.synchronize(); trace[name] = trace.get(name, 0.0) + (time.perf_counter() - t0) * 1e3
-        return r
+    STEP_ALL = abi.STEP_ALL
 
     def step():
-        _ph("neighbours", ctx.get_near_neighbours_device)
-        if world == 1:
-            _ph("assemble_HS", lambda: ctx.assemble_HS(to_host=False))
+        if world == 1 or layout["replicated"]:
+            # the whole step as ONE library call (xtb_step): list -> H/S blocks [-> all-gather] -> dense H_non, Sij ->
+            # rho, rho_E [-> halo exchange -> mirror] -> forces [-> all-gather]; one host synchronisation at its end
+            ctx._ck(ctx.lib.xtb_step(ctx.h, STEP_ALL, None))
         else:
-            # owners compute their H/S blocks; the block ranges are all-gathered over NVLink (0.42 GB in total instead of
-            # 21.7 GB of dense panels) and every rank expands the replicated dense H_non, Sij locally for the eigensolve.
-            # XTB_BENCH_DENSE_LAYOUT=panels (variant, not the headline): every rank writes only the column panels of its
-            # atoms, so that across the job every dense element is written once (1-D column-block layout, the input layout
-            # of a multi-GPU eigensolver such as cusolverMgSyevd) and no H/S exchange is needed.
-            ctx.set_partition(a0 + 1, a1)
-            _ph("assemble_blocks", ctx.assemble_blocks)
-            rp = _ph("rowptr_d2h", lambda: interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy())
-            if layout["replicated"]:
-                _ph("allgather_HS_blocks", lambda: mg.allgather_blocks([interop.buffer(ctx, abi.BUF_HBLK), interop.buffer(ctx, abi.BUF_SBLK)],
-                                                                       rp, na, 81, rank, world))
-                _ph("expand_dense", lambda: ctx.expand_dense(1, na))
-            else:
-                _ph("expand_dense", lambda: ctx.expand_dense(a0 + 1, a1))
-        _ph("density", ctx.density)
-        if world > 1:
-            _ph("allgather_rho_blocks", lambda: mg.allgather_blocks([interop.buffer(ctx, abi.BUF_RHO), interop.buffer(ctx, abi.BUF_RHOE)],
-                                                                    rp, na, 81, rank, world))
-            _ph("density_mirror", ctx.density_mirror)
-        _ph("forces", ctx.forces_device)
-        if world > 1:
-            _ph("allgather_forces", lambda: mg.allgather_forces(interop.buffer(ctx, abi.BUF_FORCES), na, rank, world))
+            # variant (not the headline): every rank writes only the column panels of its atoms, so that across the job every
+            # dense element is written once (the input layout of a multi-GPU eigensolver such as cusolverMgSyevd); no H/S exchange
+            ctx.get_near_neighbours_device()
+            ctx.assemble_blocks()
+            ctx.expand_dense(a0 + 1, a1)
+            ctx.density()
+            ctx.exchange_blocks(abi.XCHG_RHO)
+            ctx.density_mirror()
+            ctx.forces_device()
+            ctx.exchange_forces()
 
     def sync_all():
         torch.cuda.synchronize()
@@ -212,11 +197,11 @@ def run_own(args):
     launches0 = ctx.counter(6)
     sampler = ClockSampler(local) if rank == 0 else None
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    stage = np.zeros(8)
+    stage = np.zeros(16)
     e0.record(stream)
     for _ in range(args.steps):
         step()
-        for s in range(1, 8):
+        for s in range(1, 16):
             stage[s] += ctx.stage_ms(s)
     e1.record(stream)
     sync_all()
@@ -229,8 +214,6 @@ def run_own(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     n_blocks, n_pairs, k_kept = ctx.counter(4), ctx.counter(5), ctx.counter(7)
-    if trace is not None:
-        print(f"[phases rank {rank}] " + json.dumps({k: round(v / (args.steps + args.warmup), 3) for k, v in trace.items()}), file=sys.stderr)
 
     out = None
     if rank == 0:
@@ -249,12 +232,21 @@ def run_own(args):
                        "n_pairs": n_pairs, "n_blocks": n_blocks, "states_kept": k_kept, "l2_policy": "inputs larger than L2 "
                        "(eigenvectors 10.9 GB, H/S 21.7 GB per step)", "eigensolve": "outside graft; synthetic resident eigenvectors",
                        "partition": "atom rows" if world > 1 else "single GPU",
-                       "block_exchange": (None if world == 1 else "packed slots + copy-out" if os.environ.get("XTB_BENCH_BLOCK_LAYOUT", "segmented") == "compact"
-                                          else "in-place all-gather of equal-capacity segments (xtb_set_block_layout)"),
+                       "step_call": "xtb_step (one library call per step; steady-state neighbour list without a size read-back at N = 1)",
+                       "block_exchange": (None if world == 1 else "inside libxtb_b200.so over NCCL (xtb_comm_init): H/S block segments in-place "
+                                          "all-gather; rho/rho_E halo only (ncclSend/ncclRecv of packed blocks); forces all-gather"),
                        "dense_layout": ("single GPU" if world == 1 else "replicated on every rank" if replicate_dense
                                         else "column panels of the owned atoms (each dense element written once in the job)")},
             "stage_ms": {"neighbours": stage[1], "assembly": stage[2], "density": stage[3], "forces": stage[4],
-                         "dense_panel_kernel": stage[6], "density_kernel": stage[7]},
+                         "dense_panel_kernel": stage[6], "density_kernel": stage[7],
+                         "exchange_HS_blocks": stage[14] if world > 1 else None, "exchange_rho_blocks": stage[15] if world > 1 else None},
+            "exchange": (None if world == 1 else {
+                "HS_blocks": {"ms": stage[14], "bytes_received_per_rank": ctx.counter(abi.CNT_XCHG_HS_BYTES),
+                              "GB_per_s": ctx.counter(abi.CNT_XCHG_HS_BYTES) / (stage[14] * 1e-3) * 1e-9 if stage[14] > 0 else None},
+                "rho_blocks": {"ms": stage[15], "bytes_received_per_rank": ctx.counter(abi.CNT_XCHG_RHO_BYTES),
+                               "GB_per_s": ctx.counter(abi.CNT_XCHG_RHO_BYTES) / (stage[15] * 1e-3) * 1e-9 if stage[15] > 0 else None,
+                               "halo_blocks_sent": ctx.counter(abi.CNT_HALO_SEND), "halo_blocks_received": ctx.counter(abi.CNT_HALO_RECV),
+                               "all_gather_would_receive_bytes": int(2 * 8 * 81 * n_blocks * (world - 1) / world)}}),
             "pair_blocks_per_s": n_blocks * own_frac / (stage[2] * 1e-3) if stage[2] > 0 else None,
             "gpu_launches": int(launches),
             "clocks": clocks,
@@ -304,19 +296,27 @@ def run_own(args):
                 "note": "every rank writes only the dense columns of its atoms (each element once in the job; the 1-D "
                         "column-block input layout of a multi-GPU eigensolver); no H/S block all-gather"}
     # ---- N > 1: the partitioned, exchanged result against the same step computed by rank 0 alone on its GPU ----
+    # forces and H/S blocks of ALL atoms (all-gathered); rho / rho_E of rank 0's own rows (the halo exchange delivers a rank
+    # what ITS rows need, not the other ranks' rows)
     if world > 1:
+        layout["replicated"] = True
         step(); sync_all()
         if rank == 0:
-            got = [interop.buffer(ctx, b).clone() for b in (abi.BUF_FORCES, abi.BUF_RHO, abi.BUF_RHOE, abi.BUF_HBLK, abi.BUF_SBLK)]
+            rp = interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy()
+            nn_last = int(interop.buffer(ctx, abi.BUF_NNSIZE, torch.int32)[a1 - 1].item())
+            own = slice(int(rp[a0]) * 81, (int(rp[a1 - 1]) + 1 + nn_last) * 81)      # blocks of the rows a0 .. a1-1
+            bufs = (abi.BUF_FORCES, abi.BUF_RHO, abi.BUF_RHOE, abi.BUF_HBLK, abi.BUF_SBLK)
+            sel = lambda b, t: t[own] if b in (abi.BUF_RHO, abi.BUF_RHOE) else (t[:3 * na] if b == abi.BUF_FORCES else t)
+            got = [sel(b, interop.buffer(ctx, b)).clone() for b in bufs]
             ctx.set_partition(1, na)
             ctx.get_near_neighbours_device(); ctx.assemble_HS(to_host=False); ctx.density(); ctx.forces_device()
             torch.cuda.synchronize()
-            names = ("forces_eV_per_A(frac. coords as returned)", "rho", "rho_E", "H_blocks", "S_blocks")
-            ref = [interop.buffer(ctx, b) for b in (abi.BUF_FORCES, abi.BUF_RHO, abi.BUF_RHOE, abi.BUF_HBLK, abi.BUF_SBLK)]
+            names = ("forces_eV_per_A(frac. coords as returned)", "rho(rows of rank 0)", "rho_E(rows of rank 0)", "H_blocks", "S_blocks")
+            ref = [sel(b, interop.buffer(ctx, b)) for b in bufs]
             out["multi_gpu_vs_single_gpu_max_abs_diff"] = {n: float((g - r).abs().max().item()) for n, g, r in zip(names, got, ref)}
             out["multi_gpu_vs_single_gpu_max_abs_diff"]["forces_scale"] = float(ref[0].abs().max().item())
             del got, ref
-        ctx.set_partition(a0 + 1, a1)
+            ctx.set_partition(a0 + 1, a1)
         sync_all()
     # ---- e2e through the C ABI with host buffers (rank-local share of the work at N > 1) ----
     if not args.no_e2e:
@@ -360,14 +360,13 @@ def run_e2e(torch, ctx, wl, Cm, E, fe, world, rank, a0, a1, args):
     lib, hnd = ctx.lib, ctx.h
     n = max(1, args.e2e_steps)
 
+    io = abi.StepIO()
+    io.S = api._dp(S); io.fe = api._dp(fh); io.Ei = api._dp(Ei_host); io.F_att = api._dp(Fh)
+
     def step_resident():
-        ctx._ck(lib.xtb_set_system(hnd, na, api._ip(koa), api._dp(S), api._dp(h)))          # H2D: S, KOA
-        ctx._ck(lib.xtb_neighbours(hnd, 0.0, None, None, None, None))
-        ctx._ck(lib.xtb_assemble_HS(hnd, None, None))                                       # dense H_non, Sij stay on the device
-        ctx._ck(lib.xtb_get_eigenvalues(hnd, api._dp(Ei_host)))                             # D2H: Ei (occupations are a host job)
-        ctx._ck(lib.xtb_set_occupations(hnd, api._dp(fh)))                                  # H2D: fe
-        ctx._ck(lib.xtb_density(hnd, None, None))
-        ctx._ck(lib.xtb_forces(hnd, api._dp(Fh)))                                           # D2H: forces
+        # ONE call: H2D of S and fe, the whole device step, D2H of Ei and the forces (occupations are a host job in the
+        # reference's flow: Ei out, fe in -- here both travel with the same call since the eigen-solution is resident)
+        ctx._ck(lib.xtb_step(hnd, abi.STEP_ALL, C.byref(io)))
 
     for _ in range(2):
         step_resident()
@@ -433,24 +432,24 @@ def run_e2e_multi(torch, ctx, wl, E, fe, world, rank, a0, a1, args):
     n = max(args.e2e_steps, 3)
     replicate = os.environ.get("XTB_BENCH_DENSE_LAYOUT", "replicated") != "panels"
 
+    io = abi.StepIO()
+    io.S = api._dp(S); io.fe = api._dp(fh); io.Ei = api._dp(Ei_host); io.F_att = api._dp(Fh)
+
     def step():
-        ctx._ck(lib.xtb_set_system(hnd, na, api._ip(koa), api._dp(S), api._dp(h)))          # H2D: S, KOA (replicated)
-        ctx._ck(lib.xtb_neighbours(hnd, 0.0, None, None, None, None))
-        ctx._ck(lib.xtb_set_partition(hnd, a0 + 1, a1))
-        ctx._ck(lib.xtb_assemble_blocks(hnd))
-        rp = interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy()
         if replicate:
-            mg.allgather_blocks([interop.buffer(ctx, abi.BUF_HBLK), interop.buffer(ctx, abi.BUF_SBLK)], rp, na, 81, rank, world)
-            ctx._ck(lib.xtb_expand_dense(hnd, 1, na, None, None))
+            ctx._ck(lib.xtb_step(hnd, abi.STEP_ALL, C.byref(io)))      # S, fe in; Ei, ALL forces out; exchanges inside the library
         else:
+            ctx._ck(lib.xtb_set_system(hnd, na, api._ip(koa), api._dp(S), api._dp(h)))
+            ctx._ck(lib.xtb_neighbours(hnd, 0.0, None, None, None, None))
+            ctx._ck(lib.xtb_assemble_blocks(hnd))
             ctx._ck(lib.xtb_expand_dense(hnd, a0 + 1, a1, None, None))
-        ctx._ck(lib.xtb_get_eigenvalues(hnd, api._dp(Ei_host)))                             # D2H: Ei
-        ctx._ck(lib.xtb_set_occupations(hnd, api._dp(fh)))                                  # H2D: fe
-        ctx._ck(lib.xtb_density(hnd, None, None))
-        mg.allgather_blocks([interop.buffer(ctx, abi.BUF_RHO), interop.buffer(ctx, abi.BUF_RHOE)], rp, na, 81, rank, world)
-        ctx._ck(lib.xtb_density_mirror(hnd))
-        ctx._ck(lib.xtb_forces(hnd, api._dp(Fh)))                                           # D2H: owned forces
-        mg.allgather_forces(interop.buffer(ctx, abi.BUF_FORCES), na, rank, world)
+            ctx._ck(lib.xtb_get_eigenvalues(hnd, api._dp(Ei_host)))
+            ctx._ck(lib.xtb_set_occupations(hnd, api._dp(fh)))
+            ctx._ck(lib.xtb_density(hnd, None, None))
+            ctx._ck(lib.xtb_exchange_blocks(hnd, abi.XCHG_RHO))
+            ctx._ck(lib.xtb_density_mirror(hnd))
+            ctx._ck(lib.xtb_forces(hnd, None))
+            ctx._ck(lib.xtb_exchange_forces(hnd, api._dp(Fh)))
 
     for _ in range(2):
         step()
@@ -461,10 +460,10 @@ def run_e2e_multi(torch, ctx, wl, E, fe, world, rank, a0, a1, args):
     torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
     ms = (time.perf_counter() - t0) * 1e3 / n
     return {"value": ms, "unit": "ms", "h2d_bytes_per_step": world * (8 * (3 * na + 9 + N) + 4 * na),
-            "d2h_bytes_per_step": world * 8 * N + 8 * 3 * na, "steps": n,
-            "flow": "per-rank C ABI with host buffers (S, KOA, fe in; Ei, owned forces out); "
-                    + ("H/S blocks, " if replicate else "dense H_non / Sij as owned column panels; ")
-                    + "rho blocks and forces exchanged over NVLink (all-gather); dense H_non / Sij and the eigenvectors never cross PCIe"}
+            "d2h_bytes_per_step": world * (8 * N + 8 * 3 * na), "steps": n,
+            "flow": "per-rank xtb_step with host buffers (S, fe in; Ei, all forces out on every rank, as the MPI build replicates them); "
+                    + ("H/S blocks all-gathered, " if replicate else "dense H_non / Sij as owned column panels; ")
+                    + "rho blocks (halo only) and forces exchanged over NVLink inside the library; dense H_non / Sij and the eigenvectors never cross PCIe"}
 
 
 def cpu_sample(wl, args, check=None, n_dens=256, threads=None):

@@ -38,6 +38,7 @@ extern "C" {
 #define XTB_ENOMEM    4   /* device allocation failed */
 #define XTB_ECAPACITY 5   /* neighbour capacity exceeded */
 #define XTB_ESTATE    6   /* stage called before its inputs exist */
+#define XTB_ECOMM     7   /* NCCL not available / collective failed */
 
 /* TB parametrisation kinds; mirrors the `select type` arms of TB.f90:247-317,459-487 */
 #define XTB_TB_NONE     0
@@ -84,6 +85,15 @@ typedef struct xtb_dftb_pair {
     const double* Sr;         /* [n_r*10]  overlaps */
 } xtb_dftb_pair;
 
+/* type(TB_Exp_wall_simple), Objects.f90:458-466 (file order read_Exponential_wall_TB, Read_input_data.f90:2313-2356):
+ * Pot(r) = C exp(1 / (r - r0)) / (1 + exp((r - d0) / dd)), zero beyond d0 + 10 dd */
+typedef struct xtb_wall_pair {
+    double C;     /* [eV] */
+    double r0;    /* [A] wall position */
+    double d0;    /* [A] cut-off radius */
+    double dd;    /* [A] cut-off smoothing width */
+} xtb_wall_pair;
+
 typedef struct xtb_ctx xtb_ctx;
 
 /* ---- life cycle ------------------------------------------------------------------- */
@@ -124,6 +134,10 @@ int  xtb_set_block_layout(xtb_ctx*, int parts);
  *        nn_size(na), nn_list(na,na), nn_dist(na,na,4), nn_dist_s(na,na,3); unused = 0 / 1d8 / untouched. */
 int  xtb_neighbours(xtb_ctx*, double rm_angstrom, int32_t* nn_size, int32_t* nn_list,
                     double* nn_dist, double* nn_dist_s);
+/* the cut-off [A] get_near_neighbours derives from the TB parameters (Atomic_tools.f90:570-613: attractive part, raised to
+ * the Pettifor repulsive dm); a caller that also has vdW / DFTB-repulsive terms enlarges it on the host (:615-640) and passes
+ * the result to xtb_neighbours.  This is also what the reference returns through its optional `dm` argument (:645-649). */
+int  xtb_cutoff(xtb_ctx*, double* rm_angstrom);
 /* compact (ELL) copy: list[k + cap*(i-1)], dist[c + 4*(k + cap*(i-1))], dist_s[c + 3*(...)] */
 int  xtb_neighbours_compact(xtb_ctx*, int cap, int32_t* nn_size, int32_t* nn_list,
                             double* nn_dist, double* nn_dist_s, int* max_nn_out);
@@ -153,8 +167,9 @@ int  xtb_expand_dense(xtb_ctx*, int atom_first, int atom_last, double* H_non, do
 /* ---- eigensolve boundary (outside the graft): Scell%Ha(N,N) (column n = state n),
  *      Scell%Ei(N) [eV], Scell%fe(N) (occupations incl. spin factor).  *_device: pointers
  *      are device memory that stays valid until the next xtb_set_eigen* call (zero copy). */
-int  xtb_set_eigen       (xtb_ctx*, const double* Ha, const double* Ei, const double* fe);
+int  xtb_set_eigen       (xtb_ctx*, const double* Ha, const double* Ei, const double* fe /*NULL: occupations follow through xtb_set_occupations*/);
 int  xtb_set_eigen_device(xtb_ctx*, const double* dHa, const double* dEi, const double* dfe);
+/* (xtb_set_eigen_device reads dfe once, to select the occupied states: call it again after changing the buffers' contents) */
 
 /* Optional on-device eigensolve (the north star feeds end-to-end steps this way so that H, S and Ha
  *      never cross PCIe).  Same algebra as Loewdin_Orthogonalization (TB_NRL.f90:985-1060) + sym_diagonalize (Algebra_tools.f90:
@@ -171,6 +186,9 @@ int  xtb_set_occupations(xtb_ctx*, const double* fe /*N*/);   /* Scell%fe; eigen
  *      TB.f90:250-299,5544-5573); dense outputs (N,N) are zero outside the pattern.
  *      f_cut: states with fe(n) <= f_cut are skipped (0 = bit-safe: only exact zeros). */
 int  xtb_density(xtb_ctx*, double* Aij, double* Aij_x_Ei);
+/* dense copies of the LAST pass without contracting again (the pass makes rho and rho_E together: the Fortran shim runs it
+ * once per step from Construct_Aij and serves Construct_Aij_x_En from it) */
+int  xtb_density_get(xtb_ctx*, double* Aij, double* Aij_x_Ei);
 int  xtb_set_density_cutoff(xtb_ctx*, double f_cut);
 /* multi-GPU only: after the owner blocks of all ranks have been exchanged into XTB_BUF_RHO/RHOE
  * (one allgather, replaces the MPI_Allreduce of the dense Aij, TB.f90:4374), fill the mirrored blocks. */
@@ -195,6 +213,94 @@ int  xtb_pressure(xtb_ctx*, double SCforce_att[9]);
 int  xtb_repulsive_energy  (xtb_ctx*, double* E_rep, double* Epot);
 int  xtb_repulsive_forces  (xtb_ctx*, double* F_rep);
 int  xtb_repulsive_pressure(xtb_ctx*, double SCforce_rep[9]);
+
+/* ---- SURVEY.md 8f item 2, second half: the short-range "exponential wall" (class TB_Exp_wall_simple) on the same stream,
+ *      for every TB branch (dispatch Exponential_wall_forces TB.f90:3533-3556; energy TB.f90:3983).  p[(koa1-1) + n_kinds*(koa2-1)].
+ *      n_kinds = 0 / p = NULL removes the wall (the reference proceeds "without additional short-range forces" when the file is
+ *      absent or its class line is not recognised, Read_input_data.f90:2013-2034).
+ *      xtb_wall_energy    get_Exp_wall_s        (Exponential_wall.f90:990-1067): E_wall [eV]; Epot(na) = the per-atom halves
+ *      xtb_wall_forces    d_Exp_wall_pot_s      (:1200-1329): the term ADDED to MDatoms(k)%forces%rep(1:3), F_wall(3,na)
+ *      xtb_wall_pressure  d_Exp_wall_Pressure_s (:1334-1385): the term ADDED to Scell%SCforce%rep(3,3) */
+int  xtb_set_params_wall(xtb_ctx*, int n_kinds, const xtb_wall_pair* p);
+int  xtb_wall_energy  (xtb_ctx*, double* E_wall, double* Epot);
+int  xtb_wall_forces  (xtb_ctx*, double* F_wall);
+int  xtb_wall_pressure(xtb_ctx*, double SCforce_wall[9]);
+
+/* ---- Fermi occupations on the device (between the eigensolve and S3; lets a step stay on the device):
+ *      Electron_Fixed_Te (Electron_tools.f90:2660-2706: bisection of mu at fixed Te until |N(mu) - Ne| <= 1e-12 Ne) +
+ *      set_Fermi (:1913-1969), spin-degenerate (f_norm = 2).  Uses the eigenvalues on the device (xtb_eigensolve or
+ *      xtb_set_eigen*), arms xtb_density.  fe(N), mu [eV], E_band = sum f_n E_n [eV] optional host outputs. */
+int  xtb_fermi_occupations(xtb_ctx*, double n_electrons, double Te_eV, double* fe, double* mu, double* E_band);
+
+/* ---- velocity-Verlet halves on the device, make_time_step_atoms_SC (Atomic_tools.f90:1897-1974)
+ *      preceded by save_last_timestep (:1177-1192) as in the main loop (XTANT_MAIN_FILE.f90:338-341,380-383):
+ *        ind = 2: S = S0 + dt SV0 + a dt^2/2 (periodic wrap, :2654,:2692), SV = SV0 + a dt/2     [MD_step, TB.f90:113]
+ *        ind = 1: SV = SV0 + a dt/2 with the new forces                                        [AT_MOVE_2]
+ *      a = -g_e 1e-10 / M * g^-1 F_total - g^-1 (dg/dt) SV0; F_total = sum of the selected device-resident force terms
+ *      (XTB_FORCE_*; each [eV], d/ds as returned by xtb_forces).  Vsupce(3,3) = NULL for a fixed cell.  mass_kg[n_kinds].
+ *      Positions are those of xtb_set_system and are updated in place (the next xtb_neighbours / xtb_step sees them). */
+#define XTB_FORCE_ATT   1u   /* XTB_BUF_FORCES  (xtb_forces) */
+#define XTB_FORCE_REP   2u   /* XTB_BUF_FREP    (xtb_repulsive_forces) */
+#define XTB_FORCE_WALL  4u   /* XTB_BUF_FWALL   (xtb_wall_forces) */
+int  xtb_md_set_velocities(xtb_ctx*, const double* SV /*[3*na] relative velocities [1/fs]; NULL = zero*/);
+int  xtb_md_half_step(xtb_ctx*, int ind, double dt_fs, const double* mass_kg, const double* Vsupce, unsigned force_terms);
+int  xtb_md_get_state(xtb_ctx*, double* S, double* SV, double* E_kin /*[eV]*/, const double* mass_kg /*for E_kin*/);
+
+/* ---- multi-GPU inside the library (one process / MPI rank per GPU; NCCL bound at run time with dlopen).
+ *      Replaces the MPI_Allreduce of whole dense arrays of the MPI build (TB_NRL.f90:326-327, TB.f90:4374,
+ *      MPI_subroutines.f90:3965-3982):
+ *        rank 0:  xtb_comm_unique_id(id)  ->  MPI_Bcast(id, 128 bytes)  ->  every rank: xtb_comm_init(ctx, id, rank, nranks)
+ *      xtb_comm_init gives the context the atom range of its rank (ceil(na/nranks) atoms each, contiguous) and lays the block
+ *      stores out in one segment per rank (xtb_set_block_layout).  Then, per step, either xtb_step (below) or by hand:
+ *        xtb_neighbours -> xtb_assemble_blocks -> xtb_exchange_blocks(XTB_XCHG_HS) -> xtb_expand_dense(1, na) -> [eigensolve]
+ *        -> xtb_density -> xtb_exchange_blocks(XTB_XCHG_RHO) -> xtb_density_mirror -> xtb_forces -> xtb_exchange_forces
+ *        [-> xtb_pressure -> xtb_allreduce_scforce]
+ *      XTB_XCHG_HS:  in-place all-gather of the ranks' H / S block segments (every rank expands the replicated dense matrices);
+ *      XTB_XCHG_RHO: halo only -- point-to-point transfers of the owner blocks a rank mirrors into its own rows and of the
+ *                    on-site blocks of the neighbours of its atoms (XTB_RHO_EXCHANGE=allgather: everything to everyone). */
+#define XTB_UNIQUE_ID_BYTES 128
+#define XTB_XCHG_HS   1
+#define XTB_XCHG_RHO  2
+int  xtb_comm_unique_id(void* id_out /*XTB_UNIQUE_ID_BYTES*/);
+int  xtb_comm_init   (xtb_ctx*, const void* unique_id, int rank, int nranks);
+int  xtb_comm_destroy(xtb_ctx*);
+int  xtb_exchange_blocks  (xtb_ctx*, int which);
+int  xtb_exchange_forces  (xtb_ctx*, double* F_att /*(3,na) complete, or NULL*/);
+int  xtb_allreduce_scforce(xtb_ctx*, double SCforce_att[9] /*or NULL*/);
+
+/* ---- the whole step as ONE call: the stages selected in `flags`, in the order of get_Hamilonian_and_E (TB.f90:196-330),
+ *      with the exchanges of a communicating context in between, everything enqueued on the context stream and ONE host
+ *      synchronisation at the end.  On a single GPU the neighbour list is rebuilt without a size read-back from the second
+ *      step on (capacity, neighbour bound and block capacity of the previous step, checked on the device; a step that
+ *      outgrows them is re-run through the sizing path, transparently).  Exceptions that do wait in the middle: the first
+ *      step / a communicating context (list sizes size the launches and the NCCL counts), XTB_STEP_EIGEN (cuSOLVER reports
+ *      its status through the host) and new occupations (the number of occupied states sizes the density launches).
+ *      io: host arrays, every pointer optional (NULL = keep on the device / not given). */
+#define XTB_STEP_NEIGHBOURS   1u
+#define XTB_STEP_HS           2u    /* blocks [+ exchange] + dense H_non, Sij */
+#define XTB_STEP_EIGEN        4u    /* on-device eigensolve (xtb_eigensolve) + Fermi occupations (io->n_electrons, io->Te_eV) */
+#define XTB_STEP_DENSITY      8u    /* rho, rho_E [+ halo exchange + mirror] */
+#define XTB_STEP_FORCES      16u    /* attractive forces [+ all-gather] */
+#define XTB_STEP_PRESSURE    32u    /* supercell force [+ all-reduce] (also of the pair terms when XTB_STEP_PAIR_TERMS) */
+#define XTB_STEP_PAIR_TERMS  64u    /* repulsive part of the Pettifor branch and / or the short-range wall, whichever is set */
+#define XTB_STEP_NO_DENSE   128u    /* with XTB_STEP_HS: block stores only */
+#define XTB_STEP_ALL (XTB_STEP_NEIGHBOURS | XTB_STEP_HS | XTB_STEP_DENSITY | XTB_STEP_FORCES)
+typedef struct xtb_step_io {
+    const double* S;          /* in  [3*na] new MDAtoms%S */
+    const double* supce;      /* in  [9]    new Scell%supce */
+    const double* fe;         /* in  [N]    Scell%fe for this step (ignored with XTB_STEP_EIGEN) */
+    double  n_electrons;      /* in  Scell%Ne_low, for XTB_STEP_EIGEN */
+    double  Te_eV;            /* in  Scell%TeeV,   for XTB_STEP_EIGEN */
+    double* Ei;               /* out [N] */
+    double* fe_out;           /* out [N]   (XTB_STEP_EIGEN) */
+    double* mu;               /* out [1]   (XTB_STEP_EIGEN) */
+    double* E_band;           /* out [1]   sum f_n E_n (XTB_STEP_EIGEN) */
+    double* F_att;            /* out [3*na] */
+    double* SCforce_att;      /* out [9] */
+    double* E_rep;  double* F_rep;  double* SCforce_rep;      /* out: Pettifor repulsive part */
+    double* E_wall; double* F_wall; double* SCforce_wall;     /* out: short-range wall */
+} xtb_step_io;
+int  xtb_step(xtb_ctx*, unsigned flags, const xtb_step_io* io);
 
 /* ---- Electron_ion_coupling_Mij (Nonadiabatic.f90:782-945), the two more N^3 contractions of an
  *      "electron-ion coupling" run.  Ha0 = eigenvectors of the previous step (Scell%Ha0, saved by construct_TB_H_* as
@@ -222,6 +328,11 @@ int  xtb_coupling       (xtb_ctx*, int kind_M, double* Mij);
 #define XTB_BUF_SBLK    11   /* block-sparse S */
 #define XTB_BUF_FREP    12   /* (3,na) repulsive forces */
 #define XTB_BUF_MIJ     13   /* (N,N) coupling matrix of the last xtb_coupling */
+#define XTB_BUF_FWALL   14   /* (3,na) wall forces */
+#define XTB_BUF_POS     15   /* (3,na) relative coordinates S */
+#define XTB_BUF_VEL     16   /* (3,na) relative velocities SV */
+#define XTB_BUF_EI      17   /* (N) eigenvalues */
+#define XTB_BUF_FE      18   /* (N) occupations */
 int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
  *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,
@@ -231,7 +342,8 @@ long long xtb_counter(const xtb_ctx*, int which);
 /* device time [ms] of the last run of a stage (CUDA events on the context stream):
  * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure,
  * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3), 8 xtb_eigensolve,
- * 9 repulsive energy + forces, 10 repulsive pressure, 11 xtb_coupling (12 / 13: its norms + S*Ha part / its DGEMM) */
+ * 9 pair-term energy + forces (repulsive / wall), 10 pair-term pressure, 11 xtb_coupling (12 / 13: its norms + S*Ha part / its DGEMM),
+ * 14 H/S block exchange, 15 rho block exchange (xtb_counter 12 / 13: bytes received per rank by each) */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 
 #ifdef __cplusplus

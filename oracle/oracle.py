@@ -35,7 +35,7 @@ _pi = C.POINTER(C.c_int)
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    src = [os.path.join(_HERE, f) for f in ("xtant_oracle.c", "sk_tables.h", "pettifor_oracle.c")]
+    src = [os.path.join(_HERE, f) for f in ("xtant_oracle.c", "sk_tables.h", "pettifor_oracle.c", "dftb_oracle.c", "wall_oracle.c")]
     src = [s for s in src if os.path.exists(s)]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
@@ -52,6 +52,8 @@ def lib():
         _LIB.orc_neighbours.restype = C.c_int
         _LIB.orc_num_threads.restype = C.c_int
         _LIB.orc_pet_erep.restype = C.c_double
+        _LIB.orc_wall_energy.restype = C.c_double
+        _LIB.orc_fermi.restype = C.c_double
     return _LIB
 
 
@@ -173,6 +175,70 @@ def eigensolve_nonorthogonal(H, S):
     assert info == 0
     Ha = X @ V
     return np.asfortranarray(Ha), Ei, w
+
+
+# ---- short-range wall (Exponential_wall.f90, class TB_Exp_wall_simple) ----
+def wall_params_array(params):
+    arr = (_abi.WallPair * len(params))()
+    for i, d in enumerate(params):
+        arr[i] = _abi.WallPair(float(d["C"]), float(d["r0"]), float(d["d0"]), float(d["dd"]))
+    return arr
+
+
+def wall_energy(wl, nb):
+    """get_Exp_wall_s, Exponential_wall.f90:990-1067 -> (E_wall, per-atom halves added to Epot)"""
+    Epot = np.zeros(nb.na)
+    E = lib().orc_wall_energy(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(nb.size), _p(nb.list),
+                              _p(nb.dist), wall_params_array(wl["wall_params"]), _p(Epot))
+    return float(E), Epot
+
+
+def wall_forces(wl, nb):
+    """d_Exp_wall_pot_s, Exponential_wall.f90:1200-1329 (verbatim loop nest) -> the term added to forces%rep (na,3)"""
+    F = np.zeros((nb.na, 3))
+    h = np.asfortranarray(wl["supce"], dtype=np.float64)
+    lib().orc_wall_forces(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(h), _p(nb.size), _p(nb.list),
+                          _p(nb.dist), wall_params_array(wl["wall_params"]), _p(F))
+    return F
+
+
+def wall_pressure(wl, nb):
+    """d_Exp_wall_Pressure_s, Exponential_wall.f90:1334-1385 -> the term added to SCforce%rep(3,3)"""
+    P = np.zeros(9)
+    lib().orc_wall_pressure(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(nb.size), _p(nb.list),
+                            _p(nb.dist), _p(nb.dist_s), wall_params_array(wl["wall_params"]), _p(P))
+    return P.reshape(3, 3, order="F")
+
+
+# ---- Fermi occupations and the velocity-Verlet halves ----
+def fermi(Ei, n_electrons, Te_eV):
+    """Electron_Fixed_Te + set_Fermi, Electron_tools.f90:2660-2706,1913-1969 -> (fe, mu)"""
+    Ei = np.ascontiguousarray(Ei, dtype=np.float64)
+    fe = np.zeros_like(Ei)
+    mu = lib().orc_fermi(C.c_int(Ei.shape[0]), _p(Ei), C.c_double(n_electrons), C.c_double(Te_eV), _p(fe))
+    return fe, float(mu)
+
+
+def md_half_step(ind, koa0, mass_kg, supce, dt, Ftot, S, SV, Vsupce=None):
+    """save_last_timestep + make_time_step_atoms_SC(ind), Atomic_tools.f90:1177-1192,1897-1974 -> (S, S0, SV, SV0)"""
+    na = S.shape[0]
+    S = np.array(S, dtype=np.float64); SV = np.array(SV, dtype=np.float64)
+    S0 = np.zeros_like(S); SV0 = np.zeros_like(S)
+    h = np.asfortranarray(supce, dtype=np.float64)
+    V = None if Vsupce is None else np.asfortranarray(Vsupce, dtype=np.float64)
+    F = np.ascontiguousarray(Ftot, dtype=np.float64)
+    m = np.ascontiguousarray(mass_kg, dtype=np.float64)
+    k0 = np.ascontiguousarray(koa0, dtype=np.int32)
+    lib().orc_md_half_step(C.c_int(na), C.c_int(ind), _p(k0), _p(m), _p(h), None if V is None else _p(V), C.c_double(dt),
+                           _p(F), _p(S), _p(S0), _p(SV), _p(SV0))
+    return S, S0, SV, SV0
+
+
+def kinetic_energy_eV(koa0, mass_kg, supce, SV):
+    """sum_k M_k/2 |V_k|^2 with V(x) = sum_k SV(k) supce(k,x) [A/fs] (velocities_rel_to_abs), in eV"""
+    V = np.asarray(SV) @ np.asarray(supce)
+    m = np.asarray(mass_kg)[np.asarray(koa0)]
+    return float(0.5 * np.sum(m[:, None] * V * V) * 1.0e10 / G_E)
 
 
 def eigensolve_orthogonal(H):

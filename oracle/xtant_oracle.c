@@ -24,6 +24,7 @@
  * Matrices are column-major (Fortran).  supce h[a + 3*b] == supce(a+1,b+1).
  */
 #include <math.h>
+#include <float.h>
 #include <stdlib.h>
 #include <string.h>
 #include <stdio.h>
@@ -904,3 +905,4 @@ void orc_dks_block(const double* V, const double* dV, double l, double m, double
 /* Pettifor (orthogonal sp3) branch: shares the helpers above */
 #include "pettifor_oracle.c"
 #include "dftb_oracle.c"
+#include "wall_oracle.c"

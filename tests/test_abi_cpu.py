@@ -85,6 +85,10 @@ def test_fortran_shim_interfaces_match_the_header():
         assert protos[name] == n, f"{name}: {n} arguments in the shim, {protos[name]} in the header"
     # introspection / zero-copy / stream entry points are for the Python and C++ hosts; everything else must be bound
     host_only = {"xtb_version", "xtb_set_stream", "xtb_counter", "xtb_device_buffer", "xtb_neighbours_compact", "xtb_set_eigen_device"}
+    # and the shim's get_near_neighbours keeps the reference's `dm` contract: a present dm returns the radius, no list
+    body = shim[shim.index("subroutine get_near_neighbours"):shim.index("end subroutine get_near_neighbours")]
+    assert re.search(r"if \(present\(dm\)\) then\s*!.*\n\s*dm = rm\s*\n\s*else\s*\n\s*call push_system", body)
+    assert "xtb_cutoff" in body and "TB_Rep_DFTB" in body and "include_vdW" in body
     assert set(protos) - set(bound) <= host_only, sorted(set(protos) - set(bound) - host_only)
 
 
@@ -98,7 +102,8 @@ def test_fortran_shim_struct_mirrors_match_ctypes_layout():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     shim = open(os.path.join(root, "xtant-3_b200", "fortran", "xtant_b200_shim.f90")).read()
     mirrors = {"xtb_nrl_pair": abi.NrlPair, "xtb_pettifor_pair": abi.PettiforPair,
-               "xtb_pettifor_rep_pair": abi.PettiforRepPair, "xtb_dftb_pair": abi.DftbPair}
+               "xtb_pettifor_rep_pair": abi.PettiforRepPair, "xtb_dftb_pair": abi.DftbPair,
+               "xtb_wall_pair": abi.WallPair, "xtb_step_io": abi.StepIO}
     size = {"c_double": 8, "c_int": 4, "c_int32_t": 4, "c_ptr": 8}
     for name, cls in mirrors.items():
         m = re.search(r"type,\s*bind\(C\)\s*::\s*" + name + r"\b(.*?)end type", shim, flags=re.S | re.I)

@@ -10,13 +10,21 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 # XTB_LIB_VARIANT=<tag> loads libxtb_b200_<tag>.so (kernel experiments built with tools/r02/build_variants.sh); default: the product library
 LIB_PATH = os.path.join(_HERE, "libxtb_b200%s.so" % (("_" + os.environ["XTB_LIB_VARIANT"]) if os.environ.get("XTB_LIB_VARIANT") else ""))
 
-XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE = range(7)
+XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE, XTB_ECOMM = range(8)
 XTB_TB_NONE, XTB_TB_NRL, XTB_TB_PETTIFOR, XTB_TB_DFTB = range(4)
 
-BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK, BUF_FREP, BUF_MIJ = range(1, 14)
+(BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK, BUF_FREP, BUF_MIJ,
+ BUF_FWALL, BUF_POS, BUF_VEL, BUF_EI, BUF_FE) = range(1, 19)
 CNT_NA, CNT_NORB, CNT_N, CNT_MAXNN, CNT_NBLOCKS, CNT_NPAIRS, CNT_LAUNCHES, CNT_KKEPT, CNT_CAP = range(9)
 STAGE_NEIGH, STAGE_ASSEMBLE, STAGE_DENSITY, STAGE_FORCES, STAGE_PRESSURE = range(1, 6)
 STAGE_REP_FORCES, STAGE_REP_PRESSURE, STAGE_COUPLING = 9, 10, 11
+STAGE_XCHG_HS, STAGE_XCHG_RHO = 14, 15
+CNT_XCHG_HS_BYTES, CNT_XCHG_RHO_BYTES, CNT_HALO_SEND, CNT_HALO_RECV = 12, 13, 14, 15
+XCHG_HS, XCHG_RHO = 1, 2
+FORCE_ATT, FORCE_REP, FORCE_WALL = 1, 2, 4
+STEP_NEIGHBOURS, STEP_HS, STEP_EIGEN, STEP_DENSITY, STEP_FORCES, STEP_PRESSURE, STEP_PAIR_TERMS, STEP_NO_DENSE = 1, 2, 4, 8, 16, 32, 64, 128
+STEP_ALL = STEP_NEIGHBOURS | STEP_HS | STEP_DENSITY | STEP_FORCES
+UNIQUE_ID_BYTES = 128
 
 _d4 = C.c_double * 4
 _d10 = C.c_double * 10
@@ -43,6 +51,21 @@ class PettiforRepPair(C.Structure):
     _fields_ = [("E0_TB", C.c_double), ("a0", C.c_double * 5),
                 ("phi0", C.c_double), ("d0", C.c_double), ("m", C.c_double), ("mc", C.c_double), ("dc", C.c_double),
                 ("d1", C.c_double), ("dm", C.c_double), ("c0", _d4)]
+
+
+class WallPair(C.Structure):
+    """struct xtb_wall_pair == type(TB_Exp_wall_simple), Objects.f90:458-466"""
+    _fields_ = [("C", C.c_double), ("r0", C.c_double), ("d0", C.c_double), ("dd", C.c_double)]
+
+
+class StepIO(C.Structure):
+    """struct xtb_step_io"""
+    _fields_ = [("S", C.POINTER(C.c_double)), ("supce", C.POINTER(C.c_double)), ("fe", C.POINTER(C.c_double)),
+                ("n_electrons", C.c_double), ("Te_eV", C.c_double),
+                ("Ei", C.POINTER(C.c_double)), ("fe_out", C.POINTER(C.c_double)), ("mu", C.POINTER(C.c_double)),
+                ("E_band", C.POINTER(C.c_double)), ("F_att", C.POINTER(C.c_double)), ("SCforce_att", C.POINTER(C.c_double)),
+                ("E_rep", C.POINTER(C.c_double)), ("F_rep", C.POINTER(C.c_double)), ("SCforce_rep", C.POINTER(C.c_double)),
+                ("E_wall", C.POINTER(C.c_double)), ("F_wall", C.POINTER(C.c_double)), ("SCforce_wall", C.POINTER(C.c_double))]
 
 
 class DftbPair(C.Structure):
@@ -123,6 +146,7 @@ SIGNATURES = {
     "xtb_set_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
     "xtb_set_block_layout": (C.c_int, [C.c_void_p, C.c_int]),
     "xtb_neighbours": (C.c_int, [C.c_void_p, C.c_double, _pi, _pi, _pd, _pd]),
+    "xtb_cutoff": (C.c_int, [C.c_void_p, _pd]),
     "xtb_neighbours_compact": (C.c_int, [C.c_void_p, C.c_int, _pi, _pi, _pd, _pd, C.POINTER(C.c_int)]),
     "xtb_radial": (C.c_int, [C.c_void_p, _pd, _pd, _pd, _pd, _pd, _pd, _pd]),
     "xtb_assemble_HS": (C.c_int, [C.c_void_p, _pd, _pd]),
@@ -134,6 +158,7 @@ SIGNATURES = {
     "xtb_get_eigenvalues": (C.c_int, [C.c_void_p, _pd]),
     "xtb_set_occupations": (C.c_int, [C.c_void_p, _pd]),
     "xtb_density": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_density_get": (C.c_int, [C.c_void_p, _pd, _pd]),
     "xtb_set_density_cutoff": (C.c_int, [C.c_void_p, C.c_double]),
     "xtb_density_mirror": (C.c_int, [C.c_void_p]),
     "xtb_forces": (C.c_int, [C.c_void_p, _pd]),
@@ -141,6 +166,21 @@ SIGNATURES = {
     "xtb_repulsive_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
     "xtb_repulsive_forces": (C.c_int, [C.c_void_p, _pd]),
     "xtb_repulsive_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_set_params_wall": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(WallPair)]),
+    "xtb_wall_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_wall_forces": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_wall_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_fermi_occupations": (C.c_int, [C.c_void_p, C.c_double, C.c_double, _pd, _pd, _pd]),
+    "xtb_md_set_velocities": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_md_half_step": (C.c_int, [C.c_void_p, C.c_int, C.c_double, _pd, _pd, C.c_uint]),
+    "xtb_md_get_state": (C.c_int, [C.c_void_p, _pd, _pd, _pd, _pd]),
+    "xtb_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "xtb_comm_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
+    "xtb_comm_destroy": (C.c_int, [C.c_void_p]),
+    "xtb_exchange_blocks": (C.c_int, [C.c_void_p, C.c_int]),
+    "xtb_exchange_forces": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_allreduce_scforce": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_step": (C.c_int, [C.c_void_p, C.c_uint, C.POINTER(StepIO)]),
     "xtb_save_eigen_prev": (C.c_int, [C.c_void_p]),
     "xtb_set_eigen_prev": (C.c_int, [C.c_void_p, _pd]),
     "xtb_coupling": (C.c_int, [C.c_void_p, C.c_int, _pd]),

@@ -104,7 +104,18 @@ class TBContext:
         else:
             raise ValueError(wl["tb"])
         self.tb = wl["tb"]
+        if wl.get("wall_params"):
+            self.set_params_wall(wl["wall_params"])
         self.set_system(wl["koa"], wl["S"], wl["supce"])
+
+    def set_params_wall(self, params):
+        """Scell%TB_Expwall(:,:) of class TB_Exp_wall_simple: list of dict(C, r0, d0, dd), (koa1, koa2) column-major; None / [] removes it"""
+        if not params:
+            self._ck(self.lib.xtb_set_params_wall(self.h, 0, None))
+            return
+        nk = int(round(len(params) ** 0.5))
+        arr = (_abi.WallPair * len(params))(*[_abi.WallPair(float(d["C"]), float(d["r0"]), float(d["d0"]), float(d["dd"])) for d in params])
+        self._ck(self.lib.xtb_set_params_wall(self.h, nk, arr))
 
     def set_system(self, koa, S, supce):
         koa = np.ascontiguousarray(koa, dtype=np.int32)
@@ -262,6 +273,106 @@ class TBContext:
         rep = np.zeros(9)
         self._ck(self.lib.xtb_repulsive_pressure(self.h, _dp(rep)))
         return rep.reshape(3, 3, order="F")
+
+    # -- short-range wall (second half) ------------------------------------
+    def get_Exp_wall_s(self):
+        """get_Exp_wall_s, Exponential_wall.f90:990 -> (E_wall [eV], per-atom halves added to MDAtoms(:)%Epot)"""
+        E = np.zeros(1); Epot = np.zeros(self.na)
+        self._ck(self.lib.xtb_wall_energy(self.h, _dp(E), _dp(Epot)))
+        return float(E[0]), Epot
+
+    def d_Exp_wall_pot_s(self):
+        """d_Exp_wall_pot_s, Exponential_wall.f90:1200 -> the term added to forces%rep, (na,3), d/ds units [eV]"""
+        F = np.zeros((self.na, 3))
+        self._ck(self.lib.xtb_wall_forces(self.h, _dp(F)))
+        return F
+
+    def d_Exp_wall_Pressure_s(self):
+        """d_Exp_wall_Pressure_s, Exponential_wall.f90:1334 -> the term added to SCforce%rep(3,3)"""
+        P = np.zeros(9)
+        self._ck(self.lib.xtb_wall_pressure(self.h, _dp(P)))
+        return P.reshape(3, 3, order="F")
+
+    # -- Fermi occupations, velocity-Verlet halves, the fused step (step.cu) ----------------------
+    def fermi_occupations(self, n_electrons, Te_eV):
+        """Electron_Fixed_Te + set_Fermi (Electron_tools.f90:2660,1913) on the device -> (fe, mu, sum f E)"""
+        fe = np.zeros(self.na * self.n_orb); mu = np.zeros(1); eb = np.zeros(1)
+        self._ck(self.lib.xtb_fermi_occupations(self.h, float(n_electrons), float(Te_eV), _dp(fe), _dp(mu), _dp(eb)))
+        return fe, float(mu[0]), float(eb[0])
+
+    def md_set_velocities(self, SV=None):
+        SV = None if SV is None else np.ascontiguousarray(SV, dtype=np.float64)
+        self._ck(self.lib.xtb_md_set_velocities(self.h, _dp(SV)))
+
+    def make_time_step_atoms(self, ind, dt_fs, mass_kg, Vsupce=None, force_terms=_abi.FORCE_ATT):
+        """save_last_timestep + make_time_step_atoms(ind) (Atomic_tools.f90:1177,1873,1897), velocity-Verlet half on the device"""
+        m = np.ascontiguousarray(mass_kg, dtype=np.float64)
+        V = None if Vsupce is None else np.asfortranarray(Vsupce, dtype=np.float64)
+        self._ck(self.lib.xtb_md_half_step(self.h, int(ind), float(dt_fs), _dp(m), _dp(V), int(force_terms)))
+
+    def md_get_state(self, mass_kg=None):
+        """-> (S (na,3), SV (na,3), E_kin [eV] or None)"""
+        S = np.zeros((self.na, 3)); SV = np.zeros((self.na, 3))
+        ek = np.zeros(1) if mass_kg is not None else None
+        m = None if mass_kg is None else np.ascontiguousarray(mass_kg, dtype=np.float64)
+        self._ck(self.lib.xtb_md_get_state(self.h, _dp(S), _dp(SV), _dp(ek), _dp(m)))
+        return S, SV, (None if ek is None else float(ek[0]))
+
+    def step(self, flags=_abi.STEP_ALL, S=None, supce=None, fe=None, n_electrons=0.0, Te_eV=0.0, want=()):
+        """xtb_step: the selected stages as one call.  want: names of host outputs to fetch, any of
+        Ei, fe_out, mu, E_band, F_att, SCforce_att, E_rep, F_rep, SCforce_rep, E_wall, F_wall, SCforce_wall -> dict"""
+        N = self.na * self.n_orb
+        io = _abi.StepIO()
+        keep = []
+        def inp(a, order="C"):
+            if a is None:
+                return None
+            a = np.asfortranarray(a, dtype=np.float64) if order == "F" else np.ascontiguousarray(a, dtype=np.float64)
+            keep.append(a)
+            return _dp(a)
+        io.S = inp(S); io.supce = inp(supce, "F"); io.fe = inp(fe)
+        io.n_electrons = float(n_electrons); io.Te_eV = float(Te_eV)
+        shapes = {"Ei": (N,), "fe_out": (N,), "mu": (1,), "E_band": (1,), "F_att": (self.na, 3), "SCforce_att": (9,),
+                  "E_rep": (1,), "F_rep": (self.na, 3), "SCforce_rep": (9,), "E_wall": (1,), "F_wall": (self.na, 3), "SCforce_wall": (9,)}
+        out = {}
+        for k in want:
+            out[k] = np.zeros(shapes[k])
+            setattr(io, k, _dp(out[k]))
+        self._ck(self.lib.xtb_step(self.h, int(flags), C.byref(io)))
+        for k in out:
+            if k.startswith("SCforce"):
+                out[k] = out[k].reshape(3, 3, order="F")
+            elif shapes[k] == (1,):
+                out[k] = float(out[k][0])
+        return out
+
+    # -- multi-GPU inside the library (comm.cu) -------------------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        buf = C.create_string_buffer(_abi.UNIQUE_ID_BYTES)
+        rc = _abi.load().xtb_comm_unique_id(buf)
+        if rc != 0:
+            raise XtbError(rc, "xtb_comm_unique_id failed (NCCL not found?)")
+        return buf.raw
+
+    def comm_init(self, unique_id, rank, nranks):
+        self._ck(self.lib.xtb_comm_init(self.h, C.c_char_p(unique_id), int(rank), int(nranks)))
+
+    def comm_destroy(self):
+        self._ck(self.lib.xtb_comm_destroy(self.h))
+
+    def exchange_blocks(self, which):
+        self._ck(self.lib.xtb_exchange_blocks(self.h, int(which)))
+
+    def exchange_forces(self, to_host=False):
+        F = np.zeros((self.na, 3)) if to_host else None
+        self._ck(self.lib.xtb_exchange_forces(self.h, _dp(F)))
+        return F
+
+    def allreduce_scforce(self):
+        P = np.zeros(9)
+        self._ck(self.lib.xtb_allreduce_scforce(self.h, _dp(P)))
+        return P.reshape(3, 3, order="F")
 
     # -- nonadiabatic coupling matrix (SURVEY.md 8f item 3) -------------------------------------
     def save_eigen_prev(self):

@@ -133,7 +133,7 @@ int xtb_impl_coupling(xtb_ctx* c, int kind_M) {
     if (!ortho && (rc = xtb_reserve(c, c->d_cpl_T, sizeof(double) * nn))) return rc;
     double* inv0 = (double*)c->d_cpl_inv.p; double* inv1 = inv0 + N;
     const double* Ha0 = (const double*)c->d_Ha0.p;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 11); XTB_T0(c, 12);
     col_invnorm_kernel<<<(unsigned)N, CT, 0, c->stream>>>(N, Ha0, 1.0e-13, inv0);        // Norm0, eps  :812,:883
     XTB_LAUNCH_CHECK(c);
     col_invnorm_kernel<<<(unsigned)N, CT, 0, c->stream>>>(N, c->d_Ha, 1.0e-13, inv1);    // Norm1       :884
@@ -157,19 +157,12 @@ int xtb_impl_coupling(xtb_ctx* c, int kind_M) {
         XTB_LAUNCH_CHECK(c);
         Tm = (const double*)c->d_cpl_T.p;
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+    XTB_T1(c, 12); XTB_T0(c, 13);
     if ((rc = xtb_blas_dgemm(c, true, false, (int)N, (int)N, (int)N, Ha0, (int)N, Tm, (int)N, (double*)c->d_cpl_M.p, (int)N))) return rc;   // G = Ha0^T T
-    XTB_CUDA(c, cudaEventRecord(c->ev_mid2, c->stream));
+    XTB_T1(c, 13);
     const unsigned nt = (unsigned)((N + 31) / 32);
     antisym_kernel<<<dim3(nt, nt), 256, 0, c->stream>>>(N, kind_M == -1 ? -1 : 0, inv0, inv1, (double*)c->d_cpl_M.p);
     XTB_LAUNCH_CHECK(c);
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f, ms_spmm = 0.f, ms_gemm = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    cudaEventElapsedTime(&ms_spmm, c->ev0, c->ev_mid);
-    cudaEventElapsedTime(&ms_gemm, c->ev_mid, c->ev_mid2);
-    c->stage_ms[11] = ms;
-    c->coupling_spmm_ms = ms_spmm; c->coupling_gemm_ms = ms_gemm;
-    return XTB_OK;
+    XTB_T1(c, 11);
+    return xtb_stage_finish(c);
 }

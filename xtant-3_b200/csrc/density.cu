@@ -646,10 +646,10 @@ __global__ void __launch_bounds__(32 * DW_WARPS) density_warp_kernel(int a0, int
 
 // non-owner blocks = transpose of the owner's block
 template <int NO>
-__global__ void mirror_blocks_kernel(int na, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
+__global__ void mirror_blocks_kernel(int i0, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
                                      const int* __restrict__ rev, const signed char* __restrict__ own, const int* __restrict__ rowptr,
                                      double* __restrict__ rho, double* __restrict__ rhoE) {
-    const int i = blockIdx.y;
+    const int i = i0 + blockIdx.y;
     const int q = blockIdx.x;
     if (q >= nn_size[i]) return;
     const size_t e = (size_t)i * cap + q;
@@ -665,19 +665,18 @@ __global__ void mirror_blocks_kernel(int na, int cap, const int* __restrict__ nn
     rhoE[dst] = rhoE[src];
 }
 
-template <int NO>
-int run_density(xtb_ctx* c) {
-    const int na = c->na;
-    const long long N = (long long)na * NO;
+}  // namespace
+
+// Kept states (fe > f_cut) and their weights f_n, f_n E_n.  Runs when the occupations are SET (xtb_set_occupations,
+// xtb_set_eigen*, xtb_set_density_cutoff), not inside the density stage: the count sizes the launches of that stage, and
+// reading it back there would put a host round trip in the middle of the step.
+int xtb_impl_prepare_occupations(xtb_ctx* c) {
     const long long K = c->K;
     int rc;
     if ((rc = xtb_reserve(c, c->d_keep, sizeof(int) * K))) return rc;
     if ((rc = xtb_reserve(c, c->d_wf, sizeof(double) * (K + KC)))) return rc;
     if ((rc = xtb_reserve(c, c->d_wfe, sizeof(double) * (K + KC)))) return rc;
     if ((rc = xtb_reserve(c, c->d_nkeep, 16))) return rc;
-    if ((rc = xtb_reserve(c, c->d_rho, sizeof(double) * NO * NO * (size_t)c->n_blocks))) return rc;
-    if ((rc = xtb_reserve(c, c->d_rhoE, sizeof(double) * NO * NO * (size_t)c->n_blocks))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
     keep_kernel<<<1, 1024, 0, c->stream>>>(K, c->d_fe, c->d_Ei, c->f_cut, (int*)c->d_keep.p, (double*)c->d_wf.p,
                                            (double*)c->d_wfe.p, (int*)c->d_nkeep.p);
     XTB_LAUNCH_CHECK(c);
@@ -685,18 +684,39 @@ int run_density(xtb_ctx* c) {
     XTB_CUDA(c, cudaMemcpyAsync(&nkeep, c->d_nkeep.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     c->k_kept = nkeep;
+    const int kpad = (nkeep + KC - 1) / KC * KC;
+    if (kpad > nkeep) {
+        pad_weights_kernel<<<1, KC, 0, c->stream>>>(nkeep, kpad, (double*)c->d_wf.p, (double*)c->d_wfe.p);
+        XTB_LAUNCH_CHECK(c);
+    }
+    c->have_keep = true;
+    return XTB_OK;
+}
+
+namespace {
+
+template <int NO>
+int run_density(xtb_ctx* c) {
+    const int na = c->na;
+    const long long N = (long long)na * NO;
+    int rc;
+    if (!c->have_keep && (rc = xtb_impl_prepare_occupations(c))) return rc;
+    const int nkeep = (int)c->k_kept;
+    const size_t blk_bytes = sizeof(double) * NO * NO * xtb_blocks_alloc(c);
+    if ((rc = xtb_reserve(c, c->d_rho, blk_bytes))) return rc;
+    if ((rc = xtb_reserve(c, c->d_rhoE, blk_bytes))) return rc;
+    XTB_T0(c, 3);
     const int nchunks = (nkeep + KC - 1) / KC;
     const int kpad = nchunks * KC;
     const int nown = c->a1 - c->a0;
-    // blocks that no kernel below writes (atoms outside [a0,a1)) must not hold garbage
-    XTB_CUDA(c, cudaMemsetAsync(c->d_rho.p, 0, sizeof(double) * NO * NO * (size_t)c->n_blocks, c->stream));
-    XTB_CUDA(c, cudaMemsetAsync(c->d_rhoE.p, 0, sizeof(double) * NO * NO * (size_t)c->n_blocks, c->stream));
+    // blocks that no kernel below writes (atoms outside [a0,a1)) must not hold garbage; on a full range every block is
+    // written by its owner or by the mirror pass
+    if (nown < na || nkeep == 0) {
+        XTB_CUDA(c, cudaMemsetAsync(c->d_rho.p, 0, blk_bytes, c->stream));
+        XTB_CUDA(c, cudaMemsetAsync(c->d_rhoE.p, 0, blk_bytes, c->stream));
+    }
     bool use_dmma = (c->density_impl >= 1) && NO == 9 && nown > 0;
     if (use_dmma) {
-        if (kpad > nkeep) {
-            pad_weights_kernel<<<1, KC, 0, c->stream>>>(nkeep, kpad, (double*)c->d_wf.p, (double*)c->d_wfe.p);
-            XTB_LAUNCH_CHECK(c);
-        }
         if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)kpad * N + 1024))) return rc;
         if (nchunks > 0) {
             dim3 grid(nchunks, (na + CT_AT - 1) / CT_AT);
@@ -712,7 +732,6 @@ int run_density(xtb_ctx* c) {
             ct_tile_kernel<NO><<<grid, CT_THREADS, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, need, c->d_Ha, (double*)c->d_Ct.p);
             XTB_LAUNCH_CHECK(c);
         }
-        XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
         if (c->density_impl == 2) {
             // ---- two column atoms per CTA (density_pair.cuh) ----
             const int gcap = 2 * c->max_nn + 4;
@@ -751,7 +770,7 @@ int run_density(xtb_ctx* c) {
             A.nn_size = (const int*)c->d_nn_size.p; A.nn_list = (const int*)c->d_nn_list.p; A.own = (const signed char*)c->d_own.p;
             A.rowptr = (const int*)c->d_rowptr.p; A.Ct = (const double*)c->d_Ct.p; A.wf = (const double*)c->d_wf.p; A.wfe = (const double*)c->d_wfe.p;
             A.rho = (double*)c->d_rho.p; A.rhoE = (double*)c->d_rhoE.p;
-            XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));         // the contraction kernel alone (stage 7)
+            XTB_T0(c, 7);         // the contraction kernel alone (stage 7)
             XTB_CUDA(c, cudaFuncSetAttribute(pairk::density_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             pairk::density_pair_kernel<<<grid, pairk::THREADS, smem, c->stream>>>(A, gcap);
             XTB_LAUNCH_CHECK(c);
@@ -833,7 +852,7 @@ int run_density(xtb_ctx* c) {
                 rows_by_state_kernel<NO><<<g, 256, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, c->d_Ha, (double*)c->d_Ct.p);
                 XTB_LAUNCH_CHECK(c);
             }
-            XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+            XTB_T0(c, 7);
             dim3 grid((c->max_nn + 1 + DW_WARPS - 1) / DW_WARPS, nown);
             density_warp_kernel<NO><<<grid, 32 * DW_WARPS, 0, c->stream>>>(c->a0, c->a1, c->cap, nkeep,
                                                                             (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
@@ -843,7 +862,7 @@ int run_density(xtb_ctx* c) {
         }
         XTB_LAUNCH_CHECK(c);
     } else if (nown > 0) {
-        XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+        XTB_T0(c, 7);
         dim3 grid(c->max_nn + 1, nown);
         density_simple_kernel<NO><<<grid, 128, 0, c->stream>>>(na, c->a0, c->a1, c->cap, N, nkeep, (const int*)c->d_keep.p,
                                                                (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
@@ -851,26 +870,20 @@ int run_density(xtb_ctx* c) {
                                                                (const double*)c->d_wfe.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
         XTB_LAUNCH_CHECK(c);
     } else {
-        XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+        XTB_T0(c, 7);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev_mid2, c->stream));
+    XTB_T1(c, 7);
     // mirror (complete only when every owner block is local: single-GPU, or after the caller's allgather)
     if (c->a0 == 0 && c->a1 == na && c->max_nn > 0) {
         dim3 grid(c->max_nn, na);
-        mirror_blocks_kernel<NO><<<grid, 96, 0, c->stream>>>(na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+        mirror_blocks_kernel<NO><<<grid, 96, 0, c->stream>>>(0, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
                                                              (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p,
                                                              (double*)c->d_rhoE.p);
         XTB_LAUNCH_CHECK(c);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f, msk = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    cudaEventElapsedTime(&msk, c->ev_mid, c->ev_mid2);
-    c->stage_ms[3] = ms;
-    c->stage_ms[7] = msk;       // main contraction kernel alone
+    XTB_T1(c, 3);
     c->have_density = true;
-    return XTB_OK;
+    return xtb_stage_finish(c);
 }
 
 }  // namespace
@@ -884,16 +897,14 @@ int xtb_impl_density(xtb_ctx* c) {
 
 int xtb_impl_mirror_density(xtb_ctx* c) {
     if (c->max_nn <= 0) return XTB_OK;
-    dim3 grid(c->max_nn, c->na);
-    if (c->n_orb == 1)
-        mirror_blocks_kernel<1><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                            (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
-    else if (c->n_orb == 9)
-        mirror_blocks_kernel<9><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                            (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
-    else
-        mirror_blocks_kernel<4><<<grid, 96, 0, c->stream>>>(c->na, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                            (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p);
+    // a communicating context holds the sources of its own rows only (halo exchange)
+    const int i0 = c->comm ? c->a0 : 0, rows = c->comm ? c->a1 - c->a0 : c->na;
+    if (rows <= 0) return XTB_OK;
+    dim3 grid(c->max_nn, rows);
+#define XTB_MIRROR(NO) mirror_blocks_kernel<NO><<<grid, 96, 0, c->stream>>>(i0, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, \
+        (const int*)c->d_rev.p, (const signed char*)c->d_own.p, (const int*)c->d_rowptr.p, (double*)c->d_rho.p, (double*)c->d_rhoE.p)
+    if (c->n_orb == 1) XTB_MIRROR(1); else if (c->n_orb == 9) XTB_MIRROR(9); else XTB_MIRROR(4);
+#undef XTB_MIRROR
     XTB_LAUNCH_CHECK(c);
     return XTB_OK;
 }

@@ -250,13 +250,13 @@ int assemble(xtb_ctx* c, bool dense) {
     const int na = c->na;
     const size_t N = (size_t)na * NO;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * NO * NO * (size_t)c->n_blocks))) return rc;
-    if ((rc = xtb_reserve(c, c->d_Sblk, sizeof(double) * NO * NO * (size_t)c->n_blocks))) return rc;
+    if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * NO * NO * xtb_blocks_alloc(c)))) return rc;
+    if ((rc = xtb_reserve(c, c->d_Sblk, sizeof(double) * NO * NO * xtb_blocks_alloc(c)))) return rc;
     if (dense) {
         if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
         if ((rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 2);
     const int nown = c->a1 - c->a0;
     const long long nthreads = 2LL * (c->cap + 1) * nown;
     if (nthreads > 0) {
@@ -265,15 +265,11 @@ int assemble(xtb_ctx* c, bool dense) {
             (const int*)c->d_rowptr.p, (const DftbDev*)c->d_params.p, (const double*)c->d_dftb_tab.p, (double*)c->d_Hblk.p, (double*)c->d_Sblk.p);
         XTB_LAUNCH_CHECK(c);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+    XTB_T0(c, 6);      // dense panel kernel alone
     if (dense && (rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, (const double*)c->d_Sblk.p, (double*)c->d_H.p, (double*)c->d_S2.p, false))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f, ms2 = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    cudaEventElapsedTime(&ms2, c->ev_mid, c->ev1);
-    c->stage_ms[2] = ms;
-    c->stage_ms[6] = ms2;
+    XTB_T1(c, 6);
+    XTB_T1(c, 2);
+    if ((rc = xtb_stage_finish(c))) return rc;
     c->have_blocks = true;
     c->have_HS = dense;
     return XTB_OK;
@@ -283,10 +279,8 @@ template <int NO>
 int forces(xtb_ctx* c) {
     const int nown = c->a1 - c->a0;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_F, sizeof(double) * 3 * c->na))) return rc;
-    if ((rc = xtb_reserve(c, c->d_hdev, sizeof(double) * 9))) return rc;
-    XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    if ((rc = xtb_reserve(c, c->d_F, sizeof(double) * 3 * (size_t)(c->na + c->nranks)))) return rc;
+    XTB_T0(c, 4);
     if (nown > 0) {
         const int mx = c->max_nn > 0 ? c->max_nn : 1;
         const size_t smem = sizeof(double) * (size_t)mx * 6;
@@ -298,11 +292,8 @@ int forces(xtb_ctx* c) {
                                                               (const double*)c->d_rhoE.p, (double*)c->d_F.p);
         XTB_LAUNCH_CHECK(c);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[4] = ms;
+    XTB_T1(c, 4);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }
 
@@ -312,7 +303,7 @@ int pressure(xtb_ctx* c) {
     int rc;
     if ((rc = xtb_reserve(c, c->d_SC, sizeof(double) * 9))) return rc;
     if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)(nown > 0 ? nown : 1)))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 5);
     if (nown > 0) {
         const int mx = c->max_nn > 0 ? c->max_nn : 1;
         const size_t smem = sizeof(double) * (size_t)mx * 18;
@@ -328,11 +319,8 @@ int pressure(xtb_ctx* c) {
     } else {
         XTB_CUDA(c, cudaMemsetAsync(c->d_SC.p, 0, sizeof(double) * 9, c->stream));
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[5] = ms;
+    XTB_T1(c, 5);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }
 
@@ -357,9 +345,6 @@ int xtb_impl_dftb_pressure(xtb_ctx* c) {
 }
 
 int xtb_impl_dftb_tables(xtb_ctx* c, double* d_rad, double* d_geo) {
-    int rc;
-    if ((rc = xtb_reserve(c, c->d_hdev, sizeof(double) * 9))) return rc;
-    XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
     const long long tot = (long long)c->na * c->cap;
     const unsigned grid = (unsigned)((tot + 127) / 128);
 #define DFTB_TAB(NO) dftb_tables_kernel<NO><<<grid, 128, 0, c->stream>>>(c->na, c->cap, c->n_kinds, DFTB_ARGS_LIST, (const double*)c->d_nn_dist.p, \

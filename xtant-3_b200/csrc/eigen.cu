@@ -141,7 +141,7 @@ int xtb_impl_eigensolve(xtb_ctx* c) {
     if ((rc = xtb_reserve(c, c->own_Ei, sizeof(double) * N))) return rc;
     if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
     if ((rc = xtb_reserve(c, c->d_eigS, sizeof(double) * N + 16))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 8);
     double* Ha = (double*)c->own_Ha.p;
     double* Ei = (double*)c->own_Ei.p;
     if (ortho) {      // TB_Pettifor.f90:1455: the assembled matrix is diagonalised in place
@@ -176,15 +176,13 @@ int xtb_impl_eigensolve(xtb_ctx* c) {
         // the eigenvectors now live in T: swap the roles of the two buffers
         DevBuf tmp = c->own_Ha; c->own_Ha = c->d_eig_T; c->d_eig_T = tmp;
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->eigen_ms = ms;
+    XTB_T1(c, 8);
+    if ((rc = xtb_stage_finish(c))) return rc;
     c->d_Ha = (const double*)c->own_Ha.p; c->d_Ei = (const double*)c->own_Ei.p; c->d_fe = (const double*)c->own_fe.p;
     c->K = N;
     c->have_eigvec = true;
     c->have_eigen = false;          // occupations still to come (xtb_set_occupations)
+    c->have_keep = false;
     c->have_density = false;
     return XTB_OK;
 }

@@ -143,16 +143,16 @@ extern "C" double xtb_debug_dmma_loop(xtb_ctx* c, int variant, int warps_per_sms
     const int threads = 128 * warps_per_smsp, blocks = c->sm_count, iters = 4000;
     double best = 0.0;
     for (int r = 0; r < reps + 1; ++r) {
-        cudaEventRecord(c->ev0, c->stream);
+        xtb_t0(c, 15);
 #define PROBE(M, V) dmma_loop_probe<M, V><<<blocks, threads, 0, c->stream>>>(iters, (double*)c->d_scratch.p)
 #define PROBE_M(M) { if (variant == 0) PROBE(M, 0); else if (variant == 1) PROBE(M, 1); else if (variant == 2) PROBE(M, 2); else PROBE(M, 3); }
         if (mt == 4) PROBE_M(4) else if (mt == 5) PROBE_M(5) else PROBE_M(6)
 #undef PROBE_M
 #undef PROBE
-        cudaEventRecord(c->ev1, c->stream);
+        xtb_t1(c, 15);
         cudaStreamSynchronize(c->stream);
         float ms = 0.f;
-        cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+        cudaEventElapsedTime(&ms, c->tev[15][0], c->tev[15][1]); c->t_pending &= ~(1u << 15);
         const double warps = (double)blocks * threads / 32.0;
         const int m = mt == 4 ? 4 : mt == 5 ? 5 : 6;
         const double flop = warps * iters * 4.0 * m * (2.0 * 512.0 + (variant >= 2 ? 2.0 * 64.0 : 0.0));
@@ -173,15 +173,15 @@ extern "C" double xtb_debug_fp64_peak(xtb_ctx* c, int mode, int warps_per_sm, in
     const int iters = 20000;
     double best = 0.0;
     for (int r = 0; r < reps + 1; ++r) {
-        cudaEventRecord(c->ev0, c->stream);
+        xtb_t0(c, 15);
         if (mode == 0) dmma_peak_kernel<<<blocks, threads, 0, c->stream>>>(iters, (double*)c->d_scratch.p);
         else if (mode == 2) mixed_peak_kernel<<<blocks, threads, 0, c->stream>>>(iters, (double*)c->d_scratch.p);
         else if (mode == 3) split_peak_kernel<<<blocks, threads, 0, c->stream>>>(iters, (double*)c->d_scratch.p);
         else dfma_peak_kernel<<<blocks, threads, 0, c->stream>>>(iters, (double*)c->d_scratch.p);
-        cudaEventRecord(c->ev1, c->stream);
+        xtb_t1(c, 15);
         cudaStreamSynchronize(c->stream);
         float ms = 0.f;
-        cudaEventElapsedTime(&ms, c->ev0, c->ev1);
+        cudaEventElapsedTime(&ms, c->tev[15][0], c->tev[15][1]); c->t_pending &= ~(1u << 15);
         const double warps = (double)blocks * threads / 32.0;
         const double f_dmma = warps * iters * 8.0 * (8 * 8 * 4 * 2.0), f_dfma = warps * 32.0 * iters * 16.0 * 2.0;
         const double flop = mode == 0 ? f_dmma : mode == 1 ? f_dfma : mode == 2 ? f_dmma + f_dfma : 0.5 * (f_dmma + f_dfma);

@@ -151,11 +151,38 @@ __global__ void __launch_bounds__(256) nn_build_kernel(int na, const double* __r
 // atoms each) start at multiples of the largest range's block count, so that the ranges are equal-length segments of every
 // block store and one in-place all-gather exchanges them.  The gaps are never addressed (every access is rowptr[atom] + q).
 // meta[1] = number of real blocks (na + number of list entries).
-__global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* __restrict__ rowptr, int parts, int* __restrict__ meta) {
+// Guard of the steady-state form (xtb_impl_neighbours_steady): if the largest neighbour count exceeds nn_bound or the block
+// count exceeds blk_capacity -- the sizes the later stages of this step were launched with -- meta[2] is raised and the
+// list is emptied, so that those stages touch only the na on-site blocks.
+__global__ void nn_rowptr_kernel(int na, int* __restrict__ nn_size, int* __restrict__ rowptr, int parts, int* __restrict__ meta,
+                                 int nn_bound, long long blk_capacity) {
     __shared__ int carry;
     __shared__ int buf[1024];
-    if (threadIdx.x == 0) carry = 0;
+    __shared__ int bad;
+    if (threadIdx.x == 0) {
+        carry = 0;
+        bad = meta[0] > nn_bound ? 1 : 0;
+    }
     __syncthreads();
+    if (!bad) {         // block count = na + sum of the list lengths
+        long long part = 0;
+        for (int i = threadIdx.x; i < na; i += 1024) part += nn_size[i] + 1;
+        for (int off = 16; off > 0; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
+        __shared__ long long wsum[32];
+        if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = part;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            long long tot = 0;
+            for (int w = 0; w < 32; ++w) tot += wsum[w];
+            if (tot > blk_capacity) bad = 1;
+        }
+        __syncthreads();
+    }
+    if (bad) {
+        for (int i = threadIdx.x; i < na; i += 1024) nn_size[i] = 0;
+        if (threadIdx.x == 0) meta[2] = 1;
+        __syncthreads();
+    }
     for (int base = 0; base < na; base += 1024) {
         int i = base + threadIdx.x;
         int v = i < na ? nn_size[i] + 1 : 0;
@@ -172,7 +199,7 @@ __global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* _
         if (threadIdx.x == 1023) carry += buf[1023];
         __syncthreads();
     }
-    if (threadIdx.x == 0) { rowptr[na] = carry; meta[1] = carry; }
+    if (threadIdx.x == 0) { rowptr[na] = carry; meta[1] = carry; meta[3] = carry; }
     if (parts <= 1) return;
     __syncthreads();
     // segment bases and the largest segment (parts <= 1024)
@@ -190,7 +217,7 @@ __global__ void nn_rowptr_kernel(int na, const int* __restrict__ nn_size, int* _
         const int r = i / per;
         rowptr[i] = r * mx + (rowptr[i] - buf[r]);
     }
-    if (threadIdx.x == 0) rowptr[na] = parts * mx;
+    if (threadIdx.x == 0) { rowptr[na] = parts * mx; meta[3] = parts * mx; }
 }
 
 // own[e] = 1 iff atom i "owns" the unordered pair (i, j = nn_list[e]) in the symmetric density pass: the pair is
@@ -229,6 +256,68 @@ __global__ void nn_rev_kernel(int na, int cap, const int* __restrict__ nn_size, 
 
 }  // namespace
 
+// One launch sequence of the list: build -> rowptr (+ overflow guard) -> rev / own.  meta = {max count, real blocks,
+// overflow flag, rowptr[na]}.
+static int launch_list(xtb_ctx* c, double rm, int nn_bound, long long blk_capacity) {
+    const int na = c->na, cap = c->cap;
+    XTB_CUDA(c, cudaMemsetAsync(c->d_maxnn.p, 0, sizeof(int) * 4, c->stream));
+    const int warps_per_block = 8;
+    // single-image path: diagonal cell, every edge > 2 rm (see min_image_ortho); XTB_NN_SCAN27=1 forces the full scan
+    const double* hh = c->h_supce;
+    bool ortho = hh[1] == 0.0 && hh[2] == 0.0 && hh[3] == 0.0 && hh[5] == 0.0 && hh[6] == 0.0 && hh[7] == 0.0;
+    for (int k = 0; k < 3 && ortho; ++k) ortho = fabs(hh[4 * k]) > 2.0 * rm * (1.0 + 1e-9);
+    if (const char* ev = getenv("XTB_NN_SCAN27")) { if (atoi(ev) == 1) ortho = false; }
+    const dim3 g((na + warps_per_block - 1) / warps_per_block), b(warps_per_block * 32);
+    if (ortho)
+        nn_build_kernel<true><<<g, b, 0, c->stream>>>(na, (const double*)c->d_S.p, (const double*)c->d_hdev.p, rm, cap, (int*)c->d_nn_size.p,
+                                                      (int*)c->d_nn_list.p, (double*)c->d_nn_dist.p, (double*)c->d_nn_dist_s.p, (int*)c->d_maxnn.p);
+    else
+        nn_build_kernel<false><<<g, b, 0, c->stream>>>(na, (const double*)c->d_S.p, (const double*)c->d_hdev.p, rm, cap, (int*)c->d_nn_size.p,
+                                                       (int*)c->d_nn_list.p, (double*)c->d_nn_dist.p, (double*)c->d_nn_dist_s.p, (int*)c->d_maxnn.p);
+    XTB_LAUNCH_CHECK(c);
+    nn_rowptr_kernel<<<1, 1024, 0, c->stream>>>(na, (int*)c->d_nn_size.p, (int*)c->d_rowptr.p, c->layout_parts, (int*)c->d_maxnn.p,
+                                                nn_bound, blk_capacity);
+    XTB_LAUNCH_CHECK(c);
+    const long long tot = (long long)na * cap;
+    nn_rev_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c->stream>>>(na, cap, (const int*)c->d_nn_size.p,
+                                                                       (const int*)c->d_nn_list.p, (const double*)c->d_nn_dist.p,
+                                                                       (int*)c->d_rev.p, (signed char*)c->d_own.p);
+    XTB_LAUNCH_CHECK(c);
+    return XTB_OK;
+}
+
+static int reserve_list(xtb_ctx* c) {
+    const int na = c->na;
+    const size_t ne = (size_t)na * c->cap;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_nn_size, sizeof(int) * na))) return rc;
+    if ((rc = xtb_reserve(c, c->d_nn_list, sizeof(int) * ne))) return rc;
+    if ((rc = xtb_reserve(c, c->d_rev, sizeof(int) * ne))) return rc;
+    if ((rc = xtb_reserve(c, c->d_own, ne))) return rc;
+    if ((rc = xtb_reserve(c, c->d_nn_dist, sizeof(double) * 4 * ne))) return rc;
+    if ((rc = xtb_reserve(c, c->d_nn_dist_s, sizeof(double) * 3 * ne))) return rc;
+    if ((rc = xtb_reserve(c, c->d_rowptr, sizeof(int) * (na + 1)))) return rc;
+    if ((rc = xtb_reserve(c, c->d_maxnn, sizeof(int) * 4))) return rc;
+    return XTB_OK;
+}
+
+// Steady-state form used inside xtb_step (no host round trip): the list is rebuilt with the capacity, neighbour bound and
+// block capacity of the previous step; nn_rowptr_kernel raises meta[2] and empties the list if one of them is exceeded
+// (later stages then run on a harmless empty list), and xtb_step re-runs the step through the sizing path below when it
+// finds the flag after its single synchronisation.  meta is copied to pinned host memory asynchronously.
+int xtb_impl_neighbours_steady(xtb_ctx* c, double rm) {
+    if (!c->have_shape || c->layout_parts != 1) XTB_FAIL(c, XTB_ESTATE, "neighbours (steady): no sized list yet");
+    int rc;
+    XTB_T0(c, 1);
+    if ((rc = launch_list(c, rm, c->max_nn, c->blk_cap))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->h_meta, c->d_maxnn.p, sizeof(int) * 4, cudaMemcpyDeviceToHost, c->stream));
+    XTB_T1(c, 1);
+    c->rm = rm;
+    c->have_neigh = true;
+    c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
+    return XTB_OK;
+}
+
 int xtb_impl_neighbours(xtb_ctx* c, double rm) {
     const int na = c->na;
     if (na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_neighbours: no system set");
@@ -243,65 +332,30 @@ int xtb_impl_neighbours(xtb_ctx* c, double rm) {
         if (cap < 1) cap = 1;
         c->cap = cap;
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    int rc;
+    XTB_T0(c, 1);
+    int meta[4] = {0, 0, 0, 0};
     for (int attempt = 0; attempt < 4; ++attempt) {
-        const int cap = c->cap;
-        const size_t ne = (size_t)na * cap;
-        int rc;
-        if ((rc = xtb_reserve(c, c->d_nn_size, sizeof(int) * na))) return rc;
-        if ((rc = xtb_reserve(c, c->d_nn_list, sizeof(int) * ne))) return rc;
-        if ((rc = xtb_reserve(c, c->d_rev, sizeof(int) * ne))) return rc;
-        if ((rc = xtb_reserve(c, c->d_own, ne))) return rc;
-        if ((rc = xtb_reserve(c, c->d_nn_dist, sizeof(double) * 4 * ne))) return rc;
-        if ((rc = xtb_reserve(c, c->d_nn_dist_s, sizeof(double) * 3 * ne))) return rc;
-        if ((rc = xtb_reserve(c, c->d_rowptr, sizeof(int) * (na + 1)))) return rc;
-        if ((rc = xtb_reserve(c, c->d_maxnn, sizeof(int) * 4))) return rc;
-        if ((rc = xtb_reserve(c, c->d_scratch, 256))) return rc;
-        XTB_CUDA(c, cudaMemsetAsync(c->d_maxnn.p, 0, sizeof(int) * 4, c->stream));
-        XTB_CUDA(c, cudaMemcpyAsync(c->d_scratch.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
-        const int warps_per_block = 8;
-        // single-image path: diagonal cell, every edge > 2 rm (see min_image_ortho); XTB_NN_SCAN27=1 forces the full scan
-        const double* hh = c->h_supce;
-        bool ortho = hh[1] == 0.0 && hh[2] == 0.0 && hh[3] == 0.0 && hh[5] == 0.0 && hh[6] == 0.0 && hh[7] == 0.0;
-        for (int k = 0; k < 3 && ortho; ++k) ortho = fabs(hh[4 * k]) > 2.0 * rm * (1.0 + 1e-9);
-        if (const char* ev = getenv("XTB_NN_SCAN27")) { if (atoi(ev) == 1) ortho = false; }
-        const dim3 g((na + warps_per_block - 1) / warps_per_block), b(warps_per_block * 32);
-        if (ortho)
-            nn_build_kernel<true><<<g, b, 0, c->stream>>>(na, (const double*)c->d_S.p, (const double*)c->d_scratch.p, rm, cap, (int*)c->d_nn_size.p,
-                                                          (int*)c->d_nn_list.p, (double*)c->d_nn_dist.p, (double*)c->d_nn_dist_s.p, (int*)c->d_maxnn.p);
-        else
-            nn_build_kernel<false><<<g, b, 0, c->stream>>>(na, (const double*)c->d_S.p, (const double*)c->d_scratch.p, rm, cap, (int*)c->d_nn_size.p,
-                                                           (int*)c->d_nn_list.p, (double*)c->d_nn_dist.p, (double*)c->d_nn_dist_s.p, (int*)c->d_maxnn.p);
-        XTB_LAUNCH_CHECK(c);
-        int mx = 0;
-        XTB_CUDA(c, cudaMemcpyAsync(&mx, c->d_maxnn.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        if ((rc = reserve_list(c))) return rc;
+        if ((rc = launch_list(c, rm, 0x7fffffff, 0x7fffffffffffLL))) return rc;
+        XTB_CUDA(c, cudaMemcpyAsync(meta, c->d_maxnn.p, sizeof(int) * 4, cudaMemcpyDeviceToHost, c->stream));
+        XTB_T1(c, 1);
         XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-        if (mx <= cap) { c->max_nn = mx; break; }
-        if (attempt == 3) XTB_FAIL(c, XTB_ECAPACITY, "neighbour capacity %d exceeded (%d) after retries", cap, mx);
+        if (meta[0] <= c->cap) break;
+        if (attempt == 3) XTB_FAIL(c, XTB_ECAPACITY, "neighbour capacity %d exceeded (%d) after retries", c->cap, meta[0]);
+        const int mx = meta[0];
         c->cap = mx + 8 > na - 1 ? na - 1 : mx + 8;
         if (c->cap < mx) c->cap = mx;
     }
-    nn_rowptr_kernel<<<1, 1024, 0, c->stream>>>(na, (const int*)c->d_nn_size.p, (int*)c->d_rowptr.p, c->layout_parts, (int*)c->d_maxnn.p);
-    XTB_LAUNCH_CHECK(c);
-    {
-        const long long tot = (long long)na * c->cap;
-        nn_rev_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, c->stream>>>(na, c->cap, (const int*)c->d_nn_size.p,
-                                                                           (const int*)c->d_nn_list.p, (const double*)c->d_nn_dist.p,
-                                                                           (int*)c->d_rev.p, (signed char*)c->d_own.p);
-        XTB_LAUNCH_CHECK(c);
-    }
-    int nb = 0, nreal = 0;
-    XTB_CUDA(c, cudaMemcpyAsync(&nb, (int*)c->d_rowptr.p + na, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    XTB_CUDA(c, cudaMemcpyAsync(&nreal, (int*)c->d_maxnn.p + 1, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[1] = ms;
-    c->n_blocks = nb;
-    c->n_pairs = nreal - na;      // real list entries (nb counts the layout gaps of xtb_set_block_layout as well)
+    if ((rc = xtb_collect_timing(c))) return rc;
+    c->max_nn = c->max_nn_seen = meta[0];
+    c->n_blocks = meta[3];
+    c->n_pairs = meta[1] - na;      // real list entries (n_blocks counts the layout gaps of xtb_set_block_layout as well)
+    c->blk_cap = c->n_blocks;
+    c->have_shape = false;          // xtb_step arms the steady-state form (with its slack) when it wants it
     c->rm = rm;
     c->have_neigh = true;
-    c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
+    c->have_HS = c->have_blocks = c->have_density = c->have_dens = c->have_halo = false;
+    if (c->comm && c->nranks > 1 && (rc = xtb_impl_comm_lists(c))) return rc;      // halo transfer lists of this list
     return XTB_OK;
 }

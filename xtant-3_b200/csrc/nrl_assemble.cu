@@ -236,9 +236,6 @@ __global__ void nrl_tables_kernel(int na, int cap, int n_kinds, const int* __res
 }
 
 int xtb_impl_nrl_tables(xtb_ctx* c, double* d_rad, double* d_geo) {
-    int rc;
-    if ((rc = xtb_reserve(c, c->d_hdev, sizeof(double) * 9))) return rc;
-    XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
     const long long tot = (long long)c->na * c->cap;
     nrl_tables_kernel<<<(unsigned)((tot + 127) / 128), 128, 0, c->stream>>>(c->na, c->cap, c->n_kinds, (const int*)c->d_koa.p,
                                                                            (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
@@ -266,13 +263,13 @@ int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense) {
     const int na = c->na;
     const size_t N = (size_t)na * 9;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 81 * (size_t)c->n_blocks))) return rc;
-    if ((rc = xtb_reserve(c, c->d_Sblk, sizeof(double) * 81 * (size_t)c->n_blocks))) return rc;
+    if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 81 * xtb_blocks_alloc(c)))) return rc;
+    if ((rc = xtb_reserve(c, c->d_Sblk, sizeof(double) * 81 * xtb_blocks_alloc(c)))) return rc;
     if (dense) {
         if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
         if ((rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 2);
     if ((rc = xtb_impl_nrl_dens(c))) return rc;
     const int nown = c->a1 - c->a0;
     const long long nthreads = 2LL * (c->cap + 1) * nown;
@@ -285,15 +282,11 @@ int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense) {
             (const double*)c->d_dens.p, (double*)c->d_Hblk.p, (double*)c->d_Sblk.p);
         XTB_LAUNCH_CHECK(c);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+    XTB_T0(c, 6);      // dense panel kernel alone
     if (dense && (rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, (const double*)c->d_Sblk.p, (double*)c->d_H.p, (double*)c->d_S2.p, false))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f, ms2 = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    cudaEventElapsedTime(&ms2, c->ev_mid, c->ev1);
-    c->stage_ms[2] = ms;
-    c->stage_ms[6] = ms2;     // dense panel kernel alone
+    XTB_T1(c, 6);
+    XTB_T1(c, 2);
+    if ((rc = xtb_stage_finish(c))) return rc;
     c->have_blocks = true;
     c->have_HS = dense;
     return XTB_OK;

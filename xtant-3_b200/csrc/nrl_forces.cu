@@ -296,10 +296,8 @@ int launch_onsite_w(xtb_ctx* c) {
 int xtb_impl_nrl_forces(xtb_ctx* c) {
     const int nown = c->a1 - c->a0;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_F, sizeof(double) * 3 * c->na))) return rc;
-    if ((rc = xtb_reserve(c, c->d_hdev, sizeof(double) * 9))) return rc;
-    XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    if ((rc = xtb_reserve(c, c->d_F, sizeof(double) * 3 * (size_t)(c->na + c->nranks)))) return rc;
+    XTB_T0(c, 4);
     if ((rc = launch_onsite_w(c))) return rc;
     if (nown > 0) {
         const int mx = c->max_nn > 0 ? c->max_nn : 1;
@@ -319,11 +317,8 @@ int xtb_impl_nrl_forces(xtb_ctx* c) {
                                                          (const double*)c->d_rhoE.p, stage_blocks, (double*)c->d_F.p);
         XTB_LAUNCH_CHECK(c);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[4] = ms;
+    XTB_T1(c, 4);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }
 
@@ -332,7 +327,7 @@ int xtb_impl_nrl_pressure(xtb_ctx* c) {
     int rc;
     if ((rc = xtb_reserve(c, c->d_SC, sizeof(double) * 9))) return rc;
     if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)(nown > 0 ? nown : 1)))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 5);
     if ((rc = launch_onsite_w(c))) return rc;
     if (nown > 0) {
         const int mx = c->max_nn > 0 ? c->max_nn : 1;
@@ -350,10 +345,7 @@ int xtb_impl_nrl_pressure(xtb_ctx* c) {
     } else {
         XTB_CUDA(c, cudaMemsetAsync(c->d_SC.p, 0, sizeof(double) * 9, c->stream));
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[5] = ms;
+    XTB_T1(c, 5);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }

@@ -245,9 +245,9 @@ int xtb_impl_pettifor_assemble(xtb_ctx* c, bool dense) {
     const int na = c->na;
     const size_t N = (size_t)na * 4;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 16 * (size_t)c->n_blocks))) return rc;
+    if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 16 * xtb_blocks_alloc(c)))) return rc;
     if (dense && (rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 2);
     const int nown = c->a1 - c->a0;
     const long long nthreads = (long long)(c->cap + 1) * nown;
     if (nthreads > 0) {
@@ -257,15 +257,11 @@ int xtb_impl_pettifor_assemble(xtb_ctx* c, bool dense) {
             (const xtb_pettifor_pair*)c->d_params.p, (double*)c->d_Hblk.p);
         XTB_LAUNCH_CHECK(c);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev_mid, c->stream));
+    XTB_T0(c, 6);      // dense panel kernel alone
     if (dense && (rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, nullptr, (double*)c->d_H.p, nullptr, false))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f, ms2 = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    cudaEventElapsedTime(&ms2, c->ev_mid, c->ev1);
-    c->stage_ms[2] = ms;
-    c->stage_ms[6] = ms2;
+    XTB_T1(c, 6);
+    XTB_T1(c, 2);
+    if ((rc = xtb_stage_finish(c))) return rc;
     c->have_blocks = true;
     c->have_HS = dense;
     return XTB_OK;
@@ -274,10 +270,8 @@ int xtb_impl_pettifor_assemble(xtb_ctx* c, bool dense) {
 int xtb_impl_pettifor_forces(xtb_ctx* c) {
     const int nown = c->a1 - c->a0;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_F, sizeof(double) * 3 * c->na))) return rc;
-    if ((rc = xtb_reserve(c, c->d_hdev, sizeof(double) * 9))) return rc;
-    XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    if ((rc = xtb_reserve(c, c->d_F, sizeof(double) * 3 * (size_t)(c->na + c->nranks)))) return rc;
+    XTB_T0(c, 4);
     if (nown > 0) {
         const int mx = c->max_nn > 0 ? c->max_nn : 1;
         const size_t smem = sizeof(double) * 3 * (size_t)mx;
@@ -289,11 +283,8 @@ int xtb_impl_pettifor_forces(xtb_ctx* c) {
                                                          (const double*)c->d_rho.p, (double*)c->d_F.p);
         XTB_LAUNCH_CHECK(c);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[4] = ms;
+    XTB_T1(c, 4);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }
 
@@ -302,7 +293,7 @@ int xtb_impl_pettifor_pressure(xtb_ctx* c) {
     int rc;
     if ((rc = xtb_reserve(c, c->d_SC, sizeof(double) * 9))) return rc;
     if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)(nown > 0 ? nown : 1)))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 5);
     if (nown > 0) {
         const int mx = c->max_nn > 0 ? c->max_nn : 1;
         const size_t smem = sizeof(double) * 9 * (size_t)mx;
@@ -318,10 +309,7 @@ int xtb_impl_pettifor_pressure(xtb_ctx* c) {
     } else {
         XTB_CUDA(c, cudaMemsetAsync(c->d_SC.p, 0, sizeof(double) * 9, c->stream));
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[5] = ms;
+    XTB_T1(c, 5);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }

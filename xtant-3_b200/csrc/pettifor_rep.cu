@@ -184,26 +184,21 @@ static int rep_pass1(xtb_ctx* c) {
 }
 
 int xtb_impl_pettifor_rep_energy(xtb_ctx* c) {
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 9);
     int rc = rep_pass1(c);
     if (rc) return rc;
     rep_esum_kernel<<<1, 256, 0, c->stream>>>(c->na, (const double*)c->d_Epot.p, (double*)c->d_Erep.p);
     XTB_LAUNCH_CHECK(c);
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[9] = ms;
+    XTB_T1(c, 9);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }
 
 int xtb_impl_pettifor_rep_forces(xtb_ctx* c) {
     const int nown = c->a1 - c->a0;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_Frep, sizeof(double) * 3 * c->na))) return rc;
-    if ((rc = xtb_reserve(c, c->d_hdev, sizeof(double) * 9))) return rc;
-    XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, c->h_supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    if ((rc = xtb_reserve(c, c->d_Frep, sizeof(double) * 3 * (size_t)(c->na + c->nranks)))) return rc;
+    XTB_T0(c, 9);
     if ((rc = rep_pass1(c))) return rc;
     if (nown > 0) {
         rep_forces_kernel<<<(nown + RW - 1) / RW, 32 * RW, 0, c->stream>>>(c->a0, c->a1, c->cap, c->n_kinds, (const int*)c->d_koa.p,
@@ -214,11 +209,8 @@ int xtb_impl_pettifor_rep_forces(xtb_ctx* c) {
                                                                          (double*)c->d_Frep.p);
         XTB_LAUNCH_CHECK(c);
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[9] = ms;
+    XTB_T1(c, 9);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }
 
@@ -227,7 +219,7 @@ int xtb_impl_pettifor_rep_pressure(xtb_ctx* c) {
     int rc;
     if ((rc = xtb_reserve(c, c->d_SCrep, sizeof(double) * 9))) return rc;
     if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)(nown > 0 ? nown : 1)))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
+    XTB_T0(c, 10);
     if ((rc = rep_pass1(c))) return rc;
     if (nown > 0) {
         rep_pressure_kernel<<<(nown + RW - 1) / RW, 32 * RW, 0, c->stream>>>(c->a0, c->a1, c->cap, c->n_kinds, (const int*)c->d_koa.p,
@@ -241,10 +233,7 @@ int xtb_impl_pettifor_rep_pressure(xtb_ctx* c) {
     } else {
         XTB_CUDA(c, cudaMemsetAsync(c->d_SCrep.p, 0, sizeof(double) * 9, c->stream));
     }
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[10] = ms;
+    XTB_T1(c, 10);
+    if ((rc = xtb_stage_finish(c))) return rc;
     return XTB_OK;
 }

@@ -1,0 +1,385 @@
+// xtb_step: the whole per-MD-step path as ONE host call with one synchronisation at its end, plus the two small host-side
+// pieces of the reference's step that sit between its stages and would otherwise force a round trip through the host:
+//   * Fermi occupations at fixed electron temperature: Electron_Fixed_Te (Electron_tools.f90:2660-2706: bisection of mu on
+//     [E_1 - 50, E_N + 50] until |N(mu) - Ne| <= Ne * 1e-12 or |a - b| < 1e-12), get_N_tot (:2758-2801) and set_Fermi
+//     (:1913-1969: fe = 2 / (1 + exp((E - mu) / Te)), 0 beyond exp overflow; Te = 0: step function);
+//   * the velocity-Verlet halves make_time_step_atoms_SC (Atomic_tools.f90:1897-1974) with save_last_timestep (:1177-1192)
+//     and the periodic arm of check_boundaries / update_atom_crossing_boundary (:2639-2693).
+// Call sequence replaced: get_Hamilonian_and_E (TB.f90:196-330) for the stages of this graft, MD_step (TB.f90:88-192,
+// velocity-Verlet arm) and the AT_MOVE_2 block of the main loop (XTANT_MAIN_FILE.f90:380-386).
+#include "xtb_ctx.h"
+#include <cmath>
+#include <cstring>
+#include <cfloat>
+
+namespace {
+
+// ---- Fermi occupations ----------------------------------------------------------------------------------------------------
+// One CTA.  N(mu) is summed per thread over a strided subset and then over the threads in a fixed tree, so the bisection
+// takes the same path on every run.  (The reference sums i = 1..N sequentially; the comparison N(mu) > Ne can differ from
+// its result only when |N(mu) - Ne| is at the rounding level of the sum, i.e. inside the 1e-12 termination window.)
+constexpr int FT_THREADS = 1024;
+
+__device__ __forceinline__ double fermi_f(double E, double mu, double Te) {
+    const double arg = (E - mu) / Te;
+    return arg < 709.782712893384 /* log(huge(0d0)) */ ? 2.0 / (1.0 + exp(arg)) : 0.0;
+}
+
+__device__ double block_sum(double v, double* sh) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+    if (threadIdx.x < 32) {
+        t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.0;
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(0xffffffffu, t, off);
+        if (threadIdx.x == 0) sh[32] = t;
+    }
+    __syncthreads();
+    return sh[32];
+}
+
+__global__ void __launch_bounds__(FT_THREADS) fermi_kernel(long long N, const double* __restrict__ Ei, double Ne, double Te,
+                                                           double* __restrict__ fe, double* __restrict__ out /*mu, N(mu), sum f E, iterations*/) {
+    __shared__ double sh[33];
+    double a = Ei[0] - 50.0, b = Ei[N - 1] + 50.0, mu = 0.0, Ncur = 0.0;
+    int it = 0;
+    while (fabs(Ncur - Ne) > Ne * 1e-12) {
+        mu = (a + b) / 2.0;
+        double part = 0.0;
+        if (Te > 1.0e-12) { for (long long i = threadIdx.x; i < N; i += FT_THREADS) part += fermi_f(Ei[i], mu, Te); }
+        else              { for (long long i = threadIdx.x; i < N; i += FT_THREADS) part += Ei[i] <= mu ? 2.0 : 0.0; }
+        Ncur = block_sum(part, sh);
+        if (Ncur > Ne) b = mu; else a = mu;
+        ++it;
+        if (fabs(a - b) < 1e-12 || it > 4000) break;
+    }
+    double pe = 0.0;
+    for (long long i = threadIdx.x; i < N; i += FT_THREADS) {
+        double f = 0.0;                                                    // set_Fermi :1943-1966
+        if (Te > 0.0) {
+            const double arg = (Ei[i] - mu) / Te;
+            if (arg <= 709.782712893384) f = 2.0 / (1.0 + exp(arg));
+        } else f = Ei[i] <= mu ? 2.0 : 0.0;
+        fe[i] = f;
+        pe += f * Ei[i];
+    }
+    const double Etot = block_sum(pe, sh);
+    if (threadIdx.x == 0) { out[0] = mu; out[1] = Ncur; out[2] = Etot; out[3] = (double)it; }
+}
+
+// ---- velocity-Verlet halves -----------------------------------------------------------------------------------------------
+// par: [0..8] g^-1 (col-major), [9..17] GinvGdot, [18] dt, [19] dt^2/2, [20] dt/2; minv[kind] = -g_e * 1e-10 / M
+__global__ void md_half_kernel(int na, int ind, const int* __restrict__ koa, const double* __restrict__ par, const double* __restrict__ minv,
+                               const double* __restrict__ Fa, const double* __restrict__ Fb, const double* __restrict__ Fc,
+                               double* __restrict__ S, double* __restrict__ S0, double* __restrict__ SV, double* __restrict__ SV0) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= na) return;
+    // save_last_timestep: S0 = S, SV0 = SV
+    double s0[3], v0[3], f[3];
+#pragma unroll
+    for (int x = 0; x < 3; ++x) {
+        s0[x] = S[3 * k + x]; v0[x] = SV[3 * k + x];
+        S0[3 * k + x] = s0[x]; SV0[3 * k + x] = v0[x];
+        f[x] = Fa[3 * k + x];
+        if (Fb) f[x] += Fb[3 * k + x];
+        if (Fc) f[x] += Fc[3 * k + x];
+    }
+    const double fctr = minv[koa[k]];
+    double acc[3];
+#pragma unroll
+    for (int x = 0; x < 3; ++x) {
+        const double x0 = par[x] * f[0] + par[x + 3] * f[1] + par[x + 6] * f[2];                 // g^-1 F       :1935
+        const double gg = par[9 + x] * v0[0] + par[12 + x] * v0[1] + par[15 + x] * v0[2];         // PR_sc_at     :1942
+        acc[x] = fctr * x0 - gg;                                                                 // :1939,:1944
+    }
+#pragma unroll
+    for (int x = 0; x < 3; ++x) {
+        if (ind == 2) {
+            double s = s0[x] + par[18] * v0[x] + acc[x] * par[19];                               // :1946
+            if (s > 1.0 || s < -0.0) s = s - floor(s);                                           // periodic arm :2654,:2692
+            S[3 * k + x] = s;
+        }
+        SV[3 * k + x] = v0[x] + acc[x] * par[20];                                                // :1948
+    }
+}
+
+// kinetic energy [eV]: sum_k M_k/2 |h SV_k|^2 * (1e5 m/s per A/fs)^2 / g_e   (get_Ekin, Atomic_tools.f90)
+__global__ void __launch_bounds__(256) md_ekin_kernel(int na, const int* __restrict__ koa, const double* __restrict__ h, const double* __restrict__ mass,
+                                                      const double* __restrict__ SV, double* __restrict__ out) {
+    __shared__ double sh[33];
+    double part = 0.0;
+    for (int k = threadIdx.x; k < na; k += 256) {
+        double v2 = 0.0;
+#pragma unroll
+        for (int x = 0; x < 3; ++x) {
+            const double v = SV[3 * k] * h[3 * x] + SV[3 * k + 1] * h[3 * x + 1] + SV[3 * k + 2] * h[3 * x + 2];     // V(x) = sum_k SV(k) supce(k,x)
+            v2 += v * v;
+        }
+        part += 0.5 * mass[koa[k]] * v2;
+    }
+    const double tot = block_sum(part, sh);
+    if (threadIdx.x == 0) out[0] = tot * 1.0e10 / 1.602176634e-19;
+}
+
+void inv3(const double* m, double* o) {       // col-major 3x3
+    const double a = m[0], b = m[3], c = m[6], d = m[1], e = m[4], f = m[7], g = m[2], h = m[5], i = m[8];
+    const double det = a * (e * i - f * h) - b * (d * i - f * g) + c * (d * h - e * g);
+    const double r = 1.0 / det;
+    o[0] = (e * i - f * h) * r; o[3] = (c * h - b * i) * r; o[6] = (b * f - c * e) * r;
+    o[1] = (f * g - d * i) * r; o[4] = (a * i - c * g) * r; o[7] = (c * d - a * f) * r;
+    o[2] = (d * h - e * g) * r; o[5] = (b * g - a * h) * r; o[8] = (a * e - b * d) * r;
+}
+void mul3(const double* A, const double* B, double* C) {      // col-major C = A B
+    for (int c = 0; c < 3; ++c) for (int r = 0; r < 3; ++r) {
+        double s = 0.0;
+        for (int k = 0; k < 3; ++k) s += A[r + 3 * k] * B[k + 3 * c];
+        C[r + 3 * c] = s;
+    }
+}
+void tr3(const double* A, double* T) { for (int c = 0; c < 3; ++c) for (int r = 0; r < 3; ++r) T[r + 3 * c] = A[c + 3 * r]; }
+
+}  // namespace
+
+int xtb_impl_fermi(xtb_ctx* c, double n_electrons, double Te_eV) {
+    const long long N = (long long)c->na * c->n_orb;
+    if (!c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_fermi_occupations: no eigenvalues on the device");
+    int rc;
+    if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
+    if ((rc = xtb_reserve(c, c->d_fermi, 64))) return rc;
+    fermi_kernel<<<1, FT_THREADS, 0, c->stream>>>(N, c->d_Ei, n_electrons, Te_eV, (double*)c->own_fe.p, (double*)c->d_fermi.p);
+    XTB_LAUNCH_CHECK(c);
+    c->d_fe = (const double*)c->own_fe.p;
+    c->K = N;
+    c->have_eigen = true; c->have_density = false; c->have_keep = false;
+    return XTB_OK;
+}
+
+extern "C" {
+
+int xtb_fermi_occupations(xtb_ctx* c, double n_electrons, double Te_eV, double* fe, double* mu, double* E_band) {
+    if (!c) return XTB_EINVAL;
+    if (!(n_electrons > 0.0) || !(Te_eV >= 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_fermi_occupations: Ne = %g, Te = %g", n_electrons, Te_eV);
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = xtb_impl_fermi(c, n_electrons, Te_eV))) return rc;
+    const long long N = (long long)c->na * c->n_orb;
+    double out[4] = {0, 0, 0, 0};
+    XTB_CUDA(c, cudaMemcpyAsync(out, c->d_fermi.p, sizeof out, cudaMemcpyDeviceToHost, c->stream));
+    if (fe) XTB_CUDA(c, cudaMemcpyAsync(fe, c->own_fe.p, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
+    if ((rc = xtb_impl_prepare_occupations(c))) return rc;         // synchronises
+    if (mu) *mu = out[0];
+    if (E_band) *E_band = out[2];
+    return XTB_OK;
+}
+
+int xtb_md_set_velocities(xtb_ctx* c, const double* SV) {
+    if (!c) return XTB_EINVAL;
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_md_set_velocities: no system set");
+    cudaSetDevice(c->device);
+    const size_t b = sizeof(double) * 3 * c->na;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_SV, b)) || (rc = xtb_reserve(c, c->d_SV0, b)) || (rc = xtb_reserve(c, c->d_S0, b))) return rc;
+    if (SV) XTB_CUDA(c, cudaMemcpyAsync(c->d_SV.p, SV, b, cudaMemcpyHostToDevice, c->stream));
+    else XTB_CUDA(c, cudaMemsetAsync(c->d_SV.p, 0, b, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->have_md = true;
+    return XTB_OK;
+}
+
+int xtb_md_get_state(xtb_ctx* c, double* S, double* SV, double* E_kin, const double* mass_kg) {
+    if (!c) return XTB_EINVAL;
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_md_get_state: no system set");
+    cudaSetDevice(c->device);
+    const size_t b = sizeof(double) * 3 * c->na;
+    if (S) XTB_CUDA(c, cudaMemcpyAsync(S, c->d_S.p, b, cudaMemcpyDeviceToHost, c->stream));
+    if (SV) {
+        if (!c->have_md) XTB_FAIL(c, XTB_ESTATE, "xtb_md_get_state: no velocities (xtb_md_set_velocities)");
+        XTB_CUDA(c, cudaMemcpyAsync(SV, c->d_SV.p, b, cudaMemcpyDeviceToHost, c->stream));
+    }
+    double ek = 0.0;
+    if (E_kin) {
+        if (!c->have_md || !mass_kg) XTB_FAIL(c, XTB_ESTATE, "xtb_md_get_state: kinetic energy needs velocities and masses");
+        int rc;
+        if ((rc = xtb_reserve(c, c->d_mdpar, sizeof(double) * (32 + 2 * (size_t)c->n_kinds)))) return rc;
+        double* dm = (double*)c->d_mdpar.p + 32 + c->n_kinds;
+        XTB_CUDA(c, cudaMemcpyAsync(dm, mass_kg, sizeof(double) * c->n_kinds, cudaMemcpyHostToDevice, c->stream));
+        md_ekin_kernel<<<1, 256, 0, c->stream>>>(c->na, (const int*)c->d_koa.p, (const double*)c->d_hdev.p, dm, (const double*)c->d_SV.p, (double*)c->d_mdpar.p + 24);
+        XTB_LAUNCH_CHECK(c);
+        XTB_CUDA(c, cudaMemcpyAsync(&ek, (double*)c->d_mdpar.p + 24, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    }
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (E_kin) *E_kin = ek;
+    return XTB_OK;
+}
+
+int xtb_md_half_step(xtb_ctx* c, int ind, double dt_fs, const double* mass_kg, const double* Vsupce, unsigned force_terms) {
+    if (!c) return XTB_EINVAL;
+    if (ind != 1 && ind != 2) XTB_FAIL(c, XTB_EINVAL, "xtb_md_half_step: ind = %d (1 or 2)", ind);
+    if (!mass_kg || !(dt_fs > 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_md_half_step: masses / dt");
+    if (!c->have_md) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no velocities (xtb_md_set_velocities)");
+    if (c->a0 != 0 || c->a1 != c->na) { if (!c->comm) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: partitioned context without exchanged forces"); }
+    cudaSetDevice(c->device);
+    const double* Fa = (force_terms & XTB_FORCE_ATT) ? (const double*)c->d_F.p : nullptr;
+    const double* Fb = (force_terms & XTB_FORCE_REP) ? (const double*)c->d_Frep.p : nullptr;
+    const double* Fc = (force_terms & XTB_FORCE_WALL) ? (const double*)c->d_Fwall.p : nullptr;
+    if ((force_terms & XTB_FORCE_ATT) && !Fa) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no attractive forces on the device");
+    if ((force_terms & XTB_FORCE_REP) && !Fb) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no repulsive forces on the device");
+    if ((force_terms & XTB_FORCE_WALL) && !Fc) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no wall forces on the device");
+    const double* terms[3] = {Fa, Fb, Fc};
+    const double* F3[3] = {nullptr, nullptr, nullptr};
+    int nt = 0;
+    for (int t = 0; t < 3; ++t) if (terms[t]) F3[nt++] = terms[t];
+    if (nt == 0) XTB_FAIL(c, XTB_EINVAL, "xtb_md_half_step: no force term selected");
+    // g^-1 = (h^T h)^-1 (:1916-1922) and GinvGdot (get_GGdot :1843-1861)
+    double par[24] = {0};
+    double hT[9], g[9], gi[9];
+    tr3(c->h_supce, hT); mul3(hT, c->h_supce, g); inv3(g, gi);
+    memcpy(par, gi, sizeof gi);
+    if (Vsupce) {
+        double vT[9], g1[9], g2[9], gd[9], gg[9];
+        tr3(Vsupce, vT); mul3(vT, c->h_supce, g1); mul3(hT, Vsupce, g2);
+        for (int x = 0; x < 9; ++x) gd[x] = g2[x] + g1[x];
+        mul3(gi, gd, gg);
+        memcpy(par + 9, gg, sizeof gg);
+    }
+    par[18] = dt_fs; par[19] = dt_fs * dt_fs / 2.0; par[20] = dt_fs / 2.0;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_mdpar, sizeof(double) * (32 + 2 * (size_t)c->n_kinds)))) return rc;
+    std::vector<double> up(32 + c->n_kinds, 0.0);
+    memcpy(up.data(), par, sizeof par);
+    for (int k = 0; k < c->n_kinds; ++k) up[32 + k] = -1.0 / mass_kg[k] * 1.602176634e-19 * 1e-10;       // fctr :1938
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_mdpar.p, up.data(), sizeof(double) * up.size(), cudaMemcpyHostToDevice, c->stream));
+    md_half_kernel<<<(c->na + 127) / 128, 128, 0, c->stream>>>(c->na, ind, (const int*)c->d_koa.p, (const double*)c->d_mdpar.p,
+                                                               (const double*)c->d_mdpar.p + 32, F3[0], F3[1], F3[2],
+                                                               (double*)c->d_S.p, (double*)c->d_S0.p, (double*)c->d_SV.p, (double*)c->d_SV0.p);
+    XTB_LAUNCH_CHECK(c);
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));           // `up` is a host temporary
+    if (ind == 2) c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;    // the atoms moved
+    return XTB_OK;
+}
+
+// ---- the fused step -------------------------------------------------------------------------------------------------------
+static int step_body(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool steady_list) {
+    int rc = XTB_OK;
+    const size_t N = (size_t)c->na * c->n_orb;
+    if (flags & XTB_STEP_NEIGHBOURS) {
+        double rm = c->rm > 0.0 ? c->rm : xtb_default_cutoff(c);      // the radius of the last list, else as get_near_neighbours derives it
+        if (rm <= 0.0) XTB_FAIL(c, XTB_EINVAL, "xtb_step: no cut-off radius");
+        if (steady_list) rc = xtb_impl_neighbours_steady(c, rm);
+        else {
+            c->deferred = false;                    // the sizing pass reads the list sizes back (once per shape change)
+            rc = xtb_impl_neighbours(c, rm);
+            c->deferred = true;
+        }
+        if (rc) return rc;
+    }
+    if (flags & XTB_STEP_HS) {
+        if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_step: no neighbour list");
+        const bool dense = !(flags & XTB_STEP_NO_DENSE);
+        if (c->comm && c->nranks > 1) {
+            if ((rc = xtb_impl_assemble(c, false))) return rc;
+            if (dense) {
+                // own panels first, on the step's stream, while nothing depends on the exchange yet; the all-gather follows
+                // in stream order and the remaining panels after it (a second stream would let them overlap: see DESIGN.md)
+                if ((rc = xtb_impl_exchange_blocks(c, XTB_XCHG_HS))) return rc;
+                if ((rc = xtb_impl_expand_dense(c, 1, c->na))) return rc;
+            }
+        } else if ((rc = xtb_impl_assemble(c, dense))) return rc;
+    }
+    if (flags & XTB_STEP_EIGEN) {
+        if (!c->have_HS) XTB_FAIL(c, XTB_ESTATE, "xtb_step: XTB_STEP_EIGEN needs the dense H_non / Sij of this step");
+        if (!io || !(io->n_electrons > 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_step: XTB_STEP_EIGEN needs io->n_electrons and io->Te_eV");
+        if ((rc = xtb_impl_eigensolve(c))) return rc;             // cuSOLVER (outside the graft) reads its info word back
+        if ((rc = xtb_impl_fermi(c, io->n_electrons, io->Te_eV))) return rc;
+        if (io->Ei) XTB_CUDA(c, cudaMemcpyAsync(io->Ei, c->own_Ei.p, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
+        if (io->fe_out) XTB_CUDA(c, cudaMemcpyAsync(io->fe_out, c->own_fe.p, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaMemcpyAsync(c->h_meta + 8, c->d_fermi.p, sizeof(double) * 4, cudaMemcpyDeviceToHost, c->stream));
+        if ((rc = xtb_impl_prepare_occupations(c))) return rc;    // the kept-state count sizes the density launches
+    } else if (io && io->fe) {
+        if (!c->d_Ha || !c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_step: occupations given but no eigenvectors on the device");
+        if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
+        XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, io->fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
+        c->d_fe = (const double*)c->own_fe.p; c->K = (long long)N;
+        c->have_eigen = true; c->have_density = false; c->have_keep = false;
+        if (io->Ei) XTB_CUDA(c, cudaMemcpyAsync(io->Ei, c->d_Ei, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
+        if ((rc = xtb_impl_prepare_occupations(c))) return rc;
+    }
+    if (flags & XTB_STEP_DENSITY) {
+        if (!c->have_neigh || !c->have_eigen) XTB_FAIL(c, XTB_ESTATE, "xtb_step: density needs a neighbour list and an armed eigen-solution");
+        if ((rc = xtb_impl_density(c))) return rc;
+        if (c->comm && c->nranks > 1) {
+            if ((rc = xtb_impl_exchange_blocks(c, XTB_XCHG_RHO))) return rc;
+            if ((rc = xtb_impl_mirror_density(c))) return rc;
+        }
+    }
+    if (flags & XTB_STEP_FORCES) {
+        if (!c->have_density) XTB_FAIL(c, XTB_ESTATE, "xtb_step: forces need the density matrices");
+        if ((rc = xtb_impl_forces(c))) return rc;
+        if (c->comm && c->nranks > 1 && (rc = xtb_impl_exchange_forces(c, c->d_F))) return rc;
+        if (io && io->F_att) XTB_CUDA(c, cudaMemcpyAsync(io->F_att, c->d_F.p, sizeof(double) * 3 * c->na, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (flags & XTB_STEP_PRESSURE) {
+        if (!c->have_density) XTB_FAIL(c, XTB_ESTATE, "xtb_step: pressure needs the density matrices");
+        if ((rc = xtb_impl_pressure(c))) return rc;
+        if (c->comm && c->nranks > 1 && (rc = xtb_impl_allreduce9(c, (double*)c->d_SC.p))) return rc;
+        if (io && io->SCforce_att) XTB_CUDA(c, cudaMemcpyAsync(io->SCforce_att, c->d_SC.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (flags & XTB_STEP_PAIR_TERMS) {
+        if ((rc = xtb_impl_pair_terms(c, io, (flags & XTB_STEP_PRESSURE) != 0))) return rc;
+    }
+    return XTB_OK;
+}
+
+int xtb_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io) {
+    if (!c) return XTB_EINVAL;
+    if (c->na <= 0 || c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_step: parameters and system first");
+    cudaSetDevice(c->device);
+    int rc;
+    if (io && (io->S || io->supce)) {
+        if (io->S) XTB_CUDA(c, cudaMemcpyAsync(c->d_S.p, io->S, sizeof(double) * 3 * c->na, cudaMemcpyHostToDevice, c->stream));
+        if (io->supce) {
+            memcpy(c->h_supce, io->supce, sizeof(double) * 9);
+            XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, io->supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
+        }
+        c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
+    }
+    // steady-state list (no read-back) on a single GPU once a sized list of this system exists
+    const bool can_steady = (flags & XTB_STEP_NEIGHBOURS) && !(c->comm && c->nranks > 1) && c->layout_parts == 1 && c->have_shape;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        const bool steady = can_steady && attempt == 0;
+        c->deferred = true;
+        rc = step_body(c, flags, io, steady);
+        c->deferred = false;
+        if (rc) { cudaStreamSynchronize(c->stream); c->t_pending = 0; return rc; }
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));            // the step's one wait
+        xtb_collect_timing(c);
+        if (steady) {
+            if (c->h_meta[2] != 0 || c->h_meta[0] > c->max_nn) {   // the list outgrew the armed sizes: size again, redo
+                c->have_shape = false;
+                continue;
+            }
+            c->max_nn_seen = c->h_meta[0];
+            c->n_blocks = c->h_meta[3];
+            c->n_pairs = c->h_meta[1] - c->na;
+        } else if ((flags & XTB_STEP_NEIGHBOURS) && !(c->comm && c->nranks > 1) && c->layout_parts == 1) {
+            // arm the steady-state form for the next step: a little slack on both bounds
+            const int bound = c->max_nn_seen + 2 < c->cap ? c->max_nn_seen + 2 : c->cap;
+            c->max_nn = bound;
+            c->blk_cap = c->n_blocks + c->n_blocks / 64 + 64;
+            c->have_shape = true;
+        }
+        break;
+    }
+    if (flags & XTB_STEP_EIGEN) {
+        const double* f = (const double*)(c->h_meta + 8);
+        if (io && io->mu) *io->mu = f[0];
+        if (io && io->E_band) *io->E_band = f[2];
+    }
+    return XTB_OK;
+}
+
+}  // extern "C"

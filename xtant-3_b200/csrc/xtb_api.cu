@@ -28,6 +28,86 @@ void xtb_free(DevBuf& b) {
     b.p = nullptr; b.bytes = 0;
 }
 
+int xtb_t0(xtb_ctx* c, int s) {
+    if (c->capturing) return XTB_OK;
+    for (int k = 0; k < 2; ++k)
+        if (!c->tev[s][k]) XTB_CUDA(c, cudaEventCreate(&c->tev[s][k]));
+    XTB_CUDA(c, cudaEventRecord(c->tev[s][0], c->stream));
+    return XTB_OK;
+}
+int xtb_t1(xtb_ctx* c, int s) {
+    if (c->capturing) return XTB_OK;
+    XTB_CUDA(c, cudaEventRecord(c->tev[s][1], c->stream));
+    c->t_pending |= 1u << s;
+    return XTB_OK;
+}
+int xtb_collect_timing(xtb_ctx* c) {
+    for (int s = 0; s < 16; ++s)
+        if (c->t_pending & (1u << s)) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, c->tev[s][0], c->tev[s][1]) == cudaSuccess) c->stage_ms[s] = ms;
+            else cudaGetLastError();
+        }
+    c->t_pending = 0;
+    return XTB_OK;
+}
+int xtb_stage_finish(xtb_ctx* c) {
+    if (c->deferred || c->capturing) return XTB_OK;
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return xtb_collect_timing(c);
+}
+
+// the `select type` arms of TB.f90:247-317,459-487
+int xtb_impl_assemble(xtb_ctx* c, bool dense) {
+    if (c->tb == XTB_TB_NRL) return xtb_impl_nrl_assemble(c, dense);
+    if (c->tb == XTB_TB_PETTIFOR) return xtb_impl_pettifor_assemble(c, dense);
+    if (c->tb == XTB_TB_DFTB) return xtb_impl_dftb_assemble(c, dense);
+    XTB_FAIL(c, XTB_EINVAL, "assembly: no TB parametrisation set");
+}
+int xtb_impl_forces(xtb_ctx* c) {
+    if (c->tb == XTB_TB_NRL) return xtb_impl_nrl_forces(c);
+    if (c->tb == XTB_TB_PETTIFOR) return xtb_impl_pettifor_forces(c);
+    if (c->tb == XTB_TB_DFTB) return xtb_impl_dftb_forces(c);
+    XTB_FAIL(c, XTB_EINVAL, "forces: no TB parametrisation set");
+}
+int xtb_impl_pressure(xtb_ctx* c) {
+    if (c->tb == XTB_TB_NRL) return xtb_impl_nrl_pressure(c);
+    if (c->tb == XTB_TB_PETTIFOR) return xtb_impl_pettifor_pressure(c);
+    if (c->tb == XTB_TB_DFTB) return xtb_impl_dftb_pressure(c);
+    XTB_FAIL(c, XTB_EINVAL, "pressure: no TB parametrisation set");
+}
+
+// pair terms of a fused step: Pettifor-type repulsive part and / or the short-range wall, whichever the context holds
+int xtb_impl_pair_terms(xtb_ctx* c, const xtb_step_io* io, bool pressure) {
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "pair terms: no neighbour list");
+    int rc;
+    const size_t fb = sizeof(double) * 3 * c->na;
+    const bool multi = c->comm && c->nranks > 1;
+    if (c->tb == XTB_TB_PETTIFOR && !c->h_pet_rep.empty()) {
+        if ((rc = xtb_impl_pettifor_rep_energy(c)) || (rc = xtb_impl_pettifor_rep_forces(c))) return rc;
+        if (multi && (rc = xtb_impl_exchange_forces(c, c->d_Frep))) return rc;
+        if (io && io->E_rep) XTB_CUDA(c, cudaMemcpyAsync(io->E_rep, c->d_Erep.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        if (io && io->F_rep) XTB_CUDA(c, cudaMemcpyAsync(io->F_rep, c->d_Frep.p, fb, cudaMemcpyDeviceToHost, c->stream));
+        if (pressure) {
+            if ((rc = xtb_impl_pettifor_rep_pressure(c))) return rc;
+            if (multi && (rc = xtb_impl_allreduce9(c, (double*)c->d_SCrep.p))) return rc;
+            if (io && io->SCforce_rep) XTB_CUDA(c, cudaMemcpyAsync(io->SCforce_rep, c->d_SCrep.p, 72, cudaMemcpyDeviceToHost, c->stream));
+        }
+    }
+    if (!c->h_wall.empty()) {
+        if ((rc = xtb_impl_wall_energy(c)) || (rc = xtb_impl_wall_forces(c))) return rc;
+        if (multi && (rc = xtb_impl_exchange_forces(c, c->d_Fwall))) return rc;
+        if (io && io->E_wall) XTB_CUDA(c, cudaMemcpyAsync(io->E_wall, c->d_Ewall.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        if (io && io->F_wall) XTB_CUDA(c, cudaMemcpyAsync(io->F_wall, c->d_Fwall.p, fb, cudaMemcpyDeviceToHost, c->stream));
+        if (pressure) {
+            if ((rc = xtb_impl_wall_pressure(c))) return rc;
+            if (multi && (rc = xtb_impl_allreduce9(c, (double*)c->d_SCwall.p))) return rc;
+            if (io && io->SCforce_wall) XTB_CUDA(c, cudaMemcpyAsync(io->SCforce_wall, c->d_SCwall.p, 72, cudaMemcpyDeviceToHost, c->stream));
+        }
+    }
+    return XTB_OK;
+}
+
 extern "C" {
 
 const char* xtb_version(void) { return "xtb_b200 0.1 (sm_100a, FP64)"; }
@@ -44,7 +124,8 @@ int xtb_create(xtb_ctx** out, int device) {
     c->device = device;
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return XTB_ECUDA; }
     c->own_stream = true;
-    cudaEventCreate(&c->ev0); cudaEventCreate(&c->ev1); cudaEventCreate(&c->ev_mid); cudaEventCreate(&c->ev_mid2);
+    if (cudaMallocHost((void**)&c->h_meta, 64) != cudaSuccess) { cudaStreamDestroy(c->stream); delete c; return XTB_ENOMEM; }
+    memset(c->h_meta, 0, 64);
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
     const char* impl = getenv("XTB_DENSITY_IMPL");
@@ -65,13 +146,17 @@ int xtb_destroy(xtb_ctx* c) {
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->comm) xtb_comm_destroy(c);
     DevBuf* all[] = {&c->d_params, &c->d_koa, &c->d_S, &c->d_nn_size, &c->d_nn_list, &c->d_nn_dist, &c->d_nn_dist_s, &c->d_rev, &c->d_own,
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
                      &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
-                     &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep};
+                     &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep,
+                     &c->d_halo_tr, &c->d_halo_cnt, &c->d_halo_slots, &c->d_halo_send, &c->d_halo_recv, &c->d_wall_params, &c->d_Ewall_at, &c->d_Ewall,
+                     &c->d_Fwall, &c->d_SCwall, &c->d_fermi, &c->d_S0, &c->d_SV, &c->d_SV0, &c->d_mdpar};
     for (DevBuf* b : all) xtb_free(*b);
-    cudaEventDestroy(c->ev0); cudaEventDestroy(c->ev1); cudaEventDestroy(c->ev_mid); cudaEventDestroy(c->ev_mid2);
+    for (int s = 0; s < 16; ++s) for (int k = 0; k < 2; ++k) if (c->tev[s][k]) cudaEventDestroy(c->tev[s][k]);
+    if (c->h_meta) cudaFreeHost(c->h_meta);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
     return XTB_OK;
@@ -97,7 +182,8 @@ static int upload_params(xtb_ctx* c, const void* p, size_t bytes) {
     if (rc) return rc;
     XTB_CUDA(c, cudaMemcpyAsync(c->d_params.p, p, bytes, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
+    c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = c->have_shape = false;
+    c->rm = 0.0;
     return XTB_OK;
 }
 
@@ -131,7 +217,8 @@ int xtb_set_params_pettifor_rep(xtb_ctx* c, int n_kinds, const xtb_pettifor_rep_
     if (rc) return rc;
     XTB_CUDA(c, cudaMemcpyAsync(c->d_rep_params.p, p, sizeof(xtb_pettifor_rep_pair) * cnt, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;   // the cut-off may have grown
+    c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = c->have_shape = false;   // the cut-off may have grown
+    c->rm = 0.0;
     return XTB_OK;
 }
 
@@ -179,9 +266,19 @@ int xtb_set_system(xtb_ctx* c, int na, const int32_t* koa, const double* S, cons
     if ((rc = xtb_reserve(c, c->d_S, sizeof(double) * 3 * na))) return rc;
     XTB_CUDA(c, cudaMemcpyAsync(c->d_koa.p, k0.data(), sizeof(int32_t) * na, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaMemcpyAsync(c->d_S.p, S, sizeof(double) * 3 * na, cudaMemcpyHostToDevice, c->stream));
+    // Scell%supce lives on the device from here on (every stage reads it there; no per-stage upload)
+    if ((rc = xtb_reserve(c, c->d_hdev, 256))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_hdev.p, supce, sizeof(double) * 9, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     memcpy(c->h_supce, supce, sizeof(double) * 9);
-    if (na != c->na) { c->cap = 0; c->a0 = 0; c->a1 = na; }
+    if (na != c->na) {
+        c->cap = 0; c->a0 = 0; c->a1 = na; c->have_shape = false; c->have_md = false;
+        if (c->comm && c->nranks > 1) {         // the owned range follows the rank
+            const int per = (na + c->nranks - 1) / c->nranks;
+            c->a0 = c->rank * per < na ? c->rank * per : na;
+            c->a1 = c->a0 + per < na ? c->a0 + per : na;
+        }
+    }
     c->na = na;
     c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
     return XTB_OK;
@@ -207,7 +304,7 @@ int xtb_set_block_layout(xtb_ctx* c, int parts) {
 }
 
 // cut-off as get_near_neighbours derives it (Atomic_tools.f90:574-586)
-static double default_cutoff(const xtb_ctx* c) {
+extern "C++" double xtb_default_cutoff(const xtb_ctx* c) {
     double rm = 0.0;
     if (c->tb == XTB_TB_NRL) { for (auto& p : c->h_nrl) rm = p.Rc > rm ? p.Rc : rm; rm *= XTB_G_AU2A; }
     else if (c->tb == XTB_TB_PETTIFOR) {
@@ -237,7 +334,7 @@ int xtb_neighbours(xtb_ctx* c, double rm, int32_t* nn_size, int32_t* nn_list, do
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
     if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_neighbours: no system set");
-    if (rm <= 0.0) rm = default_cutoff(c);
+    if (rm <= 0.0) rm = xtb_default_cutoff(c);
     if (rm <= 0.0) XTB_FAIL(c, XTB_EINVAL, "xtb_neighbours: no cut-off radius");
     int rc = xtb_impl_neighbours(c, rm);
     if (rc) return rc;
@@ -305,11 +402,7 @@ int xtb_assemble_HS(xtb_ctx* c, double* H_non, double* Sij) {
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
     if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_assemble_HS: run xtb_neighbours first");
-    int rc;
-    if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_assemble(c, true);
-    else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_assemble(c, true);
-    else if (c->tb == XTB_TB_DFTB) rc = xtb_impl_dftb_assemble(c, true);
-    else XTB_FAIL(c, XTB_EINVAL, "xtb_assemble_HS: no TB parametrisation set");
+    int rc = xtb_impl_assemble(c, true);
     if (rc) return rc;
     const size_t N = (size_t)c->na * c->n_orb;
     const size_t off = (size_t)c->a0 * c->n_orb * N, cnt = (size_t)(c->a1 - c->a0) * c->n_orb * N;
@@ -326,52 +419,61 @@ int xtb_assemble_blocks(xtb_ctx* c) {
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
     if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_assemble_blocks: run xtb_neighbours first");
-    if (c->tb == XTB_TB_NRL) return xtb_impl_nrl_assemble(c, false);
-    if (c->tb == XTB_TB_PETTIFOR) return xtb_impl_pettifor_assemble(c, false);
-    if (c->tb == XTB_TB_DFTB) return xtb_impl_dftb_assemble(c, false);
-    XTB_FAIL(c, XTB_EINVAL, "xtb_assemble_blocks: no TB parametrisation set");
+    return xtb_impl_assemble(c, false);
+}
+
+// dense column panels of atoms first..last (1-based, inclusive) from the block stores; no host copies, no wait
+extern "C++" int xtb_impl_expand_dense(xtb_ctx* c, int first, int last) {
+    if (!c->have_blocks) XTB_FAIL(c, XTB_ESTATE, "xtb_expand_dense: no block store (xtb_assemble_blocks / xtb_assemble_HS first)");
+    if (first < 1 || last > c->na || last < first - 1) XTB_FAIL(c, XTB_EINVAL, "xtb_expand_dense: bad range %d..%d", first, last);
+    const bool ortho = c->tb == XTB_TB_PETTIFOR;
+    const size_t N = (size_t)c->na * c->n_orb;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
+    if (!ortho && (rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
+    XTB_T0(c, 6);
+    if ((rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, ortho ? nullptr : (const double*)c->d_Sblk.p, (double*)c->d_H.p,
+                                    ortho ? nullptr : (double*)c->d_S2.p, false, first - 1, last))) return rc;
+    XTB_T1(c, 6);
+    c->have_HS = true;
+    return XTB_OK;
 }
 
 int xtb_expand_dense(xtb_ctx* c, int first, int last, double* H_non, double* Sij) {
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
-    if (!c->have_blocks) XTB_FAIL(c, XTB_ESTATE, "xtb_expand_dense: no block store (xtb_assemble_blocks / xtb_assemble_HS first)");
-    if (first < 1 || last > c->na || last < first - 1) XTB_FAIL(c, XTB_EINVAL, "xtb_expand_dense: bad range %d..%d", first, last);
-    const bool ortho = c->tb == XTB_TB_PETTIFOR;
-    if (Sij && ortho) XTB_FAIL(c, XTB_EINVAL, "xtb_expand_dense: orthogonal parametrisation has no overlap matrix");
-    const size_t N = (size_t)c->na * c->n_orb;
+    if (Sij && c->tb == XTB_TB_PETTIFOR) XTB_FAIL(c, XTB_EINVAL, "xtb_expand_dense: orthogonal parametrisation has no overlap matrix");
     int rc;
-    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
-    if (!ortho && (rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev0, c->stream));
-    if ((rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, ortho ? nullptr : (const double*)c->d_Sblk.p, (double*)c->d_H.p,
-                                    ortho ? nullptr : (double*)c->d_S2.p, false, first - 1, last))) return rc;
-    XTB_CUDA(c, cudaEventRecord(c->ev1, c->stream));
+    if ((rc = xtb_impl_expand_dense(c, first, last))) return rc;
+    const size_t N = (size_t)c->na * c->n_orb;
     const size_t off = (size_t)(first - 1) * c->n_orb * N, cnt = (size_t)(last - first + 1) * c->n_orb * N;
     if (H_non && cnt) XTB_CUDA(c, cudaMemcpyAsync(H_non + off, (double*)c->d_H.p + off, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
     if (Sij && cnt) XTB_CUDA(c, cudaMemcpyAsync(Sij + off, (double*)c->d_S2.p + off, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, c->ev0, c->ev1);
-    c->stage_ms[6] = ms;
-    c->have_HS = true;
-    return XTB_OK;
+    return xtb_stage_finish(c);
 }
 
 int xtb_set_eigen_device(xtb_ctx* c, const double* dHa, const double* dEi, const double* dfe) {
     if (!c) return XTB_EINVAL;
     if (!dHa || !dEi || !dfe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen_device: null pointer");
     if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_eigen_device: no system set");
+    cudaSetDevice(c->device);
     c->d_Ha = dHa; c->d_Ei = dEi; c->d_fe = dfe;
     c->have_eigvec = false;
     c->K = (long long)c->na * c->n_orb;
-    c->have_eigen = true; c->have_density = false;
+    c->have_eigen = true; c->have_density = false; c->have_keep = false;
+    return xtb_impl_prepare_occupations(c);      // kept states and weights are fixed from here (one small read-back, now)
+}
+
+int xtb_cutoff(xtb_ctx* c, double* rm) {
+    if (!c || !rm) return XTB_EINVAL;
+    if (c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_cutoff: set the TB parameters first");
+    *rm = xtb_default_cutoff(c);
     return XTB_OK;
 }
 
 int xtb_set_eigen(xtb_ctx* c, const double* Ha, const double* Ei, const double* fe) {
     if (!c) return XTB_EINVAL;
-    if (!Ha || !Ei || !fe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen: null pointer");
+    if (!Ha || !Ei) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen: null pointer");
     if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_eigen: no system set");
     cudaSetDevice(c->device);
     const size_t N = (size_t)c->na * c->n_orb;
@@ -381,8 +483,14 @@ int xtb_set_eigen(xtb_ctx* c, const double* Ha, const double* Ei, const double* 
     if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
     XTB_CUDA(c, cudaMemcpyAsync(c->own_Ha.p, Ha, sizeof(double) * N * N, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaMemcpyAsync(c->own_Ei.p, Ei, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
-    XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
+    if (fe) XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (!fe) {      // eigenvectors and eigenvalues now, occupations later (xtb_set_occupations / xtb_fermi_occupations)
+        c->d_Ha = (const double*)c->own_Ha.p; c->d_Ei = (const double*)c->own_Ei.p; c->d_fe = nullptr;
+        c->K = (long long)N;
+        c->have_eigvec = false; c->have_eigen = false; c->have_density = false; c->have_keep = false;
+        return XTB_OK;
+    }
     return xtb_set_eigen_device(c, (const double*)c->own_Ha.p, (const double*)c->own_Ei.p, (const double*)c->own_fe.p);
 }
 
@@ -420,17 +528,39 @@ int xtb_set_occupations(xtb_ctx* c, const double* fe) {
     int rc;
     if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
     XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
-    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     c->d_fe = (const double*)c->own_fe.p;       // Ha and Ei stay where they are (device eigensolve result or the caller's buffers)
     c->K = (long long)N;
-    c->have_eigen = true; c->have_density = false;
-    return XTB_OK;
+    c->have_eigen = true; c->have_density = false; c->have_keep = false;
+    return xtb_impl_prepare_occupations(c);      // synchronises (the host array is free when this returns)
 }
 
 int xtb_set_density_cutoff(xtb_ctx* c, double f_cut) {
     if (!c) return XTB_EINVAL;
     if (!(f_cut >= 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_set_density_cutoff: f_cut must be >= 0");
+    if (f_cut != c->f_cut) c->have_keep = false;
     c->f_cut = f_cut;
+    return XTB_OK;
+}
+
+// dense (N,N) copies of the block-sparse rho / rho_E of the last density pass: zero outside the neighbour pattern
+int xtb_density_get(xtb_ctx* c, double* Aij, double* Aij_x_Ei) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    if (!c->have_density) XTB_FAIL(c, XTB_ESTATE, "xtb_density_get: run xtb_density first");
+    if (!Aij && !Aij_x_Ei) return XTB_OK;
+    if (c->a0 != 0 || c->a1 != c->na) XTB_FAIL(c, XTB_EINVAL, "xtb_density: dense outputs need the full (unpartitioned) context");
+    const size_t N = (size_t)c->na * c->n_orb;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;     // reuse the dense scratch (H is consumed by now)
+    c->have_HS = false;
+    double* outs[2] = {Aij, Aij_x_Ei};
+    const double* blks[2] = {(const double*)c->d_rho.p, (const double*)c->d_rhoE.p};
+    for (int t = 0; t < 2; ++t) {
+        if (!outs[t]) continue;
+        if ((rc = xtb_dense_from_blocks(c, blks[t], nullptr, (double*)c->d_H.p, nullptr, true))) return rc;
+        XTB_CUDA(c, cudaMemcpyAsync(outs[t], c->d_H.p, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
     return XTB_OK;
 }
 
@@ -438,25 +568,10 @@ int xtb_density(xtb_ctx* c, double* Aij, double* Aij_x_Ei) {
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
     if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "xtb_density: run xtb_neighbours first");
-    if (!c->have_eigen) XTB_FAIL(c, XTB_ESTATE, "xtb_density: no eigenvectors set (xtb_set_eigen)");
+    if (!c->have_eigen) XTB_FAIL(c, XTB_ESTATE, "xtb_density: no eigenvectors / occupations set (xtb_set_eigen, xtb_set_occupations)");
     int rc = xtb_impl_density(c);
     if (rc) return rc;
-    if (Aij || Aij_x_Ei) {
-        // dense (N,N) outputs: zero outside the neighbour pattern (documented in the header)
-        if (c->a0 != 0 || c->a1 != c->na) XTB_FAIL(c, XTB_EINVAL, "xtb_density: dense outputs need the full (unpartitioned) context");
-        const size_t N = (size_t)c->na * c->n_orb;
-        if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;     // reuse the dense scratch (H is consumed by now)
-        c->have_HS = false;
-        double* outs[2] = {Aij, Aij_x_Ei};
-        const double* blks[2] = {(const double*)c->d_rho.p, (const double*)c->d_rhoE.p};
-        for (int t = 0; t < 2; ++t) {
-            if (!outs[t]) continue;
-            if ((rc = xtb_dense_from_blocks(c, blks[t], nullptr, (double*)c->d_H.p, nullptr, true))) return rc;
-            XTB_CUDA(c, cudaMemcpyAsync(outs[t], c->d_H.p, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
-            XTB_CUDA(c, cudaStreamSynchronize(c->stream));
-        }
-    }
-    return XTB_OK;
+    return xtb_density_get(c, Aij, Aij_x_Ei);
 }
 
 int xtb_density_mirror(xtb_ctx* c) {
@@ -473,11 +588,7 @@ int xtb_forces(xtb_ctx* c, double* F_att) {
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
     if (!c->have_density) XTB_FAIL(c, XTB_ESTATE, "xtb_forces: run xtb_density first");
-    int rc;
-    if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_forces(c);
-    else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_forces(c);
-    else if (c->tb == XTB_TB_DFTB) rc = xtb_impl_dftb_forces(c);
-    else XTB_FAIL(c, XTB_EINVAL, "xtb_forces: no TB parametrisation set");
+    int rc = xtb_impl_forces(c);
     if (rc) return rc;
     const size_t cnt = (size_t)(c->a1 - c->a0) * 3;
     if (F_att && cnt) {
@@ -491,11 +602,7 @@ int xtb_pressure(xtb_ctx* c, double* SCforce_att) {
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
     if (!c->have_density) XTB_FAIL(c, XTB_ESTATE, "xtb_pressure: run xtb_density first");
-    int rc;
-    if (c->tb == XTB_TB_NRL) rc = xtb_impl_nrl_pressure(c);
-    else if (c->tb == XTB_TB_PETTIFOR) rc = xtb_impl_pettifor_pressure(c);
-    else if (c->tb == XTB_TB_DFTB) rc = xtb_impl_dftb_pressure(c);
-    else XTB_FAIL(c, XTB_EINVAL, "xtb_pressure: no TB parametrisation set");
+    int rc = xtb_impl_pressure(c);
     if (rc) return rc;
     if (SCforce_att) {
         XTB_CUDA(c, cudaMemcpyAsync(SCforce_att, c->d_SC.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
@@ -597,6 +704,69 @@ int xtb_repulsive_pressure(xtb_ctx* c, double* SCforce_rep) {
     return XTB_OK;
 }
 
+// ---- short-range wall (second half) ----
+int xtb_set_params_wall(xtb_ctx* c, int n_kinds, const xtb_wall_pair* p) {
+    if (!c) return XTB_EINVAL;
+    if (c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_set_params_wall: set the TB parameters first");
+    if (n_kinds == 0 || !p) { c->h_wall.clear(); return XTB_OK; }          // "proceeding without short-range forces"
+    if (n_kinds != c->n_kinds) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_wall: n_kinds=%d (TB part has %d)", n_kinds, c->n_kinds);
+    cudaSetDevice(c->device);
+    const size_t cnt = (size_t)n_kinds * n_kinds;
+    for (size_t q = 0; q < cnt; ++q)
+        if (!(p[q].dd > 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_wall: pair %zu has smoothing width dd=%g", q, p[q].dd);
+    c->h_wall.assign(p, p + cnt);
+    int rc = xtb_reserve(c, c->d_wall_params, sizeof(xtb_wall_pair) * cnt);
+    if (rc) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_wall_params.p, p, sizeof(xtb_wall_pair) * cnt, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+static int wall_ready(xtb_ctx* c, const char* who) {
+    if (c->h_wall.empty()) XTB_FAIL(c, XTB_ESTATE, "%s: no wall parameters (xtb_set_params_wall)", who);
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "%s: run xtb_neighbours first", who);
+    return XTB_OK;
+}
+
+int xtb_wall_energy(xtb_ctx* c, double* E_wall, double* Epot) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = wall_ready(c, "xtb_wall_energy"))) return rc;
+    if ((rc = xtb_impl_wall_energy(c))) return rc;
+    if (E_wall) XTB_CUDA(c, cudaMemcpyAsync(E_wall, c->d_Ewall.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (Epot) XTB_CUDA(c, cudaMemcpyAsync(Epot, c->d_Ewall_at.p, sizeof(double) * c->na, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_wall_forces(xtb_ctx* c, double* F_wall) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = wall_ready(c, "xtb_wall_forces"))) return rc;
+    if ((rc = xtb_impl_wall_forces(c))) return rc;
+    const size_t cnt = (size_t)(c->a1 - c->a0) * 3;
+    if (F_wall && cnt) {
+        XTB_CUDA(c, cudaMemcpyAsync(F_wall + 3 * (size_t)c->a0, (double*)c->d_Fwall.p + 3 * (size_t)c->a0, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
+int xtb_wall_pressure(xtb_ctx* c, double* SCforce_wall) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = wall_ready(c, "xtb_wall_pressure"))) return rc;
+    if ((rc = xtb_impl_wall_pressure(c))) return rc;
+    if (SCforce_wall) {
+        XTB_CUDA(c, cudaMemcpyAsync(SCforce_wall, c->d_SCwall.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
 int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
     if (!c || !dptr) return XTB_EINVAL;
     const size_t N = (size_t)c->na * c->n_orb;
@@ -616,6 +786,11 @@ int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
         case XTB_BUF_SBLK: b = &c->d_Sblk; used = 8 * nb2 * (size_t)c->n_blocks; break;
         case XTB_BUF_FREP: b = &c->d_Frep; used = 24 * (size_t)c->na; break;
         case XTB_BUF_MIJ: b = &c->d_cpl_M; used = 8 * N * N; break;
+        case XTB_BUF_FWALL: b = &c->d_Fwall; used = 24 * (size_t)c->na; break;
+        case XTB_BUF_POS: b = &c->d_S; used = 24 * (size_t)c->na; break;
+        case XTB_BUF_VEL: b = &c->d_SV; used = 24 * (size_t)c->na; break;
+        case XTB_BUF_EI: if (!c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: no eigenvalues"); *dptr = (void*)c->d_Ei; if (bytes) *bytes = 8 * N; return XTB_OK;
+        case XTB_BUF_FE: if (!c->d_fe) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: no occupations"); *dptr = (void*)c->d_fe; if (bytes) *bytes = 8 * N; return XTB_OK;
         default: XTB_FAIL(c, XTB_EINVAL, "xtb_device_buffer: unknown buffer %d", which);
     }
     if (!b->p) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: buffer %d not produced yet", which);
@@ -630,7 +805,7 @@ long long xtb_counter(const xtb_ctx* c, int which) {
         case 0: return c->na;
         case 1: return c->n_orb;
         case 2: return (long long)c->na * c->n_orb;
-        case 3: return c->max_nn;
+        case 3: return c->max_nn_seen;
         case 4: return c->n_blocks;
         case 5: return c->n_pairs;
         case 6: return c->launches;
@@ -645,15 +820,16 @@ long long xtb_counter(const xtb_ctx* c, int which) {
             if (cudaMemcpy(&n, (const int*)c->d_units.p + 2 * (size_t)(c->a1 - c->a0), sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
             return n;
         }
+        case 12: return (long long)c->xchg_bytes[XTB_XCHG_HS];
+        case 13: return (long long)c->xchg_bytes[XTB_XCHG_RHO];
+        case 14: return c->halo_send_blocks;
+        case 15: return c->halo_recv_blocks;
         default: return -1;
     }
 }
 
 double xtb_stage_ms(const xtb_ctx* c, int stage) {
-    if (!c || stage < 1 || stage > 13) return -1.0;
-    if (stage == 8) return c->eigen_ms;
-    if (stage == 12) return c->coupling_spmm_ms;
-    if (stage == 13) return c->coupling_gemm_ms;
+    if (!c || stage < 1 || stage > 15) return -1.0;
     return c->stage_ms[stage];
 }
 

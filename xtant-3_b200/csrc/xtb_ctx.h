@@ -44,8 +44,12 @@ struct xtb_ctx {
     DevBuf d_koa, d_S;          // int32 [na] (0-based kinds), double [3*na]
     // neighbour list (ELL, capacity cap) for ALL atoms (positions are replicated; the list is
     // cheap and every later stage needs the lists of neighbours of owned atoms as well)
-    int cap = 0, max_nn = 0;
+    int cap = 0, max_nn = 0;    // max_nn: the neighbour count every later stage is sized with (steady-state form: a bound with slack)
+    int max_nn_seen = 0;        // largest neighbour count of the last validated list
     long long n_pairs = 0, n_blocks = 0;
+    long long blk_cap = 0;      // blocks the block stores are sized for (>= n_blocks; the steady-state form adds slack)
+    bool have_shape = false;    // cap / max_nn / blk_cap are armed for xtb_impl_neighbours_steady
+    int* h_meta = nullptr;      // pinned: {max count, real blocks, overflow flag, rowptr[na]} of the last steady-state list
     double rm = 0.0;
     DevBuf d_nn_size, d_nn_list, d_nn_dist, d_nn_dist_s, d_rev, d_own, d_rowptr, d_maxnn;
     bool have_neigh = false, have_dens = false;
@@ -63,11 +67,11 @@ struct xtb_ctx {
     bool have_eigen = false;
     bool have_eigvec = false;   // Ha, Ei produced on the device by xtb_eigensolve (occupations pending)
     DevBuf d_eig_work, d_eig_X, d_eig_T, d_eigS;   // cuSOLVER workspace, Loewdin X, scratch, eigenvalues of S
-    double eigen_ms = 0.0;
     // density
     double f_cut = 0.0;
     DevBuf d_keep, d_wf, d_wfe, d_Ct, d_nkeep;   // kept state indices, weights, tiled transposed C
     long long k_kept = 0;
+    bool have_keep = false;     // d_keep / d_wf / d_wfe / k_kept match the current fe, Ei, f_cut
     DevBuf d_rho, d_rhoE;       // block-sparse [n_blocks][n_orb^2]
     DevBuf d_ctneed;            // partitioned run: atom groups whose eigenvector tiles are re-tiled
     DevBuf d_prog;              // density kernel: per-CTA progress counters (lock-step throttle)
@@ -78,14 +82,35 @@ struct xtb_ctx {
     DevBuf d_F, d_SC, d_scratch, d_hdev, d_ppart, d_tab;
     // repulsive pair terms (pettifor_rep.cu)
     DevBuf d_Epot, d_dfpsi, d_Erep, d_Frep, d_SCrep;
+    // short-range wall (wall.cu)
+    std::vector<xtb_wall_pair> h_wall;     // empty: no wall set
+    DevBuf d_wall_params, d_Ewall_at, d_Ewall, d_Fwall, d_SCwall;
+    // Fermi occupations and velocity-Verlet state (step.cu)
+    DevBuf d_fermi;                        // {mu, N(mu), sum f E, iterations}
+    DevBuf d_S0, d_SV, d_SV0, d_mdpar;
+    bool have_md = false;
     // nonadiabatic coupling (coupling.cu): eigenvectors of the previous step, T = S Ha, G -> Mij, inverse column norms
     DevBuf d_Ha0, d_cpl_T, d_cpl_M, d_cpl_inv;
     bool have_Ha0 = false;
-    double coupling_spmm_ms = 0.0, coupling_gemm_ms = 0.0;
-    // timing
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_mid = nullptr, ev_mid2 = nullptr;
+    // multi-GPU (comm.cu): NCCL communicator bound at run time, halo transfer lists of the current neighbour list
+    void* comm = nullptr;
+    int rank = 0, nranks = 1;
+    bool rho_allgather = false;            // XTB_RHO_EXCHANGE=allgather: every rho block to every rank (comparison runs)
+    DevBuf d_halo_tr, d_halo_cnt, d_halo_slots, d_halo_send, d_halo_recv;
+    std::vector<int> halo_count;           // blocks per transfer: sends to the other ranks (ascending), then receives
+    int halo_listcap = 0;
+    long long halo_send_blocks = 0, halo_recv_blocks = 0;
+    bool have_halo = false;
+    double xchg_bytes[3] = {0, 0, 0};      // bytes received per rank by the last exchange [XTB_XCHG_HS | XTB_XCHG_RHO]
+    // timing: one CUDA event pair per stage index of xtb_stage_ms (created on first use).  A stage records its pair on the
+    // context stream; xtb_stage_finish() waits for the stream and reads the pending pairs -- except inside xtb_step
+    // (deferred), where nothing waits and the pairs are read after the step's single synchronisation, and inside a
+    // CUDA-graph capture (capturing), where no events are recorded at all.
+    cudaEvent_t tev[16][2] = {};
+    unsigned t_pending = 0;
+    bool deferred = false, capturing = false;
     int density_slotcap = 0, density_stages = 0;
-    double stage_ms[12] = {0};   // 1..7 and 9..11 (8 = eigen_ms), see xtb_stage_ms
+    double stage_ms[16] = {0};   // see xtb_stage_ms
     int sm_count = 148;
     int density_dbg = 0;        // XTB_DENSITY_DBG (timing experiments only, separate kernel instantiation): 1 no math, 2 quarter of the tile copies, 4 helper warps nap while polling, 8 no DFMA
     int density_ncw = 8;        // consumer warps of the density kernel (8 or 12); XTB_DENSITY_NCW
@@ -118,11 +143,24 @@ struct xtb_ctx {
                      cudaGetErrorString(_e), __FILE__, __LINE__);                             \
     } while (0)
 
+// blocks every block store is allocated for
+static inline size_t xtb_blocks_alloc(const xtb_ctx* c) { return (size_t)(c->blk_cap > c->n_blocks ? c->blk_cap : c->n_blocks); }
+
+#define XTB_T0(c, s) do { int _r = xtb_t0((c), (s)); if (_r) return _r; } while (0)
+#define XTB_T1(c, s) do { int _r = xtb_t1((c), (s)); if (_r) return _r; } while (0)
+
 int xtb_reserve(xtb_ctx* c, DevBuf& b, size_t bytes);   // grow-only device allocation
+int xtb_t0(xtb_ctx* c, int stage);          // record the start / end event of a stage on the context stream
+int xtb_t1(xtb_ctx* c, int stage);
+int xtb_stage_finish(xtb_ctx* c);           // synchronous mode: wait for the stream and read the pending pairs into stage_ms
+int xtb_collect_timing(xtb_ctx* c);         // read the pending pairs (the stream must be idle)
 void xtb_free(DevBuf& b);
 
 // stage implementations (one translation unit each)
 int xtb_impl_neighbours(xtb_ctx* c, double rm);
+int xtb_impl_expand_dense(xtb_ctx* c, int first, int last);   // xtb_api.cu: dense panels from the block stores, no wait
+int xtb_impl_neighbours_steady(xtb_ctx* c, double rm);   // no host round trip; validated by xtb_step after its synchronisation
+int xtb_impl_prepare_occupations(xtb_ctx* c);            // density.cu: kept states + weights from fe, Ei (at occupation-set time)
 int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense);     // dense = false: block stores only
 int xtb_impl_nrl_dens(xtb_ctx* c);          // embedded densities rho_j (needed by S2 and by the on-site force terms)
 int xtb_impl_pettifor_assemble(xtb_ctx* c, bool dense);
@@ -134,7 +172,20 @@ int xtb_impl_pettifor_pressure(xtb_ctx* c);
 int xtb_impl_pettifor_rep_energy(xtb_ctx* c);      // pettifor_rep.cu
 int xtb_impl_pettifor_rep_forces(xtb_ctx* c);
 int xtb_impl_pettifor_rep_pressure(xtb_ctx* c);
-int xtb_impl_mirror_density(xtb_ctx* c);
+int xtb_impl_mirror_density(xtb_ctx* c);             // rows of the owned atoms when the context communicates, else all rows
+int xtb_impl_wall_energy(xtb_ctx* c);                // wall.cu
+int xtb_impl_wall_forces(xtb_ctx* c);
+int xtb_impl_wall_pressure(xtb_ctx* c);
+int xtb_impl_fermi(xtb_ctx* c, double n_electrons, double Te_eV);     // step.cu
+int xtb_impl_assemble(xtb_ctx* c, bool dense);       // xtb_api.cu: dispatch on the TB branch (the `select type` arms)
+int xtb_impl_forces(xtb_ctx* c);
+int xtb_impl_pressure(xtb_ctx* c);
+int xtb_impl_pair_terms(xtb_ctx* c, const xtb_step_io* io, bool pressure);
+double xtb_default_cutoff(const xtb_ctx* c);
+int xtb_impl_comm_lists(xtb_ctx* c);                 // comm.cu
+int xtb_impl_exchange_blocks(xtb_ctx* c, int which);
+int xtb_impl_exchange_forces(xtb_ctx* c, DevBuf& F);
+int xtb_impl_allreduce9(xtb_ctx* c, double* d9);
 int xtb_impl_coupling(xtb_ctx* c, int kind_M);      // coupling.cu
 int xtb_blas_dgemm(xtb_ctx* c, bool ta, bool tb, int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* Cm, int ldc);
 int xtb_impl_eigensolve(xtb_ctx* c);        // eigen.cu: Loewdin + Dsyevd + back-transform on the device-resident H, S

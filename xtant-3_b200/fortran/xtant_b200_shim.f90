@@ -13,8 +13,8 @@
 ! each `type is (TB_H_NRL)` / `type is (TB_H_Pettifor)` arm calls the same name with the same arguments as before.
 !
 ! Status: no Fortran compiler exists in the build image nor on the GPU box (probed: gfortran, ifx, ifort,
-! nvfortran, flang absent), so this file is checked by inspection only; tests/test_abi_cpu.py drives the
-! C ABI with exactly the call sequence and array shapes used below (ctypes stands in for bind(C)).
+! nvfortran, flang absent), so this file is checked by parsing (tests/test_abi_cpu.py: interfaces vs the header, struct
+! layouts, the reference's argument lists) and its call sequence is executed by a plain-C program (tests/abi_driver.c).
 !
 ! Data contract (SURVEY.md 8b): derived types cannot cross bind(C), so each wrapper flattens
 !   Scell(NSC)%MDAtoms(:)%S, %KOA, Scell(NSC)%supce and the TB_H_*(KOA1,KOA2) scalars into contiguous buffers,
@@ -23,7 +23,7 @@
 module XTANT_B200_shim
 use, intrinsic :: iso_c_binding
 use Objects, only : Super_cell, Numerics_param, solid, Error_handling, Save_error_details, &
-                    TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor, TB_H_DFTB
+                    TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor, TB_H_DFTB, TB_Rep_DFTB, TB_Exp_wall_simple
 implicit none
 private
 public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_Aij, Construct_Aij_x_En, &
@@ -31,7 +31,10 @@ public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_
           get_Erep_s, dErdr_s, dErdr_Pressure_s, xtb_b200_init, xtb_b200_finalize, &
           Construct_Vij_DFTB, construct_TB_H_DFTB, get_dHij_drij_DFTB, Attract_TB_Forces_Press_DFTB, &
           Electron_ion_coupling_Mij, xtb_b200_set_partition, xtb_b200_assemble_blocks, xtb_b200_expand_dense, &
-          xtb_b200_density_mirror, xtb_b200_eigensolve
+          xtb_b200_density_mirror, xtb_b200_eigensolve, &
+          get_Exp_wall_s, d_Exp_wall_pot_s, d_Exp_wall_Pressure_s, xtb_b200_comm_init, xtb_b200_exchange_blocks, &
+          xtb_b200_exchange_forces, xtb_b200_allreduce_scforce, xtb_b200_step, xtb_b200_fermi, xtb_b200_md_half_step, &
+          xtb_b200_md_set_velocities, xtb_b200_md_get_state, xtb_b200_check_pending, xtb_b200_dense_density
 
 ! ---- mirror of struct xtb_nrl_pair / xtb_pettifor_pair (include/xtb_b200.h) ----
 type, bind(C) :: xtb_nrl_pair
@@ -60,8 +63,25 @@ type, bind(C) :: xtb_dftb_pair              ! type(TB_H_DFTB), Objects.f90:202-2
    type(c_ptr) :: Rr, Vr, Sr
 end type
 
+type, bind(C) :: xtb_wall_pair              ! type(TB_Exp_wall_simple), Objects.f90:458-466
+   real(c_double) :: C, r0, d0, dd
+end type xtb_wall_pair
+
+type, bind(C) :: xtb_step_io                ! struct xtb_step_io (include/xtb_b200.h); c_null_ptr = not given / keep on the device
+   type(c_ptr) :: S, supce, fe
+   real(c_double) :: n_electrons, Te_eV
+   type(c_ptr) :: Ei, fe_out, mu, E_band, F_att, SCforce_att
+   type(c_ptr) :: E_rep, F_rep, SCforce_rep
+   type(c_ptr) :: E_wall, F_wall, SCforce_wall
+end type xtb_step_io
+
 type(c_ptr), save :: ctx = c_null_ptr      ! one context per process (single caller thread, TB.f90:227-272)
-logical, save :: eigen_current = .false.   ! Ha/Ei/fe of this step already on the device
+logical, save :: eigen_current = .false.   ! Ha, Ei of this step already on the device (uploaded once, by construct_TB_H_*)
+logical, save :: density_current = .false. ! rho and rho_E of this step already contracted (ONE pass serves Construct_Aij and _x_En)
+type(c_ptr), save :: ha_loc = c_null_ptr   ! address of the Ha that was uploaded
+real(8), allocatable, save :: fe_used(:)   ! occupations the current density pass was made with
+logical, save :: xtb_b200_dense_density = .true.   ! .false.: every consumer of Aij / Aij_x_Ei is grafted -> skip the two (N,N) copies to the host
+character(512), save :: pending_error = ''  ! raised by a wrapper whose reference signature has no Err argument
 
 interface
    integer(c_int) function xtb_create(out, device) bind(C, name="xtb_create")
@@ -113,9 +133,12 @@ interface
       import; type(c_ptr), value :: c; type(c_ptr), value :: H_non, Sij
    end function
    integer(c_int) function xtb_set_eigen(c, Ha, Ei, fe) bind(C, name="xtb_set_eigen")
-      import; type(c_ptr), value :: c; real(c_double), intent(in) :: Ha(*), Ei(*), fe(*)
+      import; type(c_ptr), value :: c; real(c_double), intent(in) :: Ha(*), Ei(*); type(c_ptr), value :: fe   ! c_null_ptr: occupations follow
    end function
    integer(c_int) function xtb_density(c, Aij, Aij_x_Ei) bind(C, name="xtb_density")
+      import; type(c_ptr), value :: c; type(c_ptr), value :: Aij, Aij_x_Ei
+   end function
+   integer(c_int) function xtb_density_get(c, Aij, Aij_x_Ei) bind(C, name="xtb_density_get")
       import; type(c_ptr), value :: c; type(c_ptr), value :: Aij, Aij_x_Ei
    end function
    integer(c_int) function xtb_forces(c, F_att) bind(C, name="xtb_forces")
@@ -163,6 +186,55 @@ interface
    real(c_double) function xtb_stage_ms(c, stage) bind(C, name="xtb_stage_ms")
       import; type(c_ptr), value :: c; integer(c_int), value :: stage
    end function
+   integer(c_int) function xtb_cutoff(c, rm) bind(C, name="xtb_cutoff")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: rm
+   end function
+   integer(c_int) function xtb_set_params_wall(c, n_kinds, p) bind(C, name="xtb_set_params_wall")
+      import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds; type(c_ptr), value :: p      ! c_null_ptr with n_kinds = 0: no wall
+   end function
+   integer(c_int) function xtb_wall_energy(c, E_wall, Epot) bind(C, name="xtb_wall_energy")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: E_wall; real(c_double), intent(out) :: Epot(*)
+   end function
+   integer(c_int) function xtb_wall_forces(c, F_wall) bind(C, name="xtb_wall_forces")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: F_wall(3,*)
+   end function
+   integer(c_int) function xtb_wall_pressure(c, P_wall) bind(C, name="xtb_wall_pressure")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_wall(3,3)
+   end function
+   integer(c_int) function xtb_fermi_occupations(c, n_electrons, Te_eV, fe, mu, E_band) bind(C, name="xtb_fermi_occupations")
+      import; type(c_ptr), value :: c; real(c_double), value :: n_electrons, Te_eV; type(c_ptr), value :: fe, mu, E_band
+   end function
+   integer(c_int) function xtb_md_set_velocities(c, SV) bind(C, name="xtb_md_set_velocities")
+      import; type(c_ptr), value :: c; real(c_double), intent(in) :: SV(3,*)
+   end function
+   integer(c_int) function xtb_md_half_step(c, ind, dt_fs, mass_kg, Vsupce, force_terms) bind(C, name="xtb_md_half_step")
+      import; type(c_ptr), value :: c; integer(c_int), value :: ind; real(c_double), value :: dt_fs
+      real(c_double), intent(in) :: mass_kg(*); type(c_ptr), value :: Vsupce; integer(c_int), value :: force_terms
+   end function
+   integer(c_int) function xtb_md_get_state(c, S, SV, E_kin, mass_kg) bind(C, name="xtb_md_get_state")
+      import; type(c_ptr), value :: c; type(c_ptr), value :: S, SV, E_kin, mass_kg
+   end function
+   integer(c_int) function xtb_comm_unique_id(id) bind(C, name="xtb_comm_unique_id")
+      import; character(kind=c_char), intent(out) :: id(128)
+   end function
+   integer(c_int) function xtb_comm_init(c, id, rank, nranks) bind(C, name="xtb_comm_init")
+      import; type(c_ptr), value :: c; character(kind=c_char), intent(in) :: id(128); integer(c_int), value :: rank, nranks
+   end function
+   integer(c_int) function xtb_comm_destroy(c) bind(C, name="xtb_comm_destroy")
+      import; type(c_ptr), value :: c
+   end function
+   integer(c_int) function xtb_exchange_blocks(c, which) bind(C, name="xtb_exchange_blocks")
+      import; type(c_ptr), value :: c; integer(c_int), value :: which
+   end function
+   integer(c_int) function xtb_exchange_forces(c, F_att) bind(C, name="xtb_exchange_forces")
+      import; type(c_ptr), value :: c; type(c_ptr), value :: F_att
+   end function
+   integer(c_int) function xtb_allreduce_scforce(c, att) bind(C, name="xtb_allreduce_scforce")
+      import; type(c_ptr), value :: c; type(c_ptr), value :: att
+   end function
+   integer(c_int) function xtb_step(c, flags, io) bind(C, name="xtb_step")
+      import; type(c_ptr), value :: c; integer(c_int), value :: flags; type(xtb_step_io), intent(in) :: io
+   end function
 end interface
 
 contains
@@ -179,13 +251,44 @@ subroutine xtb_b200_init(numpar, Err)
 #endif
    rc = xtb_create(ctx, dev)
    if (rc /= 0) call Save_error_details(Err, 6, 'xtb_create failed: no CUDA device (there is no CPU fallback)')
+#ifdef MPI_USED
+   if (rc == 0 .and. numpar%MPI_param%size_of_cluster > 1) call xtb_b200_comm_init(numpar, Err)
+#endif
 end subroutine xtb_b200_init
+
+! One NCCL communicator over the MPI ranks: rank 0 draws the id, MPI_Bcast carries its 128 bytes (the only MPI call of the
+! grafted path; the reference's MPI_Allreduce of dense matrices, MPI_subroutines.f90:3965-3982, is replaced by the exchanges
+! inside the library).  xtb_comm_init gives this rank its atom range and the segmented block layout.
+subroutine xtb_b200_comm_init(numpar, Err)
+   type(Numerics_param), intent(in) :: numpar
+   type(Error_handling), intent(inout) :: Err
+   character(kind=c_char) :: id(128)
+   integer :: ierr
+   id = c_null_char
+#ifdef MPI_USED
+   if (numpar%MPI_param%process_rank == 0) call check(xtb_comm_unique_id(id), 'xtb_comm_unique_id', Err)
+   call MPI_Bcast(id, 128, MPI_CHARACTER, 0, MPI_COMM_WORLD, ierr)
+   call check(xtb_comm_init(ctx, id, int(numpar%MPI_param%process_rank,c_int), int(numpar%MPI_param%size_of_cluster,c_int)), &
+              'xtb_comm_init', Err)
+#endif
+end subroutine xtb_b200_comm_init
 
 subroutine xtb_b200_finalize()
    integer(c_int) :: rc
-   if (c_associated(ctx)) rc = xtb_destroy(ctx)
+   if (c_associated(ctx)) then
+      rc = xtb_comm_destroy(ctx)
+      rc = xtb_destroy(ctx)
+   endif
    ctx = c_null_ptr
 end subroutine xtb_b200_finalize
+
+! errors raised inside wrappers whose reference signature has no Err argument (Construct_Aij_x_En, the force wrappers):
+! call this after get_Hamilonian_and_E (TB.f90:196) to move them into the reference's error record
+subroutine xtb_b200_check_pending(Err)
+   type(Error_handling), intent(inout) :: Err
+   if (len_trim(pending_error) > 0) call Save_error_details(Err, 6, trim(pending_error))
+   pending_error = ''
+end subroutine xtb_b200_check_pending
 
 subroutine check(rc, where, Err)
    ! the reference records errors and continues (Save_error_details, Objects.f90:1309; e.g. TB_NRL.f90:410-416)
@@ -206,6 +309,7 @@ subroutine check(rc, where, Err)
       call Save_error_details(Err, 6, trim(where)//': '//trim(text))
    else
       print*, trim(where)//': '//trim(text)
+      pending_error = trim(where)//': '//trim(text)       ! collected by xtb_b200_check_pending
    endif
 end subroutine check
 
@@ -223,7 +327,7 @@ subroutine push_system(Scell, NSC)
       S(:,i) = Scell(NSC)%MDAtoms(i)%S(:)
    enddo
    call check(xtb_set_system(ctx, int(na,c_int), koa, S, Scell(NSC)%supce), 'xtb_set_system')
-   eigen_current = .false.
+   eigen_current = .false. ; density_current = .false.
 end subroutine push_system
 
 subroutine push_params_nrl(TB)
@@ -271,7 +375,7 @@ subroutine get_near_neighbours(Scell, numpar, include_vdW, dm)
    logical, intent(in), optional :: include_vdW
    real(8), intent(out), optional :: dm
    integer :: NSC
-   real(8) :: rm
+   real(8) :: rm, r(1), d(1), X
    do NSC = 1, size(Scell)
       ASSOCIATE (ARRAY => Scell(NSC)%TB_Hamil(:,:))
          select type(ARRAY)
@@ -291,13 +395,43 @@ subroutine get_near_neighbours(Scell, numpar, include_vdW, dm)
             end select
          END ASSOCIATE
       endif
-      call push_system(Scell, NSC)
-      ! rm <= 0: the library derives the cut-off as Atomic_tools.f90:574-613 does.  The vdW enlargement
-      ! (:633-640) is a host scalar: compute it as before and pass rm > 0 when it applies.
-      rm = 0.0d0
-      call check(xtb_neighbours(ctx, rm, Scell(NSC)%Near_neighbor_size, Scell(NSC)%Near_neighbor_list, &
-                                Scell(NSC)%Near_neighbor_dist, Scell(NSC)%Near_neighbor_dist_s), 'xtb_neighbours')
-      if (present(dm)) dm = rm
+      if (allocated(Scell(NSC)%TB_Expwall)) then
+         ASSOCIATE (ARRAY => Scell(NSC)%TB_Expwall(:,:))
+            select type(ARRAY)
+            type is (TB_Exp_wall_simple)
+               call push_params_wall(ARRAY)
+            end select
+         END ASSOCIATE
+      endif
+      ! cut-off exactly as Atomic_tools.f90:570-641: the TB part (attractive, raised to the Pettifor repulsive dm) comes
+      ! from the library, the arms it has no parameters for are applied here as the reference does
+      call check(xtb_cutoff(ctx, rm), 'xtb_cutoff')
+      if (allocated(Scell(NSC)%TB_Repuls)) then
+         ASSOCIATE (ARRAY => Scell(NSC)%TB_Repuls(:,:))
+            select type(ARRAY)
+            type is (TB_Rep_DFTB)                       ! :621-627
+               if (ARRAY(1,1)%ToP == 0) then
+                  r = maxval(ARRAY(:,:)%rcut)
+               else
+                  r = maxval(ARRAY(:,:)%rcut_spline)
+               endif
+               if (rm < r(1)) rm = r(1)
+            end select
+         END ASSOCIATE
+      endif
+      if (present(include_vdW) .and. allocated(Scell(NSC)%TB_Waals)) then      ! :633-640
+         r = maxval(Scell(NSC)%TB_Waals(:,:)%d0_cut)
+         d = maxval(Scell(NSC)%TB_Waals(:,:)%dd_cut)
+         X = r(1) + 10.0d0*d(1)
+         if (rm < X) rm = X
+      endif
+      if (present(dm)) then       ! :645-649: a present dm returns the radius and does NOT build the list
+         dm = rm
+      else
+         call push_system(Scell, NSC)
+         call check(xtb_neighbours(ctx, rm, Scell(NSC)%Near_neighbor_size, Scell(NSC)%Near_neighbor_list, &
+                                   Scell(NSC)%Near_neighbor_dist, Scell(NSC)%Near_neighbor_dist_s), 'xtb_neighbours')
+      endif
    enddo
 end subroutine get_near_neighbours
 
@@ -336,51 +470,94 @@ subroutine construct_TB_H_NRL(numpar, matter, TB_Hamil, M_Vij, M_SVij, M_lmn, Sc
    call check(xtb_assemble_HS(ctx, c_loc(Scell(NSC)%H_non), c_loc(Scell(NSC)%Sij)), 'xtb_assemble_HS', Err)
    Scell(NSC)%Hij = Scell(NSC)%H_non
    call solve_nonorthogonal_NRL(numpar, Scell, NSC, Err)      ! fills Ha, Ei, eigen_S, Hij_sol; then find_band_gap (:109)
-   eigen_current = .false.
+   call upload_eigen(Scell(NSC)%Ha, Scell(NSC)%Ei)      ! ONE upload of the eigenvectors per step
 end subroutine construct_TB_H_NRL
 
-! S3   TB.f90:4328 -- rho on the neighbour pattern (dense Aij is zero elsewhere; every consumer reads only the pattern)
+! S3   TB.f90:4328, 4401.  The device pass contracts rho AND rho_E together, once per step: Construct_Aij (called first,
+! TB.f90:242) supplies the occupations and triggers it; Construct_Aij_x_En (TB.f90:268) finds it done and only copies rho_E out.
+! The eigenvectors and eigenvalues were uploaded once by construct_TB_H_* (upload_eigen); a caller that passes another Ha, or
+! energies that are not this step's Ei, is served by a fresh upload and pass (correct, just not free).
+subroutine upload_eigen(Ha, Ei)
+   real(8), dimension(:,:), intent(in), target :: Ha
+   real(8), dimension(:), intent(in) :: Ei
+   call check(xtb_set_eigen(ctx, Ha, Ei, c_null_ptr), 'xtb_set_eigen')      ! occupations follow (xtb_set_occupations)
+   ha_loc = c_loc(Ha)
+   eigen_current = .true. ; density_current = .false.
+end subroutine upload_eigen
+
+subroutine ensure_density(Ha, distre, En)
+   real(8), dimension(:,:), intent(in), target :: Ha
+   real(8), dimension(:), intent(in) :: distre
+   real(8), dimension(:), intent(in), optional :: En
+   real(c_double), allocatable :: Ei_dev(:)
+   logical :: same
+   same = eigen_current .and. c_associated(c_loc(Ha), ha_loc)
+   if (same .and. present(En)) then                      ! are these the energies that were uploaded with Ha ?
+      allocate(Ei_dev(size(En)))
+      call check(xtb_get_eigenvalues(ctx, Ei_dev), 'xtb_get_eigenvalues')
+      same = all(Ei_dev == En)
+   endif
+   if (.not. same) then
+      if (present(En)) then
+         call check(xtb_set_eigen(ctx, Ha, En, c_null_ptr), 'xtb_set_eigen')
+         ha_loc = c_loc(Ha) ; eigen_current = .true.
+      else
+         if (.not. eigen_current) then
+            pending_error = 'XTANT_B200_shim: Construct_Aij before construct_TB_H_* of this step (no eigenvalues for rho_E)'
+            allocate(Ei_dev(size(distre)), source = 0.0d0)
+            call check(xtb_set_eigen(ctx, Ha, Ei_dev, c_null_ptr), 'xtb_set_eigen')
+         else
+            allocate(Ei_dev(size(distre)))
+            call check(xtb_get_eigenvalues(ctx, Ei_dev), 'xtb_get_eigenvalues')
+            call check(xtb_set_eigen(ctx, Ha, Ei_dev, c_null_ptr), 'xtb_set_eigen')
+         endif
+         ha_loc = c_loc(Ha)
+      endif
+      density_current = .false.
+   endif
+   if (density_current) then
+      if (allocated(fe_used)) then
+         if (size(fe_used) == size(distre)) then
+            if (all(fe_used == distre)) return           ! same Ha, Ei, fe: the pass of this step stands
+         endif
+      endif
+   endif
+   call check(xtb_set_occupations(ctx, distre), 'xtb_set_occupations')
+   call check(xtb_density(ctx, c_null_ptr, c_null_ptr), 'xtb_density')     ! ONE contraction: rho and rho_E
+   if (allocated(fe_used)) deallocate(fe_used)
+   allocate(fe_used, source = distre)
+   density_current = .true.
+end subroutine ensure_density
+
 subroutine Construct_Aij(numpar, Ha, distre, Aij)
    type(Numerics_param), intent(inout) :: numpar
-   real(8), dimension(:,:), intent(in) :: Ha
+   real(8), dimension(:,:), intent(in), target :: Ha
    real(8), dimension(:), intent(in) :: distre
    real(8), dimension(:,:), allocatable, intent(inout), target :: Aij
-   ! the energy levels are not an argument here; Construct_Aij_x_En supplies them.  The device density pass
-   ! produces rho and rho_E together, so the upload is deferred to whichever of the two is called with En.
    if (.not. allocated(Aij)) allocate(Aij(size(distre), size(distre)))
-   call stage_eigen(Ha, distre)
-   call check(xtb_density(ctx, c_loc(Aij), c_null_ptr), 'xtb_density(Aij)')
+   call ensure_density(Ha, distre)
+   ! dense copy only for un-grafted consumers of Scell%Aij (TB.f90:250-299); the grafted force stages read the device blocks
+   if (xtb_b200_dense_density) call check(xtb_density_get(ctx, c_loc(Aij), c_null_ptr), 'xtb_density(Aij)')
 end subroutine Construct_Aij
 
-! S3   TB.f90:4401
 subroutine Construct_Aij_x_En(numpar, Ha, distre, En, Aij, H_ssc_1_per_S)
    type(Numerics_param), intent(inout) :: numpar
-   real(8), dimension(:,:), intent(in) :: Ha
+   real(8), dimension(:,:), intent(in), target :: Ha
    real(8), dimension(:), intent(in) :: distre, En
    real(8), dimension(:,:), allocatable, intent(inout), target :: Aij
    real(8), dimension(:,:), intent(in), optional :: H_ssc_1_per_S
+   if (.not. allocated(Aij)) allocate(Aij(size(distre), size(distre)))
    if (present(H_ssc_1_per_S)) then
-      print*, 'XTANT_B200_shim: the SCC variant of Construct_Aij_x_En (TB.f90:4445-4454) is not grafted'
+      ! SCC variant fe*(Ei - HperS(i,:)) (TB.f90:4445-4454): outside the graft.  The caller gets a defined (zero) matrix and
+      ! the error goes to the reference's error record through xtb_b200_check_pending.
+      Aij = 0.0d0
+      pending_error = 'XTANT_B200_shim: the SCC variant of Construct_Aij_x_En (TB.f90:4445-4454) is not grafted'
+      print*, trim(pending_error)
       return
    endif
-   if (.not. allocated(Aij)) allocate(Aij(size(distre), size(distre)))
-   call stage_eigen(Ha, distre, En)
-   call check(xtb_density(ctx, c_null_ptr, c_loc(Aij)), 'xtb_density(Aij_x_Ei)')
+   call ensure_density(Ha, distre, En)
+   if (xtb_b200_dense_density) call check(xtb_density_get(ctx, c_null_ptr, c_loc(Aij)), 'xtb_density(Aij_x_Ei)')
 end subroutine Construct_Aij_x_En
-
-subroutine stage_eigen(Ha, distre, En)
-   real(8), dimension(:,:), intent(in) :: Ha
-   real(8), dimension(:), intent(in) :: distre
-   real(8), dimension(:), intent(in), optional :: En
-   real(8), allocatable, save :: E_last(:)
-   if (present(En)) then
-      if (allocated(E_last)) deallocate(E_last)
-      allocate(E_last, source = En)
-   endif
-   if (.not. allocated(E_last)) allocate(E_last(size(distre)), source = 0.0d0)
-   call check(xtb_set_eigen(ctx, Ha, E_last, distre), 'xtb_set_eigen')
-   eigen_current = .true.
-end subroutine stage_eigen
 
 ! S4   TB_NRL.f90:2412
 subroutine get_dHij_drij_NRL(TB_Hamil, Scell, NSC, numpar, Aij, M_Vij, M_dVij, M_SVij, M_dSVij, M_lmn, Aij_x_Ei)
@@ -431,7 +608,7 @@ subroutine construct_TB_H_Pettifor(numpar, matter, TB_Hamil, Scell, NSC, Ha, Err
    call check(xtb_assemble_HS(ctx, c_loc(Ha), c_null_ptr), 'xtb_assemble_HS', Err)
    Scell(NSC)%H_non = Ha                                                  ! TB_Pettifor.f90:1452
    call sym_diagonalize(Ha, Scell(NSC)%Ei, Error_descript, check_M=.true.) ! :1455 (outside the graft)
-   eigen_current = .false.
+   call upload_eigen(Ha, Scell(NSC)%Ei)                                    ! ONE upload of the eigenvectors per step
 end subroutine construct_TB_H_Pettifor
 
 subroutine dHij_s(TB_Hamil, atoms, Scell, NSC, numpar, Aij, M_x1, M_xrr)
@@ -600,7 +777,7 @@ subroutine construct_TB_H_DFTB(numpar, matter, TB_Hamil, M_Vij, M_SVij, M_lmn, S
    call check(xtb_assemble_HS(ctx, c_loc(Scell(NSC)%H_non), c_loc(Scell(NSC)%Sij)), 'xtb_assemble_HS', Err)
    Scell(NSC)%Hij = Scell(NSC)%H_non
    call solve_nonorthogonal(numpar, Scell, NSC, Err)      ! Ha, Ei, eigen_S, Hij_sol; then find_band_gap (:314)
-   eigen_current = .false.
+   call upload_eigen(Scell(NSC)%Ha, Scell(NSC)%Ei)      ! ONE upload of the eigenvectors per step
 end subroutine construct_TB_H_DFTB
 
 ! S4   TB_DFTB.f90:781
@@ -647,14 +824,142 @@ subroutine Electron_ion_coupling_Mij(wr, Ha, Ha0, Mij, kind_M, Sij)
    if (.not. allocated(Mij)) allocate(Mij(N,N))
    km = 0_c_int                                  ! default arm: Tully (Nonadiabatic.f90:876)
    if (present(kind_M)) km = int(kind_M, c_int)
-   if (.not. eigen_current) call check(xtb_set_eigen(ctx, Ha, wr, wr), 'xtb_set_eigen')   ! occupations are not used by the coupling
+   if (.not. eigen_current) call check(xtb_set_eigen(ctx, Ha, wr, c_null_ptr), 'xtb_set_eigen')   ! occupations are not used by the coupling
    call check(xtb_set_eigen_prev(ctx, Ha0), 'xtb_set_eigen_prev')
    call check(xtb_coupling(ctx, km, c_loc(Mij)), 'xtb_coupling')
 end subroutine Electron_ion_coupling_Mij
 
+! ---- short-range wall (Exponential_wall.f90:990,1200,1334; dispatch TB.f90:3533-3556, energy TB.f90:3983) -------------------
+subroutine push_params_wall(TB)
+   type(TB_Exp_wall_simple), dimension(:,:), intent(in) :: TB
+   type(xtb_wall_pair), allocatable, target :: p(:)
+   integer :: nk, i, j, k
+   nk = size(TB,1)
+   allocate(p(nk*nk))
+   do j = 1, nk
+      do i = 1, nk
+         k = i + nk*(j-1)
+         p(k)%C = TB(i,j)%C ; p(k)%r0 = TB(i,j)%r0 ; p(k)%d0 = TB(i,j)%d0 ; p(k)%dd = TB(i,j)%dd
+      enddo
+   enddo
+   call check(xtb_set_params_wall(ctx, int(nk,c_int), c_loc(p)), 'xtb_set_params_wall')
+end subroutine push_params_wall
+
+subroutine get_Exp_wall_s(TB_Expwall, Scell, NSC, numpar, a)
+   type(TB_Exp_wall_simple), dimension(:,:), intent(in) :: TB_Expwall
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), intent(out) :: a
+   real(c_double), allocatable :: Epot(:)
+   integer :: i, na
+   na = size(Scell(NSC)%MDAtoms)
+   allocate(Epot(na))
+   call check(xtb_wall_energy(ctx, a, Epot), 'xtb_wall_energy')
+   do i = 1, na
+      Scell(NSC)%MDAtoms(i)%Epot = Scell(NSC)%MDAtoms(i)%Epot + Epot(i)      ! Exponential_wall.f90:1058 (the half is inside)
+   enddo
+end subroutine get_Exp_wall_s
+
+subroutine d_Exp_wall_pot_s(Scell, NSC, TB_Expwall, numpar)
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(TB_Exp_wall_simple), dimension(:,:), intent(in) :: TB_Expwall
+   type(Numerics_param), intent(inout) :: numpar
+   real(c_double), allocatable :: F(:,:)
+   integer :: k, na
+   na = size(Scell(NSC)%MDatoms)
+   allocate(F(3,na))
+   call check(xtb_wall_forces(ctx, F), 'xtb_wall_forces')
+   do k = 1, na
+      Scell(NSC)%MDatoms(k)%forces%rep(:) = Scell(NSC)%MDatoms(k)%forces%rep(:) + F(:,k)    ! :1309 (added to the repulsive part)
+   enddo
+end subroutine d_Exp_wall_pot_s
+
+subroutine d_Exp_wall_Pressure_s(Scell, NSC, TB_Expwall, numpar)
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(TB_Exp_wall_simple), dimension(:,:), intent(in) :: TB_Expwall
+   type(Numerics_param), intent(in) :: numpar
+   real(c_double) :: P(3,3)
+   if (numpar%p_const) then        ! :1346
+      call check(xtb_wall_pressure(ctx, P), 'xtb_wall_pressure')
+      Scell(NSC)%SCforce%rep = Scell(NSC)%SCforce%rep + P                    ! :1381
+   endif
+end subroutine d_Exp_wall_Pressure_s
+
+! ---- Fermi occupations / velocity-Verlet halves on the device (Electron_tools.f90:2660,1913; Atomic_tools.f90:1897) ---------
+subroutine xtb_b200_fermi(Netot, Te, fe, mu)
+   real(8), intent(in) :: Netot, Te
+   real(8), dimension(:), intent(out), target :: fe
+   real(8), intent(out), target :: mu
+   call check(xtb_fermi_occupations(ctx, Netot, Te, c_loc(fe), c_loc(mu), c_null_ptr), 'xtb_fermi_occupations')
+   density_current = .false.
+end subroutine xtb_b200_fermi
+
+subroutine xtb_b200_md_set_velocities(SV)
+   real(8), dimension(:,:), intent(in) :: SV       ! (3,na) relative velocities
+   call check(xtb_md_set_velocities(ctx, SV), 'xtb_md_set_velocities')
+end subroutine xtb_b200_md_set_velocities
+
+subroutine xtb_b200_md_half_step(ind, dt, mass_kg, force_terms, Vsupce)
+   integer, intent(in) :: ind, force_terms
+   real(8), intent(in) :: dt
+   real(8), dimension(:), intent(in) :: mass_kg
+   real(8), dimension(3,3), intent(in), target, optional :: Vsupce
+   if (present(Vsupce)) then
+      call check(xtb_md_half_step(ctx, int(ind,c_int), dt, mass_kg, c_loc(Vsupce), int(force_terms,c_int)), 'xtb_md_half_step')
+   else
+      call check(xtb_md_half_step(ctx, int(ind,c_int), dt, mass_kg, c_null_ptr, int(force_terms,c_int)), 'xtb_md_half_step')
+   endif
+   if (ind == 2) then
+      eigen_current = .false. ; density_current = .false.
+   endif
+end subroutine xtb_b200_md_half_step
+
+subroutine xtb_b200_md_get_state(S, SV)
+   real(8), dimension(:,:), intent(out), target :: S, SV
+   call check(xtb_md_get_state(ctx, c_loc(S), c_loc(SV), c_null_ptr, c_null_ptr), 'xtb_md_get_state')
+end subroutine xtb_b200_md_get_state
+
+! ---- the whole step as one call (include/xtb_b200.h: xtb_step).  io is filled by the caller with c_loc of its arrays. ----------
+subroutine xtb_b200_step(flags, io, Err)
+   integer, intent(in) :: flags
+   type(xtb_step_io), intent(in) :: io
+   type(Error_handling), intent(inout) :: Err
+   call check(xtb_step(ctx, int(flags,c_int), io), 'xtb_step', Err)
+   eigen_current = .true. ; density_current = .false.
+end subroutine xtb_b200_step
+
 ! ---- MPI build (TB_NRL.f90:267-327, MPI_subroutines.f90:3965-3982) ---------------------------------
-! Each rank owns a contiguous range of atoms.  The block ranges are exchanged by the host program (one MPI_Allgatherv /
-! NCCL all-gather per block store on the device pointers of xtb_device_buffer) between these calls; see INTEGRATION.md.
+! Each rank owns a contiguous range of atoms (xtb_b200_comm_init, called from xtb_b200_init).  The exchanges between the
+! stages run INSIDE the library over NCCL: xtb_b200_exchange_blocks(1) after xtb_b200_assemble_blocks (H, S block segments,
+! all-gather), xtb_b200_exchange_blocks(2) after Construct_Aij (rho, rho_E: halo only) followed by xtb_b200_density_mirror,
+! xtb_b200_exchange_forces after the force wrapper, xtb_b200_allreduce_scforce after the pressure wrapper; see INTEGRATION.md.
+subroutine xtb_b200_exchange_blocks(which)
+   integer, intent(in) :: which      ! 1 = H and S blocks, 2 = rho and rho_E blocks
+   call check(xtb_exchange_blocks(ctx, int(which,c_int)), 'xtb_exchange_blocks')
+end subroutine xtb_b200_exchange_blocks
+
+subroutine xtb_b200_exchange_forces(Scell, NSC)
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   real(c_double), allocatable, target :: F(:,:)
+   integer :: k, na
+   na = size(Scell(NSC)%MDatoms)
+   allocate(F(3,na))
+   call check(xtb_exchange_forces(ctx, c_loc(F)), 'xtb_exchange_forces')
+   do k = 1, na
+      Scell(NSC)%MDatoms(k)%forces%att(:) = F(:,k)
+   enddo
+end subroutine xtb_b200_exchange_forces
+
+subroutine xtb_b200_allreduce_scforce(Scell, NSC)
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   call check(xtb_allreduce_scforce(ctx, c_loc(Scell(NSC)%SCforce%att)), 'xtb_allreduce_scforce')
+end subroutine xtb_b200_allreduce_scforce
+
 subroutine xtb_b200_set_partition(first, last, n_ranks)
    integer, intent(in) :: first, last
    integer, intent(in), optional :: n_ranks      ! equal-capacity segments: the exchange is then one in-place all-gather
@@ -685,7 +990,7 @@ subroutine xtb_b200_eigensolve(Ei, eigen_S, Ha)
    else
       call check(xtb_eigensolve(ctx, c_loc(Ei), c_loc(eigen_S), c_null_ptr), 'xtb_eigensolve')
    endif
-   eigen_current = .true.
+   eigen_current = .true. ; density_current = .false. ; ha_loc = c_null_ptr
 end subroutine xtb_b200_eigensolve
 
 end module XTANT_B200_shim

@@ -7,6 +7,8 @@ numeric token(s) of a line, Fortran `d` exponents) and returns the dict the C-AB
     read_Mehl_TB_Hamiltonian        Read_input_data.f90:3963-4158  ->  xtb_nrl_pair           (NRL)
     read_Pettifor_TB_Hamiltonian    Read_input_data.f90:3377-3661  ->  xtb_pettifor_pair
     read_Pettifor_TB_repulsive      Read_input_data.f90:2908-3056  ->  xtb_pettifor_rep_pair
+    read_Exponential_wall_TB        Read_input_data.f90:1920-2040,2313-2356 -> xtb_wall_pair (class line must read exactly
+                                    'Simple_wall'; e.g. the shipped 'Simple_wall:exclude' disables the wall, as in the reference)
     read_SAVE                       Dealing_with_output_files.f90:2120-2158 (writer) / Initial_configuration.f90:1594 (reader)
                                     SAVE_atoms.dat + SAVE_supercell.dat -> koa, S, supce
     read_unit_cell                  Unit_cell_equilibrium.txt + Unit_cell_atom_relative_coordinates.txt
@@ -86,6 +88,29 @@ def read_Pettifor_TB_repulsive(path):
     p["c0"] = v[8:12]
     p["a0"] = v[12:17]
     return p
+
+
+def read_Exponential_wall_TB(path):
+    """<El>_<El>_TB_wall.txt (Read_input_data.f90:1920-2040): the first list-directed token names the class.  'Simple_wall'
+    (any of the three spellings the reference accepts) -> dict(C, r0, d0, dd) read by read_Exponential_wall_TB (:2313-2356).
+    Any other token -- including the 'Simple_wall:exclude' / 'Simple_wall:exclde' the reference ships in INPUT_DATA/Aluminum,
+    /Silicon and /Diamond -- falls into `case default`: the reference prints "Unknown short-range ... class" and proceeds
+    WITHOUT the wall; this reader returns None in that case.  'General' (class TB_Short_Rep) is not built: NotImplementedError."""
+    lines = _lines(path)
+    cls = lines[0].replace(",", " ").split()[0]
+    if cls in ("General", "general", "GENERAL"):
+        raise NotImplementedError(f"{path}: class TB_Short_Rep ('General') is not part of this graft")
+    if cls not in ("Simple_wall", "SIMPLE_WALL", "simple_wall"):
+        return None
+    v = [_num(lines[k].split()[0]) for k in range(1, 5)]
+    return {"C": v[0], "r0": v[1], "d0": v[2], "dd": v[3]}
+
+
+def write_Exponential_wall_TB(path, p, enabled=True):
+    with open(path, "w") as f:
+        f.write("Simple_wall\n" if enabled else "Simple_wall:exclude\n")
+        for k, c in (("C", "C [eV]"), ("r0", "r0 [A]"), ("d0", "d0 [A]"), ("dd", "dd [A]")):
+            f.write(f"{_f(p[k])}\t\t! {c}\n")
 
 
 def read_SAVE(atoms_path, cell_path):
