@@ -327,6 +327,8 @@ def run_own(args):
             e2e["value"] = float(t.item())
         if out is not None:
             out["e2e"] = e2e
+    if rank == 0 and world == 1 and not args.no_configs:
+        out["configs"] = small_configs(torch, api, abi, wk)
     if rank == 0 and world == 1 and not args.no_cpu:
         rp = interop.buffer(ctx, abi.BUF_ROWPTR, torch.int32).cpu().numpy()
         chk = (rp, interop.buffer(ctx, abi.BUF_RHO).cpu().numpy(), interop.buffer(ctx, abi.BUF_RHOE).cpu().numpy(),
@@ -339,6 +341,52 @@ def run_own(args):
         print(json.dumps(out))
 
 
+def small_configs(torch, api, abi, wk, reps=40):
+    """BASELINE.json configs 1-4 (parity-test cases, not the headline): ms per step of the same four stages, host clock
+    around the calls a caller makes (these sizes are launch- / synchronisation-bound, so the wall time is the honest figure):
+      staged   xtb_neighbours, xtb_assemble_HS, xtb_density, xtb_forces one after the other (each waits for the device)
+      step     xtb_step, eager (one wait per step, steady-state list)
+      graph    xtb_step | XTB_STEP_GRAPH (the step's launch sequence replayed as one CUDA graph)
+    Eigenvectors: the configuration's own, from xtb_eigensolve once (outside the metric); occupations from the host."""
+    out = {}
+    for name in ("diamond64", "si216", "al500", "ac1000"):
+        wl = wk.CONFIGS[name]()
+        c = api.TBContext(0)            # own (capturable) stream
+        try:
+            c.set_workload(wl)
+            c.get_near_neighbours_device(); c.assemble_HS(to_host=False)
+            Ei = c.eigensolve()[0]
+            fe, mu = wk.occupations(Ei, wl["n_electrons"], wl["Te_eV"])
+            c.set_occupations(fe)
+
+            def staged():
+                c.get_near_neighbours_device(); c.assemble_HS(to_host=False); c.density(); c.forces_device()
+
+            def fused(flags):
+                c._ck(c.lib.xtb_step(c.h, flags, None))
+
+            res = {"na": wl["na"], "N": wl["na"] * c.n_orb, "tb": wl["tb"]}
+            for key, fn in (("staged", staged), ("step", lambda: fused(abi.STEP_ALL)), ("graph", lambda: fused(abi.STEP_ALL | abi.STEP_GRAPH))):
+                for _ in range(4):
+                    fn()
+                c.sync()
+                l0 = c.counter(6)
+                t0 = time.perf_counter()
+                for _ in range(reps):
+                    fn()
+                c.sync()
+                res[key + "_ms"] = (time.perf_counter() - t0) * 1e3 / reps
+                res[key + "_launches"] = (c.counter(6) - l0) / reps
+            res["graph_device_ms"] = c.stage_ms(0)
+            res["graphs_captured"] = c.counter(16)
+            out[name] = res
+        except Exception as ex:      # a parity-test case must not take the headline line down
+            out[name] = {"error": str(ex)[:200]}
+        finally:
+            c.close()
+    return out
+
+
 def run_e2e(torch, ctx, wl, Cm, E, fe, world, rank, a0, a1, args):
     """The step through the reference-facing C ABI with HOST buffers, copies inside the timed region, timed with the
     host clock around the calls a Fortran caller would make.  Two flavours:
@@ -349,6 +397,7 @@ def run_e2e(torch, ctx, wl, Cm, E, fe, world, rank, a0, a1, args):
       host_eigensolver       the reference's own flow kept verbatim: H_non + Sij out to host LAPACK, Ha + Ei + fe back in.
     """
     api = importlib.import_module("xtant-3_b200.api")
+    abi = importlib.import_module("xtant-3_b200._abi")
     na, N = wl["na"], wl["na"] * 9
     if world > 1:
         return run_e2e_multi(torch, ctx, wl, E, fe, world, rank, a0, a1, args)
@@ -584,6 +633,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-configs", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

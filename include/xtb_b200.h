@@ -284,6 +284,9 @@ int  xtb_allreduce_scforce(xtb_ctx*, double SCforce_att[9] /*or NULL*/);
 #define XTB_STEP_PRESSURE    32u    /* supercell force [+ all-reduce] (also of the pair terms when XTB_STEP_PAIR_TERMS) */
 #define XTB_STEP_PAIR_TERMS  64u    /* repulsive part of the Pettifor branch and / or the short-range wall, whichever is set */
 #define XTB_STEP_NO_DENSE   128u    /* with XTB_STEP_HS: block stores only */
+#define XTB_STEP_GRAPH      256u    /* single GPU, no XTB_STEP_EIGEN / new occupations: once a steady step with the same flags has
+                                       run, replay its launch sequence as ONE CUDA graph (launch-bound small systems); host
+                                       inputs / outputs travel through pinned staging; falls back to the eager path otherwise */
 #define XTB_STEP_ALL (XTB_STEP_NEIGHBOURS | XTB_STEP_HS | XTB_STEP_DENSITY | XTB_STEP_FORCES)
 typedef struct xtb_step_io {
     const double* S;          /* in  [3*na] new MDAtoms%S */
@@ -343,7 +346,8 @@ long long xtb_counter(const xtb_ctx*, int which);
  * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure,
  * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3), 8 xtb_eigensolve,
  * 9 pair-term energy + forces (repulsive / wall), 10 pair-term pressure, 11 xtb_coupling (12 / 13: its norms + S*Ha part / its DGEMM),
- * 14 H/S block exchange, 15 rho block exchange (xtb_counter 12 / 13: bytes received per rank by each) */
+ * 14 H/S block exchange, 15 rho block exchange (xtb_counter 12 / 13: bytes received per rank by each),
+ * 0 the last graph replay of xtb_step as a whole (xtb_counter 16: graphs captured so far) */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 
 #ifdef __cplusplus

@@ -22,7 +22,7 @@ STAGE_XCHG_HS, STAGE_XCHG_RHO = 14, 15
 CNT_XCHG_HS_BYTES, CNT_XCHG_RHO_BYTES, CNT_HALO_SEND, CNT_HALO_RECV = 12, 13, 14, 15
 XCHG_HS, XCHG_RHO = 1, 2
 FORCE_ATT, FORCE_REP, FORCE_WALL = 1, 2, 4
-STEP_NEIGHBOURS, STEP_HS, STEP_EIGEN, STEP_DENSITY, STEP_FORCES, STEP_PRESSURE, STEP_PAIR_TERMS, STEP_NO_DENSE = 1, 2, 4, 8, 16, 32, 64, 128
+STEP_NEIGHBOURS, STEP_HS, STEP_EIGEN, STEP_DENSITY, STEP_FORCES, STEP_PRESSURE, STEP_PAIR_TERMS, STEP_NO_DENSE, STEP_GRAPH = 1, 2, 4, 8, 16, 32, 64, 128, 256
 STEP_ALL = STEP_NEIGHBOURS | STEP_HS | STEP_DENSITY | STEP_FORCES
 UNIQUE_ID_BYTES = 128
 

@@ -318,7 +318,7 @@ class TBContext:
         self._ck(self.lib.xtb_md_get_state(self.h, _dp(S), _dp(SV), _dp(ek), _dp(m)))
         return S, SV, (None if ek is None else float(ek[0]))
 
-    def step(self, flags=_abi.STEP_ALL, S=None, supce=None, fe=None, n_electrons=0.0, Te_eV=0.0, want=()):
+    def step(self, flags=_abi.STEP_ALL, S=None, supce=None, fe=None, n_electrons=0.0, Te_eV=0.0, want=(), graph=False):
         """xtb_step: the selected stages as one call.  want: names of host outputs to fetch, any of
         Ei, fe_out, mu, E_band, F_att, SCforce_att, E_rep, F_rep, SCforce_rep, E_wall, F_wall, SCforce_wall -> dict"""
         N = self.na * self.n_orb
@@ -338,7 +338,7 @@ class TBContext:
         for k in want:
             out[k] = np.zeros(shapes[k])
             setattr(io, k, _dp(out[k]))
-        self._ck(self.lib.xtb_step(self.h, int(flags), C.byref(io)))
+        self._ck(self.lib.xtb_step(self.h, int(flags) | (_abi.STEP_GRAPH if graph else 0), C.byref(io)))
         for k in out:
             if k.startswith("SCforce"):
                 out[k] = out[k].reshape(3, 3, order="F")

@@ -247,9 +247,17 @@ int xtb_impl_comm_lists(xtb_ctx* c) {
 
 // which = XTB_XCHG_HS: all-gather of the H and S block segments; XTB_XCHG_RHO: halo exchange of rho / rho_E (or the
 // all-gather when XTB_RHO_EXCHANGE=allgather).  Everything is enqueued on the context stream; no host wait.
-int xtb_impl_exchange_blocks(xtb_ctx* c, int which) {
+int xtb_impl_exchange_blocks(xtb_ctx* c, int which, bool side_stream) {
     const int G = c->nranks, me = c->rank;
     if (G <= 1) return XTB_OK;
+    // side_stream (H/S all-gather only): the collective starts when the blocks are written (ev_comm0) and runs on
+    // comm_stream; the caller keeps working on the step's stream and waits for ev_comm1 before it reads foreign blocks
+    cudaStream_t st = c->stream;
+    if (side_stream && which == XTB_XCHG_HS && c->comm_stream && !c->capturing) {
+        XTB_CUDA(c, cudaEventRecord(c->ev_comm0, c->stream));
+        XTB_CUDA(c, cudaStreamWaitEvent(c->comm_stream, c->ev_comm0, 0));
+        st = c->comm_stream;
+    } else side_stream = false;
     Nccl& L = g_nccl;
     const size_t nb2 = (size_t)c->n_orb * c->n_orb;
     if (c->layout_parts != G) XTB_FAIL(c, XTB_ESTATE, "exchange: block layout has %d segments for %d ranks", c->layout_parts, G);
@@ -258,12 +266,17 @@ int xtb_impl_exchange_blocks(xtb_ctx* c, int which) {
     double* B = (double*)(which == XTB_XCHG_HS ? c->d_Sblk.p : c->d_rhoE.p);
     const bool two = !(which == XTB_XCHG_HS && c->tb == XTB_TB_PETTIFOR);      // the orthogonal branch has no S blocks
     const int stage = which == XTB_XCHG_HS ? 14 : 15;
-    XTB_T0(c, stage);
+    if (!side_stream) XTB_T0(c, stage);
     if (which == XTB_XCHG_HS || c->rho_allgather) {
         XTB_NCCL(c, L.gstart());
-        XTB_NCCL(c, L.allgather(A + seg * me, A, seg, NCCL_F64, (nccl_comm_t)c->comm, c->stream));
-        if (two) XTB_NCCL(c, L.allgather(B + seg * me, B, seg, NCCL_F64, (nccl_comm_t)c->comm, c->stream));
+        XTB_NCCL(c, L.allgather(A + seg * me, A, seg, NCCL_F64, (nccl_comm_t)c->comm, st));
+        if (two) XTB_NCCL(c, L.allgather(B + seg * me, B, seg, NCCL_F64, (nccl_comm_t)c->comm, st));
         XTB_NCCL(c, L.gend());
+        if (side_stream) {
+            XTB_CUDA(c, cudaEventRecord(c->ev_comm1, st));
+            c->xchg_bytes[which] = (double)seg * 8 * (two ? 2 : 1) * (G - 1);
+            return XTB_OK;          // timed by the caller (stage 14 brackets the overlapped region)
+        }
         c->xchg_bytes[which] = (double)seg * 8 * (two ? 2 : 1) * (G - 1);      // received per rank
     } else {
         if (!c->have_halo) XTB_FAIL(c, XTB_ESTATE, "exchange: no halo transfer lists (run the neighbour stage after xtb_comm_init)");
@@ -346,6 +359,11 @@ int xtb_comm_init(xtb_ctx* c, const void* unique_id, int rank, int nranks) {
     nccl_comm_t comm = nullptr;
     XTB_NCCL(c, g_nccl.init(&comm, nranks, id, rank));
     c->comm = comm; c->rank = rank; c->nranks = nranks;
+    if (!c->comm_stream) {
+        XTB_CUDA(c, cudaStreamCreateWithFlags(&c->comm_stream, cudaStreamNonBlocking));
+        XTB_CUDA(c, cudaEventCreateWithFlags(&c->ev_comm0, cudaEventDisableTiming));
+        XTB_CUDA(c, cudaEventCreateWithFlags(&c->ev_comm1, cudaEventDisableTiming));
+    }
     if (const char* ev = getenv("XTB_RHO_EXCHANGE")) c->rho_allgather = strcmp(ev, "allgather") == 0;
     // block stores in one equal-capacity segment per rank; the owned range follows the rank
     c->layout_parts = nranks;
@@ -359,8 +377,10 @@ int xtb_comm_destroy(xtb_ctx* c) {
     if (c->comm) {
         cudaSetDevice(c->device);
         cudaStreamSynchronize(c->stream);
+        if (c->comm_stream) cudaStreamSynchronize(c->comm_stream);
         g_nccl.destroy((nccl_comm_t)c->comm);
         c->comm = nullptr;
+        if (c->comm_stream) { cudaStreamDestroy(c->comm_stream); cudaEventDestroy(c->ev_comm0); cudaEventDestroy(c->ev_comm1); c->comm_stream = nullptr; }
     }
     c->rank = 0; c->nranks = 1; c->have_halo = false;
     return XTB_OK;

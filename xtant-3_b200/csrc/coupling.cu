@@ -12,6 +12,7 @@
 //        and one in-place tile-pair kernel that applies the norms, antisymmetrises and mirrors (HBM-bound, N^2 doubles
 //        read and written once).  Normalisation is applied to G(i,j) instead of to the vectors (same value up to rounding).
 #include "xtb_ctx.h"
+#include <cstdlib>
 
 namespace {
 
@@ -38,8 +39,11 @@ __global__ void __launch_bounds__(CT) col_invnorm_kernel(long long N, const doub
 // T(rows of atom j, n) = sum_{q} blk(j,q)^T C(rows of atom i_q, n);  blk(j,q)(mu,nu) = S(i_q mu, j nu)  (block store of S2).
 // CTA = (atom j, 2*ST consecutive states); the atom's blocks are staged once in shared memory (stride 82: 16-byte aligned
 // rows), each thread carries two states: 18 accumulators, 81 broadcast LDS per 162 DFMA.
+// XT = true: the eigenvector rows come from X[atom][state][NO] (xtb_rows_by_state), so the 32 lanes of a load cover 32
+// consecutive states of one atom = 32 * 72 contiguous bytes (8 sectors per load instruction) instead of 32 columns of Ha
+// (32 sectors per load instruction, each fetched for 8 of its 32 bytes at a time): the kernel was bound by those wavefronts.
 constexpr int ST = 128;
-template <int NO>
+template <int NO, bool XT>
 __global__ void __launch_bounds__(ST) spmm_blocks_kernel(int na, long long N, long long K, int cap, const int* __restrict__ nn_size,
                                                         const int* __restrict__ nn_list, const int* __restrict__ rowptr,
                                                         const double* __restrict__ Sblk, const double* __restrict__ Cm,
@@ -59,8 +63,8 @@ __global__ void __launch_bounds__(ST) spmm_blocks_kernel(int na, long long N, lo
     for (int nu = 0; nu < NO; ++nu) { a0[nu] = 0.0; a1[nu] = 0.0; }
     for (int q = 0; q <= m; ++q) {
         const int i = q == 0 ? j : nn_list[(size_t)j * cap + q - 1];
-        const double* c0 = Cm + (size_t)i * NO + (size_t)N * n0;
-        const double* c1 = Cm + (size_t)i * NO + (size_t)N * (ok1 ? n1 : n0);
+        const double* c0 = XT ? Cm + ((size_t)i * K + n0) * NO : Cm + (size_t)i * NO + (size_t)N * n0;
+        const double* c1 = XT ? Cm + ((size_t)i * K + (ok1 ? n1 : n0)) * NO : Cm + (size_t)i * NO + (size_t)N * (ok1 ? n1 : n0);
         double x0[NO], x1[NO];
 #pragma unroll
         for (int mu = 0; mu < NO; ++mu) { x0[mu] = __ldg(c0 + mu); x1[mu] = __ldg(c1 + mu); }
@@ -142,18 +146,22 @@ int xtb_impl_coupling(xtb_ctx* c, int kind_M) {
     if (!ortho) {
         const dim3 grid((unsigned)c->na, (unsigned)((K + 2 * ST - 1) / (2 * ST)));
         const size_t smem = sizeof(double) * (size_t)(c->max_nn + 1) * 82;
-        if (c->n_orb == 9) {
-            XTB_CUDA(c, cudaFuncSetAttribute(spmm_blocks_kernel<9>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            spmm_blocks_kernel<9><<<grid, ST, smem, c->stream>>>(c->na, N, K, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                                  (const int*)c->d_rowptr.p, (const double*)c->d_Sblk.p, c->d_Ha, (double*)c->d_cpl_T.p);
-        } else if (c->n_orb == 4) {
-            XTB_CUDA(c, cudaFuncSetAttribute(spmm_blocks_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            spmm_blocks_kernel<4><<<grid, ST, smem, c->stream>>>(c->na, N, K, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                                  (const int*)c->d_rowptr.p, (const double*)c->d_Sblk.p, c->d_Ha, (double*)c->d_cpl_T.p);
-        } else {
-            spmm_blocks_kernel<1><<<grid, ST, smem, c->stream>>>(c->na, N, K, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
-                                                                  (const int*)c->d_rowptr.p, (const double*)c->d_Sblk.p, c->d_Ha, (double*)c->d_cpl_T.p);
+        // eigenvector rows by state (one HBM-bound transposition, 2 * 8 * N * K bytes) unless XTB_COUPLING_XT=0
+        const char* ev = getenv("XTB_COUPLING_XT");
+        const bool xt = ev ? atoi(ev) != 0 : true;
+        const double* Cm = c->d_Ha;
+        if (xt) {
+            if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)N * K + 1024))) return rc;      // shares the density stage's scratch
+            if ((rc = xtb_rows_by_state(c, c->d_Ha, K, (double*)c->d_Ct.p))) return rc;
+            Cm = (const double*)c->d_Ct.p;
         }
+#define XTB_SPMM(NO, XT) { XTB_CUDA(c, cudaFuncSetAttribute(spmm_blocks_kernel<NO, XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        spmm_blocks_kernel<NO, XT><<<grid, ST, smem, c->stream>>>(c->na, N, K, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, \
+                                                                  (const int*)c->d_rowptr.p, (const double*)c->d_Sblk.p, Cm, (double*)c->d_cpl_T.p); }
+        if (c->n_orb == 9) { if (xt) XTB_SPMM(9, true) else XTB_SPMM(9, false) }
+        else if (c->n_orb == 4) { if (xt) XTB_SPMM(4, true) else XTB_SPMM(4, false) }
+        else { if (xt) XTB_SPMM(1, true) else XTB_SPMM(1, false) }
+#undef XTB_SPMM
         XTB_LAUNCH_CHECK(c);
         Tm = (const double*)c->d_cpl_T.p;
     }

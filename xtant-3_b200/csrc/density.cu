@@ -568,7 +568,7 @@ __global__ void __launch_bounds__(256) rows_by_state_kernel(int na, long long N,
     __shared__ long long colbase[32];
     const int k0 = blockIdx.x * 32, atom0 = blockIdx.y * DR_AT;
     const int nat = min(DR_AT, na - atom0), ns = min(32, nkeep - k0);
-    if (threadIdx.x < 32) colbase[threadIdx.x] = threadIdx.x < ns ? (long long)keep[k0 + threadIdx.x] * N + (long long)atom0 * NO : -1;
+    if (threadIdx.x < 32) colbase[threadIdx.x] = threadIdx.x < ns ? (long long)(keep ? keep[k0 + threadIdx.x] : k0 + threadIdx.x) * N + (long long)atom0 * NO : -1;
     __syncthreads();
     const int w = nat * NO;
     for (int idx = threadIdx.x; idx < 32 * w; idx += 256) {
@@ -732,6 +732,7 @@ int run_density(xtb_ctx* c) {
             ct_tile_kernel<NO><<<grid, CT_THREADS, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, need, c->d_Ha, (double*)c->d_Ct.p);
             XTB_LAUNCH_CHECK(c);
         }
+        XTB_T0(c, 7);             // the contraction kernel alone (stage 7)
         if (c->density_impl == 2) {
             // ---- two column atoms per CTA (density_pair.cuh) ----
             const int gcap = 2 * c->max_nn + 4;
@@ -887,6 +888,19 @@ int run_density(xtb_ctx* c) {
 }
 
 }  // namespace
+
+// X[atom][state][n_orb rows] of ALL states of Ha (coupling.cu reads the eigenvector rows of an atom through it: a warp's load
+// then covers 32 consecutive states of one atom = contiguous memory, where Ha itself has them a whole column apart)
+int xtb_rows_by_state(xtb_ctx* c, const double* Ha, long long K, double* X) {
+    const int na = c->na;
+    const long long N = (long long)na * c->n_orb;
+    dim3 g((unsigned)((K + 31) / 32), (na + DR_AT - 1) / DR_AT);
+    if (c->n_orb == 9) rows_by_state_kernel<9><<<g, 256, 0, c->stream>>>(na, N, (int)K, nullptr, Ha, X);
+    else if (c->n_orb == 4) rows_by_state_kernel<4><<<g, 256, 0, c->stream>>>(na, N, (int)K, nullptr, Ha, X);
+    else rows_by_state_kernel<1><<<g, 256, 0, c->stream>>>(na, N, (int)K, nullptr, Ha, X);
+    XTB_LAUNCH_CHECK(c);
+    return XTB_OK;
+}
 
 int xtb_impl_density(xtb_ctx* c) {
     if (c->n_orb == 9) return run_density<9>(c);

@@ -11,6 +11,8 @@
 #include <cmath>
 #include <cstring>
 #include <cfloat>
+#include <cstdlib>
+#include <cstdint>
 
 namespace {
 
@@ -283,10 +285,22 @@ static int step_body(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool ste
         if (c->comm && c->nranks > 1) {
             if ((rc = xtb_impl_assemble(c, false))) return rc;
             if (dense) {
-                // own panels first, on the step's stream, while nothing depends on the exchange yet; the all-gather follows
-                // in stream order and the remaining panels after it (a second stream would let them overlap: see DESIGN.md)
-                if ((rc = xtb_impl_exchange_blocks(c, XTB_XCHG_HS))) return rc;
-                if ((rc = xtb_impl_expand_dense(c, 1, c->na))) return rc;
+                // the all-gather of the block segments runs on the side stream while this stream expands the panels of the
+                // own atoms (they need only own blocks); the foreign panels follow once the exchange has landed
+                const bool overlap = getenv("XTB_HS_OVERLAP") ? atoi(getenv("XTB_HS_OVERLAP")) != 0 : true;
+                XTB_T0(c, 14);
+                if ((rc = xtb_impl_exchange_blocks(c, XTB_XCHG_HS, overlap))) return rc;
+                if (overlap) {          // stage 6 then brackets all three expansions, the wait for the exchange included
+                    XTB_T0(c, 6);
+                    if (c->a1 > c->a0 && (rc = xtb_impl_expand_dense(c, c->a0 + 1, c->a1, false))) return rc;
+                    XTB_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_comm1, 0));
+                    XTB_T1(c, 14);
+                    if (c->a0 > 0 && (rc = xtb_impl_expand_dense(c, 1, c->a0, false))) return rc;
+                    if (c->a1 < c->na && (rc = xtb_impl_expand_dense(c, c->a1 + 1, c->na, false))) return rc;
+                    XTB_T1(c, 6);
+                } else {
+                    if ((rc = xtb_impl_expand_dense(c, 1, c->na))) return rc;
+                }
             }
         } else if ((rc = xtb_impl_assemble(c, dense))) return rc;
     }
@@ -334,11 +348,137 @@ static int step_body(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool ste
     return XTB_OK;
 }
 
+// ---- CUDA-graph replay of a steady step (XTB_STEP_GRAPH) ---------------------------------------------------------------------
+// Small systems are launch-bound (diamond64: ~20 launches of a few microseconds each).  Once a steady-state step with the same
+// flags has run eagerly (every buffer sized), the same launch sequence is captured once and replayed with one cudaGraphLaunch.
+// Inputs / outputs travel through a pinned staging block (a captured copy node must not touch pageable memory).  The key below
+// holds everything a captured launch bakes in; any change re-captures.  Overflow of the armed list sizes is detected after the
+// replay exactly as for the eager steady step, and the step is then re-run through the sizing path.
+struct GraphKey {
+    unsigned flags, iomask;
+    int na, cap, max_nn, tb, n_orb, a0, a1, n_kinds;
+    long long blk_cap, k_kept, K;
+    const void *Ha, *Ei, *fe;
+    cudaStream_t stream;
+    double rm, f_cut;
+    bool rep, wall;
+};
+static unsigned io_mask(const xtb_step_io* io) {
+    if (!io) return 0;
+    unsigned m = 0;
+    const void* p[] = {io->S, io->F_att, io->SCforce_att, io->E_rep, io->F_rep, io->SCforce_rep, io->E_wall, io->F_wall, io->SCforce_wall};
+    for (int k = 0; k < 9; ++k) if (p[k]) m |= 1u << k;
+    return m;
+}
+static GraphKey make_key(const xtb_ctx* c, unsigned flags, const xtb_step_io* io) {
+    GraphKey k;
+    memset(&k, 0, sizeof k);
+    k.flags = flags; k.iomask = io_mask(io);
+    k.na = c->na; k.cap = c->cap; k.max_nn = c->max_nn; k.tb = c->tb; k.n_orb = c->n_orb; k.a0 = c->a0; k.a1 = c->a1; k.n_kinds = c->n_kinds;
+    k.blk_cap = c->blk_cap; k.k_kept = c->k_kept; k.K = c->K;
+    k.Ha = c->d_Ha; k.Ei = c->d_Ei; k.fe = c->d_fe; k.stream = c->stream; k.rm = c->rm; k.f_cut = c->f_cut;
+    k.rep = !c->h_pet_rep.empty(); k.wall = !c->h_wall.empty();
+    return k;
+}
+static void graph_drop(xtb_ctx* c) {
+    if (c->graph_exec) { cudaGraphExecDestroy((cudaGraphExec_t)c->graph_exec); c->graph_exec = nullptr; }
+    c->graph_key.clear();
+}
+// staging layout (doubles): S[3 na] | F_att[3 na] | F_rep[3 na] | F_wall[3 na] | SC_att[9] SC_rep[9] SC_wall[9] | E_rep E_wall
+static int graph_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool* overflow) {
+    const size_t na3 = 3 * (size_t)c->na, need = sizeof(double) * (4 * na3 + 32);
+    *overflow = false;
+    if (c->h_stage_bytes < need) {
+        if (c->h_stage) cudaFreeHost(c->h_stage);
+        c->h_stage = nullptr; c->h_stage_bytes = 0;
+        XTB_CUDA(c, cudaMallocHost((void**)&c->h_stage, need));
+        c->h_stage_bytes = need;
+        graph_drop(c);
+    }
+    double* st = c->h_stage;
+    xtb_step_io g;
+    memset(&g, 0, sizeof g);
+    if (io) {
+        if (io->S) g.S = st;
+        if (io->F_att) g.F_att = st + na3;
+        if (io->F_rep) g.F_rep = st + 2 * na3;
+        if (io->F_wall) g.F_wall = st + 3 * na3;
+        if (io->SCforce_att) g.SCforce_att = st + 4 * na3;
+        if (io->SCforce_rep) g.SCforce_rep = st + 4 * na3 + 9;
+        if (io->SCforce_wall) g.SCforce_wall = st + 4 * na3 + 18;
+        if (io->E_rep) g.E_rep = st + 4 * na3 + 27;
+        if (io->E_wall) g.E_wall = st + 4 * na3 + 28;
+    }
+    const GraphKey key = make_key(c, flags, io);
+    if (!c->graph_exec || c->graph_key.size() != sizeof key || memcmp(c->graph_key.data(), &key, sizeof key) != 0) {
+        graph_drop(c);
+        cudaGraph_t graph = nullptr;
+        XTB_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+        c->capturing = true; c->deferred = true;
+        int rc = XTB_OK;
+        if (g.S && cudaMemcpyAsync(c->d_S.p, g.S, sizeof(double) * na3, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = XTB_ECUDA;
+        if (!rc) { c->have_neigh = false; rc = step_body(c, flags & ~XTB_STEP_GRAPH, &g, true); }
+        c->capturing = false; c->deferred = false;
+        const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+        if (rc || e != cudaSuccess || !graph) {
+            if (graph) cudaGraphDestroy(graph);
+            cudaGetLastError();
+            if (rc) return rc;
+            XTB_FAIL(c, XTB_ECUDA, "xtb_step: graph capture failed: %s", cudaGetErrorString(e));
+        }
+        cudaGraphExec_t exec = nullptr;
+        const cudaError_t e2 = cudaGraphInstantiate(&exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e2 != cudaSuccess) { cudaGetLastError(); XTB_FAIL(c, XTB_ECUDA, "xtb_step: cudaGraphInstantiate failed: %s", cudaGetErrorString(e2)); }
+        c->graph_exec = exec;
+        c->graph_key.assign((const char*)&key, (const char*)&key + sizeof key);
+        c->graph_captures++;
+    }
+    if (io && io->S) memcpy(st, io->S, sizeof(double) * na3);
+    XTB_T0(c, 0);
+    XTB_CUDA(c, cudaGraphLaunch((cudaGraphExec_t)c->graph_exec, c->stream));
+    XTB_T1(c, 0);
+    c->launches++;
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    xtb_collect_timing(c);
+    c->have_neigh = c->have_blocks = true;
+    c->have_HS = (flags & XTB_STEP_HS) && !(flags & XTB_STEP_NO_DENSE);
+    c->have_dens = false;
+    if (flags & XTB_STEP_DENSITY) c->have_density = true;
+    if (c->h_meta[2] != 0 || c->h_meta[0] > c->max_nn) { *overflow = true; graph_drop(c); return XTB_OK; }
+    c->max_nn_seen = c->h_meta[0]; c->n_blocks = c->h_meta[3]; c->n_pairs = c->h_meta[1] - c->na;
+    if (io) {
+        if (io->F_att) memcpy(io->F_att, g.F_att, sizeof(double) * na3);
+        if (io->F_rep) memcpy(io->F_rep, g.F_rep, sizeof(double) * na3);
+        if (io->F_wall) memcpy(io->F_wall, g.F_wall, sizeof(double) * na3);
+        if (io->SCforce_att) memcpy(io->SCforce_att, g.SCforce_att, 72);
+        if (io->SCforce_rep) memcpy(io->SCforce_rep, g.SCforce_rep, 72);
+        if (io->SCforce_wall) memcpy(io->SCforce_wall, g.SCforce_wall, 72);
+        if (io->E_rep) *io->E_rep = *g.E_rep;
+        if (io->E_wall) *io->E_wall = *g.E_wall;
+    }
+    return XTB_OK;
+}
+
 int xtb_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io) {
     if (!c) return XTB_EINVAL;
     if (c->na <= 0 || c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_step: parameters and system first");
     cudaSetDevice(c->device);
     int rc;
+    // steady-state list (no read-back) on a single GPU once a sized list of this system exists
+    const bool single = !(c->comm && c->nranks > 1) && c->layout_parts == 1;
+    bool can_steady = (flags & XTB_STEP_NEIGHBOURS) && single && c->have_shape;
+    // graph replay: a steady step with these flags has already run eagerly; nothing in this call needs the host mid-way
+    if ((flags & XTB_STEP_GRAPH) && can_steady && c->steady_flags_done == (flags & ~XTB_STEP_GRAPH) && !(flags & XTB_STEP_EIGEN) &&
+        !(io && (io->fe || io->supce || io->Ei || io->fe_out)) && (!(flags & XTB_STEP_DENSITY) || (c->have_eigen && c->have_keep)) &&
+        (uintptr_t)c->stream > 2 /* the legacy / per-thread default streams cannot be captured */) {
+        bool overflow = false;
+        if ((rc = graph_step(c, flags, io, &overflow))) return rc;
+        if (!overflow) return XTB_OK;
+        c->have_shape = false; can_steady = false;          // fall through to the sizing path below
+        if (io && io->S) c->have_neigh = false;
+    }
+    flags &= ~XTB_STEP_GRAPH;
     if (io && (io->S || io->supce)) {
         if (io->S) XTB_CUDA(c, cudaMemcpyAsync(c->d_S.p, io->S, sizeof(double) * 3 * c->na, cudaMemcpyHostToDevice, c->stream));
         if (io->supce) {
@@ -347,30 +487,29 @@ int xtb_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io) {
         }
         c->have_neigh = c->have_HS = c->have_blocks = c->have_density = c->have_dens = false;
     }
-    // steady-state list (no read-back) on a single GPU once a sized list of this system exists
-    const bool can_steady = (flags & XTB_STEP_NEIGHBOURS) && !(c->comm && c->nranks > 1) && c->layout_parts == 1 && c->have_shape;
     for (int attempt = 0; attempt < 2; ++attempt) {
         const bool steady = can_steady && attempt == 0;
         c->deferred = true;
         rc = step_body(c, flags, io, steady);
         c->deferred = false;
-        if (rc) { cudaStreamSynchronize(c->stream); c->t_pending = 0; return rc; }
+        if (rc) { cudaStreamSynchronize(c->stream); c->t_pending = 0; c->t_started = 0; return rc; }
         XTB_CUDA(c, cudaStreamSynchronize(c->stream));            // the step's one wait
         xtb_collect_timing(c);
         if (steady) {
             if (c->h_meta[2] != 0 || c->h_meta[0] > c->max_nn) {   // the list outgrew the armed sizes: size again, redo
-                c->have_shape = false;
+                c->have_shape = false; c->steady_flags_done = 0;
                 continue;
             }
             c->max_nn_seen = c->h_meta[0];
             c->n_blocks = c->h_meta[3];
             c->n_pairs = c->h_meta[1] - c->na;
-        } else if ((flags & XTB_STEP_NEIGHBOURS) && !(c->comm && c->nranks > 1) && c->layout_parts == 1) {
+            c->steady_flags_done = flags;                          // every buffer of this flag set is sized: a graph may follow
+        } else if ((flags & XTB_STEP_NEIGHBOURS) && single) {
             // arm the steady-state form for the next step: a little slack on both bounds
             const int bound = c->max_nn_seen + 2 < c->cap ? c->max_nn_seen + 2 : c->cap;
             c->max_nn = bound;
             c->blk_cap = c->n_blocks + c->n_blocks / 64 + 64;
-            c->have_shape = true;
+            c->have_shape = true; c->steady_flags_done = 0;
         }
         break;
     }

@@ -33,10 +33,11 @@ int xtb_t0(xtb_ctx* c, int s) {
     for (int k = 0; k < 2; ++k)
         if (!c->tev[s][k]) XTB_CUDA(c, cudaEventCreate(&c->tev[s][k]));
     XTB_CUDA(c, cudaEventRecord(c->tev[s][0], c->stream));
+    c->t_started |= 1u << s;
     return XTB_OK;
 }
 int xtb_t1(xtb_ctx* c, int s) {
-    if (c->capturing) return XTB_OK;
+    if (c->capturing || !(c->t_started & (1u << s))) return XTB_OK;       // an end without a start is not a measurement
     XTB_CUDA(c, cudaEventRecord(c->tev[s][1], c->stream));
     c->t_pending |= 1u << s;
     return XTB_OK;
@@ -48,7 +49,7 @@ int xtb_collect_timing(xtb_ctx* c) {
             if (cudaEventElapsedTime(&ms, c->tev[s][0], c->tev[s][1]) == cudaSuccess) c->stage_ms[s] = ms;
             else cudaGetLastError();
         }
-    c->t_pending = 0;
+    c->t_pending = 0; c->t_started = 0;
     return XTB_OK;
 }
 int xtb_stage_finish(xtb_ctx* c) {
@@ -157,6 +158,8 @@ int xtb_destroy(xtb_ctx* c) {
     for (DevBuf* b : all) xtb_free(*b);
     for (int s = 0; s < 16; ++s) for (int k = 0; k < 2; ++k) if (c->tev[s][k]) cudaEventDestroy(c->tev[s][k]);
     if (c->h_meta) cudaFreeHost(c->h_meta);
+    if (c->graph_exec) cudaGraphExecDestroy((cudaGraphExec_t)c->graph_exec);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
     return XTB_OK;
@@ -423,7 +426,7 @@ int xtb_assemble_blocks(xtb_ctx* c) {
 }
 
 // dense column panels of atoms first..last (1-based, inclusive) from the block stores; no host copies, no wait
-extern "C++" int xtb_impl_expand_dense(xtb_ctx* c, int first, int last) {
+extern "C++" int xtb_impl_expand_dense(xtb_ctx* c, int first, int last, bool timed) {
     if (!c->have_blocks) XTB_FAIL(c, XTB_ESTATE, "xtb_expand_dense: no block store (xtb_assemble_blocks / xtb_assemble_HS first)");
     if (first < 1 || last > c->na || last < first - 1) XTB_FAIL(c, XTB_EINVAL, "xtb_expand_dense: bad range %d..%d", first, last);
     const bool ortho = c->tb == XTB_TB_PETTIFOR;
@@ -431,10 +434,10 @@ extern "C++" int xtb_impl_expand_dense(xtb_ctx* c, int first, int last) {
     int rc;
     if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
     if (!ortho && (rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
-    XTB_T0(c, 6);
+    if (timed) XTB_T0(c, 6);
     if ((rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, ortho ? nullptr : (const double*)c->d_Sblk.p, (double*)c->d_H.p,
                                     ortho ? nullptr : (double*)c->d_S2.p, false, first - 1, last))) return rc;
-    XTB_T1(c, 6);
+    if (timed) XTB_T1(c, 6);
     c->have_HS = true;
     return XTB_OK;
 }
@@ -820,6 +823,7 @@ long long xtb_counter(const xtb_ctx* c, int which) {
             if (cudaMemcpy(&n, (const int*)c->d_units.p + 2 * (size_t)(c->a1 - c->a0), sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
             return n;
         }
+        case 16: return c->graph_captures;
         case 12: return (long long)c->xchg_bytes[XTB_XCHG_HS];
         case 13: return (long long)c->xchg_bytes[XTB_XCHG_RHO];
         case 14: return c->halo_send_blocks;
@@ -829,7 +833,7 @@ long long xtb_counter(const xtb_ctx* c, int which) {
 }
 
 double xtb_stage_ms(const xtb_ctx* c, int stage) {
-    if (!c || stage < 1 || stage > 15) return -1.0;
+    if (!c || stage < 0 || stage > 15) return -1.0;
     return c->stage_ms[stage];
 }
 

@@ -50,6 +50,12 @@ struct xtb_ctx {
     long long blk_cap = 0;      // blocks the block stores are sized for (>= n_blocks; the steady-state form adds slack)
     bool have_shape = false;    // cap / max_nn / blk_cap are armed for xtb_impl_neighbours_steady
     int* h_meta = nullptr;      // pinned: {max count, real blocks, overflow flag, rowptr[na]} of the last steady-state list
+    // CUDA-graph replay of a steady step (step.cu)
+    void* graph_exec = nullptr;
+    std::vector<char> graph_key;
+    double* h_stage = nullptr; size_t h_stage_bytes = 0;     // pinned staging of the step's host inputs / outputs
+    unsigned steady_flags_done = 0;                           // flag set of the last eager steady step (its buffers are sized)
+    long long graph_captures = 0;
     double rm = 0.0;
     DevBuf d_nn_size, d_nn_list, d_nn_dist, d_nn_dist_s, d_rev, d_own, d_rowptr, d_maxnn;
     bool have_neigh = false, have_dens = false;
@@ -95,6 +101,8 @@ struct xtb_ctx {
     // multi-GPU (comm.cu): NCCL communicator bound at run time, halo transfer lists of the current neighbour list
     void* comm = nullptr;
     int rank = 0, nranks = 1;
+    cudaStream_t comm_stream = nullptr;    // the H/S block all-gather runs here while the step's stream expands the own panels
+    cudaEvent_t ev_comm0 = nullptr, ev_comm1 = nullptr;
     bool rho_allgather = false;            // XTB_RHO_EXCHANGE=allgather: every rho block to every rank (comparison runs)
     DevBuf d_halo_tr, d_halo_cnt, d_halo_slots, d_halo_send, d_halo_recv;
     std::vector<int> halo_count;           // blocks per transfer: sends to the other ranks (ascending), then receives
@@ -107,7 +115,7 @@ struct xtb_ctx {
     // (deferred), where nothing waits and the pairs are read after the step's single synchronisation, and inside a
     // CUDA-graph capture (capturing), where no events are recorded at all.
     cudaEvent_t tev[16][2] = {};
-    unsigned t_pending = 0;
+    unsigned t_pending = 0, t_started = 0;
     bool deferred = false, capturing = false;
     int density_slotcap = 0, density_stages = 0;
     double stage_ms[16] = {0};   // see xtb_stage_ms
@@ -129,9 +137,11 @@ struct xtb_ctx {
 #define XTB_CUDA(ctx, call)                                                                   \
     do {                                                                                      \
         cudaError_t _e = (call);                                                              \
-        if (_e != cudaSuccess)                                                                \
+        if (_e != cudaSuccess) {                                                              \
+            cudaGetLastError();     /* not sticky: do not let it surface at the next launch check */ \
             XTB_FAIL(ctx, XTB_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e),  \
                      __FILE__, __LINE__);                                                     \
+        }                                                                                     \
     } while (0)
 
 #define XTB_LAUNCH_CHECK(ctx)                                                                 \
@@ -158,7 +168,7 @@ void xtb_free(DevBuf& b);
 
 // stage implementations (one translation unit each)
 int xtb_impl_neighbours(xtb_ctx* c, double rm);
-int xtb_impl_expand_dense(xtb_ctx* c, int first, int last);   // xtb_api.cu: dense panels from the block stores, no wait
+int xtb_impl_expand_dense(xtb_ctx* c, int first, int last, bool timed = true);   // xtb_api.cu: dense panels from the block stores, no wait
 int xtb_impl_neighbours_steady(xtb_ctx* c, double rm);   // no host round trip; validated by xtb_step after its synchronisation
 int xtb_impl_prepare_occupations(xtb_ctx* c);            // density.cu: kept states + weights from fe, Ei (at occupation-set time)
 int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense);     // dense = false: block stores only
@@ -183,10 +193,11 @@ int xtb_impl_pressure(xtb_ctx* c);
 int xtb_impl_pair_terms(xtb_ctx* c, const xtb_step_io* io, bool pressure);
 double xtb_default_cutoff(const xtb_ctx* c);
 int xtb_impl_comm_lists(xtb_ctx* c);                 // comm.cu
-int xtb_impl_exchange_blocks(xtb_ctx* c, int which);
+int xtb_impl_exchange_blocks(xtb_ctx* c, int which, bool side_stream = false);   // side_stream: enqueue on comm_stream, fenced by ev_comm0 / ev_comm1
 int xtb_impl_exchange_forces(xtb_ctx* c, DevBuf& F);
 int xtb_impl_allreduce9(xtb_ctx* c, double* d9);
 int xtb_impl_coupling(xtb_ctx* c, int kind_M);      // coupling.cu
+int xtb_rows_by_state(xtb_ctx* c, const double* Ha, long long K, double* X);      // density.cu
 int xtb_blas_dgemm(xtb_ctx* c, bool ta, bool tb, int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* Cm, int ldc);
 int xtb_impl_eigensolve(xtb_ctx* c);        // eigen.cu: Loewdin + Dsyevd + back-transform on the device-resident H, S
 int xtb_impl_dftb_assemble(xtb_ctx* c, bool dense);
