@@ -347,7 +347,9 @@ long long xtb_counter(const xtb_ctx*, int which);
  * 6 dense-panel kernel alone (inside 2), 7 density contraction kernel alone (inside 3), 8 xtb_eigensolve,
  * 9 pair-term energy + forces (repulsive / wall), 10 pair-term pressure, 11 xtb_coupling (12 / 13: its norms + S*Ha part / its DGEMM),
  * 14 H/S block exchange, 15 rho block exchange (xtb_counter 12 / 13: bytes received per rank by each),
- * 0 the last graph replay of xtb_step as a whole (xtb_counter 16: graphs captured so far) */
+ * 0 the last graph replay of xtb_step as a whole (xtb_counter 16: graphs captured so far),
+ * 16 the eigenvector re-tiling kernel alone (inside 3).  Stage 6 is the dense H_non / Sij update: the matrices stay resident and
+ * only the blocks of the previous and of the new pattern are touched (XTB_DENSE_FULL=1: every element, every step) */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 
 #ifdef __cplusplus

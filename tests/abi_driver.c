@@ -159,11 +159,13 @@ int main(int argc, char** argv) {
     /* reference result in a child process (CUDA must not be initialised before fork) */
     int pfd[2];
     if (pipe(pfd) != 0) return 4;
+    fflush(stdout);
     pid_t pid = fork();
     if (pid == 0) {
         close(pfd[0]);
         int r = single(&q, Fref, Pref);
         if (r == 0) { if (write(pfd[1], Fref, sizeof(double) * 3 * q.na) < 0 || write(pfd[1], Pref, sizeof Pref) < 0) r = 5; }
+        fflush(stdout);
         _exit(r);
     }
     close(pfd[1]);
@@ -177,10 +179,11 @@ int main(int argc, char** argv) {
     char idfile[256];
     snprintf(idfile, sizeof idfile, "/tmp/xtb_nccl_id_%d", (int)getpid());
     unlink(idfile);
+    fflush(stdout);
     pid_t kids[16];
     for (int r = 0; r < nranks && r < 16; ++r) {
         kids[r] = fork();
-        if (kids[r] == 0) _exit(rank_main(&q, r, nranks, idfile, Fref, Pref));
+        if (kids[r] == 0) { int rr = rank_main(&q, r, nranks, idfile, Fref, Pref); fflush(stdout); _exit(rr); }
     }
     int bad = 0;
     for (int r = 0; r < nranks && r < 16; ++r) { waitpid(kids[r], &st, 0); bad |= !WIFEXITED(st) || WEXITSTATUS(st) != 0; }

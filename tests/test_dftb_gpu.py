@@ -104,8 +104,15 @@ def test_s_basis(wk, orc, api):
     g = orc.gather_blocks(o["nb"], 1, A)
     mask = (np.arange(o["nb"].cap + 1)[None, :] <= o["nb"].size[:, None])
     assert np.abs(g[mask] - o["rho"][mask]).max() <= 1e-11 * np.abs(o["rho"][mask]).max()
+    # forces of the s basis AS WRITTEN in the reference (get_forces_DFTB / d_Hamilton_one_DFTB hand d_KS_s the value vectors,
+    # TB_DFTB.f90:1047-1048): one number for every atom and direction; the oracle's verbatim loop nest gives the same
+    Fv = orc.dftb_forces_verbatim(wl, o["nb"], o["lmn"], o["rad"], orc.density_dense(o["Ha"], o["fe"]), orc.density_dense(o["Ha"], o["fe"], o["Ei"]))
+    F = c.forces()
+    assert np.abs(Fv).max() > 1e-3 and np.abs(Fv - Fv[0, 0]).max() <= 1e-9 * np.abs(Fv).max()
+    assert np.abs(F - Fv).max() <= 1e-10 * np.abs(Fv).max(), (F[0], Fv[0])
+    assert np.array_equal(F, np.full_like(F, F[0, 0]))
     with pytest.raises(api.XtbError):
-        c.forces()                              # refused, see dftb.cu header
+        c.pressure()                            # the supercell-force arm of the s basis stays refused (TB_DFTB.f90:1393-1394)
     c.close()
 
 

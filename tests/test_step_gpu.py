@@ -21,12 +21,13 @@ def _staged(api, wl, o, S=None, supce=None):
         w["supce"] = supce
     c.set_workload(w)
     c.get_near_neighbours_device()
-    c.assemble_HS(to_host=False)
+    HS = c.assemble_HS(to_host=True)
     c.set_eigen(o["Ha"], o["Ei"], o["fe"])
     c.density()
     F = c.forces(); P = c.pressure()
     n = c.counter(3)
     c.close()
+    _staged.HS = HS             # dense H_non, Sij of this configuration (fresh context: written from scratch)
     return F, P, n
 
 
@@ -52,17 +53,38 @@ def test_step_equals_staged_calls(name, wk, orc, api):
     rng = np.random.default_rng(2)
     S2 = np.mod(wl["S"] + rng.normal(0, 2e-3, size=wl["S"].shape), 1.0)
     F2, P2, n2 = _staged(api, wl, o, S=S2)
+    HS2 = _staged.HS
     out = c.step(flags, S=S2, want=("F_att", "SCforce_att"))
     assert np.array_equal(out["F_att"], F2) and np.array_equal(out["SCforce_att"], P2)
     assert c.counter(3) == n2
+
+    def dense_equal(ref):
+        """the RESIDENT dense matrices (only the blocks of the old and of the new pattern were touched by the step) hold
+        exactly what a fresh context writes from scratch"""
+        import ctypes as C
+        N = wl["na"] * c.n_orb
+        H = np.full((N, N), np.nan, order="F"); S = np.full((N, N), np.nan, order="F") if ref[1] is not None else None
+        for which, arr in ((abi.BUF_H, H), (abi.BUF_S, S)):
+            if arr is None:
+                continue
+            ptr, nbytes = c.device_buffer(which)
+            assert nbytes == 8 * N * N
+            torch = importlib.import_module("torch")
+            interop = importlib.import_module("xtant-3_b200.interop")
+            arr[...] = interop.buffer(c, which).cpu().numpy().reshape(N, N, order="F")
+        return np.array_equal(H, ref[0]) and (S is None or np.array_equal(S, ref[1]))
+
+    assert dense_equal(HS2)
     # a compressed cell: more neighbours than the armed bound -> the step is re-run through the sizing path, transparently
     h3 = wl["supce"] * 0.9
     F3, P3, n3 = _staged(api, wl, o, S=S2, supce=h3)
     if name == "si64":
         assert n3 > n2 + 2                                      # (au32: every atom already lists all the others)
+    HS3 = _staged.HS
     out = c.step(flags, supce=h3, want=("F_att", "SCforce_att"))
     assert np.array_equal(out["F_att"], F3) and np.array_equal(out["SCforce_att"], P3)
     assert c.counter(3) == n3
+    assert dense_equal(HS3)                                     # also after the list changed its stride (capacity grew)
     out = c.step(flags, want=("F_att",))                        # and steady again
     assert np.array_equal(out["F_att"], F3)
     assert launches_steady > 0

@@ -729,8 +729,10 @@ int run_density(xtb_ctx* c) {
                 XTB_LAUNCH_CHECK(c);
                 need = (const int*)c->d_ctneed.p;
             }
+            XTB_T0(c, 16);        // the re-tiling kernel alone (HBM-bound: reads the kept columns of Ha, writes Ct)
             ct_tile_kernel<NO><<<grid, CT_THREADS, 0, c->stream>>>(na, N, nkeep, (const int*)c->d_keep.p, need, c->d_Ha, (double*)c->d_Ct.p);
             XTB_LAUNCH_CHECK(c);
+            XTB_T1(c, 16);
         }
         XTB_T0(c, 7);             // the contraction kernel alone (stage 7)
         if (c->density_impl == 2) {

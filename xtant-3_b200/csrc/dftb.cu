@@ -248,13 +248,10 @@ __global__ void dftb_sum9_kernel(int n, const double* __restrict__ partial, doub
 template <int NO>
 int assemble(xtb_ctx* c, bool dense) {
     const int na = c->na;
-    const size_t N = (size_t)na * NO;
     int rc;
     if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * NO * NO * xtb_blocks_alloc(c)))) return rc;
     if ((rc = xtb_reserve(c, c->d_Sblk, sizeof(double) * NO * NO * xtb_blocks_alloc(c)))) return rc;
     if (dense) {
-        if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
-        if ((rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
     }
     XTB_T0(c, 2);
     const int nown = c->a1 - c->a0;
@@ -266,13 +263,78 @@ int assemble(xtb_ctx* c, bool dense) {
         XTB_LAUNCH_CHECK(c);
     }
     XTB_T0(c, 6);      // dense panel kernel alone
-    if (dense && (rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, (const double*)c->d_Sblk.p, (double*)c->d_H.p, (double*)c->d_S2.p, false))) return rc;
+    if (dense && (rc = xtb_dense_update(c, c->a0, c->a1))) return rc;
     XTB_T1(c, 6);
     XTB_T1(c, 2);
     if ((rc = xtb_stage_finish(c))) return rc;
     c->have_blocks = true;
     c->have_HS = dense;
     return XTB_OK;
+}
+
+// ---- s basis, AS WRITTEN in the reference -----------------------------------------------------------------------------------
+// d_Hamilton_one_DFTB hands d_KS_s the VALUE vectors (vec_M_Vij12, vec_M_SVij12) where the other bases get the derivative
+// vectors (TB_DFTB.f90:1047-1048, and again for y and z), so dH_alpha(i,j) = V_ss(r_ij), dS_alpha(i,j) = S_ss(r_ij) for EVERY
+// atom k and direction alpha, whether k belongs to the pair or not.  get_forces_DFTB / Attract_TB_forces_DFTB (:829-972) then
+// give every atom, in every direction, the same number  sum_i sum_{j in NN(i), listed both ways} [V rho(i,j) - S rho_E(i,j)].
+// It is not a derivative; it is reproduced because the parity target is the reference's own output.  One warp per atom,
+// fixed-order reductions; needs the blocks of all atoms (unpartitioned context).
+__global__ void __launch_bounds__(128) dftb_s_aswritten_partial_kernel(int na, int cap, int n_kinds, const int* __restrict__ koa,
+                                                                       const int* __restrict__ nn_size, const int* __restrict__ nn_list,
+                                                                       const int* __restrict__ rev, const double* __restrict__ nn_dist,
+                                                                       const int* __restrict__ rowptr, const DftbDev* __restrict__ TB,
+                                                                       const double* __restrict__ tab, const double* __restrict__ rho,
+                                                                       const double* __restrict__ rhoE, double* __restrict__ part) {
+    const int i2 = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i2 >= na) return;
+    const int m = nn_size[i2];
+    double acc = 0.0;
+    for (int q = lane; q < m; q += 32) {
+        const size_t e = (size_t)i2 * cap + q;
+        const int j1 = nn_list[e], rv = rev[e];
+        if (rv < 0) continue;                                   // the block of the ordered pair was never written (:868)
+        const bool small = i2 < j1;
+        const int ia = small ? i2 : j1, ja = small ? j1 : i2;   // block rows = smaller index i, cols = larger j
+        const size_t e_ji = small ? (size_t)j1 * cap + rv : e;  // list entry of j pointing at i: M(j,i,:) = vec_12 (:1029-1032)
+        double V[10], dV[10], S[10];
+        entry_radial<1>(TB, tab, n_kinds, koa, ja, ia, nn_dist[4 * e_ji + 3], 0, V, dV);
+        entry_radial<1>(TB, tab, n_kinds, koa, ja, ia, nn_dist[4 * e_ji + 3], 1, S, dV);
+        const size_t b = (size_t)rowptr[i2] + 1 + q;
+        acc += V[0] * rho[b] - S[0] * rhoE[b];
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    if (lane == 0) part[i2] = acc;
+}
+__global__ void __launch_bounds__(256) dftb_s_aswritten_fill_kernel(int na, const double* __restrict__ part, double* __restrict__ F) {
+    __shared__ double buf[256];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < na; i += 256) s += part[i];
+    buf[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = 128; off > 0; off >>= 1) {
+        if (threadIdx.x < off) buf[threadIdx.x] += buf[threadIdx.x + off];
+        __syncthreads();
+    }
+    const double tot = buf[0];
+    for (int i = threadIdx.x; i < 3 * na; i += 256) F[i] = tot;
+}
+
+static int forces_s_aswritten(xtb_ctx* c) {
+    if (c->a0 != 0 || c->a1 != c->na) XTB_FAIL(c, XTB_EINVAL, "DFTB s basis: the reference's force expression sums over all atoms; unpartitioned context only");
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_F, sizeof(double) * 3 * (size_t)(c->na + c->nranks)))) return rc;
+    if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)c->na))) return rc;
+    XTB_T0(c, 4);
+    dftb_s_aswritten_partial_kernel<<<(c->na + 3) / 4, 128, 0, c->stream>>>(c->na, c->cap, c->n_kinds, DFTB_ARGS_LIST, (const int*)c->d_rev.p,
+                                                                          (const double*)c->d_nn_dist.p, (const int*)c->d_rowptr.p,
+                                                                          (const DftbDev*)c->d_params.p, (const double*)c->d_dftb_tab.p,
+                                                                          (const double*)c->d_rho.p, (const double*)c->d_rhoE.p, (double*)c->d_ppart.p);
+    XTB_LAUNCH_CHECK(c);
+    dftb_s_aswritten_fill_kernel<<<1, 256, 0, c->stream>>>(c->na, (const double*)c->d_ppart.p, (double*)c->d_F.p);
+    XTB_LAUNCH_CHECK(c);
+    XTB_T1(c, 4);
+    return xtb_stage_finish(c);
 }
 
 template <int NO>
@@ -335,7 +397,7 @@ int xtb_impl_dftb_assemble(xtb_ctx* c, bool dense) {
 int xtb_impl_dftb_forces(xtb_ctx* c) {
     if (c->n_orb == 9) return forces<9>(c);
     if (c->n_orb == 4) return forces<4>(c);
-    XTB_FAIL(c, XTB_EINVAL, "DFTB s basis: the reference's force formula is not a derivative (TB_DFTB.f90:1047-1048); not provided");
+    return forces_s_aswritten(c);       // the reference's expression as written (not a derivative, TB_DFTB.f90:1047-1048)
 }
 
 int xtb_impl_dftb_pressure(xtb_ctx* c) {

@@ -209,6 +209,112 @@ int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, do
     return XTB_OK;
 }
 
+// ---- dense H_non / Sij kept RESIDENT and updated in place -----------------------------------------------------------------
+// The dense matrices are 2 * 8 * N^2 bytes (21.7 GB at the north-star size) of which 2 % are non-zero (the blocks of the
+// neighbour pattern).  Writing every element every step costs 3.8 ms at the HBM roofline -- on every rank of a multi-GPU run
+// with a replicated eigensolve.  Instead the matrices stay in HBM from step to step together with the pattern they were
+// written with; a step clears the blocks of the PREVIOUS pattern and writes the blocks of the new one (2 * 2 * 8 * n_orb^2
+// bytes per block: 0.84 GB), so every element still has exactly the value a full write would give it.  A full clear happens
+// only when the buffers are new, were used as scratch (xtb_density_get), or the system changed shape.  XTB_DENSE_FULL=1
+// restores the full column-panel write of every step (dense_panel_kernel; the HBM-roofline measurement of bench.py).
+template <int NO>
+__global__ void __launch_bounds__(256) dense_zero_prev_kernel(int f0, int pcap, const int* __restrict__ psize, const int* __restrict__ plist,
+                                                             size_t N, double* __restrict__ A, double* __restrict__ B) {
+    const int j = f0 + blockIdx.x;
+    const int m = psize[j];
+    if (m < 0) return;                                   // no previous content in this column panel
+    const int tot = (m + 1) * NO * NO;
+    for (int idx = threadIdx.x; idx < tot; idx += 256) {
+        const int q = idx / (NO * NO), e = idx - q * (NO * NO);
+        const int nu = e / NO, mu = e - nu * NO;
+        const int i = q == 0 ? j : plist[(size_t)j * pcap + q - 1];
+        const size_t d = ((size_t)i * NO + mu) + N * ((size_t)j * NO + nu);
+        A[d] = 0.0;
+        if (B) B[d] = 0.0;
+    }
+}
+template <int NO>
+__global__ void __launch_bounds__(256) dense_scatter_kernel(int f0, int cap, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
+                                                           const int* __restrict__ rowptr, const double* __restrict__ Ablk,
+                                                           const double* __restrict__ Bblk, size_t N, double* __restrict__ A, double* __restrict__ B,
+                                                           int pcap, int* __restrict__ psize, int* __restrict__ plist) {
+    const int j = f0 + blockIdx.x;
+    const int m = nn_size[j];
+    const int tot = (m + 1) * NO * NO;
+    const size_t b0 = (size_t)rowptr[j] * (NO * NO);
+    for (int idx = threadIdx.x; idx < tot; idx += 256) {
+        const int q = idx / (NO * NO), e = idx - q * (NO * NO);
+        const int nu = e / NO, mu = e - nu * NO;
+        const int i = q == 0 ? j : nn_list[(size_t)j * cap + q - 1];
+        const size_t d = ((size_t)i * NO + mu) + N * ((size_t)j * NO + nu);
+        A[d] = Ablk[b0 + idx];
+        if (B) B[d] = Bblk[b0 + idx];
+    }
+    // remember the pattern this panel now holds
+    for (int q = threadIdx.x; q < m; q += 256) plist[(size_t)j * pcap + q] = nn_list[(size_t)j * cap + q];
+    if (threadIdx.x == 0) psize[j] = m;
+}
+__global__ void fill_int_kernel(int n, int v, int* __restrict__ p) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// dense column panels of atoms [f0, f1) (0-based) of H_non (and Sij unless orthogonal) from the block stores
+int xtb_dense_update(xtb_ctx* c, int f0, int f1) {
+    const bool ortho = c->tb == XTB_TB_PETTIFOR;
+    const int na = c->na, NO = c->n_orb;
+    const size_t N = (size_t)na * NO;
+    int rc;
+    const void* pH = c->d_H.p; const void* pS = c->d_S2.p;
+    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
+    if (!ortho && (rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
+    if (f1 <= f0) return XTB_OK;
+    double* A = (double*)c->d_H.p; double* B = ortho ? nullptr : (double*)c->d_S2.p;
+    const double* Ablk = (const double*)c->d_Hblk.p; const double* Bblk = ortho ? nullptr : (const double*)c->d_Sblk.p;
+    const char* ev = getenv("XTB_DENSE_FULL");
+    if (ev && atoi(ev) != 0) {       // every element of the panels, every step
+        c->dense_state = 0;
+        return xtb_dense_from_blocks(c, Ablk, Bblk, A, B, false, f0, f1);
+    }
+    // (xtb_reserve zero-fills what it allocates: a new buffer is clean and empty)
+    const bool fresh = c->d_H.p != pH || (!ortho && c->d_S2.p != pS);
+    const bool shape = c->dense_na != na || c->dense_norb != NO || c->dense_ortho != (int)ortho;
+    if ((rc = xtb_reserve(c, c->d_prev_size, sizeof(int) * na))) return rc;
+    if (fresh || shape || c->dense_state == 0) {
+        if (!(fresh && c->d_H.p != pH && (ortho || c->d_S2.p != pS))) {          // not both brand new: clear what is there
+            XTB_CUDA(c, cudaMemsetAsync(A, 0, sizeof(double) * N * N, c->stream));
+            if (B) XTB_CUDA(c, cudaMemsetAsync(B, 0, sizeof(double) * N * N, c->stream));
+        }
+        fill_int_kernel<<<(na + 255) / 256, 256, 0, c->stream>>>(na, -1, (int*)c->d_prev_size.p);
+        XTB_LAUNCH_CHECK(c);
+        c->dense_pcap = 0;
+        c->dense_na = na; c->dense_norb = NO; c->dense_ortho = (int)ortho; c->dense_state = 1;
+    }
+    if (c->dense_pcap != c->cap) {
+        if (c->dense_pcap > 0) {      // the list stride changed: clear every panel with the old layout, then adopt the new one
+#define XTB_ZERO(NOV) dense_zero_prev_kernel<NOV><<<na, 256, 0, c->stream>>>(0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B)
+            if (NO == 9) XTB_ZERO(9); else if (NO == 4) XTB_ZERO(4); else XTB_ZERO(1);
+            XTB_LAUNCH_CHECK(c);
+            fill_int_kernel<<<(na + 255) / 256, 256, 0, c->stream>>>(na, -1, (int*)c->d_prev_size.p);
+            XTB_LAUNCH_CHECK(c);
+        }
+        if ((rc = xtb_reserve(c, c->d_prev_list, sizeof(int) * (size_t)na * c->cap))) return rc;
+        c->dense_pcap = c->cap;
+    }
+    const int n = f1 - f0;
+    if (NO == 9) dense_zero_prev_kernel<9><<<n, 256, 0, c->stream>>>(f0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B);
+    else if (NO == 4) dense_zero_prev_kernel<4><<<n, 256, 0, c->stream>>>(f0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B);
+    else dense_zero_prev_kernel<1><<<n, 256, 0, c->stream>>>(f0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B);
+    XTB_LAUNCH_CHECK(c);
+#define XTB_SCATTER(NOV) dense_scatter_kernel<NOV><<<n, 256, 0, c->stream>>>(f0, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, \
+        (const int*)c->d_rowptr.p, Ablk, Bblk, N, A, B, c->dense_pcap, (int*)c->d_prev_size.p, (int*)c->d_prev_list.p)
+    if (NO == 9) XTB_SCATTER(9); else if (NO == 4) XTB_SCATTER(4); else XTB_SCATTER(1);
+#undef XTB_SCATTER
+#undef XTB_ZERO
+    XTB_LAUNCH_CHECK(c);
+    return XTB_OK;
+}
+
 // compact per-entry tables for the drop-in outputs of xtb_radial (never used by the device hot path)
 __global__ void nrl_tables_kernel(int na, int cap, int n_kinds, const int* __restrict__ koa, const int* __restrict__ nn_size,
                                   const int* __restrict__ nn_list, const int* __restrict__ rev, const double* __restrict__ nn_dist,
@@ -261,14 +367,9 @@ int xtb_impl_nrl_dens(xtb_ctx* c) {
 
 int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense) {
     const int na = c->na;
-    const size_t N = (size_t)na * 9;
     int rc;
     if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 81 * xtb_blocks_alloc(c)))) return rc;
     if ((rc = xtb_reserve(c, c->d_Sblk, sizeof(double) * 81 * xtb_blocks_alloc(c)))) return rc;
-    if (dense) {
-        if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
-        if ((rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
-    }
     XTB_T0(c, 2);
     if ((rc = xtb_impl_nrl_dens(c))) return rc;
     const int nown = c->a1 - c->a0;
@@ -283,7 +384,7 @@ int xtb_impl_nrl_assemble(xtb_ctx* c, bool dense) {
         XTB_LAUNCH_CHECK(c);
     }
     XTB_T0(c, 6);      // dense panel kernel alone
-    if (dense && (rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, (const double*)c->d_Sblk.p, (double*)c->d_H.p, (double*)c->d_S2.p, false))) return rc;
+    if (dense && (rc = xtb_dense_update(c, c->a0, c->a1))) return rc;
     XTB_T1(c, 6);
     XTB_T1(c, 2);
     if ((rc = xtb_stage_finish(c))) return rc;

@@ -243,10 +243,8 @@ __global__ void pet_sum9_kernel(int n, const double* __restrict__ partial, doubl
 
 int xtb_impl_pettifor_assemble(xtb_ctx* c, bool dense) {
     const int na = c->na;
-    const size_t N = (size_t)na * 4;
     int rc;
     if ((rc = xtb_reserve(c, c->d_Hblk, sizeof(double) * 16 * xtb_blocks_alloc(c)))) return rc;
-    if (dense && (rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
     XTB_T0(c, 2);
     const int nown = c->a1 - c->a0;
     const long long nthreads = (long long)(c->cap + 1) * nown;
@@ -258,7 +256,7 @@ int xtb_impl_pettifor_assemble(xtb_ctx* c, bool dense) {
         XTB_LAUNCH_CHECK(c);
     }
     XTB_T0(c, 6);      // dense panel kernel alone
-    if (dense && (rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, nullptr, (double*)c->d_H.p, nullptr, false))) return rc;
+    if (dense && (rc = xtb_dense_update(c, c->a0, c->a1))) return rc;
     XTB_T1(c, 6);
     XTB_T1(c, 2);
     if ((rc = xtb_stage_finish(c))) return rc;

@@ -43,7 +43,7 @@ int xtb_t1(xtb_ctx* c, int s) {
     return XTB_OK;
 }
 int xtb_collect_timing(xtb_ctx* c) {
-    for (int s = 0; s < 16; ++s)
+    for (int s = 0; s < 24; ++s)
         if (c->t_pending & (1u << s)) {
             float ms = 0.f;
             if (cudaEventElapsedTime(&ms, c->tev[s][0], c->tev[s][1]) == cudaSuccess) c->stage_ms[s] = ms;
@@ -154,9 +154,9 @@ int xtb_destroy(xtb_ctx* c) {
                      &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
                      &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep,
                      &c->d_halo_tr, &c->d_halo_cnt, &c->d_halo_slots, &c->d_halo_send, &c->d_halo_recv, &c->d_wall_params, &c->d_Ewall_at, &c->d_Ewall,
-                     &c->d_Fwall, &c->d_SCwall, &c->d_fermi, &c->d_S0, &c->d_SV, &c->d_SV0, &c->d_mdpar};
+                     &c->d_Fwall, &c->d_SCwall, &c->d_prev_size, &c->d_prev_list, &c->d_dense_out, &c->d_fermi, &c->d_S0, &c->d_SV, &c->d_SV0, &c->d_mdpar};
     for (DevBuf* b : all) xtb_free(*b);
-    for (int s = 0; s < 16; ++s) for (int k = 0; k < 2; ++k) if (c->tev[s][k]) cudaEventDestroy(c->tev[s][k]);
+    for (int s = 0; s < 24; ++s) for (int k = 0; k < 2; ++k) if (c->tev[s][k]) cudaEventDestroy(c->tev[s][k]);
     if (c->h_meta) cudaFreeHost(c->h_meta);
     if (c->graph_exec) cudaGraphExecDestroy((cudaGraphExec_t)c->graph_exec);
     if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -429,14 +429,9 @@ int xtb_assemble_blocks(xtb_ctx* c) {
 extern "C++" int xtb_impl_expand_dense(xtb_ctx* c, int first, int last, bool timed) {
     if (!c->have_blocks) XTB_FAIL(c, XTB_ESTATE, "xtb_expand_dense: no block store (xtb_assemble_blocks / xtb_assemble_HS first)");
     if (first < 1 || last > c->na || last < first - 1) XTB_FAIL(c, XTB_EINVAL, "xtb_expand_dense: bad range %d..%d", first, last);
-    const bool ortho = c->tb == XTB_TB_PETTIFOR;
-    const size_t N = (size_t)c->na * c->n_orb;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;
-    if (!ortho && (rc = xtb_reserve(c, c->d_S2, sizeof(double) * N * N))) return rc;
     if (timed) XTB_T0(c, 6);
-    if ((rc = xtb_dense_from_blocks(c, (const double*)c->d_Hblk.p, ortho ? nullptr : (const double*)c->d_Sblk.p, (double*)c->d_H.p,
-                                    ortho ? nullptr : (double*)c->d_S2.p, false, first - 1, last))) return rc;
+    if ((rc = xtb_dense_update(c, first - 1, last))) return rc;
     if (timed) XTB_T1(c, 6);
     c->have_HS = true;
     return XTB_OK;
@@ -554,14 +549,13 @@ int xtb_density_get(xtb_ctx* c, double* Aij, double* Aij_x_Ei) {
     if (c->a0 != 0 || c->a1 != c->na) XTB_FAIL(c, XTB_EINVAL, "xtb_density: dense outputs need the full (unpartitioned) context");
     const size_t N = (size_t)c->na * c->n_orb;
     int rc;
-    if ((rc = xtb_reserve(c, c->d_H, sizeof(double) * N * N))) return rc;     // reuse the dense scratch (H is consumed by now)
-    c->have_HS = false;
+    if ((rc = xtb_reserve(c, c->d_dense_out, sizeof(double) * N * N))) return rc;     // own scratch: H_non / Sij stay resident (xtb_dense_update)
     double* outs[2] = {Aij, Aij_x_Ei};
     const double* blks[2] = {(const double*)c->d_rho.p, (const double*)c->d_rhoE.p};
     for (int t = 0; t < 2; ++t) {
         if (!outs[t]) continue;
-        if ((rc = xtb_dense_from_blocks(c, blks[t], nullptr, (double*)c->d_H.p, nullptr, true))) return rc;
-        XTB_CUDA(c, cudaMemcpyAsync(outs[t], c->d_H.p, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
+        if ((rc = xtb_dense_from_blocks(c, blks[t], nullptr, (double*)c->d_dense_out.p, nullptr, true))) return rc;
+        XTB_CUDA(c, cudaMemcpyAsync(outs[t], c->d_dense_out.p, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
         XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     }
     return XTB_OK;
@@ -833,7 +827,7 @@ long long xtb_counter(const xtb_ctx* c, int which) {
 }
 
 double xtb_stage_ms(const xtb_ctx* c, int stage) {
-    if (!c || stage < 0 || stage > 15) return -1.0;
+    if (!c || stage < 0 || stage > 23) return -1.0;
     return c->stage_ms[stage];
 }
 

@@ -65,6 +65,9 @@ struct xtb_ctx {
     // block-sparse H, S ([n_blocks][n_orb^2], block (j,q): rows = neighbour / j itself, cols = j) and dense H, S
     DevBuf d_Hblk, d_Sblk;
     DevBuf d_H, d_S2;
+    // the dense matrices stay resident; the pattern they were written with (xtb_dense_update, nrl_assemble.cu)
+    DevBuf d_prev_size, d_prev_list, d_dense_out;
+    int dense_state = 0, dense_na = 0, dense_norb = 0, dense_ortho = -1, dense_pcap = 0;
     bool have_HS = false, have_blocks = false;
     // eigen
     const double* d_Ha = nullptr; const double* d_Ei = nullptr; const double* d_fe = nullptr;
@@ -114,11 +117,11 @@ struct xtb_ctx {
     // context stream; xtb_stage_finish() waits for the stream and reads the pending pairs -- except inside xtb_step
     // (deferred), where nothing waits and the pairs are read after the step's single synchronisation, and inside a
     // CUDA-graph capture (capturing), where no events are recorded at all.
-    cudaEvent_t tev[16][2] = {};
+    cudaEvent_t tev[24][2] = {};
     unsigned t_pending = 0, t_started = 0;
     bool deferred = false, capturing = false;
     int density_slotcap = 0, density_stages = 0;
-    double stage_ms[16] = {0};   // see xtb_stage_ms
+    double stage_ms[24] = {0};   // see xtb_stage_ms
     int sm_count = 148;
     int density_dbg = 0;        // XTB_DENSITY_DBG (timing experiments only, separate kernel instantiation): 1 no math, 2 quarter of the tile copies, 4 helper warps nap while polling, 8 no DFMA
     int density_ncw = 8;        // consumer warps of the density kernel (8 or 12); XTB_DENSITY_NCW
@@ -206,4 +209,5 @@ int xtb_impl_dftb_pressure(xtb_ctx* c);
 int xtb_impl_dftb_tables(xtb_ctx* c, double* d_rad, double* d_geo);  // compact tables, nv channels per list entry
 int xtb_impl_nrl_tables(xtb_ctx* c, double* d_rad, double* d_geo);   // compact M_V*/M_lmn/M_xrr/M_x1 per list entry
 // dense column panels of the owned atoms from a block store; tr: block holds (rows j, cols neighbour)
+int xtb_dense_update(xtb_ctx* c, int f0, int f1);      // resident dense H_non / Sij: clear the previous pattern, write the new one
 int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, double* A, double* B, bool tr, int f0 = -1, int f1 = -1);
