@@ -224,6 +224,10 @@ constexpr int NPROD = 3;                // producer warps (bulk-copy issue is se
 // instead of ~50 GB per launch, measured).  The producers therefore publish their position (round, sub-task, chunk) and
 // do not run more than `lead` chunks ahead of the slowest CTA.  The slowest CTA never waits; should a CTA not be
 // resident (foreign work on an SM) the wait gives up after a bounded number of polls and throttling is switched off.
+// "finished" marker of a CTA (and the identity of the min below).  Half of LLONG_MAX: `m + lead` must not wrap -- with
+// ~LLONG_MAX a CTA that found every other CTA finished saw a NEGATIVE sum, polled until the 8192-try timeout (3.4 ms) and only
+// then went on: 3.5 ms instead of 0.035 ms for the density stage of a 32-atom cell (profiles/r02l_probe_small_density_*.log).
+#define XTB_PROG_DONE 0x3fffffffffffffffLL
 constexpr int SYNC_EVERY = 16;      // position published / checked every this many chunks (one L2 round trip per check)
 __device__ __forceinline__ void st_relaxed(long long* p, long long v) {
     asm volatile("st.relaxed.gpu.global.s64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -238,7 +242,7 @@ __device__ __forceinline__ long long ld_relaxed(const long long* p) {
 __device__ __forceinline__ bool throttle(long long* prog, long long pos, int lead, int lane) {
     if (lane == 0) st_relaxed(prog + blockIdx.x, pos);
     for (int tries = 0; tries < 8192; ++tries) {
-        long long m = 0x7fffffffffffffffLL;
+        long long m = XTB_PROG_DONE;
         for (int b = lane; b < (int)gridDim.x; b += 32)
             if (b != (int)blockIdx.x) { const long long v = ld_relaxed(prog + b); m = v < m ? v : m; }
 #pragma unroll
@@ -517,7 +521,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
         }
     }
     // this CTA is done: it no longer holds anyone back
-    if (warp == NCW + 1 && lane == 0) st_relaxed(prog + blockIdx.x, 0x7ffffffffffffff0LL);
+    if (warp == NCW + 1 && lane == 0) st_relaxed(prog + blockIdx.x, XTB_PROG_DONE);
 }
 
 #include "density_pair.cuh"
@@ -711,7 +715,8 @@ int run_density(xtb_ctx* c) {
     const int nown = c->a1 - c->a0;
     // blocks that no kernel below writes (atoms outside [a0,a1)) must not hold garbage; on a full range every block is
     // written by its owner or by the mirror pass
-    if (nown < na || nkeep == 0) {
+    // (a communicating context reads only its own rows and what the halo exchange delivers: nothing to clear there)
+    if ((nown < na && !(c->comm && c->nranks > 1)) || nkeep == 0) {
         XTB_CUDA(c, cudaMemsetAsync(c->d_rho.p, 0, blk_bytes, c->stream));
         XTB_CUDA(c, cudaMemsetAsync(c->d_rhoE.p, 0, blk_bytes, c->stream));
     }

@@ -642,7 +642,7 @@ __device__ __forceinline__ void helper_main(const Smem& S, const KArgs& A, int w
             w0 = w1;
         }
     }
-    if (warp == NCW + 1 && lane == 0) st_relaxed(A.prog + blockIdx.x, 0x7ffffffffffffff0LL);
+    if (warp == NCW + 1 && lane == 0) st_relaxed(A.prog + blockIdx.x, XTB_PROG_DONE);
 }
 
 // Shared memory per stage (doubles): [slotcap][SLOT] tiles | [KS][2][BROW] weighted B operands of i1, i2 | [2][KC] weights.
