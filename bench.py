@@ -110,7 +110,9 @@ def fp64_peak_tflops(torch, ctx):
             best = max(best, 2 * n ** 3 / (e0.elapsed_time(e1) * 1e-3) * 1e-12)
     del a, b, c
     torch.cuda.empty_cache()
-    f = ctx.lib.xtb_debug_fp64_peak
+    # the DMMA issue-rate probe lives in its own library (not in the product .so)
+    probe = C.CDLL(os.path.join(ROOT, "xtant-3_b200", "libxtb_b200_probe.so"), mode=C.RTLD_GLOBAL)
+    f = probe.xtb_debug_fp64_peak
     f.restype = C.c_double; f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
     return best, float(f(ctx.h, 0, 16, 3))
 

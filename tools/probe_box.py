@@ -24,7 +24,9 @@ out["dgemm_8192_tflops"] = best
 del a, b, c
 api = importlib.import_module("xtant-3_b200.api")
 ctx = api.TBContext(0)
-f = ctx.lib.xtb_debug_fp64_peak; f.restype = C.c_double; f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
+import ctypes as _C, os as _os
+_probe = _C.CDLL(_os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "xtant-3_b200", "libxtb_b200_probe.so"), mode=_C.RTLD_GLOBAL)
+f = _probe.xtb_debug_fp64_peak; f.restype = C.c_double; f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
 for w in (4, 8, 16, 32):
     out[f"dmma884_tflops_w{w}"] = f(ctx.h, 0, w, 3)
     out[f"dfma_tflops_w{w}"] = f(ctx.h, 1, w, 3)

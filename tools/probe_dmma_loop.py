@@ -6,7 +6,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 api = importlib.import_module("xtant-3_b200.api")
 ctx = api.TBContext(0)
-f = ctx.lib.xtb_debug_dmma_loop; f.restype = C.c_double; f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+import ctypes as _C, os as _os
+_probe = _C.CDLL(_os.path.join(_os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))), "xtant-3_b200", "libxtb_b200_probe.so"), mode=_C.RTLD_GLOBAL)
+f = _probe.xtb_debug_dmma_loop; f.restype = C.c_double; f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
 out = {}
 for var in (0, 1, 2, 3):
     for w in (2, 3):

@@ -785,7 +785,7 @@ int run_density(xtb_ctx* c) {
             c->density_slotcap = slotcap; c->density_stages = stages;
         } else {
         // slot capacity / stages from the shared-memory budget (227 KB per CTA)
-        const int NCW = c->density_ncw == 12 ? 12 : 8;
+        const int NCW = (c->density_ncw == 12 && !c->density_dbg) ? 12 : 8;     // the debug instantiation exists for 8 consumer warps only
         const int MTMAX = NCW == 8 ? 7 : 5;
         int slotcap = (c->max_nn + 1) / 2 + 6;                 // balanced ownership: half the neighbours (+ slack), + self
         if (slotcap > MTMAX * NCW * 8 / NO) slotcap = MTMAX * NCW * 8 / NO;     // rows must fit MTMAX tiles per warp

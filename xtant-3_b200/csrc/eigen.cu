@@ -33,9 +33,8 @@ struct Libs {
     fn_create_t sv_create = nullptr; fn_destroy_t sv_destroy = nullptr; fn_setstream_t sv_stream = nullptr;
     fn_syevd_buf_t sv_buf = nullptr; fn_syevd_t sv_syevd = nullptr;
     fn_create_t bl_create = nullptr; fn_destroy_t bl_destroy = nullptr; fn_setstream_t bl_stream = nullptr; fn_dgemm_t bl_dgemm = nullptr;
-    handle_t sv = nullptr, bl = nullptr;
 };
-Libs g_libs;
+Libs g_libs;            // the two libraries and their entry points (process-wide); the HANDLES live in the context
 
 void* open_any(const char* const* names) {
     for (int i = 0; names[i]; ++i) {
@@ -65,9 +64,18 @@ bool bind_libs() {
     BIND(bl_stream, so_blas, fn_setstream_t, "cublasSetStream_v2")
     BIND(bl_dgemm, so_blas, fn_dgemm_t, "cublasDgemm_v2")
 #undef BIND
-    if (L.sv_create(&L.sv) != 0 || L.bl_create(&L.bl) != 0) { L.why = "cusolverDnCreate / cublasCreate failed"; return false; }
     L.ok = true;
     return true;
+}
+
+// cuSOLVER / cuBLAS handles of this context: created on the context's device at first use, destroyed with it
+// (xtb_release_lib_handles, called by xtb_destroy), so two contexts on two GPUs never share a handle
+int ctx_handles(xtb_ctx* c) {
+    Libs& L = g_libs;
+    cudaSetDevice(c->device);
+    if (!c->h_cusolver && L.sv_create(&c->h_cusolver) != 0) XTB_FAIL(c, XTB_ECUDA, "cusolverDnCreate failed");
+    if (!c->h_cublas && L.bl_create(&c->h_cublas) != 0) XTB_FAIL(c, XTB_ECUDA, "cublasCreate failed");
+    return XTB_OK;
 }
 
 constexpr int JOB_VECTOR = 1;     // CUSOLVER_EIG_MODE_VECTOR
@@ -101,11 +109,11 @@ __global__ void chop_kernel(long long n, double* __restrict__ A, double eps) {
 int syevd(xtb_ctx* c, int n, double* A, double* W, std::string what) {
     Libs& L = g_libs;
     int lwork = 0;
-    if (L.sv_buf(L.sv, JOB_VECTOR, FILL_UPPER, n, A, n, W, &lwork) != 0) XTB_FAIL(c, XTB_ECUDA, "cusolverDnDsyevd_bufferSize failed (%s)", what.c_str());
+    if (L.sv_buf(c->h_cusolver, JOB_VECTOR, FILL_UPPER, n, A, n, W, &lwork) != 0) XTB_FAIL(c, XTB_ECUDA, "cusolverDnDsyevd_bufferSize failed (%s)", what.c_str());
     int rc;
     if ((rc = xtb_reserve(c, c->d_eig_work, sizeof(double) * (size_t)lwork + 16))) return rc;
     int* d_info = (int*)((double*)c->d_eig_work.p + lwork);
-    if (L.sv_syevd(L.sv, JOB_VECTOR, FILL_UPPER, n, A, n, W, (double*)c->d_eig_work.p, lwork, d_info) != 0)
+    if (L.sv_syevd(c->h_cusolver, JOB_VECTOR, FILL_UPPER, n, A, n, W, (double*)c->d_eig_work.p, lwork, d_info) != 0)
         XTB_FAIL(c, XTB_ECUDA, "cusolverDnDsyevd failed to launch (%s)", what.c_str());
     int info = 0;
     XTB_CUDA(c, cudaMemcpyAsync(&info, d_info, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -116,13 +124,20 @@ int syevd(xtb_ctx* c, int n, double* A, double* W, std::string what) {
 
 }  // namespace
 
+void xtb_release_lib_handles(xtb_ctx* c) {
+    if (c->h_cusolver && g_libs.sv_destroy) g_libs.sv_destroy(c->h_cusolver);
+    if (c->h_cublas && g_libs.bl_destroy) g_libs.bl_destroy(c->h_cublas);
+    c->h_cusolver = nullptr; c->h_cublas = nullptr;
+}
+
 // C = op(A) op(B) through the run-time bound cuBLAS (plain library GEMM; also used by coupling.cu)
 int xtb_blas_dgemm(xtb_ctx* c, bool ta, bool tb, int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* Cm, int ldc) {
     if (!bind_libs()) XTB_FAIL(c, XTB_ESTATE, "cuBLAS not available: %s", g_libs.why.c_str());
     Libs& L = g_libs;
-    L.bl_stream(L.bl, c->stream);
+    { int rc = ctx_handles(c); if (rc) return rc; }
+    L.bl_stream(c->h_cublas, c->stream);
     const double one = 1.0, zero = 0.0;
-    if (L.bl_dgemm(L.bl, ta ? OP_T : OP_N, tb ? OP_T : OP_N, m, n, k, &one, A, lda, B, ldb, &zero, Cm, ldc) != 0)
+    if (L.bl_dgemm(c->h_cublas, ta ? OP_T : OP_N, tb ? OP_T : OP_N, m, n, k, &one, A, lda, B, ldb, &zero, Cm, ldc) != 0)
         XTB_FAIL(c, XTB_ECUDA, "cublasDgemm failed (m=%d n=%d k=%d)", m, n, k);
     return XTB_OK;
 }
@@ -136,7 +151,8 @@ int xtb_impl_eigensolve(xtb_ctx* c) {
     const size_t nn = (size_t)N * N;
     const bool ortho = c->tb == XTB_TB_PETTIFOR;
     int rc;
-    L.sv_stream(L.sv, c->stream); L.bl_stream(L.bl, c->stream);
+    if ((rc = ctx_handles(c))) return rc;
+    L.sv_stream(c->h_cusolver, c->stream); L.bl_stream(c->h_cublas, c->stream);
     if ((rc = xtb_reserve(c, c->own_Ha, sizeof(double) * nn))) return rc;
     if ((rc = xtb_reserve(c, c->own_Ei, sizeof(double) * N))) return rc;
     if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
@@ -161,9 +177,9 @@ int xtb_impl_eigensolve(xtb_ctx* c) {
         XTB_LAUNCH_CHECK(c);
         loewdin_scale_kernel<<<dim3(8, n), 256, 0, c->stream>>>(N, wS, fix, X);             // X = U s^-1/2   :1036
         XTB_LAUNCH_CHECK(c);
-        if (L.bl_dgemm(L.bl, OP_N, OP_N, n, n, n, &one, (const double*)c->d_H.p, n, X, n, &zero, T, n) != 0)   // H X   (dsymm, :1049)
+        if (L.bl_dgemm(c->h_cublas, OP_N, OP_N, n, n, n, &one, (const double*)c->d_H.p, n, X, n, &zero, T, n) != 0)   // H X   (dsymm, :1049)
             XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(H X) failed");
-        if (L.bl_dgemm(L.bl, OP_T, OP_N, n, n, n, &one, X, n, T, n, &zero, Ha, n) != 0)                       // X^T (H X)  :1054
+        if (L.bl_dgemm(c->h_cublas, OP_T, OP_N, n, n, n, &one, X, n, T, n, &zero, Ha, n) != 0)                       // X^T (H X)  :1054
             XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(X^T H X) failed");
         if (c->tb == XTB_TB_DFTB) {
             chop_kernel<<<1184, 256, 0, c->stream>>>((long long)nn, Ha, 1e-10);
@@ -171,7 +187,7 @@ int xtb_impl_eigensolve(xtb_ctx* c) {
         }
         rc = syevd(c, n, Ha, Ei, "H'");
         if (rc) return rc;                                     // TB_NRL.f90:409
-        if (L.bl_dgemm(L.bl, OP_N, OP_N, n, n, n, &one, X, n, Ha, n, &zero, T, n) != 0)      // Ha = X V   :421
+        if (L.bl_dgemm(c->h_cublas, OP_N, OP_N, n, n, n, &one, X, n, Ha, n, &zero, T, n) != 0)      // Ha = X V   :421
             XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(X V) failed");
         // the eigenvectors now live in T: swap the roles of the two buffers
         DevBuf tmp = c->own_Ha; c->own_Ha = c->d_eig_T; c->d_eig_T = tmp;

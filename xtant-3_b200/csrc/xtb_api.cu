@@ -148,6 +148,7 @@ int xtb_destroy(xtb_ctx* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->comm) xtb_comm_destroy(c);
+    xtb_release_lib_handles(c);
     DevBuf* all[] = {&c->d_params, &c->d_koa, &c->d_S, &c->d_nn_size, &c->d_nn_list, &c->d_nn_dist, &c->d_nn_dist_s, &c->d_rev, &c->d_own,
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,

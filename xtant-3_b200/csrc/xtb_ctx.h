@@ -75,6 +75,7 @@ struct xtb_ctx {
     long long K = 0;            // number of states (columns of Ha)
     bool have_eigen = false;
     bool have_eigvec = false;   // Ha, Ei produced on the device by xtb_eigensolve (occupations pending)
+    void* h_cusolver = nullptr; void* h_cublas = nullptr;      // library handles of this context (eigen.cu)
     DevBuf d_eig_work, d_eig_X, d_eig_T, d_eigS;   // cuSOLVER workspace, Loewdin X, scratch, eigenvalues of S
     // density
     double f_cut = 0.0;
@@ -202,6 +203,7 @@ int xtb_impl_allreduce9(xtb_ctx* c, double* d9);
 int xtb_impl_coupling(xtb_ctx* c, int kind_M);      // coupling.cu
 int xtb_rows_by_state(xtb_ctx* c, const double* Ha, long long K, double* X);      // density.cu
 int xtb_blas_dgemm(xtb_ctx* c, bool ta, bool tb, int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* Cm, int ldc);
+void xtb_release_lib_handles(xtb_ctx* c);   // eigen.cu
 int xtb_impl_eigensolve(xtb_ctx* c);        // eigen.cu: Loewdin + Dsyevd + back-transform on the device-resident H, S
 int xtb_impl_dftb_assemble(xtb_ctx* c, bool dense);
 int xtb_impl_dftb_forces(xtb_ctx* c);
