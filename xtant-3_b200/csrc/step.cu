@@ -357,7 +357,7 @@ static int step_body(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool ste
 struct GraphKey {
     unsigned flags, iomask;
     int na, cap, max_nn, tb, n_orb, a0, a1, n_kinds;
-    long long blk_cap, k_kept, K;
+    long long blk_cap, k_kept, K, alloc_epoch;
     const void *Ha, *Ei, *fe;
     cudaStream_t stream;
     double rm, f_cut;
@@ -375,7 +375,7 @@ static GraphKey make_key(const xtb_ctx* c, unsigned flags, const xtb_step_io* io
     memset(&k, 0, sizeof k);
     k.flags = flags; k.iomask = io_mask(io);
     k.na = c->na; k.cap = c->cap; k.max_nn = c->max_nn; k.tb = c->tb; k.n_orb = c->n_orb; k.a0 = c->a0; k.a1 = c->a1; k.n_kinds = c->n_kinds;
-    k.blk_cap = c->blk_cap; k.k_kept = c->k_kept; k.K = c->K;
+    k.blk_cap = c->blk_cap; k.k_kept = c->k_kept; k.K = c->K; k.alloc_epoch = c->alloc_epoch;
     k.Ha = c->d_Ha; k.Ei = c->d_Ei; k.fe = c->d_fe; k.stream = c->stream; k.rm = c->rm; k.f_cut = c->f_cut;
     k.rep = !c->h_pet_rep.empty(); k.wall = !c->h_wall.empty();
     return k;
@@ -413,16 +413,18 @@ static int graph_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool* o
     if (!c->graph_exec || c->graph_key.size() != sizeof key || memcmp(c->graph_key.data(), &key, sizeof key) != 0) {
         graph_drop(c);
         cudaGraph_t graph = nullptr;
-        XTB_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+        XTB_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeRelaxed));
         c->capturing = true; c->deferred = true;
         int rc = XTB_OK;
         if (g.S && cudaMemcpyAsync(c->d_S.p, g.S, sizeof(double) * na3, cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = XTB_ECUDA;
         if (!rc) { c->have_neigh = false; rc = step_body(c, flags & ~XTB_STEP_GRAPH, &g, true); }
         c->capturing = false; c->deferred = false;
         const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+        if (!rc && c->alloc_epoch != key.alloc_epoch) rc = XTB_ESTATE;      // a buffer grew while capturing: not replayable
         if (rc || e != cudaSuccess || !graph) {
             if (graph) cudaGraphDestroy(graph);
             cudaGetLastError();
+            if (rc == XTB_ESTATE && c->alloc_epoch != key.alloc_epoch) { *overflow = true; c->have_neigh = false; return XTB_OK; }   // eager path
             if (rc) return rc;
             XTB_FAIL(c, XTB_ECUDA, "xtb_step: graph capture failed: %s", cudaGetErrorString(e));
         }

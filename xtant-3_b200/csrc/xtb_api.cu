@@ -18,6 +18,7 @@ int xtb_reserve(xtb_ctx* c, DevBuf& b, size_t bytes) {
         XTB_FAIL(c, XTB_ENOMEM, "cudaMalloc(%zu bytes) failed: %s", bytes, cudaGetErrorString(e));
     }
     b.bytes = bytes;
+    c->alloc_epoch++;        // a captured graph holds the old address: it must not be replayed (step.cu, GraphKey)
     // zero once at (re)allocation: padding that no kernel addresses (ELL slack, the gaps of xtb_set_block_layout) then holds
     // zeros instead of stale memory, so whole-buffer copies and exchanges are deterministic
     cudaMemsetAsync(b.p, 0, bytes, c->stream);

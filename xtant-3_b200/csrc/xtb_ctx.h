@@ -56,6 +56,7 @@ struct xtb_ctx {
     double* h_stage = nullptr; size_t h_stage_bytes = 0;     // pinned staging of the step's host inputs / outputs
     unsigned steady_flags_done = 0;                           // flag set of the last eager steady step (its buffers are sized)
     long long graph_captures = 0;
+    long long alloc_epoch = 0;                                // bumped by every (re)allocation of a device buffer
     double rm = 0.0;
     DevBuf d_nn_size, d_nn_list, d_nn_dist, d_nn_dist_s, d_rev, d_own, d_rowptr, d_maxnn;
     bool have_neigh = false, have_dens = false;
