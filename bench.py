@@ -119,7 +119,9 @@ def fp64_peak_tflops(torch, ctx):
 
 def make_eigen_device(torch, wk, wl, N):
     """synthetic eigen-solution resident in HBM: C ~ N(0,1)/sqrt(N), E sorted uniform(-10,40),
-    f = Fermi at 61 % filling.  Memory layout = Fortran Ha(N,N): state n contiguous at offset n*N."""
+    f = Fermi at 61 % filling.  An (N, N) block of i.i.d. numbers: read as Fortran Ha(N,N) (state n contiguous at offset n*N,
+    xtb_set_eigen_device) or as the state-minor HaT (row r contiguous at offset r*N, xtb_set_eigen_device_t -- the layout
+    xtb_eigensolve leaves on the device) it is the same kind of synthetic eigenvector matrix."""
     g = torch.Generator(device="cuda"); g.manual_seed(7)
     Cm = torch.empty((N, N), dtype=torch.float64, device="cuda")
     step = 2048
@@ -155,7 +157,15 @@ def run_own(args):
     ctx.set_workload(wl)
     a0, a1 = mg.partition(na, world, rank)      # = the range xtb_comm_init gives this rank
     Cm, dE, dfe, E, fe = make_eigen_device(torch, wk, wl, N)
-    ctx.set_eigen_device(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
+    # headline: eigenvectors resident in the layout the on-device eigensolve leaves them in (state-minor; its last GEMM writes
+    # it at no extra cost), which the density kernel streams through a tensor map -- no re-tiled copy.  XTB_BENCH_EIGEN_LAYOUT=
+    # fortran: Fortran-layout Ha(N,N) as a host eigensolver would upload it (re-tiling pass inside the density stage); that
+    # flow is also timed below as `variant_fortran_layout_eigenvectors`.
+    state_minor = os.environ.get("XTB_BENCH_EIGEN_LAYOUT", "state_minor") != "fortran"
+    if state_minor:
+        ctx.set_eigen_device_t(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
+    else:
+        ctx.set_eigen_device(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
 
     # N > 1: one NCCL communicator INSIDE the library (xtb_comm_init): rank 0 draws the id, torch.distributed only carries its
     # 128 bytes to the other ranks (what MPI_Bcast does for the Fortran caller).  Every exchange of the step then runs in
@@ -236,7 +246,9 @@ def run_own(args):
             "data": "synthetic",
             "config": {"workload": f"{wl['name']}: synthetic Au fcc 8x8x16 supercell ({na} atoms, N={N} orbitals), NRL spd TB",
                        "n_pairs": n_pairs, "n_blocks": n_blocks, "states_kept": k_kept, "l2_policy": "inputs larger than L2 "
-                       "(eigenvectors 10.9 GB, H/S 21.7 GB per step)", "eigensolve": "outside graft; synthetic resident eigenvectors",
+                       "(eigenvectors 10.9 GB per step)", "eigensolve": "outside graft; synthetic resident eigenvectors, "
+                       + ("state-minor (the layout xtb_eigensolve leaves on the device)" if state_minor else "Fortran layout Ha(N,N)"),
+                       "density_reads": "eigenvectors through a tensor map, no re-tiled copy" if ctx.counter(17) == 1 else "re-tiled copy of the eigenvectors",
                        "partition": "atom rows" if world > 1 else "single GPU",
                        "step_call": "xtb_step (one library call per step; steady-state neighbour list without a size read-back at N = 1)",
                        "block_exchange": (None if world == 1 else "inside libxtb_b200.so over NCCL (xtb_comm_init): H/S block segments in-place "
@@ -262,11 +274,7 @@ def run_own(args):
                          "flops_per_launch": flops,
                          "peak_source": "in-run torch.matmul fp64 8192^3 (cuBLAS DGEMM, burst); MEASURED_PEAKS.json has no FP64 entry",
                          "peak_pipe_dmma884": dmma_tf},
-            "roofline_hbm_stage": (None if world > 1 else {
-                "bound": "hbm", "kernel": "ct_tile_kernel (eigenvector columns re-tiled into TMA / DMMA-fragment order)",
-                "achieved": retile_bytes / (stage[16] * 1e-3) * 1e-9 if stage[16] > 0 else None, "peak": hbm, "unit": "GB/s",
-                "frac": (retile_bytes / (stage[16] * 1e-3) * 1e-9 / hbm) if stage[16] > 0 else None, "ms": stage[16],
-                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)"}),
+            "roofline_hbm_stage": None,      # filled below from the Fortran-layout variant (the only HBM-bound kernel left: re-tiling)
             "dense_update": {"ms": stage[6], "bytes_touched": 2 * 2 * 8 * 81 * n_blocks,
                              "note": "dense H_non, Sij (2 x 10.9 GB) stay resident in HBM; a step clears the blocks of the previous "
                                      "neighbour pattern and writes the blocks of the new one (every element ends up exactly as after a full write)"},
@@ -284,6 +292,23 @@ def run_own(args):
         finally:
             ctx.set_density_cutoff(0.0)
             ctx.density()
+    # ---- variant: Fortran-layout eigenvectors (what a host eigensolver uploads): the density stage then re-tiles them first
+    if rank == 0 and world == 1 and state_minor:
+        ctx.set_eigen_device(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
+        for _ in range(3):
+            ctx.density()
+        t3, t7, t16 = ctx.stage_ms(3), ctx.stage_ms(7), ctx.stage_ms(16)
+        out["variant_fortran_layout_eigenvectors"] = {
+            "density_ms": t3, "density_kernel_ms": t7, "retile_kernel_ms": t16, "ms_per_step_estimate": ms - stage[3] + t3,
+            "note": "xtb_set_eigen_device with Ha(N,N) column-major: ct_tile_kernel writes the tiled copy (10.9 GB in, 10.8 GB out) "
+                    "before the contraction; same rho / rho_E bits (tests/test_density_tm_gpu.py)"}
+        out["roofline_hbm_stage"] = {
+            "bound": "hbm", "kernel": "ct_tile_kernel (Fortran-layout variant only: eigenvector columns re-tiled into TMA / DMMA-fragment order)",
+            "achieved": retile_bytes / (t16 * 1e-3) * 1e-9 if t16 > 0 else None, "peak": hbm, "unit": "GB/s",
+            "frac": (retile_bytes / (t16 * 1e-3) * 1e-9 / hbm) if t16 > 0 else None, "ms": t16,
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)"}
+        ctx.set_eigen_device_t(Cm.data_ptr(), dE.data_ptr(), dfe.data_ptr())
+        ctx.density()
     # ---- informational variant: the dense H_non / Sij written in full (every element) as up to round 2
     if rank == 0 and world == 1:
         os.environ["XTB_DENSE_FULL"] = "1"

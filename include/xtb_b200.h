@@ -169,6 +169,11 @@ int  xtb_expand_dense(xtb_ctx*, int atom_first, int atom_last, double* H_non, do
  *      are device memory that stays valid until the next xtb_set_eigen* call (zero copy). */
 int  xtb_set_eigen       (xtb_ctx*, const double* Ha, const double* Ei, const double* fe /*NULL: occupations follow through xtb_set_occupations*/);
 int  xtb_set_eigen_device(xtb_ctx*, const double* dHa, const double* dEi, const double* dfe);
+/* State-minor device eigenvectors: dHaT[n + K*r] = Ha(r, n) (row r of state n; the K = N states of a row are contiguous),
+ * 16-byte aligned.  This is the layout xtb_eigensolve leaves for 9-orbital sets (its last GEMM writes it at no extra cost) and
+ * the one the rho / rho_E kernel streams straight through a tensor map -- with it no re-tiled copy of the eigenvectors is made.
+ * The Fortran-layout Ha is derived on the device only when something asks for it (xtb_coupling, xtb_save_eigen_prev, a host copy). */
+int  xtb_set_eigen_device_t(xtb_ctx*, const double* dHaT, const double* dEi, const double* dfe);
 /* (xtb_set_eigen_device reads dfe once, to select the occupied states: call it again after changing the buffers' contents) */
 
 /* Optional on-device eigensolve (the north star feeds end-to-end steps this way so that H, S and Ha
@@ -340,7 +345,9 @@ int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
  *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,
  *           9 / 10 shared-memory slots / pipeline stages of the last density kernel,
- *           11 work units (atom pairs + single atoms) of the last two-column-atom density launch */
+ *           11 work units (atom pairs + single atoms) of the last two-column-atom density launch,
+ *           12 / 13 bytes received per rank by the last H/S / rho exchange, 14 / 15 halo blocks sent / received, 16 CUDA graphs captured,
+ *           17 = 1 if the last density launch read the state-minor eigenvectors through the tensor map (no re-tiled copy) */
 long long xtb_counter(const xtb_ctx*, int which);
 /* device time [ms] of the last run of a stage (CUDA events on the context stream):
  * 1 neighbours, 2 radial+assembly, 3 density, 4 forces, 5 pressure,

@@ -84,7 +84,7 @@ def test_fortran_shim_interfaces_match_the_header():
         assert name in protos, f"shim binds {name}, which the header does not declare"
         assert protos[name] == n, f"{name}: {n} arguments in the shim, {protos[name]} in the header"
     # introspection / zero-copy / stream entry points are for the Python and C++ hosts; everything else must be bound
-    host_only = {"xtb_version", "xtb_set_stream", "xtb_counter", "xtb_device_buffer", "xtb_neighbours_compact", "xtb_set_eigen_device"}
+    host_only = {"xtb_version", "xtb_set_stream", "xtb_counter", "xtb_device_buffer", "xtb_neighbours_compact", "xtb_set_eigen_device", "xtb_set_eigen_device_t"}
     # and the shim's get_near_neighbours keeps the reference's `dm` contract: a present dm returns the radius, no list
     body = shim[shim.index("subroutine get_near_neighbours"):shim.index("end subroutine get_near_neighbours")]
     assert re.search(r"if \(present\(dm\)\) then\s*!.*\n\s*dm = rm\s*\n\s*else\s*\n\s*call push_system", body)

@@ -154,6 +154,7 @@ SIGNATURES = {
     "xtb_expand_dense": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _pd, _pd]),
     "xtb_set_eigen": (C.c_int, [C.c_void_p, _pd, _pd, _pd]),
     "xtb_set_eigen_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "xtb_set_eigen_device_t": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "xtb_eigensolve": (C.c_int, [C.c_void_p, _pd, _pd, _pd]),
     "xtb_get_eigenvalues": (C.c_int, [C.c_void_p, _pd]),
     "xtb_set_occupations": (C.c_int, [C.c_void_p, _pd]),

@@ -204,6 +204,10 @@ class TBContext:
         """device pointers (ints), e.g. torch tensors' data_ptr(); zero copy"""
         self._ck(self.lib.xtb_set_eigen_device(self.h, C.c_void_p(dHa), C.c_void_p(dEi), C.c_void_p(dfe)))
 
+    def set_eigen_device_t(self, dHaT, dEi, dfe):
+        """state-minor device eigenvectors HaT[row][state] (device pointers as ints); zero copy, no re-tiling"""
+        self._ck(self.lib.xtb_set_eigen_device_t(self.h, C.c_void_p(dHaT), C.c_void_p(dEi), C.c_void_p(dfe)))
+
     def eigensolve(self, want_Ha=False):
         """on-device Loewdin + Dsyevd + back-transform (TB_NRL.f90:985-1060,402-421); returns (Ei, eigen_S[, Ha])"""
         N = self.na * self.n_orb

@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(256) antisym_kernel(long long N, int kind, con
 }  // namespace
 
 int xtb_impl_coupling(xtb_ctx* c, int kind_M) {
+    { int rc0 = xtb_ensure_Ha_std(c); if (rc0) return rc0; }      // the coupling reads the Fortran-layout Ha
     const long long N = (long long)c->na * c->n_orb, K = c->K;
     if (K != N) XTB_FAIL(c, XTB_EINVAL, "xtb_coupling: needs all N = %lld states (have %lld)", N, K);
     if (N > 46000) XTB_FAIL(c, XTB_EINVAL, "xtb_coupling: N = %lld exceeds the 32-bit leading dimension of cublasDgemm", N);

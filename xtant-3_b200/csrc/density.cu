@@ -23,6 +23,7 @@
 //   mirror : non-owner blocks filled by transposition, so S4/S5 stream complete rows of blocks.
 // Algorithmic flops (roofline numerator): 2 matrices * 2 * n_orb^2 * K_kept * (n_pairs/2 + na).
 #include "xtb_ctx.h"
+#include <cuda.h>            // CUtensorMap and its enums only; the encoder is fetched through the runtime (no -lcuda)
 #include <cstdint>
 #include <cstdlib>
 #include <type_traits>
@@ -192,6 +193,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+// TMA tensor copy (2-D tiled, swizzled) global -> shared through a tensor map that lives in global memory (SASS: UTMALDG)
+__device__ __forceinline__ void tensor_g2s(void* dst, const void* tmap, int c0, int c1, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(smem_u32(dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
     asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
         : "+d"(d0), "+d"(d1) : "d"(a), "d"(b));
@@ -214,6 +220,17 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 // execution resource on B200 (profiles/r01_probe_fp64_peaks.json), so this issues exactly the useful flops,
 // where a third, 2/8-full DMMA column tile would waste 25 % of the pipe.
 constexpr int SLOT = 9 * KC + 4;       // 148 (KC = 16) / 292 (KC = 32): both = 4 mod 16
+// ---- state-minor eigenvectors (TM = true): no re-tiled copy --------------------------------------------------------------
+// When the eigenvectors are resident as HaT[row r][state n] (states contiguous: what xtb_eigensolve's last GEMM writes, or
+// xtb_set_eigen_device_t), the (atom, chunk) tile -- 9 rows x 16 states = 9 x 128 bytes -- is ONE 2-D TMA box straight from
+// HaT, with the 128-byte swizzle: the 16-byte piece c of smem row R lands at piece c ^ (R & 7).  Slots are 9 rows = 1152
+// bytes apart from a 1024-byte aligned stage base, so R is simply the row index of the sub-task (9 * slot + r), the 8 rows
+// of a DMMA row tile are 8 consecutive R, and the A fragment of lane (g, t) at k-step s sits at
+//     R * 16 + 2 * ((2 s + (t >> 1)) ^ (R & 7)) + (t & 1)        [doubles]
+// -- for the 32 lanes every 8-byte bank pair is hit exactly twice: the two wavefronts a 64-bit warp load needs anyway.
+// Same bytes per tile, same number of TMA operations per chunk as the Ct path, and the 21.7 GB re-tiling pass is gone.
+constexpr int SLOT_TM = 9 * KC;        // 144 doubles = 9 rows of 128 bytes (KC = 16)
+__host__ __device__ constexpr int stage_doubles_tm(int slotcap) { return (slotcap * SLOT_TM + (KC / 4) * 72 + 2 * KC + 127) / 128 * 128; }
 constexpr int BROW = 72;
 constexpr int NPROD = 3;                // producer warps (bulk-copy issue is serialised per lane within a warp); 8 + 1 + 3 = 12 warps = 3 per SM sub-partition -> 168 registers per thread
 
@@ -263,22 +280,25 @@ template <int MT>
 struct Frag {
     double a[MT], b0, b1, b8f, b8e;
 };
-template <int NO, int MT>
+template <int NO, int MT, bool TM = false, int NCW = 8>
 __device__ __forceinline__ void load_frag(Frag<MT>& f, const double* __restrict__ stg, const double* __restrict__ Bs,
-                                          const int (&off)[MT], int s, int lane, int t) {
+                                          const int (&off)[MT], int s, int lane, int t, const int (&ks)[KS]) {
     f.b0 = Bs[s * BROW + lane];
     f.b1 = Bs[s * BROW + 32 + lane];
     f.b8f = Bs[s * BROW + 64 + t];
     f.b8e = Bs[s * BROW + 68 + t];
+    // TM: the rows of this lane's tiles are 8 NCW rows = NCW KB apart, so one register per k-step (row of tile 0 + swizzled
+    // position) and an immediate per tile address every fragment; rows past the sub-task (at most 7, in its last tile) read on
+    // into the stage (finite or not, their results are never stored)
 #pragma unroll
-    for (int mt = 0; mt < MT; ++mt) f.a[mt] = stg[off[mt] + NO * 4 * s];
+    for (int mt = 0; mt < MT; ++mt) f.a[mt] = TM ? stg[ks[s] + mt * (NCW * 8 * 16)] : stg[off[mt] + NO * 4 * s];
 }
 
 // Consumer warp, one sub-task (atom i + up to slotcap-1 owned neighbours), MT row tiles.
 // The chunk loop is software-pipelined across the stage boundary: the operands of k-step 0 of the NEXT chunk are
 // fetched (after its barriers) before the math of the last k-step of the current chunk is issued, so the barrier
 // round trip and the shared-memory latency hide behind 12 DMMAs instead of idling the FP64 pipe once per chunk.
-template <int NO, int NCW, int MT, bool DBG>
+template <int NO, int NCW, int MT, bool DBG, bool TM = false>
 __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_doubles, int boff, uint32_t stages,
                                                 uint64_t* full, uint64_t* bready, uint64_t* empty, Ring& rg, int nchunks,
                                                 int nrows, int warp, int lane, const int* slot_q, size_t b0i,
@@ -293,7 +313,13 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
         const int R = 8 * (warp + NCW * mt) + g;
         const int sl = R / NO, r = R - sl * NO;
         off[mt] = (R < nrows) ? sl * SLOT + 4 * r + t : t;      // rows beyond the task read row 0 (results dropped)
-        asm volatile("" : "+r"(off[mt]));                      // keep it in a register (no per-chunk re-derivation)
+        if (!TM) asm volatile("" : "+r"(off[mt]));             // keep it in a register (no per-chunk re-derivation)
+    }
+    int ks[KS];                                                // TM: row (8 warp + g) of tile 0 + swizzled position of (k-step s, t); R & 7 = g
+#pragma unroll
+    for (int s = 0; s < KS; ++s) {
+        ks[s] = (8 * warp + g) * 16 + 2 * ((2 * s + (t >> 1)) ^ g) + (t & 1);
+        if (TM) asm volatile("" : "+r"(ks[s]));
     }
     if (nchunks > 0) {
         const double* stg = sbuf + (size_t)rg.st * stage_doubles;
@@ -303,7 +329,7 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
         mbar_wait(&full[rg.st], rg.ph);
         mbar_wait(&bready[rg.st], rg.ph);
         Frag<MT> f0, f1;      // double buffer: even k-steps compute from f0 while f1 is loaded, odd k-steps the other way round
-        load_frag<NO, MT>(f0, stg, stg + boff, off, 0, lane, t);
+        load_frag<NO, MT, TM, NCW>(f0, stg, stg + boff, off, 0, lane, t, ks);
         static_assert(KS % 2 == 0, "the fragment double buffer needs an even number of k-steps per chunk");
         for (int ch = 0; ch < nchunks; ++ch) {
             Ring rn = rg;
@@ -315,12 +341,12 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
                 Frag<MT>& cu = (s & 1) ? f1 : f0;
                 Frag<MT>& nx = (s & 1) ? f0 : f1;
                 if (s + 1 < KS) {
-                    load_frag<NO, MT>(nx, stg, stg + boff, off, s + 1, lane, t);
+                    load_frag<NO, MT, TM, NCW>(nx, stg, stg + boff, off, s + 1, lane, t, ks);
                     // probe the barriers of the next stage one k-step early: the answer is in a register long before it is needed
                     if (s + 2 == KS && ch + 1 < nchunks) ready = mbar_test(&full[rn.st], rn.ph) & mbar_test(&bready[rn.st], rn.ph);
                 } else if (ch + 1 < nchunks) {
                     if (!ready) { mbar_wait(&full[rn.st], rn.ph); mbar_wait(&bready[rn.st], rn.ph); }
-                    load_frag<NO, MT>(nx, stg_n, stg_n + boff, off, 0, lane, t);
+                    load_frag<NO, MT, TM, NCW>(nx, stg_n, stg_n + boff, off, 0, lane, t, ks);
                 }
                 if (!DBG || !(dbg & 1)) {
 #pragma unroll
@@ -374,7 +400,7 @@ __device__ __forceinline__ void consume_idle(uint32_t stages, uint64_t* full, ui
     }
 }
 
-template <int NO, int NCW, bool DBG>
+template <int NO, int NCW, bool DBG, bool TM = false>      // TM: `Ct` carries the address of the tensor map of HaT (global memory)
 __global__ void __launch_bounds__((NCW + 1 + NPROD) * 32, 1)
 density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, int nchunks, int dbg, int maxsub, int lead, int split, long long* __restrict__ prog,
                     const int* __restrict__ nn_size, const int* __restrict__ nn_list, const signed char* __restrict__ own,
@@ -384,8 +410,10 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
     constexpr int TILE = NO * KC;                       // doubles per (atom, chunk) tile in global memory
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const uint32_t stages = (uint32_t)stages_;
-    const int stage_doubles = slotcap * SLOT + KS * BROW + 2 * KC;
+    const int stage_doubles = TM ? stage_doubles_tm(slotcap) : slotcap * SLOT + KS * BROW + 2 * KC;
+    constexpr int SLOTW = TM ? SLOT_TM : SLOT;          // doubles between the slots of a stage
     double* sbuf = reinterpret_cast<double*>(smem_raw);
+    if (TM) sbuf += ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u) >> 3;      // swizzle pattern = address bits: 1 KB aligned stages
     uint64_t* full = reinterpret_cast<uint64_t*>(sbuf + (size_t)stages * stage_doubles);
     uint64_t* bfull = full + stages;          // slot 0 (atom i) + weights landed: the B warp can start early
     uint64_t* bready = bfull + stages;
@@ -459,6 +487,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
                 const int k1 = lane + 32 < mine ? 1 + (lane + 32) * NPROD + pw : -1;
                 const size_t src0 = k0 >= 0 ? (size_t)slot_atom[k0] * TILE : 0, src1 = k1 >= 0 ? (size_t)slot_atom[k1] * TILE : 0;
                 const size_t srcB = (size_t)slot_atom[0] * TILE;
+                const int row0 = k0 >= 0 ? slot_atom[k0] * NO : 0, row1 = k1 >= 0 ? slot_atom[k1] * NO : 0, rowB = slot_atom[0] * NO;   // TM: first row of the box
                 const long long pos0 = ((long long)round * maxsub + sub) * nchunks;
                 for (int ch = 0; ch < nchunks; ++ch) {
                     if (lead > 0 && pw == 0 && (ch % SYNC_EVERY) == 0 && !throttle(prog, pos0 + ch, lead, lane)) lead = 0;   // the other producers cannot pass warp 0 by more than the ring
@@ -467,18 +496,28 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
                     if (lane == 0) {
                         if (pw == 0) {
                             mbar_expect_tx(&bfull[rg.st], (uint32_t)(TILE + 2 * KC) * 8u);
-                            bulk_g2s(dstage, csrc + srcB, TILE * 8, &bfull[rg.st]);
-                            bulk_g2s(dstage + slotcap * SLOT + KS * BROW, w1, KC * 8, &bfull[rg.st]);
-                            bulk_g2s(dstage + slotcap * SLOT + KS * BROW + KC, w2, KC * 8, &bfull[rg.st]);
+                            if (TM) tensor_g2s(dstage, Ct, ch * KC, rowB, &bfull[rg.st]);
+                            else bulk_g2s(dstage, csrc + srcB, TILE * 8, &bfull[rg.st]);
+                            bulk_g2s(dstage + slotcap * SLOTW + KS * BROW, w1, KC * 8, &bfull[rg.st]);
+                            bulk_g2s(dstage + slotcap * SLOTW + KS * BROW + KC, w2, KC * 8, &bfull[rg.st]);
                         }
                         mbar_expect_tx(&full[rg.st], bytes);
                     }
                     __syncwarp();
+                    if (TM) {
+                        if (k0 >= 0) tensor_g2s(dstage + k0 * SLOT_TM, Ct, ch * KC, row0, &full[rg.st]);
+                        if (k1 >= 0) tensor_g2s(dstage + k1 * SLOT_TM, Ct, ch * KC, row1, &full[rg.st]);
+                        for (int k = lane + 64; k < mine; k += 32) {
+                            const int s = 1 + k * NPROD + pw;
+                            tensor_g2s(dstage + s * SLOT_TM, Ct, ch * KC, slot_atom[s] * NO, &full[rg.st]);
+                        }
+                    } else {
                     if (k0 >= 0) bulk_g2s(dstage + k0 * SLOT, csrc + src0, TILE * 8, &full[rg.st]);
                     if (k1 >= 0) bulk_g2s(dstage + k1 * SLOT, csrc + src1, TILE * 8, &full[rg.st]);
                     for (int k = lane + 64; k < mine; k += 32) {      // only for slot capacities beyond 64 * NPROD
                         const int s = 1 + k * NPROD + pw;
                         bulk_g2s(dstage + s * SLOT, csrc + (size_t)slot_atom[s] * TILE, TILE * 8, &full[rg.st]);
+                    }
                     }
                     csrc += (size_t)na * TILE; w1 += KC; w2 += KC;
                     rg.next(stages);
@@ -489,16 +528,18 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
                 for (int ch = 0; ch < nchunks; ++ch) {
                     mbar_spin(&bfull[rg.st], rg.ph, DBG && (dbg & 4));
                     double* stg = sbuf + (size_t)rg.st * stage_doubles;
-                    double* Bs = stg + slotcap * SLOT;
+                    double* Bs = stg + slotcap * SLOTW;
                     const double* wsm = Bs + KS * BROW;
 #pragma unroll
                     for (int s = 0; s < KS; ++s) {
                         const double w_f = wsm[4 * s + t], w_e = wsm[KC + 4 * s + t];
-                        const double ci = stg[NO * 4 * s + 4 * g + t];            // C[i, mu = g][state 4 s + t]
+                        const double ci = TM ? stg[g * 16 + 2 * ((2 * s + (t >> 1)) ^ g) + (t & 1)]      // row R = mu = g of slot 0, swizzled
+                                             : stg[NO * 4 * s + 4 * g + t];       // C[i, mu = g][state 4 s + t]
                         Bs[s * BROW + lane] = ci * w_f;                           // Atemp = distre * Ha        TB.f90:4378
                         Bs[s * BROW + 32 + lane] = ci * w_e;                      // Atemp = distre * En * Ha   TB.f90:4459
                         if (g == 0) {
-                            const double c8 = stg[NO * 4 * s + 32 + t];           // C[i, mu = 8][state]
+                            const double c8 = TM ? stg[8 * 16 + 4 * s + t]        // row 8: R & 7 = 0, no swizzle
+                                                 : stg[NO * 4 * s + 32 + t];     // C[i, mu = 8][state]
                             Bs[s * BROW + 64 + t] = c8 * w_f;
                             Bs[s * BROW + 68 + t] = c8 * w_e;
                         }
@@ -511,9 +552,9 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
                 // ===== consumer warps: row tiles warp, warp + NCW, ... of this sub-task =====
                 const int my_tiles = ntiles > warp ? (ntiles - warp + NCW - 1) / NCW : 0;
                 const bool fs = first == 0;
-                const int boff = slotcap * SLOT;
+                const int boff = slotcap * SLOTW;
                 constexpr int MTMAX = NCW == 8 ? 7 : 5;      // row tiles per warp (register budget)
-#define XTB_CASE(M) if constexpr (M <= MTMAX) { if (my_tiles == M) consume_subtask<NO, NCW, M, DBG>(sbuf, stage_doubles, boff, stages, full, bready, empty, rg, nchunks, nrows, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); }
+#define XTB_CASE(M) if constexpr (M <= MTMAX) { if (my_tiles == M) consume_subtask<NO, NCW, M, DBG, TM>(sbuf, stage_doubles, boff, stages, full, bready, empty, rg, nchunks, nrows, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); }
                 if (my_tiles == 0) consume_idle(stages, full, bready, empty, rg, nchunks, lane);
                 XTB_CASE(1) XTB_CASE(2) XTB_CASE(3) XTB_CASE(4) XTB_CASE(5) XTB_CASE(6) XTB_CASE(7)
 #undef XTB_CASE
@@ -684,10 +725,12 @@ int xtb_impl_prepare_occupations(xtb_ctx* c) {
     keep_kernel<<<1, 1024, 0, c->stream>>>(K, c->d_fe, c->d_Ei, c->f_cut, (int*)c->d_keep.p, (double*)c->d_wf.p,
                                            (double*)c->d_wfe.p, (int*)c->d_nkeep.p);
     XTB_LAUNCH_CHECK(c);
-    int nkeep = 0;
+    int nkeep = 0, last = -1;
     XTB_CUDA(c, cudaMemcpyAsync(&nkeep, c->d_nkeep.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (nkeep > 0) XTB_CUDA(c, cudaMemcpy(&last, (const int*)c->d_keep.p + (nkeep - 1), sizeof(int), cudaMemcpyDeviceToHost));
     c->k_kept = nkeep;
+    c->keep_prefix = nkeep == 0 || last == nkeep - 1;      // kept states are ascending and distinct: a prefix iff the last one is nkeep-1
     const int kpad = (nkeep + KC - 1) / KC * KC;
     if (kpad > nkeep) {
         pad_weights_kernel<<<1, KC, 0, c->stream>>>(nkeep, kpad, (double*)c->d_wf.p, (double*)c->d_wfe.p);
@@ -698,6 +741,37 @@ int xtb_impl_prepare_occupations(xtb_ctx* c) {
 }
 
 namespace {
+
+// tensor map of HaT (rows x states, states contiguous): boxes of 16 states x 9 rows, 128-byte swizzle; kept in global memory
+int ensure_tensor_map(xtb_ctx* c, long long nrows, long long nstates) {
+    if (c->tmap_for == (const void*)c->d_HaT && c->tmap_rows == nrows && c->tmap_states == nstates && c->d_tmap.p) return XTB_OK;
+    typedef CUresult (*encode_t)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                 const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_t enc = nullptr;
+    if (!enc) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) {
+            cudaGetLastError();
+            XTB_FAIL(c, XTB_ECUDA, "cuTensorMapEncodeTiled is not available from this driver");
+        }
+        enc = (encode_t)fn;
+    }
+    alignas(64) CUtensorMap tm;
+    const cuuint64_t dims[2] = {(cuuint64_t)nstates, (cuuint64_t)nrows};
+    const cuuint64_t strides[1] = {(cuuint64_t)nstates * 8};
+    const cuuint32_t box[2] = {(cuuint32_t)KC, 9};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)c->d_HaT, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) XTB_FAIL(c, XTB_ECUDA, "cuTensorMapEncodeTiled failed (%d): HaT %p, %lld rows x %lld states", (int)r, (const void*)c->d_HaT, nrows, nstates);
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_tmap, sizeof tm))) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_tmap.p, &tm, sizeof tm, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));      // `tm` is a stack object
+    c->tmap_for = (const void*)c->d_HaT; c->tmap_rows = nrows; c->tmap_states = nstates;
+    return XTB_OK;
+}
 
 template <int NO>
 int run_density(xtb_ctx* c) {
@@ -721,9 +795,19 @@ int run_density(xtb_ctx* c) {
         XTB_CUDA(c, cudaMemsetAsync(c->d_rhoE.p, 0, blk_bytes, c->stream));
     }
     bool use_dmma = (c->density_impl >= 1) && NO == 9 && nown > 0;
+    // state-minor eigenvectors on the device and the kept states a prefix: the tiles come straight from HaT (tensor-map TMA),
+    // no re-tiled copy.  XTB_DENSITY_TM=0 forces the Ct path (needs the Fortran-layout Ha: transposed on demand).
+    bool use_tm = use_dmma && c->density_impl == 1 && !c->density_dbg && c->density_ncw != 12 && c->d_HaT && c->keep_prefix && KC == 16;
+    if (const char* ev = getenv("XTB_DENSITY_TM")) { if (atoi(ev) == 0) use_tm = false; }
+    if (use_dmma && !use_tm && (rc = xtb_ensure_Ha_std(c))) return rc;
+    if (!use_dmma && nown > 0 && (rc = xtb_ensure_Ha_std(c))) return rc;
+    if (use_tm) {
+        if ((rc = ensure_tensor_map(c, N, c->K))) return rc;
+        XTB_T0(c, 7);
+    }
     if (use_dmma) {
-        if ((rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)kpad * N + 1024))) return rc;
-        if (nchunks > 0) {
+        if (!use_tm && (rc = xtb_reserve(c, c->d_Ct, sizeof(double) * (size_t)kpad * N + 1024))) return rc;
+        if (nchunks > 0 && !use_tm) {
             dim3 grid(nchunks, (na + CT_AT - 1) / CT_AT);
             const int* need = nullptr;
             if (nown < na) {      // re-tile only what the owned atoms read (own rows + halo)
@@ -739,7 +823,7 @@ int run_density(xtb_ctx* c) {
             XTB_LAUNCH_CHECK(c);
             XTB_T1(c, 16);
         }
-        XTB_T0(c, 7);             // the contraction kernel alone (stage 7)
+        if (!use_tm) XTB_T0(c, 7);             // the contraction kernel alone (stage 7)
         if (c->density_impl == 2) {
             // ---- two column atoms per CTA (density_pair.cuh) ----
             const int gcap = 2 * c->max_nn + 4;
@@ -791,8 +875,8 @@ int run_density(xtb_ctx* c) {
         if (slotcap > MTMAX * NCW * 8 / NO) slotcap = MTMAX * NCW * 8 / NO;     // rows must fit MTMAX tiles per warp
         if (slotcap > c->max_nn + 1) slotcap = c->max_nn + 1;
         if (slotcap < 2) slotcap = 2;
-        auto stage_bytes = [](int sc) { return (size_t)(sc * SLOT + KS * BROW + 2 * KC) * 8; };
-        auto fixed_bytes = [&](int sc, int st) { return (size_t)4 * 8 * st + sizeof(int) * (2 * (size_t)sc + c->cap) + 64; };
+        auto stage_bytes = [&](int sc) { return use_tm ? (size_t)stage_doubles_tm(sc) * 8 : (size_t)(sc * SLOT + KS * BROW + 2 * KC) * 8; };
+        auto fixed_bytes = [&](int sc, int st) { return (size_t)4 * 8 * st + sizeof(int) * (2 * (size_t)sc + c->cap) + 64 + (use_tm ? 1024 : 0); };
         const size_t budget = 227 * 1024 - 1024;
         int stages = 4;
         while (stages > 2 && stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages) > budget) {
@@ -814,7 +898,8 @@ int run_density(xtb_ctx* c) {
         long long* a_prog = (long long*)c->d_prog.p;
         const int* a_sz = (const int*)c->d_nn_size.p; const int* a_li = (const int*)c->d_nn_list.p;
         const signed char* a_own = (const signed char*)c->d_own.p; const int* a_rp = (const int*)c->d_rowptr.p;
-        const double* a_ct = (const double*)c->d_Ct.p; const double* a_wf = (const double*)c->d_wf.p; const double* a_wfe = (const double*)c->d_wfe.p;
+        const double* a_ct = use_tm ? (const double*)c->d_tmap.p : (const double*)c->d_Ct.p;      // TM: the tensor map travels in the Ct slot
+        const double* a_wf = (const double*)c->d_wf.p; const double* a_wfe = (const double*)c->d_wfe.p;
         double* a_rho = (double*)c->d_rho.p; double* a_rhoE = (double*)c->d_rhoE.p;
         void* args[] = {&a_na, &a_a0, &a_a1, &a_cap, &a_slot, &a_st, &a_nch, &a_dbg, &a_ms, &a_lead, &a_split, &a_prog, &a_sz, &a_li, &a_own, &a_rp,
                         &a_ct, &a_wf, &a_wfe, &a_rho, &a_rhoE};
@@ -834,7 +919,10 @@ int run_density(xtb_ctx* c) {
             const int v = atoi(ev);
             tail_from = (split == 1 && v >= 0 && v < nown) ? v : nown;
         }
-#define XTB_LAUNCH_ALL if (c->density_dbg) XTB_LAUNCH(8, true) else if (NCW == 12) XTB_LAUNCH(12, false) else XTB_LAUNCH(8, false)
+#define XTB_LAUNCH_TM { auto kern = density_dmma_kernel<9, 8, false, true>; \
+        XTB_CUDA(c, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        XTB_CUDA(c, cudaLaunchKernel((const void*)kern, dim3(grid), dim3((8 + 1 + NPROD) * 32), args, smem, c->stream)); }
+#define XTB_LAUNCH_ALL if (use_tm) XTB_LAUNCH_TM else if (c->density_dbg) XTB_LAUNCH(8, true) else if (NCW == 12) XTB_LAUNCH(12, false) else XTB_LAUNCH(8, false)
         if (tail_from > 0) {
             a_a1 = c->a0 + tail_from;
             grid = c->sm_count < tail_from * split ? c->sm_count : tail_from * split;
@@ -849,8 +937,9 @@ int run_density(xtb_ctx* c) {
             XTB_LAUNCH_CHECK(c);
         }
 #undef XTB_LAUNCH_ALL
+#undef XTB_LAUNCH_TM
 #undef XTB_LAUNCH
-        c->density_slotcap = slotcap; c->density_stages = stages;
+        c->density_slotcap = slotcap; c->density_stages = stages; c->density_tm = use_tm ? 1 : 0;
         }
     } else if (nown > 0 && NO <= 4 && c->density_impl >= 1) {
         if constexpr (NO <= 4) {

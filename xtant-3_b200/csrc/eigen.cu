@@ -13,6 +13,7 @@
 // The libraries are bound at run time (dlopen), so libxtb_b200.so itself has no link-time dependency on them; when they
 // are missing xtb_eigensolve reports XTB_ESTATE and the caller keeps using xtb_set_eigen with host LAPACK eigenvectors.
 #include "xtb_ctx.h"
+#include <cstdlib>
 #include <dlfcn.h>
 
 namespace {
@@ -101,6 +102,21 @@ __global__ void loewdin_flag_kernel(long long N, const double* __restrict__ w, i
     __syncthreads();
     if (threadIdx.x == 0) *fix = any;
 }
+// out(r, n) = in(n, r): 32 x 32 tiles through shared memory, both sides coalesced.  in: ld_in = rows of `in` (its fast index)
+__global__ void __launch_bounds__(256) transpose_kernel(long long n_fast_in, long long n_slow_in, const double* __restrict__ in, double* __restrict__ out) {
+    __shared__ double tile[32][33];
+    const long long f0 = 32LL * blockIdx.x, s0 = 32LL * blockIdx.y;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (int yy = ty; yy < 32; yy += 8) {
+        const long long f = f0 + tx, sl = s0 + yy;
+        tile[yy][tx] = (f < n_fast_in && sl < n_slow_in) ? in[f + n_fast_in * sl] : 0.0;
+    }
+    __syncthreads();
+    for (int yy = ty; yy < 32; yy += 8) {
+        const long long sl = s0 + tx, f = f0 + yy;          // out fast index = in slow index
+        if (sl < n_slow_in && f < n_fast_in) out[sl + n_slow_in * f] = tile[tx][yy];
+    }
+}
 __global__ void chop_kernel(long long n, double* __restrict__ A, double eps) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
         if (fabs(A[i]) < eps) A[i] = 0.0;
@@ -123,6 +139,22 @@ int syevd(xtb_ctx* c, int n, double* A, double* W, std::string what) {
 }
 
 }  // namespace
+
+// The Fortran-layout eigenvectors Ha(N,N) (column n = state n) on the device.  When the context only holds the state-minor
+// copy HaT (xtb_eigensolve with 9 orbitals per atom, xtb_set_eigen_device_t) it is transposed into own_Ha here, once.
+int xtb_ensure_Ha_std(xtb_ctx* c) {
+    if (c->d_Ha) return XTB_OK;
+    if (!c->d_HaT) XTB_FAIL(c, XTB_ESTATE, "no eigenvectors on the device");
+    const long long N = (long long)c->na * c->n_orb, K = c->K > 0 ? c->K : N;
+    int rc;
+    if ((rc = xtb_reserve(c, c->own_Ha, sizeof(double) * (size_t)N * K))) return rc;
+    // HaT: fast index = state (K of them), slow = row (N).  Ha: fast = row, slow = state.
+    const dim3 grid((unsigned)((K + 31) / 32), (unsigned)((N + 31) / 32));
+    transpose_kernel<<<grid, 256, 0, c->stream>>>(K, N, c->d_HaT, (double*)c->own_Ha.p);
+    XTB_LAUNCH_CHECK(c);
+    c->d_Ha = (const double*)c->own_Ha.p;
+    return XTB_OK;
+}
 
 void xtb_release_lib_handles(xtb_ctx* c) {
     if (c->h_cusolver && g_libs.sv_destroy) g_libs.sv_destroy(c->h_cusolver);
@@ -160,6 +192,7 @@ int xtb_impl_eigensolve(xtb_ctx* c) {
     XTB_T0(c, 8);
     double* Ha = (double*)c->own_Ha.p;
     double* Ei = (double*)c->own_Ei.p;
+    bool have_std = true;
     if (ortho) {      // TB_Pettifor.f90:1455: the assembled matrix is diagonalised in place
         XTB_CUDA(c, cudaMemcpyAsync(Ha, c->d_H.p, sizeof(double) * nn, cudaMemcpyDeviceToDevice, c->stream));
         rc = syevd(c, n, Ha, Ei, "H");
@@ -187,14 +220,28 @@ int xtb_impl_eigensolve(xtb_ctx* c) {
         }
         rc = syevd(c, n, Ha, Ei, "H'");
         if (rc) return rc;                                     // TB_NRL.f90:409
-        if (L.bl_dgemm(c->h_cublas, OP_N, OP_N, n, n, n, &one, X, n, Ha, n, &zero, T, n) != 0)      // Ha = X V   :421
-            XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(X V) failed");
-        // the eigenvectors now live in T: swap the roles of the two buffers
-        DevBuf tmp = c->own_Ha; c->own_Ha = c->d_eig_T; c->d_eig_T = tmp;
+        // Ha = X V (:421).  With 9 orbitals per atom the product is written state-minor, HaT = V^T X^T (the same GEMM with
+        // both operands transposed, same cost): the layout the density kernel streams through its tensor map, so no re-tiled
+        // copy is ever made.  The Fortran-layout Ha is derived on demand (xtb_ensure_Ha_std).  XTB_EIGEN_STATE_MINOR=0: as before.
+        bool state_minor = c->n_orb == 9;
+        if (const char* ev = getenv("XTB_EIGEN_STATE_MINOR")) state_minor = state_minor && atoi(ev) != 0;
+        if (state_minor) {
+            if (L.bl_dgemm(c->h_cublas, OP_T, OP_T, n, n, n, &one, Ha, n, X, n, &zero, T, n) != 0)
+                XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(V^T X^T) failed");
+            DevBuf tmp = c->own_HaT; c->own_HaT = c->d_eig_T; c->d_eig_T = tmp;      // T now holds HaT: it becomes own_HaT
+            have_std = false;
+        } else {
+            if (L.bl_dgemm(c->h_cublas, OP_N, OP_N, n, n, n, &one, X, n, Ha, n, &zero, T, n) != 0)
+                XTB_FAIL(c, XTB_ECUDA, "cublasDgemm(X V) failed");
+            // the eigenvectors now live in T: swap the roles of the two buffers
+            DevBuf tmp = c->own_Ha; c->own_Ha = c->d_eig_T; c->d_eig_T = tmp;
+        }
     }
     XTB_T1(c, 8);
     if ((rc = xtb_stage_finish(c))) return rc;
-    c->d_Ha = (const double*)c->own_Ha.p; c->d_Ei = (const double*)c->own_Ei.p; c->d_fe = (const double*)c->own_fe.p;
+    c->d_Ha = have_std ? (const double*)c->own_Ha.p : nullptr;
+    c->d_HaT = have_std ? nullptr : (const double*)c->own_HaT.p;
+    c->d_Ei = (const double*)c->own_Ei.p; c->d_fe = (const double*)c->own_fe.p;
     c->K = N;
     c->have_eigvec = true;
     c->have_eigen = false;          // occupations still to come (xtb_set_occupations)

@@ -314,7 +314,7 @@ static int step_body(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool ste
         XTB_CUDA(c, cudaMemcpyAsync(c->h_meta + 8, c->d_fermi.p, sizeof(double) * 4, cudaMemcpyDeviceToHost, c->stream));
         if ((rc = xtb_impl_prepare_occupations(c))) return rc;    // the kept-state count sizes the density launches
     } else if (io && io->fe) {
-        if (!c->d_Ha || !c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_step: occupations given but no eigenvectors on the device");
+        if ((!c->d_Ha && !c->d_HaT) || !c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_step: occupations given but no eigenvectors on the device");
         if ((rc = xtb_reserve(c, c->own_fe, sizeof(double) * N))) return rc;
         XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, io->fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
         c->d_fe = (const double*)c->own_fe.p; c->K = (long long)N;
@@ -376,7 +376,7 @@ static GraphKey make_key(const xtb_ctx* c, unsigned flags, const xtb_step_io* io
     k.flags = flags; k.iomask = io_mask(io);
     k.na = c->na; k.cap = c->cap; k.max_nn = c->max_nn; k.tb = c->tb; k.n_orb = c->n_orb; k.a0 = c->a0; k.a1 = c->a1; k.n_kinds = c->n_kinds;
     k.blk_cap = c->blk_cap; k.k_kept = c->k_kept; k.K = c->K; k.alloc_epoch = c->alloc_epoch;
-    k.Ha = c->d_Ha; k.Ei = c->d_Ei; k.fe = c->d_fe; k.stream = c->stream; k.rm = c->rm; k.f_cut = c->f_cut;
+    k.Ha = c->d_Ha ? (const void*)c->d_Ha : (const void*)c->d_HaT; k.Ei = c->d_Ei; k.fe = c->d_fe; k.stream = c->stream; k.rm = c->rm; k.f_cut = c->f_cut;
     k.rep = !c->h_pet_rep.empty(); k.wall = !c->h_wall.empty();
     return k;
 }

@@ -4,6 +4,7 @@
 #include "xtb_ctx.h"
 #include "dftb_device.cuh"
 #include <cstdlib>
+#include <cstdint>
 #include <cstring>
 #include <new>
 
@@ -152,7 +153,7 @@ int xtb_destroy(xtb_ctx* c) {
     xtb_release_lib_handles(c);
     DevBuf* all[] = {&c->d_params, &c->d_koa, &c->d_S, &c->d_nn_size, &c->d_nn_list, &c->d_nn_dist, &c->d_nn_dist_s, &c->d_rev, &c->d_own,
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
-                     &c->own_Ei, &c->own_fe, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
+                     &c->own_Ei, &c->own_fe, &c->own_HaT, &c->d_tmap, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
                      &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
                      &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep,
                      &c->d_halo_tr, &c->d_halo_cnt, &c->d_halo_slots, &c->d_halo_send, &c->d_halo_recv, &c->d_wall_params, &c->d_Ewall_at, &c->d_Ewall,
@@ -457,7 +458,7 @@ int xtb_set_eigen_device(xtb_ctx* c, const double* dHa, const double* dEi, const
     if (!dHa || !dEi || !dfe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen_device: null pointer");
     if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_eigen_device: no system set");
     cudaSetDevice(c->device);
-    c->d_Ha = dHa; c->d_Ei = dEi; c->d_fe = dfe;
+    c->d_Ha = dHa; c->d_HaT = nullptr; c->d_Ei = dEi; c->d_fe = dfe;
     c->have_eigvec = false;
     c->K = (long long)c->na * c->n_orb;
     c->have_eigen = true; c->have_density = false; c->have_keep = false;
@@ -469,6 +470,19 @@ int xtb_cutoff(xtb_ctx* c, double* rm) {
     if (c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_cutoff: set the TB parameters first");
     *rm = xtb_default_cutoff(c);
     return XTB_OK;
+}
+
+int xtb_set_eigen_device_t(xtb_ctx* c, const double* dHaT, const double* dEi, const double* dfe) {
+    if (!c) return XTB_EINVAL;
+    if (!dHaT || !dEi || !dfe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen_device_t: null pointer");
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_set_eigen_device_t: no system set");
+    if (((uintptr_t)dHaT & 15) != 0) XTB_FAIL(c, XTB_EINVAL, "xtb_set_eigen_device_t: HaT must be 16-byte aligned");
+    cudaSetDevice(c->device);
+    c->d_HaT = dHaT; c->d_Ha = nullptr; c->d_Ei = dEi; c->d_fe = dfe;
+    c->have_eigvec = false;
+    c->K = (long long)c->na * c->n_orb;
+    c->have_eigen = true; c->have_density = false; c->have_keep = false;
+    return xtb_impl_prepare_occupations(c);
 }
 
 int xtb_set_eigen(xtb_ctx* c, const double* Ha, const double* Ei, const double* fe) {
@@ -486,7 +500,7 @@ int xtb_set_eigen(xtb_ctx* c, const double* Ha, const double* Ei, const double* 
     if (fe) XTB_CUDA(c, cudaMemcpyAsync(c->own_fe.p, fe, sizeof(double) * N, cudaMemcpyHostToDevice, c->stream));
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     if (!fe) {      // eigenvectors and eigenvalues now, occupations later (xtb_set_occupations / xtb_fermi_occupations)
-        c->d_Ha = (const double*)c->own_Ha.p; c->d_Ei = (const double*)c->own_Ei.p; c->d_fe = nullptr;
+        c->d_Ha = (const double*)c->own_Ha.p; c->d_HaT = nullptr; c->d_Ei = (const double*)c->own_Ei.p; c->d_fe = nullptr;
         c->K = (long long)N;
         c->have_eigvec = false; c->have_eigen = false; c->have_density = false; c->have_keep = false;
         return XTB_OK;
@@ -504,7 +518,10 @@ int xtb_eigensolve(xtb_ctx* c, double* Ei, double* eigen_S, double* Ha) {
     const size_t N = (size_t)c->na * c->n_orb;
     if (Ei) XTB_CUDA(c, cudaMemcpyAsync(Ei, c->own_Ei.p, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
     if (eigen_S && c->tb != XTB_TB_PETTIFOR) XTB_CUDA(c, cudaMemcpyAsync(eigen_S, c->d_eigS.p, sizeof(double) * N, cudaMemcpyDeviceToHost, c->stream));
-    if (Ha) XTB_CUDA(c, cudaMemcpyAsync(Ha, c->own_Ha.p, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
+    if (Ha) {
+        if ((rc = xtb_ensure_Ha_std(c))) return rc;
+        XTB_CUDA(c, cudaMemcpyAsync(Ha, c->d_Ha, sizeof(double) * N * N, cudaMemcpyDeviceToHost, c->stream));
+    }
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     return XTB_OK;
 }
@@ -522,7 +539,7 @@ int xtb_get_eigenvalues(xtb_ctx* c, double* Ei) {
 int xtb_set_occupations(xtb_ctx* c, const double* fe) {
     if (!c) return XTB_EINVAL;
     if (!fe) XTB_FAIL(c, XTB_EINVAL, "xtb_set_occupations: null pointer");
-    if (!c->d_Ha || !c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_set_occupations: no eigenvectors on the device (xtb_eigensolve, xtb_set_eigen or xtb_set_eigen_device first)");
+    if ((!c->d_Ha && !c->d_HaT) || !c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_set_occupations: no eigenvectors on the device (xtb_eigensolve, xtb_set_eigen or xtb_set_eigen_device first)");
     cudaSetDevice(c->device);
     const size_t N = (size_t)c->na * c->n_orb;
     int rc;
@@ -613,8 +630,9 @@ int xtb_pressure(xtb_ctx* c, double* SCforce_att) {
 // ---- nonadiabatic coupling ----
 int xtb_save_eigen_prev(xtb_ctx* c) {
     if (!c) return XTB_EINVAL;
-    if (!c->d_Ha) XTB_FAIL(c, XTB_ESTATE, "xtb_save_eigen_prev: no eigenvectors on the device");
+    if (!c->d_Ha && !c->d_HaT) XTB_FAIL(c, XTB_ESTATE, "xtb_save_eigen_prev: no eigenvectors on the device");
     cudaSetDevice(c->device);
+    { int rc0 = xtb_ensure_Ha_std(c); if (rc0) return rc0; }
     const size_t N = (size_t)c->na * c->n_orb;
     int rc;
     if ((rc = xtb_reserve(c, c->d_Ha0, sizeof(double) * N * N))) return rc;
@@ -641,7 +659,7 @@ int xtb_set_eigen_prev(xtb_ctx* c, const double* Ha0) {
 int xtb_coupling(xtb_ctx* c, int kind_M, double* Mij) {
     if (!c) return XTB_EINVAL;
     cudaSetDevice(c->device);
-    if (!c->d_Ha) XTB_FAIL(c, XTB_ESTATE, "xtb_coupling: no eigenvectors on the device (xtb_set_eigen / xtb_eigensolve first)");
+    if (!c->d_Ha && !c->d_HaT) XTB_FAIL(c, XTB_ESTATE, "xtb_coupling: no eigenvectors on the device (xtb_set_eigen / xtb_eigensolve first)");
     if (!c->have_Ha0) XTB_FAIL(c, XTB_ESTATE, "xtb_coupling: no previous-step eigenvectors (xtb_save_eigen_prev / xtb_set_eigen_prev first)");
     if (c->tb != XTB_TB_PETTIFOR) {
         if (!c->have_blocks) XTB_FAIL(c, XTB_ESTATE, "xtb_coupling: no overlap blocks on the device (xtb_assemble_HS first)");
@@ -820,6 +838,7 @@ long long xtb_counter(const xtb_ctx* c, int which) {
             return n;
         }
         case 16: return c->graph_captures;
+        case 17: return c->density_tm;
         case 12: return (long long)c->xchg_bytes[XTB_XCHG_HS];
         case 13: return (long long)c->xchg_bytes[XTB_XCHG_RHO];
         case 14: return c->halo_send_blocks;

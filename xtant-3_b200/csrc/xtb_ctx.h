@@ -72,6 +72,13 @@ struct xtb_ctx {
     bool have_HS = false, have_blocks = false;
     // eigen
     const double* d_Ha = nullptr; const double* d_Ei = nullptr; const double* d_fe = nullptr;
+    // state-minor copy of the eigenvectors HaT[row r][state n] (states contiguous): what the 9-orbital density kernel streams
+    // straight through tensor-map TMA.  Either layout may be the primary one; the other is made on demand (eigen.cu).
+    const double* d_HaT = nullptr;
+    DevBuf own_HaT, d_tmap;
+    const void* tmap_for = nullptr; long long tmap_rows = 0, tmap_states = 0;
+    bool keep_prefix = false;   // the kept states are 0 .. k_kept-1
+    int density_tm = 0;         // the last density launch read HaT through the tensor map
     DevBuf own_Ha, own_Ei, own_fe;
     long long K = 0;            // number of states (columns of Ha)
     bool have_eigen = false;
@@ -205,6 +212,7 @@ int xtb_impl_coupling(xtb_ctx* c, int kind_M);      // coupling.cu
 int xtb_rows_by_state(xtb_ctx* c, const double* Ha, long long K, double* X);      // density.cu
 int xtb_blas_dgemm(xtb_ctx* c, bool ta, bool tb, int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* Cm, int ldc);
 void xtb_release_lib_handles(xtb_ctx* c);   // eigen.cu
+int xtb_ensure_Ha_std(xtb_ctx* c);          // eigen.cu: the Fortran-layout Ha(N,N) on the device (transposed from HaT if that is all there is)
 int xtb_impl_eigensolve(xtb_ctx* c);        // eigen.cu: Loewdin + Dsyevd + back-transform on the device-resident H, S
 int xtb_impl_dftb_assemble(xtb_ctx* c, bool dense);
 int xtb_impl_dftb_forces(xtb_ctx* c);
