@@ -303,6 +303,10 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
                                                 uint64_t* full, uint64_t* bready, uint64_t* empty, Ring& rg, int nchunks,
                                                 int nrows, int warp, int lane, const int* slot_q, size_t b0i,
                                                 bool first_subtask, int dbg, double* __restrict__ rho, double* __restrict__ rhoE) {
+    // (TM: the four rows of a half warp carry the swizzle keys 0..3, whose sixteen-byte pieces pair up on four positions of the
+    // 128-byte line, so a fragment load takes four wavefronts instead of two -- ncu: 3.6e9 bank-conflict wavefronts per launch.
+    // Giving the half warps the rows 0,2,4,6 / 1,3,5,7 removes them and was measured SLOWER, 69.7 against 69.1 ms: shared
+    // memory is at a quarter of its wavefront rate either way, the allocation of the loop decides.)
     const int g = lane >> 2, t = lane & 3;
     double acc0[MT][2], acc1[MT][2], p8f[MT], p8e[MT];
     int off[MT];
