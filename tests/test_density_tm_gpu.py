@@ -65,6 +65,30 @@ def test_tensor_map_path_is_bit_identical(name, wk, api, monkeypatch):
     c1.close(); c2.close()
 
 
+def test_odd_orbital_count_falls_back(wk, api):
+    """N = 9 na odd: the row pitch of HaT (N * 8 bytes) is not a multiple of 16, a tensor map cannot describe it; the kernel
+    then takes the re-tiled path on a transposed copy -- same results as the Fortran-layout input"""
+    import torch
+    w0 = wk.au_fcc((3, 3, 3), sigma=0.1, seed=3)
+    wl = wk._wl("au107", "nrl", "Au", w0["S"][:-1], w0["supce"], 11, 0.1)
+    N = wl["na"] * 9
+    assert N % 2 == 1
+    C_, E, fe = wk.synthetic_eigen(N, seed=13)
+    c1 = api.TBContext(0); c1.set_workload(wl); c1.get_near_neighbours_device(); c1.set_eigen(C_, E, fe); c1.density()
+    HaT = torch.from_numpy(np.ascontiguousarray(np.asarray(C_))).cuda()
+    dE = torch.from_numpy(np.ascontiguousarray(E)).cuda(); dfe = torch.from_numpy(np.ascontiguousarray(fe)).cuda()
+    torch.cuda.synchronize()
+    c2 = api.TBContext(0); c2.set_workload(wl); c2.get_near_neighbours_device()
+    c2.set_eigen_device_t(HaT.data_ptr(), dE.data_ptr(), dfe.data_ptr()); c2.density()
+    a, b = _blocks(c1), _blocks(c2)
+    assert c2.counter(17) == 0 and np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    # and the on-device eigensolve (state-minor output) works for it as well
+    c2.assemble_HS(to_host=False); Ei = c2.eigensolve()[0]
+    fe2, mu = wk.occupations(Ei, wl["n_electrons"], wl["Te_eV"]); c2.set_occupations(fe2); c2.density()
+    assert c2.counter(17) == 0 and np.isfinite(c2.forces()).all()
+    c1.close(); c2.close()
+
+
 def test_eigensolve_leaves_state_minor_eigenvectors(wk, orc, api):
     """xtb_eigensolve (9 orbitals) writes HaT with its last GEMM; the density kernel streams it through the tensor map; the
     Fortran-layout Ha handed back to the host is the transpose made on demand"""

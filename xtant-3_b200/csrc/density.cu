@@ -801,7 +801,8 @@ int run_density(xtb_ctx* c) {
     bool use_dmma = (c->density_impl >= 1) && NO == 9 && nown > 0;
     // state-minor eigenvectors on the device and the kept states a prefix: the tiles come straight from HaT (tensor-map TMA),
     // no re-tiled copy.  XTB_DENSITY_TM=0 forces the Ct path (needs the Fortran-layout Ha: transposed on demand).
-    bool use_tm = use_dmma && c->density_impl == 1 && !c->density_dbg && c->density_ncw != 12 && c->d_HaT && c->keep_prefix && KC == 16;
+    bool use_tm = use_dmma && c->density_impl == 1 && !c->density_dbg && c->density_ncw != 12 && c->d_HaT && c->keep_prefix && KC == 16 &&
+                  (c->K % 2) == 0;       // the row pitch of the tensor map (K * 8 bytes) must be a multiple of 16
     if (const char* ev = getenv("XTB_DENSITY_TM")) { if (atoi(ev) == 0) use_tm = false; }
     if (use_dmma && !use_tm && (rc = xtb_ensure_Ha_std(c))) return rc;
     if (!use_dmma && nown > 0 && (rc = xtb_ensure_Ha_std(c))) return rc;
