@@ -94,6 +94,25 @@ typedef struct xtb_wall_pair {
     double dd;    /* [A] cut-off smoothing width */
 } xtb_wall_pair;
 
+/* class(TB_vdW), Objects.f90:43-46 (parent: d0_cut, dd_cut) with its three usable extensions in one record:
+ *   XTB_VDW_GIRIFALCO  type(TB_vdW_Girifalco) :302-328, file order read_vdW_Girifalco_TB (Read_input_data.f90:2392-2574):
+ *                      C12 / r^12 - C6 / r^6 for dsm <= r <= dm, cubic a r^3 + b r^2 + c r + d on (dm, d_cut], quintic
+ *                      as r^5 + bs r^4 + cs r^3 + ds r^2 + es r + fs on [ds_cut, dsm), zero outside [ds_cut, d_cut];
+ *                      the reader sets d0_cut = d_cut, dd_cut = 0 (:1799-1800)
+ *   XTB_VDW_LJ_CUT     type(TB_vdW_LJ_cut) :336-343: eps ((r0/r)^n - 2) (r0/r)^n times the short- and long-range Fermi cut-offs
+ *   XTB_VDW_ILJ_CUT    type(TB_vdW_ILJ_cut) :346-354: eps (m/(n-m) (r0/r)^n - n/(n-m) (r0/r)^m) times the same cut-offs
+ * (TB_vdW_Dumitrica is marked "UNFINISHED, DO NOT USE" in the reference and returns zero: not offered.) */
+#define XTB_VDW_GIRIFALCO 1
+#define XTB_VDW_LJ_CUT    2
+#define XTB_VDW_ILJ_CUT   3
+typedef struct xtb_vdw_pair {
+    double d0_cut, dd_cut;                       /* [A] long-range cut-off radius and width (parent type) */
+    double C12, C6, dm, d_cut, a, b, c, d;       /* Girifalco */
+    double dsm, ds_cut, as, bs, cs, ds, es, fs;
+    double eps, r0, n, m;                        /* LJ_cut (m unused) / ILJ_cut */
+    double d0_short, dd_short;                   /* [A] short-range cut-off radius and width */
+} xtb_vdw_pair;
+
 typedef struct xtb_ctx xtb_ctx;
 
 /* ---- life cycle ------------------------------------------------------------------- */
@@ -231,6 +250,23 @@ int  xtb_wall_energy  (xtb_ctx*, double* E_wall, double* Epot);
 int  xtb_wall_forces  (xtb_ctx*, double* F_wall);
 int  xtb_wall_pressure(xtb_ctx*, double SCforce_wall[9]);
 
+/* ---- SURVEY.md 8f item 2, third part: the van der Waals pair term (class TB_vdW; Van_der_Waals.f90, dispatch vdW_forces
+ *      TB.f90:3599-3633 / vdW_s TB.f90:4017-4035).  Unlike every other term it does NOT use the neighbour list: it sums over
+ *      ALL atom pairs in (2Nx+1)(2Ny+1)(2Nz+1) images of the supercell, the image counts from get_mirror_cell_num
+ *      (Van_der_Waals.f90:132-157: R_cut = max(TB cut-off, max d0_cut + 10 max dd_cut), images until n |supce row| >= 2 R_cut,
+ *      at least one per axis).  p[(koa1-1) + n_kinds*(koa2-1)] = TB_Waals(koa1, koa2); n_kinds = 0 / p = NULL removes the term
+ *      (a missing file or an unrecognised class line -- the shipped 'Girifalco:exclude' -- "proceeds without van der Waals
+ *      forces", Read_input_data.f90:1777-1784).  Needs only xtb_set_system.
+ *      xtb_vdw_image_cells  get_mirror_cell_num: N[3], R_cut [A]
+ *      xtb_vdw_energy       get_vdW_s     (Van_der_Waals.f90:158-250): E_vdW [eV]; Epot(na) = the per-atom halves
+ *      xtb_vdw_forces       Construct_B + d_Forces_s (:251-421, TB.f90:3638-3781): the term ADDED to forces%rep, F_vdw(3,na)
+ *      xtb_vdw_pressure     d_Forces_Pressure (TB.f90:3785-3848): the term ADDED to Scell%SCforce%rep(3,3) */
+int  xtb_set_params_vdw(xtb_ctx*, int kind /*XTB_VDW_**/, int n_kinds, const xtb_vdw_pair* p);
+int  xtb_vdw_image_cells(xtb_ctx*, int N[3], double* R_cut);
+int  xtb_vdw_energy  (xtb_ctx*, double* E_vdw, double* Epot);
+int  xtb_vdw_forces  (xtb_ctx*, double* F_vdw);
+int  xtb_vdw_pressure(xtb_ctx*, double SCforce_vdw[9]);
+
 /* ---- Fermi occupations on the device (between the eigensolve and S3; lets a step stay on the device):
  *      Electron_Fixed_Te (Electron_tools.f90:2660-2706: bisection of mu at fixed Te until |N(mu) - Ne| <= 1e-12 Ne) +
  *      set_Fermi (:1913-1969), spin-degenerate (f_norm = 2).  Uses the eigenvalues on the device (xtb_eigensolve or
@@ -247,6 +283,7 @@ int  xtb_fermi_occupations(xtb_ctx*, double n_electrons, double Te_eV, double* f
 #define XTB_FORCE_ATT   1u   /* XTB_BUF_FORCES  (xtb_forces) */
 #define XTB_FORCE_REP   2u   /* XTB_BUF_FREP    (xtb_repulsive_forces) */
 #define XTB_FORCE_WALL  4u   /* XTB_BUF_FWALL   (xtb_wall_forces) */
+#define XTB_FORCE_VDW   8u   /* XTB_BUF_FVDW    (xtb_vdw_forces) */
 int  xtb_md_set_velocities(xtb_ctx*, const double* SV /*[3*na] relative velocities [1/fs]; NULL = zero*/);
 int  xtb_md_half_step(xtb_ctx*, int ind, double dt_fs, const double* mass_kg, const double* Vsupce, unsigned force_terms);
 int  xtb_md_get_state(xtb_ctx*, double* S, double* SV, double* E_kin /*[eV]*/, const double* mass_kg /*for E_kin*/);
@@ -287,7 +324,7 @@ int  xtb_allreduce_scforce(xtb_ctx*, double SCforce_att[9] /*or NULL*/);
 #define XTB_STEP_DENSITY      8u    /* rho, rho_E [+ halo exchange + mirror] */
 #define XTB_STEP_FORCES      16u    /* attractive forces [+ all-gather] */
 #define XTB_STEP_PRESSURE    32u    /* supercell force [+ all-reduce] (also of the pair terms when XTB_STEP_PAIR_TERMS) */
-#define XTB_STEP_PAIR_TERMS  64u    /* repulsive part of the Pettifor branch and / or the short-range wall, whichever is set */
+#define XTB_STEP_PAIR_TERMS  64u    /* repulsive part of the Pettifor branch, the short-range wall and the van der Waals term, whichever are set */
 #define XTB_STEP_NO_DENSE   128u    /* with XTB_STEP_HS: block stores only */
 #define XTB_STEP_GRAPH      256u    /* single GPU, no XTB_STEP_EIGEN / new occupations: once a steady step with the same flags has
                                        run, replay its launch sequence as ONE CUDA graph (launch-bound small systems); host
@@ -307,6 +344,7 @@ typedef struct xtb_step_io {
     double* SCforce_att;      /* out [9] */
     double* E_rep;  double* F_rep;  double* SCforce_rep;      /* out: Pettifor repulsive part */
     double* E_wall; double* F_wall; double* SCforce_wall;     /* out: short-range wall */
+    double* E_vdw;  double* F_vdw;  double* SCforce_vdw;      /* out: van der Waals term */
 } xtb_step_io;
 int  xtb_step(xtb_ctx*, unsigned flags, const xtb_step_io* io);
 
@@ -341,6 +379,7 @@ int  xtb_coupling       (xtb_ctx*, int kind_M, double* Mij);
 #define XTB_BUF_VEL     16   /* (3,na) relative velocities SV */
 #define XTB_BUF_EI      17   /* (N) eigenvalues */
 #define XTB_BUF_FE      18   /* (N) occupations */
+#define XTB_BUF_FVDW    19   /* (3,na) van der Waals forces */
 int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
  *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,

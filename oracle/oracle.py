@@ -35,7 +35,7 @@ _pi = C.POINTER(C.c_int)
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    src = [os.path.join(_HERE, f) for f in ("xtant_oracle.c", "sk_tables.h", "pettifor_oracle.c", "dftb_oracle.c", "wall_oracle.c")]
+    src = [os.path.join(_HERE, f) for f in ("xtant_oracle.c", "sk_tables.h", "pettifor_oracle.c", "dftb_oracle.c", "wall_oracle.c", "vdw_oracle.c")]
     src = [s for s in src if os.path.exists(s)]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
@@ -54,6 +54,9 @@ def lib():
         _LIB.orc_pet_erep.restype = C.c_double
         _LIB.orc_wall_energy.restype = C.c_double
         _LIB.orc_fermi.restype = C.c_double
+        _LIB.orc_vdw_energy.restype = C.c_double
+        _LIB.orc_vdw_V.restype = C.c_double
+        _LIB.orc_vdw_dV.restype = C.c_double
     return _LIB
 
 
@@ -87,6 +90,8 @@ def cutoff_radius(wl):
         if wl.get("rep_params"):                       # repulsive part longer than the attractive: Atomic_tools.f90:609-613
             rm = max(rm, max(p["dm"] for p in wl["rep_params"]))
         return rm
+    if wl["tb"] == "dftb":                             # :588-591
+        return max(p["rcut"] for p in wl["params"]) + 10.0 * max(p["d"] for p in wl["params"])
     raise ValueError(wl["tb"])
 
 
@@ -183,6 +188,70 @@ def wall_params_array(params):
     for i, d in enumerate(params):
         arr[i] = _abi.WallPair(float(d["C"]), float(d["r0"]), float(d["d0"]), float(d["dd"]))
     return arr
+
+
+# ---- van der Waals term (Van_der_Waals.f90, class TB_vdW) ----
+_VDW_KIND = {"Girifalco": _abi.VDW_GIRIFALCO, "LJ": _abi.VDW_LJ_CUT, "ILJ": _abi.VDW_ILJ_CUT}
+
+
+def vdw_params_array(params):
+    arr = (_abi.VdwPair * len(params))()
+    for i, d in enumerate(params):
+        arr[i] = _abi.vdw_pair_from_dict(d)
+    return arr
+
+
+def vdw_pair_value(kind, p, r, deriv=False):
+    """vdW_energy / dvdW of one pair at distance r (Van_der_Waals.f90:578-627)"""
+    W = _abi.vdw_pair_from_dict(p)
+    f = lib().orc_vdw_dV if deriv else lib().orc_vdw_V
+    return float(f(C.c_int(_VDW_KIND[kind]), C.byref(W), C.c_double(float(r))))
+
+
+def _vdw_geom(wl):
+    S = np.ascontiguousarray(wl["S"], dtype=np.float64)
+    h = np.asfortranarray(wl["supce"], dtype=np.float64).ravel(order="F").copy()
+    return S, h
+
+
+def vdw_cells(wl, rm_tb):
+    """get_mirror_cell_num, Van_der_Waals.f90:132-157 -> ((Nx, Ny, Nz), R_cut); rm_tb = cut-off of the TB part (cutoff_radius)"""
+    S, h = _vdw_geom(wl)
+    N = np.zeros(3, dtype=np.int32); R = np.zeros(1)
+    lib().orc_vdw_cells(C.c_int(wl["n_kinds"]), vdw_params_array(wl["vdw_params"]), C.c_double(float(rm_tb)), _p(S), _p(h), _p(N), _p(R))
+    return tuple(int(x) for x in N), float(R[0])
+
+
+def vdw_energy(wl, N):
+    """get_vdW_s, Van_der_Waals.f90:158-250 -> (E_vdW, per-atom halves added to Epot)"""
+    S, h = _vdw_geom(wl)
+    Epot = np.zeros(len(S)); Nc = np.asarray(N, dtype=np.int32)
+    E = lib().orc_vdw_energy(C.c_int(len(S)), C.c_int(_VDW_KIND[wl["vdw_kind"]]), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(S), _p(h),
+                             vdw_params_array(wl["vdw_params"]), _p(Nc), _p(Epot))
+    return float(E), Epot
+
+
+def vdw_forces(wl, N, literal=False):
+    """vdW_forces -> Construct_B + d_Forces_s (TB.f90:3599-3781) -> the term added to forces%rep (na,3).
+    literal: the O(Na^3) loop nest as written; else the same sums without the pairs whose (dik - djk) is zero"""
+    S, h = _vdw_geom(wl)
+    F = np.zeros((len(S), 3)); Nc = np.asarray(N, dtype=np.int32)
+    rc = lib().orc_vdw_forces(C.c_int(len(S)), C.c_int(_VDW_KIND[wl["vdw_kind"]]), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(S), _p(h),
+                              vdw_params_array(wl["vdw_params"]), _p(Nc), C.c_int(1 if literal else 0), _p(F))
+    if rc:
+        raise MemoryError("orc_vdw_forces")
+    return F
+
+
+def vdw_pressure(wl, N):
+    """vdW_forces -> d_Forces_Pressure (TB.f90:3785-3848) -> the term added to SCforce%rep(3,3)"""
+    S, h = _vdw_geom(wl)
+    P = np.zeros(9); Nc = np.asarray(N, dtype=np.int32)
+    rc = lib().orc_vdw_pressure(C.c_int(len(S)), C.c_int(_VDW_KIND[wl["vdw_kind"]]), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(S), _p(h),
+                                vdw_params_array(wl["vdw_params"]), _p(Nc), _p(P))
+    if rc:
+        raise MemoryError("orc_vdw_pressure")
+    return P.reshape(3, 3, order="F")
 
 
 def wall_energy(wl, nb):

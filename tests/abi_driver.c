@@ -36,6 +36,14 @@ static int load(const char* fp, const char* fs, problem* q) {
     return 0;
 }
 
+/* an artificial Lennard-Jones pair table for the metal cell of the driver (type(TB_vdW_LJ_cut), Objects.f90:336-343) */
+static xtb_vdw_pair vdw_table(void) {
+    xtb_vdw_pair W;
+    memset(&W, 0, sizeof W);
+    W.eps = 0.05; W.r0 = 3.2; W.n = 6.0; W.d0_short = 2.0; W.dd_short = 0.03; W.d0_cut = 5.0; W.dd_cut = 0.1;
+    return W;
+}
+
 static int single(const problem* q, double* F_out, double* P_out) {
     xtb_ctx* ctx = NULL;
     const int na = q->na, N = 9 * na;
@@ -91,6 +99,31 @@ static int single(const problem* q, double* F_out, double* P_out) {
     }
     if (F_out) memcpy(F_out, F, sizeof(double) * 3 * na);
     if (P_out) memcpy(P_out, P, sizeof P);
+    /* a pair term that does not use the list: van der Waals (here a Lennard-Jones table on the same cell), staged calls vs
+     * the fused step with XTB_STEP_PAIR_TERMS, bit for bit; F_out[3 na ..), P_out[9 ..] carry it to the partitioned run */
+    {
+        const xtb_vdw_pair W = vdw_table();
+        double Ev = 0.0, Ev2 = 0.0, Pv[9], Pv2[9];
+        double* Fv = (double*)malloc(sizeof(double) * 3 * na);
+        double* Fv2 = (double*)malloc(sizeof(double) * 3 * na);
+        int Nc[3]; double Rc = 0.0;
+        CK(xtb_set_params_vdw(ctx, XTB_VDW_LJ_CUT, 1, &W));
+        CK(xtb_vdw_image_cells(ctx, Nc, &Rc));
+        CK(xtb_vdw_energy(ctx, &Ev, NULL));
+        CK(xtb_vdw_forces(ctx, Fv));
+        CK(xtb_vdw_pressure(ctx, Pv));
+        io.E_vdw = &Ev2; io.F_vdw = Fv2; io.SCforce_vdw = Pv2;
+        CK(xtb_step(ctx, XTB_STEP_ALL | XTB_STEP_EIGEN | XTB_STEP_PRESSURE | XTB_STEP_PAIR_TERMS, &io));
+        double dF = 0.0, dP = 0.0, fs[3] = {0, 0, 0}, fmx = 0.0;
+        for (int i = 0; i < 3 * na; ++i) { dF = fmax(dF, fabs(Fv2[i] - Fv[i])); fs[i % 3] += Fv[i]; fmx = fmax(fmx, fabs(Fv[i])); }
+        for (int i = 0; i < 9; ++i) dP = fmax(dP, fabs(Pv2[i] - Pv[i]));
+        printf("OK vdw cells=%d,%d,%d R_cut=%.3f E=%.12g Fmax=%.6g Fsum=%.3g dE=%.3g dF=%.3g dP=%.3g ms=%.3f\n", Nc[0], Nc[1], Nc[2], Rc, Ev, fmx,
+               fmax(fabs(fs[0]), fmax(fabs(fs[1]), fabs(fs[2]))), fabs(Ev2 - Ev), dF, dP, xtb_stage_ms(ctx, 17));
+        bad |= !(Ev2 == Ev) || !(dF == 0.0) || !(dP == 0.0) || !(fmx > 0.0) || !(fmax(fabs(fs[0]), fmax(fabs(fs[1]), fabs(fs[2]))) <= 1e-10 * fmx * na);
+        if (F_out) memcpy(F_out + 3 * na, Fv, sizeof(double) * 3 * na);
+        if (P_out) { memcpy(P_out + 9, Pv, sizeof Pv); P_out[18] = Ev; }
+        free(Fv); free(Fv2);
+    }
     /* error path: a stage before its inputs -> XTB_ESTATE with a message, as the shim forwards to Save_error_details */
     xtb_ctx* c2 = NULL;
     xtb_create(&c2, 0);
@@ -122,21 +155,29 @@ static int rank_main(const problem* q, int rank, int nranks, const char* idfile,
     CK(xtb_set_params_nrl(ctx, 1, &q->p));
     CK(xtb_set_system(ctx, na, koa, q->S, q->supce));
     CK(xtb_comm_init(ctx, id, rank, nranks));
+    const xtb_vdw_pair W = vdw_table();
+    CK(xtb_set_params_vdw(ctx, XTB_VDW_LJ_CUT, 1, &W));
     double* F = (double*)malloc(sizeof(double) * 3 * na);
-    double P[9];
+    double* Fv = (double*)malloc(sizeof(double) * 3 * na);
+    double P[9], Pv[9], Ev = 0.0;
     xtb_step_io io;
     memset(&io, 0, sizeof io);
-    io.n_electrons = q->ne; io.Te_eV = q->te; io.F_att = F; io.SCforce_att = P;
+    io.n_electrons = q->ne; io.Te_eV = q->te; io.F_att = F; io.SCforce_att = P; io.E_vdw = &Ev; io.F_vdw = Fv; io.SCforce_vdw = Pv;
     int bad = 0;
     for (int rep = 0; rep < 2; ++rep) {
-        CK(xtb_step(ctx, XTB_STEP_ALL | XTB_STEP_EIGEN | XTB_STEP_PRESSURE, &io));
-        double dF = 0.0, dP = 0.0;
-        for (int i = 0; i < 3 * na; ++i) dF = fmax(dF, fabs(F[i] - Fref[i]));
-        for (int i = 0; i < 9; ++i) dP = fmax(dP, fabs(P[i] - Pref[i]) / (fabs(Pref[i]) + 1e-300));
-        printf("OK rank %d/%d rep=%d dF=%.3g dP_rel=%.3g halo_send_blocks=%lld halo_recv_blocks=%lld xchg_HS_bytes=%lld xchg_rho_bytes=%lld\n", rank, nranks, rep,
-               dF, dP, xtb_counter(ctx, 14), xtb_counter(ctx, 15), xtb_counter(ctx, 12), xtb_counter(ctx, 13));
-        bad |= !(dF == 0.0) || !(dP <= 1e-13);      /* every block has one owner: forces bit-identical; the 9-vector is summed in another order */
+        CK(xtb_step(ctx, XTB_STEP_ALL | XTB_STEP_EIGEN | XTB_STEP_PRESSURE | XTB_STEP_PAIR_TERMS, &io));
+        double dF = 0.0, dP = 0.0, dFv = 0.0, dPv = 0.0;
+        for (int i = 0; i < 3 * na; ++i) { dF = fmax(dF, fabs(F[i] - Fref[i])); dFv = fmax(dFv, fabs(Fv[i] - Fref[3 * na + i])); }
+        for (int i = 0; i < 9; ++i) {
+            dP = fmax(dP, fabs(P[i] - Pref[i]) / (fabs(Pref[i]) + 1e-300));
+            dPv = fmax(dPv, fabs(Pv[i] - Pref[9 + i]) / (fabs(Pref[9]) + 1e-300));
+        }
+        printf("OK rank %d/%d rep=%d dF=%.3g dP_rel=%.3g dF_vdw=%.3g dP_vdw_rel=%.3g dE_vdw=%.3g halo_send_blocks=%lld halo_recv_blocks=%lld xchg_HS_bytes=%lld xchg_rho_bytes=%lld\n",
+               rank, nranks, rep, dF, dP, dFv, dPv, fabs(Ev - Pref[18]), xtb_counter(ctx, 14), xtb_counter(ctx, 15), xtb_counter(ctx, 12), xtb_counter(ctx, 13));
+        /* every block / atom has one owner: forces bit-identical; the 9-vectors are summed in another order; E_vdw is replicated */
+        bad |= !(dF == 0.0) || !(dP <= 1e-13) || !(dFv == 0.0) || !(dPv <= 1e-13) || !(Ev == Pref[18]);
     }
+    free(Fv);
     CK(xtb_comm_destroy(ctx));
     CK(xtb_destroy(ctx));
     free(koa); free(F);
@@ -149,8 +190,8 @@ int main(int argc, char** argv) {
     int rc = load(argv[1], argv[2], &q);
     if (rc) { fprintf(stderr, "FAIL reading inputs (%d)\n", rc); return 3; }
     const int nranks = argc > 3 ? atoi(argv[3]) : 1;
-    double* Fref = (double*)malloc(sizeof(double) * 3 * q.na);
-    double Pref[9];
+    double* Fref = (double*)malloc(sizeof(double) * 6 * q.na);      /* attractive | van der Waals */
+    double Pref[19];                                                /* attractive | van der Waals | E_vdW */
     if (nranks <= 1) {
         rc = single(&q, Fref, Pref);
         if (rc == 0) printf("OK all\n");
@@ -164,12 +205,12 @@ int main(int argc, char** argv) {
     if (pid == 0) {
         close(pfd[0]);
         int r = single(&q, Fref, Pref);
-        if (r == 0) { if (write(pfd[1], Fref, sizeof(double) * 3 * q.na) < 0 || write(pfd[1], Pref, sizeof Pref) < 0) r = 5; }
+        if (r == 0) { if (write(pfd[1], Fref, sizeof(double) * 6 * q.na) < 0 || write(pfd[1], Pref, sizeof Pref) < 0) r = 5; }
         fflush(stdout);
         _exit(r);
     }
     close(pfd[1]);
-    size_t got = 0, want = sizeof(double) * 3 * q.na;
+    size_t got = 0, want = sizeof(double) * 6 * q.na;
     while (got < want) { ssize_t n = read(pfd[0], (char*)Fref + got, want - got); if (n <= 0) break; got += (size_t)n; }
     size_t gotp = 0;
     while (gotp < sizeof Pref) { ssize_t n = read(pfd[0], (char*)Pref + gotp, sizeof Pref - gotp); if (n <= 0) break; gotp += (size_t)n; }

@@ -8,6 +8,9 @@ It writes
     xtant-3_b200/data/params_pettifor{,_rep}_Si.json   second Pettifor-type set (Silicon/Pettifor): physics pin of the oracle
     xtant-3_b200/data/params_pettifor_C.json        Pettifor parameter set
     xtant-3_b200/data/params_pettifor_rep_C.json    Pettifor repulsive parameter set
+    xtant-3_b200/data/params_vdw_{C_amorphous,I_lj}.json   van der Waals sets: Girifalco (INPUT_DATA/Amorphous_Carbon, the only
+                                                    carbon folder of the configurations whose class line is active) and LJ (PbI2)
+    xtant-3_b200/data/cell_ac216.json               the reference's own 216-atom amorphous-carbon cell
     xtant-3_b200/data/cell_{diamond64,al500,au108}.json   relative coords + supercell
     xtant-3_b200/data/dftb_{matsci_SiAl,mio_CH}.npz  DFTB Slater-Koster tables (INPUT_DATA/DFTB/<set>/<A>-<B>.skf, read by
                                                      xtant-3_b200/skf.py = read_skf_file, Dealing_with_DFTB.f90:48-149)
@@ -35,6 +38,11 @@ parse_nrl, parse_pettifor, parse_pettifor_rep, parse_cell = (_rd.read_Mehl_TB_Ha
                                                              _rd.read_Pettifor_TB_repulsive, _rd.read_SAVE)
 
 
+def vdw(path):
+    kind, p = _rd.read_vdW_TB(path)
+    return dict(p, kind=kind)
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
     jobs = {
@@ -49,6 +57,9 @@ def main():
                                                   f"{REF}/Diamond/64_atoms/SAVE_supercell.dat"),
         "cell_al500.json": lambda: parse_cell(f"{REF}/Aluminum/SAVE_atoms_500atoms.dat",
                                               f"{REF}/Aluminum/SAVE_supercell_500atoms.dat"),
+        "params_vdw_C_amorphous.json": lambda: vdw(f"{REF}/Amorphous_Carbon/C_C_TB_vdW.txt"),
+        "params_vdw_I_lj.json": lambda: vdw(f"{REF}/PbI2/I_I_TB_vdW.txt"),
+        "cell_ac216.json": lambda: parse_cell(f"{REF}/Amorphous_Carbon/SAVE_atoms.dat", f"{REF}/Amorphous_Carbon/SAVE_supercell.dat"),
         "cell_au108.json": lambda: parse_cell(f"{REF}/Gold/SAVE_atoms.dat", f"{REF}/Gold/SAVE_supercell.dat"),
     }
     for name, fn in jobs.items():

@@ -14,14 +14,16 @@ XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE
 XTB_TB_NONE, XTB_TB_NRL, XTB_TB_PETTIFOR, XTB_TB_DFTB = range(4)
 
 (BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK, BUF_FREP, BUF_MIJ,
- BUF_FWALL, BUF_POS, BUF_VEL, BUF_EI, BUF_FE) = range(1, 19)
+ BUF_FWALL, BUF_POS, BUF_VEL, BUF_EI, BUF_FE, BUF_FVDW) = range(1, 20)
 CNT_NA, CNT_NORB, CNT_N, CNT_MAXNN, CNT_NBLOCKS, CNT_NPAIRS, CNT_LAUNCHES, CNT_KKEPT, CNT_CAP = range(9)
 STAGE_NEIGH, STAGE_ASSEMBLE, STAGE_DENSITY, STAGE_FORCES, STAGE_PRESSURE = range(1, 6)
 STAGE_REP_FORCES, STAGE_REP_PRESSURE, STAGE_COUPLING = 9, 10, 11
 STAGE_XCHG_HS, STAGE_XCHG_RHO = 14, 15
 CNT_XCHG_HS_BYTES, CNT_XCHG_RHO_BYTES, CNT_HALO_SEND, CNT_HALO_RECV = 12, 13, 14, 15
 XCHG_HS, XCHG_RHO = 1, 2
-FORCE_ATT, FORCE_REP, FORCE_WALL = 1, 2, 4
+FORCE_ATT, FORCE_REP, FORCE_WALL, FORCE_VDW = 1, 2, 4, 8
+VDW_GIRIFALCO, VDW_LJ_CUT, VDW_ILJ_CUT = 1, 2, 3
+STAGE_VDW = 17
 STEP_NEIGHBOURS, STEP_HS, STEP_EIGEN, STEP_DENSITY, STEP_FORCES, STEP_PRESSURE, STEP_PAIR_TERMS, STEP_NO_DENSE, STEP_GRAPH = 1, 2, 4, 8, 16, 32, 64, 128, 256
 STEP_ALL = STEP_NEIGHBOURS | STEP_HS | STEP_DENSITY | STEP_FORCES
 UNIQUE_ID_BYTES = 128
@@ -58,6 +60,23 @@ class WallPair(C.Structure):
     _fields_ = [("C", C.c_double), ("r0", C.c_double), ("d0", C.c_double), ("dd", C.c_double)]
 
 
+VDW_FIELDS = ("d0_cut", "dd_cut", "C12", "C6", "dm", "d_cut", "a", "b", "c", "d", "dsm", "ds_cut", "as", "bs", "cs", "ds", "es", "fs",
+              "eps", "r0", "n", "m", "d0_short", "dd_short")
+
+
+class VdwPair(C.Structure):
+    """struct xtb_vdw_pair == class(TB_vdW) Objects.f90:43-46 + TB_vdW_Girifalco :302-328 / TB_vdW_LJ_cut :336-343 / TB_vdW_ILJ_cut :346-354"""
+    _fields_ = [(k, C.c_double) for k in VDW_FIELDS]
+
+
+def vdw_pair_from_dict(d):
+    """missing members are zero (each class reads only its own)"""
+    p = VdwPair()
+    for k in VDW_FIELDS:
+        setattr(p, k, float(d.get(k, 0.0)))
+    return p
+
+
 class StepIO(C.Structure):
     """struct xtb_step_io"""
     _fields_ = [("S", C.POINTER(C.c_double)), ("supce", C.POINTER(C.c_double)), ("fe", C.POINTER(C.c_double)),
@@ -65,7 +84,8 @@ class StepIO(C.Structure):
                 ("Ei", C.POINTER(C.c_double)), ("fe_out", C.POINTER(C.c_double)), ("mu", C.POINTER(C.c_double)),
                 ("E_band", C.POINTER(C.c_double)), ("F_att", C.POINTER(C.c_double)), ("SCforce_att", C.POINTER(C.c_double)),
                 ("E_rep", C.POINTER(C.c_double)), ("F_rep", C.POINTER(C.c_double)), ("SCforce_rep", C.POINTER(C.c_double)),
-                ("E_wall", C.POINTER(C.c_double)), ("F_wall", C.POINTER(C.c_double)), ("SCforce_wall", C.POINTER(C.c_double))]
+                ("E_wall", C.POINTER(C.c_double)), ("F_wall", C.POINTER(C.c_double)), ("SCforce_wall", C.POINTER(C.c_double)),
+                ("E_vdw", C.POINTER(C.c_double)), ("F_vdw", C.POINTER(C.c_double)), ("SCforce_vdw", C.POINTER(C.c_double))]
 
 
 class DftbPair(C.Structure):
@@ -171,6 +191,11 @@ SIGNATURES = {
     "xtb_wall_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
     "xtb_wall_forces": (C.c_int, [C.c_void_p, _pd]),
     "xtb_wall_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_set_params_vdw": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(VdwPair)]),
+    "xtb_vdw_image_cells": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), _pd]),
+    "xtb_vdw_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_vdw_forces": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_vdw_pressure": (C.c_int, [C.c_void_p, _pd]),
     "xtb_fermi_occupations": (C.c_int, [C.c_void_p, C.c_double, C.c_double, _pd, _pd, _pd]),
     "xtb_md_set_velocities": (C.c_int, [C.c_void_p, _pd]),
     "xtb_md_half_step": (C.c_int, [C.c_void_p, C.c_int, C.c_double, _pd, _pd, C.c_uint]),

@@ -106,7 +106,20 @@ class TBContext:
         self.tb = wl["tb"]
         if wl.get("wall_params"):
             self.set_params_wall(wl["wall_params"])
+        if wl.get("vdw_params"):
+            self.set_params_vdw(wl["vdw_kind"], wl["vdw_params"])
         self.set_system(wl["koa"], wl["S"], wl["supce"])
+
+    def set_params_vdw(self, kind, params):
+        """Scell%TB_Waals(:,:): kind 'Girifalco' | 'LJ' | 'ILJ' (or XTB_VDW_*), list of dicts with the members of that class
+        (readers.read_vdW_TB), (koa1, koa2) column-major; None / [] removes the term"""
+        if not params:
+            self._ck(self.lib.xtb_set_params_vdw(self.h, 0, 0, None))
+            return
+        kind = {"Girifalco": _abi.VDW_GIRIFALCO, "LJ": _abi.VDW_LJ_CUT, "ILJ": _abi.VDW_ILJ_CUT}.get(kind, kind)
+        nk = int(round(len(params) ** 0.5))
+        arr = (_abi.VdwPair * len(params))(*[_abi.vdw_pair_from_dict(d) for d in params])
+        self._ck(self.lib.xtb_set_params_vdw(self.h, int(kind), nk, arr))
 
     def set_params_wall(self, params):
         """Scell%TB_Expwall(:,:) of class TB_Exp_wall_simple: list of dict(C, r0, d0, dd), (koa1, koa2) column-major; None / [] removes it"""
@@ -297,6 +310,31 @@ class TBContext:
         self._ck(self.lib.xtb_wall_pressure(self.h, _dp(P)))
         return P.reshape(3, 3, order="F")
 
+    # -- van der Waals term (third part) -------------------------------------
+    def get_mirror_cell_num(self):
+        """get_mirror_cell_num, Van_der_Waals.f90:132 -> ((Nx, Ny, Nz), R_cut [A])"""
+        N = (C.c_int * 3)(); R = np.zeros(1)
+        self._ck(self.lib.xtb_vdw_image_cells(self.h, N, _dp(R)))
+        return (int(N[0]), int(N[1]), int(N[2])), float(R[0])
+
+    def get_vdW_s(self):
+        """get_vdW_s, Van_der_Waals.f90:158 -> (E_vdW [eV], per-atom halves added to MDAtoms(:)%Epot)"""
+        E = np.zeros(1); Epot = np.zeros(self.na)
+        self._ck(self.lib.xtb_vdw_energy(self.h, _dp(E), _dp(Epot)))
+        return float(E[0]), Epot
+
+    def vdW_forces(self):
+        """vdW_forces -> Construct_B + d_Forces_s, TB.f90:3599,3638 -> the term added to forces%rep, (na,3), d/ds units [eV]"""
+        F = np.zeros((self.na, 3))
+        self._ck(self.lib.xtb_vdw_forces(self.h, _dp(F)))
+        return F
+
+    def vdW_Pressure(self):
+        """vdW_forces -> d_Forces_Pressure, TB.f90:3785 -> the term added to SCforce%rep(3,3)"""
+        P = np.zeros(9)
+        self._ck(self.lib.xtb_vdw_pressure(self.h, _dp(P)))
+        return P.reshape(3, 3, order="F")
+
     # -- Fermi occupations, velocity-Verlet halves, the fused step (step.cu) ----------------------
     def fermi_occupations(self, n_electrons, Te_eV):
         """Electron_Fixed_Te + set_Fermi (Electron_tools.f90:2660,1913) on the device -> (fe, mu, sum f E)"""
@@ -324,7 +362,8 @@ class TBContext:
 
     def step(self, flags=_abi.STEP_ALL, S=None, supce=None, fe=None, n_electrons=0.0, Te_eV=0.0, want=(), graph=False):
         """xtb_step: the selected stages as one call.  want: names of host outputs to fetch, any of
-        Ei, fe_out, mu, E_band, F_att, SCforce_att, E_rep, F_rep, SCforce_rep, E_wall, F_wall, SCforce_wall -> dict"""
+        Ei, fe_out, mu, E_band, F_att, SCforce_att, E_rep, F_rep, SCforce_rep, E_wall, F_wall, SCforce_wall,
+        E_vdw, F_vdw, SCforce_vdw -> dict"""
         N = self.na * self.n_orb
         io = _abi.StepIO()
         keep = []
@@ -337,7 +376,8 @@ class TBContext:
         io.S = inp(S); io.supce = inp(supce, "F"); io.fe = inp(fe)
         io.n_electrons = float(n_electrons); io.Te_eV = float(Te_eV)
         shapes = {"Ei": (N,), "fe_out": (N,), "mu": (1,), "E_band": (1,), "F_att": (self.na, 3), "SCforce_att": (9,),
-                  "E_rep": (1,), "F_rep": (self.na, 3), "SCforce_rep": (9,), "E_wall": (1,), "F_wall": (self.na, 3), "SCforce_wall": (9,)}
+                  "E_rep": (1,), "F_rep": (self.na, 3), "SCforce_rep": (9,), "E_wall": (1,), "F_wall": (self.na, 3), "SCforce_wall": (9,),
+                  "E_vdw": (1,), "F_vdw": (self.na, 3), "SCforce_vdw": (9,)}
         out = {}
         for k in want:
             out[k] = np.zeros(shapes[k])

@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(FT_THREADS) fermi_kernel(long long N, const do
 // par: [0..8] g^-1 (col-major), [9..17] GinvGdot, [18] dt, [19] dt^2/2, [20] dt/2; minv[kind] = -g_e * 1e-10 / M
 __global__ void md_half_kernel(int na, int ind, const int* __restrict__ koa, const double* __restrict__ par, const double* __restrict__ minv,
                                const double* __restrict__ Fa, const double* __restrict__ Fb, const double* __restrict__ Fc,
-                               double* __restrict__ S, double* __restrict__ S0, double* __restrict__ SV, double* __restrict__ SV0) {
+                               const double* __restrict__ Fd, double* __restrict__ S, double* __restrict__ S0, double* __restrict__ SV, double* __restrict__ SV0) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= na) return;
     // save_last_timestep: S0 = S, SV0 = SV
@@ -89,6 +89,7 @@ __global__ void md_half_kernel(int na, int ind, const int* __restrict__ koa, con
         f[x] = Fa[3 * k + x];
         if (Fb) f[x] += Fb[3 * k + x];
         if (Fc) f[x] += Fc[3 * k + x];
+        if (Fd) f[x] += Fd[3 * k + x];
     }
     const double fctr = minv[koa[k]];
     double acc[3];
@@ -230,11 +231,13 @@ int xtb_md_half_step(xtb_ctx* c, int ind, double dt_fs, const double* mass_kg, c
     const double* Fc = (force_terms & XTB_FORCE_WALL) ? (const double*)c->d_Fwall.p : nullptr;
     if ((force_terms & XTB_FORCE_ATT) && !Fa) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no attractive forces on the device");
     if ((force_terms & XTB_FORCE_REP) && !Fb) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no repulsive forces on the device");
+    const double* Fd = (force_terms & XTB_FORCE_VDW) ? (const double*)c->d_Fvdw.p : nullptr;
     if ((force_terms & XTB_FORCE_WALL) && !Fc) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no wall forces on the device");
-    const double* terms[3] = {Fa, Fb, Fc};
-    const double* F3[3] = {nullptr, nullptr, nullptr};
+    if ((force_terms & XTB_FORCE_VDW) && !Fd) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no van der Waals forces on the device");
+    const double* terms[4] = {Fa, Fb, Fc, Fd};
+    const double* F3[4] = {nullptr, nullptr, nullptr, nullptr};
     int nt = 0;
-    for (int t = 0; t < 3; ++t) if (terms[t]) F3[nt++] = terms[t];
+    for (int t = 0; t < 4; ++t) if (terms[t]) F3[nt++] = terms[t];
     if (nt == 0) XTB_FAIL(c, XTB_EINVAL, "xtb_md_half_step: no force term selected");
     // g^-1 = (h^T h)^-1 (:1916-1922) and GinvGdot (get_GGdot :1843-1861)
     double par[24] = {0};
@@ -256,7 +259,7 @@ int xtb_md_half_step(xtb_ctx* c, int ind, double dt_fs, const double* mass_kg, c
     for (int k = 0; k < c->n_kinds; ++k) up[32 + k] = -1.0 / mass_kg[k] * 1.602176634e-19 * 1e-10;       // fctr :1938
     XTB_CUDA(c, cudaMemcpyAsync(c->d_mdpar.p, up.data(), sizeof(double) * up.size(), cudaMemcpyHostToDevice, c->stream));
     md_half_kernel<<<(c->na + 127) / 128, 128, 0, c->stream>>>(c->na, ind, (const int*)c->d_koa.p, (const double*)c->d_mdpar.p,
-                                                               (const double*)c->d_mdpar.p + 32, F3[0], F3[1], F3[2],
+                                                               (const double*)c->d_mdpar.p + 32, F3[0], F3[1], F3[2], F3[3],
                                                                (double*)c->d_S.p, (double*)c->d_S0.p, (double*)c->d_SV.p, (double*)c->d_SV0.p);
     XTB_LAUNCH_CHECK(c);
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));           // `up` is a host temporary
@@ -362,12 +365,14 @@ struct GraphKey {
     cudaStream_t stream;
     double rm, f_cut;
     bool rep, wall;
+    int vdw_kind, vdw_cells[3];
 };
 static unsigned io_mask(const xtb_step_io* io) {
     if (!io) return 0;
     unsigned m = 0;
-    const void* p[] = {io->S, io->F_att, io->SCforce_att, io->E_rep, io->F_rep, io->SCforce_rep, io->E_wall, io->F_wall, io->SCforce_wall};
-    for (int k = 0; k < 9; ++k) if (p[k]) m |= 1u << k;
+    const void* p[] = {io->S, io->F_att, io->SCforce_att, io->E_rep, io->F_rep, io->SCforce_rep, io->E_wall, io->F_wall, io->SCforce_wall,
+                       io->E_vdw, io->F_vdw, io->SCforce_vdw};
+    for (int k = 0; k < 12; ++k) if (p[k]) m |= 1u << k;
     return m;
 }
 static GraphKey make_key(const xtb_ctx* c, unsigned flags, const xtb_step_io* io) {
@@ -378,15 +383,19 @@ static GraphKey make_key(const xtb_ctx* c, unsigned flags, const xtb_step_io* io
     k.blk_cap = c->blk_cap; k.k_kept = c->k_kept; k.K = c->K; k.alloc_epoch = c->alloc_epoch;
     k.Ha = c->d_Ha ? (const void*)c->d_Ha : (const void*)c->d_HaT; k.Ei = c->d_Ei; k.fe = c->d_fe; k.stream = c->stream; k.rm = c->rm; k.f_cut = c->f_cut;
     k.rep = !c->h_pet_rep.empty(); k.wall = !c->h_wall.empty();
+    if (!c->h_vdw.empty()) {                 // the image counts are launch arguments (supce cannot change inside a graph step)
+        k.vdw_kind = c->vdw_kind;
+        xtb_impl_vdw_cells(const_cast<xtb_ctx*>(c), k.vdw_cells, nullptr);
+    }
     return k;
 }
 static void graph_drop(xtb_ctx* c) {
     if (c->graph_exec) { cudaGraphExecDestroy((cudaGraphExec_t)c->graph_exec); c->graph_exec = nullptr; }
     c->graph_key.clear();
 }
-// staging layout (doubles): S[3 na] | F_att[3 na] | F_rep[3 na] | F_wall[3 na] | SC_att[9] SC_rep[9] SC_wall[9] | E_rep E_wall
+// staging layout (doubles): S[3 na] | F_att[3 na] | F_rep[3 na] | F_wall[3 na] | F_vdw[3 na] | SC_att[9] SC_rep[9] SC_wall[9] SC_vdw[9] | E_rep E_wall E_vdw
 static int graph_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool* overflow) {
-    const size_t na3 = 3 * (size_t)c->na, need = sizeof(double) * (4 * na3 + 32);
+    const size_t na3 = 3 * (size_t)c->na, need = sizeof(double) * (5 * na3 + 48);
     *overflow = false;
     if (c->h_stage_bytes < need) {
         if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -403,11 +412,14 @@ static int graph_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool* o
         if (io->F_att) g.F_att = st + na3;
         if (io->F_rep) g.F_rep = st + 2 * na3;
         if (io->F_wall) g.F_wall = st + 3 * na3;
-        if (io->SCforce_att) g.SCforce_att = st + 4 * na3;
-        if (io->SCforce_rep) g.SCforce_rep = st + 4 * na3 + 9;
-        if (io->SCforce_wall) g.SCforce_wall = st + 4 * na3 + 18;
-        if (io->E_rep) g.E_rep = st + 4 * na3 + 27;
-        if (io->E_wall) g.E_wall = st + 4 * na3 + 28;
+        if (io->F_vdw) g.F_vdw = st + 4 * na3;
+        if (io->SCforce_att) g.SCforce_att = st + 5 * na3;
+        if (io->SCforce_rep) g.SCforce_rep = st + 5 * na3 + 9;
+        if (io->SCforce_wall) g.SCforce_wall = st + 5 * na3 + 18;
+        if (io->SCforce_vdw) g.SCforce_vdw = st + 5 * na3 + 27;
+        if (io->E_rep) g.E_rep = st + 5 * na3 + 36;
+        if (io->E_wall) g.E_wall = st + 5 * na3 + 37;
+        if (io->E_vdw) g.E_vdw = st + 5 * na3 + 38;
     }
     const GraphKey key = make_key(c, flags, io);
     if (!c->graph_exec || c->graph_key.size() != sizeof key || memcmp(c->graph_key.data(), &key, sizeof key) != 0) {
@@ -453,11 +465,14 @@ static int graph_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool* o
         if (io->F_att) memcpy(io->F_att, g.F_att, sizeof(double) * na3);
         if (io->F_rep) memcpy(io->F_rep, g.F_rep, sizeof(double) * na3);
         if (io->F_wall) memcpy(io->F_wall, g.F_wall, sizeof(double) * na3);
+        if (io->F_vdw) memcpy(io->F_vdw, g.F_vdw, sizeof(double) * na3);
         if (io->SCforce_att) memcpy(io->SCforce_att, g.SCforce_att, 72);
         if (io->SCforce_rep) memcpy(io->SCforce_rep, g.SCforce_rep, 72);
         if (io->SCforce_wall) memcpy(io->SCforce_wall, g.SCforce_wall, 72);
         if (io->E_rep) *io->E_rep = *g.E_rep;
         if (io->E_wall) *io->E_wall = *g.E_wall;
+        if (io->SCforce_vdw) memcpy(io->SCforce_vdw, g.SCforce_vdw, 72);
+        if (io->E_vdw) *io->E_vdw = *g.E_vdw;
     }
     return XTB_OK;
 }

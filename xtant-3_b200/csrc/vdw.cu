@@ -1,0 +1,306 @@
+// van der Waals pair term (third part; class TB_vdW).
+//
+// Replaces, in Source_files/Van_der_Waals.f90 and TB.f90 (dispatch vdW_forces TB.f90:3599-3633, vdW_s TB.f90:4017-4035):
+//   get_mirror_cell_num :132-157        R_cut = max(TB cut-off, max d0_cut + 10 max dd_cut) (get_near_neighbours with include_vdW,
+//                                       Atomic_tools.f90:636-641); get_number_of_image_cells (Atomic_tools.f90:654-702); >= 1 per axis
+//   get_vdW_s :158-250                  E = 1/2 sum_cells sum_i sum_j V(r_ij,cell), (j /= i) or (cell /= 0); Epot(i) += 1/2 sum_j V
+//   vdW_energy / dvdW :578-627          dispatch on the class: Girifalco :933-1057, LJ_cut :650-675, ILJ_cut :718-745
+//   Construct_B / cell_cycle_B :251-421 Bij = dV/dr with TB_Waals(KOA(j1), KOA(i1)), geometry from distance_to_given_cell
+//                                       (Atomic_tools.f90:4135-4166)
+//   d_Forces_s TB.f90:3638-3781         forces%rep(ian) += 1/2 sum_{i1} sum_{j1,cell} Bij (d_{ian,i1} - d_{ian,j1}) / r * (h . r)
+//   d_Forces_Pressure TB.f90:3785-3848  SCforce%rep(l,k) += 1/2 sum_cells sum_i sum_j Bij r_k s_l / r
+// The reference builds eleven (cells, Na, Na) arrays and then loops ian x i1 x j1 x cells (O(Na^3)); only i1 = ian and j1 = ian
+// contribute, and the j1 = ian term of cell zb is the mirror image of the i1 = ian term of cell -zb (the displacement changes
+// sign exactly in floating point), so one pass over (j, cell) per atom gives energy, force and supercell force together.  Here:
+// one CTA per owned atom, threads stride the other atoms, every thread walks the image cells; fixed-order reductions, nothing
+// stored per pair.  Every class is exactly zero (value and slope) beyond R_max = max d_cut (Girifalco) / max (d0_cut + 10 dd_cut)
+// (Fermi_function returns 0.0 there), so image cells whose slab |s_a + c_a| * (spacing of the cell planes along a) > R_max are
+// not visited: they would add +-0.0.  At config 4 (17.8 A cell, R_max 6 A) that leaves ~1.4 of the 27 images per pair.
+// FP64 CUDA cores, compute-bound (no memory traffic to speak of: positions and kinds of Na atoms, L1-resident).
+#include <cmath>
+#include <cstdlib>
+#include "xtb_ctx.h"
+
+namespace {
+
+constexpr int VT = 128;             // threads per CTA (one CTA per atom)
+constexpr unsigned FULL = 0xffffffffu;
+enum : unsigned { DO_E = 1u, DO_F = 2u, DO_P = 4u };
+
+__device__ __forceinline__ double fermi_f(double rcut, double d, double r) {        // Fermi_function, Little_subroutines.f90:349
+    if (r >= rcut + 10.0 * d) return 0.0;
+    return 1.0 / (1.0 + exp((r - rcut) / d));
+}
+__device__ __forceinline__ double d_fermi_f(double rcut, double d, double r) {      // d_Fermi_function :360 (cut-off on)
+    if (r >= rcut + 10.0 * d) return 0.0;
+    const double e = exp((r - rcut) / d), e1 = 1.0 + e;
+    return -e / (d * e1 * e1);
+}
+
+template <int KIND> struct Vdw;
+template <> struct Vdw<XTB_VDW_GIRIFALCO> {
+    static __device__ __forceinline__ double V(const xtb_vdw_pair& W, double r) {   // vdW_Girifalco :933-991
+        if (r > W.d_cut || r < W.ds_cut) return 0.0;
+        if (r > W.dm) { const double r2 = r * r; return W.a * r2 * r + W.b * r2 + W.c * r + W.d; }
+        if (r < W.dsm) {
+            const double r2 = r * r, r4 = r2 * r2;
+            return W.as * r4 * r + W.bs * r4 + W.cs * r2 * r + W.ds * r2 + W.es * r + W.fs;
+        }
+        const double r2 = r * r, r3 = r2 * r, r6 = r3 * r3, r12 = r6 * r6;          // LJ_potential :1116, fast_pow(r, 6)
+        return W.C12 / r12 - W.C6 / r6;
+    }
+    static __device__ __forceinline__ double dV(const xtb_vdw_pair& W, double r) {  // d_vdW_Girifalco :995-1057
+        if (r > W.d_cut || r < W.ds_cut) return 0.0;
+        if (r > W.dm) return 3.0 * W.a * r * r + 2.0 * W.b * r + W.c;
+        if (r < W.dsm) {
+            const double r2 = r * r, r4 = r2 * r2;
+            return 5.0 * W.as * r4 + 4.0 * W.bs * r2 * r + 3.0 * W.cs * r2 + 2.0 * W.ds * r + W.es;
+        }
+        const double r2 = r * r, r3 = r2 * r, r6 = r3 * r3, r7 = r6 * r, r13 = r6 * r7;   // d_LJ_potential :1126
+        return -12.0 * W.C12 / r13 + 6.0 * W.C6 / r7;
+    }
+};
+template <> struct Vdw<XTB_VDW_LJ_CUT> {
+    static __device__ __forceinline__ double V(const xtb_vdw_pair& W, double r) {   // double_truncated_LJ :650-660
+        double v = 0.0;                                                             // General_LJ_potential :839
+        if (r > 0.0) { const double q = pow(W.r0 / r, W.n); v = W.eps * (q - 2.0) * q; }
+        return v * (1.0 - fermi_f(W.d0_short, W.dd_short, r)) * fermi_f(W.d0_cut, W.dd_cut, r);
+    }
+    static __device__ __forceinline__ double dV(const xtb_vdw_pair& W, double r) {  // d_double_truncated_LJ :663-675
+        double v = 0.0, dv = 0.0;
+        if (r > 0.0) {
+            const double q = pow(W.r0 / r, W.n);
+            v = W.eps * (q - 2.0) * q;
+            dv = -W.eps * 2.0 * W.n / r * q * (q - 1.0);                            // d_General_LJ_potential :853
+        }
+        const double fl = fermi_f(W.d0_cut, W.dd_cut, r), dfl = d_fermi_f(W.d0_cut, W.dd_cut, r);
+        const double fs = 1.0 - fermi_f(W.d0_short, W.dd_short, r), dfs = -d_fermi_f(W.d0_short, W.dd_short, r);
+        return v * (dfs * fl + fs * dfl) + dv * (fs * fl);
+    }
+};
+template <> struct Vdw<XTB_VDW_ILJ_CUT> {
+    static __device__ __forceinline__ double V(const xtb_vdw_pair& W, double r) {   // ILJ :718-727, Improved_LJ_potential :882
+        double v = 0.0;
+        if (r > 0.0) { const double q = W.r0 / r, nm = W.n - W.m; v = W.eps * (W.m / nm * pow(q, W.n) - W.n / nm * pow(q, W.m)); }
+        return v * (1.0 - fermi_f(W.d0_short, W.dd_short, r)) * fermi_f(W.d0_cut, W.dd_cut, r);
+    }
+    static __device__ __forceinline__ double dV(const xtb_vdw_pair& W, double r) {  // d_ILJ :730-745
+        double v = 0.0, dv = 0.0;
+        if (r > 0.0) {
+            const double q = W.r0 / r, nm = W.n - W.m, qn = pow(q, W.n), qm = pow(q, W.m);
+            v = W.eps * (W.m / nm * qn - W.n / nm * qm);
+            dv = -W.eps * (qn - qm) * W.n * W.m / (nm * r);                         // d_Improved_LJ_potential :896
+        }
+        const double fl = fermi_f(W.d0_cut, W.dd_cut, r), dfl = d_fermi_f(W.d0_cut, W.dd_cut, r);
+        const double fs = 1.0 - fermi_f(W.d0_short, W.dd_short, r), dfs = -d_fermi_f(W.d0_short, W.dd_short, r);
+        return v * (dfs * fl + fs * dfl) + dv * (fs * fl);
+    }
+};
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(FULL, v, off);
+    return v;
+}
+
+// atom i = a0 + blockIdx.x.  sym: TB_Waals(k1,k2) == TB_Waals(k2,k1) bit for bit (the mirrored force term then equals the direct one).
+template <int KIND>
+// reach[a] = R_max / (plane spacing along cell axis a), a little widened: the range of |s_a| inside which a pair can interact
+__global__ void __launch_bounds__(VT) vdw_atom_kernel(int a0, int na, int n_kinds, int Nx, int Ny, int Nz, unsigned what, int sym,
+                                                      double reach_x, double reach_y, double reach_z,
+                                                      const int* __restrict__ koa, const double* __restrict__ S,
+                                                      const xtb_vdw_pair* __restrict__ WP, const double* __restrict__ hdev,
+                                                      double* __restrict__ Epot, double* __restrict__ F, double* __restrict__ ppart) {
+    __shared__ double red[VT / 32][13];
+    const int i = a0 + blockIdx.x, tid = threadIdx.x;
+    double h[9];
+#pragma unroll
+    for (int e = 0; e < 9; ++e) h[e] = hdev[e];             // supce(a,b) = h[a + 3b]
+    const double sxi = S[3 * i], syi = S[3 * i + 1], szi = S[3 * i + 2];
+    const int ki = koa[i];
+    double acc[13];                                          // 0 energy, 1-3 force, 4-12 supercell force (l + 3k)
+#pragma unroll
+    for (int e = 0; e < 13; ++e) acc[e] = 0.0;
+    for (int j = tid; j < na; j += VT) {
+        const int kj = koa[j];
+        const xtb_vdw_pair& Wij = WP[ki + n_kinds * kj];    // TB_Waals(KOAi, KOAj): energy (:597-604); Bij of (i1 = j, j1 = i)
+        const xtb_vdw_pair& Wji = WP[kj + n_kinds * ki];    // TB_Waals(KOA(j1), KOA(i1)): Bij of (i1 = i, j1 = j) (:353)
+        const double dsx = sxi - S[3 * j], dsy = syi - S[3 * j + 1], dsz = szi - S[3 * j + 2];
+        // image range per axis: |ds_a + c_a| <= reach_a, inside [-N_a, N_a] (compared as doubles: reach may be huge)
+        const int x0 = (int)fmax(-(double)Nx, ceil(-reach_x - dsx)), x1 = (int)fmin((double)Nx, floor(reach_x - dsx));
+        const int y0 = (int)fmax(-(double)Ny, ceil(-reach_y - dsy)), y1 = (int)fmin((double)Ny, floor(reach_y - dsy));
+        const int z0 = (int)fmax(-(double)Nz, ceil(-reach_z - dsz)), z1 = (int)fmin((double)Nz, floor(reach_z - dsz));
+        for (int cx = x0; cx <= x1; ++cx)
+            for (int cy = y0; cy <= y1; ++cy)
+                for (int cz = z0; cz <= z1; ++cz) {
+                    if (j == i && cx == 0 && cy == 0 && cz == 0) continue;          // no self-interaction in the origin cell
+                    const double s[3] = {dsx + (double)cx, dsy + (double)cy, dsz + (double)cz};     // distance_to_given_cell :4163-4165
+                    double x[3];
+#pragma unroll
+                    for (int al = 0; al < 3; ++al) x[al] = s[0] * h[3 * al] + s[1] * h[1 + 3 * al] + s[2] * h[2 + 3 * al];   // :4153-4155
+                    const double r = sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
+                    if (what & DO_E) acc[0] += Vdw<KIND>::V(Wij, r);
+                    if (what & (DO_F | DO_P)) {
+                        const double b = Vdw<KIND>::dV(Wji, r);
+                        if ((what & DO_F) && j != i) {
+                            const double bb = (sym ? b + b : b + Vdw<KIND>::dV(Wij, r)) / r;
+#pragma unroll
+                            for (int al = 0; al < 3; ++al) acc[1 + al] += bb * (x[0] * h[al] + x[1] * h[al + 3] + x[2] * h[al + 6]);   // XijSupce :343-345
+                        }
+                        if (what & DO_P) {
+                            const double br = b / r;
+#pragma unroll
+                            for (int k = 0; k < 3; ++k)
+#pragma unroll
+                                for (int l = 0; l < 3; ++l) acc[4 + l + 3 * k] += br * x[k] * s[l];                                   // TB.f90:3829
+                        }
+                    }
+                }
+    }
+#pragma unroll
+    for (int e = 0; e < 13; ++e) {
+        const double v = warp_sum(acc[e]);
+        if ((tid & 31) == 0) red[tid >> 5][e] = v;
+    }
+    __syncthreads();
+    if (tid < 13) {
+        double v = 0.0;
+#pragma unroll
+        for (int w = 0; w < VT / 32; ++w) v += red[w][tid];
+        v *= 0.5;                                            // :246, TB.f90:3765, TB.f90:3838
+        if (tid == 0) { if (what & DO_E) Epot[i] = v; }
+        else if (tid < 4) { if (what & DO_F) F[3 * (size_t)i + tid - 1] = v; }
+        else if (what & DO_P) ppart[(size_t)blockIdx.x * 9 + tid - 4] = v;
+    }
+}
+
+__global__ void __launch_bounds__(256) vdw_esum_kernel(int na, const double* __restrict__ Epot, double* __restrict__ out) {
+    __shared__ double buf[256];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < na; i += 256) s += Epot[i];
+    buf[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = 128; off > 0; off >>= 1) {
+        if (threadIdx.x < off) buf[threadIdx.x] += buf[threadIdx.x + off];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[0] = buf[0];
+}
+
+__global__ void vdw_sum9_kernel(int n, const double* __restrict__ partial, double* __restrict__ out) {
+    __shared__ double buf[128];
+    const int k1 = blockIdx.x;
+    double s = 0.0;
+    for (int a = threadIdx.x; a < n; a += 128) s += partial[(size_t)a * 9 + k1];
+    buf[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = 64; off > 0; off >>= 1) {
+        if (threadIdx.x < off) buf[threadIdx.x] += buf[threadIdx.x + off];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[k1] = buf[0];
+}
+
+int launch_atoms(xtb_ctx* c, int first, int count, unsigned what, const int N[3]) {
+    if (count <= 0) return XTB_OK;
+    // R_max of the pair table and the plane spacings of the cell (volume / face area)
+    double Rmax = 0.0, reach[3];
+    for (auto& p : c->h_vdw) {
+        const double r = c->vdw_kind == XTB_VDW_GIRIFALCO ? p.d_cut : p.d0_cut + 10.0 * p.dd_cut;
+        if (r > Rmax) Rmax = r;
+    }
+    {
+        const double* h = c->h_supce;               // row a of supce = cell vector a: (h[a], h[a+3], h[a+6])
+        double v[3][3], vol;
+        for (int a = 0; a < 3; ++a) for (int k = 0; k < 3; ++k) v[a][k] = h[a + 3 * k];
+        auto cross = [](const double* p, const double* q, double* o) { o[0] = p[1] * q[2] - p[2] * q[1]; o[1] = p[2] * q[0] - p[0] * q[2]; o[2] = p[0] * q[1] - p[1] * q[0]; };
+        double bc[3];
+        cross(v[1], v[2], bc);
+        vol = fabs(v[0][0] * bc[0] + v[0][1] * bc[1] + v[0][2] * bc[2]);
+        for (int a = 0; a < 3; ++a) {
+            double n[3];
+            cross(v[(a + 1) % 3], v[(a + 2) % 3], n);
+            const double area = sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+            const double spacing = area > 0.0 ? vol / area : 0.0;
+            reach[a] = (spacing > 0.0 && !getenv("XTB_VDW_NO_PRUNE")) ? Rmax / spacing * (1.0 + 1e-9) + 1e-9 : 1e300;
+        }
+    }
+#define XTB_VDW_LAUNCH(KIND)                                                                                                          \
+    vdw_atom_kernel<KIND><<<count, VT, 0, c->stream>>>(first, c->na, c->n_kinds, N[0], N[1], N[2], what, c->vdw_sym ? 1 : 0,           \
+                                                       reach[0], reach[1], reach[2],                                                  \
+                                                       (const int*)c->d_koa.p, (const double*)c->d_S.p, (const xtb_vdw_pair*)c->d_vdw_params.p, \
+                                                       (const double*)c->d_hdev.p, (double*)c->d_Evdw_at.p, (double*)c->d_Fvdw.p,      \
+                                                       (double*)c->d_ppart.p)
+    switch (c->vdw_kind) {
+        case XTB_VDW_GIRIFALCO: XTB_VDW_LAUNCH(XTB_VDW_GIRIFALCO); break;
+        case XTB_VDW_LJ_CUT:    XTB_VDW_LAUNCH(XTB_VDW_LJ_CUT); break;
+        case XTB_VDW_ILJ_CUT:   XTB_VDW_LAUNCH(XTB_VDW_ILJ_CUT); break;
+        default: XTB_FAIL(c, XTB_ESTATE, "vdW: unknown class %d", c->vdw_kind);
+    }
+#undef XTB_VDW_LAUNCH
+    XTB_LAUNCH_CHECK(c);
+    return XTB_OK;
+}
+
+}  // namespace
+
+// get_mirror_cell_num (Van_der_Waals.f90:132-157) on the host: supce and the parameters live there
+int xtb_impl_vdw_cells(xtb_ctx* c, int N[3], double* R_cut) {
+    double Rc = xtb_default_cutoff(c), r = 0.0, d = 0.0;
+    bool first = true;
+    for (auto& p : c->h_vdw) {                                // maxval over the pair table, Atomic_tools.f90:637-638
+        if (first || p.d0_cut > r) r = p.d0_cut;
+        if (first || p.dd_cut > d) d = p.dd_cut;
+        first = false;
+    }
+    const double X = r + 10.0 * d;
+    if (Rc < X) Rc = X;
+    if (R_cut) *R_cut = Rc;
+    const double* h = c->h_supce;
+    long long cells = 1;
+    for (int a = 0; a < 3; ++a) {                             // get_number_of_image_cells, Atomic_tools.f90:654-702
+        auto dist = [&](double zb) { const double x0 = zb * h[a], y0 = zb * h[a + 3], z0 = zb * h[a + 6]; return sqrt(x0 * x0 + y0 * y0 + z0 * z0); };
+        if (!(dist(1.0) > 0.0)) XTB_FAIL(c, XTB_EINVAL, "vdW: supercell vector %d has no length", a + 1);
+        int n = 0;
+        double R = dist(1.0);
+        while (R < 2.0 * Rc) {
+            n++;
+            R = dist((double)n);
+            if (n > 64) XTB_FAIL(c, XTB_EINVAL, "vdW: more than 64 images of the supercell along axis %d (R_cut = %g A)", a + 1, Rc);
+        }
+        if (n < 1) n = 1;
+        N[a] = n;
+        cells *= 2 * n + 1;
+    }
+    if (cells > 100000) XTB_FAIL(c, XTB_EINVAL, "vdW: %lld image cells (R_cut = %g A)", cells, Rc);
+    return XTB_OK;
+}
+
+// what: XTB_VDW_DO_* mask.  Energy of every atom on every rank (replicated, like the wall); forces and the supercell-force
+// partial sums of the owned atoms (exchanged / all-reduced by the caller when the context communicates).
+int xtb_impl_vdw(xtb_ctx* c, unsigned what) {
+    const int na = c->na, nown = c->a1 - c->a0;
+    int rc, N[3];
+    if ((rc = xtb_impl_vdw_cells(c, N, nullptr))) return rc;
+    c->vdw_cells[0] = N[0]; c->vdw_cells[1] = N[1]; c->vdw_cells[2] = N[2];
+    if ((rc = xtb_reserve(c, c->d_Evdw_at, sizeof(double) * na))) return rc;
+    if ((rc = xtb_reserve(c, c->d_Evdw, sizeof(double)))) return rc;
+    if ((rc = xtb_reserve(c, c->d_Fvdw, sizeof(double) * 3 * (size_t)(na + c->nranks)))) return rc;
+    if ((rc = xtb_reserve(c, c->d_SCvdw, sizeof(double) * 9))) return rc;
+    if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)(nown > 0 ? nown : 1)))) return rc;
+    XTB_T0(c, 17);
+    if ((rc = launch_atoms(c, c->a0, nown, what, N))) return rc;
+    if (what & DO_E) {
+        if ((rc = launch_atoms(c, 0, c->a0, DO_E, N)) || (rc = launch_atoms(c, c->a1, na - c->a1, DO_E, N))) return rc;
+        vdw_esum_kernel<<<1, 256, 0, c->stream>>>(na, (const double*)c->d_Evdw_at.p, (double*)c->d_Evdw.p);
+        XTB_LAUNCH_CHECK(c);
+    }
+    if (what & DO_P) {
+        if (nown > 0) {
+            vdw_sum9_kernel<<<9, 128, 0, c->stream>>>(nown, (const double*)c->d_ppart.p, (double*)c->d_SCvdw.p);
+            XTB_LAUNCH_CHECK(c);
+        } else XTB_CUDA(c, cudaMemsetAsync(c->d_SCvdw.p, 0, sizeof(double) * 9, c->stream));
+    }
+    XTB_T1(c, 17);
+    return xtb_stage_finish(c);
+}

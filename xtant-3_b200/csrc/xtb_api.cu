@@ -80,9 +80,10 @@ int xtb_impl_pressure(xtb_ctx* c) {
     XTB_FAIL(c, XTB_EINVAL, "pressure: no TB parametrisation set");
 }
 
-// pair terms of a fused step: Pettifor-type repulsive part and / or the short-range wall, whichever the context holds
+// pair terms of a fused step: Pettifor-type repulsive part, short-range wall, van der Waals term, whichever the context holds
 int xtb_impl_pair_terms(xtb_ctx* c, const xtb_step_io* io, bool pressure) {
-    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "pair terms: no neighbour list");
+    const bool list_terms = (c->tb == XTB_TB_PETTIFOR && !c->h_pet_rep.empty()) || !c->h_wall.empty();
+    if (list_terms && !c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "pair terms: no neighbour list");
     int rc;
     const size_t fb = sizeof(double) * 3 * c->na;
     const bool multi = c->comm && c->nranks > 1;
@@ -106,6 +107,16 @@ int xtb_impl_pair_terms(xtb_ctx* c, const xtb_step_io* io, bool pressure) {
             if ((rc = xtb_impl_wall_pressure(c))) return rc;
             if (multi && (rc = xtb_impl_allreduce9(c, (double*)c->d_SCwall.p))) return rc;
             if (io && io->SCforce_wall) XTB_CUDA(c, cudaMemcpyAsync(io->SCforce_wall, c->d_SCwall.p, 72, cudaMemcpyDeviceToHost, c->stream));
+        }
+    }
+    if (!c->h_vdw.empty()) {
+        if ((rc = xtb_impl_vdw(c, pressure ? 7u : 3u))) return rc;          // energy, forces [, supercell force] in one pass
+        if (multi && (rc = xtb_impl_exchange_forces(c, c->d_Fvdw))) return rc;
+        if (io && io->E_vdw) XTB_CUDA(c, cudaMemcpyAsync(io->E_vdw, c->d_Evdw.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        if (io && io->F_vdw) XTB_CUDA(c, cudaMemcpyAsync(io->F_vdw, c->d_Fvdw.p, fb, cudaMemcpyDeviceToHost, c->stream));
+        if (pressure) {
+            if (multi && (rc = xtb_impl_allreduce9(c, (double*)c->d_SCvdw.p))) return rc;
+            if (io && io->SCforce_vdw) XTB_CUDA(c, cudaMemcpyAsync(io->SCforce_vdw, c->d_SCvdw.p, 72, cudaMemcpyDeviceToHost, c->stream));
         }
     }
     return XTB_OK;
@@ -157,7 +168,8 @@ int xtb_destroy(xtb_ctx* c) {
                      &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
                      &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep,
                      &c->d_halo_tr, &c->d_halo_cnt, &c->d_halo_slots, &c->d_halo_send, &c->d_halo_recv, &c->d_wall_params, &c->d_Ewall_at, &c->d_Ewall,
-                     &c->d_Fwall, &c->d_SCwall, &c->d_prev_size, &c->d_prev_list, &c->d_dense_out, &c->d_fermi, &c->d_S0, &c->d_SV, &c->d_SV0, &c->d_mdpar};
+                     &c->d_Fwall, &c->d_SCwall, &c->d_prev_size, &c->d_prev_list, &c->d_dense_out, &c->d_fermi, &c->d_S0, &c->d_SV, &c->d_SV0, &c->d_mdpar,
+                     &c->d_vdw_params, &c->d_Evdw_at, &c->d_Evdw, &c->d_Fvdw, &c->d_SCvdw};
     for (DevBuf* b : all) xtb_free(*b);
     for (int s = 0; s < 24; ++s) for (int k = 0; k < 2; ++k) if (c->tev[s][k]) cudaEventDestroy(c->tev[s][k]);
     if (c->h_meta) cudaFreeHost(c->h_meta);
@@ -784,6 +796,81 @@ int xtb_wall_pressure(xtb_ctx* c, double* SCforce_wall) {
     return XTB_OK;
 }
 
+// ---- van der Waals term (third part) ----
+int xtb_set_params_vdw(xtb_ctx* c, int kind, int n_kinds, const xtb_vdw_pair* p) {
+    if (!c) return XTB_EINVAL;
+    if (c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_set_params_vdw: set the TB parameters first");
+    if (n_kinds == 0 || !p) { c->h_vdw.clear(); c->vdw_kind = 0; return XTB_OK; }          // "proceeding without van der Waals forces"
+    if (kind != XTB_VDW_GIRIFALCO && kind != XTB_VDW_LJ_CUT && kind != XTB_VDW_ILJ_CUT)
+        XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_vdw: class %d (1 Girifalco, 2 LJ_cut, 3 ILJ_cut)", kind);
+    if (n_kinds != c->n_kinds) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_vdw: n_kinds=%d (TB part has %d)", n_kinds, c->n_kinds);
+    cudaSetDevice(c->device);
+    const size_t cnt = (size_t)n_kinds * n_kinds;
+    c->h_vdw.assign(p, p + cnt);
+    c->vdw_kind = kind;
+    c->vdw_sym = true;
+    for (int a = 0; a < n_kinds; ++a)
+        for (int b = 0; b < a; ++b)
+            if (memcmp(&p[a + n_kinds * b], &p[b + n_kinds * a], sizeof(xtb_vdw_pair)) != 0) c->vdw_sym = false;
+    int rc = xtb_reserve(c, c->d_vdw_params, sizeof(xtb_vdw_pair) * cnt);
+    if (rc) return rc;
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_vdw_params.p, p, sizeof(xtb_vdw_pair) * cnt, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+static int vdw_ready(xtb_ctx* c, const char* who) {
+    if (c->h_vdw.empty()) XTB_FAIL(c, XTB_ESTATE, "%s: no vdW parameters (xtb_set_params_vdw)", who);
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "%s: no system set", who);
+    return XTB_OK;
+}
+
+int xtb_vdw_image_cells(xtb_ctx* c, int* N, double* R_cut) {
+    if (!c || !N) return XTB_EINVAL;
+    int rc;
+    if ((rc = vdw_ready(c, "xtb_vdw_image_cells"))) return rc;
+    return xtb_impl_vdw_cells(c, N, R_cut);
+}
+
+int xtb_vdw_energy(xtb_ctx* c, double* E_vdw, double* Epot) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = vdw_ready(c, "xtb_vdw_energy"))) return rc;
+    if ((rc = xtb_impl_vdw(c, 1u))) return rc;
+    if (E_vdw) XTB_CUDA(c, cudaMemcpyAsync(E_vdw, c->d_Evdw.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (Epot) XTB_CUDA(c, cudaMemcpyAsync(Epot, c->d_Evdw_at.p, sizeof(double) * c->na, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_vdw_forces(xtb_ctx* c, double* F_vdw) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = vdw_ready(c, "xtb_vdw_forces"))) return rc;
+    if ((rc = xtb_impl_vdw(c, 2u))) return rc;
+    const size_t cnt = 3 * (size_t)(c->a1 - c->a0);
+    if (F_vdw && cnt) {
+        XTB_CUDA(c, cudaMemcpyAsync(F_vdw + 3 * (size_t)c->a0, (double*)c->d_Fvdw.p + 3 * (size_t)c->a0, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
+int xtb_vdw_pressure(xtb_ctx* c, double* SCforce_vdw) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = vdw_ready(c, "xtb_vdw_pressure"))) return rc;
+    if ((rc = xtb_impl_vdw(c, 4u))) return rc;
+    if (SCforce_vdw) {
+        XTB_CUDA(c, cudaMemcpyAsync(SCforce_vdw, c->d_SCvdw.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
 int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
     if (!c || !dptr) return XTB_EINVAL;
     const size_t N = (size_t)c->na * c->n_orb;
@@ -804,6 +891,7 @@ int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
         case XTB_BUF_FREP: b = &c->d_Frep; used = 24 * (size_t)c->na; break;
         case XTB_BUF_MIJ: b = &c->d_cpl_M; used = 8 * N * N; break;
         case XTB_BUF_FWALL: b = &c->d_Fwall; used = 24 * (size_t)c->na; break;
+        case XTB_BUF_FVDW: b = &c->d_Fvdw; used = 24 * (size_t)c->na; break;
         case XTB_BUF_POS: b = &c->d_S; used = 24 * (size_t)c->na; break;
         case XTB_BUF_VEL: b = &c->d_SV; used = 24 * (size_t)c->na; break;
         case XTB_BUF_EI: if (!c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: no eigenvalues"); *dptr = (void*)c->d_Ei; if (bytes) *bytes = 8 * N; return XTB_OK;

@@ -103,6 +103,12 @@ struct xtb_ctx {
     // short-range wall (wall.cu)
     std::vector<xtb_wall_pair> h_wall;     // empty: no wall set
     DevBuf d_wall_params, d_Ewall_at, d_Ewall, d_Fwall, d_SCwall;
+    // van der Waals term (vdw.cu)
+    std::vector<xtb_vdw_pair> h_vdw;       // empty: no vdW term set
+    int vdw_kind = 0;                      // XTB_VDW_*
+    bool vdw_sym = true;                   // TB_Waals(k1,k2) == TB_Waals(k2,k1) bit for bit
+    int vdw_cells[3] = {0, 0, 0};          // image counts of the last launch
+    DevBuf d_vdw_params, d_Evdw_at, d_Evdw, d_Fvdw, d_SCvdw;
     // Fermi occupations and velocity-Verlet state (step.cu)
     DevBuf d_fermi;                        // {mu, N(mu), sum f E, iterations}
     DevBuf d_S0, d_SV, d_SV0, d_mdpar;
@@ -198,6 +204,8 @@ int xtb_impl_mirror_density(xtb_ctx* c);             // rows of the owned atoms 
 int xtb_impl_wall_energy(xtb_ctx* c);                // wall.cu
 int xtb_impl_wall_forces(xtb_ctx* c);
 int xtb_impl_wall_pressure(xtb_ctx* c);
+int xtb_impl_vdw_cells(xtb_ctx* c, int N[3], double* R_cut);   // vdw.cu: get_mirror_cell_num on the host
+int xtb_impl_vdw(xtb_ctx* c, unsigned what);         // what: 1 energy | 2 forces | 4 supercell force, one pass
 int xtb_impl_fermi(xtb_ctx* c, double n_electrons, double Te_eV);     // step.cu
 int xtb_impl_assemble(xtb_ctx* c, bool dense);       // xtb_api.cu: dispatch on the TB branch (the `select type` arms)
 int xtb_impl_forces(xtb_ctx* c);

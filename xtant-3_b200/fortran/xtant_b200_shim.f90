@@ -23,7 +23,8 @@
 module XTANT_B200_shim
 use, intrinsic :: iso_c_binding
 use Objects, only : Super_cell, Numerics_param, solid, Error_handling, Save_error_details, &
-                    TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor, TB_H_DFTB, TB_Rep_DFTB, TB_Exp_wall_simple
+                    TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor, TB_H_DFTB, TB_Rep_DFTB, TB_Exp_wall_simple, &
+                    TB_vdW, TB_vdW_Girifalco, TB_vdW_LJ_cut, TB_vdW_ILJ_cut
 implicit none
 private
 public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_Aij, Construct_Aij_x_En, &
@@ -32,7 +33,7 @@ public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_
           Construct_Vij_DFTB, construct_TB_H_DFTB, get_dHij_drij_DFTB, Attract_TB_Forces_Press_DFTB, &
           Electron_ion_coupling_Mij, xtb_b200_set_partition, xtb_b200_assemble_blocks, xtb_b200_expand_dense, &
           xtb_b200_density_mirror, xtb_b200_eigensolve, &
-          get_Exp_wall_s, d_Exp_wall_pot_s, d_Exp_wall_Pressure_s, xtb_b200_comm_init, xtb_b200_exchange_blocks, &
+          get_Exp_wall_s, d_Exp_wall_pot_s, d_Exp_wall_Pressure_s, get_vdW_s, vdW_forces, get_mirror_cell_num, xtb_b200_comm_init, xtb_b200_exchange_blocks, &
           xtb_b200_exchange_forces, xtb_b200_allreduce_scforce, xtb_b200_step, xtb_b200_fermi, xtb_b200_md_half_step, &
           xtb_b200_md_set_velocities, xtb_b200_md_get_state, xtb_b200_check_pending, xtb_b200_dense_density
 
@@ -67,15 +68,25 @@ type, bind(C) :: xtb_wall_pair              ! type(TB_Exp_wall_simple), Objects.
    real(c_double) :: C, r0, d0, dd
 end type xtb_wall_pair
 
+type, bind(C) :: xtb_vdw_pair               ! class(TB_vdW) Objects.f90:43-46 + Girifalco :302-328 / LJ_cut :336-343 / ILJ_cut :346-354
+   real(c_double) :: d0_cut, dd_cut
+   real(c_double) :: C12, C6, dm, d_cut, a, b, c, d
+   real(c_double) :: dsm, ds_cut, as, bs, cs, ds, es, fs
+   real(c_double) :: eps, r0, n, m
+   real(c_double) :: d0_short, dd_short
+end type xtb_vdw_pair
+
 type, bind(C) :: xtb_step_io                ! struct xtb_step_io (include/xtb_b200.h); c_null_ptr = not given / keep on the device
    type(c_ptr) :: S, supce, fe
    real(c_double) :: n_electrons, Te_eV
    type(c_ptr) :: Ei, fe_out, mu, E_band, F_att, SCforce_att
    type(c_ptr) :: E_rep, F_rep, SCforce_rep
    type(c_ptr) :: E_wall, F_wall, SCforce_wall
+   type(c_ptr) :: E_vdw, F_vdw, SCforce_vdw
 end type xtb_step_io
 
 type(c_ptr), save :: ctx = c_null_ptr      ! one context per process (single caller thread, TB.f90:227-272)
+logical, save :: vdw_active = .false.       ! a usable class(TB_vdW) was pushed (push_params_vdw)
 logical, save :: eigen_current = .false.   ! Ha, Ei of this step already on the device (uploaded once, by construct_TB_H_*)
 logical, save :: density_current = .false. ! rho and rho_E of this step already contracted (ONE pass serves Construct_Aij and _x_En)
 type(c_ptr), save :: ha_loc = c_null_ptr   ! address of the Ha that was uploaded
@@ -200,6 +211,21 @@ interface
    end function
    integer(c_int) function xtb_wall_pressure(c, P_wall) bind(C, name="xtb_wall_pressure")
       import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_wall(3,3)
+   end function
+   integer(c_int) function xtb_set_params_vdw(c, kind, n_kinds, p) bind(C, name="xtb_set_params_vdw")
+      import; type(c_ptr), value :: c; integer(c_int), value :: kind, n_kinds; type(c_ptr), value :: p   ! c_null_ptr with n_kinds = 0: no vdW
+   end function
+   integer(c_int) function xtb_vdw_image_cells(c, N, R_cut) bind(C, name="xtb_vdw_image_cells")
+      import; type(c_ptr), value :: c; integer(c_int), intent(out) :: N(3); real(c_double), intent(out) :: R_cut
+   end function
+   integer(c_int) function xtb_vdw_energy(c, E_vdw, Epot) bind(C, name="xtb_vdw_energy")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: E_vdw; real(c_double), intent(out) :: Epot(*)
+   end function
+   integer(c_int) function xtb_vdw_forces(c, F_vdw) bind(C, name="xtb_vdw_forces")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: F_vdw(3,*)
+   end function
+   integer(c_int) function xtb_vdw_pressure(c, P_vdw) bind(C, name="xtb_vdw_pressure")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_vdw(3,3)
    end function
    integer(c_int) function xtb_fermi_occupations(c, n_electrons, Te_eV, fe, mu, E_band) bind(C, name="xtb_fermi_occupations")
       import; type(c_ptr), value :: c; real(c_double), value :: n_electrons, Te_eV; type(c_ptr), value :: fe, mu, E_band
@@ -403,6 +429,7 @@ subroutine get_near_neighbours(Scell, numpar, include_vdW, dm)
             end select
          END ASSOCIATE
       endif
+      if (allocated(Scell(NSC)%TB_Waals)) call push_params_vdw(Scell(NSC)%TB_Waals)
       ! cut-off exactly as Atomic_tools.f90:570-641: the TB part (attractive, raised to the Pettifor repulsive dm) comes
       ! from the library, the arms it has no parameters for are applied here as the reference does
       call check(xtb_cutoff(ctx, rm), 'xtb_cutoff')
@@ -887,6 +914,116 @@ subroutine d_Exp_wall_Pressure_s(Scell, NSC, TB_Expwall, numpar)
       Scell(NSC)%SCforce%rep = Scell(NSC)%SCforce%rep + P                    ! :1381
    endif
 end subroutine d_Exp_wall_Pressure_s
+
+! ---- van der Waals term (Van_der_Waals.f90:132,158; vdW_forces TB.f90:3599 -> Construct_B, d_Forces_s, d_Forces_Pressure) --------
+subroutine push_params_vdw(TB)
+   class(TB_vdW), dimension(:,:), allocatable, intent(in) :: TB
+   type(xtb_vdw_pair), allocatable, target :: p(:)
+   integer :: nk, i, j, k
+   integer(c_int) :: kind
+   nk = size(TB,1)
+   allocate(p(nk*nk))
+   kind = 0_c_int
+   do j = 1, nk
+      do i = 1, nk
+         k = i + nk*(j-1)
+         p(k) = xtb_vdw_pair(0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, &
+                             0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0, 0.0d0)
+         p(k)%d0_cut = TB(i,j)%d0_cut ; p(k)%dd_cut = TB(i,j)%dd_cut
+      enddo
+   enddo
+   select type (TB)
+   type is (TB_vdW_Girifalco)
+      kind = 1_c_int
+      do j = 1, nk
+         do i = 1, nk
+            k = i + nk*(j-1)
+            p(k)%C12 = TB(i,j)%C12 ; p(k)%C6 = TB(i,j)%C6 ; p(k)%dm = TB(i,j)%dm ; p(k)%d_cut = TB(i,j)%d_cut
+            p(k)%a = TB(i,j)%a ; p(k)%b = TB(i,j)%b ; p(k)%c = TB(i,j)%c ; p(k)%d = TB(i,j)%d
+            p(k)%dsm = TB(i,j)%dsm ; p(k)%ds_cut = TB(i,j)%ds_cut
+            p(k)%as = TB(i,j)%as ; p(k)%bs = TB(i,j)%bs ; p(k)%cs = TB(i,j)%cs
+            p(k)%ds = TB(i,j)%ds ; p(k)%es = TB(i,j)%es ; p(k)%fs = TB(i,j)%fs
+         enddo
+      enddo
+   type is (TB_vdW_LJ_cut)
+      kind = 2_c_int
+      do j = 1, nk
+         do i = 1, nk
+            k = i + nk*(j-1)
+            p(k)%eps = TB(i,j)%eps ; p(k)%r0 = TB(i,j)%r0 ; p(k)%n = TB(i,j)%n
+            p(k)%d0_short = TB(i,j)%d0_short ; p(k)%dd_short = TB(i,j)%dd_short
+         enddo
+      enddo
+   type is (TB_vdW_ILJ_cut)
+      kind = 3_c_int
+      do j = 1, nk
+         do i = 1, nk
+            k = i + nk*(j-1)
+            p(k)%eps = TB(i,j)%eps ; p(k)%r0 = TB(i,j)%r0 ; p(k)%n = TB(i,j)%n ; p(k)%m = TB(i,j)%m
+            p(k)%d0_short = TB(i,j)%d0_short ; p(k)%dd_short = TB(i,j)%dd_short
+         enddo
+      enddo
+   end select
+   if (kind == 0_c_int) then        ! TB_vdW_Dumitrica: zero energy and zero force in the reference (Van_der_Waals.f90:598,621)
+      call check(xtb_set_params_vdw(ctx, 0_c_int, 0_c_int, c_null_ptr), 'xtb_set_params_vdw')
+   else
+      call check(xtb_set_params_vdw(ctx, kind, int(nk,c_int), c_loc(p)), 'xtb_set_params_vdw')
+   endif
+   vdw_active = kind /= 0_c_int
+end subroutine push_params_vdw
+
+subroutine get_mirror_cell_num(Scell, NSC, numpar, atoms, Nx, Ny, Nz)
+   use Objects, only : Atom
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(in) :: numpar
+   type(Atom), dimension(:), intent(in) :: atoms
+   integer, intent(out) :: Nx, Ny, Nz
+   integer(c_int) :: N(3)
+   real(c_double) :: R_cut
+   call check(xtb_vdw_image_cells(ctx, N, R_cut), 'xtb_vdw_image_cells')
+   Nx = N(1) ; Ny = N(2) ; Nz = N(3)
+end subroutine get_mirror_cell_num
+
+subroutine get_vdW_s(TB_Waals, Scell, NSC, numpar, a)
+   class(TB_vdW), dimension(:,:), allocatable, intent(in) :: TB_Waals
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), intent(out) :: a
+   real(c_double), allocatable :: Epot(:)
+   integer :: i, na
+   a = 0.0d0
+   if (.not. vdw_active) return     ! Dumitrica class: zero
+   na = size(Scell(NSC)%MDAtoms)
+   allocate(Epot(na))
+   call check(xtb_vdw_energy(ctx, a, Epot), 'xtb_vdw_energy')
+   do i = 1, na
+      Scell(NSC)%MDAtoms(i)%Epot = Scell(NSC)%MDAtoms(i)%Epot + Epot(i)      ! Van_der_Waals.f90:241 (the half is inside)
+   enddo
+end subroutine get_vdW_s
+
+subroutine vdW_forces(TB_Waals, Scell, NSC, numpar)      ! TB.f90:3599-3633
+   class(TB_vdW), allocatable, dimension(:,:), intent(in) :: TB_Waals
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(c_double), allocatable :: F(:,:)
+   real(c_double) :: P(3,3)
+   integer :: k, na
+   if (.not. allocated(TB_Waals)) return
+   if (.not. vdw_active) return
+   na = size(Scell(NSC)%MDatoms)
+   allocate(F(3,na))
+   call check(xtb_vdw_forces(ctx, F), 'xtb_vdw_forces')
+   do k = 1, na
+      Scell(NSC)%MDatoms(k)%forces%rep(:) = Scell(NSC)%MDatoms(k)%forces%rep(:) + F(:,k)    ! TB.f90:3777 (added to the repulsive part)
+   enddo
+   if (numpar%p_const) then         ! TB.f90:3800
+      call check(xtb_vdw_pressure(ctx, P), 'xtb_vdw_pressure')
+      Scell(NSC)%SCforce%rep = Scell(NSC)%SCforce%rep + P                                   ! TB.f90:3845
+   endif
+end subroutine vdW_forces
 
 ! ---- Fermi occupations / velocity-Verlet halves on the device (Electron_tools.f90:2660,1913; Atomic_tools.f90:1897) ---------
 subroutine xtb_b200_fermi(Netot, Te, fe, mu)

@@ -9,6 +9,8 @@ numeric token(s) of a line, Fortran `d` exponents) and returns the dict the C-AB
     read_Pettifor_TB_repulsive      Read_input_data.f90:2908-3056  ->  xtb_pettifor_rep_pair
     read_Exponential_wall_TB        Read_input_data.f90:1920-2040,2313-2356 -> xtb_wall_pair (class line must read exactly
                                     'Simple_wall'; e.g. the shipped 'Simple_wall:exclude' disables the wall, as in the reference)
+    read_vdW_TB                     Read_input_data.f90:1660-1840 + read_vdW_Girifalco_TB :2392-2574, read_vdW_LJ_TB :2576-2652,
+                                    read_vdW_ILJ_TB :2654-2716 -> (class, xtb_vdw_pair); the shipped 'Girifalco:exclude' disables it
     read_SAVE                       Dealing_with_output_files.f90:2120-2158 (writer) / Initial_configuration.f90:1594 (reader)
                                     SAVE_atoms.dat + SAVE_supercell.dat -> koa, S, supce
     read_unit_cell                  Unit_cell_equilibrium.txt + Unit_cell_atom_relative_coordinates.txt
@@ -111,6 +113,89 @@ def write_Exponential_wall_TB(path, p, enabled=True):
         f.write("Simple_wall\n" if enabled else "Simple_wall:exclude\n")
         for k, c in (("C", "C [eV]"), ("r0", "r0 [A]"), ("d0", "d0 [A]"), ("dd", "dd [A]")):
             f.write(f"{_f(p[k])}\t\t! {c}\n")
+
+
+_GIRIFALCO_ORDER = ("C12", "C6", "dm", "d_cut", "a", "b", "c", "d", "dsm", "ds_cut", "as", "bs", "cs", "ds", "es", "fs")
+_LJ_NAMES = ("LJ", "Lennar-Jones", "Lennard_Jones", "lj", "Lj", "LENNARD-JONES", "LENNARD_JONES", "lennard-jones", "lennard_jones")
+_ILJ_NAMES = ("ILJ", "ilj", "Improved_LJ", "Ilj", "improved_lj", "I_LJ", "i_lj")
+
+
+def _leading_numbers(line, most):
+    """what a list-directed `read(line,*) a, b, ...` would take: numeric tokens until the first that is not a number"""
+    out = []
+    for tok in line.replace(",", " ").split():
+        if len(out) == most:
+            break
+        try:
+            out.append(_num(tok))
+        except ValueError:
+            break
+    return out
+
+
+def read_vdW_TB(path):
+    """<El>_<El>_TB_vdW.txt (Read_input_data.f90:1709-1840): the first list-directed token names the class.
+      'Girifalco'                   -> ('Girifalco', dict of the 16 numbers in file order; d0_cut = d_cut, dd_cut = 0 as :1799-1800)
+      'LJ' (and spellings :1732)    -> ('LJ', eps, r0, n from the 'SE' / 'AB' / 'n-exp' form (:2611-2623), d0_short dd_short, d0_cut dd_cut)
+      'ILJ' (and spellings :1750)   -> ('ILJ', eps, r0, n, m (defaults 12, 6), d0_short dd_short, d0_cut dd_cut)
+    Any other token -- including the 'Girifalco:exclude' the reference ships for diamond, graphite, ... -- falls into
+    `case default`: the reference prints "Unknown TB-vdW parametrization class" and proceeds WITHOUT van der Waals forces; this
+    reader returns None.  'Dumitrica' ("UNFINISHED, DO NOT USE", returns zero energy and force) is refused."""
+    lines = _lines(path)
+    cls = lines[0].replace(",", " ").split()[0]
+    if cls == "Dumitrica":
+        raise NotImplementedError(f"{path}: class TB_vdW_Dumitrica is unfinished in the reference and not part of this graft")
+    if cls == "Girifalco":
+        v = [_num(lines[k].split()[0]) for k in range(1, 17)]
+        p = dict(zip(_GIRIFALCO_ORDER, v))
+        p["d0_cut"] = p["d_cut"]; p["dd_cut"] = 0.0
+        return "Girifalco", p
+    if cls in _LJ_NAMES:
+        form = lines[1].split()[0]
+        ab = _leading_numbers(lines[2], 3)
+        if len(ab) < 2:
+            raise ValueError(f"{path}: could not read the LJ coefficients")
+        A, B = ab[0], ab[1]
+        n = ab[2] if len(ab) == 3 else 6.0
+        p = {"eps": 0.0, "r0": 0.0, "n": n}                         # defaults :1742-1744 stay when the form is not recognised
+        if form in ("SE", "Se", "se", "sE", "Segma-E", "sigma-e", "SIGMA-E"):
+            p["eps"] = A / 8.0; p["r0"] = 2.0 ** 0.5 * B
+        elif form in ("AB", "Ab", "ab", "aB"):
+            p["eps"] = B ** 2 / (4.0 * A); p["r0"] = (A / B) ** (1.0 / 6.0)
+        elif form in ("n-exp", "N-exp", "N-Exp", "N-EXP"):
+            p["eps"] = A; p["r0"] = B
+        p["d0_short"], p["dd_short"] = _leading_numbers(lines[3], 2)
+        p["d0_cut"], p["dd_cut"] = _leading_numbers(lines[4], 2)
+        return "LJ", p
+    if cls in _ILJ_NAMES:
+        ab = _leading_numbers(lines[1], 4)
+        if len(ab) < 2:
+            raise ValueError(f"{path}: could not read the ILJ coefficients")
+        p = {"eps": ab[0], "r0": ab[1], "n": ab[2] if len(ab) > 2 else 12.0, "m": ab[3] if len(ab) > 3 else 6.0}
+        p["d0_short"], p["dd_short"] = _leading_numbers(lines[2], 2)
+        p["d0_cut"], p["dd_cut"] = _leading_numbers(lines[3], 2)
+        return "ILJ", p
+    return None
+
+
+def write_vdW_TB(path, kind, p, enabled=True):
+    with open(path, "w") as f:
+        if kind == "Girifalco":
+            f.write("Girifalco\n" if enabled else "Girifalco:exclude\n")
+            for k in _GIRIFALCO_ORDER:
+                f.write(f"{_f(p[k])}\t\t! {k}\n")
+        elif kind == "LJ":
+            f.write(("LJ\n" if enabled else "LJ:exclude\n") + "n-exp\n")
+            f.write(f"{_f(p['eps'])}\t{_f(p['r0'])}\t{_f(p['n'])}\t! epsylon, r0, n\n")
+            f.write(f"{_f(p['d0_short'])}\t{_f(p['dd_short'])}\t! d0_short, dd_short\n")
+            f.write(f"{_f(p['d0_cut'])}\t{_f(p['dd_cut'])}\t! d0_cut, dd_cut\n")
+        elif kind == "ILJ":
+            f.write("ILJ\n" if enabled else "ILJ:exclude\n")
+            f.write(f"{_f(p['eps'])}\t{_f(p['r0'])}\t{_f(p['n'])}\t{_f(p['m'])}\t! epsylon, r0, n, m\n")
+            f.write(f"{_f(p['d0_short'])}\t{_f(p['dd_short'])}\t! d0_short, dd_short\n")
+            f.write(f"{_f(p['d0_cut'])}\t{_f(p['dd_cut'])}\t! d0_cut, dd_cut\n")
+        else:
+            raise ValueError(kind)
 
 
 def read_SAVE(atoms_path, cell_path):

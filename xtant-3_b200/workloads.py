@@ -71,9 +71,23 @@ def al500():       # config 3 (triclinic cell from the reference's SAVE files)
     return _from_cell("al500", "nrl", "Al", "cell_al500.json", 3, 1000.0 * K_B_EV)
 
 
+def with_vdw(wl, setname):
+    """attach Scell%TB_Waals from xtant-3_b200/data/params_vdw_<setname>.json (one kind of atom)"""
+    p = dict(_load(f"params_vdw_{setname}.json"))
+    wl["vdw_kind"] = p.pop("kind")
+    wl["vdw_params"] = [p]
+    return wl
+
+
 def ac1000():      # config 4
+    """The reference's amorphous-carbon folder (INPUT_DATA/Amorphous_Carbon) is the Diamond Pettifor set plus an ACTIVE
+    Girifalco van der Waals file (its class line carries no ':exclude'), so this configuration runs with the vdW term."""
     S, h = lattice(_DIA, 3.5588, (5, 5, 5), 0.25, 1000)
-    return _wl("ac1000", "pettifor", "C", S, h, 4, 1.0)
+    return with_vdw(_wl("ac1000", "pettifor", "C", S, h, 4, 1.0), "C_amorphous")
+
+
+def ac216():       # the reference's own 216-atom amorphous-carbon cell (INPUT_DATA/Amorphous_Carbon/SAVE_*.dat), with its vdW term
+    return with_vdw(_from_cell("ac216", "pettifor", "C", "cell_ac216.json", 4, 1.0), "C_amorphous")
 
 
 def au4096():      # config 5 (north star): 8 x 8 x 16 conventional cells
