@@ -397,6 +397,8 @@ def small_configs(torch, api, abi, wk, reps=40):
       staged   xtb_neighbours, xtb_assemble_HS, xtb_density, xtb_forces one after the other (each waits for the device)
       step     xtb_step, eager (one wait per step, steady-state list)
       graph    xtb_step | XTB_STEP_GRAPH (the step's launch sequence replayed as one CUDA graph)
+      graph_with_pair_terms   the same plus XTB_STEP_PAIR_TERMS where the configuration has pair terms (`pair_terms`: the Pettifor
+               repulsive part; config 4 also the Girifalco van der Waals term its material folder ships) -- the complete force
     Eigenvectors: the configuration's own, from xtb_eigensolve once (outside the metric); occupations from the host."""
     out = {}
     for name in ("diamond64", "si216", "al500", "ac1000"):
@@ -416,7 +418,12 @@ def small_configs(torch, api, abi, wk, reps=40):
                 c._ck(c.lib.xtb_step(c.h, flags, None))
 
             res = {"na": wl["na"], "N": wl["na"] * c.n_orb, "tb": wl["tb"]}
-            for key, fn in (("staged", staged), ("step", lambda: fused(abi.STEP_ALL)), ("graph", lambda: fused(abi.STEP_ALL | abi.STEP_GRAPH))):
+            legs = [("staged", staged), ("step", lambda: fused(abi.STEP_ALL)), ("graph", lambda: fused(abi.STEP_ALL | abi.STEP_GRAPH))]
+            res["pair_terms"] = [k for k, on in (("repulsive", bool(wl.get("rep_params"))), ("wall", bool(wl.get("wall_params"))),
+                                                 ("vdw_" + str(wl.get("vdw_kind")), bool(wl.get("vdw_params")))) if on]
+            if res["pair_terms"]:
+                legs.append(("graph_with_pair_terms", lambda: fused(abi.STEP_ALL | abi.STEP_PAIR_TERMS | abi.STEP_GRAPH)))
+            for key, fn in legs:
                 for _ in range(4):
                     fn()
                 c.sync()
@@ -428,6 +435,8 @@ def small_configs(torch, api, abi, wk, reps=40):
                 res[key + "_ms"] = (time.perf_counter() - t0) * 1e3 / reps
                 res[key + "_launches"] = (c.counter(6) - l0) / reps
             res["graph_device_ms"] = c.stage_ms(0)
+            if wl.get("vdw_params"):
+                res["vdw_ms"] = c.stage_ms(17) if c.stage_ms(17) > 0 else None      # eager legs only: no events inside a graph
             res["graphs_captured"] = c.counter(16)
             out[name] = res
         except Exception as ex:      # a parity-test case must not take the headline line down
