@@ -113,6 +113,15 @@ typedef struct xtb_vdw_pair {
     double d0_short, dd_short;                   /* [A] short-range cut-off radius and width */
 } xtb_vdw_pair;
 
+/* type(TB_Coulomb_cut), Objects.f90:359-366 (reader Read_input_data.f90:1874-1910, 2360-2386): V(r) = k Q^2 / r / (1 + exp((r - dm) / dd)),
+ * zero beyond dm + 10 dd; k = g_e / (4 pi g_e0) * 1e10 [eV A] is set by the reader.  (`ind`, `alpha` select the Wolf / Ewald forms of
+ * the SCC part, Coulomb.f90:69-164, which this path does not reach.) */
+typedef struct xtb_coulomb_pair {
+    double k;     /* [eV A] coupling constant */
+    double dm;    /* [A] cut-off radius */
+    double dd;    /* [A] cut-off smoothing width */
+} xtb_coulomb_pair;
+
 typedef struct xtb_ctx xtb_ctx;
 
 /* ---- life cycle ------------------------------------------------------------------- */
@@ -267,6 +276,22 @@ int  xtb_vdw_energy  (xtb_ctx*, double* E_vdw, double* Epot);
 int  xtb_vdw_forces  (xtb_ctx*, double* F_vdw);
 int  xtb_vdw_pressure(xtb_ctx*, double SCforce_vdw[9]);
 
+/* ---- SURVEY.md 8f item 2, fourth part: the Coulomb term of a charged supercell (class TB_Coulomb_cut; Coulomb.f90, dispatch
+ *      Coulomb_forces TB.f90:3560-3596 / Coulomb_s TB.f90:3995-4012).  Same all-pairs-in-image-cells structure as the van der Waals
+ *      term and the same d_Forces_s / d_Forces_Pressure, with the reference's differences kept: image counts from
+ *      R_cut = TB_Coul(1,1)%dm alone (get_mirror_cell_num_C :435-452); the energy is NOT halved (get_Coulomb_s :549, Epot(i) gets the
+ *      full sum); Construct_B_C contracts the distance with the TRANSPOSE of supce (:864-866) and returns zero forces when
+ *      Q <= 1e-12 (:762).  Q = Scell%Q, the mean unbalanced charge per atom [e], changes from step to step: xtb_set_charge.
+ *      xtb_coulomb_energy    get_Coulomb_s   (Coulomb.f90:454-550): E_coul [eV]; Epot(na) = what is added to MDAtoms(:)%Epot
+ *      xtb_coulomb_forces    Construct_B_C + d_Forces_s (:715-880, TB.f90:3638): the term ADDED to forces%rep, F_coul(3,na)
+ *      xtb_coulomb_pressure  d_Forces_Pressure (TB.f90:3785): the term ADDED to Scell%SCforce%rep(3,3) */
+int  xtb_set_params_coulomb(xtb_ctx*, int n_kinds, const xtb_coulomb_pair* p);
+int  xtb_set_charge(xtb_ctx*, double Q);
+int  xtb_coulomb_image_cells(xtb_ctx*, int N[3]);
+int  xtb_coulomb_energy  (xtb_ctx*, double* E_coul, double* Epot);
+int  xtb_coulomb_forces  (xtb_ctx*, double* F_coul);
+int  xtb_coulomb_pressure(xtb_ctx*, double SCforce_coul[9]);
+
 /* ---- Fermi occupations on the device (between the eigensolve and S3; lets a step stay on the device):
  *      Electron_Fixed_Te (Electron_tools.f90:2660-2706: bisection of mu at fixed Te until |N(mu) - Ne| <= 1e-12 Ne) +
  *      set_Fermi (:1913-1969), spin-degenerate (f_norm = 2).  Uses the eigenvalues on the device (xtb_eigensolve or
@@ -284,6 +309,7 @@ int  xtb_fermi_occupations(xtb_ctx*, double n_electrons, double Te_eV, double* f
 #define XTB_FORCE_REP   2u   /* XTB_BUF_FREP    (xtb_repulsive_forces) */
 #define XTB_FORCE_WALL  4u   /* XTB_BUF_FWALL   (xtb_wall_forces) */
 #define XTB_FORCE_VDW   8u   /* XTB_BUF_FVDW    (xtb_vdw_forces) */
+#define XTB_FORCE_COUL 16u   /* XTB_BUF_FCOUL   (xtb_coulomb_forces) */
 int  xtb_md_set_velocities(xtb_ctx*, const double* SV /*[3*na] relative velocities [1/fs]; NULL = zero*/);
 int  xtb_md_half_step(xtb_ctx*, int ind, double dt_fs, const double* mass_kg, const double* Vsupce, unsigned force_terms);
 int  xtb_md_get_state(xtb_ctx*, double* S, double* SV, double* E_kin /*[eV]*/, const double* mass_kg /*for E_kin*/);
@@ -324,7 +350,7 @@ int  xtb_allreduce_scforce(xtb_ctx*, double SCforce_att[9] /*or NULL*/);
 #define XTB_STEP_DENSITY      8u    /* rho, rho_E [+ halo exchange + mirror] */
 #define XTB_STEP_FORCES      16u    /* attractive forces [+ all-gather] */
 #define XTB_STEP_PRESSURE    32u    /* supercell force [+ all-reduce] (also of the pair terms when XTB_STEP_PAIR_TERMS) */
-#define XTB_STEP_PAIR_TERMS  64u    /* repulsive part of the Pettifor branch, the short-range wall and the van der Waals term, whichever are set */
+#define XTB_STEP_PAIR_TERMS  64u    /* repulsive part of the Pettifor branch, the short-range wall and the van der Waals term, and the Coulomb term, whichever are set */
 #define XTB_STEP_NO_DENSE   128u    /* with XTB_STEP_HS: block stores only */
 #define XTB_STEP_GRAPH      256u    /* single GPU, no XTB_STEP_EIGEN / new occupations: once a steady step with the same flags has
                                        run, replay its launch sequence as ONE CUDA graph (launch-bound small systems); host
@@ -345,6 +371,7 @@ typedef struct xtb_step_io {
     double* E_rep;  double* F_rep;  double* SCforce_rep;      /* out: Pettifor repulsive part */
     double* E_wall; double* F_wall; double* SCforce_wall;     /* out: short-range wall */
     double* E_vdw;  double* F_vdw;  double* SCforce_vdw;      /* out: van der Waals term */
+    double* E_coul; double* F_coul; double* SCforce_coul;     /* out: Coulomb term */
 } xtb_step_io;
 int  xtb_step(xtb_ctx*, unsigned flags, const xtb_step_io* io);
 
@@ -380,6 +407,7 @@ int  xtb_coupling       (xtb_ctx*, int kind_M, double* Mij);
 #define XTB_BUF_EI      17   /* (N) eigenvalues */
 #define XTB_BUF_FE      18   /* (N) occupations */
 #define XTB_BUF_FVDW    19   /* (3,na) van der Waals forces */
+#define XTB_BUF_FCOUL   20   /* (3,na) Coulomb forces */
 int  xtb_device_buffer(xtb_ctx*, int which, void** dptr, size_t* bytes);
 /* counters: 0 na, 1 n_orb, 2 N, 3 max_nn, 4 n_blocks (incl. on-site), 5 n_pairs (directed),
  *           6 kernels launched since create, 7 states kept by the last xtb_density, 8 cap,
@@ -394,7 +422,7 @@ long long xtb_counter(const xtb_ctx*, int which);
  * 9 pair-term energy + forces (repulsive / wall), 10 pair-term pressure, 11 xtb_coupling (12 / 13: its norms + S*Ha part / its DGEMM),
  * 14 H/S block exchange, 15 rho block exchange (xtb_counter 12 / 13: bytes received per rank by each),
  * 0 the last graph replay of xtb_step as a whole (xtb_counter 16: graphs captured so far),
- * 16 the eigenvector re-tiling kernel alone (inside 3).  Stage 6 is the dense H_non / Sij update: the matrices stay resident and
+ * 16 the eigenvector re-tiling kernel alone (inside 3), 17 van der Waals term, 18 Coulomb term (energy / forces / supercell force of one call).  Stage 6 is the dense H_non / Sij update: the matrices stay resident and
  * only the blocks of the previous and of the new pattern are touched (XTB_DENSE_FULL=1: every element, every step) */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 

@@ -254,6 +254,54 @@ def vdw_pressure(wl, N):
     return P.reshape(3, 3, order="F")
 
 
+# ---- Coulomb term of a charged supercell (Coulomb.f90, class TB_Coulomb_cut): same loops, kind 4 of vdw_oracle.c ----
+_COULOMB = 4
+
+
+def _coulomb_table(wl):
+    """the record the C side evaluates: eps = k*Q*Q (left to right, Coulomb_potential), d0_cut = dm, dd_cut = dd"""
+    Q = float(wl.get("Q", 0.0))
+    return vdw_params_array([{"eps": float(p.get("k", _abi.COULOMB_K)) * Q * Q, "d0_cut": p["dm"], "dd_cut": p["dd"]} for p in wl["coulomb_params"]])
+
+
+def coulomb_cells(wl):
+    """get_mirror_cell_num_C, Coulomb.f90:435-452 -> (Nx, Ny, Nz)"""
+    S, h = _vdw_geom(wl)
+    N = np.zeros(3, dtype=np.int32)
+    lib().orc_coulomb_cells(C.c_double(float(wl["coulomb_params"][0]["dm"])), _p(S), _p(h), _p(N))
+    return tuple(int(x) for x in N)
+
+
+def coulomb_energy(wl, N):
+    """get_Coulomb_s, Coulomb.f90:454-550 -> (E_coul (not halved, as written), amounts added to Epot)"""
+    S, h = _vdw_geom(wl)
+    Epot = np.zeros(len(S)); Nc = np.asarray(N, dtype=np.int32)
+    E = lib().orc_vdw_energy(C.c_int(len(S)), C.c_int(_COULOMB), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(S), _p(h), _coulomb_table(wl), _p(Nc), _p(Epot))
+    return float(E), Epot
+
+
+def coulomb_forces(wl, N, literal=False):
+    """Coulomb_forces -> Construct_B_C + d_Forces_s (TB.f90:3560-3596,3638-3781); zero when Q <= 1e-12 (Coulomb.f90:762)"""
+    S, h = _vdw_geom(wl)
+    F = np.zeros((len(S), 3)); Nc = np.asarray(N, dtype=np.int32)
+    if float(wl.get("Q", 0.0)) <= 1.0e-12:
+        return F
+    rc = lib().orc_vdw_forces(C.c_int(len(S)), C.c_int(_COULOMB), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(S), _p(h), _coulomb_table(wl), _p(Nc),
+                              C.c_int(1 if literal else 0), _p(F))
+    if rc:
+        raise MemoryError("orc_vdw_forces")
+    return F
+
+
+def coulomb_pressure(wl, N):
+    """Coulomb_forces -> d_Forces_Pressure (TB.f90:3785-3848); zero when Q <= 1e-12"""
+    S, h = _vdw_geom(wl)
+    P = np.zeros(9); Nc = np.asarray(N, dtype=np.int32)
+    if float(wl.get("Q", 0.0)) > 1.0e-12:
+        lib().orc_vdw_pressure(C.c_int(len(S)), C.c_int(_COULOMB), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(S), _p(h), _coulomb_table(wl), _p(Nc), _p(P))
+    return P.reshape(3, 3, order="F")
+
+
 def wall_energy(wl, nb):
     """get_Exp_wall_s, Exponential_wall.f90:990-1067 -> (E_wall, per-atom halves added to Epot)"""
     Epot = np.zeros(nb.na)

@@ -1,5 +1,5 @@
-/* ORACLE (test infrastructure; included by xtant_oracle.c) -- van der Waals pair term (class TB_vdW), restated statement
- * by statement from the reference:
+/* ORACLE (test infrastructure; included by xtant_oracle.c) -- van der Waals pair term (class TB_vdW) and Coulomb term of a
+ * charged supercell (class TB_Coulomb_cut), restated statement by statement from the reference:
  *   Source_files/Van_der_Waals.f90   get_mirror_cell_num :132-157, get_vdW_s :158-250 (OpenMP arm :223-246), Construct_B :251-284,
  *                                    cell_cycle_B :287-421 (OpenMP arm :384-420), vdW_energy :578-604, dvdW :608-627,
  *                                    double_truncated_LJ :650-660, d_double_truncated_LJ :663-675, ILJ :718-727, d_ILJ :730-745,
@@ -9,6 +9,11 @@
  *   Source_files/TB.f90              vdW_forces :3599-3633, d_Forces_s :3638-3781 (OpenMP arm :3727-3778), d_Forces_Pressure :3785-3848
  *   Source_files/Atomic_tools.f90    get_near_neighbours (vdW arm) :636-641, get_number_of_image_cells :654-702,
  *                                    distance_to_given_cell_0 :4135-4166
+ *   Source_files/Coulomb.f90         get_mirror_cell_num_C :435-452, get_Coulomb_s :454-550 (OpenMP arm :526-547: a = sum_a, NOT halved),
+ *                                    Coulomb_pot :552-587, Coulomb_potential :589-594, d_Coulomb_potential :596-601, f_cut_L_C :610-614,
+ *                                    d_f_cut_L_C :617-629 (both restated in wall_oracle.c), dCoulomb :641-672, Construct_B_C :715-880
+ *                                    (zero arrays for Q <= 1e-12 :762; XijSupce contracted with the TRANSPOSE of supce :864-866);
+ *                                    TB.f90 Coulomb_forces :3560-3596 -> the same d_Forces_s / d_Forces_Pressure
  *   Source_files/Little_subroutines.f90   Fermi_function :349-357, d_Fermi_function :360-381, fast_pow :436-516, count_3d
  * The reference has no test, fixture or golden vector for this term and there is no Fortran compiler here: PARITY UNPINNED, like
  * the rest of oracle/ (see the header of xtant_oracle.c).  What pins it instead (tests/test_vdw_cpu.py): the shipped Girifalco
@@ -83,9 +88,26 @@ static double vdw_d_truncate(const xtb_vdw_pair* W, double V_LJ, double d_V_LJ, 
     const double d_f_short = -vdw_d_Fermi_function(W->d0_short, W->dd_short, a_r);
     return V_LJ * (d_f_short * f_long + f_short * d_f_long) + d_V_LJ * (f_short * f_long);
 }
+/* class TB_Coulomb_cut rides on the same record: eps = k*Q*Q (Coulomb_potential's k*Q1*Q2), d0_cut = dm, dd_cut = dd */
+#define ORC_KIND_COULOMB 4
+static double coul_Coulomb_pot(const xtb_vdw_pair* W, double a_r) {
+    if (a_r > W->d0_cut + W->dd_cut * 10.0) return 0.0;
+    const double f_cut_large = wall_f_cut_L_C(a_r, W->d0_cut, W->dd_cut);
+    return W->eps / a_r * f_cut_large;
+}
+static double coul_dCoulomb(const xtb_vdw_pair* W, double a_r) {
+    if (a_r > W->d0_cut + W->dd_cut * 10.0) return 0.0;
+    const double f_cut_large = wall_f_cut_L_C(a_r, W->d0_cut, W->dd_cut);
+    const double E_C = W->eps / a_r;
+    const double d_E_C = -W->eps / (a_r * a_r);
+    const double d_f_large = wall_d_f_cut_L_C(a_r, W->d0_cut, W->dd_cut);
+    return d_E_C * f_cut_large + E_C * d_f_large;
+}
+
 /* vdW_energy: `select type`; the caller passes TB_Waals(KOAi, KOAj) */
 static double vdw_energy_one(int kind, const xtb_vdw_pair* W, double a_r) {
     switch (kind) {
+        case ORC_KIND_COULOMB:  return coul_Coulomb_pot(W, a_r);
         case XTB_VDW_GIRIFALCO: return vdw_Girifalco(W, a_r);
         case XTB_VDW_LJ_CUT:    return vdw_truncate(W, vdw_General_LJ(W->eps, W->r0, W->n, a_r), a_r);
         case XTB_VDW_ILJ_CUT:   return vdw_truncate(W, vdw_Improved_LJ(W->eps, W->r0, W->n, W->m, a_r), a_r);
@@ -95,6 +117,7 @@ static double vdw_energy_one(int kind, const xtb_vdw_pair* W, double a_r) {
 /* dvdW: the caller passes TB_Waals(KOA1, KOA2) */
 static double vdw_dvdW(int kind, const xtb_vdw_pair* W, double a_r) {
     switch (kind) {
+        case ORC_KIND_COULOMB:  return coul_dCoulomb(W, a_r);
         case XTB_VDW_GIRIFALCO: return vdw_d_Girifalco(W, a_r);
         case XTB_VDW_LJ_CUT:    return vdw_d_truncate(W, vdw_General_LJ(W->eps, W->r0, W->n, a_r), vdw_d_General_LJ(W->eps, W->r0, W->n, a_r), a_r);
         case XTB_VDW_ILJ_CUT:   return vdw_d_truncate(W, vdw_Improved_LJ(W->eps, W->r0, W->n, W->m, a_r),
@@ -140,10 +163,28 @@ void orc_vdw_cells(int n_kinds, const xtb_vdw_pair* WP, double rm_tb, const doub
     }
 }
 
-/* get_vdW_s (OpenMP arm): returns a = sum_a * 0.5; Epot[i] = the amount added to MDAtoms(i)%Epot */
+/* get_mirror_cell_num_C: R_cut = TB_Coul(1,1)%dm */
+void orc_coulomb_cells(double dm11, const double* S, const double* h, int* N) {
+    for (int a = 0; a < 3; ++a) {
+        double zb[3] = {0.0, 0.0, 0.0}, R;
+        int n = 0;
+        zb[a] = 1.0;
+        R = vdw_distance_to_cell(S, h, zb, 0, 0, NULL, NULL);
+        while (R < 2.0 * dm11 && n < 1000) {
+            n = n + 1;
+            zb[a] = (double)n;
+            R = vdw_distance_to_cell(S, h, zb, 0, 0, NULL, NULL);
+        }
+        N[a] = n < 1 ? 1 : n;
+    }
+}
+
+/* get_vdW_s (OpenMP arm): returns a = sum_a * 0.5; Epot[i] = the amount added to MDAtoms(i)%Epot.
+ * kind = ORC_KIND_COULOMB: get_Coulomb_s, the same loops without either half (a = sum_a, Epot(i) += E_rep) */
 double orc_vdw_energy(int na, int kind, int n_kinds, const int* koa, const double* S, const double* h, const xtb_vdw_pair* WP,
                       const int* N, double* Epot) {
     double sum_a = 0.0;
+    const double half = kind == ORC_KIND_COULOMB ? 1.0 : 0.5;
     if (Epot) for (int i = 0; i < na; ++i) Epot[i] = 0.0;
     for (int x_cell = -N[0]; x_cell <= N[0]; ++x_cell)
         for (int y_cell = -N[1]; y_cell <= N[1]; ++y_cell)
@@ -159,10 +200,10 @@ double orc_vdw_energy(int na, int kind, int n_kinds, const int* koa, const doubl
                             sum_a = sum_a + E_pot_one;
                             E_pot = E_pot + E_pot_one;
                         }
-                    if (Epot) Epot[i1] = Epot[i1] + E_pot * 0.5;
+                    if (Epot) Epot[i1] = Epot[i1] + E_pot * half;
                 }
             }
-    return sum_a * 0.5;
+    return sum_a * half;
 }
 
 /* one (cell, i1, j1) entry of the arrays cell_cycle_B fills (:394-408) */
@@ -170,7 +211,10 @@ typedef struct { double Bij, A_rij, X[3], XS[3], SX[3]; } vdw_entry;
 static void vdw_B_entry(vdw_entry* e, int kind, int n_kinds, const int* koa, const double* S, const double* h, const xtb_vdw_pair* WP,
                         const double* zb, int i1, int j1) {
     e->A_rij = vdw_distance_to_cell(S, h, zb, i1, j1, e->X, e->SX);
-    for (int k = 0; k < 3; ++k) e->XS[k] = e->X[0] * h[k] + e->X[1] * h[k + 3] + e->X[2] * h[k + 6];      /* supce(k,1..3) */
+    if (kind == ORC_KIND_COULOMB)     /* Construct_B_C :864-866: x*supce(1,k) + y*supce(2,k) + z*supce(3,k) */
+        for (int k = 0; k < 3; ++k) e->XS[k] = e->X[0] * h[3 * k] + e->X[1] * h[3 * k + 1] + e->X[2] * h[3 * k + 2];
+    else
+        for (int k = 0; k < 3; ++k) e->XS[k] = e->X[0] * h[k] + e->X[1] * h[k + 3] + e->X[2] * h[k + 6];  /* supce(k,1..3) */
     e->Bij = vdw_dvdW(kind, WP + koa[j1] + n_kinds * koa[i1], e->A_rij);                                 /* TB_Waals(KOA(j1), KOA(i1)) */
 }
 

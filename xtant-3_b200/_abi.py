@@ -14,16 +14,17 @@ XTB_OK, XTB_EINVAL, XTB_ENODEV, XTB_ECUDA, XTB_ENOMEM, XTB_ECAPACITY, XTB_ESTATE
 XTB_TB_NONE, XTB_TB_NRL, XTB_TB_PETTIFOR, XTB_TB_DFTB = range(4)
 
 (BUF_H, BUF_S, BUF_RHO, BUF_RHOE, BUF_FORCES, BUF_ROWPTR, BUF_NNLIST, BUF_NNSIZE, BUF_SCFORCE, BUF_HBLK, BUF_SBLK, BUF_FREP, BUF_MIJ,
- BUF_FWALL, BUF_POS, BUF_VEL, BUF_EI, BUF_FE, BUF_FVDW) = range(1, 20)
+ BUF_FWALL, BUF_POS, BUF_VEL, BUF_EI, BUF_FE, BUF_FVDW, BUF_FCOUL) = range(1, 21)
 CNT_NA, CNT_NORB, CNT_N, CNT_MAXNN, CNT_NBLOCKS, CNT_NPAIRS, CNT_LAUNCHES, CNT_KKEPT, CNT_CAP = range(9)
 STAGE_NEIGH, STAGE_ASSEMBLE, STAGE_DENSITY, STAGE_FORCES, STAGE_PRESSURE = range(1, 6)
 STAGE_REP_FORCES, STAGE_REP_PRESSURE, STAGE_COUPLING = 9, 10, 11
 STAGE_XCHG_HS, STAGE_XCHG_RHO = 14, 15
 CNT_XCHG_HS_BYTES, CNT_XCHG_RHO_BYTES, CNT_HALO_SEND, CNT_HALO_RECV = 12, 13, 14, 15
 XCHG_HS, XCHG_RHO = 1, 2
-FORCE_ATT, FORCE_REP, FORCE_WALL, FORCE_VDW = 1, 2, 4, 8
+FORCE_ATT, FORCE_REP, FORCE_WALL, FORCE_VDW, FORCE_COUL = 1, 2, 4, 8, 16
 VDW_GIRIFALCO, VDW_LJ_CUT, VDW_ILJ_CUT = 1, 2, 3
-STAGE_VDW = 17
+STAGE_VDW, STAGE_COULOMB = 17, 18
+COULOMB_K = 1.602176634e-19 / (4.0 * 3.1415926535897932384626433832795 * 8.854187817620e-12) * 1.0e10     # Read_input_data.f90:1907 [eV A]
 STEP_NEIGHBOURS, STEP_HS, STEP_EIGEN, STEP_DENSITY, STEP_FORCES, STEP_PRESSURE, STEP_PAIR_TERMS, STEP_NO_DENSE, STEP_GRAPH = 1, 2, 4, 8, 16, 32, 64, 128, 256
 STEP_ALL = STEP_NEIGHBOURS | STEP_HS | STEP_DENSITY | STEP_FORCES
 UNIQUE_ID_BYTES = 128
@@ -77,6 +78,11 @@ def vdw_pair_from_dict(d):
     return p
 
 
+class CoulombPair(C.Structure):
+    """struct xtb_coulomb_pair == type(TB_Coulomb_cut), Objects.f90:359-366 (k, dm, dd)"""
+    _fields_ = [("k", C.c_double), ("dm", C.c_double), ("dd", C.c_double)]
+
+
 class StepIO(C.Structure):
     """struct xtb_step_io"""
     _fields_ = [("S", C.POINTER(C.c_double)), ("supce", C.POINTER(C.c_double)), ("fe", C.POINTER(C.c_double)),
@@ -85,7 +91,8 @@ class StepIO(C.Structure):
                 ("E_band", C.POINTER(C.c_double)), ("F_att", C.POINTER(C.c_double)), ("SCforce_att", C.POINTER(C.c_double)),
                 ("E_rep", C.POINTER(C.c_double)), ("F_rep", C.POINTER(C.c_double)), ("SCforce_rep", C.POINTER(C.c_double)),
                 ("E_wall", C.POINTER(C.c_double)), ("F_wall", C.POINTER(C.c_double)), ("SCforce_wall", C.POINTER(C.c_double)),
-                ("E_vdw", C.POINTER(C.c_double)), ("F_vdw", C.POINTER(C.c_double)), ("SCforce_vdw", C.POINTER(C.c_double))]
+                ("E_vdw", C.POINTER(C.c_double)), ("F_vdw", C.POINTER(C.c_double)), ("SCforce_vdw", C.POINTER(C.c_double)),
+                ("E_coul", C.POINTER(C.c_double)), ("F_coul", C.POINTER(C.c_double)), ("SCforce_coul", C.POINTER(C.c_double))]
 
 
 class DftbPair(C.Structure):
@@ -196,6 +203,12 @@ SIGNATURES = {
     "xtb_vdw_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
     "xtb_vdw_forces": (C.c_int, [C.c_void_p, _pd]),
     "xtb_vdw_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_set_params_coulomb": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(CoulombPair)]),
+    "xtb_set_charge": (C.c_int, [C.c_void_p, C.c_double]),
+    "xtb_coulomb_image_cells": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
+    "xtb_coulomb_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_coulomb_forces": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_coulomb_pressure": (C.c_int, [C.c_void_p, _pd]),
     "xtb_fermi_occupations": (C.c_int, [C.c_void_p, C.c_double, C.c_double, _pd, _pd, _pd]),
     "xtb_md_set_velocities": (C.c_int, [C.c_void_p, _pd]),
     "xtb_md_half_step": (C.c_int, [C.c_void_p, C.c_int, C.c_double, _pd, _pd, C.c_uint]),

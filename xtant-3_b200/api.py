@@ -108,7 +108,24 @@ class TBContext:
             self.set_params_wall(wl["wall_params"])
         if wl.get("vdw_params"):
             self.set_params_vdw(wl["vdw_kind"], wl["vdw_params"])
+        if wl.get("coulomb_params"):
+            self.set_params_coulomb(wl["coulomb_params"])
+            self.set_charge(wl.get("Q", 0.0))
         self.set_system(wl["koa"], wl["S"], wl["supce"])
+
+    def set_params_coulomb(self, params):
+        """Scell%TB_Coul(:,:) of class TB_Coulomb_cut: list of dict(dm, dd[, k]) (k defaults to the reader's constant,
+        Read_input_data.f90:1907), (koa1, koa2) column-major; None / [] removes the term"""
+        if not params:
+            self._ck(self.lib.xtb_set_params_coulomb(self.h, 0, None))
+            return
+        nk = int(round(len(params) ** 0.5))
+        arr = (_abi.CoulombPair * len(params))(*[_abi.CoulombPair(float(d.get("k", _abi.COULOMB_K)), float(d["dm"]), float(d["dd"])) for d in params])
+        self._ck(self.lib.xtb_set_params_coulomb(self.h, nk, arr))
+
+    def set_charge(self, Q):
+        """Scell%Q: mean unbalanced charge per atom [e]"""
+        self._ck(self.lib.xtb_set_charge(self.h, float(Q)))
 
     def set_params_vdw(self, kind, params):
         """Scell%TB_Waals(:,:): kind 'Girifalco' | 'LJ' | 'ILJ' (or XTB_VDW_*), list of dicts with the members of that class
@@ -335,6 +352,31 @@ class TBContext:
         self._ck(self.lib.xtb_vdw_pressure(self.h, _dp(P)))
         return P.reshape(3, 3, order="F")
 
+    # -- Coulomb term of a charged supercell (fourth part) -------------------
+    def get_mirror_cell_num_C(self):
+        """get_mirror_cell_num_C, Coulomb.f90:435 -> (Nx, Ny, Nz)"""
+        N = (C.c_int * 3)()
+        self._ck(self.lib.xtb_coulomb_image_cells(self.h, N))
+        return int(N[0]), int(N[1]), int(N[2])
+
+    def get_Coulomb_s(self):
+        """get_Coulomb_s, Coulomb.f90:454 -> (E_coul [eV] (not halved, as written), what is added to MDAtoms(:)%Epot)"""
+        E = np.zeros(1); Epot = np.zeros(self.na)
+        self._ck(self.lib.xtb_coulomb_energy(self.h, _dp(E), _dp(Epot)))
+        return float(E[0]), Epot
+
+    def Coulomb_forces(self):
+        """Coulomb_forces -> Construct_B_C + d_Forces_s, TB.f90:3560,3638 -> the term added to forces%rep, (na,3)"""
+        F = np.zeros((self.na, 3))
+        self._ck(self.lib.xtb_coulomb_forces(self.h, _dp(F)))
+        return F
+
+    def Coulomb_Pressure(self):
+        """Coulomb_forces -> d_Forces_Pressure, TB.f90:3785 -> the term added to SCforce%rep(3,3)"""
+        P = np.zeros(9)
+        self._ck(self.lib.xtb_coulomb_pressure(self.h, _dp(P)))
+        return P.reshape(3, 3, order="F")
+
     # -- Fermi occupations, velocity-Verlet halves, the fused step (step.cu) ----------------------
     def fermi_occupations(self, n_electrons, Te_eV):
         """Electron_Fixed_Te + set_Fermi (Electron_tools.f90:2660,1913) on the device -> (fe, mu, sum f E)"""
@@ -363,7 +405,7 @@ class TBContext:
     def step(self, flags=_abi.STEP_ALL, S=None, supce=None, fe=None, n_electrons=0.0, Te_eV=0.0, want=(), graph=False):
         """xtb_step: the selected stages as one call.  want: names of host outputs to fetch, any of
         Ei, fe_out, mu, E_band, F_att, SCforce_att, E_rep, F_rep, SCforce_rep, E_wall, F_wall, SCforce_wall,
-        E_vdw, F_vdw, SCforce_vdw -> dict"""
+        E_vdw, F_vdw, SCforce_vdw, E_coul, F_coul, SCforce_coul -> dict"""
         N = self.na * self.n_orb
         io = _abi.StepIO()
         keep = []
@@ -377,7 +419,8 @@ class TBContext:
         io.n_electrons = float(n_electrons); io.Te_eV = float(Te_eV)
         shapes = {"Ei": (N,), "fe_out": (N,), "mu": (1,), "E_band": (1,), "F_att": (self.na, 3), "SCforce_att": (9,),
                   "E_rep": (1,), "F_rep": (self.na, 3), "SCforce_rep": (9,), "E_wall": (1,), "F_wall": (self.na, 3), "SCforce_wall": (9,),
-                  "E_vdw": (1,), "F_vdw": (self.na, 3), "SCforce_vdw": (9,)}
+                  "E_vdw": (1,), "F_vdw": (self.na, 3), "SCforce_vdw": (9,),
+                  "E_coul": (1,), "F_coul": (self.na, 3), "SCforce_coul": (9,)}
         out = {}
         for k in want:
             out[k] = np.zeros(shapes[k])

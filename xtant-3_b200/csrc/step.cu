@@ -77,7 +77,7 @@ __global__ void __launch_bounds__(FT_THREADS) fermi_kernel(long long N, const do
 // par: [0..8] g^-1 (col-major), [9..17] GinvGdot, [18] dt, [19] dt^2/2, [20] dt/2; minv[kind] = -g_e * 1e-10 / M
 __global__ void md_half_kernel(int na, int ind, const int* __restrict__ koa, const double* __restrict__ par, const double* __restrict__ minv,
                                const double* __restrict__ Fa, const double* __restrict__ Fb, const double* __restrict__ Fc,
-                               const double* __restrict__ Fd, double* __restrict__ S, double* __restrict__ S0, double* __restrict__ SV, double* __restrict__ SV0) {
+                               const double* __restrict__ Fd, const double* __restrict__ Fe, double* __restrict__ S, double* __restrict__ S0, double* __restrict__ SV, double* __restrict__ SV0) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= na) return;
     // save_last_timestep: S0 = S, SV0 = SV
@@ -90,6 +90,7 @@ __global__ void md_half_kernel(int na, int ind, const int* __restrict__ koa, con
         if (Fb) f[x] += Fb[3 * k + x];
         if (Fc) f[x] += Fc[3 * k + x];
         if (Fd) f[x] += Fd[3 * k + x];
+        if (Fe) f[x] += Fe[3 * k + x];
     }
     const double fctr = minv[koa[k]];
     double acc[3];
@@ -234,10 +235,12 @@ int xtb_md_half_step(xtb_ctx* c, int ind, double dt_fs, const double* mass_kg, c
     const double* Fd = (force_terms & XTB_FORCE_VDW) ? (const double*)c->d_Fvdw.p : nullptr;
     if ((force_terms & XTB_FORCE_WALL) && !Fc) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no wall forces on the device");
     if ((force_terms & XTB_FORCE_VDW) && !Fd) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no van der Waals forces on the device");
-    const double* terms[4] = {Fa, Fb, Fc, Fd};
-    const double* F3[4] = {nullptr, nullptr, nullptr, nullptr};
+    const double* Fe = (force_terms & XTB_FORCE_COUL) ? (const double*)c->d_Fcoul.p : nullptr;
+    if ((force_terms & XTB_FORCE_COUL) && !Fe) XTB_FAIL(c, XTB_ESTATE, "xtb_md_half_step: no Coulomb forces on the device");
+    const double* terms[5] = {Fa, Fb, Fc, Fd, Fe};
+    const double* F3[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     int nt = 0;
-    for (int t = 0; t < 4; ++t) if (terms[t]) F3[nt++] = terms[t];
+    for (int t = 0; t < 5; ++t) if (terms[t]) F3[nt++] = terms[t];
     if (nt == 0) XTB_FAIL(c, XTB_EINVAL, "xtb_md_half_step: no force term selected");
     // g^-1 = (h^T h)^-1 (:1916-1922) and GinvGdot (get_GGdot :1843-1861)
     double par[24] = {0};
@@ -259,7 +262,7 @@ int xtb_md_half_step(xtb_ctx* c, int ind, double dt_fs, const double* mass_kg, c
     for (int k = 0; k < c->n_kinds; ++k) up[32 + k] = -1.0 / mass_kg[k] * 1.602176634e-19 * 1e-10;       // fctr :1938
     XTB_CUDA(c, cudaMemcpyAsync(c->d_mdpar.p, up.data(), sizeof(double) * up.size(), cudaMemcpyHostToDevice, c->stream));
     md_half_kernel<<<(c->na + 127) / 128, 128, 0, c->stream>>>(c->na, ind, (const int*)c->d_koa.p, (const double*)c->d_mdpar.p,
-                                                               (const double*)c->d_mdpar.p + 32, F3[0], F3[1], F3[2], F3[3],
+                                                               (const double*)c->d_mdpar.p + 32, F3[0], F3[1], F3[2], F3[3], F3[4],
                                                                (double*)c->d_S.p, (double*)c->d_S0.p, (double*)c->d_SV.p, (double*)c->d_SV0.p);
     XTB_LAUNCH_CHECK(c);
     XTB_CUDA(c, cudaStreamSynchronize(c->stream));           // `up` is a host temporary
@@ -366,13 +369,15 @@ struct GraphKey {
     double rm, f_cut;
     bool rep, wall;
     int vdw_kind, vdw_cells[3];
+    int coul, coul_cells[3];
+    double coul_Q;
 };
 static unsigned io_mask(const xtb_step_io* io) {
     if (!io) return 0;
     unsigned m = 0;
     const void* p[] = {io->S, io->F_att, io->SCforce_att, io->E_rep, io->F_rep, io->SCforce_rep, io->E_wall, io->F_wall, io->SCforce_wall,
-                       io->E_vdw, io->F_vdw, io->SCforce_vdw};
-    for (int k = 0; k < 12; ++k) if (p[k]) m |= 1u << k;
+                       io->E_vdw, io->F_vdw, io->SCforce_vdw, io->E_coul, io->F_coul, io->SCforce_coul};
+    for (int k = 0; k < 15; ++k) if (p[k]) m |= 1u << k;
     return m;
 }
 static GraphKey make_key(const xtb_ctx* c, unsigned flags, const xtb_step_io* io) {
@@ -387,15 +392,19 @@ static GraphKey make_key(const xtb_ctx* c, unsigned flags, const xtb_step_io* io
         k.vdw_kind = c->vdw_kind;
         xtb_impl_vdw_cells(const_cast<xtb_ctx*>(c), k.vdw_cells, nullptr);
     }
+    if (!c->h_coul.empty()) {                // the charge decides between the kernel and the zero fill; the table upload is not capturable
+        k.coul = c->coul_dirty ? 2 : 1; k.coul_Q = c->coul_Q;
+        xtb_impl_coulomb_cells(const_cast<xtb_ctx*>(c), k.coul_cells);
+    }
     return k;
 }
 static void graph_drop(xtb_ctx* c) {
     if (c->graph_exec) { cudaGraphExecDestroy((cudaGraphExec_t)c->graph_exec); c->graph_exec = nullptr; }
     c->graph_key.clear();
 }
-// staging layout (doubles): S[3 na] | F_att[3 na] | F_rep[3 na] | F_wall[3 na] | F_vdw[3 na] | SC_att[9] SC_rep[9] SC_wall[9] SC_vdw[9] | E_rep E_wall E_vdw
+// staging layout (doubles): S[3 na] | F_att[3 na] | F_rep[3 na] | F_wall[3 na] | F_vdw[3 na] | F_coul[3 na] | SC_att[9] SC_rep[9] SC_wall[9] SC_vdw[9] SC_coul[9] | E_rep E_wall E_vdw E_coul
 static int graph_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool* overflow) {
-    const size_t na3 = 3 * (size_t)c->na, need = sizeof(double) * (5 * na3 + 48);
+    const size_t na3 = 3 * (size_t)c->na, need = sizeof(double) * (6 * na3 + 56);
     *overflow = false;
     if (c->h_stage_bytes < need) {
         if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -413,13 +422,16 @@ static int graph_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool* o
         if (io->F_rep) g.F_rep = st + 2 * na3;
         if (io->F_wall) g.F_wall = st + 3 * na3;
         if (io->F_vdw) g.F_vdw = st + 4 * na3;
-        if (io->SCforce_att) g.SCforce_att = st + 5 * na3;
-        if (io->SCforce_rep) g.SCforce_rep = st + 5 * na3 + 9;
-        if (io->SCforce_wall) g.SCforce_wall = st + 5 * na3 + 18;
-        if (io->SCforce_vdw) g.SCforce_vdw = st + 5 * na3 + 27;
-        if (io->E_rep) g.E_rep = st + 5 * na3 + 36;
-        if (io->E_wall) g.E_wall = st + 5 * na3 + 37;
-        if (io->E_vdw) g.E_vdw = st + 5 * na3 + 38;
+        if (io->F_coul) g.F_coul = st + 5 * na3;
+        if (io->SCforce_att) g.SCforce_att = st + 6 * na3;
+        if (io->SCforce_rep) g.SCforce_rep = st + 6 * na3 + 9;
+        if (io->SCforce_wall) g.SCforce_wall = st + 6 * na3 + 18;
+        if (io->SCforce_vdw) g.SCforce_vdw = st + 6 * na3 + 27;
+        if (io->SCforce_coul) g.SCforce_coul = st + 6 * na3 + 36;
+        if (io->E_rep) g.E_rep = st + 6 * na3 + 45;
+        if (io->E_wall) g.E_wall = st + 6 * na3 + 46;
+        if (io->E_vdw) g.E_vdw = st + 6 * na3 + 47;
+        if (io->E_coul) g.E_coul = st + 6 * na3 + 48;
     }
     const GraphKey key = make_key(c, flags, io);
     if (!c->graph_exec || c->graph_key.size() != sizeof key || memcmp(c->graph_key.data(), &key, sizeof key) != 0) {
@@ -473,6 +485,9 @@ static int graph_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io, bool* o
         if (io->E_wall) *io->E_wall = *g.E_wall;
         if (io->SCforce_vdw) memcpy(io->SCforce_vdw, g.SCforce_vdw, 72);
         if (io->E_vdw) *io->E_vdw = *g.E_vdw;
+        if (io->F_coul) memcpy(io->F_coul, g.F_coul, sizeof(double) * na3);
+        if (io->SCforce_coul) memcpy(io->SCforce_coul, g.SCforce_coul, 72);
+        if (io->E_coul) *io->E_coul = *g.E_coul;
     }
     return XTB_OK;
 }
@@ -486,7 +501,8 @@ int xtb_step(xtb_ctx* c, unsigned flags, const xtb_step_io* io) {
     const bool single = !(c->comm && c->nranks > 1) && c->layout_parts == 1;
     bool can_steady = (flags & XTB_STEP_NEIGHBOURS) && single && c->have_shape;
     // graph replay: a steady step with these flags has already run eagerly; nothing in this call needs the host mid-way
-    if ((flags & XTB_STEP_GRAPH) && can_steady && c->steady_flags_done == (flags & ~XTB_STEP_GRAPH) && !(flags & XTB_STEP_EIGEN) &&
+    const bool coul_upload = (flags & XTB_STEP_PAIR_TERMS) && !c->h_coul.empty() && c->coul_dirty;      // a new charge: the table is rebuilt by the eager path
+    if ((flags & XTB_STEP_GRAPH) && can_steady && !coul_upload && c->steady_flags_done == (flags & ~XTB_STEP_GRAPH) && !(flags & XTB_STEP_EIGEN) &&
         !(io && (io->fe || io->supce || io->Ei || io->fe_out)) && (!(flags & XTB_STEP_DENSITY) || (c->have_eigen && c->have_keep)) &&
         (uintptr_t)c->stream > 2 /* the legacy / per-thread default streams cannot be captured */) {
         bool overflow = false;

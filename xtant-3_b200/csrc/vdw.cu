@@ -1,4 +1,5 @@
-// van der Waals pair term (third part; class TB_vdW).
+// van der Waals and Coulomb pair terms (third part; classes TB_vdW and TB_Coulomb_cut): the two terms of
+// the reference that sum over ALL atom pairs in the periodic images of the supercell instead of over the neighbour list.
 //
 // Replaces, in Source_files/Van_der_Waals.f90 and TB.f90 (dispatch vdW_forces TB.f90:3599-3633, vdW_s TB.f90:4017-4035):
 //   get_mirror_cell_num :132-157        R_cut = max(TB cut-off, max d0_cut + 10 max dd_cut) (get_near_neighbours with include_vdW,
@@ -9,6 +10,13 @@
 //                                       (Atomic_tools.f90:4135-4166)
 //   d_Forces_s TB.f90:3638-3781         forces%rep(ian) += 1/2 sum_{i1} sum_{j1,cell} Bij (d_{ian,i1} - d_{ian,j1}) / r * (h . r)
 //   d_Forces_Pressure TB.f90:3785-3848  SCforce%rep(l,k) += 1/2 sum_cells sum_i sum_j Bij r_k s_l / r
+// The Coulomb term (Coulomb.f90; dispatch Coulomb_forces TB.f90:3560-3596, Coulomb_s TB.f90:3995-4012) goes through the same
+// d_Forces_s / d_Forces_Pressure with its own arrays:
+//   get_mirror_cell_num_C :435-452      R_cut = TB_Coul(1,1)%dm alone
+//   get_Coulomb_s :454-550              E = sum_cells sum_i sum_j V -- NO factor 1/2 (as written); Epot(i) += sum_j V
+//   Coulomb_pot :552-587 / dCoulomb :641-672   V = k Q Q / r * f_cut_L_C, zero for r > dm + 10 dd; Q = Scell%Q, the mean unbalanced charge
+//   Construct_B_C :715-880              all zero when Q <= 1e-12; XijSupce = x supce(1,1) + y supce(2,1) + z supce(3,1): the
+//                                       TRANSPOSE of the contraction Construct_B uses (identical for a symmetric supce) -- kept
 // The reference builds eleven (cells, Na, Na) arrays and then loops ian x i1 x j1 x cells (O(Na^3)); only i1 = ian and j1 = ian
 // contribute, and the j1 = ian term of cell zb is the mirror image of the i1 = ian term of cell -zb (the displacement changes
 // sign exactly in floating point), so one pass over (j, cell) per atom gives energy, force and supercell force together.  Here:
@@ -19,6 +27,8 @@
 // FP64 CUDA cores, compute-bound (no memory traffic to speak of: positions and kinds of Na atoms, L1-resident).
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
+#include <vector>
 #include "xtb_ctx.h"
 
 namespace {
@@ -97,6 +107,27 @@ template <> struct Vdw<XTB_VDW_ILJ_CUT> {
     }
 };
 
+constexpr int KIND_COULOMB = 4;      // internal: the table entry carries eps = k Q Q, d0_cut = dm, dd_cut = dd
+template <> struct Vdw<KIND_COULOMB> {
+    static __device__ __forceinline__ double V(const xtb_vdw_pair& W, double r) {   // Coulomb_pot :552-587
+        if (r > W.d0_cut + W.dd_cut * 10.0) return 0.0;
+        const double fcut = 1.0 / (1.0 + exp((r - W.d0_cut) / W.dd_cut));           // f_cut_L_C :610
+        return W.eps / r * fcut;                                                    // Coulomb_potential :589
+    }
+    static __device__ __forceinline__ double dV(const xtb_vdw_pair& W, double r) {  // dCoulomb :641-672
+        if (r > W.d0_cut + W.dd_cut * 10.0) return 0.0;
+        const double arg = (r - W.d0_cut) / W.dd_cut;
+        const double fcut = 1.0 / (1.0 + exp(arg));
+        const double E_C = W.eps / r, d_E_C = -W.eps / (r * r);                     // d_Coulomb_potential :596
+        double dfcut = 0.0;                                                         // d_f_cut_L_C :617-629
+        if (arg < 709.782712893384) {
+            const double er = exp(arg), e2 = 1.0 + er;
+            dfcut = -er / (W.dd_cut * e2 * e2);
+        }
+        return d_E_C * fcut + E_C * dfcut;
+    }
+};
+
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(FULL, v, off);
@@ -107,7 +138,7 @@ __device__ __forceinline__ double warp_sum(double v) {
 template <int KIND>
 // reach[a] = R_max / (plane spacing along cell axis a), a little widened: the range of |s_a| inside which a pair can interact
 __global__ void __launch_bounds__(VT) vdw_atom_kernel(int a0, int na, int n_kinds, int Nx, int Ny, int Nz, unsigned what, int sym,
-                                                      double reach_x, double reach_y, double reach_z,
+                                                      double reach_x, double reach_y, double reach_z, double e_scale, int xs_t,
                                                       const int* __restrict__ koa, const double* __restrict__ S,
                                                       const xtb_vdw_pair* __restrict__ WP, const double* __restrict__ hdev,
                                                       double* __restrict__ Epot, double* __restrict__ F, double* __restrict__ ppart) {
@@ -145,7 +176,9 @@ __global__ void __launch_bounds__(VT) vdw_atom_kernel(int a0, int na, int n_kind
                         if ((what & DO_F) && j != i) {
                             const double bb = (sym ? b + b : b + Vdw<KIND>::dV(Wij, r)) / r;
 #pragma unroll
-                            for (int al = 0; al < 3; ++al) acc[1 + al] += bb * (x[0] * h[al] + x[1] * h[al + 3] + x[2] * h[al + 6]);   // XijSupce :343-345
+                            for (int al = 0; al < 3; ++al)      // XijSupce :343-345; Coulomb.f90:864-866 contracts with the transpose
+                                acc[1 + al] += bb * (xs_t ? x[0] * h[3 * al] + x[1] * h[3 * al + 1] + x[2] * h[3 * al + 2]
+                                                          : x[0] * h[al] + x[1] * h[al + 3] + x[2] * h[al + 6]);
                         }
                         if (what & DO_P) {
                             const double br = b / r;
@@ -167,7 +200,7 @@ __global__ void __launch_bounds__(VT) vdw_atom_kernel(int a0, int na, int n_kind
         double v = 0.0;
 #pragma unroll
         for (int w = 0; w < VT / 32; ++w) v += red[w][tid];
-        v *= 0.5;                                            // :246, TB.f90:3765, TB.f90:3838
+        v *= tid == 0 ? e_scale : 0.5;                       // :246 (vdW 1/2; Coulomb.f90:549 none), TB.f90:3765, TB.f90:3838
         if (tid == 0) { if (what & DO_E) Epot[i] = v; }
         else if (tid < 4) { if (what & DO_F) F[3 * (size_t)i + tid - 1] = v; }
         else if (what & DO_P) ppart[(size_t)blockIdx.x * 9 + tid - 4] = v;
@@ -201,14 +234,17 @@ __global__ void vdw_sum9_kernel(int n, const double* __restrict__ partial, doubl
     if (threadIdx.x == 0) out[k1] = buf[0];
 }
 
-int launch_atoms(xtb_ctx* c, int first, int count, unsigned what, const int N[3]) {
+// one image-cell pair term of the context: its table, class and output buffers
+struct PairSet {
+    int kind;  bool sym;  double Rmax, e_scale;  int xs_t;
+    DevBuf *params, *E_at, *E, *F, *SC;
+    int stage;
+};
+
+int launch_atoms(xtb_ctx* c, const PairSet& t, int first, int count, unsigned what, const int N[3]) {
     if (count <= 0) return XTB_OK;
-    // R_max of the pair table and the plane spacings of the cell (volume / face area)
-    double Rmax = 0.0, reach[3];
-    for (auto& p : c->h_vdw) {
-        const double r = c->vdw_kind == XTB_VDW_GIRIFALCO ? p.d_cut : p.d0_cut + 10.0 * p.dd_cut;
-        if (r > Rmax) Rmax = r;
-    }
+    // reach of the pair table in units of the plane spacings of the cell (volume / face area)
+    double reach[3];
     {
         const double* h = c->h_supce;               // row a of supce = cell vector a: (h[a], h[a+3], h[a+6])
         double v[3][3], vol;
@@ -222,24 +258,79 @@ int launch_atoms(xtb_ctx* c, int first, int count, unsigned what, const int N[3]
             cross(v[(a + 1) % 3], v[(a + 2) % 3], n);
             const double area = sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
             const double spacing = area > 0.0 ? vol / area : 0.0;
-            reach[a] = (spacing > 0.0 && !getenv("XTB_VDW_NO_PRUNE")) ? Rmax / spacing * (1.0 + 1e-9) + 1e-9 : 1e300;
+            reach[a] = (spacing > 0.0 && !getenv("XTB_VDW_NO_PRUNE")) ? t.Rmax / spacing * (1.0 + 1e-9) + 1e-9 : 1e300;
         }
     }
 #define XTB_VDW_LAUNCH(KIND)                                                                                                          \
-    vdw_atom_kernel<KIND><<<count, VT, 0, c->stream>>>(first, c->na, c->n_kinds, N[0], N[1], N[2], what, c->vdw_sym ? 1 : 0,           \
-                                                       reach[0], reach[1], reach[2],                                                  \
-                                                       (const int*)c->d_koa.p, (const double*)c->d_S.p, (const xtb_vdw_pair*)c->d_vdw_params.p, \
-                                                       (const double*)c->d_hdev.p, (double*)c->d_Evdw_at.p, (double*)c->d_Fvdw.p,      \
+    vdw_atom_kernel<KIND><<<count, VT, 0, c->stream>>>(first, c->na, c->n_kinds, N[0], N[1], N[2], what, t.sym ? 1 : 0,                \
+                                                       reach[0], reach[1], reach[2], t.e_scale, t.xs_t,                               \
+                                                       (const int*)c->d_koa.p, (const double*)c->d_S.p, (const xtb_vdw_pair*)t.params->p, \
+                                                       (const double*)c->d_hdev.p, (double*)t.E_at->p, (double*)t.F->p,                \
                                                        (double*)c->d_ppart.p)
-    switch (c->vdw_kind) {
+    switch (t.kind) {
         case XTB_VDW_GIRIFALCO: XTB_VDW_LAUNCH(XTB_VDW_GIRIFALCO); break;
         case XTB_VDW_LJ_CUT:    XTB_VDW_LAUNCH(XTB_VDW_LJ_CUT); break;
         case XTB_VDW_ILJ_CUT:   XTB_VDW_LAUNCH(XTB_VDW_ILJ_CUT); break;
-        default: XTB_FAIL(c, XTB_ESTATE, "vdW: unknown class %d", c->vdw_kind);
+        case KIND_COULOMB:      XTB_VDW_LAUNCH(KIND_COULOMB); break;
+        default: XTB_FAIL(c, XTB_ESTATE, "pair term: unknown class %d", t.kind);
     }
 #undef XTB_VDW_LAUNCH
     XTB_LAUNCH_CHECK(c);
     return XTB_OK;
+}
+
+// get_number_of_image_cells (Atomic_tools.f90:654-702) for cut-off Rc, then "at least one image per axis"
+int image_cells(xtb_ctx* c, double Rc, int N[3], const char* who) {
+    const double* h = c->h_supce;
+    long long cells = 1;
+    for (int a = 0; a < 3; ++a) {
+        auto dist = [&](double zb) { const double x0 = zb * h[a], y0 = zb * h[a + 3], z0 = zb * h[a + 6]; return sqrt(x0 * x0 + y0 * y0 + z0 * z0); };
+        if (!(dist(1.0) > 0.0)) XTB_FAIL(c, XTB_EINVAL, "%s: supercell vector %d has no length", who, a + 1);
+        int n = 0;
+        double R = dist(1.0);
+        while (R < 2.0 * Rc) {
+            n++;
+            R = dist((double)n);
+            if (n > 64) XTB_FAIL(c, XTB_EINVAL, "%s: more than 64 images of the supercell along axis %d (R_cut = %g A)", who, a + 1, Rc);
+        }
+        if (n < 1) n = 1;
+        N[a] = n;
+        cells *= 2 * n + 1;
+    }
+    if (cells > 100000) XTB_FAIL(c, XTB_EINVAL, "%s: %lld image cells (R_cut = %g A)", who, cells, Rc);
+    return XTB_OK;
+}
+
+// Energy of every atom on every rank (replicated, like the wall); forces and the supercell-force partial sums of the owned
+// atoms (exchanged / all-reduced by the caller when the context communicates).
+int run_set(xtb_ctx* c, const PairSet& t, unsigned what, const int N[3], bool forces_off) {
+    const int na = c->na, nown = c->a1 - c->a0;
+    int rc;
+    if ((rc = xtb_reserve(c, *t.E_at, sizeof(double) * na))) return rc;
+    if ((rc = xtb_reserve(c, *t.E, sizeof(double)))) return rc;
+    if ((rc = xtb_reserve(c, *t.F, sizeof(double) * 3 * (size_t)(na + c->nranks)))) return rc;
+    if ((rc = xtb_reserve(c, *t.SC, sizeof(double) * 9))) return rc;
+    if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)(nown > 0 ? nown : 1)))) return rc;
+    XTB_T0(c, t.stage);
+    if (forces_off) {                       // Construct_B_C with Q <= 1e-12: every array zero
+        if (what & DO_F) XTB_CUDA(c, cudaMemsetAsync(t.F->p, 0, sizeof(double) * 3 * (size_t)na, c->stream));
+        if (what & DO_P) XTB_CUDA(c, cudaMemsetAsync(t.SC->p, 0, sizeof(double) * 9, c->stream));
+        what &= DO_E;
+    }
+    if (what && (rc = launch_atoms(c, t, c->a0, nown, what, N))) return rc;
+    if (what & DO_E) {
+        if ((rc = launch_atoms(c, t, 0, c->a0, DO_E, N)) || (rc = launch_atoms(c, t, c->a1, na - c->a1, DO_E, N))) return rc;
+        vdw_esum_kernel<<<1, 256, 0, c->stream>>>(na, (const double*)t.E_at->p, (double*)t.E->p);
+        XTB_LAUNCH_CHECK(c);
+    }
+    if (what & DO_P) {
+        if (nown > 0) {
+            vdw_sum9_kernel<<<9, 128, 0, c->stream>>>(nown, (const double*)c->d_ppart.p, (double*)t.SC->p);
+            XTB_LAUNCH_CHECK(c);
+        } else XTB_CUDA(c, cudaMemsetAsync(t.SC->p, 0, sizeof(double) * 9, c->stream));
+    }
+    XTB_T1(c, t.stage);
+    return xtb_stage_finish(c);
 }
 
 }  // namespace
@@ -256,51 +347,43 @@ int xtb_impl_vdw_cells(xtb_ctx* c, int N[3], double* R_cut) {
     const double X = r + 10.0 * d;
     if (Rc < X) Rc = X;
     if (R_cut) *R_cut = Rc;
-    const double* h = c->h_supce;
-    long long cells = 1;
-    for (int a = 0; a < 3; ++a) {                             // get_number_of_image_cells, Atomic_tools.f90:654-702
-        auto dist = [&](double zb) { const double x0 = zb * h[a], y0 = zb * h[a + 3], z0 = zb * h[a + 6]; return sqrt(x0 * x0 + y0 * y0 + z0 * z0); };
-        if (!(dist(1.0) > 0.0)) XTB_FAIL(c, XTB_EINVAL, "vdW: supercell vector %d has no length", a + 1);
-        int n = 0;
-        double R = dist(1.0);
-        while (R < 2.0 * Rc) {
-            n++;
-            R = dist((double)n);
-            if (n > 64) XTB_FAIL(c, XTB_EINVAL, "vdW: more than 64 images of the supercell along axis %d (R_cut = %g A)", a + 1, Rc);
-        }
-        if (n < 1) n = 1;
-        N[a] = n;
-        cells *= 2 * n + 1;
-    }
-    if (cells > 100000) XTB_FAIL(c, XTB_EINVAL, "vdW: %lld image cells (R_cut = %g A)", cells, Rc);
-    return XTB_OK;
+    return image_cells(c, Rc, N, "vdW");
 }
 
-// what: XTB_VDW_DO_* mask.  Energy of every atom on every rank (replicated, like the wall); forces and the supercell-force
-// partial sums of the owned atoms (exchanged / all-reduced by the caller when the context communicates).
+// what: 1 energy | 2 forces | 4 supercell force, one pass
 int xtb_impl_vdw(xtb_ctx* c, unsigned what) {
-    const int na = c->na, nown = c->a1 - c->a0;
     int rc, N[3];
     if ((rc = xtb_impl_vdw_cells(c, N, nullptr))) return rc;
     c->vdw_cells[0] = N[0]; c->vdw_cells[1] = N[1]; c->vdw_cells[2] = N[2];
-    if ((rc = xtb_reserve(c, c->d_Evdw_at, sizeof(double) * na))) return rc;
-    if ((rc = xtb_reserve(c, c->d_Evdw, sizeof(double)))) return rc;
-    if ((rc = xtb_reserve(c, c->d_Fvdw, sizeof(double) * 3 * (size_t)(na + c->nranks)))) return rc;
-    if ((rc = xtb_reserve(c, c->d_SCvdw, sizeof(double) * 9))) return rc;
-    if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)(nown > 0 ? nown : 1)))) return rc;
-    XTB_T0(c, 17);
-    if ((rc = launch_atoms(c, c->a0, nown, what, N))) return rc;
-    if (what & DO_E) {
-        if ((rc = launch_atoms(c, 0, c->a0, DO_E, N)) || (rc = launch_atoms(c, c->a1, na - c->a1, DO_E, N))) return rc;
-        vdw_esum_kernel<<<1, 256, 0, c->stream>>>(na, (const double*)c->d_Evdw_at.p, (double*)c->d_Evdw.p);
-        XTB_LAUNCH_CHECK(c);
+    PairSet t{c->vdw_kind, c->vdw_sym, 0.0, 0.5, 0, &c->d_vdw_params, &c->d_Evdw_at, &c->d_Evdw, &c->d_Fvdw, &c->d_SCvdw, 17};
+    for (auto& p : c->h_vdw) {              // beyond this every class returns exactly zero, value and slope
+        const double r = c->vdw_kind == XTB_VDW_GIRIFALCO ? p.d_cut : p.d0_cut + 10.0 * p.dd_cut;
+        if (r > t.Rmax) t.Rmax = r;
     }
-    if (what & DO_P) {
-        if (nown > 0) {
-            vdw_sum9_kernel<<<9, 128, 0, c->stream>>>(nown, (const double*)c->d_ppart.p, (double*)c->d_SCvdw.p);
-            XTB_LAUNCH_CHECK(c);
-        } else XTB_CUDA(c, cudaMemsetAsync(c->d_SCvdw.p, 0, sizeof(double) * 9, c->stream));
+    return run_set(c, t, what, N, false);
+}
+
+// get_mirror_cell_num_C (Coulomb.f90:435-452): R_cut = TB_Coul(1,1)%dm
+int xtb_impl_coulomb_cells(xtb_ctx* c, int N[3]) {
+    if (c->h_coul.empty()) XTB_FAIL(c, XTB_ESTATE, "Coulomb: no parameters");
+    return image_cells(c, c->h_coul[0].dm, N, "Coulomb");
+}
+
+int xtb_impl_coulomb(xtb_ctx* c, unsigned what) {
+    int rc, N[3];
+    if ((rc = xtb_impl_coulomb_cells(c, N))) return rc;
+    c->coul_cells[0] = N[0]; c->coul_cells[1] = N[1]; c->coul_cells[2] = N[2];
+    const size_t cnt = c->h_coul.size();
+    if (c->coul_dirty) {                    // the device table carries k Q Q (Coulomb_potential: k*Q1*Q2, left to right)
+        std::vector<xtb_vdw_pair> tab(cnt);
+        memset(tab.data(), 0, sizeof(xtb_vdw_pair) * cnt);
+        for (size_t q = 0; q < cnt; ++q) { tab[q].eps = c->h_coul[q].k * c->coul_Q * c->coul_Q; tab[q].d0_cut = c->h_coul[q].dm; tab[q].dd_cut = c->h_coul[q].dd; }
+        if ((rc = xtb_reserve(c, c->d_coul_params, sizeof(xtb_vdw_pair) * cnt))) return rc;
+        XTB_CUDA(c, cudaMemcpyAsync(c->d_coul_params.p, tab.data(), sizeof(xtb_vdw_pair) * cnt, cudaMemcpyHostToDevice, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));        // `tab` is a host temporary
+        c->coul_dirty = false;
     }
-    XTB_T1(c, 17);
-    return xtb_stage_finish(c);
+    PairSet t{KIND_COULOMB, c->coul_sym, 0.0, 1.0, 1, &c->d_coul_params, &c->d_Ecoul_at, &c->d_Ecoul, &c->d_Fcoul, &c->d_SCcoul, 18};
+    for (auto& p : c->h_coul) { const double r = p.dm + p.dd * 10.0; if (r > t.Rmax) t.Rmax = r; }
+    return run_set(c, t, what, N, c->coul_Q <= 1.0e-12);      // CHARGE: Coulomb.f90:762
 }

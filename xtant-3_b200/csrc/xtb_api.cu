@@ -119,6 +119,16 @@ int xtb_impl_pair_terms(xtb_ctx* c, const xtb_step_io* io, bool pressure) {
             if (io && io->SCforce_vdw) XTB_CUDA(c, cudaMemcpyAsync(io->SCforce_vdw, c->d_SCvdw.p, 72, cudaMemcpyDeviceToHost, c->stream));
         }
     }
+    if (!c->h_coul.empty()) {
+        if ((rc = xtb_impl_coulomb(c, pressure ? 7u : 3u))) return rc;
+        if (multi && (rc = xtb_impl_exchange_forces(c, c->d_Fcoul))) return rc;
+        if (io && io->E_coul) XTB_CUDA(c, cudaMemcpyAsync(io->E_coul, c->d_Ecoul.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        if (io && io->F_coul) XTB_CUDA(c, cudaMemcpyAsync(io->F_coul, c->d_Fcoul.p, fb, cudaMemcpyDeviceToHost, c->stream));
+        if (pressure) {
+            if (multi && (rc = xtb_impl_allreduce9(c, (double*)c->d_SCcoul.p))) return rc;
+            if (io && io->SCforce_coul) XTB_CUDA(c, cudaMemcpyAsync(io->SCforce_coul, c->d_SCcoul.p, 72, cudaMemcpyDeviceToHost, c->stream));
+        }
+    }
     return XTB_OK;
 }
 
@@ -169,7 +179,8 @@ int xtb_destroy(xtb_ctx* c) {
                      &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep,
                      &c->d_halo_tr, &c->d_halo_cnt, &c->d_halo_slots, &c->d_halo_send, &c->d_halo_recv, &c->d_wall_params, &c->d_Ewall_at, &c->d_Ewall,
                      &c->d_Fwall, &c->d_SCwall, &c->d_prev_size, &c->d_prev_list, &c->d_dense_out, &c->d_fermi, &c->d_S0, &c->d_SV, &c->d_SV0, &c->d_mdpar,
-                     &c->d_vdw_params, &c->d_Evdw_at, &c->d_Evdw, &c->d_Fvdw, &c->d_SCvdw};
+                     &c->d_vdw_params, &c->d_Evdw_at, &c->d_Evdw, &c->d_Fvdw, &c->d_SCvdw,
+                     &c->d_coul_params, &c->d_Ecoul_at, &c->d_Ecoul, &c->d_Fcoul, &c->d_SCcoul};
     for (DevBuf* b : all) xtb_free(*b);
     for (int s = 0; s < 24; ++s) for (int k = 0; k < 2; ++k) if (c->tev[s][k]) cudaEventDestroy(c->tev[s][k]);
     if (c->h_meta) cudaFreeHost(c->h_meta);
@@ -871,6 +882,80 @@ int xtb_vdw_pressure(xtb_ctx* c, double* SCforce_vdw) {
     return XTB_OK;
 }
 
+// ---- Coulomb term of a charged supercell (fourth part) ----
+int xtb_set_params_coulomb(xtb_ctx* c, int n_kinds, const xtb_coulomb_pair* p) {
+    if (!c) return XTB_EINVAL;
+    if (c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_set_params_coulomb: set the TB parameters first");
+    if (n_kinds == 0 || !p) { c->h_coul.clear(); return XTB_OK; }
+    if (n_kinds != c->n_kinds) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_coulomb: n_kinds=%d (TB part has %d)", n_kinds, c->n_kinds);
+    const size_t cnt = (size_t)n_kinds * n_kinds;
+    c->h_coul.assign(p, p + cnt);
+    c->coul_sym = true;
+    for (int a = 0; a < n_kinds; ++a)
+        for (int b = 0; b < a; ++b)
+            if (memcmp(&p[a + n_kinds * b], &p[b + n_kinds * a], sizeof(xtb_coulomb_pair)) != 0) c->coul_sym = false;
+    c->coul_dirty = true;
+    return XTB_OK;
+}
+
+int xtb_set_charge(xtb_ctx* c, double Q) {
+    if (!c) return XTB_EINVAL;
+    if (Q != c->coul_Q) { c->coul_Q = Q; c->coul_dirty = true; }
+    return XTB_OK;
+}
+
+static int coulomb_ready(xtb_ctx* c, const char* who) {
+    if (c->h_coul.empty()) XTB_FAIL(c, XTB_ESTATE, "%s: no Coulomb parameters (xtb_set_params_coulomb)", who);
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "%s: no system set", who);
+    return XTB_OK;
+}
+
+int xtb_coulomb_image_cells(xtb_ctx* c, int* N) {
+    if (!c || !N) return XTB_EINVAL;
+    int rc;
+    if ((rc = coulomb_ready(c, "xtb_coulomb_image_cells"))) return rc;
+    return xtb_impl_coulomb_cells(c, N);
+}
+
+int xtb_coulomb_energy(xtb_ctx* c, double* E_coul, double* Epot) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = coulomb_ready(c, "xtb_coulomb_energy"))) return rc;
+    if ((rc = xtb_impl_coulomb(c, 1u))) return rc;
+    if (E_coul) XTB_CUDA(c, cudaMemcpyAsync(E_coul, c->d_Ecoul.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (Epot) XTB_CUDA(c, cudaMemcpyAsync(Epot, c->d_Ecoul_at.p, sizeof(double) * c->na, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_coulomb_forces(xtb_ctx* c, double* F_coul) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = coulomb_ready(c, "xtb_coulomb_forces"))) return rc;
+    if ((rc = xtb_impl_coulomb(c, 2u))) return rc;
+    const size_t cnt = 3 * (size_t)(c->a1 - c->a0);
+    if (F_coul && cnt) {
+        XTB_CUDA(c, cudaMemcpyAsync(F_coul + 3 * (size_t)c->a0, (double*)c->d_Fcoul.p + 3 * (size_t)c->a0, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
+int xtb_coulomb_pressure(xtb_ctx* c, double* SCforce_coul) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = coulomb_ready(c, "xtb_coulomb_pressure"))) return rc;
+    if ((rc = xtb_impl_coulomb(c, 4u))) return rc;
+    if (SCforce_coul) {
+        XTB_CUDA(c, cudaMemcpyAsync(SCforce_coul, c->d_SCcoul.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
 int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
     if (!c || !dptr) return XTB_EINVAL;
     const size_t N = (size_t)c->na * c->n_orb;
@@ -892,6 +977,7 @@ int xtb_device_buffer(xtb_ctx* c, int which, void** dptr, size_t* bytes) {
         case XTB_BUF_MIJ: b = &c->d_cpl_M; used = 8 * N * N; break;
         case XTB_BUF_FWALL: b = &c->d_Fwall; used = 24 * (size_t)c->na; break;
         case XTB_BUF_FVDW: b = &c->d_Fvdw; used = 24 * (size_t)c->na; break;
+        case XTB_BUF_FCOUL: b = &c->d_Fcoul; used = 24 * (size_t)c->na; break;
         case XTB_BUF_POS: b = &c->d_S; used = 24 * (size_t)c->na; break;
         case XTB_BUF_VEL: b = &c->d_SV; used = 24 * (size_t)c->na; break;
         case XTB_BUF_EI: if (!c->d_Ei) XTB_FAIL(c, XTB_ESTATE, "xtb_device_buffer: no eigenvalues"); *dptr = (void*)c->d_Ei; if (bytes) *bytes = 8 * N; return XTB_OK;

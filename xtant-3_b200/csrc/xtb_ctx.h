@@ -109,6 +109,12 @@ struct xtb_ctx {
     bool vdw_sym = true;                   // TB_Waals(k1,k2) == TB_Waals(k2,k1) bit for bit
     int vdw_cells[3] = {0, 0, 0};          // image counts of the last launch
     DevBuf d_vdw_params, d_Evdw_at, d_Evdw, d_Fvdw, d_SCvdw;
+    // Coulomb term of a charged cell (vdw.cu): the device table holds k Q Q per pair, rebuilt when Q or the parameters change
+    std::vector<xtb_coulomb_pair> h_coul;  // empty: no Coulomb term set
+    double coul_Q = 0.0;
+    bool coul_dirty = true, coul_sym = true;
+    int coul_cells[3] = {0, 0, 0};
+    DevBuf d_coul_params, d_Ecoul_at, d_Ecoul, d_Fcoul, d_SCcoul;
     // Fermi occupations and velocity-Verlet state (step.cu)
     DevBuf d_fermi;                        // {mu, N(mu), sum f E, iterations}
     DevBuf d_S0, d_SV, d_SV0, d_mdpar;
@@ -206,6 +212,8 @@ int xtb_impl_wall_forces(xtb_ctx* c);
 int xtb_impl_wall_pressure(xtb_ctx* c);
 int xtb_impl_vdw_cells(xtb_ctx* c, int N[3], double* R_cut);   // vdw.cu: get_mirror_cell_num on the host
 int xtb_impl_vdw(xtb_ctx* c, unsigned what);         // what: 1 energy | 2 forces | 4 supercell force, one pass
+int xtb_impl_coulomb_cells(xtb_ctx* c, int N[3]);     // vdw.cu: get_mirror_cell_num_C
+int xtb_impl_coulomb(xtb_ctx* c, unsigned what);
 int xtb_impl_fermi(xtb_ctx* c, double n_electrons, double Te_eV);     // step.cu
 int xtb_impl_assemble(xtb_ctx* c, bool dense);       // xtb_api.cu: dispatch on the TB branch (the `select type` arms)
 int xtb_impl_forces(xtb_ctx* c);

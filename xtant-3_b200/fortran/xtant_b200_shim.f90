@@ -24,7 +24,7 @@ module XTANT_B200_shim
 use, intrinsic :: iso_c_binding
 use Objects, only : Super_cell, Numerics_param, solid, Error_handling, Save_error_details, &
                     TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor, TB_H_DFTB, TB_Rep_DFTB, TB_Exp_wall_simple, &
-                    TB_vdW, TB_vdW_Girifalco, TB_vdW_LJ_cut, TB_vdW_ILJ_cut
+                    TB_vdW, TB_vdW_Girifalco, TB_vdW_LJ_cut, TB_vdW_ILJ_cut, TB_Coulomb, TB_Coulomb_cut
 implicit none
 private
 public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_Aij, Construct_Aij_x_En, &
@@ -33,7 +33,8 @@ public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_
           Construct_Vij_DFTB, construct_TB_H_DFTB, get_dHij_drij_DFTB, Attract_TB_Forces_Press_DFTB, &
           Electron_ion_coupling_Mij, xtb_b200_set_partition, xtb_b200_assemble_blocks, xtb_b200_expand_dense, &
           xtb_b200_density_mirror, xtb_b200_eigensolve, &
-          get_Exp_wall_s, d_Exp_wall_pot_s, d_Exp_wall_Pressure_s, get_vdW_s, vdW_forces, get_mirror_cell_num, xtb_b200_comm_init, xtb_b200_exchange_blocks, &
+          get_Exp_wall_s, d_Exp_wall_pot_s, d_Exp_wall_Pressure_s, get_vdW_s, vdW_forces, get_mirror_cell_num, get_Coulomb_s, Coulomb_forces, &
+          xtb_b200_comm_init, xtb_b200_exchange_blocks, &
           xtb_b200_exchange_forces, xtb_b200_allreduce_scforce, xtb_b200_step, xtb_b200_fermi, xtb_b200_md_half_step, &
           xtb_b200_md_set_velocities, xtb_b200_md_get_state, xtb_b200_check_pending, xtb_b200_dense_density
 
@@ -76,6 +77,10 @@ type, bind(C) :: xtb_vdw_pair               ! class(TB_vdW) Objects.f90:43-46 + 
    real(c_double) :: d0_short, dd_short
 end type xtb_vdw_pair
 
+type, bind(C) :: xtb_coulomb_pair           ! type(TB_Coulomb_cut), Objects.f90:359-366
+   real(c_double) :: k, dm, dd
+end type xtb_coulomb_pair
+
 type, bind(C) :: xtb_step_io                ! struct xtb_step_io (include/xtb_b200.h); c_null_ptr = not given / keep on the device
    type(c_ptr) :: S, supce, fe
    real(c_double) :: n_electrons, Te_eV
@@ -83,6 +88,7 @@ type, bind(C) :: xtb_step_io                ! struct xtb_step_io (include/xtb_b2
    type(c_ptr) :: E_rep, F_rep, SCforce_rep
    type(c_ptr) :: E_wall, F_wall, SCforce_wall
    type(c_ptr) :: E_vdw, F_vdw, SCforce_vdw
+   type(c_ptr) :: E_coul, F_coul, SCforce_coul
 end type xtb_step_io
 
 type(c_ptr), save :: ctx = c_null_ptr      ! one context per process (single caller thread, TB.f90:227-272)
@@ -226,6 +232,24 @@ interface
    end function
    integer(c_int) function xtb_vdw_pressure(c, P_vdw) bind(C, name="xtb_vdw_pressure")
       import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_vdw(3,3)
+   end function
+   integer(c_int) function xtb_set_params_coulomb(c, n_kinds, p) bind(C, name="xtb_set_params_coulomb")
+      import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds; type(c_ptr), value :: p     ! c_null_ptr with n_kinds = 0: no Coulomb term
+   end function
+   integer(c_int) function xtb_set_charge(c, Q) bind(C, name="xtb_set_charge")
+      import; type(c_ptr), value :: c; real(c_double), value :: Q
+   end function
+   integer(c_int) function xtb_coulomb_image_cells(c, N) bind(C, name="xtb_coulomb_image_cells")
+      import; type(c_ptr), value :: c; integer(c_int), intent(out) :: N(3)
+   end function
+   integer(c_int) function xtb_coulomb_energy(c, E_coul, Epot) bind(C, name="xtb_coulomb_energy")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: E_coul; real(c_double), intent(out) :: Epot(*)
+   end function
+   integer(c_int) function xtb_coulomb_forces(c, F_coul) bind(C, name="xtb_coulomb_forces")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: F_coul(3,*)
+   end function
+   integer(c_int) function xtb_coulomb_pressure(c, P_coul) bind(C, name="xtb_coulomb_pressure")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_coul(3,3)
    end function
    integer(c_int) function xtb_fermi_occupations(c, n_electrons, Te_eV, fe, mu, E_band) bind(C, name="xtb_fermi_occupations")
       import; type(c_ptr), value :: c; real(c_double), value :: n_electrons, Te_eV; type(c_ptr), value :: fe, mu, E_band
@@ -430,6 +454,14 @@ subroutine get_near_neighbours(Scell, numpar, include_vdW, dm)
          END ASSOCIATE
       endif
       if (allocated(Scell(NSC)%TB_Waals)) call push_params_vdw(Scell(NSC)%TB_Waals)
+      if (allocated(Scell(NSC)%TB_Coul)) then
+         ASSOCIATE (ARRAY => Scell(NSC)%TB_Coul(:,:))
+            select type(ARRAY)
+            type is (TB_Coulomb_cut)
+               call push_params_coulomb(ARRAY)
+            end select
+         END ASSOCIATE
+      endif
       ! cut-off exactly as Atomic_tools.f90:570-641: the TB part (attractive, raised to the Pettifor repulsive dm) comes
       ! from the library, the arms it has no parameters for are applied here as the reference does
       call check(xtb_cutoff(ctx, rm), 'xtb_cutoff')
@@ -1024,6 +1056,64 @@ subroutine vdW_forces(TB_Waals, Scell, NSC, numpar)      ! TB.f90:3599-3633
       Scell(NSC)%SCforce%rep = Scell(NSC)%SCforce%rep + P                                   ! TB.f90:3845
    endif
 end subroutine vdW_forces
+
+! ---- Coulomb term of a charged supercell (Coulomb.f90:454,715; Coulomb_forces TB.f90:3560 -> d_Forces_s, d_Forces_Pressure) --------
+subroutine push_params_coulomb(TB)
+   type(TB_Coulomb_cut), dimension(:,:), intent(in) :: TB
+   type(xtb_coulomb_pair), allocatable, target :: p(:)
+   integer :: nk, i, j, k
+   nk = size(TB,1)
+   allocate(p(nk*nk))
+   do j = 1, nk
+      do i = 1, nk
+         k = i + nk*(j-1)
+         p(k)%k = TB(i,j)%k ; p(k)%dm = TB(i,j)%dm ; p(k)%dd = TB(i,j)%dd
+      enddo
+   enddo
+   call check(xtb_set_params_coulomb(ctx, int(nk,c_int), c_loc(p)), 'xtb_set_params_coulomb')
+end subroutine push_params_coulomb
+
+subroutine get_Coulomb_s(TB_Coul, Scell, NSC, numpar, a)
+   type(TB_Coulomb_cut), dimension(:,:), intent(in) :: TB_Coul
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), intent(out) :: a
+   real(c_double), allocatable :: Epot(:)
+   integer :: i, na
+   na = size(Scell(NSC)%MDAtoms)
+   allocate(Epot(na))
+   call check(xtb_set_charge(ctx, Scell(NSC)%Q), 'xtb_set_charge')           ! the mean unbalanced charge of THIS step
+   call check(xtb_coulomb_energy(ctx, a, Epot), 'xtb_coulomb_energy')
+   do i = 1, na
+      Scell(NSC)%MDAtoms(i)%Epot = Scell(NSC)%MDAtoms(i)%Epot + Epot(i)      ! Coulomb.f90:543 (not halved, as written)
+   enddo
+end subroutine get_Coulomb_s
+
+subroutine Coulomb_forces(TB_Coul, Scell, NSC, numpar)      ! TB.f90:3560-3596
+   class(TB_Coulomb), allocatable, dimension(:,:), intent(in) :: TB_Coul
+   type(Super_cell), dimension(:), intent(inout) :: Scell
+   integer, intent(in) :: NSC
+   type(Numerics_param), intent(inout) :: numpar
+   real(c_double), allocatable :: F(:,:)
+   real(c_double) :: P(3,3)
+   integer :: k, na
+   if (.not. allocated(TB_Coul)) return
+   select type (TB_Coul)
+   type is (TB_Coulomb_cut)
+      na = size(Scell(NSC)%MDatoms)
+      allocate(F(3,na))
+      call check(xtb_set_charge(ctx, Scell(NSC)%Q), 'xtb_set_charge')
+      call check(xtb_coulomb_forces(ctx, F), 'xtb_coulomb_forces')
+      do k = 1, na
+         Scell(NSC)%MDatoms(k)%forces%rep(:) = Scell(NSC)%MDatoms(k)%forces%rep(:) + F(:,k)    ! TB.f90:3777
+      enddo
+      if (numpar%p_const) then      ! TB.f90:3800
+         call check(xtb_coulomb_pressure(ctx, P), 'xtb_coulomb_pressure')
+         Scell(NSC)%SCforce%rep = Scell(NSC)%SCforce%rep + P                                   ! TB.f90:3845
+      endif
+   end select
+end subroutine Coulomb_forces
 
 ! ---- Fermi occupations / velocity-Verlet halves on the device (Electron_tools.f90:2660,1913; Atomic_tools.f90:1897) ---------
 subroutine xtb_b200_fermi(Netot, Te, fe, mu)

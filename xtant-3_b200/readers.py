@@ -11,6 +11,7 @@ numeric token(s) of a line, Fortran `d` exponents) and returns the dict the C-AB
                                     'Simple_wall'; e.g. the shipped 'Simple_wall:exclude' disables the wall, as in the reference)
     read_vdW_TB                     Read_input_data.f90:1660-1840 + read_vdW_Girifalco_TB :2392-2574, read_vdW_LJ_TB :2576-2652,
                                     read_vdW_ILJ_TB :2654-2716 -> (class, xtb_vdw_pair); the shipped 'Girifalco:exclude' disables it
+    read_Coulomb_TB                 Read_input_data.f90:1846-1917 + read_Coulomb_cut_TB :2360-2386 -> xtb_coulomb_pair ('Coulomb_cut' only)
     read_SAVE                       Dealing_with_output_files.f90:2120-2158 (writer) / Initial_configuration.f90:1594 (reader)
                                     SAVE_atoms.dat + SAVE_supercell.dat -> koa, S, supce
     read_unit_cell                  Unit_cell_equilibrium.txt + Unit_cell_atom_relative_coordinates.txt
@@ -196,6 +197,28 @@ def write_vdW_TB(path, kind, p, enabled=True):
             f.write(f"{_f(p['d0_cut'])}\t{_f(p['dd_cut'])}\t! d0_cut, dd_cut\n")
         else:
             raise ValueError(kind)
+
+
+COULOMB_K = 1.602176634e-19 / (4.0 * 3.1415926535897932384626433832795 * 8.854187817620e-12) * 1.0e10     # g_e/(4 g_Pi g_e0)*1d10, :1907
+
+
+def read_Coulomb_TB(path):
+    """<El>_<El>_TB_Coulomb.txt (Read_input_data.f90:1846-1917): class line 'Coulomb_cut' -> dict(k, dm, dd), k set by the reader
+    (:1907).  Any other first token -- the shipped 'Coulomb_cut:exclude' of INPUT_DATA/Diamond, /C, ... -- falls into
+    `case default` ("Proceeding without Coulomb forces from unballanced charge"): None.  'Cutie' (testing only) is refused."""
+    lines = _lines(path)
+    cls = lines[0].replace(",", " ").split()[0]
+    if cls == "Cutie":
+        raise NotImplementedError(f"{path}: class Cutie is a test stub of the reference")
+    if cls != "Coulomb_cut":
+        return None
+    return {"k": COULOMB_K, "dm": _num(lines[1].split()[0]), "dd": _num(lines[2].split()[0])}
+
+
+def write_Coulomb_TB(path, p, enabled=True):
+    with open(path, "w") as f:
+        f.write("Coulomb_cut\n" if enabled else "Coulomb_cut:exclude\n")
+        f.write(f"{_f(p['dm'])}\t! dm\n{_f(p['dd'])}\t! dd\n")
 
 
 def read_SAVE(atoms_path, cell_path):
