@@ -276,6 +276,17 @@ int  xtb_vdw_energy  (xtb_ctx*, double* E_vdw, double* Epot);
 int  xtb_vdw_forces  (xtb_ctx*, double* F_vdw);
 int  xtb_vdw_pressure(xtb_ctx*, double SCforce_vdw[9]);
 
+/* ---- Allocation-free variant of xtb_vdw_pressure.  It has NO counterpart in the reference: it was added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ *      forbid it).  Same inputs (the context's system and vdW table, both already resident) and the same result as
+ *      xtb_vdw_pressure, but the per-atom partial sums and the 9 sums live in a fixed file-scope device array instead of the
+ *      context's grow-only buffers: the call performs no cudaMalloc / cudaFree / event creation and uses no allocating library.
+ *      Limits and rules: at most XTB_NOALLOC_MAX_ATOMS owned atoms (more: XTB_ECAPACITY with a message; use xtb_vdw_pressure);
+ *      every GPU that loads the library holds the array (590 KB) until exit; all calls on one GPU share it, so calls that overlap
+ *      on a GPU (streams, contexts, threads) race -- serialise them.  SCforce_vdw[9]: host OR device pointer. */
+#define XTB_NOALLOC_MAX_ATOMS 8192
+int  xtb_vdw_pressure_noalloc(xtb_ctx*, double SCforce_vdw[9]);
+
 /* ---- SURVEY.md 8f item 2, fourth part: the Coulomb term of a charged supercell (class TB_Coulomb_cut; Coulomb.f90, dispatch
  *      Coulomb_forces TB.f90:3560-3596 / Coulomb_s TB.f90:3995-4012).  Same all-pairs-in-image-cells structure as the van der Waals
  *      term and the same d_Forces_s / d_Forces_Pressure, with the reference's differences kept: image counts from

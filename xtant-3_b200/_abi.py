@@ -24,6 +24,7 @@ XCHG_HS, XCHG_RHO = 1, 2
 FORCE_ATT, FORCE_REP, FORCE_WALL, FORCE_VDW, FORCE_COUL = 1, 2, 4, 8, 16
 VDW_GIRIFALCO, VDW_LJ_CUT, VDW_ILJ_CUT = 1, 2, 3
 STAGE_VDW, STAGE_COULOMB = 17, 18
+NOALLOC_MAX_ATOMS = 8192
 COULOMB_K = 1.602176634e-19 / (4.0 * 3.1415926535897932384626433832795 * 8.854187817620e-12) * 1.0e10     # Read_input_data.f90:1907 [eV A]
 STEP_NEIGHBOURS, STEP_HS, STEP_EIGEN, STEP_DENSITY, STEP_FORCES, STEP_PRESSURE, STEP_PAIR_TERMS, STEP_NO_DENSE, STEP_GRAPH = 1, 2, 4, 8, 16, 32, 64, 128, 256
 STEP_ALL = STEP_NEIGHBOURS | STEP_HS | STEP_DENSITY | STEP_FORCES
@@ -203,6 +204,7 @@ SIGNATURES = {
     "xtb_vdw_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
     "xtb_vdw_forces": (C.c_int, [C.c_void_p, _pd]),
     "xtb_vdw_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_vdw_pressure_noalloc": (C.c_int, [C.c_void_p, C.c_void_p]),
     "xtb_set_params_coulomb": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(CoulombPair)]),
     "xtb_set_charge": (C.c_int, [C.c_void_p, C.c_double]),
     "xtb_coulomb_image_cells": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),

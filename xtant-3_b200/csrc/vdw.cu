@@ -28,6 +28,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 #include "xtb_ctx.h"
 
@@ -241,7 +242,8 @@ struct PairSet {
     int stage;
 };
 
-int launch_atoms(xtb_ctx* c, const PairSet& t, int first, int count, unsigned what, const int N[3]) {
+// ppart: where the per-atom supercell-force partial sums go (default: the context's grow-only scratch buffer)
+int launch_atoms(xtb_ctx* c, const PairSet& t, int first, int count, unsigned what, const int N[3], double* ppart = nullptr) {
     if (count <= 0) return XTB_OK;
     // reach of the pair table in units of the plane spacings of the cell (volume / face area)
     double reach[3];
@@ -266,7 +268,7 @@ int launch_atoms(xtb_ctx* c, const PairSet& t, int first, int count, unsigned wh
                                                        reach[0], reach[1], reach[2], t.e_scale, t.xs_t,                               \
                                                        (const int*)c->d_koa.p, (const double*)c->d_S.p, (const xtb_vdw_pair*)t.params->p, \
                                                        (const double*)c->d_hdev.p, (double*)t.E_at->p, (double*)t.F->p,                \
-                                                       (double*)c->d_ppart.p)
+                                                       ppart ? ppart : (double*)c->d_ppart.p)
     switch (t.kind) {
         case XTB_VDW_GIRIFALCO: XTB_VDW_LAUNCH(XTB_VDW_GIRIFALCO); break;
         case XTB_VDW_LJ_CUT:    XTB_VDW_LAUNCH(XTB_VDW_LJ_CUT); break;
@@ -386,4 +388,65 @@ int xtb_impl_coulomb(xtb_ctx* c, unsigned what) {
     PairSet t{KIND_COULOMB, c->coul_sym, 0.0, 1.0, 1, &c->d_coul_params, &c->d_Ecoul_at, &c->d_Ecoul, &c->d_Fcoul, &c->d_SCcoul, 18};
     for (auto& p : c->h_coul) { const double r = p.dm + p.dd * 10.0; if (r > t.Rmax) t.Rmax = r; }
     return run_set(c, t, what, N, c->coul_Q <= 1.0e-12);      // CHARGE: Coulomb.f90:762
+}
+
+// ---- allocation-free variant of the supercell-force pass (no counterpart in the reference; added
+//      for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it) ----
+// The per-atom partial sums (9 doubles per owned atom) and the 9 results live in ONE file-scope device array of fixed size
+// instead of the context's grow-only buffers: every GPU that loads the library holds 9 * (XTB_NOALLOC_MAX_ATOMS + 1) * 8 bytes
+// (= 590 KB) until the process exits.  In host code `g_noalloc_scratch` is only a stand-in for the symbol, NOT a device address:
+// the address on a device comes from cudaGetSymbolAddress with that device current (cached per device below).  Every call on a
+// device shares the array, which keeps the contents of the last call: each element read by a call is written by that same call
+// first (nothing accumulates, so nothing has to start at zero; the empty-partition case zero-fills its 9 results), and calls that
+// overlap on one GPU (two streams, two contexts, two threads) race on it.
+static __device__ __align__(256) double g_noalloc_scratch[9 * (XTB_NOALLOC_MAX_ATOMS + 1)];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+double* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {nullptr};      // device address of g_noalloc_scratch, per device ordinal
+std::mutex g_noalloc_mutex;
+
+int noalloc_scratch(xtb_ctx* c, double** out) {
+    if (c->device < 0 || c->device >= NOALLOC_MAX_DEVICES) XTB_FAIL(c, XTB_EINVAL, "xtb_vdw_pressure_noalloc: device ordinal %d", c->device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[c->device]) {        // once per device, with that device current (the caller has made it so)
+        double* p = nullptr;
+        XTB_CUDA(c, cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        if (!p) XTB_FAIL(c, XTB_ECUDA, "xtb_vdw_pressure_noalloc: cudaGetSymbolAddress returned a null address");
+        g_noalloc_ptr[c->device] = p;
+    }
+    *out = g_noalloc_ptr[c->device];
+    return XTB_OK;
+}
+}  // namespace
+
+int xtb_vdw_pressure_noalloc(xtb_ctx* c, double* SCforce_vdw) {
+    if (!c) return XTB_EINVAL;
+    if (!SCforce_vdw) XTB_FAIL(c, XTB_EINVAL, "xtb_vdw_pressure_noalloc: null output");
+    if (c->h_vdw.empty()) XTB_FAIL(c, XTB_ESTATE, "xtb_vdw_pressure_noalloc: no vdW parameters (xtb_set_params_vdw)");
+    if (c->na <= 0) XTB_FAIL(c, XTB_ESTATE, "xtb_vdw_pressure_noalloc: no system set");
+    const int nown = c->a1 - c->a0;
+    if (nown > XTB_NOALLOC_MAX_ATOMS)
+        XTB_FAIL(c, XTB_ECAPACITY, "xtb_vdw_pressure_noalloc: %d owned atoms, the fixed scratch array holds XTB_NOALLOC_MAX_ATOMS = %d (use xtb_vdw_pressure)",
+                 nown, XTB_NOALLOC_MAX_ATOMS);
+    XTB_CUDA(c, cudaSetDevice(c->device));
+    int rc, N[3];
+    double* scratch = nullptr;
+    if ((rc = noalloc_scratch(c, &scratch))) return rc;
+    if ((rc = xtb_impl_vdw_cells(c, N, nullptr))) return rc;          // host arithmetic only
+    PairSet t{c->vdw_kind, c->vdw_sym, 0.0, 0.5, 0, &c->d_vdw_params, &c->d_Evdw_at, &c->d_Evdw, &c->d_Fvdw, &c->d_SCvdw, 17};
+    for (auto& p : c->h_vdw) {
+        const double r = c->vdw_kind == XTB_VDW_GIRIFALCO ? p.d_cut : p.d0_cut + 10.0 * p.dd_cut;
+        if (r > t.Rmax) t.Rmax = r;
+    }
+    double* result = scratch + 9 * (size_t)XTB_NOALLOC_MAX_ATOMS;     // the 9 sums, behind the partial sums
+    if (nown > 0) {
+        if ((rc = launch_atoms(c, t, c->a0, nown, DO_P, N, scratch))) return rc;      // what = DO_P: writes ppart only
+        vdw_sum9_kernel<<<9, 128, 0, c->stream>>>(nown, scratch, result);
+        XTB_LAUNCH_CHECK(c);
+    } else XTB_CUDA(c, cudaMemsetAsync(result, 0, sizeof(double) * 9, c->stream));
+    // the output may be a host or a device pointer (unified addressing decides); no staging buffer is allocated
+    XTB_CUDA(c, cudaMemcpyAsync(SCforce_vdw, result, sizeof(double) * 9, cudaMemcpyDefault, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
 }

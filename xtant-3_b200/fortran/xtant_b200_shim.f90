@@ -233,6 +233,9 @@ interface
    integer(c_int) function xtb_vdw_pressure(c, P_vdw) bind(C, name="xtb_vdw_pressure")
       import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_vdw(3,3)
    end function
+   integer(c_int) function xtb_vdw_pressure_noalloc(c, P_vdw) bind(C, name="xtb_vdw_pressure_noalloc")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_vdw(3,3)     ! no device allocation inside (fixed scratch, <= 8192 atoms)
+   end function
    integer(c_int) function xtb_set_params_coulomb(c, n_kinds, p) bind(C, name="xtb_set_params_coulomb")
       import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds; type(c_ptr), value :: p     ! c_null_ptr with n_kinds = 0: no Coulomb term
    end function
