@@ -94,6 +94,26 @@ typedef struct xtb_wall_pair {
     double dd;    /* [A] cut-off smoothing width */
 } xtb_wall_pair;
 
+/* type(TB_Short_Rep), Objects.f90:437-454, the 'General' class of <El>_<El>_TB_short.txt / _TB_wall.txt (reader read_Short_Rep_TB,
+ * Read_input_data.f90:2110-2312): the sum of up to six functions of r under one Fermi cut-off,
+ *   Pot(r) = [ C exp(1/(r - r0))  +  Phi exp(-(r - r0)/a)  +  sum_i Phi_i (r/r0_i)^m_i  +  ZBL(Z1,Z2,r)  +  NLH(Z1,Z2,r)  +  Tab(r) ] / (1 + exp((r - d0)/dd)),
+ * zero for r >= d0 + 10 dd (Shortrange_pot, Exponential_wall.f90:130-157).  (f_cut_inv is read by the reference but never used.)
+ * Tab: grid tab_R[n_tab] (increasing), tab_E[n_tab]; tab_spline = 0: linear interpolation (linear_interpolation, Little_subroutines.f90:1031),
+ * tab_spline = 1: cubic a + b x + c x^2 + d x^3 with the coefficients of make_cubic_splines (Algebra_tools.f90:115-190), all [n_tab];
+ * the arrays are copied by xtb_set_params_short during the call.  NLH: a[3], b[3] of the pair from nlh_coeffs.dat (get_NLH_coefficients). */
+#define XTB_SHORT_MAX_POW 8
+typedef struct xtb_short_pair {
+    double  d0, dd;                                   /* f_cut [A] */
+    int32_t use_exp, use_inv_exp, use_zbl, use_nlh;
+    double  exp_Phi, exp_r0, exp_a;                   /* f_exp */
+    double  inv_C, inv_r0;                            /* f_inv_exp */
+    int32_t n_pow, n_tab;
+    double  pow_Phi[XTB_SHORT_MAX_POW], pow_r0[XTB_SHORT_MAX_POW], pow_m[XTB_SHORT_MAX_POW];   /* f_pow(1:n_pow) */
+    double  nlh_a[3], nlh_b[3];                       /* f_NLH */
+    int32_t tab_spline, pad_;
+    const double *tab_R, *tab_E, *tab_a, *tab_b, *tab_c, *tab_d;      /* f_tab; a..d may be NULL when tab_spline = 0 */
+} xtb_short_pair;
+
 /* class(TB_vdW), Objects.f90:43-46 (parent: d0_cut, dd_cut) with its three usable extensions in one record:
  *   XTB_VDW_GIRIFALCO  type(TB_vdW_Girifalco) :302-328, file order read_vdW_Girifalco_TB (Read_input_data.f90:2392-2574):
  *                      C12 / r^12 - C6 / r^6 for dsm <= r <= dm, cubic a r^3 + b r^2 + c r + d on (dm, d_cut], quintic
@@ -258,6 +278,18 @@ int  xtb_set_params_wall(xtb_ctx*, int n_kinds, const xtb_wall_pair* p);
 int  xtb_wall_energy  (xtb_ctx*, double* E_wall, double* Epot);
 int  xtb_wall_forces  (xtb_ctx*, double* F_wall);
 int  xtb_wall_pressure(xtb_ctx*, double SCforce_wall[9]);
+
+/* ---- The 'General' short-range class (TB_Short_Rep) in the same slot as the simple wall (Scell%TB_Expwall holds ONE class; setting
+ *      one here replaces the other; dispatch Exponential_wall_forces TB.f90:3533-3556, Exponential_wall_s TB.f90:3975-3993).
+ *      Z[n_kinds] = matter%Atoms(:)%Z, the atomic numbers (ZBL / NLH).  Results land in the wall buffers: xtb_step reports them as
+ *      E_wall / F_wall / SCforce_wall, XTB_FORCE_WALL selects them in the integrator.
+ *      xtb_short_energy    get_short_range_rep_s    (Exponential_wall.f90:48-127)
+ *      xtb_short_forces    d_Short_range_pot_s      (:519-659): the term ADDED to forces%rep
+ *      xtb_short_pressure  d_Short_range_Pressure_s (:664-719): the term ADDED to SCforce%rep */
+int  xtb_set_params_short(xtb_ctx*, int n_kinds, const xtb_short_pair* p, const double* Z);
+int  xtb_short_energy  (xtb_ctx*, double* E_short, double* Epot);
+int  xtb_short_forces  (xtb_ctx*, double* F_short);
+int  xtb_short_pressure(xtb_ctx*, double SCforce_short[9]);
 
 /* ---- SURVEY.md 8f item 2, third part: the van der Waals pair term (class TB_vdW; Van_der_Waals.f90, dispatch vdW_forces
  *      TB.f90:3599-3633 / vdW_s TB.f90:4017-4035).  Unlike every other term it does NOT use the neighbour list: it sums over

@@ -35,7 +35,7 @@ _pi = C.POINTER(C.c_int)
 
 def build(force=False):
     so = os.path.join(_HERE, "liboracle.so")
-    src = [os.path.join(_HERE, f) for f in ("xtant_oracle.c", "sk_tables.h", "pettifor_oracle.c", "dftb_oracle.c", "wall_oracle.c", "vdw_oracle.c")]
+    src = [os.path.join(_HERE, f) for f in ("xtant_oracle.c", "sk_tables.h", "pettifor_oracle.c", "dftb_oracle.c", "wall_oracle.c", "vdw_oracle.c", "short_oracle.c")]
     src = [s for s in src if os.path.exists(s)]
     if force or not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in src):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
@@ -55,6 +55,9 @@ def lib():
         _LIB.orc_wall_energy.restype = C.c_double
         _LIB.orc_fermi.restype = C.c_double
         _LIB.orc_vdw_energy.restype = C.c_double
+        _LIB.orc_short_energy.restype = C.c_double
+        _LIB.orc_short_V.restype = C.c_double
+        _LIB.orc_short_dV.restype = C.c_double
         _LIB.orc_vdw_V.restype = C.c_double
         _LIB.orc_vdw_dV.restype = C.c_double
     return _LIB
@@ -188,6 +191,56 @@ def wall_params_array(params):
     for i, d in enumerate(params):
         arr[i] = _abi.WallPair(float(d["C"]), float(d["r0"]), float(d["d0"]), float(d["dd"]))
     return arr
+
+
+# ---- the 'General' short-range class (Exponential_wall.f90, class TB_Short_Rep) ----
+def _short_args(wl):
+    arr, keep = _abi.short_pair_array(wl["short_params"])
+    Z = np.ascontiguousarray(wl["Z"], dtype=np.float64)
+    return arr, Z, keep
+
+
+def short_pair_value(p, r, Z1=1.0, Z2=1.0, deriv=False):
+    """Shortrange_pot / d_Short_range_pot of one pair (Exponential_wall.f90:130-203)"""
+    arr, keep = _abi.short_pair_array([p])
+    f = lib().orc_short_dV if deriv else lib().orc_short_V
+    return float(f(arr, C.c_double(float(r)), C.c_double(float(Z1)), C.c_double(float(Z2))))
+
+
+def make_cubic_splines(x, y):
+    """make_cubic_splines, Algebra_tools.f90:115-190 (the oracle's own restatement, independent of readers.py)"""
+    x = np.ascontiguousarray(x, dtype=np.float64); y = np.ascontiguousarray(y, dtype=np.float64)
+    out = [np.zeros(len(x)) for _ in range(4)]
+    lib().orc_make_cubic_splines(C.c_int(len(x)), _p(x), _p(y), *[_p(o) for o in out])
+    return tuple(out)
+
+
+def short_energy(wl, nb):
+    """get_short_range_rep_s, Exponential_wall.f90:48-127 -> (E, per-atom halves added to Epot)"""
+    arr, Z, keep = _short_args(wl)
+    Epot = np.zeros(nb.na)
+    E = lib().orc_short_energy(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(Z), _p(nb.size), _p(nb.list),
+                               _p(nb.dist), arr, _p(Epot))
+    return float(E), Epot
+
+
+def short_forces(wl, nb):
+    """d_Short_range_pot_s, Exponential_wall.f90:519-659 (verbatim loop nest) -> the term added to forces%rep (na,3)"""
+    arr, Z, keep = _short_args(wl)
+    F = np.zeros((nb.na, 3))
+    h = np.asfortranarray(wl["supce"], dtype=np.float64).ravel(order="F").copy()
+    lib().orc_short_forces(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(Z), _p(h), _p(nb.size), _p(nb.list),
+                           _p(nb.dist), arr, _p(F))
+    return F
+
+
+def short_pressure(wl, nb):
+    """d_Short_range_Pressure_s, Exponential_wall.f90:664-719 -> the term added to SCforce%rep(3,3)"""
+    arr, Z, keep = _short_args(wl)
+    P = np.zeros(9)
+    lib().orc_short_pressure(C.c_int(nb.na), C.c_int(nb.cap), C.c_int(wl["n_kinds"]), _p(_koa0(wl)), _p(Z), _p(nb.size), _p(nb.list),
+                             _p(nb.dist), _p(nb.dist_s), arr, _p(P))
+    return P.reshape(3, 3, order="F")
 
 
 # ---- van der Waals term (Van_der_Waals.f90, class TB_vdW) ----

@@ -906,4 +906,5 @@ void orc_dks_block(const double* V, const double* dV, double l, double m, double
 #include "pettifor_oracle.c"
 #include "dftb_oracle.c"
 #include "wall_oracle.c"
+#include "short_oracle.c"
 #include "vdw_oracle.c"

@@ -10,6 +10,7 @@ It writes
     xtant-3_b200/data/params_pettifor_rep_C.json    Pettifor repulsive parameter set
     xtant-3_b200/data/params_vdw_{C_amorphous,I_lj}.json   van der Waals sets: Girifalco (INPUT_DATA/Amorphous_Carbon, the only
                                                     carbon folder of the configurations whose class line is active) and LJ (PbI2)
+    xtant-3_b200/data/params_short_{I_I,Pb_I,Pb_Pb,Fe_Fe,O_O_tab}.json   'General' short-range sets: Pow + ZBL (PbI2), Exp (Fe), Tab (PbO2)
     xtant-3_b200/data/cell_ac216.json               the reference's own 216-atom amorphous-carbon cell
     xtant-3_b200/data/cell_{diamond64,al500,au108}.json   relative coords + supercell
     xtant-3_b200/data/dftb_{matsci_SiAl,mio_CH}.npz  DFTB Slater-Koster tables (INPUT_DATA/DFTB/<set>/<A>-<B>.skf, read by
@@ -38,6 +39,13 @@ parse_nrl, parse_pettifor, parse_pettifor_rep, parse_cell = (_rd.read_Mehl_TB_Ha
                                                              _rd.read_Pettifor_TB_repulsive, _rd.read_SAVE)
 
 
+def short(path):
+    p = _rd.read_Short_Rep_TB(path)
+    if p["tab"] is not None:            # the splines are remade on load (workloads.load_short)
+        p["tab"] = {"R": [float(x) for x in p["tab"]["R"]], "E": [float(x) for x in p["tab"]["E"]], "spline": p["tab"]["spline"]}
+    return p
+
+
 def vdw(path):
     kind, p = _rd.read_vdW_TB(path)
     return dict(p, kind=kind)
@@ -59,6 +67,11 @@ def main():
                                               f"{REF}/Aluminum/SAVE_supercell_500atoms.dat"),
         "params_vdw_C_amorphous.json": lambda: vdw(f"{REF}/Amorphous_Carbon/C_C_TB_vdW.txt"),
         "params_vdw_I_lj.json": lambda: vdw(f"{REF}/PbI2/I_I_TB_vdW.txt"),
+        "params_short_I_I.json": lambda: short(f"{REF}/PbI2/I_I_TB_short.txt"),
+        "params_short_Pb_I.json": lambda: short(f"{REF}/PbI2/Pb_I_TB_short.txt"),
+        "params_short_Pb_Pb.json": lambda: short(f"{REF}/PbI2/Pb_Pb_TB_short.txt"),
+        "params_short_Fe_Fe.json": lambda: short(f"{REF}/Fe/Fe_Fe_TB_short.txt"),
+        "params_short_O_O_tab.json": lambda: short(f"{REF}/PbO2/O_O_TB_short.txt"),
         "cell_ac216.json": lambda: parse_cell(f"{REF}/Amorphous_Carbon/SAVE_atoms.dat", f"{REF}/Amorphous_Carbon/SAVE_supercell.dat"),
         "cell_au108.json": lambda: parse_cell(f"{REF}/Gold/SAVE_atoms.dat", f"{REF}/Gold/SAVE_supercell.dat"),
     }

@@ -16,7 +16,8 @@ NAMES = ["get_near_neighbours", "Construct_Vij_NRL", "construct_TB_H_NRL", "Cons
          "get_Erep_s", "dErdr_s", "dErdr_Pressure_s", "Construct_Vij_DFTB", "construct_TB_H_DFTB", "get_dHij_drij_DFTB",
          "Attract_TB_Forces_Press_DFTB", "Electron_ion_coupling_Mij",
          "get_Exp_wall_s", "d_Exp_wall_pot_s", "d_Exp_wall_Pressure_s", "get_vdW_s", "vdW_forces", "get_mirror_cell_num",
-         "get_Coulomb_s", "Coulomb_forces"]
+         "get_Coulomb_s", "Coulomb_forces",
+         "get_short_range_rep_s", "d_Short_range_pot_s", "d_Short_range_Pressure_s"]
 
 
 def subroutines(text):

@@ -109,7 +109,7 @@ def test_fortran_shim_struct_mirrors_match_ctypes_layout():
     shim = open(os.path.join(root, "xtant-3_b200", "fortran", "xtant_b200_shim.f90")).read()
     mirrors = {"xtb_nrl_pair": abi.NrlPair, "xtb_pettifor_pair": abi.PettiforPair,
                "xtb_pettifor_rep_pair": abi.PettiforRepPair, "xtb_dftb_pair": abi.DftbPair,
-               "xtb_wall_pair": abi.WallPair, "xtb_vdw_pair": abi.VdwPair, "xtb_coulomb_pair": abi.CoulombPair,
+               "xtb_wall_pair": abi.WallPair, "xtb_vdw_pair": abi.VdwPair, "xtb_coulomb_pair": abi.CoulombPair, "xtb_short_pair": abi.ShortPair,
                "xtb_step_io": abi.StepIO}
     size = {"c_double": 8, "c_int": 4, "c_int32_t": 4, "c_ptr": 8}
     for name, cls in mirrors.items():
@@ -145,7 +145,7 @@ def test_fortran_shim_wrappers_keep_the_reference_argument_lists():
     for m in re.finditer(r"^\s*subroutine\s+(\w+)\s*\(([^)]*)\)", shim, flags=re.M | re.I):
         mine.setdefault(m.group(1).lower(), [a.strip().lower() for a in m.group(2).split(",") if a.strip()])
     pub = re.search(r"public ::(.*?)\n\s*\n", shim, flags=re.S).group(1).lower()
-    assert len(ref) == 26
+    assert len(ref) == 29
     for name, sig in ref.items():
         assert name.lower() in mine, name
         assert re.search(r"\b" + name.lower() + r"\b", pub), f"{name} is not public in the shim"

@@ -37,9 +37,8 @@ def test_reader_class_line_semantics(tmp_path):
     assert rd.read_Exponential_wall_TB(str(p)) == WALL_AL
     rd.write_Exponential_wall_TB(str(p), WALL_AL, enabled=False)       # 'Simple_wall:exclude' -> case default -> no wall
     assert rd.read_Exponential_wall_TB(str(p)) is None
-    p.write_text("General\n")
-    with pytest.raises(NotImplementedError):
-        rd.read_Exponential_wall_TB(str(p))
+    p.write_text("General\n")                                            # the other class of the slot: read_Short_Rep_TB's
+    assert rd.read_Exponential_wall_TB(str(p)) is None and rd.read_Short_Rep_TB(str(p))["d0"] == 0.0
 
 
 def test_reference_fixture_files_when_present():

@@ -79,6 +79,58 @@ def vdw_pair_from_dict(d):
     return p
 
 
+SHORT_MAX_POW = 8
+
+
+class ShortPair(C.Structure):
+    """struct xtb_short_pair == type(TB_Short_Rep), Objects.f90:437-454 (tables by address)"""
+    _fields_ = [("d0", C.c_double), ("dd", C.c_double),
+                ("use_exp", C.c_int32), ("use_inv_exp", C.c_int32), ("use_zbl", C.c_int32), ("use_nlh", C.c_int32),
+                ("exp_Phi", C.c_double), ("exp_r0", C.c_double), ("exp_a", C.c_double),
+                ("inv_C", C.c_double), ("inv_r0", C.c_double),
+                ("n_pow", C.c_int32), ("n_tab", C.c_int32),
+                ("pow_Phi", C.c_double * SHORT_MAX_POW), ("pow_r0", C.c_double * SHORT_MAX_POW), ("pow_m", C.c_double * SHORT_MAX_POW),
+                ("nlh_a", C.c_double * 3), ("nlh_b", C.c_double * 3),
+                ("tab_spline", C.c_int32), ("pad_", C.c_int32),
+                ("tab_R", C.POINTER(C.c_double)), ("tab_E", C.POINTER(C.c_double)), ("tab_a", C.POINTER(C.c_double)),
+                ("tab_b", C.POINTER(C.c_double)), ("tab_c", C.POINTER(C.c_double)), ("tab_d", C.POINTER(C.c_double))]
+
+
+def short_pair_array(params):
+    """list of dicts as readers.read_Short_Rep_TB returns them -> (ShortPair array, objects to keep alive during the call).
+    dict keys: d0, dd; exp = (Phi, r0, a); inv_exp = (C, r0); pow = [(Phi, r0, m), ...]; zbl, nlh = bool; nlh_a, nlh_b;
+    tab = dict(R, E, spline[, a, b, c, d])"""
+    import numpy as np
+    arr = (ShortPair * len(params))()
+    keep = []
+    for q, d in enumerate(params):
+        s = arr[q]
+        s.d0 = float(d.get("d0", 0.0)); s.dd = float(d.get("dd", 0.01))                  # defaults of read_Short_Rep_TB
+        if d.get("exp") is not None:
+            s.use_exp = 1; s.exp_Phi, s.exp_r0, s.exp_a = (float(x) for x in d["exp"])
+        if d.get("inv_exp") is not None:
+            s.use_inv_exp = 1; s.inv_C, s.inv_r0 = (float(x) for x in d["inv_exp"])
+        pw = d.get("pow") or []
+        if len(pw) > SHORT_MAX_POW:
+            raise ValueError(f"{len(pw)} power terms (max {SHORT_MAX_POW})")
+        s.n_pow = len(pw)
+        for k, (Phi, r0, m) in enumerate(pw):
+            s.pow_Phi[k] = float(Phi); s.pow_r0[k] = float(r0); s.pow_m[k] = float(m)
+        s.use_zbl = 1 if d.get("zbl") else 0
+        s.use_nlh = 1 if d.get("nlh") else 0
+        for k in range(3):
+            s.nlh_a[k] = float(d.get("nlh_a", (0, 0, 0))[k]); s.nlh_b[k] = float(d.get("nlh_b", (0, 0, 0))[k])
+        t = d.get("tab")
+        if t is not None:
+            s.n_tab = len(t["R"]); s.tab_spline = 1 if t.get("spline") else 0
+            for name in ("R", "E", "a", "b", "c", "d"):
+                if t.get(name) is not None:
+                    a = np.ascontiguousarray(t[name], dtype=np.float64)
+                    keep.append(a)
+                    setattr(s, "tab_" + name, a.ctypes.data_as(C.POINTER(C.c_double)))
+    return arr, keep
+
+
 class CoulombPair(C.Structure):
     """struct xtb_coulomb_pair == type(TB_Coulomb_cut), Objects.f90:359-366 (k, dm, dd)"""
     _fields_ = [("k", C.c_double), ("dm", C.c_double), ("dd", C.c_double)]
@@ -199,6 +251,10 @@ SIGNATURES = {
     "xtb_wall_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
     "xtb_wall_forces": (C.c_int, [C.c_void_p, _pd]),
     "xtb_wall_pressure": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_set_params_short": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(ShortPair), _pd]),
+    "xtb_short_energy": (C.c_int, [C.c_void_p, _pd, _pd]),
+    "xtb_short_forces": (C.c_int, [C.c_void_p, _pd]),
+    "xtb_short_pressure": (C.c_int, [C.c_void_p, _pd]),
     "xtb_set_params_vdw": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(VdwPair)]),
     "xtb_vdw_image_cells": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), _pd]),
     "xtb_vdw_energy": (C.c_int, [C.c_void_p, _pd, _pd]),

@@ -106,6 +106,8 @@ class TBContext:
         self.tb = wl["tb"]
         if wl.get("wall_params"):
             self.set_params_wall(wl["wall_params"])
+        if wl.get("short_params"):
+            self.set_params_short(wl["short_params"], wl["Z"])
         if wl.get("vdw_params"):
             self.set_params_vdw(wl["vdw_kind"], wl["vdw_params"])
         if wl.get("coulomb_params"):
@@ -137,6 +139,17 @@ class TBContext:
         nk = int(round(len(params) ** 0.5))
         arr = (_abi.VdwPair * len(params))(*[_abi.vdw_pair_from_dict(d) for d in params])
         self._ck(self.lib.xtb_set_params_vdw(self.h, int(kind), nk, arr))
+
+    def set_params_short(self, params, Z):
+        """Scell%TB_Expwall(:,:) of class TB_Short_Rep ('General'): list of dicts (readers.read_Short_Rep_TB), (koa1, koa2)
+        column-major, Z = atomic numbers per kind; replaces a simple wall; None / [] removes it"""
+        if not params:
+            self._ck(self.lib.xtb_set_params_short(self.h, 0, None, None))
+            return
+        nk = int(round(len(params) ** 0.5))
+        arr, keep = _abi.short_pair_array(params)
+        Zs = np.ascontiguousarray(Z, dtype=np.float64)
+        self._ck(self.lib.xtb_set_params_short(self.h, nk, arr, _dp(Zs)))
 
     def set_params_wall(self, params):
         """Scell%TB_Expwall(:,:) of class TB_Exp_wall_simple: list of dict(C, r0, d0, dd), (koa1, koa2) column-major; None / [] removes it"""
@@ -325,6 +338,25 @@ class TBContext:
         """d_Exp_wall_Pressure_s, Exponential_wall.f90:1334 -> the term added to SCforce%rep(3,3)"""
         P = np.zeros(9)
         self._ck(self.lib.xtb_wall_pressure(self.h, _dp(P)))
+        return P.reshape(3, 3, order="F")
+
+    # -- the 'General' short-range class in the slot of the wall ----------------------------------
+    def get_short_range_rep_s(self):
+        """get_short_range_rep_s, Exponential_wall.f90:48 -> (E [eV], per-atom halves added to MDAtoms(:)%Epot)"""
+        E = np.zeros(1); Epot = np.zeros(self.na)
+        self._ck(self.lib.xtb_short_energy(self.h, _dp(E), _dp(Epot)))
+        return float(E[0]), Epot
+
+    def d_Short_range_pot_s(self):
+        """d_Short_range_pot_s, Exponential_wall.f90:519 -> the term added to forces%rep, (na,3)"""
+        F = np.zeros((self.na, 3))
+        self._ck(self.lib.xtb_short_forces(self.h, _dp(F)))
+        return F
+
+    def d_Short_range_Pressure_s(self):
+        """d_Short_range_Pressure_s, Exponential_wall.f90:664 -> the term added to SCforce%rep(3,3)"""
+        P = np.zeros(9)
+        self._ck(self.lib.xtb_short_pressure(self.h, _dp(P)))
         return P.reshape(3, 3, order="F")
 
     # -- van der Waals term (SURVEY.md 8f item 2, third part) -------------------------------------

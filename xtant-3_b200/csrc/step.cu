@@ -367,7 +367,8 @@ struct GraphKey {
     const void *Ha, *Ei, *fe;
     cudaStream_t stream;
     double rm, f_cut;
-    bool rep, wall;
+    bool rep;
+    int wall;                // 0 none, 1 simple wall, 2 General class (different kernels)
     int vdw_kind, vdw_cells[3];
     int coul, coul_cells[3];
     double coul_Q;
@@ -387,7 +388,7 @@ static GraphKey make_key(const xtb_ctx* c, unsigned flags, const xtb_step_io* io
     k.na = c->na; k.cap = c->cap; k.max_nn = c->max_nn; k.tb = c->tb; k.n_orb = c->n_orb; k.a0 = c->a0; k.a1 = c->a1; k.n_kinds = c->n_kinds;
     k.blk_cap = c->blk_cap; k.k_kept = c->k_kept; k.K = c->K; k.alloc_epoch = c->alloc_epoch;
     k.Ha = c->d_Ha ? (const void*)c->d_Ha : (const void*)c->d_HaT; k.Ei = c->d_Ei; k.fe = c->d_fe; k.stream = c->stream; k.rm = c->rm; k.f_cut = c->f_cut;
-    k.rep = !c->h_pet_rep.empty(); k.wall = !c->h_wall.empty();
+    k.rep = !c->h_pet_rep.empty(); k.wall = !c->h_short.empty() ? 2 : (!c->h_wall.empty() ? 1 : 0);
     if (!c->h_vdw.empty()) {                 // the image counts are launch arguments (supce cannot change inside a graph step)
         k.vdw_kind = c->vdw_kind;
         xtb_impl_vdw_cells(const_cast<xtb_ctx*>(c), k.vdw_cells, nullptr);

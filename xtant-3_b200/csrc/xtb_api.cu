@@ -82,7 +82,7 @@ int xtb_impl_pressure(xtb_ctx* c) {
 
 // pair terms of a fused step: Pettifor-type repulsive part, short-range wall, van der Waals term, whichever the context holds
 int xtb_impl_pair_terms(xtb_ctx* c, const xtb_step_io* io, bool pressure) {
-    const bool list_terms = (c->tb == XTB_TB_PETTIFOR && !c->h_pet_rep.empty()) || !c->h_wall.empty();
+    const bool list_terms = (c->tb == XTB_TB_PETTIFOR && !c->h_pet_rep.empty()) || xtb_has_wall(c);
     if (list_terms && !c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "pair terms: no neighbour list");
     int rc;
     const size_t fb = sizeof(double) * 3 * c->na;
@@ -98,7 +98,7 @@ int xtb_impl_pair_terms(xtb_ctx* c, const xtb_step_io* io, bool pressure) {
             if (io && io->SCforce_rep) XTB_CUDA(c, cudaMemcpyAsync(io->SCforce_rep, c->d_SCrep.p, 72, cudaMemcpyDeviceToHost, c->stream));
         }
     }
-    if (!c->h_wall.empty()) {
+    if (xtb_has_wall(c)) {
         if ((rc = xtb_impl_wall_energy(c)) || (rc = xtb_impl_wall_forces(c))) return rc;
         if (multi && (rc = xtb_impl_exchange_forces(c, c->d_Fwall))) return rc;
         if (io && io->E_wall) XTB_CUDA(c, cudaMemcpyAsync(io->E_wall, c->d_Ewall.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
@@ -180,7 +180,7 @@ int xtb_destroy(xtb_ctx* c) {
                      &c->d_halo_tr, &c->d_halo_cnt, &c->d_halo_slots, &c->d_halo_send, &c->d_halo_recv, &c->d_wall_params, &c->d_Ewall_at, &c->d_Ewall,
                      &c->d_Fwall, &c->d_SCwall, &c->d_prev_size, &c->d_prev_list, &c->d_dense_out, &c->d_fermi, &c->d_S0, &c->d_SV, &c->d_SV0, &c->d_mdpar,
                      &c->d_vdw_params, &c->d_Evdw_at, &c->d_Evdw, &c->d_Fvdw, &c->d_SCvdw,
-                     &c->d_coul_params, &c->d_Ecoul_at, &c->d_Ecoul, &c->d_Fcoul, &c->d_SCcoul};
+                     &c->d_coul_params, &c->d_Ecoul_at, &c->d_Ecoul, &c->d_Fcoul, &c->d_SCcoul, &c->d_short_params, &c->d_short_tab};
     for (DevBuf* b : all) xtb_free(*b);
     for (int s = 0; s < 24; ++s) for (int k = 0; k < 2; ++k) if (c->tev[s][k]) cudaEventDestroy(c->tev[s][k]);
     if (c->h_meta) cudaFreeHost(c->h_meta);
@@ -755,6 +755,7 @@ int xtb_set_params_wall(xtb_ctx* c, int n_kinds, const xtb_wall_pair* p) {
     for (size_t q = 0; q < cnt; ++q)
         if (!(p[q].dd > 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_wall: pair %zu has smoothing width dd=%g", q, p[q].dd);
     c->h_wall.assign(p, p + cnt);
+    c->h_short.clear();                      // one class in the TB_Expwall slot
     int rc = xtb_reserve(c, c->d_wall_params, sizeof(xtb_wall_pair) * cnt);
     if (rc) return rc;
     XTB_CUDA(c, cudaMemcpyAsync(c->d_wall_params.p, p, sizeof(xtb_wall_pair) * cnt, cudaMemcpyHostToDevice, c->stream));
@@ -802,6 +803,108 @@ int xtb_wall_pressure(xtb_ctx* c, double* SCforce_wall) {
     if ((rc = xtb_impl_wall_pressure(c))) return rc;
     if (SCforce_wall) {
         XTB_CUDA(c, cudaMemcpyAsync(SCforce_wall, c->d_SCwall.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
+// ---- the 'General' short-range class (TB_Short_Rep) in the slot of the simple wall ----
+int xtb_set_params_short(xtb_ctx* c, int n_kinds, const xtb_short_pair* p, const double* Z) {
+    if (!c) return XTB_EINVAL;
+    if (c->tb == XTB_TB_NONE) XTB_FAIL(c, XTB_ESTATE, "xtb_set_params_short: set the TB parameters first");
+    if (n_kinds == 0 || !p) { c->h_short.clear(); return XTB_OK; }        // "proceeding without short-range forces"
+    if (n_kinds != c->n_kinds) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: n_kinds=%d (TB part has %d)", n_kinds, c->n_kinds);
+    if (!Z) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: atomic numbers Z[n_kinds] are required");
+    cudaSetDevice(c->device);
+    const size_t cnt = (size_t)n_kinds * n_kinds;
+    size_t tab_doubles = 0;
+    for (size_t q = 0; q < cnt; ++q) {
+        const xtb_short_pair& a = p[q];
+        if (!(a.dd > 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: pair %zu has cut-off width dd=%g", q, a.dd);
+        if (a.n_pow < 0 || a.n_pow > XTB_SHORT_MAX_POW) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: pair %zu has %d power terms (max %d)", q, a.n_pow, XTB_SHORT_MAX_POW);
+        if (a.n_tab < 0 || a.n_tab == 1) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: pair %zu has a %d-point table", q, a.n_tab);
+        if (a.n_tab > 0) {
+            if (!a.tab_R || !a.tab_E) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: pair %zu: table without R / E", q);
+            if (a.tab_spline && (!a.tab_a || !a.tab_b || !a.tab_c || !a.tab_d)) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: pair %zu: spline without coefficients", q);
+            for (int k = 1; k < a.n_tab; ++k)
+                if (!(a.tab_R[k] > a.tab_R[k - 1])) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: pair %zu: table radii not increasing at point %d", q, k + 1);
+            tab_doubles += 6 * (size_t)a.n_tab;
+        }
+        if ((a.use_zbl || a.use_nlh) && !(Z[q % n_kinds] > 0.0 && Z[q / n_kinds] > 0.0)) XTB_FAIL(c, XTB_EINVAL, "xtb_set_params_short: pair %zu: ZBL / NLH need atomic numbers", q);
+    }
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_short_params, sizeof(ShortDev) * cnt))) return rc;
+    if ((rc = xtb_reserve(c, c->d_short_tab, sizeof(double) * (tab_doubles ? tab_doubles : 1)))) return rc;
+    std::vector<ShortDev> dev(cnt);
+    std::vector<double> tab(tab_doubles ? tab_doubles : 1, 0.0);
+    size_t off = 0;
+    for (size_t q = 0; q < cnt; ++q) {
+        const xtb_short_pair& a = p[q];
+        ShortDev& d = dev[q];
+        memset(&d, 0, sizeof d);
+        d.d0 = a.d0; d.dd = a.dd;
+        d.use_exp = a.use_exp != 0; d.use_inv_exp = a.use_inv_exp != 0; d.use_zbl = a.use_zbl != 0; d.use_nlh = a.use_nlh != 0;
+        d.exp_Phi = a.exp_Phi; d.exp_r0 = a.exp_r0; d.exp_a = a.exp_a; d.inv_C = a.inv_C; d.inv_r0 = a.inv_r0;
+        d.n_pow = a.n_pow; d.n_tab = a.n_tab; d.tab_spline = a.tab_spline != 0;
+        for (int k = 0; k < a.n_pow; ++k) { d.pow_Phi[k] = a.pow_Phi[k]; d.pow_r0[k] = a.pow_r0[k]; d.pow_m[k] = a.pow_m[k]; }
+        for (int k = 0; k < 3; ++k) { d.nlh_a[k] = a.nlh_a[k]; d.nlh_b[k] = a.nlh_b[k]; }
+        d.Z1 = Z[q % n_kinds]; d.Z2 = Z[q / n_kinds];                   // TB_Expwall(KOA1,KOA2) with Z1 = Z(KOA1), Z2 = Z(KOA2)
+        d.tab = (const double*)c->d_short_tab.p + off;
+        if (a.n_tab > 0) {
+            const double* src[6] = {a.tab_R, a.tab_E, a.tab_a, a.tab_b, a.tab_c, a.tab_d};
+            for (int w = 0; w < 6; ++w)
+                for (int k = 0; k < a.n_tab; ++k) tab[off + (size_t)w * a.n_tab + k] = (src[w] && (w < 2 || a.tab_spline)) ? src[w][k] : 0.0;
+            off += 6 * (size_t)a.n_tab;
+        }
+    }
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_short_params.p, dev.data(), sizeof(ShortDev) * cnt, cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaMemcpyAsync(c->d_short_tab.p, tab.data(), sizeof(double) * tab.size(), cudaMemcpyHostToDevice, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->h_short = dev;
+    c->h_wall.clear();                       // one class in the TB_Expwall slot
+    return XTB_OK;
+}
+
+static int short_ready(xtb_ctx* c, const char* who) {
+    if (c->h_short.empty()) XTB_FAIL(c, XTB_ESTATE, "%s: no short-range parameters (xtb_set_params_short)", who);
+    if (!c->have_neigh) XTB_FAIL(c, XTB_ESTATE, "%s: run xtb_neighbours first", who);
+    return XTB_OK;
+}
+
+int xtb_short_energy(xtb_ctx* c, double* E_short, double* Epot) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = short_ready(c, "xtb_short_energy"))) return rc;
+    if ((rc = xtb_impl_wall_energy(c))) return rc;
+    if (E_short) XTB_CUDA(c, cudaMemcpyAsync(E_short, c->d_Ewall.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (Epot) XTB_CUDA(c, cudaMemcpyAsync(Epot, c->d_Ewall_at.p, sizeof(double) * c->na, cudaMemcpyDeviceToHost, c->stream));
+    XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return XTB_OK;
+}
+
+int xtb_short_forces(xtb_ctx* c, double* F_short) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = short_ready(c, "xtb_short_forces"))) return rc;
+    if ((rc = xtb_impl_wall_forces(c))) return rc;
+    const size_t cnt = 3 * (size_t)(c->a1 - c->a0);
+    if (F_short && cnt) {
+        XTB_CUDA(c, cudaMemcpyAsync(F_short + 3 * (size_t)c->a0, (double*)c->d_Fwall.p + 3 * (size_t)c->a0, sizeof(double) * cnt, cudaMemcpyDeviceToHost, c->stream));
+        XTB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    return XTB_OK;
+}
+
+int xtb_short_pressure(xtb_ctx* c, double* SCforce_short) {
+    if (!c) return XTB_EINVAL;
+    cudaSetDevice(c->device);
+    int rc;
+    if ((rc = short_ready(c, "xtb_short_pressure"))) return rc;
+    if ((rc = xtb_impl_wall_pressure(c))) return rc;
+    if (SCforce_short) {
+        XTB_CUDA(c, cudaMemcpyAsync(SCforce_short, c->d_SCwall.p, sizeof(double) * 9, cudaMemcpyDeviceToHost, c->stream));
         XTB_CUDA(c, cudaStreamSynchronize(c->stream));
     }
     return XTB_OK;

@@ -17,6 +17,18 @@ struct DevBuf {
     size_t bytes = 0;
 };
 
+// device record of one (KOA1, KOA2) entry of class TB_Short_Rep (wall.cu); tab -> R | E | a | b | c | d, each [n_tab]
+struct ShortDev {
+    double d0, dd;
+    int use_exp, use_inv_exp, use_zbl, use_nlh;
+    double exp_Phi, exp_r0, exp_a, inv_C, inv_r0;
+    int n_pow, n_tab, tab_spline, pad_;
+    double pow_Phi[XTB_SHORT_MAX_POW], pow_r0[XTB_SHORT_MAX_POW], pow_m[XTB_SHORT_MAX_POW];
+    double nlh_a[3], nlh_b[3];
+    double Z1, Z2;              // atomic numbers of KOA1, KOA2
+    const double* tab;
+};
+
 struct xtb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -102,6 +114,8 @@ struct xtb_ctx {
     DevBuf d_Epot, d_dfpsi, d_Erep, d_Frep, d_SCrep;
     // short-range wall (wall.cu)
     std::vector<xtb_wall_pair> h_wall;     // empty: no wall set
+    std::vector<ShortDev> h_short;         // class TB_Short_Rep in the same slot (at most one of h_wall / h_short is non-empty)
+    DevBuf d_short_params, d_short_tab;
     DevBuf d_wall_params, d_Ewall_at, d_Ewall, d_Fwall, d_SCwall;
     // van der Waals term (vdw.cu)
     std::vector<xtb_vdw_pair> h_vdw;       // empty: no vdW term set
@@ -207,7 +221,8 @@ int xtb_impl_pettifor_rep_energy(xtb_ctx* c);      // pettifor_rep.cu
 int xtb_impl_pettifor_rep_forces(xtb_ctx* c);
 int xtb_impl_pettifor_rep_pressure(xtb_ctx* c);
 int xtb_impl_mirror_density(xtb_ctx* c);             // rows of the owned atoms when the context communicates, else all rows
-int xtb_impl_wall_energy(xtb_ctx* c);                // wall.cu
+static inline bool xtb_has_wall(const xtb_ctx* c) { return !c->h_wall.empty() || !c->h_short.empty(); }
+int xtb_impl_wall_energy(xtb_ctx* c);                // wall.cu (simple wall or the General class, whichever is set)
 int xtb_impl_wall_forces(xtb_ctx* c);
 int xtb_impl_wall_pressure(xtb_ctx* c);
 int xtb_impl_vdw_cells(xtb_ctx* c, int N[3], double* R_cut);   // vdw.cu: get_mirror_cell_num on the host

@@ -24,7 +24,7 @@ module XTANT_B200_shim
 use, intrinsic :: iso_c_binding
 use Objects, only : Super_cell, Numerics_param, solid, Error_handling, Save_error_details, &
                     TB_H_NRL, TB_H_Pettifor, TB_Rep_Pettifor, TB_H_DFTB, TB_Rep_DFTB, TB_Exp_wall_simple, &
-                    TB_vdW, TB_vdW_Girifalco, TB_vdW_LJ_cut, TB_vdW_ILJ_cut, TB_Coulomb, TB_Coulomb_cut
+                    TB_vdW, TB_vdW_Girifalco, TB_vdW_LJ_cut, TB_vdW_ILJ_cut, TB_Coulomb, TB_Coulomb_cut, TB_Short_Rep
 implicit none
 private
 public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_Aij, Construct_Aij_x_En, &
@@ -34,6 +34,7 @@ public :: get_near_neighbours, Construct_Vij_NRL, construct_TB_H_NRL, Construct_
           Electron_ion_coupling_Mij, xtb_b200_set_partition, xtb_b200_assemble_blocks, xtb_b200_expand_dense, &
           xtb_b200_density_mirror, xtb_b200_eigensolve, &
           get_Exp_wall_s, d_Exp_wall_pot_s, d_Exp_wall_Pressure_s, get_vdW_s, vdW_forces, get_mirror_cell_num, get_Coulomb_s, Coulomb_forces, &
+          get_short_range_rep_s, d_Short_range_pot_s, d_Short_range_Pressure_s, &
           xtb_b200_comm_init, xtb_b200_exchange_blocks, &
           xtb_b200_exchange_forces, xtb_b200_allreduce_scforce, xtb_b200_step, xtb_b200_fermi, xtb_b200_md_half_step, &
           xtb_b200_md_set_velocities, xtb_b200_md_get_state, xtb_b200_check_pending, xtb_b200_dense_density
@@ -69,6 +70,18 @@ type, bind(C) :: xtb_wall_pair              ! type(TB_Exp_wall_simple), Objects.
    real(c_double) :: C, r0, d0, dd
 end type xtb_wall_pair
 
+type, bind(C) :: xtb_short_pair             ! type(TB_Short_Rep), Objects.f90:437-454 (tables by address)
+   real(c_double) :: d0, dd
+   integer(c_int32_t) :: use_exp, use_inv_exp, use_zbl, use_nlh
+   real(c_double) :: exp_Phi, exp_r0, exp_a
+   real(c_double) :: inv_C, inv_r0
+   integer(c_int32_t) :: n_pow, n_tab
+   real(c_double) :: pow_Phi(8), pow_r0(8), pow_m(8)
+   real(c_double) :: nlh_a(3), nlh_b(3)
+   integer(c_int32_t) :: tab_spline, pad_
+   type(c_ptr) :: tab_R, tab_E, tab_a, tab_b, tab_c, tab_d
+end type xtb_short_pair
+
 type, bind(C) :: xtb_vdw_pair               ! class(TB_vdW) Objects.f90:43-46 + Girifalco :302-328 / LJ_cut :336-343 / ILJ_cut :346-354
    real(c_double) :: d0_cut, dd_cut
    real(c_double) :: C12, C6, dm, d_cut, a, b, c, d
@@ -92,6 +105,7 @@ type, bind(C) :: xtb_step_io                ! struct xtb_step_io (include/xtb_b2
 end type xtb_step_io
 
 type(c_ptr), save :: ctx = c_null_ptr      ! one context per process (single caller thread, TB.f90:227-272)
+logical, save :: short_pushed = .false.     ! the General short-range class was pushed (needs matter%Atoms%Z: done by its own wrappers)
 logical, save :: vdw_active = .false.       ! a usable class(TB_vdW) was pushed (push_params_vdw)
 logical, save :: eigen_current = .false.   ! Ha, Ei of this step already on the device (uploaded once, by construct_TB_H_*)
 logical, save :: density_current = .false. ! rho and rho_E of this step already contracted (ONE pass serves Construct_Aij and _x_En)
@@ -218,6 +232,18 @@ interface
    integer(c_int) function xtb_wall_pressure(c, P_wall) bind(C, name="xtb_wall_pressure")
       import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_wall(3,3)
    end function
+   integer(c_int) function xtb_set_params_short(c, n_kinds, p, Z) bind(C, name="xtb_set_params_short")
+      import; type(c_ptr), value :: c; integer(c_int), value :: n_kinds; type(c_ptr), value :: p; real(c_double), intent(in) :: Z(*)
+   end function
+   integer(c_int) function xtb_short_energy(c, E_short, Epot) bind(C, name="xtb_short_energy")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: E_short; real(c_double), intent(out) :: Epot(*)
+   end function
+   integer(c_int) function xtb_short_forces(c, F_short) bind(C, name="xtb_short_forces")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: F_short(3,*)
+   end function
+   integer(c_int) function xtb_short_pressure(c, P_short) bind(C, name="xtb_short_pressure")
+      import; type(c_ptr), value :: c; real(c_double), intent(out) :: P_short(3,3)
+   end function
    integer(c_int) function xtb_set_params_vdw(c, kind, n_kinds, p) bind(C, name="xtb_set_params_vdw")
       import; type(c_ptr), value :: c; integer(c_int), value :: kind, n_kinds; type(c_ptr), value :: p   ! c_null_ptr with n_kinds = 0: no vdW
    end function
@@ -333,6 +359,7 @@ subroutine xtb_b200_finalize()
       rc = xtb_destroy(ctx)
    endif
    ctx = c_null_ptr
+   short_pushed = .false.
 end subroutine xtb_b200_finalize
 
 ! errors raised inside wrappers whose reference signature has no Err argument (Construct_Aij_x_En, the force wrappers):
@@ -949,6 +976,104 @@ subroutine d_Exp_wall_Pressure_s(Scell, NSC, TB_Expwall, numpar)
       Scell(NSC)%SCforce%rep = Scell(NSC)%SCforce%rep + P                    ! :1381
    endif
 end subroutine d_Exp_wall_Pressure_s
+
+! ---- the 'General' short-range class in the slot of the wall (Exponential_wall.f90:48,519,664; dispatch TB.f90:3533-3556,3975-3993).
+!      Its parameters need the atomic numbers (matter%Atoms(:)%Z), which get_near_neighbours does not receive: the three wrappers,
+!      which do, push them on their first call.
+subroutine ensure_short(TB, matter)
+   type(TB_Short_Rep), dimension(:,:), intent(in), target :: TB
+   type(solid), intent(in) :: matter
+   type(xtb_short_pair), allocatable, target :: p(:)
+   real(c_double), allocatable :: Z(:)
+   integer :: nk, i, j, k, n
+   if (short_pushed) return
+   nk = size(TB,1)
+   allocate(p(nk*nk), Z(nk))
+   do i = 1, nk
+      Z(i) = matter%Atoms(i)%Z
+   enddo
+   do j = 1, nk
+      do i = 1, nk
+         k = i + nk*(j-1)
+         p(k)%d0 = TB(i,j)%f_cut%d0 ; p(k)%dd = TB(i,j)%f_cut%dd
+         p(k)%use_exp = merge(1, 0, TB(i,j)%f_exp%use_it) ; p(k)%use_inv_exp = merge(1, 0, TB(i,j)%f_inv_exp%use_it)
+         p(k)%use_zbl = merge(1, 0, TB(i,j)%f_ZBL%use_it) ; p(k)%use_nlh = merge(1, 0, TB(i,j)%f_NLH%use_it)
+         p(k)%exp_Phi = TB(i,j)%f_exp%Phi ; p(k)%exp_r0 = TB(i,j)%f_exp%r0 ; p(k)%exp_a = TB(i,j)%f_exp%a
+         p(k)%inv_C = TB(i,j)%f_inv_exp%C ; p(k)%inv_r0 = TB(i,j)%f_inv_exp%r0
+         p(k)%pow_Phi = 0.0d0 ; p(k)%pow_r0 = 1.0d0 ; p(k)%pow_m = 0.0d0 ; p(k)%n_pow = 0
+         if (allocated(TB(i,j)%f_pow)) then
+            n = size(TB(i,j)%f_pow)
+            if (n > 8) pending_error = 'TB_Short_Rep: more than 8 power terms (XTB_SHORT_MAX_POW); the extra ones are dropped'
+            p(k)%n_pow = min(n, 8)
+            p(k)%pow_Phi(1:p(k)%n_pow) = TB(i,j)%f_pow(1:p(k)%n_pow)%Phi
+            p(k)%pow_r0(1:p(k)%n_pow) = TB(i,j)%f_pow(1:p(k)%n_pow)%r0
+            p(k)%pow_m(1:p(k)%n_pow) = TB(i,j)%f_pow(1:p(k)%n_pow)%m
+         endif
+         p(k)%nlh_a = TB(i,j)%f_NLH%a ; p(k)%nlh_b = TB(i,j)%f_NLH%b
+         p(k)%n_tab = 0 ; p(k)%tab_spline = 0 ; p(k)%pad_ = 0
+         p(k)%tab_R = c_null_ptr ; p(k)%tab_E = c_null_ptr
+         p(k)%tab_a = c_null_ptr ; p(k)%tab_b = c_null_ptr ; p(k)%tab_c = c_null_ptr ; p(k)%tab_d = c_null_ptr
+         if (TB(i,j)%f_tab%use_it) then
+            p(k)%n_tab = size(TB(i,j)%f_tab%R)
+            p(k)%tab_spline = merge(1, 0, TB(i,j)%f_tab%use_spline)
+            p(k)%tab_R = c_loc(TB(i,j)%f_tab%R) ; p(k)%tab_E = c_loc(TB(i,j)%f_tab%E)
+            p(k)%tab_a = c_loc(TB(i,j)%f_tab%a) ; p(k)%tab_b = c_loc(TB(i,j)%f_tab%b)
+            p(k)%tab_c = c_loc(TB(i,j)%f_tab%c) ; p(k)%tab_d = c_loc(TB(i,j)%f_tab%d)
+         endif
+      enddo
+   enddo
+   call check(xtb_set_params_short(ctx, int(nk,c_int), c_loc(p), Z), 'xtb_set_params_short')
+   short_pushed = .true.
+end subroutine ensure_short
+
+subroutine get_short_range_rep_s(TB_Expwall, Scell, NSC, matter, numpar, a)
+   type(TB_Short_Rep), dimension(:,:), intent(in) :: TB_Expwall
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(solid), intent(in), target :: matter
+   type(Numerics_param), intent(inout) :: numpar
+   real(8), intent(out) :: a
+   real(c_double), allocatable :: Epot(:)
+   integer :: i, na
+   call ensure_short(TB_Expwall, matter)
+   na = size(Scell(NSC)%MDAtoms)
+   allocate(Epot(na))
+   call check(xtb_short_energy(ctx, a, Epot), 'xtb_short_energy')
+   do i = 1, na
+      Scell(NSC)%MDAtoms(i)%Epot = Scell(NSC)%MDAtoms(i)%Epot + Epot(i)      ! Exponential_wall.f90:120 (the half is inside)
+   enddo
+end subroutine get_short_range_rep_s
+
+subroutine d_Short_range_pot_s(Scell, NSC, matter, TB_Expwall, numpar)
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(solid), intent(in), target :: matter
+   type(TB_Short_Rep), dimension(:,:), intent(in) :: TB_Expwall
+   type(Numerics_param), intent(inout) :: numpar
+   real(c_double), allocatable :: F(:,:)
+   integer :: k, na
+   call ensure_short(TB_Expwall, matter)
+   na = size(Scell(NSC)%MDatoms)
+   allocate(F(3,na))
+   call check(xtb_short_forces(ctx, F), 'xtb_short_forces')
+   do k = 1, na
+      Scell(NSC)%MDatoms(k)%forces%rep(:) = Scell(NSC)%MDatoms(k)%forces%rep(:) + F(:,k)    ! :646
+   enddo
+end subroutine d_Short_range_pot_s
+
+subroutine d_Short_range_Pressure_s(Scell, NSC, TB_Expwall, matter, numpar)
+   type(Super_cell), dimension(:), intent(inout), target :: Scell
+   integer, intent(in) :: NSC
+   type(TB_Short_Rep), dimension(:,:), intent(in) :: TB_Expwall
+   type(solid), intent(in), target :: matter
+   type(Numerics_param), intent(in) :: numpar
+   real(c_double) :: P(3,3)
+   if (numpar%p_const) then        ! :677
+      call ensure_short(TB_Expwall, matter)
+      call check(xtb_short_pressure(ctx, P), 'xtb_short_pressure')
+      Scell(NSC)%SCforce%rep = Scell(NSC)%SCforce%rep + P                    ! :715
+   endif
+end subroutine d_Short_range_Pressure_s
 
 ! ---- van der Waals term (Van_der_Waals.f90:132,158; vdW_forces TB.f90:3599 -> Construct_B, d_Forces_s, d_Forces_Pressure) --------
 subroutine push_params_vdw(TB)

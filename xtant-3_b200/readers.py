@@ -9,6 +9,8 @@ numeric token(s) of a line, Fortran `d` exponents) and returns the dict the C-AB
     read_Pettifor_TB_repulsive      Read_input_data.f90:2908-3056  ->  xtb_pettifor_rep_pair
     read_Exponential_wall_TB        Read_input_data.f90:1920-2040,2313-2356 -> xtb_wall_pair (class line must read exactly
                                     'Simple_wall'; e.g. the shipped 'Simple_wall:exclude' disables the wall, as in the reference)
+    read_Short_Rep_TB               Read_input_data.f90:2021-2071,2110-2312 -> xtb_short_pair ('General' class of *_TB_short.txt / *_TB_wall.txt),
+                                    with make_cubic_splines (Algebra_tools.f90:115-190) and read_NLH_coefficients (ZBL_potential.f90:79-147)
     read_vdW_TB                     Read_input_data.f90:1660-1840 + read_vdW_Girifalco_TB :2392-2574, read_vdW_LJ_TB :2576-2652,
                                     read_vdW_ILJ_TB :2654-2716 -> (class, xtb_vdw_pair); the shipped 'Girifalco:exclude' disables it
     read_Coulomb_TB                 Read_input_data.f90:1846-1917 + read_Coulomb_cut_TB :2360-2386 -> xtb_coulomb_pair ('Coulomb_cut' only)
@@ -98,11 +100,9 @@ def read_Exponential_wall_TB(path):
     (any of the three spellings the reference accepts) -> dict(C, r0, d0, dd) read by read_Exponential_wall_TB (:2313-2356).
     Any other token -- including the 'Simple_wall:exclude' / 'Simple_wall:exclde' the reference ships in INPUT_DATA/Aluminum,
     /Silicon and /Diamond -- falls into `case default`: the reference prints "Unknown short-range ... class" and proceeds
-    WITHOUT the wall; this reader returns None in that case.  'General' (class TB_Short_Rep) is not built: NotImplementedError."""
+    WITHOUT the wall; this reader returns None in that case, and for the 'General' class (read_Short_Rep_TB reads that one)."""
     lines = _lines(path)
     cls = lines[0].replace(",", " ").split()[0]
-    if cls in ("General", "general", "GENERAL"):
-        raise NotImplementedError(f"{path}: class TB_Short_Rep ('General') is not part of this graft")
     if cls not in ("Simple_wall", "SIMPLE_WALL", "simple_wall"):
         return None
     v = [_num(lines[k].split()[0]) for k in range(1, 5)]
@@ -114,6 +114,125 @@ def write_Exponential_wall_TB(path, p, enabled=True):
         f.write("Simple_wall\n" if enabled else "Simple_wall:exclude\n")
         for k, c in (("C", "C [eV]"), ("r0", "r0 [A]"), ("d0", "d0 [A]"), ("dd", "dd [A]")):
             f.write(f"{_f(p[k])}\t\t! {c}\n")
+
+
+_SR_KEYS = {
+    "cut": ('CUTOFF', 'Cutoff', 'cutoff', 'CUT_OFF', 'Cut_off', 'cut_off', 'CUT-OFF', 'Cut-off', 'cut-off', 'FERMI', 'Fermi', 'fermi'),
+    "cut_inv": ('CUTOFF_SHORT', 'Cutoff_short', 'cutoff_short', 'CUT_OFF_SHORT', 'Cut_off_short', 'cut_off_short', 'CUT-OFF_short',
+                'Cut-off_short', 'cut-off_short', 'FERMI_INV', 'Fermi_inv', 'fermi_inv'),
+    "exp": ('EXP', 'Exp', 'exp', 'Exponential', 'exponential', 'EXPONENTIAL'),
+    "inv_exp": ('INVEXP', 'InvExp', 'invexp', 'Invexp', 'INV_EXP', 'Inv_Exp', 'Inv_exp', 'inv_exp'),
+    "pow": ('POWER', 'Power', 'power', 'POW', 'Pow', 'pow'),
+    "zbl": ('ZBL', 'zbl'),
+    "nlh": ('NLH', 'nlh'),
+    "tab": ('TAB', 'Tab', 'tab', 'TABLE', 'Table', 'table', 'TABULATED', 'Tabulated', 'tabulated'),
+}
+
+
+def make_cubic_splines(x, y):
+    """make_cubic_splines, Algebra_tools.f90:115-190 (one-sided first / second differences, not the natural spline) -> a, b, c, d"""
+    x = np.asarray(x, dtype=np.float64); y = np.asarray(y, dtype=np.float64)
+    n = len(x)
+    if n < 2:
+        raise ValueError("a table of fewer than two points cannot be splined")
+    h = np.empty(n); h[:-1] = x[1:] - x[:-1]; h[-1] = h[-2]
+    h_inv = 1.0 / h
+    fp = np.empty(n); fp2 = np.empty(n)
+    for i in range(1, n + 1):                        # 1-based, as get_first_derivative / get_second_derivative
+        j = 1 if i <= 1 else (n - 1 if i >= n else i)
+        fp[i - 1] = (y[j] - y[j - 1]) / (x[j] - x[j - 1])
+        j = 2 if i <= 2 else (n - 1 if i >= n - 1 else i)
+        if n >= 3:
+            xnn1 = x[j] - x[j - 1]; xn1n2 = x[j - 1] - x[j - 2]; xnn2 = x[j] - x[j - 2]
+            fp2[i - 1] = 2.0 * (y[j] * xn1n2 - y[j - 1] * xnn2 + y[j - 2] * xnn1) / (xnn2 * xn1n2 * xnn1)
+        else:
+            fp2[i - 1] = 0.0
+    a = y.copy(); b = np.zeros(n); c = np.zeros(n); d = np.zeros(n)
+    b[n - 1] = fp[n - 1]; b[n - 2] = fp[n - 2]
+    for i in range(n - 2, 0, -1):
+        b[i - 1] = fp[i] + 0.75 * fp2[i] * h[i - 1]
+    for i in range(n - 2, 0, -1):
+        c[i - 1] = h_inv[i - 1] * (fp[i] - b[i - 1] - 0.5 * h[i - 1] * fp2[i])
+    for i in range(n - 2, 0, -1):
+        d[i - 1] = (1.0 / 6.0) * h_inv[i - 1] * (fp2[i] - 2.0 * c[i - 1])
+    return a, b, c, d
+
+
+def read_NLH_coefficients(path, Z1, Z2):
+    """get_NLH_coefficients, ZBL_potential.f90:79-147: nlh_coeffs.dat holds the upper triangle Z1 <= Z2 (one comment line, then
+    `Z1 Z2 a1 b1 a2 b2 a3 b3 ...` for 92 x 92 elements).  As written, the lower triangle is filled with a(:) = a(j,i) AND
+    b(:) = a(j,i) (`NLH_data(i,j)%b(:) = NLH_data(j,i)%a(:)`, :133), so a pair asked for with Z1 > Z2 gets b = a; reproduced."""
+    Z1 = int(round(Z1)); Z2 = int(round(Z2))
+    lo, hi = min(Z1, Z2), max(Z1, Z2)
+    row = None
+    for line in _lines(path)[1:]:
+        t = line.split()
+        if len(t) >= 8 and int(t[0]) == lo and int(t[1]) == hi:
+            row = [_num(x) for x in t[2:8]]
+            break
+    if row is None:
+        raise ValueError(f"{path}: no NLH coefficients for Z = {lo}, {hi}")
+    a = (row[0], row[2], row[4]); b = (row[1], row[3], row[5])
+    return (a, b) if Z1 <= Z2 else (a, a)
+
+
+def read_Short_Rep_TB(path, Z=None, nlh_file=None):
+    """'General' class of <El>_<El>_TB_short.txt / _TB_wall.txt (class line 'General' | 'general' | 'GENERAL', Read_input_data.f90:2021;
+    anything else, e.g. the shipped 'General:exclude', -> None).  read_Short_Rep_TB (:2110-2146) then reads list-directed keyword
+    records until the end of the file (interpret_short_range_data :2149-2235): Cut-off `d0 dd`; Exp `Phi r0 a`; Inv_exp `C r0`;
+    Pow `n` + n lines `Phi r0 m`; ZBL; NLH (coefficients from nlh_file for Z = (Z1, Z2)); Tab `n [diff|spline]` + n lines `R E`
+    (Process_tabulated_potential :2238-2312; the splines are made in either case).  Unknown first tokens are skipped, as there.
+    Defaults: d0 = 0, dd = 0.01 (no repulsion).  Cut-off_short is read and, as in the reference, never used."""
+    lines = _lines(path)
+    if not lines or not lines[0].strip():
+        return None
+    if lines[0].replace(",", " ").split()[0] not in ("General", "general", "GENERAL"):
+        return None
+    p = {"d0": 0.0, "dd": 0.01, "exp": None, "inv_exp": None, "pow": [], "zbl": False, "nlh": False, "tab": None}
+    k = 1
+
+    def next_record(k):                 # list-directed read: blank records are skipped
+        while k < len(lines) and not lines[k].replace(",", " ").split():
+            k += 1
+        return k
+
+    while True:
+        k = next_record(k)
+        if k >= len(lines):
+            break
+        key = lines[k].replace(",", " ").split()[0]
+        k += 1
+        if key in _SR_KEYS["cut"]:
+            k = next_record(k); p["d0"], p["dd"] = _leading_numbers(lines[k], 2); k += 1
+        elif key in _SR_KEYS["cut_inv"]:
+            k = next_record(k); p["cut_inv"] = tuple(_leading_numbers(lines[k], 2)); k += 1
+        elif key in _SR_KEYS["exp"]:
+            k = next_record(k); p["exp"] = tuple(_leading_numbers(lines[k], 3)); k += 1
+        elif key in _SR_KEYS["inv_exp"]:
+            k = next_record(k); p["inv_exp"] = tuple(_leading_numbers(lines[k], 2)); k += 1
+        elif key in _SR_KEYS["pow"]:
+            k = next_record(k); n = int(_leading_numbers(lines[k], 1)[0]); k += 1
+            p["pow"] = []
+            for _ in range(n):
+                k = next_record(k); p["pow"].append(tuple(_leading_numbers(lines[k], 3))); k += 1
+        elif key in _SR_KEYS["zbl"]:
+            p["zbl"] = True
+        elif key in _SR_KEYS["nlh"]:
+            p["nlh"] = True
+        elif key in _SR_KEYS["tab"]:
+            t = lines[k].replace(",", " ").split(); k += 1          # formatted read: the very next line
+            n = int(_num(t[0]))
+            spline = len(t) > 1 and t[1] in ("spline", "SPLINE")
+            R, E = [], []
+            for _ in range(n):
+                k = next_record(k); r, e = _leading_numbers(lines[k], 2); R.append(r); E.append(e); k += 1
+            a, b, c, d = make_cubic_splines(R, E)
+            p["tab"] = {"R": np.array(R), "E": np.array(E), "spline": bool(spline), "a": a, "b": b, "c": c, "d": d}
+    if p["nlh"]:
+        if Z is None or nlh_file is None:
+            raise ValueError(f"{path}: the NLH term needs the atomic numbers of the pair and nlh_coeffs.dat")
+        p["nlh_a"], p["nlh_b"] = read_NLH_coefficients(nlh_file, Z[0], Z[1])
+    return p
 
 
 _GIRIFALCO_ORDER = ("C12", "C6", "dm", "d_cut", "a", "b", "c", "d", "dsm", "ds_cut", "as", "bs", "cs", "ds", "es", "fs")

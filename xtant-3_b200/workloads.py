@@ -71,6 +71,21 @@ def al500():       # config 3 (triclinic cell from the reference's SAVE files)
     return _from_cell("al500", "nrl", "Al", "cell_al500.json", 3, 1000.0 * K_B_EV)
 
 
+def load_short(setname):
+    """'General' short-range parameter set xtant-3_b200/data/params_short_<setname>.json (readers.read_Short_Rep_TB of the reference file)"""
+    import importlib
+    p = dict(_load(f"params_short_{setname}.json"))
+    p["exp"] = tuple(p["exp"]) if p.get("exp") else None
+    p["inv_exp"] = tuple(p["inv_exp"]) if p.get("inv_exp") else None
+    p["pow"] = [tuple(t) for t in p.get("pow", [])]
+    if p.get("tab"):
+        rd = importlib.import_module("xtant-3_b200.readers")
+        t = p["tab"]
+        a, b, c, d = rd.make_cubic_splines(t["R"], t["E"])
+        p["tab"] = {"R": np.array(t["R"]), "E": np.array(t["E"]), "spline": bool(t["spline"]), "a": a, "b": b, "c": c, "d": d}
+    return p
+
+
 def with_vdw(wl, setname):
     """attach Scell%TB_Waals from xtant-3_b200/data/params_vdw_<setname>.json (one kind of atom)"""
     p = dict(_load(f"params_vdw_{setname}.json"))
