@@ -278,9 +278,10 @@ def run_own(args):
                          "peak_source": "in-run torch.matmul fp64 8192^3 (cuBLAS DGEMM, burst); MEASURED_PEAKS.json has no FP64 entry",
                          "peak_pipe_dmma884": dmma_tf},
             "roofline_hbm_stage": None,      # filled below from the Fortran-layout variant (the only HBM-bound kernel left: re-tiling)
-            "dense_update": {"ms": stage[6], "bytes_touched": 2 * 2 * 8 * 81 * n_blocks,
-                             "note": "dense H_non, Sij (2 x 10.9 GB) stay resident in HBM; a step clears the blocks of the previous "
-                                     "neighbour pattern and writes the blocks of the new one (every element ends up exactly as after a full write)"},
+            "dense_update": {"ms": stage[6], "bytes_touched": 2 * 8 * 81 * n_blocks,
+                             "note": "dense H_non, Sij (2 x 10.9 GB) stay resident in HBM; a step writes the blocks of the new neighbour "
+                                     "pattern and clears only the blocks the pattern dropped (none here: same positions every step); "
+                                     "every element ends up exactly as after a full write.  bytes_touched = the block writes"},
         }
     # ---- informational variant (not the headline): occupation cut-off f_n <= 1e-30 in the rho / rho_E contraction.
     # Dropping those states changes rho by < 1e-30 * (C C^T)_ii, far below the FP64 rounding of the sum itself, but it is

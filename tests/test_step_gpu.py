@@ -101,6 +101,19 @@ def test_step_equals_staged_calls(name, wk, orc, api):
     out = c.step(flags, S=S2, want=("F_att", "SCforce_att"), graph=True)
     assert np.array_equal(out["F_att"], F3) and np.array_equal(out["SCforce_att"], P3)
     assert c.counter(16) == 2
+    # back to the wider cell: blocks DROP out of the pattern; the resident matrices must lose them (only those are cleared,
+    # the blocks that stay are overwritten by the scatter) -- in both forms of the clearing kernel
+    import os
+    for zero_all in ("0", "1"):
+        os.environ["XTB_DENSE_ZERO_ALL"] = zero_all
+        try:
+            out = c.step(flags, S=S2, supce=h3, want=("F_att",))
+            assert np.array_equal(out["F_att"], F3) and dense_equal(HS3)
+            out = c.step(flags, S=S2, supce=wl["supce"], want=("F_att", "SCforce_att"))
+            assert np.array_equal(out["F_att"], F2) and np.array_equal(out["SCforce_att"], P2)
+            assert c.counter(3) == n2 and dense_equal(HS2)
+        finally:
+            del os.environ["XTB_DENSE_ZERO_ALL"]
     c.close()
 
 

@@ -217,15 +217,45 @@ int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, do
 // bytes per block: 0.84 GB), so every element still has exactly the value a full write would give it.  A full clear happens
 // only when the buffers are new, were used as scratch (xtb_density_get), or the system changed shape.  XTB_DENSE_FULL=1
 // restores the full column-panel write of every step (dense_panel_kernel; the HBM-roofline measurement of bench.py).
+// nsize / nlist (stride ncap): the pattern the scatter that follows will write.  A block of the previous pattern that is also in the
+// new one is overwritten in full by that scatter, so it is not cleared here (in a steady MD run that is every block: the kernel
+// then only compares lists).  Membership is a binary search in the index-ordered list of the column atom; a miss on an unordered
+// list merely clears a block that is rewritten anyway.  nsize = nullptr: clear every block of the previous pattern.
 template <int NO>
 __global__ void __launch_bounds__(256) dense_zero_prev_kernel(int f0, int pcap, const int* __restrict__ psize, const int* __restrict__ plist,
-                                                             size_t N, double* __restrict__ A, double* __restrict__ B) {
+                                                             size_t N, double* __restrict__ A, double* __restrict__ B,
+                                                             int ncap, const int* __restrict__ nsize, const int* __restrict__ nlist) {
+    extern __shared__ unsigned char keep[];              // [pcap + 1]: 1 = the block stays (the scatter rewrites it)
     const int j = f0 + blockIdx.x;
     const int m = psize[j];
     if (m < 0) return;                                   // no previous content in this column panel
+    int any = 1;
+    if (nsize) {
+        const int mn = nsize[j];
+        const int* row = nlist + (size_t)j * ncap;
+        int cleared = 0;
+        for (int q = threadIdx.x; q <= m; q += 256) {
+            unsigned char k = 1;                         // q == 0: the on-site block, part of every pattern
+            if (q > 0) {
+                const int i = plist[(size_t)j * pcap + q - 1];
+                int lo = 0, hi = mn - 1;
+                k = 0;
+                while (lo <= hi) {
+                    const int mid = (lo + hi) >> 1, v = row[mid];
+                    if (v == i) { k = 1; break; }
+                    if (v < i) lo = mid + 1; else hi = mid - 1;
+                }
+            }
+            keep[q] = k;
+            cleared |= !k;
+        }
+        any = __syncthreads_or(cleared);
+    }
+    if (!any) return;
     const int tot = (m + 1) * NO * NO;
     for (int idx = threadIdx.x; idx < tot; idx += 256) {
         const int q = idx / (NO * NO), e = idx - q * (NO * NO);
+        if (nsize && keep[q]) continue;
         const int nu = e / NO, mu = e - nu * NO;
         const int i = q == 0 ? j : plist[(size_t)j * pcap + q - 1];
         const size_t d = ((size_t)i * NO + mu) + N * ((size_t)j * NO + nu);
@@ -292,7 +322,7 @@ int xtb_dense_update(xtb_ctx* c, int f0, int f1) {
     }
     if (c->dense_pcap != c->cap) {
         if (c->dense_pcap > 0) {      // the list stride changed: clear every panel with the old layout, then adopt the new one
-#define XTB_ZERO(NOV) dense_zero_prev_kernel<NOV><<<na, 256, 0, c->stream>>>(0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B)
+#define XTB_ZERO(NOV) dense_zero_prev_kernel<NOV><<<na, 256, 0, c->stream>>>(0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B, 0, nullptr, nullptr)
             if (NO == 9) XTB_ZERO(9); else if (NO == 4) XTB_ZERO(4); else XTB_ZERO(1);
             XTB_LAUNCH_CHECK(c);
             fill_int_kernel<<<(na + 255) / 256, 256, 0, c->stream>>>(na, -1, (int*)c->d_prev_size.p);
@@ -302,9 +332,14 @@ int xtb_dense_update(xtb_ctx* c, int f0, int f1) {
         c->dense_pcap = c->cap;
     }
     const int n = f1 - f0;
-    if (NO == 9) dense_zero_prev_kernel<9><<<n, 256, 0, c->stream>>>(f0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B);
-    else if (NO == 4) dense_zero_prev_kernel<4><<<n, 256, 0, c->stream>>>(f0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B);
-    else dense_zero_prev_kernel<1><<<n, 256, 0, c->stream>>>(f0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B);
+    // blocks of the previous pattern that the new pattern drops (XTB_DENSE_ZERO_ALL=1: every previous block, the earlier form)
+    const bool diff = !(getenv("XTB_DENSE_ZERO_ALL") && atoi(getenv("XTB_DENSE_ZERO_ALL")) != 0);
+    const int* nsz = diff ? (const int*)c->d_nn_size.p : nullptr;
+    const int* nls = diff ? (const int*)c->d_nn_list.p : nullptr;
+    const size_t zsm = (size_t)c->dense_pcap + 1;
+#define XTB_ZERO2(NOV) dense_zero_prev_kernel<NOV><<<n, 256, zsm, c->stream>>>(f0, c->dense_pcap, (const int*)c->d_prev_size.p, (const int*)c->d_prev_list.p, N, A, B, c->cap, nsz, nls)
+    if (NO == 9) XTB_ZERO2(9); else if (NO == 4) XTB_ZERO2(4); else XTB_ZERO2(1);
+#undef XTB_ZERO2
     XTB_LAUNCH_CHECK(c);
 #define XTB_SCATTER(NOV) dense_scatter_kernel<NOV><<<n, 256, 0, c->stream>>>(f0, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, \
         (const int*)c->d_rowptr.p, Ablk, Bblk, N, A, B, c->dense_pcap, (int*)c->d_prev_size.p, (int*)c->d_prev_list.p)
