@@ -277,8 +277,27 @@ def run_own(args):
                          "flops_per_launch": flops,
                          "peak_source": "in-run torch.matmul fp64 8192^3 (cuBLAS DGEMM, burst); MEASURED_PEAKS.json has no FP64 entry",
                          "peak_pipe_dmma884": dmma_tf},
-            "roofline_hbm_stage": None,      # filled below from the Fortran-layout variant (the only HBM-bound kernel left: re-tiling)
-            "dense_update": {"ms": stage[6], "bytes_touched": 2 * 8 * 81 * n_blocks,
+            # the two HBM-side stages of the step: algorithmic bytes / measured stage time
+            "roofline_hbm_stage": (lambda by, t: {
+                "bound": "hbm", "kernel": "force stage: nrl_onsite_w_kernel + nrl_force_pairs_kernel + nrl_force_sum_kernel",
+                "achieved": by / (t * 1e-3) * 1e-9 if t > 0 else None, "peak": hbm, "unit": "GB/s",
+                "frac": (by / (t * 1e-3) * 1e-9 / hbm) if t > 0 else None, "ms": t, "bytes": by,
+                "bytes_note": "2 * 8 * 81 per block (rho, rho_E read once) + 36 per directed pair (list entry + geometry) + 24 per atom out",
+                "fp64_floor_ms": 3.0 * 2 * 1500 * (n_pairs / 2) * own_frac / 32 / (148 * 4 / 2 * 1.965e9) * 1e3,
+                "fp64_note": "each unordered pair is differentiated once: 3 coordinates x 2 matrices x ~1500 FP64 instructions per thread "
+                             "(radial functions with 11 exp, 45 dual-number SK entries, contraction) at one FP64 warp instruction per 2 cycles "
+                             "per SM sub-partition -- the stage is bound by the FP64 pipe, not by HBM",
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)"})(
+                    (2 * 8 * 81 * n_blocks + 36 * n_pairs + 24 * na) * own_frac, stage[4]),
+            "roofline_hbm_assembly": (lambda by, t: {
+                "bound": "hbm", "kernel": "assembly stage: nrl_dens_kernel + dense_zero_prev_kernel + dense_remember_kernel + nrl_blocks_kernel "
+                                          "(block stores of H and S and the same values into the resident dense H_non, Sij)",
+                "achieved": by / (t * 1e-3) * 1e-9 if t > 0 else None, "peak": hbm, "unit": "GB/s",
+                "frac": (by / (t * 1e-3) * 1e-9 / hbm) if t > 0 else None, "ms": t, "bytes": by,
+                "bytes_note": "2 * 8 * 81 per block into the block stores + the same into the dense matrices (72-byte runs: partial "
+                              "sectors, read-modify-write in L2) + 36 per directed pair read"})(
+                    (2 * 2 * 8 * 81 * n_blocks + 36 * n_pairs) * own_frac, stage[2]),
+            "dense_update": {"ms": stage[6], "ms_is": "preparation only (list comparison + pattern record): the values are written by nrl_blocks_kernel in the same pass as the block stores (XTB_DENSE_FUSED=0: separate scatter kernel)", "bytes_touched": 2 * 8 * 81 * n_blocks,
                              "note": "dense H_non, Sij (2 x 10.9 GB) stay resident in HBM; a step writes the blocks of the new neighbour "
                                      "pattern and clears only the blocks the pattern dropped (none here: same positions every step); "
                                      "every element ends up exactly as after a full write.  bytes_touched = the block writes"},
@@ -306,7 +325,7 @@ def run_own(args):
             "density_ms": t3, "density_kernel_ms": t7, "retile_kernel_ms": t16, "ms_per_step_estimate": ms - stage[3] + t3,
             "note": "xtb_set_eigen_device with Ha(N,N) column-major: ct_tile_kernel writes the tiled copy (10.9 GB in, 10.8 GB out) "
                     "before the contraction; same rho / rho_E bits (tests/test_density_tm_gpu.py)"}
-        out["roofline_hbm_stage"] = {
+        out["variant_fortran_layout_eigenvectors"]["roofline_hbm"] = {
             "bound": "hbm", "kernel": "ct_tile_kernel (Fortran-layout variant only: eigenvector columns re-tiled into TMA / DMMA-fragment order)",
             "achieved": retile_bytes / (t16 * 1e-3) * 1e-9 if t16 > 0 else None, "peak": hbm, "unit": "GB/s",
             "frac": (retile_bytes / (t16 * 1e-3) * 1e-9 / hbm) if t16 > 0 else None, "ms": t16,

@@ -128,6 +128,66 @@ def test_split_tail_round_gives_the_same_blocks(wk, api, monkeypatch):
         assert np.array_equal(r, res[0][0]) and np.array_equal(e, res[0][1])
 
 
+def test_pair_once_forces_are_bit_identical_to_the_every_entry_form(wk, api, monkeypatch):
+    """nrl_force_pairs_kernel differentiates every unordered pair once and hands the partner the negated value;
+    XTB_FORCES_MODE=0 evaluates every list entry from its own atom (the earlier single-kernel form).  Every operation on the
+    path is odd in (delta_ik - delta_jk), so the two give the same bits -- on the whole cell and on an owned range with
+    partners on both sides outside it (those pairs are evaluated by the owned atom; the context of the range is handed the
+    complete rho / rho_E stores of the whole-cell context, as the halo exchange of a partitioned run would)."""
+    import importlib
+    abi = importlib.import_module("xtant-3_b200._abi"); interop = importlib.import_module("xtant-3_b200.interop")
+    wl = wk.au108()
+    C_, E, fe = wk.synthetic_eigen(wl["na"] * 9, seed=11)
+    full = api.TBContext(0); full.set_workload(wl); full.get_near_neighbours_device(); full.assemble_blocks()
+    full.set_eigen(C_, E, fe); full.density()
+    res, prs = [], []
+    for mode in ("0", "1"):
+        monkeypatch.setenv("XTB_FORCES_MODE", mode)
+        res.append(full.forces().copy())
+        prs.append(full.pressure().copy())
+    assert np.abs(res[0]).max() > 1e-3 and np.abs(prs[0]).max() > 1e-3
+    assert np.array_equal(res[0], res[1]), np.abs(res[0] - res[1]).max()
+    assert np.array_equal(prs[0], prs[1]), np.abs(prs[0] - prs[1]).max()      # supercell force: the same pair-once rule
+    first, last = 31, 77
+    part = api.TBContext(0); part.set_workload(wl); part.get_near_neighbours_device(); part.set_partition(first, last)
+    part.assemble_blocks(); part.set_eigen(C_, E, fe); part.density()
+    for which in (abi.BUF_RHO, abi.BUF_RHOE):
+        src = interop.buffer(full, which); dst = interop.buffer(part, which)
+        n = min(src.numel(), dst.numel())
+        dst[:n].copy_(src[:n])
+    import torch
+    torch.cuda.synchronize()
+    for mode in ("0", "1"):
+        monkeypatch.setenv("XTB_FORCES_MODE", mode)
+        F = part.forces()
+        assert np.array_equal(F[first - 1:last], res[0][first - 1:last]), (mode, np.abs(F[first - 1:last] - res[0][first - 1:last]).max())
+        prs.append(part.pressure().copy())
+    assert np.array_equal(prs[2], prs[3]) and np.abs(prs[2]).max() > 1e-3       # owned range: partial sums of the two forms
+    part.close(); full.close()
+
+
+def test_pair_once_blocks_of_an_owned_range_equal_the_full_cell(wk, api):
+    """nrl_blocks_kernel evaluates an unordered pair once and writes both transposed blocks when both atoms are owned; with an
+    owned range the pairs that reach outside it are evaluated by the owned atom: same H / S block rows either way."""
+    import importlib
+    abi = importlib.import_module("xtant-3_b200._abi"); interop = importlib.import_module("xtant-3_b200.interop")
+    import torch
+    wl = wk.au108()
+    c = api.TBContext(0); c.set_workload(wl); c.get_near_neighbours_device(); c.assemble_blocks()
+    rp = interop.buffer(c, abi.BUF_ROWPTR, torch.int32).cpu().numpy().copy()
+    Hb = interop.buffer(c, abi.BUF_HBLK).cpu().numpy().copy(); Sb = interop.buffer(c, abi.BUF_SBLK).cpu().numpy().copy()
+    c.close()
+    assert np.abs(Hb).max() > 0
+    first, last = 31, 77
+    c = api.TBContext(0); c.set_workload(wl); c.get_near_neighbours_device(); c.set_partition(first, last); c.assemble_blocks()
+    rp2 = interop.buffer(c, abi.BUF_ROWPTR, torch.int32).cpu().numpy().copy()
+    Hp = interop.buffer(c, abi.BUF_HBLK).cpu().numpy().copy(); Sp = interop.buffer(c, abi.BUF_SBLK).cpu().numpy().copy()
+    c.close()
+    assert np.array_equal(rp, rp2)
+    lo, hi = rp[first - 1] * 81, rp[last] * 81
+    assert np.array_equal(Hb.ravel()[lo:hi], Hp.ravel()[lo:hi]) and np.array_equal(Sb.ravel()[lo:hi], Sp.ravel()[lo:hi])
+
+
 @pytest.mark.parametrize("name", ["c_3x3x3", "au_5x5x6", "si216"])
 def test_single_image_neighbour_path_is_bit_identical_to_the_27_image_scan(wk, api, monkeypatch, name):
     """orthorhombic cells with every edge > 2 rm take the one-image path (neighbours.cu, min_image_ortho); XTB_NN_SCAN27=1

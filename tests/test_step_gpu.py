@@ -104,8 +104,10 @@ def test_step_equals_staged_calls(name, wk, orc, api):
     # back to the wider cell: blocks DROP out of the pattern; the resident matrices must lose them (only those are cleared,
     # the blocks that stay are overwritten by the scatter) -- in both forms of the clearing kernel
     import os
-    for zero_all in ("0", "1"):
+    # -- and with the dense values written by the block kernel itself (default) or by the separate scatter kernel
+    for zero_all, fused in (("0", "1"), ("1", "1"), ("0", "0"), ("1", "0"), ("0", "1")):
         os.environ["XTB_DENSE_ZERO_ALL"] = zero_all
+        os.environ["XTB_DENSE_FUSED"] = fused
         try:
             out = c.step(flags, S=S2, supce=h3, want=("F_att",))
             assert np.array_equal(out["F_att"], F3) and dense_equal(HS3)
@@ -114,6 +116,7 @@ def test_step_equals_staged_calls(name, wk, orc, api):
             assert c.counter(3) == n2 and dense_equal(HS2)
         finally:
             del os.environ["XTB_DENSE_ZERO_ALL"]
+            del os.environ["XTB_DENSE_FUSED"]
     c.close()
 
 

@@ -110,6 +110,7 @@ struct xtb_ctx {
     bool have_density = false;
     // forces / pressure
     DevBuf d_F, d_SC, d_scratch, d_hdev, d_ppart, d_tab;
+    DevBuf d_fpair;             // NRL forces: per list entry the pair term (H - S, three coordinates) and the on-site term (nrl_forces.cu)
     // repulsive pair terms (pettifor_rep.cu)
     DevBuf d_Epot, d_dfpsi, d_Erep, d_Frep, d_SCrep;
     // short-range wall (wall.cu)
@@ -251,5 +252,5 @@ int xtb_impl_dftb_pressure(xtb_ctx* c);
 int xtb_impl_dftb_tables(xtb_ctx* c, double* d_rad, double* d_geo);  // compact tables, nv channels per list entry
 int xtb_impl_nrl_tables(xtb_ctx* c, double* d_rad, double* d_geo);   // compact M_V*/M_lmn/M_xrr/M_x1 per list entry
 // dense column panels of the owned atoms from a block store; tr: block holds (rows j, cols neighbour)
-int xtb_dense_update(xtb_ctx* c, int f0, int f1);      // resident dense H_non / Sij: clear the previous pattern, write the new one
+int xtb_dense_update(xtb_ctx* c, int f0, int f1, bool scatter = true);      // resident dense H_non / Sij: clear the previous pattern, write the new one (scatter = false: the caller's kernel writes it)
 int xtb_dense_from_blocks(xtb_ctx* c, const double* Ablk, const double* Bblk, double* A, double* B, bool tr, int f0 = -1, int f1 = -1);
