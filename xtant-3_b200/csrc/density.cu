@@ -234,7 +234,10 @@ constexpr int SLOT = 9 * KC + 4;       // 148 (KC = 16) / 292 (KC = 32): both = 
 constexpr int SLOT_TM = 9 * KC;        // 144 doubles = 9 rows of 128 bytes (KC = 16)
 __host__ __device__ constexpr int stage_doubles_tm(int slotcap) { return (slotcap * SLOT_TM + (KC / 4) * 72 + 2 * KC + 127) / 128 * 128; }
 constexpr int BROW = 72;
-constexpr int NPROD = 3;                // producer warps (bulk-copy issue is serialised per lane within a warp); 8 + 1 + 3 = 12 warps = 3 per SM sub-partition -> 168 registers per thread
+#ifndef XTB_NPROD
+#define XTB_NPROD 3
+#endif
+constexpr int NPROD = XTB_NPROD;                // producer warps (bulk-copy issue is serialised per lane within a warp); 8 + 1 + 3 = 12 warps = 3 per SM sub-partition -> 168 registers per thread
 
 // ---- lock-step between CTAs ----
 // The CTAs of one round work on spatially adjacent atoms, so at the same chunk index they read largely the same tiles of
@@ -347,6 +350,9 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
                 Frag<MT>& cu = (s & 1) ? f1 : f0;
                 Frag<MT>& nx = (s & 1) ? f0 : f1;
                 if (s + 1 < KS) {
+#ifdef XTB_EXP_HALF_LDS      // timing experiment (wrong results): odd k-steps reuse the A fragments of the even ones -- half the A loads
+                    if ((s + 1) & 1) { const double k0 = nx.b0, k1 = nx.b1; nx = cu; nx.b0 = k0 + cu.b1; nx.b1 = k1 + cu.b0; } else
+#endif
                     load_frag<NO, MT, TM, NCW>(nx, stg, stg + boff, off, s + 1, lane, t, ks);
                     // probe the barriers of the next stage one k-step early: the answer is in a register long before it is needed
                     if (s + 2 == KS && ch + 1 < nchunks) ready = mbar_test(&full[rn.st], rn.ph) & mbar_test(&bready[rn.st], rn.ph);
@@ -430,6 +436,14 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
     __shared__ int n_owned_sh;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // helper warps: with 8 consumer warps the row tiles of a sub-task fall 12 / 11 / 11 / 11 (45 tiles) or 12 / 12 / 12 / 11 (47) on
+    // the four sub-partitions, warp w on sub-partition w & 3.  XTB_BWARP_LAST puts the B warp -- the only helper that uses the
+    // FP64 pipe -- last (warp 11, sub-partition 3, the one that is never the fullest) and the producers first
+#ifdef XTB_BWARP_LAST
+    constexpr int P0 = NCW, BW = NCW + NPROD;
+#else
+    constexpr int P0 = NCW + 1, BW = NCW;
+#endif
 
     if (threadIdx.x == 0) {
         for (uint32_t s = 0; s < stages; ++s) { mbar_init(&full[s], NPROD); mbar_init(&bfull[s], 1); mbar_init(&bready[s], 1); mbar_init(&empty[s], NCW); }
@@ -478,9 +492,9 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
             const int nrows = nslots * NO;
             const int ntiles = (nrows + 7) >> 3;
 
-            if (warp > NCW) {
+            if (warp >= P0 && warp < P0 + NPROD) {
                 // ===== producer warps: stream the tiles of all slots for every chunk; slot s belongs to producer s % NPROD =====
-                const int pw = warp - NCW - 1;
+                const int pw = warp - P0;
                 const int ncopy = (DBG && (dbg & 2)) ? (nslots + 3) / 4 : nslots;     // debug: quarter of the data
                 // slot 0 and the weights go to their own barrier (bfull) so the B warp overlaps with the other copies
                 const int others = ncopy - 1;                                   // slots 1 .. ncopy-1
@@ -528,7 +542,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
                     csrc += (size_t)na * TILE; w1 += KC; w2 += KC;
                     rg.next(stages);
                 }
-            } else if (warp == NCW) {
+            } else if (warp == BW) {
                 // ===== B warp: weighted B operand of atom i, once per chunk =====
                 const int g = lane >> 2, t = lane & 3;
                 for (int ch = 0; ch < nchunks; ++ch) {
@@ -568,7 +582,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
         }
     }
     // this CTA is done: it no longer holds anyone back
-    if (warp == NCW + 1 && lane == 0) st_relaxed(prog + blockIdx.x, XTB_PROG_DONE);
+    if (warp == P0 && lane == 0) st_relaxed(prog + blockIdx.x, XTB_PROG_DONE);
 }
 
 #include "density_pair.cuh"
