@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(32 * FS_WARPS) nrl_force_sum_kernel(int a0, in
 // (always, except when two periodic images tie and the scans of i and j keep different ones): the block derivative picks up
 // (-1)^(l_a + l_b) from (l, m, n) -> -(l, m, n), the mirrored rho block is the transpose, dr/dh = r_delta s_gamma / r is even.
 // PAIR_ONCE: such a pair is evaluated by its owner of the density pass (force_theirs) and its nine (H - S) values are kept per
-// list entry (fp: [na * cap][18] = pair values, on-site values); nrl_pressure_sum_kernel then adds the entries of every atom
+// list entry (fp: [na * cap][19] = pair values, on-site values, index of the entry that holds the pair values); nrl_pressure_sum_kernel then adds the entries of every atom
 // in list order, taking the partner's values for the skipped ones -- the same bits as evaluating every directed pair
 // (XTB_FORCES_MODE=0: !PAIR_ONCE, everything in one kernel).
 __device__ __forceinline__ bool pressure_theirs(signed char own_e, int j, int rv, size_t e, int cap, int a0, int a1,
@@ -300,6 +300,7 @@ __device__ __forceinline__ bool pressure_theirs(signed char own_e, int j, int rv
     return anti;
 }
 
+constexpr int PF = 19;      // doubles per list entry in the pressure scratch: 9 pair values, 9 on-site values, source entry
 template <bool PAIR_ONCE>
 __global__ void __launch_bounds__(FT) nrl_pressure_kernel(int na, int a0, int a1, int cap, int mx, int n_kinds, const int* __restrict__ koa,
                                                          const int* __restrict__ nn_size, const int* __restrict__ nn_list,
@@ -325,7 +326,9 @@ __global__ void __launch_bounds__(FT) nrl_pressure_kernel(int na, int a0, int a1
                 bool f = false;
                 if (q < m) {
                     const size_t e = (size_t)i * cap + q;
-                    f = !pressure_theirs(own[e], nn_list[e], rev[e], e, cap, a0, a1, nn_dist, nn_dist_s);
+                    const int j = nn_list[e], rv = rev[e];
+                    f = !pressure_theirs(own[e], j, rv, e, cap, a0, a1, nn_dist, nn_dist_s);
+                    fp[e * PF + 18] = (double)(f ? e : (size_t)j * cap + rv);      // the entry that holds the pair values (exact: < 2^53)
                 }
                 const unsigned mask = __ballot_sync(0xffffffffu, f);
                 if (f) actq[cnt + __popc(mask & ((1u << threadIdx.x) - 1u))] = q;
@@ -397,11 +400,11 @@ __global__ void __launch_bounds__(FT) nrl_pressure_kernel(int na, int a0, int a1
     if (PAIR_ONCE) {
         for (int w = threadIdx.x; w < m * 9; w += FT) {
             const int q = w / 9, k1 = w - q * 9;
-            fp[((size_t)i * cap + q) * 18 + 9 + k1] = ons[q * 9 + k1];
+            fp[((size_t)i * cap + q) * PF + 9 + k1] = ons[q * 9 + k1];
         }
         for (int w = threadIdx.x; w < nact * 9; w += FT) {
             const int qi = w / 9, k1 = w - qi * 9;
-            fp[((size_t)i * cap + actq[qi]) * 18 + k1] = part[qi * 18 + k1] - part[qi * 18 + 9 + k1];
+            fp[((size_t)i * cap + actq[qi]) * PF + k1] = part[qi * 18 + k1] - part[qi * 18 + 9 + k1];
         }
     } else if (threadIdx.x < 9) {
         const int k1 = threadIdx.x;
@@ -426,11 +429,8 @@ __global__ void __launch_bounds__(32 * FS_WARPS) nrl_pressure_sum_kernel(int a0,
     for (int w = lane; w < m * 9; w += 32) {
         const int q = w / 9, k1 = w - q * 9;
         const size_t e = (size_t)i * cap + q;
-        const int j = nn_list[e];
-        const int rv = rev[e];
-        const bool theirs = pressure_theirs(own[e], j, rv, e, cap, a0, a1, nn_dist, nn_dist_s);
-        const double d = theirs ? fp[((size_t)j * cap + rv) * 18 + k1] : fp[e * 18 + k1];
-        t[w] = d + fp[e * 18 + 9 + k1];
+        const size_t se = (size_t)fp[e * PF + 18];      // own entry or the partner's (recorded by nrl_pressure_kernel)
+        t[w] = fp[se * PF + k1] + fp[e * PF + 9 + k1];
     }
     __syncwarp();
     if (lane < 9) {
@@ -516,7 +516,7 @@ int xtb_impl_nrl_pressure(xtb_ctx* c) {
     if ((rc = xtb_reserve(c, c->d_ppart, sizeof(double) * 9 * (size_t)(nown > 0 ? nown : 1)))) return rc;
     const char* ev = getenv("XTB_FORCES_MODE");              // 0: every directed pair evaluated by its atom (cross-check of the default)
     const int mode = ev ? atoi(ev) : 1;
-    if (mode != 0 && (rc = xtb_reserve(c, c->d_fpair, sizeof(double) * 18 * (size_t)c->na * c->cap))) return rc;
+    if (mode != 0 && (rc = xtb_reserve(c, c->d_fpair, sizeof(double) * PF * (size_t)c->na * c->cap))) return rc;
     XTB_T0(c, 5);
     if ((rc = launch_onsite_w(c))) return rc;
     if (nown > 0) {
