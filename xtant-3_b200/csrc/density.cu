@@ -36,6 +36,12 @@ namespace {
 #define XTB_KC 16
 #endif
 constexpr int KC = XTB_KC;             // states per chunk
+// K-split of the first row tile of the on-site block over the four sub-partitions (see density_dmma_kernel); experiment, off by default
+#ifdef XTB_KSPLIT
+constexpr bool KSPLIT = true;
+#else
+constexpr bool KSPLIT = false;
+#endif
 constexpr int KS = KC / 4;             // DMMA k-steps per chunk
 constexpr int CT_AT = 512 / KC;        // atoms per CTA of the re-tiling kernel (static shared memory budget)
 
@@ -307,7 +313,8 @@ template <int NO, int NCW, int MT, bool DBG, bool TM = false>
 __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_doubles, int boff, uint32_t stages,
                                                 uint64_t* full, uint64_t* bready, uint64_t* empty, Ring& rg, int nchunks,
                                                 int nrows, int warp, int lane, const int* slot_q, size_t b0i,
-                                                bool first_subtask, int dbg, double* __restrict__ rho, double* __restrict__ rhoE) {
+                                                bool first_subtask, int dbg, double* __restrict__ rho, double* __restrict__ rhoE,
+                                                bool ksp = false, double* spart = nullptr) {
     // (TM: the four rows of a half warp carry the swizzle keys 0..3, whose sixteen-byte pieces pair up on four positions of the
     // 128-byte line, so a fragment load takes four wavefronts instead of two -- ncu: 3.6e9 bank-conflict wavefronts per launch.
     // Giving the half warps the rows 0,2,4,6 / 1,3,5,7 removes them and was measured SLOWER, 69.7 against 69.1 ms: shared
@@ -319,7 +326,7 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
     for (int mt = 0; mt < MT; ++mt) {
         acc0[mt][0] = acc0[mt][1] = acc1[mt][0] = acc1[mt][1] = 0.0;
         p8f[mt] = p8e[mt] = 0.0;
-        const int R = 8 * (warp + NCW * mt) + g;
+        const int R = 8 * (warp + (KSPLIT && ksp ? 1 : 0) + NCW * mt) + g;      // ksp: row tile 0 is the special tile, the regular ones follow
         const int sl = R / NO, r = R - sl * NO;
         off[mt] = (R < nrows) ? sl * SLOT + 4 * r + t : t;      // rows beyond the task read row 0 (results dropped)
         if (!TM) asm volatile("" : "+r"(off[mt]));             // keep it in a register (no per-chunk re-derivation)
@@ -327,9 +334,13 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
     int ks[KS];                                                // TM: row (8 warp + g) of tile 0 + swizzled position of (k-step s, t); R & 7 = g
 #pragma unroll
     for (int s = 0; s < KS; ++s) {
-        ks[s] = (8 * warp + g) * 16 + 2 * ((2 * s + (t >> 1)) ^ g) + (t & 1);
+        ks[s] = (8 * (warp + (KSPLIT && ksp ? 1 : 0)) + g) * 16 + 2 * ((2 * s + (t >> 1)) ^ g) + (t & 1);
         if (TM) asm volatile("" : "+r"(ks[s]));
     }
+    // K-split special tile (rows 0..7 of the on-site block): warps 4..7 = one per sub-partition, each takes every fourth chunk
+    const bool doS = KSPLIT && ksp && warp >= 4 && warp < 8;
+    const int ks_sub = 128 * (warp + 1);               // TM: ks[s] - ks_sub = address of row g of tile 0
+    double sA0[2] = {0.0, 0.0}, sA1[2] = {0.0, 0.0}, s8f = 0.0, s8e = 0.0;
     if (nchunks > 0) {
         const double* stg = sbuf + (size_t)rg.st * stage_doubles;
 #ifdef XTB_EXP_STAGGER
@@ -372,6 +383,17 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
                     }
                 }
             }
+            if (KSPLIT && doS && ((ch & 3) == (warp & 3))) {
+                const double* Bs = stg + boff;
+#pragma unroll
+                for (int s = 0; s < KS; ++s) {
+                    const double a = TM ? stg[ks[s] - ks_sub] : stg[4 * g + t + NO * 4 * s];
+                    dmma884(sA0[0], sA0[1], a, Bs[s * BROW + lane]);
+                    dmma884(sA1[0], sA1[1], a, Bs[s * BROW + 32 + lane]);
+                    s8f = fma(a, Bs[s * BROW + 64 + t], s8f);
+                    s8e = fma(a, Bs[s * BROW + 68 + t], s8e);
+                }
+            }
             // every shared-memory read of this stage has been issued (in order, ahead of the arrive)
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[rg.st]);
@@ -386,7 +408,7 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
         double f8 = p8f[mt], e8 = p8e[mt];
         f8 += __shfl_xor_sync(0xffffffffu, f8, 1); e8 += __shfl_xor_sync(0xffffffffu, e8, 1);
         f8 += __shfl_xor_sync(0xffffffffu, f8, 2); e8 += __shfl_xor_sync(0xffffffffu, e8, 2);
-        const int R = 8 * (warp + NCW * mt) + g;
+        const int R = 8 * (warp + (KSPLIT && ksp ? 1 : 0) + NCW * mt) + g;
         if (R < nrows) {
             const int sl = R / NO, nu = R - sl * NO;
             if (sl > 0 || first_subtask) {     // the on-site block belongs to the first sub-task only
@@ -397,6 +419,15 @@ __device__ __forceinline__ void consume_subtask(const double* sbuf, int stage_do
                 if (t == 1) rhoE[blk + 8] = e8;
             }
         }
+    }
+    if (KSPLIT && doS) {      // partial sums of the special tile: spart[warp - 4][matrix][row g][col 0..8]; summed by warp 0 after the CTA barrier
+        s8f += __shfl_xor_sync(0xffffffffu, s8f, 1); s8e += __shfl_xor_sync(0xffffffffu, s8e, 1);
+        s8f += __shfl_xor_sync(0xffffffffu, s8f, 2); s8e += __shfl_xor_sync(0xffffffffu, s8e, 2);
+        double* pr = spart + (size_t)(warp - 4) * 144 + 9 * g;
+        pr[2 * t] = sA0[0]; pr[2 * t + 1] = sA0[1];
+        pr[72 + 2 * t] = sA1[0]; pr[72 + 2 * t + 1] = sA1[1];
+        if (t == 0) pr[8] = s8f;
+        if (t == 1) pr[72 + 8] = s8e;
     }
 }
 
@@ -433,6 +464,8 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
     int* slot_q = reinterpret_cast<int*>(empty + stages);     // [slotcap] list ordinal of slot s (s >= 1)
     int* slot_atom = slot_q + slotcap;                        // [slotcap] atom of slot s (slot 0 = i)
     int* owned_q = slot_atom + slotcap;                       // [cap] ordinals of all owned neighbours of i
+    // KSPLIT: partial sums of the special tile, [4 warps][2 matrices][8 rows][9 columns], 8-byte aligned behind the integer tables
+    double* spart = reinterpret_cast<double*>((reinterpret_cast<uintptr_t>(owned_q + cap) + 7) & ~(uintptr_t)7);
     __shared__ int n_owned_sh;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -478,6 +511,12 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
         const int lo = part * per, n_owned = min(n_all, lo + per);      // this unit: owned neighbours lo .. n_owned-1
         if (part > 0 && lo >= n_owned) continue;                        // the on-site block belongs to part 0 (uniform per CTA)
         const size_t b0i = (size_t)rowptr[i];
+        // KSPLIT rule of atom i (a function of the atom alone, so that the summation order of its blocks does not depend on the
+        // work unit they are computed in): all owned neighbours fit one sub-task and the row tiles of the whole atom are
+        // 4 m + 1 -- then the first tile (rows 0..7 of the on-site block) is summed in four interleaved quarters of the chunks,
+        // one per sub-partition, and the other 4 m tiles fall m per sub-partition.
+        const int t_full = (NO * (n_all + 1) + 7) >> 3;
+        const bool ksp_atom = KSPLIT && n_all + 1 <= slotcap && (t_full & 3) == 1 && t_full >= 13;
         // ---- sub-tasks of at most slotcap-1 neighbours (slot 0 is always atom i itself) ----
         int sub = 0;
         for (int first = lo; first == lo || first < n_owned; first += slotcap - 1, ++sub) {
@@ -491,6 +530,7 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
             __syncthreads();
             const int nrows = nslots * NO;
             const int ntiles = (nrows + 7) >> 3;
+            const bool ksp = KSPLIT && ksp_atom && first == 0;      // this sub-task holds the on-site block of a K-split atom
 
             if (warp >= P0 && warp < P0 + NPROD) {
                 // ===== producer warps: stream the tiles of all slots for every chunk; slot s belongs to producer s % NPROD =====
@@ -570,14 +610,26 @@ density_dmma_kernel(int na, int a0, int a1, int cap, int slotcap, int stages_, i
                 }
             } else {
                 // ===== consumer warps: row tiles warp, warp + NCW, ... of this sub-task =====
-                const int my_tiles = ntiles > warp ? (ntiles - warp + NCW - 1) / NCW : 0;
+                const int nreg = ntiles - (ksp ? 1 : 0);      // regular row tiles (ksp: all but the first)
+                int my_tiles = nreg > warp ? (nreg - warp + NCW - 1) / NCW : 0;
+                if (ksp && warp >= 4 && warp < 8 && my_tiles == 0) my_tiles = 1;      // the special tile needs the loop (the regular tile is past the rows: dropped)
                 const bool fs = first == 0;
                 const int boff = slotcap * SLOTW;
                 constexpr int MTMAX = NCW == 8 ? 7 : 5;      // row tiles per warp (register budget)
-#define XTB_CASE(M) if constexpr (M <= MTMAX) { if (my_tiles == M) consume_subtask<NO, NCW, M, DBG, TM>(sbuf, stage_doubles, boff, stages, full, bready, empty, rg, nchunks, nrows, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE); }
+#define XTB_CASE(M) if constexpr (M <= MTMAX) { if (my_tiles == M) consume_subtask<NO, NCW, M, DBG, TM>(sbuf, stage_doubles, boff, stages, full, bready, empty, rg, nchunks, nrows, warp, lane, slot_q, b0i, fs, dbg, rho, rhoE, ksp, spart); }
                 if (my_tiles == 0) consume_idle(stages, full, bready, empty, rg, nchunks, lane);
                 XTB_CASE(1) XTB_CASE(2) XTB_CASE(3) XTB_CASE(4) XTB_CASE(5) XTB_CASE(6) XTB_CASE(7)
 #undef XTB_CASE
+            }
+            if (KSPLIT && ksp) {      // (uniform per CTA) on-site rows 0..7: the four quarter sums in a fixed order
+                __syncthreads();
+                if (warp == 0) {
+                    for (int x = lane; x < 144; x += 32) {
+                        const double v = (spart[x] + spart[144 + x]) + (spart[288 + x] + spart[432 + x]);
+                        const int mat = x / 72, y = x - mat * 72;          // y = 9 * row + col = NO * nu + mu
+                        (mat == 0 ? rho : rhoE)[b0i * (NO * NO) + y] = v;
+                    }
+                }
             }
         }
     }
@@ -923,7 +975,7 @@ int run_density(xtb_ctx* c) {
         if (slotcap > c->max_nn + 1) slotcap = c->max_nn + 1;
         if (slotcap < 2) slotcap = 2;
         auto stage_bytes = [&](int sc) { return use_tm ? (size_t)stage_doubles_tm(sc) * 8 : (size_t)(sc * SLOT + KS * BROW + 2 * KC) * 8; };
-        auto fixed_bytes = [&](int sc, int st) { return (size_t)4 * 8 * st + sizeof(int) * (2 * (size_t)sc + c->cap) + 64 + (use_tm ? 1024 : 0); };
+        auto fixed_bytes = [&](int sc, int st) { return (size_t)4 * 8 * st + sizeof(int) * (2 * (size_t)sc + c->cap) + 64 + (use_tm ? 1024 : 0) + (KSPLIT ? 4608 + 8 : 0); };
         const size_t budget = 227 * 1024 - 1024;
         int stages = 4;
         while (stages > 2 && stages * stage_bytes(slotcap) + fixed_bytes(slotcap, stages) > budget) {
