@@ -466,7 +466,9 @@ long long xtb_counter(const xtb_ctx*, int which);
  * 14 H/S block exchange, 15 rho block exchange (xtb_counter 12 / 13: bytes received per rank by each),
  * 0 the last graph replay of xtb_step as a whole (xtb_counter 16: graphs captured so far),
  * 16 the eigenvector re-tiling kernel alone (inside 3), 17 van der Waals term, 18 Coulomb term (energy / forces / supercell force of one call).  Stage 6 is the dense H_non / Sij update: the matrices stay resident and
- * only the blocks of the previous and of the new pattern are touched (XTB_DENSE_FULL=1: every element, every step) */
+ * only the blocks of the previous and of the new pattern are touched (XTB_DENSE_FULL=1: every element, every step).  In the NRL
+ * branch on one rank the values are written by the block kernel of stage 2 in the same pass as the block stores, and stage 6 is
+ * the preparation alone (dropped blocks cleared, new pattern recorded); XTB_DENSE_FUSED=0: separate scatter kernel, inside 6 */
 double xtb_stage_ms(const xtb_ctx*, int stage);
 
 #ifdef __cplusplus
