@@ -253,13 +253,13 @@ __global__ void __launch_bounds__(FT, 2) nrl_force_pairs_kernel(int a0, int a1, 
 
 // fixed-order sum over the list of atom k; one warp per atom stages the terms, three lanes add them in list order
 constexpr int FS_WARPS = 4;
-__global__ void __launch_bounds__(32 * FS_WARPS) nrl_force_sum_kernel(int a0, int a1, int cap, int mx, const int* __restrict__ nn_size,
+__global__ void __launch_bounds__(32 * FS_WARPS) nrl_force_sum_kernel(int a0, int a1, int cap, int mx, int wpc, const int* __restrict__ nn_size,
                                                                      const int* __restrict__ nn_list, const int* __restrict__ rev,
                                                                      const signed char* __restrict__ own,
                                                                      const double* __restrict__ fpair, double* __restrict__ F) {
-    extern __shared__ double sms[];                 // [FS_WARPS][mx][3]
+    extern __shared__ double sms[];                 // [wpc][mx][3]  (wpc = warps per CTA, <= FS_WARPS: fewer when mx is large)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int k = a0 + blockIdx.x * FS_WARPS + warp;
+    const int k = a0 + blockIdx.x * wpc + warp;
     if (k >= a1) return;
     double* t = sms + (size_t)warp * mx * 3;
     const int m = nn_size[k];
@@ -415,14 +415,14 @@ __global__ void __launch_bounds__(FT) nrl_pressure_kernel(int na, int a0, int a1
 }
 
 // fixed-order sum over the list of atom i (one warp per atom stages the terms, nine lanes add them in list order)
-__global__ void __launch_bounds__(32 * FS_WARPS) nrl_pressure_sum_kernel(int a0, int a1, int cap, int mx, const int* __restrict__ nn_size,
+__global__ void __launch_bounds__(32 * FS_WARPS) nrl_pressure_sum_kernel(int a0, int a1, int cap, int mx, int wpc, const int* __restrict__ nn_size,
                                                                         const int* __restrict__ nn_list, const int* __restrict__ rev,
                                                                         const signed char* __restrict__ own,
                                                                         const double* __restrict__ nn_dist, const double* __restrict__ nn_dist_s,
                                                                         const double* __restrict__ fp, double* __restrict__ partial) {
-    extern __shared__ double sms[];                 // [FS_WARPS][mx][9]
+    extern __shared__ double sms[];                 // [wpc][mx][9]
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int i = a0 + blockIdx.x * FS_WARPS + warp;
+    const int i = a0 + blockIdx.x * wpc + warp;
     if (i >= a1) return;
     double* t = sms + (size_t)warp * mx * 9;
     const int m = nn_size[i];
@@ -497,9 +497,11 @@ int xtb_impl_nrl_forces(xtb_ctx* c) {
                                                                   (const double*)c->d_hdev.p, (const double*)c->d_onsite_w.p,
                                                                   (const double*)c->d_rho.p, (const double*)c->d_rhoE.p, (double*)c->d_fpair.p);
             XTB_LAUNCH_CHECK(c);
-            const size_t smem2 = sizeof(double) * ((size_t)mx * 3 * FS_WARPS);
+            int wpc = FS_WARPS;                                     // warps (atoms) per CTA: as many as the staged terms leave room for
+            while (wpc > 1 && sizeof(double) * (size_t)mx * 3 * wpc > 160 * 1024) wpc >>= 1;
+            const size_t smem2 = sizeof(double) * ((size_t)mx * 3 * wpc);
             XTB_CUDA(c, cudaFuncSetAttribute(nrl_force_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-            nrl_force_sum_kernel<<<(nown + FS_WARPS - 1) / FS_WARPS, 32 * FS_WARPS, smem2, c->stream>>>(c->a0, c->a1, c->cap, mx, nsz, nls, rv,
+            nrl_force_sum_kernel<<<(nown + wpc - 1) / wpc, 32 * wpc, smem2, c->stream>>>(c->a0, c->a1, c->cap, mx, wpc, nsz, nls, rv,
                                                                                                     (const signed char*)c->d_own.p, (const double*)c->d_fpair.p, (double*)c->d_F.p);
             XTB_LAUNCH_CHECK(c);
         }
@@ -532,10 +534,12 @@ int xtb_impl_nrl_pressure(xtb_ctx* c) {
                                             (const double*)c->d_rhoE.p, (double*)c->d_ppart.p, (double*)c->d_fpair.p);
         XTB_LAUNCH_CHECK(c);
         if (mode != 0) {
-            const size_t smem2 = sizeof(double) * ((size_t)mx * 9 * FS_WARPS);
+            int wpc = FS_WARPS;
+            while (wpc > 1 && sizeof(double) * (size_t)mx * 9 * wpc > 160 * 1024) wpc >>= 1;
+            const size_t smem2 = sizeof(double) * ((size_t)mx * 9 * wpc);
             XTB_CUDA(c, cudaFuncSetAttribute(nrl_pressure_sum_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-            nrl_pressure_sum_kernel<<<(nown + FS_WARPS - 1) / FS_WARPS, 32 * FS_WARPS, smem2, c->stream>>>(
-                c->a0, c->a1, c->cap, mx, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, (const int*)c->d_rev.p,
+            nrl_pressure_sum_kernel<<<(nown + wpc - 1) / wpc, 32 * wpc, smem2, c->stream>>>(
+                c->a0, c->a1, c->cap, mx, wpc, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, (const int*)c->d_rev.p,
                 (const signed char*)c->d_own.p, (const double*)c->d_nn_dist.p, (const double*)c->d_nn_dist_s.p, (const double*)c->d_fpair.p, (double*)c->d_ppart.p);
             XTB_LAUNCH_CHECK(c);
         }
