@@ -26,6 +26,14 @@ typedef int (*fn_syevd_buf_t)(handle_t, int /*jobz*/, int /*uplo*/, int n, const
 typedef int (*fn_syevd_t)(handle_t, int, int, int n, double* A, int lda, double* W, double* work, int lwork, int* info);
 typedef int (*fn_dgemm_t)(handle_t, int ta, int tb, int m, int n, int k, const double* alpha, const double* A, int lda,
                           const double* B, int ldb, const double* beta, double* Cm, int ldc);
+// 64-bit interface (cusolverDnXsyevd): workspace sizes in bytes as size_t.  The legacy Dsyevd counts its workspace in an int,
+// which the ~2 N^2 doubles of the eigenvector job overflow from N ~ 32 000 on -- below the north-star N = 36 864.
+typedef int (*fn_params_create_t)(void**);
+typedef int (*fn_params_destroy_t)(void*);
+typedef int (*fn_xsyevd_buf_t)(handle_t, void* params, int jobz, int uplo, int64_t n, int typeA, const void* A, int64_t lda, int typeW,
+                               const void* W, int compute, size_t* dev_bytes, size_t* host_bytes);
+typedef int (*fn_xsyevd_t)(handle_t, void* params, int jobz, int uplo, int64_t n, int typeA, void* A, int64_t lda, int typeW, void* W,
+                           int compute, void* dev_buf, size_t dev_bytes, void* host_buf, size_t host_bytes, int* info);
 
 struct Libs {
     bool tried = false, ok = false;
@@ -34,6 +42,8 @@ struct Libs {
     fn_create_t sv_create = nullptr; fn_destroy_t sv_destroy = nullptr; fn_setstream_t sv_stream = nullptr;
     fn_syevd_buf_t sv_buf = nullptr; fn_syevd_t sv_syevd = nullptr;
     fn_create_t bl_create = nullptr; fn_destroy_t bl_destroy = nullptr; fn_setstream_t bl_stream = nullptr; fn_dgemm_t bl_dgemm = nullptr;
+    fn_params_create_t x_create = nullptr; fn_params_destroy_t x_destroy = nullptr; fn_xsyevd_buf_t x_buf = nullptr; fn_xsyevd_t x_syevd = nullptr;
+    bool x_ok = false;      // the 64-bit interface is present (optional: older libraries only carry the legacy one)
 };
 Libs g_libs;            // the two libraries and their entry points (process-wide); the HANDLES live in the context
 
@@ -65,6 +75,11 @@ bool bind_libs() {
     BIND(bl_stream, so_blas, fn_setstream_t, "cublasSetStream_v2")
     BIND(bl_dgemm, so_blas, fn_dgemm_t, "cublasDgemm_v2")
 #undef BIND
+    L.x_create = (fn_params_create_t)dlsym(L.so_solver, "cusolverDnCreateParams");
+    L.x_destroy = (fn_params_destroy_t)dlsym(L.so_solver, "cusolverDnDestroyParams");
+    L.x_buf = (fn_xsyevd_buf_t)dlsym(L.so_solver, "cusolverDnXsyevd_bufferSize");
+    L.x_syevd = (fn_xsyevd_t)dlsym(L.so_solver, "cusolverDnXsyevd");
+    L.x_ok = L.x_create && L.x_destroy && L.x_buf && L.x_syevd;
     L.ok = true;
     return true;
 }
@@ -122,8 +137,41 @@ __global__ void chop_kernel(long long n, double* __restrict__ A, double eps) {
         if (fabs(A[i]) < eps) A[i] = 0.0;
 }
 
+// legacy interface up to LEGACY_MAX_N (its int workspace count still holds there), the 64-bit one beyond; XTB_EIGEN_X64=1 forces
+// the 64-bit interface at any size (tests)
+constexpr int LEGACY_MAX_N = 30000;
+int syevd_x64(xtb_ctx* c, int n, double* A, double* W, const std::string& what) {
+    Libs& L = g_libs;
+    constexpr int R_64F = 1;      // CUDA_R_64F
+    void* params = nullptr;
+    if (L.x_create(&params) != 0 || !params) XTB_FAIL(c, XTB_ECUDA, "cusolverDnCreateParams failed (%s)", what.c_str());
+    size_t dev_bytes = 0, host_bytes = 0;
+    const int stb = L.x_buf(c->h_cusolver, params, JOB_VECTOR, FILL_UPPER, (int64_t)n, R_64F, A, (int64_t)n, R_64F, W, R_64F, &dev_bytes, &host_bytes);
+    if (stb != 0) {
+        L.x_destroy(params);
+        XTB_FAIL(c, XTB_ECUDA, "cusolverDnXsyevd_bufferSize failed (%s): status %d at n = %d", what.c_str(), stb, n);
+    }
+    const size_t info_off = (dev_bytes + 15) & ~(size_t)15;
+    int rc;
+    if ((rc = xtb_reserve(c, c->d_eig_work, info_off + 16))) { L.x_destroy(params); return rc; }
+    std::vector<char> host_buf(host_bytes ? host_bytes : 1);
+    int* d_info = (int*)((char*)c->d_eig_work.p + info_off);
+    const int st = L.x_syevd(c->h_cusolver, params, JOB_VECTOR, FILL_UPPER, (int64_t)n, R_64F, A, (int64_t)n, R_64F, W, R_64F,
+                             c->d_eig_work.p, dev_bytes, host_buf.data(), host_bytes, d_info);
+    int info = 0;
+    cudaError_t e = cudaMemcpyAsync(&info, d_info, sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);      // also keeps host_buf alive until the solver is done with it
+    L.x_destroy(params);
+    if (st != 0) XTB_FAIL(c, XTB_ECUDA, "cusolverDnXsyevd failed to launch (%s): status %d", what.c_str(), st);
+    if (e != cudaSuccess) { cudaGetLastError(); XTB_FAIL(c, XTB_ECUDA, "cusolverDnXsyevd (%s): %s", what.c_str(), cudaGetErrorString(e)); }
+    if (info != 0) XTB_FAIL(c, XTB_ECUDA, "Xsyevd(%s): info = %d", what.c_str(), info);
+    return XTB_OK;
+}
+
 int syevd(xtb_ctx* c, int n, double* A, double* W, std::string what) {
     Libs& L = g_libs;
+    const char* ev = getenv("XTB_EIGEN_X64");
+    if (L.x_ok && (n > LEGACY_MAX_N || (ev && atoi(ev) != 0))) return syevd_x64(c, n, A, W, what);
     int lwork = 0;
     if (L.sv_buf(c->h_cusolver, JOB_VECTOR, FILL_UPPER, n, A, n, W, &lwork) != 0) XTB_FAIL(c, XTB_ECUDA, "cusolverDnDsyevd_bufferSize failed (%s)", what.c_str());
     int rc;
@@ -178,7 +226,9 @@ int xtb_impl_eigensolve(xtb_ctx* c) {
     if (!bind_libs()) XTB_FAIL(c, XTB_ESTATE, "xtb_eigensolve: %s", g_libs.why.c_str());
     Libs& L = g_libs;
     const long long N = (long long)c->na * c->n_orb;
-    if (N > 46000) XTB_FAIL(c, XTB_EINVAL, "xtb_eigensolve: N = %lld exceeds the 32-bit element count of cusolverDnDsyevd", N);
+    if (N > LEGACY_MAX_N && !L.x_ok)
+        XTB_FAIL(c, XTB_EINVAL, "xtb_eigensolve: N = %lld needs the 64-bit cusolverDnXsyevd, which this cuSOLVER library does not export", N);
+    if (N > 46000) XTB_FAIL(c, XTB_EINVAL, "xtb_eigensolve: N = %lld: N * N exceeds the 32-bit element counts of the GEMM glue", N);
     const int n = (int)N;
     const size_t nn = (size_t)N * N;
     const bool ortho = c->tb == XTB_TB_PETTIFOR;
