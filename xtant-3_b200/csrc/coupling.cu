@@ -88,6 +88,132 @@ __global__ void __launch_bounds__(ST) spmm_blocks_kernel(int na, long long N, lo
     }
 }
 
+// ---- tiled form of T = S Ha (9 orbitals, rows-by-state eigenvectors) -------------------------------------------------------------
+// spmm_blocks_kernel fetches the 72 bytes of (neighbour atom, state) once per column atom j, i.e. ~79 times: 2.25 flop per byte
+// from L2, which bounds it at 11 TF.  Here a CTA owns TJ = 4 consecutive atoms (spatial neighbours in any sensible numbering: their
+// lists overlap) and walks the UNION of their lists once: a fetched row vector feeds every tile atom that has the union atom as a
+// neighbour (2.6 of 4 on the fcc metal).  Measured: no faster than the kernel above (see xtb_impl_coupling); kept as an opt-in variant.
+//   tile_union_kernel   one warp per tile: the merged, index-ordered union of {j} U NN(j) of its atoms, and for every union atom
+//                       the block of S it forms with each tile atom (or -1)
+//   spmm_tile_kernel    CTA = (tile, 256 states), thread = 2 states, 2 x 4 x 9 accumulators; the <= 4 blocks of a union atom are
+//                       staged in shared memory (double buffer, rows padded to 10 doubles: 128-bit broadcast loads)
+constexpr int TJ = 4;
+__global__ void __launch_bounds__(32) tile_union_kernel(int na, int cap, int umax, const int* __restrict__ nn_size, const int* __restrict__ nn_list,
+                                                       const int* __restrict__ rowptr, int* __restrict__ ucount, int* __restrict__ uat,
+                                                       int* __restrict__ ublk /*[tile][umax][TJ]*/) {
+    const int tile = blockIdx.x, j0 = tile * TJ;
+    if (threadIdx.x != 0) return;      // a serial 4-way merge of short sorted lists (once per call and tile: ~1 k tiles)
+    int pos[TJ], len[TJ];
+    bool self_done[TJ];
+    for (int t = 0; t < TJ; ++t) { pos[t] = 0; len[t] = (j0 + t < na) ? nn_size[j0 + t] : 0; self_done[t] = !(j0 + t < na); }
+    int* ua = uat + (size_t)tile * umax;
+    int* ub = ublk + (size_t)tile * umax * TJ;
+    int n = 0;
+    for (;;) {
+        // smallest pending atom index over the four sequences (list of j with j itself inserted in order)
+        int best = 0x7fffffff;
+        for (int t = 0; t < TJ; ++t) {
+            const int j = j0 + t;
+            if (j >= na) continue;
+            int head = pos[t] < len[t] ? nn_list[(size_t)j * cap + pos[t]] : 0x7fffffff;
+            if (!self_done[t] && j < head) head = j;
+            if (head < best) best = head;
+        }
+        if (best == 0x7fffffff) break;
+        ua[n] = best;
+        for (int t = 0; t < TJ; ++t) {
+            const int j = j0 + t;
+            int b = -1;
+            if (j < na) {
+                if (!self_done[t] && j == best) { b = rowptr[j]; self_done[t] = true; }
+                else if (pos[t] < len[t] && nn_list[(size_t)j * cap + pos[t]] == best) { b = rowptr[j] + 1 + pos[t]; ++pos[t]; }
+            }
+            ub[n * TJ + t] = b;
+        }
+        ++n;
+    }
+    ucount[tile] = n;
+}
+
+constexpr int TS = 128;               // threads per CTA, two states each
+__global__ void __launch_bounds__(TS, 2) spmm_tile_kernel(int na, long long N, long long K, int umax, const int* __restrict__ ucount,
+                                                         const int* __restrict__ uat, const int* __restrict__ ublk,
+                                                         const double* __restrict__ Sblk, const double* __restrict__ X,
+                                                         double* __restrict__ T) {
+    constexpr int NO = 9, LDR = 10, BLK = NO * LDR;            // staged block: [nu][10]
+    extern __shared__ __align__(16) double sm[];
+    double* sS = sm;                                           // [2][TJ][BLK]
+    int* sU = reinterpret_cast<int*>(sS + 2 * TJ * BLK);       // [umax] union atoms, then [umax][TJ] block indices
+    const int tile = blockIdx.x, j0 = tile * TJ;
+    const int nu_ = ucount[tile];
+    int* sB = sU + umax;
+    for (int e = threadIdx.x; e < nu_; e += TS) sU[e] = uat[(size_t)tile * umax + e];
+    for (int e = threadIdx.x; e < nu_ * TJ; e += TS) sB[e] = ublk[(size_t)tile * umax * TJ + e];
+    __syncthreads();
+    const long long n0 = (long long)blockIdx.y * (2 * TS) + threadIdx.x, n1 = n0 + TS;
+    const bool ok0 = n0 < K, ok1 = n1 < K;
+    const long long m0 = ok0 ? n0 : 0, m1 = ok1 ? n1 : m0;      // out-of-range threads read a valid row (results dropped) and keep the barriers
+    double a0[TJ][NO], a1[TJ][NO];
+#pragma unroll
+    for (int t = 0; t < TJ; ++t)
+#pragma unroll
+        for (int v = 0; v < NO; ++v) { a0[t][v] = 0.0; a1[t][v] = 0.0; }
+    // stage the blocks of union atom `it` into buffer `buf`: element (mu, nu) of block t -> sS[buf][t][nu * 10 + mu]
+    auto stage = [&](int it, int buf) {
+        for (int e = threadIdx.x; e < TJ * NO * NO; e += TS) {
+            const int t = e / (NO * NO), r = e - t * (NO * NO);
+            const int b = sB[it * TJ + t];
+            if (b >= 0) { const int v = r / NO, mu = r - v * NO; sS[(buf * TJ + t) * BLK + v * LDR + mu] = __ldg(Sblk + (size_t)b * (NO * NO) + r); }
+        }
+    };
+    if (nu_ > 0) stage(0, 0);
+    __syncthreads();
+    for (int it = 0; it < nu_; ++it) {
+        const int buf = it & 1;
+        const int u = sU[it];
+        const double* c0 = X + ((size_t)u * K + m0) * NO;
+        const double* c1 = X + ((size_t)u * K + m1) * NO;
+        double x0[NO], x1[NO];
+#pragma unroll
+        for (int mu = 0; mu < NO; ++mu) { x0[mu] = __ldg(c0 + mu); x1[mu] = __ldg(c1 + mu); }
+        if (it + 1 < nu_) stage(it + 1, buf ^ 1);
+#pragma unroll
+        for (int t = 0; t < TJ; ++t) {
+            if (sB[it * TJ + t] < 0) continue;                   // uniform over the CTA
+            const double* b = sS + (buf * TJ + t) * BLK;
+#pragma unroll
+            for (int v = 0; v < NO; ++v) {
+                const double2 s01 = *reinterpret_cast<const double2*>(b + v * LDR), s23 = *reinterpret_cast<const double2*>(b + v * LDR + 2);
+                const double2 s45 = *reinterpret_cast<const double2*>(b + v * LDR + 4), s67 = *reinterpret_cast<const double2*>(b + v * LDR + 6);
+                const double s8 = b[v * LDR + 8];
+                double p = a0[t][v], q = a1[t][v];
+                p = fma(s01.x, x0[0], p); q = fma(s01.x, x1[0], q);
+                p = fma(s01.y, x0[1], p); q = fma(s01.y, x1[1], q);
+                p = fma(s23.x, x0[2], p); q = fma(s23.x, x1[2], q);
+                p = fma(s23.y, x0[3], p); q = fma(s23.y, x1[3], q);
+                p = fma(s45.x, x0[4], p); q = fma(s45.x, x1[4], q);
+                p = fma(s45.y, x0[5], p); q = fma(s45.y, x1[5], q);
+                p = fma(s67.x, x0[6], p); q = fma(s67.x, x1[6], q);
+                p = fma(s67.y, x0[7], p); q = fma(s67.y, x1[7], q);
+                p = fma(s8, x0[8], p);    q = fma(s8, x1[8], q);
+                a0[t][v] = p; a1[t][v] = q;
+            }
+        }
+        __syncthreads();                                          // buffer buf^1 is complete, buffer buf may be overwritten next
+    }
+#pragma unroll
+    for (int t = 0; t < TJ; ++t) {
+        const int j = j0 + t;
+        if (j >= na) continue;
+        if (ok0) { double* t0 = T + (size_t)j * NO + (size_t)N * n0;
+#pragma unroll
+            for (int v = 0; v < NO; ++v) t0[v] = a0[t][v]; }
+        if (ok1) { double* t1 = T + (size_t)j * NO + (size_t)N * n1;
+#pragma unroll
+            for (int v = 0; v < NO; ++v) t1[v] = a1[t][v]; }
+    }
+}
+
 // in place on G (N x N, column-major): tile pair (a, b), a <= b, 32 x 32 tiles through shared memory.
 //   g(i,j) = G(i,j) inv0[i] inv1[j];  Tully: M(i,j) = M(j,i) = (g(i,j) - g(j,i))/2 for i < j;  kind -1: M(i,j) = M(j,i) = g(i,j);  M(i,i) = 0
 __global__ void __launch_bounds__(256) antisym_kernel(long long N, int kind, const double* __restrict__ inv0,
@@ -156,12 +282,31 @@ int xtb_impl_coupling(xtb_ctx* c, int kind_M) {
             if ((rc = xtb_rows_by_state(c, c->d_Ha, K, (double*)c->d_Ct.p))) return rc;
             Cm = (const double*)c->d_Ct.p;
         }
+        const char* evt = getenv("XTB_COUPLING_TILE");
+        // XTB_COUPLING_TILE=1: four column atoms per CTA on the union of their lists (spmm_tile_kernel).  Parity-green and NOT
+        // faster at au4096 (172.8 vs 169.5 ms for norms + S Ha, profiles/r02as_coupling_tiled_ab.json), so one column atom per CTA
+        // (spmm_blocks_kernel) stays the default: the stage is not bound by the L2 fetches the tiling removes.
+        const bool tiled = xt && c->n_orb == 9 && evt && atoi(evt) == 1;
+        if (tiled) {
+            const int ntile = (c->na + TJ - 1) / TJ, umax = TJ * (c->max_nn + 1);
+            if ((rc = xtb_reserve(c, c->d_cpl_union, sizeof(int) * ((size_t)ntile * (1 + (size_t)umax * (1 + TJ)))))) return rc;
+            int* ucount = (int*)c->d_cpl_union.p; int* uat = ucount + ntile; int* ublk = uat + (size_t)ntile * umax;
+            tile_union_kernel<<<ntile, 32, 0, c->stream>>>(c->na, c->cap, umax, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p,
+                                                           (const int*)c->d_rowptr.p, ucount, uat, ublk);
+            XTB_LAUNCH_CHECK(c);
+            const size_t smt = sizeof(double) * 2 * TJ * 90 + sizeof(int) * (size_t)umax * (1 + TJ);
+            XTB_CUDA(c, cudaFuncSetAttribute(spmm_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smt));
+            spmm_tile_kernel<<<dim3((unsigned)ntile, (unsigned)((K + 2 * TS - 1) / (2 * TS))), TS, smt, c->stream>>>(
+                c->na, N, K, umax, ucount, uat, ublk, (const double*)c->d_Sblk.p, Cm, (double*)c->d_cpl_T.p);
+        } else
 #define XTB_SPMM(NO, XT) { XTB_CUDA(c, cudaFuncSetAttribute(spmm_blocks_kernel<NO, XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
         spmm_blocks_kernel<NO, XT><<<grid, ST, smem, c->stream>>>(c->na, N, K, c->cap, (const int*)c->d_nn_size.p, (const int*)c->d_nn_list.p, \
                                                                   (const int*)c->d_rowptr.p, (const double*)c->d_Sblk.p, Cm, (double*)c->d_cpl_T.p); }
+        {
         if (c->n_orb == 9) { if (xt) XTB_SPMM(9, true) else XTB_SPMM(9, false) }
         else if (c->n_orb == 4) { if (xt) XTB_SPMM(4, true) else XTB_SPMM(4, false) }
         else { if (xt) XTB_SPMM(1, true) else XTB_SPMM(1, false) }
+        }
 #undef XTB_SPMM
         XTB_LAUNCH_CHECK(c);
         Tm = (const double*)c->d_cpl_T.p;

@@ -176,7 +176,7 @@ int xtb_destroy(xtb_ctx* c) {
                      &c->d_rowptr, &c->d_maxnn, &c->d_dens, &c->d_onsite_w, &c->d_Hblk, &c->d_Sblk, &c->d_H, &c->d_S2, &c->own_Ha,
                      &c->own_Ei, &c->own_fe, &c->own_HaT, &c->d_tmap, &c->d_keep, &c->d_wf, &c->d_wfe, &c->d_Ct, &c->d_nkeep, &c->d_rho, &c->d_rhoE, &c->d_F,
                      &c->d_SC, &c->d_scratch, &c->d_hdev, &c->d_ppart, &c->d_fpair, &c->d_tab, &c->d_dftb_tab, &c->d_prog, &c->d_eig_work, &c->d_eig_X, &c->d_eig_T, &c->d_eigS,
-                     &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep,
+                     &c->d_ctneed, &c->d_units, &c->d_pairw, &c->d_Ha0, &c->d_cpl_T, &c->d_cpl_M, &c->d_cpl_inv, &c->d_cpl_union, &c->d_rep_params, &c->d_Epot, &c->d_dfpsi, &c->d_Erep, &c->d_Frep, &c->d_SCrep,
                      &c->d_halo_tr, &c->d_halo_cnt, &c->d_halo_slots, &c->d_halo_send, &c->d_halo_recv, &c->d_wall_params, &c->d_Ewall_at, &c->d_Ewall,
                      &c->d_Fwall, &c->d_SCwall, &c->d_prev_size, &c->d_prev_list, &c->d_dense_out, &c->d_fermi, &c->d_S0, &c->d_SV, &c->d_SV0, &c->d_mdpar,
                      &c->d_vdw_params, &c->d_Evdw_at, &c->d_Evdw, &c->d_Fvdw, &c->d_SCvdw,

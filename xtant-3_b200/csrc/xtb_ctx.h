@@ -135,7 +135,7 @@ struct xtb_ctx {
     DevBuf d_S0, d_SV, d_SV0, d_mdpar;
     bool have_md = false;
     // nonadiabatic coupling (coupling.cu): eigenvectors of the previous step, T = S Ha, G -> Mij, inverse column norms
-    DevBuf d_Ha0, d_cpl_T, d_cpl_M, d_cpl_inv;
+    DevBuf d_Ha0, d_cpl_T, d_cpl_M, d_cpl_inv, d_cpl_union;
     bool have_Ha0 = false;
     // multi-GPU (comm.cu): NCCL communicator bound at run time, halo transfer lists of the current neighbour list
     void* comm = nullptr;
