@@ -219,3 +219,38 @@ def test_single_image_rule_reproduces_the_27_image_scan(orc, wk, name):
         assert np.array_equal(js, nb.list[i, :m])
         assert np.array_equal(x[i, js], nb.dist[i, :m, :3]) and np.array_equal(r[i, js], nb.dist[i, :m, 3])
         assert np.array_equal(best[i, js], nb.dist_s[i, :m])
+
+
+def test_reference_block_derivative_symmetries_behind_the_pair_once_kernels(orc):
+    """The device force / supercell-force kernels evaluate every unordered pair once and hand the partner atom the negated
+    (forces) or the equal (supercell force) value.  That rests on two exact symmetries of the REFERENCE's own derivative
+    routines (d_KS_sp3d5 and the d_t_* functions, restated term by term in the oracle), checked here bit for bit:
+      (A) oddness in the differentials: d_KS(V, -dV, lmn, -d lmn) = -d_KS(V, dV, lmn, d lmn) -- the partner's delta is -delta;
+      (B) inversion: d_KS(V, dV, -lmn, -d lmn)(a, b) = (-1)^(l_a + l_b) d_KS(V, dV, lmn, d lmn)(a, b) -- the directed pair (j, i)
+          sees the negated direction cosines, and contracted with the transposed density block gives the same number.
+    Both hold for the quirk entry (dxz, dx2-y2) of TB_Koster_Slater.f90:839-853 as well, and for the _TEST variant."""
+    rng = np.random.default_rng(123)
+    ell = np.array([0, 1, 1, 1, 2, 2, 2, 2, 2])
+    sign = (-1.0) ** (ell[:, None] + ell[None, :])
+    for trial in range(20):
+        V = rng.normal(size=10); dV = rng.normal(size=10)
+        d = rng.normal(size=3); d /= np.linalg.norm(d)
+        dd = rng.normal(size=3)
+        for tv in (False, True):
+            D = orc.dks_block(V, dV, *d, *dd, test_variant=tv)
+            assert np.abs(D).max() > 0
+            Dneg = orc.dks_block(V, -dV, *d, *(-dd), test_variant=tv)
+            assert np.array_equal(Dneg, -D)                                    # (A)
+            Dinv = orc.dks_block(V, dV, *(-d), *(-dd), test_variant=tv)
+            assert np.array_equal(Dinv, sign * D)                              # (B)
+            # (B) as the supercell-force kernel uses it: the block of the directed pair (j, i) -- rows j, columns i -- is the
+            # transpose of d_KS at the inverted direction; contracted with rho(j, i) = rho(i, j)^T it repeats, term by term,
+            # the products of the pair (i, j) up to the exact factor sign^2 = 1
+            A = rng.normal(size=(9, 9))                                        # stands for rho(i, j)
+            terms_ij = D * A
+            terms_ji = (Dinv.T * A.T).T                                        # element (a, b): Dinv(a, b) * A(a, b)
+            assert np.array_equal(terms_ji, sign * terms_ij)
+    # the value block has the same inversion symmetry (the two H/S blocks of a pair are transposes of one computed block)
+    V = rng.normal(size=10); d = rng.normal(size=3); d /= np.linalg.norm(d)
+    B = orc.ks_block(V, *d)
+    assert np.array_equal(orc.ks_block(V, *(-d)), sign * B)
