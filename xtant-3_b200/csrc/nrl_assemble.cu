@@ -10,10 +10,13 @@
 //   k2  nrl_blocks_kernel  one thread per (unordered pair, matrix): radial functions in registers, SK rotation in
 //                          registers, 81 entries to the block-sparse store Hblk/Sblk (block (j,q) holds
 //                          rows of neighbour i, columns of outer atom j -- the reference placement) and their
-//                          transpose to the partner's block
-//   k3  dense_panel_kernel one CTA per owned atom j: writes the 9 dense columns of j for H and S, every
-//                          element exactly once (zeros included), fully coalesced streaming stores.
-//                          Algorithmic bytes = 2*8*N*(9*n_owned): the HBM-write roofline of this stage.
+//                          transpose to the partner's block; on one rank also the same values into the
+//                          RESIDENT dense H_non / Sij (xtb_dense_update prepares: dense_zero_prev_kernel clears
+//                          the blocks the new pattern drops, dense_remember_kernel records the pattern)
+//   k3  dense_scatter_kernel  the dense values from the block stores (other branches, panels of other ranks,
+//                          XTB_DENSE_FUSED=0); dense_panel_kernel (XTB_DENSE_FULL=1): one CTA per owned atom j
+//                          writes the 9 dense columns of j for H and S, every element exactly once (zeros
+//                          included), streaming stores: 2*8*N*(9*n_owned) bytes at 0.87 of the HBM roofline.
 // Semantics kept: pair (a>b) evaluated once with TB(kind(b),kind(a)) and r from the list of b (:2151-2159);
 // block (rows a, cols b) uses the direction cosines of a's list entry for b (M_lmn(:,a,b), :1849);
 // the other triangle is the element transpose (:369-390); |S| <= 1e-12 -> 0 (:359); H *= g_Ry (:394).
