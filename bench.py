@@ -458,6 +458,13 @@ def small_configs(torch, api, abi, wk, reps=40):
             if wl.get("vdw_params"):
                 res["vdw_ms"] = c.stage_ms(17) if c.stage_ms(17) > 0 else None      # eager legs only: no events inside a graph
             res["graphs_captured"] = c.counter(16)
+            try:      # BASELINE.json's second metric at this atom count: pair-blocks/s of the assembly stage (one staged pass, device-timed)
+                staged(); c.sync()
+                t2 = c.stage_ms(2)
+                res["n_blocks"] = int(c.counter(4)); res["assembly_ms"] = t2
+                res["pair_blocks_per_s"] = c.counter(4) / (t2 * 1e-3) if t2 > 0 else None
+            except Exception:
+                pass
             out[name] = res
         except Exception as ex:      # a parity-test case must not take the headline line down
             out[name] = {"error": str(ex)[:200]}
